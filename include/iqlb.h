@@ -1,0 +1,195 @@
+/*
+ * iqlb.h - C ABI of libiqlb.so, the B200 (sm_100a) implementation of the IQL hot path of
+ * ml4ai/iqlpref: replay sampling, the fused IQL update over N independent agents, the Polyak
+ * target update and the reward-model relabelling pass.
+ *
+ * The reference is pure Python/PyTorch and has no native boundary; each entry point below
+ * names the reference interface (file:line under /root/reference) it replaces.  INTEGRATION.md
+ * shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions: every function returns 0 on success and a negative iqlb_status on failure and
+ * never throws; iqlb_last_error() gives the thread-local message.  All pointers are DEVICE
+ * pointers unless the parameter name starts with `host_`.  `stream` is a cudaStream_t passed as
+ * void* (NULL = legacy default stream).  Nothing synchronises the host unless stated.  Buffers
+ * are borrowed for the duration of the call (or, for iqlb_agents_create, until destroy).
+ */
+#ifndef IQLB_H_
+#define IQLB_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IQLB_VERSION 100
+
+typedef enum {
+  IQLB_OK = 0,
+  IQLB_ERR_INVALID = -1,   /* bad argument (the reference raises ValueError/RuntimeError) */
+  IQLB_ERR_CUDA = -2,      /* CUDA runtime error, see iqlb_last_error() */
+  IQLB_ERR_UNSUPPORTED = -3,
+  IQLB_ERR_NOMEM = -4
+} iqlb_status;
+
+int iqlb_version(void);
+const char* iqlb_last_error(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * (1) Replay buffer.  Replaces ReplayBuffer.sample (algorithms/offline/iql.py:211-221):
+ *     torch.randint (Philox4x32-10, ATen DistributionTemplates.h:66-90,319-345) + 5 gathers.
+ *
+ * The table is ONE packed fp32 matrix [n_rows, row_stride]; a row is
+ *     [ obs(S) | act(A) | next_obs(S) | reward | done | zero pad ]   (row_stride % 4 == 0)
+ * so that [obs|act] is the contiguous twin-Q input and a row moves as 128-bit vectors.
+ * --------------------------------------------------------------------------------------------- */
+
+/* idx_out[b] = Philox(seed, subsequence=b, offset).x % n_rows  (bit-exact with
+ * torch.randint(0, n_rows, (batch,), device="cuda") for a generator at (seed, offset)). */
+int iqlb_philox_randint(uint64_t seed, uint64_t offset, int64_t n_rows, int32_t batch,
+                        int64_t* idx_out, void* stream);
+
+/* For each agent a: draw `batch` indices from (rng[a][0]=seed, rng[a][1]=offset), copy the rows
+ * to batch_out[a, b, :], optionally replacing the reward column by
+ * reward_cols[reward_variant[a], idx] (sweeps whose agents differ only in the reward labels).
+ * idx_out (nullable) receives the indices [n_agents, batch].  Does NOT advance rng. */
+int iqlb_replay_sample(const float* table, int64_t n_rows, int32_t row_stride, int32_t reward_col,
+                       const float* reward_cols, const int32_t* reward_variant,
+                       const uint64_t* rng, int32_t n_agents, int32_t batch,
+                       int64_t* idx_out, float* batch_out, void* stream);
+
+/* Same gather with caller-supplied indices idx[n_agents, batch]. */
+int iqlb_replay_gather(const float* table, int64_t n_rows, int32_t row_stride, int32_t reward_col,
+                       const float* reward_cols, const int32_t* reward_variant,
+                       const int64_t* idx, int32_t n_agents, int32_t batch,
+                       float* batch_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (2)-(4) The IQL update for N independent agents.  Replaces ImplicitQLearning.train
+ * (iql.py:639-662): _update_v (:581-593), _update_q (:595-613) incl. soft_update (:127-129),
+ * _update_policy (:615-637), three torch.optim.Adam steps and CosineAnnealingLR.step.
+ *
+ * Parameter packing (fp32, per agent, nn.Linear layout W[out,in] row-major then b[out]):
+ *   Q1: W0[H,S+A] b0[H] W1[H,H] b1[H] W2[1,H] b2[1] | Q2: same | V: W0[H,S] ... W2[1,H] b2[1]
+ *   | actor: W0[H,S] b0 W1 b1 W2[A,H] b2[A] | log_std[A] (Gaussian policy only)
+ * iqlb_param_count() gives P (all) and PQ (Q1+Q2, = target size).
+ * --------------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t n_agents;
+  int32_t state_dim;
+  int32_t action_dim;
+  int32_t hidden_dim;    /* 2 hidden layers of this width (iql.py:458-459,519,537) */
+  int32_t batch_size;
+  int32_t deterministic; /* 1: DeterministicPolicy (iql.py:485-504), 0: GaussianPolicy (:452-474) */
+  int32_t row_stride;    /* floats per packed replay row */
+  int32_t precision;     /* 0: fp32 FFMA (parity mode, 1e-3 vs fp32 oracle); 1: bf16 tcgen05 */
+} iqlb_agents_desc;
+
+/* per-agent hyper-parameters, float32[n_agents][8]:
+ *   0 discount  1 tau(polyak)  2 beta  3 iql_tau  4 vf_lr  5 qf_lr  6 actor_lr(base)  7 max_steps */
+#define IQLB_HP_STRIDE 8
+
+typedef struct iqlb_agents iqlb_agents;
+
+int iqlb_param_count(int32_t state_dim, int32_t action_dim, int32_t hidden_dim, int32_t deterministic,
+                     int64_t* p_all, int64_t* p_q);
+
+/* All arrays are caller-owned device memory that must outlive the handle:
+ *   params, exp_avg, exp_avg_sq : float[n_agents][P]      target : float[n_agents][PQ]
+ *   hparams : float[n_agents][8]
+ *   it      : int64[n_agents]   (ImplicitQLearning.total_it == every Adam `step`)
+ *   actor_lr: double[n_agents]  (current CosineAnnealingLR value, recursive form)
+ *   rng     : uint64[n_agents][2] (seed, philox offset); offset advances by 4 per sampled step
+ *   losses  : float[n_agents][3] (value_loss, q_loss, actor_loss of the last step)
+ *   loss_sum: float[n_agents][3] (running sum; the host divides by log_freq and zeroes it) */
+int iqlb_agents_create(const iqlb_agents_desc* desc, float* params, float* exp_avg, float* exp_avg_sq,
+                       float* target, const float* hparams, int64_t* it, double* actor_lr,
+                       uint64_t* rng, float* losses, float* loss_sum, iqlb_agents** out);
+int iqlb_agents_destroy(iqlb_agents* h);
+
+/* Attach the replay table the on-device sampler reads (see (1)).  idx_out nullable. */
+int iqlb_agents_set_replay(iqlb_agents* h, const float* table, int64_t n_rows,
+                           const float* reward_cols, const int32_t* reward_variant, int64_t* idx_out);
+
+/* One update of every agent.  batch == NULL: sample on device from the attached table and
+ * advance rng; otherwise use the packed rows batch[n_agents][batch_size][row_stride]. */
+int iqlb_agents_step(iqlb_agents* h, const float* batch, void* stream);
+
+/* Same, with the batch in (pinned) HOST memory: H2D copy of the rows, the update, D2H copy of
+ * losses[n_agents][3] into host_losses, then a stream synchronise (the reference's .item()). */
+int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_losses, void* stream);
+
+/* Number of kernels one iqlb_agents_step enqueues (for launch accounting). */
+int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled);
+
+/* Debug/parity hook: copy an internal scratch tensor to dst (device).  which: 0 H1, 1 H2,
+ * 2 head_out, 3 d_out, 4 dH2, 5 dH1, 6 grads, 7 batch.  Returns bytes via *nbytes if dst NULL. */
+int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, int64_t* nbytes, void* stream);
+
+/* (4) Stand-alone soft_update (iql.py:127-129): target += tau * (source - target), n floats. */
+int iqlb_polyak(float* target, const float* source, int64_t n, float tau, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (5) Relabelling.  Replaces the reward-model forward + reduction inside
+ * qlearning_dataset_mr (iql.py:719-724), qlearning_dataset_bnn (:982-1011),
+ * qlearning_dataset_mr_ensemble (:1162-1187) and qlearning_dataset_pt (:1259-1301).
+ * --------------------------------------------------------------------------------------------- */
+
+/* activation ids of RewardMLP (optbnn/bnn/nets/mlp.py:45-48) */
+enum { IQLB_ACT_RELU = 0, IQLB_ACT_TANH, IQLB_ACT_COS, IQLB_ACT_SIN, IQLB_ACT_LINEAR, IQLB_ACT_RBF,
+       IQLB_ACT_SWISH, IQLB_ACT_SOFTPLUS, IQLB_ACT_LEAKY_RELU };
+
+/* Ensemble of S reward MLPs (scaled-variance Linear, optbnn/bnn/layers/linear.py:43-47) over the
+ * rows x[n_rows][d_in] (row stride ldx floats), reduced per row to the mean of the n_tail
+ * smallest member predictions (n_tail == S: plain mean; S == 1: the single model).
+ *   weights : float[S][PM], member layout W0[d_in][w0] b0[w0] W1[w0][w1] b1 ... Wout[w_last][1] bout[1]
+ *             (W stored (n_in, n_out) exactly as the reference's state_dict / BNN tuples)
+ *   widths  : host int32[depth] hidden widths
+ *   out     : float[n_rows]
+ *   preds_out (nullable): float[S][n_rows] all member predictions (the reference's all_preds)
+ *   sel_out (nullable)  : uint8[S][n_rows] 1 where member s is in the tail set of row i */
+int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in,
+                     const float* weights, int32_t n_members, const int32_t* host_widths, int32_t depth,
+                     int32_t activation, int32_t n_tail, float* out, float* preds_out, uint8_t* sel_out,
+                     void* stream);
+
+/* Preference transformer (optbnn/bnn/nets/pref_trans.py:230-325) evaluated on the windows that
+ * qlearning_dataset_pt builds (iql.py:1264-1292) and reduced to value[:,0,-1,0].
+ *   obs[n_data][S], act[n_data][A]      : the dataset
+ *   win_start[n], seq_len[n] (int32)    : window i covers rows win_start[i] .. +seq_len[i]-1,
+ *                                         left-padded to query_len; timesteps 0..seq_len-1
+ *   weights: packed fp32, layout given by iqlb_pt_param_count / DESIGN.md
+ *   out[n] */
+typedef struct {
+  int32_t state_dim, action_dim, embd_dim, num_heads, intermediate_dim, num_layers;
+  int32_t pref_dim;        /* pref_attn_embd_dim (only the value column of pref_linear is used) */
+  int32_t n_timesteps;     /* rows of timestep_embed = max_episode_steps + 1 */
+  int32_t query_len;
+  float eps;               /* LayerNorm eps (model_eps) */
+} iqlb_pt_desc;
+
+int iqlb_pt_param_count(const iqlb_pt_desc* d, int64_t* n_floats);
+int iqlb_relabel_pt(const iqlb_pt_desc* d, const float* weights, const float* obs, const float* act,
+                    int64_t n_data, const int32_t* win_start, const int32_t* seq_len, int64_t n,
+                    float* out, void* stream);
+
+/* RewardPT.forward on explicit windows (pref_trans.py:269-325; what the relabel loop calls at
+ * iql.py:1294-1299): states[n][T][S], actions[n][T][A], timesteps int32[n][T], attn_mask[n][T]
+ * -> value_out[n][T] (= result["value"][:, 0, :, 0]); T = d->query_len. */
+int iqlb_pt_forward(const iqlb_pt_desc* d, const float* weights, const float* states, const float* actions,
+                    const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Host helper (plain C loop, no GPU): the keep-mask / episode-step scan every qlearning_dataset_*
+ * starts with (iql.py:701-716, 1236-1253).  terminals/timeouts are host uint8[n]; timeouts may be
+ * NULL (then `final` is ep == max_episode_steps - 1).  Writes host_keep[n-1], host_ep_steps[n-1]
+ * (either may be NULL).
+ * --------------------------------------------------------------------------------------------- */
+int iqlb_keep_mask_scan(const uint8_t* host_terminals, const uint8_t* host_timeouts, int64_t n,
+                        int32_t max_episode_steps, int32_t terminate_on_end, uint8_t* host_keep,
+                        int32_t* host_ep_steps);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IQLB_H_ */

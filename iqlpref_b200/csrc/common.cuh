@@ -1,0 +1,96 @@
+// Shared helpers for libiqlb: error plumbing, Philox4x32-10, warp/block reductions.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/iqlb.h"
+
+namespace iqlb {
+
+extern thread_local char g_err[512];
+
+inline int fail(int code, const char* fmt, const char* a = "", long long b = 0) {
+  snprintf(g_err, sizeof(g_err), fmt, a, b);
+  return code;
+}
+
+#define IQLB_CUDA(expr)                                                                     \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess) {                                                               \
+      snprintf(iqlb::g_err, sizeof(iqlb::g_err), "%s failed: %s (%s:%d)", #expr,            \
+               cudaGetErrorString(e__), __FILE__, __LINE__);                                \
+      return IQLB_ERR_CUDA;                                                                 \
+    }                                                                                       \
+  } while (0)
+
+#define IQLB_LAUNCH_CHECK() IQLB_CUDA(cudaGetLastError())
+
+#define IQLB_REQUIRE(cond, msg)                                                             \
+  do {                                                                                      \
+    if (!(cond)) {                                                                          \
+      snprintf(iqlb::g_err, sizeof(iqlb::g_err), "invalid argument: %s (%s)", msg, #cond);  \
+      return IQLB_ERR_INVALID;                                                              \
+    }                                                                                       \
+  } while (0)
+
+// ---- Philox4x32-10 exactly as cuRAND's curand_Philox4x32_10 (curand_philox4x32_x.h) ----------
+__host__ __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#ifdef __CUDA_ARCH__
+  uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+#else
+  uint64_t p0 = (uint64_t)0xD2511F53u * c[0], p1 = (uint64_t)0xCD9E8D57u * c[2];
+  uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0, hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+#endif
+  uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+
+// First curand4() of curand_init(seed, subsequence, offset) with offset % 4 == 0.
+__host__ __device__ __forceinline__ void philox4(uint64_t seed, uint64_t subsequence, uint64_t offset,
+                                                 uint32_t (&out)[4]) {
+  uint64_t blk = offset >> 2;
+  uint32_t c[4] = {(uint32_t)blk, (uint32_t)(blk >> 32), (uint32_t)subsequence, (uint32_t)(subsequence >> 32)};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+}
+
+// torch.randint on CUDA (DistributionTemplates.h:319-345): 32-bit path below 2^28.
+__host__ __device__ __forceinline__ int64_t randint_from_philox(const uint32_t (&r)[4], uint64_t range) {
+  if (range >= (1ull << 28)) {
+    uint64_t v = ((uint64_t)r[0] << 32) | r[1];
+    return (int64_t)(v % range);
+  }
+  return (int64_t)(r[0] % (uint32_t)range);
+}
+
+// ---- reductions -----------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Deterministic block sum (fixed order); blockDim.x multiple of 32, <= 1024.  All threads get it.
+__device__ __forceinline__ float block_sum(float v, float* smem32) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) smem32[w] = v;
+  __syncthreads();
+  float t = (lane < nw) ? smem32[lane] : 0.f;
+  t = warp_sum(t);
+  return t;
+}
+
+}  // namespace iqlb

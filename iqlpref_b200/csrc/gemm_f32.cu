@@ -1,0 +1,174 @@
+// Grouped fp32 FFMA GEMM (parity mode).  One launch covers one layer of every (agent, network)
+// pair: blockIdx.y = task, blockIdx.x = output tile.  Three operand arrangements:
+//   FWD        C[m,n] = relu(sum_k A[m,k] * W[n,k] + bias[n])        (nn.Linear forward)
+//   BWD_DATA   C[m,n] = mask[m,n] > 0 ? sum_k A[m,k] * W[k,n] : 0     (dX = dY W, through ReLU)
+//   BWD_WEIGHT C[m,n] = sum_k A[k,m] * X[k,n];  bias_grad[m] = sum_k A[k,m]   (dW = dY^T X, db)
+//   FWD_KN     C[m,n] = act(scale * sum_k A[m,k] * W[k,n] + bias[n])   (RewardMLP scaled Linear)
+// 128 x BN tile, BK = 8, 256 threads, 8 x TN outputs per thread, register-prefetched.
+#include "iql_step.cuh"
+
+namespace iqlb {
+
+__device__ __forceinline__ float apply_act(int act, float x) {
+  switch (act) {
+    case IQLB_ACT_RELU: return x > 0.f ? x : 0.f;
+    case IQLB_ACT_TANH: return tanhf(x);
+    case IQLB_ACT_COS: return cosf(x);
+    case IQLB_ACT_SIN: return sinf(x);
+    case IQLB_ACT_LINEAR: return x;
+    case IQLB_ACT_RBF: return expf(-x * x);
+    case IQLB_ACT_SWISH: return x * (1.0f / (1.0f + expf(-x)));
+    case IQLB_ACT_SOFTPLUS: return x > 20.f ? x : log1pf(expf(x));
+    case IQLB_ACT_LEAKY_RELU: return x > 0.f ? x : 0.01f * x;
+    default: return x;
+  }
+}
+
+constexpr int BM = 128;
+constexpr int BK = 8;
+constexpr int TM = 8;
+
+// element (r, k) of an operand tile: KC = k contiguous (ptr[r*ld+k]), RC = r contiguous (ptr[k*ld+r])
+template <bool KC, int ROWS>
+__device__ __forceinline__ void load_tile(const float* __restrict__ p, int ld, int r0, int rmax, int k0, int kmax,
+                                          float (&reg)[ROWS * BK / 256]) {
+  constexpr int PER = ROWS * BK / 256;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int e = threadIdx.x + i * 256;
+    int r, k;
+    if (KC) { r = e / BK; k = e % BK; } else { k = e / ROWS; r = e % ROWS; }
+    const int gr = r0 + r, gk = k0 + k;
+    float v = 0.f;
+    if (gr < rmax && gk < kmax) v = KC ? __ldg(p + (int64_t)gr * ld + gk) : __ldg(p + (int64_t)gk * ld + gr);
+    reg[i] = v;
+  }
+}
+
+template <bool KC, int ROWS>
+__device__ __forceinline__ void store_tile(float (*s)[ROWS + 4], const float (&reg)[ROWS * BK / 256]) {
+  constexpr int PER = ROWS * BK / 256;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int e = threadIdx.x + i * 256;
+    int r, k;
+    if (KC) { r = e / BK; k = e % BK; } else { k = e / ROWS; r = e % ROWS; }
+    s[k][r] = reg[i];
+  }
+}
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(256) grouped_gemm_kernel(const GemmTask* __restrict__ tasks) {
+  constexpr int TN = BN / 16;
+  constexpr bool A_KC = (MODE != GEMM_BWD_WEIGHT);
+  constexpr bool B_KC = (MODE == GEMM_FWD);
+  const GemmTask t = tasks[blockIdx.y];
+  const int tiles_n = (t.N + BN - 1) / BN;
+  const int tiles_m = (t.M + BM - 1) / BM;
+  if ((int)blockIdx.x >= tiles_m * tiles_n) return;
+  const int tm = blockIdx.x / tiles_n, tn = blockIdx.x % tiles_n;
+  const int m0 = tm * BM, n0 = tn * BN;
+
+  __shared__ __align__(16) float As[BK][BM + 4];
+  __shared__ __align__(16) float Bs[BK][BN + 4];
+
+  const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+  float asum[TM];
+#pragma unroll
+  for (int i = 0; i < TM; ++i) asum[i] = 0.f;
+
+  float ra[BM * BK / 256], rb[BN * BK / 256];
+  load_tile<A_KC, BM>(t.A, t.lda, m0, t.M, 0, t.K, ra);
+  load_tile<B_KC, BN>(t.Bm, t.ldb, n0, t.N, 0, t.K, rb);
+  const bool want_bsum = (MODE == GEMM_BWD_WEIGHT) && tn == 0 && t.bias_grad != nullptr;
+
+  for (int k0 = 0; k0 < t.K; k0 += BK) {
+    store_tile<A_KC, BM>(As, ra);
+    store_tile<B_KC, BN>(Bs, rb);
+    __syncthreads();
+    if (k0 + BK < t.K) {
+      load_tile<A_KC, BM>(t.A, t.lda, m0, t.M, k0 + BK, t.K, ra);
+      load_tile<B_KC, BN>(t.Bm, t.ldb, n0, t.N, k0 + BK, t.K, rb);
+    }
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float a[TM], b[TN];
+      // rows ty*4..+3 and 64+ty*4..+3: two conflict-free 128-bit reads
+      *(float4*)&a[0] = *(const float4*)&As[k][ty * 4];
+      *(float4*)&a[4] = *(const float4*)&As[k][BM / 2 + ty * 4];
+      if constexpr (TN == 8) {
+        *(float4*)&b[0] = *(const float4*)&Bs[k][tx * 4];
+        *(float4*)&b[4] = *(const float4*)&Bs[k][BN / 2 + tx * 4];
+      } else if constexpr (TN == 4) {
+        *(float4*)&b[0] = *(const float4*)&Bs[k][tx * 4];
+      } else {
+#pragma unroll
+        for (int j = 0; j < TN; ++j) b[j] = Bs[k][tx * TN + j];
+      }
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      if constexpr (MODE == GEMM_BWD_WEIGHT) {
+#pragma unroll
+        for (int i = 0; i < TM; ++i) asum[i] += a[i];
+      }
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + (i < 4 ? ty * 4 + i : BM / 2 + ty * 4 + (i - 4));
+    if (m >= t.M) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      int n;
+      if (TN == 8) n = n0 + (j < 4 ? tx * 4 + j : BN / 2 + tx * 4 + (j - 4));
+      else n = n0 + tx * TN + j;
+      if (n >= t.N) continue;
+      float v = acc[i][j];
+      if (MODE == GEMM_FWD) {
+        v += __ldg(t.bias + n);
+        v = v > 0.f ? v : 0.f;
+      } else if (MODE == GEMM_BWD_DATA) {
+        v = (__ldg(t.mask + (int64_t)m * t.ldc + n) > 0.f) ? v : 0.f;
+      } else if (MODE == GEMM_FWD_KN) {
+        v = apply_act(t.act, fmaf(t.scale, v, __ldg(t.bias + n)));
+      }
+      t.C[(int64_t)m * t.ldc + n] = v;
+    }
+    if (want_bsum && tx == 0) t.bias_grad[m] = asum[i];
+  }
+}
+
+template <int MODE>
+static int launch_mode(const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n, cudaStream_t stream) {
+  const int tiles_m = (maxM + BM - 1) / BM;
+  if (narrow_n) {
+    dim3 grid((unsigned)(tiles_m * ((maxN + 31) / 32)), (unsigned)n_tasks);
+    grouped_gemm_kernel<MODE, 32><<<grid, 256, 0, stream>>>(d_tasks);
+  } else {
+    dim3 grid((unsigned)(tiles_m * ((maxN + 127) / 128)), (unsigned)n_tasks);
+    grouped_gemm_kernel<MODE, 128><<<grid, 256, 0, stream>>>(d_tasks);
+  }
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
+                        cudaStream_t stream) {
+  switch (mode) {
+    case GEMM_FWD: return launch_mode<GEMM_FWD>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
+    case GEMM_BWD_DATA: return launch_mode<GEMM_BWD_DATA>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
+    case GEMM_FWD_KN: return launch_mode<GEMM_FWD_KN>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
+    default: return launch_mode<GEMM_BWD_WEIGHT>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
+  }
+}
+
+}  // namespace iqlb

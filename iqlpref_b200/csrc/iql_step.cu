@@ -1,0 +1,485 @@
+// The IQL update for N independent agents (fp32 parity path + orchestration).
+// Replaces ImplicitQLearning.train (/root/reference/algorithms/offline/iql.py:639-662).
+//
+// Launch sequence of one step (every launch covers ALL agents):
+//   gather -> fwd L0 (7 streams) -> fwd L1 -> heads fwd -> losses + output grads + bookkeeping
+//   -> heads bwd -> bwd L1 weights -> bwd L1 data -> bwd L0 weights -> Adam + Polyak
+// Data dependences follow SURVEY.md 3.2: every forward reads start-of-step parameters; only the
+// Polyak update must see the post-Adam Q parameters, so it is fused into the Adam kernel.
+#include <new>
+
+#include "iql_step.cuh"
+
+namespace iqlb {
+
+int launch_gather(const float* table, int64_t n_rows, int row_stride, int reward_col, const float* reward_cols,
+                  const int32_t* reward_variant, const uint64_t* rng, const int64_t* idx_in, int n_agents, int batch,
+                  int64_t* idx_out, float* batch_out, cudaStream_t stream);
+int bf16_create(iqlb_agents* h);
+void bf16_destroy(iqlb_agents* h);
+int bf16_step_gemms_fwd(iqlb_agents* h, cudaStream_t stream);
+int bf16_step_gemms_bwd(iqlb_agents* h, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------
+// Heads forward: out[o] = H2[b,:] . W2[o,:] + b2[o]   (N = 1 for V/Q, N = A (+tanh) for actor)
+// One warp per (stream, batch row); lanes stride the hidden dimension, warp-shuffle reduce.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) head_fwd_kernel(Layout L, const float* __restrict__ params,
+                                                       const float* __restrict__ target,
+                                                       const float* __restrict__ H2, float* __restrict__ head_out) {
+  const int agent = blockIdx.z, s = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 8 + warp;
+  if (b >= L.B) return;
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const float* base = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
+                                       : params + (int64_t)agent * L.Pstride + L.net_off(s);
+  const float* W2 = base + L.w2(in);
+  const float* b2 = base + L.b2(in, nout);
+  const float* h = H2 + (((int64_t)agent * kStreams + s) * L.B + b) * L.H;
+  float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
+  for (int o = 0; o < nout; ++o) {
+    float acc = 0.f;
+    for (int j = lane; j < L.H; j += 32) acc = fmaf(h[j], __ldg(W2 + (int64_t)o * L.H + j), acc);
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      float v = acc + __ldg(b2 + o);
+      if (s == 6) ho[(int64_t)(6 + o) * L.B + b] = tanhf(v);
+      else ho[(int64_t)s * L.B + b] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Losses, output gradients and per-agent bookkeeping.  One CTA per agent, one thread per row.
+//   value_loss (iql.py:404-405,587-588), q_loss (:604-606), actor_loss (:622-632)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double cosine_next(double lr, double base_lr, long long epoch, long long t_max) {
+  const double kPi = 3.14159265358979323846;
+  if ((epoch - 1 - t_max) % (2 * t_max) == 0) return lr + base_lr * (1.0 - cos(kPi / (double)t_max)) / 2.0;
+  return (1.0 + cos(kPi * (double)epoch / (double)t_max)) / (1.0 + cos(kPi * (double)(epoch - 1) / (double)t_max)) * lr;
+}
+
+__global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __restrict__ params, const float* __restrict__ hparams,
+                            const float* __restrict__ batch, const float* __restrict__ head_out,
+                            float* __restrict__ d_out, float* __restrict__ grads, float* __restrict__ losses,
+                            float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
+                            uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng) {
+  __shared__ float red[32];
+  const int agent = blockIdx.x, b = threadIdx.x;
+  const bool live = b < L.B;
+  const float* hp = hparams + agent * IQLB_HP_STRIDE;
+  const float discount = hp[0], beta = hp[2], iql_tau = hp[3];
+  const float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
+  float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
+  const float* row = batch + ((int64_t)agent * L.B + (live ? b : 0)) * L.R;
+  const float invB = 1.0f / (float)L.B;
+
+  float vl = 0.f, ql = 0.f, al = 0.f, w = 0.f;
+  if (live) {
+    const float nv = ho[0 * L.B + b], v = ho[1 * L.B + b];
+    const float tq = fminf(ho[2 * L.B + b], ho[3 * L.B + b]);
+    const float q1 = ho[4 * L.B + b], q2 = ho[5 * L.B + b];
+    const float rew = row[2 * L.S + L.A], done = row[2 * L.S + L.A + 1];
+    const float adv = tq - v;
+    const float wt = adv < 0.f ? fabsf(iql_tau - 1.0f) : fabsf(iql_tau);
+    vl = wt * (adv * adv);
+    dout[0 * L.B + b] = -2.0f * wt * adv * invB;
+    const float y = rew + (1.0f - done) * discount * nv;
+    const float e1 = q1 - y, e2 = q2 - y;
+    ql = e1 * e1 + e2 * e2;
+    dout[1 * L.B + b] = e1 * invB;
+    dout[2 * L.B + b] = e2 * invB;
+    w = fminf(expf(beta * adv), 100.0f);
+  }
+  // actor: per-action terms; log_std gradient needs a block reduction per action
+  const float* log_std = params + (int64_t)agent * L.Pstride + L.off_logstd;
+  float* g_log_std = grads + (int64_t)agent * L.Pstride + L.off_logstd;
+  float bc = 0.f;
+  for (int a = 0; a < L.A; ++a) {
+    float gls = 0.f;
+    if (live) {
+      const float mu = ho[(int64_t)(6 + a) * L.B + b];
+      const float act = row[L.S + a];
+      const float diff = mu - act;
+      float dmu;
+      if (L.deterministic) {
+        bc += diff * diff;
+        dmu = 2.0f * w * diff * invB;
+      } else {
+        const float ls_raw = log_std[a];
+        const float ls = fminf(fmaxf(ls_raw, -20.0f), 2.0f);
+        const float sigma = expf(ls);
+        const float inv_var = 1.0f / (sigma * sigma);
+        bc += 0.5f * diff * diff * inv_var + ls + 0.91893853320467274178f;
+        dmu = w * diff * inv_var * invB;
+        gls = (ls_raw >= -20.0f && ls_raw <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
+      }
+      dout[(int64_t)(3 + a) * L.B + b] = dmu * (1.0f - mu * mu);
+    }
+    if (!L.deterministic) {
+      const float tot = block_sum(gls, red);
+      if (b == 0) g_log_std[a] = tot;
+    }
+  }
+  al = w * bc;
+  const float vls = block_sum(vl, red);
+  const float qls = block_sum(ql, red);
+  const float als = block_sum(al, red);
+  if (b == 0) {
+    const float value_loss = vls * invB, q_loss = qls * invB * 0.5f, actor_loss = als * invB;
+    losses[agent * 3 + 0] = value_loss;
+    losses[agent * 3 + 1] = q_loss;
+    losses[agent * 3 + 2] = actor_loss;
+    loss_sum[agent * 3 + 0] += value_loss;
+    loss_sum[agent * 3 + 1] += q_loss;
+    loss_sum[agent * 3 + 2] += actor_loss;
+    // Adam step scalars of THIS step (torch optim/adam.py:529-547) and scheduler/rng advance.
+    const long long t = it[agent] + 1;
+    const double bc1 = 1.0 - pow(0.9, (double)t), bc2 = 1.0 - pow(0.999, (double)t);
+    const double lr_a = actor_lr[agent];
+    StepScalars sc;
+    sc.ss_v = (float)((double)hp[4] / bc1);
+    sc.ss_q = (float)((double)hp[5] / bc1);
+    sc.ss_a = (float)(lr_a / bc1);
+    sc.bc2_sqrt = (float)sqrt(bc2);
+    sc.tau = hp[1];
+    scal[agent] = sc;
+    it[agent] = t;
+    actor_lr[agent] = cosine_next(lr_a, (double)hp[6], t, (long long)hp[7]);
+    if (advance_rng) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Heads backward for the 4 trainable streams:  dW2 = dOut^T H2, db2 = sum_b dOut,
+// dH2pre[b,j] = (H2[b,j] > 0) * sum_o dOut[o,b] * W2[o,j].   One CTA per (stream, agent).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __restrict__ params,
+                                                       const float* __restrict__ H2,
+                                                       const float* __restrict__ d_out, float* __restrict__ dH2,
+                                                       float* __restrict__ grads) {
+  const int agent = blockIdx.y, t = blockIdx.x, s = train_stream(t);
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const int64_t noff = L.net_off(s);
+  const float* W2 = params + (int64_t)agent * L.Pstride + noff + L.w2(in);
+  float* gW2 = grads + (int64_t)agent * L.Pstride + noff + L.w2(in);
+  float* gb2 = grads + (int64_t)agent * L.Pstride + noff + L.b2(in, nout);
+  const float* h2 = H2 + ((int64_t)agent * kStreams + s) * L.B * L.H;
+  float* dh2 = dH2 + ((int64_t)agent * kTrain + t) * L.B * L.H;
+  const float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
+  const int drow0 = (t == 3) ? 3 : t;  // V->0, Q1->1, Q2->2, actor->3..
+  for (int j = threadIdx.x; j < L.H; j += blockDim.x) {
+    for (int o0 = 0; o0 < nout; o0 += 8) {
+      const int no = min(8, nout - o0);
+      float w2[8], acc[8];
+#pragma unroll
+      for (int oo = 0; oo < 8; ++oo) {
+        w2[oo] = oo < no ? W2[(int64_t)(o0 + oo) * L.H + j] : 0.f;
+        acc[oo] = 0.f;
+      }
+      const bool first = (o0 == 0), last = (o0 + 8 >= nout);
+#pragma unroll 4
+      for (int b = 0; b < L.B; ++b) {
+        const float h = h2[(int64_t)b * L.H + j];
+        float g = first ? 0.f : dh2[(int64_t)b * L.H + j];
+#pragma unroll
+        for (int oo = 0; oo < 8; ++oo) {
+          if (oo < no) {
+            const float d = __ldg(dout + (int64_t)(drow0 + o0 + oo) * L.B + b);
+            acc[oo] = fmaf(d, h, acc[oo]);
+            g = fmaf(d, w2[oo], g);
+          }
+        }
+        dh2[(int64_t)b * L.H + j] = last ? (h > 0.f ? g : 0.f) : g;
+      }
+#pragma unroll
+      for (int oo = 0; oo < 8; ++oo)
+        if (oo < no) gW2[(int64_t)(o0 + oo) * L.H + j] = acc[oo];
+    }
+  }
+  for (int o = threadIdx.x; o < nout; o += blockDim.x) {
+    float sacc = 0.f;
+    for (int b = 0; b < L.B; ++b) sacc += dout[(int64_t)(drow0 + o) * L.B + b];
+    gb2[o] = sacc;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Adam (torch _fused_adam math, betas (0.9, 0.999), eps 1e-8) for the three optimizers of every
+// agent, with the Polyak target update (iql.py:127-129,613) fused for the Q segment.
+// HBM-bound: 28 B read + 16 B written per parameter (+8 B per Q parameter for the target).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __restrict__ params,
+                                                          float4* __restrict__ exp_avg, float4* __restrict__ exp_avg_sq,
+                                                          float4* __restrict__ target, const float4* __restrict__ grads,
+                                                          const StepScalars* __restrict__ scal,
+                                                          __nv_bfloat16* __restrict__ shadow /*unused here*/) {
+  const int agent = blockIdx.y;
+  const int64_t n4 = L.Pstride / 4;
+  const int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i4 >= n4) return;
+  const StepScalars sc = scal[agent];
+  const int64_t g4 = (int64_t)agent * n4 + i4;
+  float4 p = params[g4], m = exp_avg[g4], v = exp_avg_sq[g4];
+  const float4 g = grads[g4];
+  float* pp = &p.x; float* mp = &m.x; float* vp = &v.x; const float* gp = &g.x;
+  const int64_t e0 = i4 * 4;
+  const int64_t v_begin = L.off_v, a_begin = L.off_a;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int64_t e = e0 + c;
+    const float ss = e < v_begin ? sc.ss_q : (e < a_begin ? sc.ss_v : sc.ss_a);
+    const float gg = gp[c];
+    const float mm = mp[c] + (1.0f - 0.9f) * (gg - mp[c]);
+    const float vv = 0.999f * vp[c] + (1.0f - 0.999f) * gg * gg;
+    const float denom = sqrtf(vv) / sc.bc2_sqrt + 1e-8f;
+    pp[c] = pp[c] - ss * (mm / denom);
+    mp[c] = mm;
+    vp[c] = vv;
+  }
+  params[g4] = p;
+  exp_avg[g4] = m;
+  exp_avg_sq[g4] = v;
+  if (e0 < L.PQ) {  // PQstride - PQ < 4 padding lanes stay zero (params there are zero)
+    const int64_t t4 = (int64_t)agent * (L.PQstride / 4) + i4;
+    float4 tg = target[t4];
+    float* tp = &tg.x;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (e0 + c < L.PQ) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);
+    target[t4] = tg;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+static int build_tasks(iqlb_agents* h) {
+  const Layout& L = h->L;
+  const int N = h->desc.n_agents;
+  std::vector<GemmTask> f0((size_t)N * kStreams), f1((size_t)N * kStreams), bw1((size_t)N * kTrain),
+      bd1((size_t)N * kTrain), bw0((size_t)N * kTrain);
+  for (int a = 0; a < N; ++a) {
+    float* P = h->params + (int64_t)a * L.Pstride;
+    float* T = h->target + (int64_t)a * L.PQstride;
+    float* G = h->grads + (int64_t)a * L.Pstride;
+    float* X = h->batch + (int64_t)a * L.B * L.R;
+    for (int s = 0; s < kStreams; ++s) {
+      const int in = L.in_dim(s);
+      const float* net = (L.uses_target(s) ? T : P) + L.net_off(s);
+      float* h1 = h->H1 + ((int64_t)a * kStreams + s) * L.B * L.H;
+      float* h2 = h->H2 + ((int64_t)a * kStreams + s) * L.B * L.H;
+      GemmTask t{};
+      t.A = X + (s == 0 ? L.S + L.A : 0); t.lda = L.R;
+      t.Bm = net + L.w0(); t.ldb = in; t.bias = net + L.b0(in);
+      t.C = h1; t.ldc = L.H; t.M = L.B; t.N = L.H; t.K = in;
+      f0[(size_t)a * kStreams + s] = t;
+      GemmTask u{};
+      u.A = h1; u.lda = L.H; u.Bm = net + L.w1(in); u.ldb = L.H; u.bias = net + L.b1(in);
+      u.C = h2; u.ldc = L.H; u.M = L.B; u.N = L.H; u.K = L.H;
+      f1[(size_t)a * kStreams + s] = u;
+    }
+    for (int tt = 0; tt < kTrain; ++tt) {
+      const int s = train_stream(tt), in = L.in_dim(s);
+      const float* net = P + L.net_off(s);
+      float* gnet = G + L.net_off(s);
+      const float* h1 = h->H1 + ((int64_t)a * kStreams + s) * L.B * L.H;
+      float* dh2 = h->dH2 + ((int64_t)a * kTrain + tt) * L.B * L.H;
+      float* dh1 = h->dH1 + ((int64_t)a * kTrain + tt) * L.B * L.H;
+      GemmTask w1{};  // dW1[H,H] = dH2^T H1 ; db1
+      w1.A = dh2; w1.lda = L.H; w1.Bm = h1; w1.ldb = L.H; w1.C = gnet + L.w1(in); w1.ldc = L.H;
+      w1.bias_grad = gnet + L.b1(in); w1.M = L.H; w1.N = L.H; w1.K = L.B;
+      bw1[(size_t)a * kTrain + tt] = w1;
+      GemmTask d1{};  // dH1 = (dH2 W1) * relu'(H1)
+      d1.A = dh2; d1.lda = L.H; d1.Bm = net + L.w1(in); d1.ldb = L.H; d1.C = dh1; d1.ldc = L.H;
+      d1.mask = h1; d1.M = L.B; d1.N = L.H; d1.K = L.H;
+      bd1[(size_t)a * kTrain + tt] = d1;
+      GemmTask w0{};  // dW0[H,in] = dH1^T X ; db0
+      w0.A = dh1; w0.lda = L.H; w0.Bm = X; w0.ldb = L.R; w0.C = gnet + L.w0(); w0.ldc = in;
+      w0.bias_grad = gnet + L.b0(in); w0.M = L.H; w0.N = in; w0.K = L.B;
+      bw0[(size_t)a * kTrain + tt] = w0;
+    }
+  }
+  auto up = [](GemmTask** dst, const std::vector<GemmTask>& v) -> int {
+    IQLB_CUDA(cudaMalloc((void**)dst, v.size() * sizeof(GemmTask)));
+    IQLB_CUDA(cudaMemcpy(*dst, v.data(), v.size() * sizeof(GemmTask), cudaMemcpyHostToDevice));
+    return IQLB_OK;
+  };
+  int rc;
+  if ((rc = up(&h->t_fwd0, f0))) return rc;
+  if ((rc = up(&h->t_fwd1, f1))) return rc;
+  if ((rc = up(&h->t_bw1, bw1))) return rc;
+  if ((rc = up(&h->t_bd1, bd1))) return rc;
+  if ((rc = up(&h->t_bw0, bw0))) return rc;
+  return IQLB_OK;
+}
+
+static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
+  const Layout& L = h->L;
+  const int N = h->desc.n_agents;
+  int rc;
+  if (sampled) {
+    IQLB_REQUIRE(h->table != nullptr, "no replay table attached (iqlb_agents_set_replay)");
+    rc = launch_gather(h->table, h->n_rows, L.R, 2 * L.S + L.A, h->reward_cols, h->reward_variant, h->rng, nullptr, N,
+                       L.B, h->idx_out, h->batch, st);
+    if (rc) return rc;
+  }
+  if (h->desc.precision == 1) {
+    if ((rc = bf16_step_gemms_fwd(h, st))) return rc;
+  } else {
+    if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd0, N * kStreams, L.B, L.H, false, st))) return rc;
+    if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd1, N * kStreams, L.B, L.H, false, st))) return rc;
+  }
+  head_fwd_kernel<<<dim3((L.B + 7) / 8, kStreams, N), 256, 0, st>>>(L, h->params, h->target, h->H2, h->head_out);
+  IQLB_LAUNCH_CHECK();
+  const int lb = (L.B + 31) / 32 * 32;
+  loss_kernel<<<N, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
+                                h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0);
+  IQLB_LAUNCH_CHECK();
+  head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
+  IQLB_LAUNCH_CHECK();
+  if (h->desc.precision == 1) {
+    if ((rc = bf16_step_gemms_bwd(h, st))) return rc;
+  } else {
+    if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw1, N * kTrain, L.H, L.H, false, st))) return rc;
+    if ((rc = launch_grouped_gemm(GEMM_BWD_DATA, h->t_bd1, N * kTrain, L.B, L.H, false, st))) return rc;
+    if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw0, N * kTrain, L.H, L.Dq, true, st))) return rc;
+  }
+  const int64_t n4 = L.Pstride / 4;
+  adam_polyak_kernel<<<dim3((unsigned)((n4 + 255) / 256), N), 256, 0, st>>>(
+      L, (float4*)h->params, (float4*)h->exp_avg, (float4*)h->exp_avg_sq, (float4*)h->target, (const float4*)h->grads,
+      h->scal, nullptr);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+}  // namespace iqlb
+
+using namespace iqlb;
+
+extern "C" int iqlb_param_count(int32_t state_dim, int32_t action_dim, int32_t hidden_dim, int32_t deterministic,
+                                int64_t* p_all, int64_t* p_q) {
+  IQLB_REQUIRE(state_dim > 0 && action_dim > 0 && hidden_dim > 0, "dims must be positive");
+  Layout L;
+  L.init(state_dim, action_dim, hidden_dim, deterministic, 4, 1);
+  if (p_all) *p_all = L.P;
+  if (p_q) *p_q = L.PQ;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, float* exp_avg, float* exp_avg_sq,
+                                  float* target, const float* hparams, int64_t* it, double* actor_lr, uint64_t* rng,
+                                  float* losses, float* loss_sum, iqlb_agents** out) {
+  IQLB_REQUIRE(d && out, "null desc/out");
+  IQLB_REQUIRE(params && exp_avg && exp_avg_sq && target && hparams && it && actor_lr && rng && losses && loss_sum,
+               "null state buffer");
+  IQLB_REQUIRE(d->n_agents > 0 && d->state_dim > 0 && d->action_dim > 0 && d->hidden_dim > 0, "dims");
+  IQLB_REQUIRE(d->batch_size > 0 && d->batch_size <= 1024, "batch_size in [1, 1024]");
+  IQLB_REQUIRE(d->row_stride % 4 == 0 && d->row_stride >= 2 * d->state_dim + d->action_dim + 2,
+               "row_stride must hold obs|act|next_obs|rew|done and be a multiple of 4");
+  IQLB_REQUIRE(d->precision == 0 || d->precision == 1, "precision must be 0 (fp32) or 1 (bf16 tcgen05)");
+  IQLB_REQUIRE(((uintptr_t)params & 15) == 0 && ((uintptr_t)exp_avg & 15) == 0 && ((uintptr_t)exp_avg_sq & 15) == 0 &&
+                   ((uintptr_t)target & 15) == 0,
+               "state buffers must be 16-byte aligned");
+  iqlb_agents* h = new (std::nothrow) iqlb_agents();
+  if (!h) return fail(IQLB_ERR_NOMEM, "out of host memory%s", "");
+  h->desc = *d;
+  h->L.init(d->state_dim, d->action_dim, d->hidden_dim, d->deterministic, d->row_stride, d->batch_size);
+  h->params = params; h->exp_avg = exp_avg; h->exp_avg_sq = exp_avg_sq; h->target = target;
+  h->hparams = hparams; h->it = it; h->actor_lr = actor_lr; h->rng = rng; h->losses = losses; h->loss_sum = loss_sum;
+  const Layout& L = h->L;
+  const int64_t N = d->n_agents, BH = (int64_t)L.B * L.H;
+  auto alloc = [&](float** p, int64_t n) -> int {
+    IQLB_CUDA(cudaMalloc((void**)p, (size_t)n * sizeof(float)));
+    IQLB_CUDA(cudaMemset(*p, 0, (size_t)n * sizeof(float)));
+    return IQLB_OK;
+  };
+  int rc = IQLB_OK;
+  if (!rc) rc = alloc(&h->batch, N * L.B * L.R);
+  if (!rc) rc = alloc(&h->H1, N * kStreams * BH);
+  if (!rc) rc = alloc(&h->H2, N * kStreams * BH);
+  if (!rc) rc = alloc(&h->head_out, N * L.head_rows() * L.B);
+  if (!rc) rc = alloc(&h->d_out, N * L.dout_rows() * L.B);
+  if (!rc) rc = alloc(&h->dH2, N * kTrain * BH);
+  if (!rc) rc = alloc(&h->dH1, N * kTrain * BH);
+  if (!rc) rc = alloc(&h->grads, N * L.Pstride);
+  if (!rc) rc = alloc((float**)&h->scal, N * (int64_t)(sizeof(StepScalars) / sizeof(float)));
+  if (!rc) rc = build_tasks(h);
+  if (!rc && d->precision == 1) rc = bf16_create(h);
+  if (rc) { iqlb_agents_destroy(h); return rc; }
+  *out = h;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
+  if (!h) return IQLB_OK;
+  bf16_destroy(h);
+  cudaFree(h->batch); cudaFree(h->H1); cudaFree(h->H2); cudaFree(h->head_out); cudaFree(h->d_out);
+  cudaFree(h->dH2); cudaFree(h->dH1); cudaFree(h->grads); cudaFree(h->scal);
+  cudaFree(h->t_fwd0); cudaFree(h->t_fwd1); cudaFree(h->t_bw1); cudaFree(h->t_bd1); cudaFree(h->t_bw0);
+  delete h;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_set_replay(iqlb_agents* h, const float* table, int64_t n_rows, const float* reward_cols,
+                                      const int32_t* reward_variant, int64_t* idx_out) {
+  IQLB_REQUIRE(h && table, "null handle/table");
+  IQLB_REQUIRE(n_rows > 0, "empty table");
+  IQLB_REQUIRE(((uintptr_t)table & 15) == 0, "table must be 16-byte aligned");
+  h->table = table; h->n_rows = n_rows; h->reward_cols = reward_cols; h->reward_variant = reward_variant;
+  h->idx_out = idx_out;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_step(iqlb_agents* h, const float* batch, void* stream) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (batch != nullptr && batch != h->batch) {
+    const Layout& L = h->L;
+    IQLB_CUDA(cudaMemcpyAsync(h->batch, batch, (size_t)h->desc.n_agents * L.B * L.R * sizeof(float),
+                              cudaMemcpyDeviceToDevice, st));
+  }
+  return step_device(h, batch == nullptr, st);
+}
+
+extern "C" int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_losses, void* stream) {
+  IQLB_REQUIRE(h && host_batch && host_losses, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const Layout& L = h->L;
+  IQLB_CUDA(cudaMemcpyAsync(h->batch, host_batch, (size_t)h->desc.n_agents * L.B * L.R * sizeof(float),
+                            cudaMemcpyHostToDevice, st));
+  int rc = step_device(h, false, st);
+  if (rc) return rc;
+  IQLB_CUDA(cudaMemcpyAsync(host_losses, h->losses, (size_t)h->desc.n_agents * 3 * sizeof(float),
+                            cudaMemcpyDeviceToHost, st));
+  IQLB_CUDA(cudaStreamSynchronize(st));
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled) {
+  if (!h) return 0;
+  // gather + fwd0 + fwd1 + head_fwd + loss + head_bwd + bw1 + bd1 + bw0 + adam
+  const int gemms = 5;
+  return (sampled ? 1 : 0) + gemms + 4;
+}
+
+extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, int64_t* nbytes, void* stream) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  const Layout& L = h->L;
+  const int64_t N = h->desc.n_agents, BH = (int64_t)L.B * L.H;
+  const float* src = nullptr;
+  int64_t n = 0;
+  switch (which) {
+    case 0: src = h->H1; n = N * kStreams * BH; break;
+    case 1: src = h->H2; n = N * kStreams * BH; break;
+    case 2: src = h->head_out; n = N * L.head_rows() * L.B; break;
+    case 3: src = h->d_out; n = N * L.dout_rows() * L.B; break;
+    case 4: src = h->dH2; n = N * kTrain * BH; break;
+    case 5: src = h->dH1; n = N * kTrain * BH; break;
+    case 6: src = h->grads; n = N * L.Pstride; break;
+    case 7: src = h->batch; n = N * L.B * L.R; break;
+    default: return fail(IQLB_ERR_INVALID, "unknown debug tensor%s", "");
+  }
+  if (nbytes) *nbytes = n * (int64_t)sizeof(float);
+  if (dst) IQLB_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return IQLB_OK;
+}

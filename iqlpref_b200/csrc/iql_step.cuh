@@ -1,0 +1,106 @@
+// Internal declarations shared by the IQL step translation units.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+namespace iqlb {
+
+// Stream order of the 7 MLP forwards of one update:
+//   0 V(next_obs)  1 V(obs)  2 Qt1(sa)  3 Qt2(sa)  4 Q1(sa)  5 Q2(sa)  6 actor(obs)
+// Trainable streams (backward + Adam): 1 (V), 4 (Q1), 5 (Q2), 6 (actor).
+constexpr int kStreams = 7;
+constexpr int kTrain = 4;
+__host__ __device__ inline int train_stream(int t) { return t == 0 ? 1 : (t == 1 ? 4 : (t == 2 ? 5 : 6)); }
+
+struct Layout {
+  int S, A, H, Dq, R, B;
+  int deterministic;
+  int64_t qnet, vnet, anet;       // floats per network
+  int64_t off_q1, off_q2, off_v, off_a, off_logstd;
+  int64_t P, PQ, Pstride, PQstride;
+  __host__ __device__ static int64_t net_size(int in, int H, int out) {
+    return (int64_t)H * in + H + (int64_t)H * H + H + (int64_t)out * H + out;
+  }
+  __host__ __device__ void init(int S_, int A_, int H_, int det, int R_, int B_) {
+    S = S_; A = A_; H = H_; Dq = S_ + A_; R = R_; B = B_; deterministic = det;
+    qnet = net_size(Dq, H, 1);
+    vnet = net_size(S, H, 1);
+    anet = net_size(S, H, A);
+    off_q1 = 0; off_q2 = qnet; off_v = 2 * qnet; off_a = off_v + vnet; off_logstd = off_a + anet;
+    PQ = 2 * qnet;
+    P = off_logstd + (det ? 0 : A);
+    Pstride = (P + 3) / 4 * 4;
+    PQstride = (PQ + 3) / 4 * 4;
+  }
+  // offsets inside one network
+  __host__ __device__ int64_t w0() const { return 0; }
+  __host__ __device__ int64_t b0(int in) const { return (int64_t)H * in; }
+  __host__ __device__ int64_t w1(int in) const { return b0(in) + H; }
+  __host__ __device__ int64_t b1(int in) const { return w1(in) + (int64_t)H * H; }
+  __host__ __device__ int64_t w2(int in) const { return b1(in) + H; }
+  __host__ __device__ int64_t b2(int in, int out) const { return w2(in) + (int64_t)out * H; }
+  // per stream: input width, output width, offset of the net inside params (or target for 2,3)
+  __host__ __device__ int in_dim(int s) const { return (s >= 2 && s <= 5) ? Dq : S; }
+  __host__ __device__ int out_dim(int s) const { return s == 6 ? A : 1; }
+  __host__ __device__ int64_t net_off(int s) const {
+    switch (s) {
+      case 0: case 1: return off_v;
+      case 2: case 4: return off_q1;
+      case 3: case 5: return off_q2;
+      default: return off_a;
+    }
+  }
+  __host__ __device__ bool uses_target(int s) const { return s == 2 || s == 3; }
+  // head_out rows: 0 next_v, 1 v, 2 tq1, 3 tq2, 4 q1, 5 q2, 6.. mu[a]
+  __host__ __device__ int head_rows() const { return 6 + A; }
+  // d_out rows: 0 dv, 1 dq1, 2 dq2, 3.. dz[a]
+  __host__ __device__ int dout_rows() const { return 3 + A; }
+};
+
+struct GemmTask {
+  const float* A;
+  const float* Bm;
+  float* C;
+  const float* bias;    // FWD: bias[n]
+  const float* mask;    // BWD_DATA: relu mask source (same shape/ld as C)
+  float* bias_grad;     // BWD_WEIGHT: column sums of A
+  int M, N, K, lda, ldb, ldc;
+  float scale;          // FWD_KN: act(scale * acc + bias)
+  int act;              // FWD_KN: IQLB_ACT_* id
+};
+
+enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3 };
+
+struct StepScalars {  // per agent, written by the loss kernel, read by Adam
+  float ss_q, ss_v, ss_a, bc2_sqrt, tau;
+};
+
+int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
+                        cudaStream_t stream);
+
+}  // namespace iqlb
+
+struct iqlb_agents {
+  iqlb_agents_desc desc;
+  iqlb::Layout L;
+  // caller-owned
+  float *params, *exp_avg, *exp_avg_sq, *target;
+  const float* hparams;
+  int64_t* it;
+  double* actor_lr;
+  uint64_t* rng;
+  float *losses, *loss_sum;
+  // replay
+  const float* table = nullptr;
+  int64_t n_rows = 0;
+  const float* reward_cols = nullptr;
+  const int32_t* reward_variant = nullptr;
+  int64_t* idx_out = nullptr;
+  // lib-owned scratch
+  float *batch = nullptr, *H1 = nullptr, *H2 = nullptr, *head_out = nullptr, *d_out = nullptr, *dH2 = nullptr,
+        *dH1 = nullptr, *grads = nullptr;
+  iqlb::StepScalars* scal = nullptr;
+  iqlb::GemmTask *t_fwd0 = nullptr, *t_fwd1 = nullptr, *t_bw1 = nullptr, *t_bd1 = nullptr, *t_bw0 = nullptr;
+  void* bf16_state = nullptr;  // precision==1 extension (tcgen05 path)
+};

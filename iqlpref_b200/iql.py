@@ -1,0 +1,640 @@
+"""Host-side mirror of `algorithms/offline/iql.py` (reference paths are relative to
+/root/reference) for the IQL hot path.  Same names, arguments and errors as the reference;
+the arithmetic runs in libiqlb.so (hand-written sm_100a CUDA, include/iqlb.h).
+
+* `TrainConfig`                       iql.py:43-124 (+ `reward_model_root`, iql_eval.py:105-110)
+* `ReplayBuffer`                      iql.py:164-226  -> packed table + Philox gather kernel
+* `MLP/TwinQ/ValueFunction/GaussianPolicy/DeterministicPolicy`  iql.py:417-543 (parameter
+  containers with the reference's state_dict keys; init consumes the torch RNG identically)
+* `ImplicitQLearning`                 iql.py:546-688  -> one agent of `BatchedIQL`
+* `BatchedIQL`                        new: N independent agents (seeds x sweep hyper-parameters,
+                                      tr_sweeps/launch.sh:82-92) advanced by one launch sequence
+* `soft_update`, `asymmetric_l2_loss` iql.py:127-129, 404-405
+
+There is no CPU path: constructing any of the compute classes without CUDA + libiqlb.so raises.
+"""
+import copy
+import ctypes as C
+import math
+import os
+import uuid
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.nn as nn
+from torch.distributions import Normal
+
+from . import _lib
+
+TensorBatch = List[torch.Tensor]
+
+EXP_ADV_MAX = 100.0
+LOG_STD_MIN = -20.0
+LOG_STD_MAX = 2.0
+
+
+@dataclass
+class TrainConfig:
+    """Field-for-field `TrainConfig` of the reference (iql.py:43-124)."""
+    project: str = "IQL-pref"
+    group: str = "IQL-D4RL"
+    name: str = "IQL"
+    env: str = "halfcheetah-medium-expert-v2"
+    discount: float = 0.99
+    tau: float = 0.005
+    beta: float = 3.0
+    iql_tau: float = 0.7
+    iql_deterministic: bool = False
+    max_timesteps: int = int(1e6)
+    buffer_size: int = 2_000_000
+    batch_size: int = 256
+    normalize: bool = True
+    normalize_reward: int = 0
+    vf_lr: float = 3e-4
+    qf_lr: float = 3e-4
+    actor_lr: float = 3e-4
+    actor_dropout: Optional[float] = None
+    log_freq: int = 250
+    eval_freq: int = int(5e3)
+    n_episodes: int = 10
+    checkpoints_path: Optional[str] = None
+    load_model: str = ""
+    reward_model_path: str = ""
+    query_length: int = 1
+    bnn_reward_model: bool = False
+    bnn_alpha: float = 0.95
+    bnn_n_samples: int = 500
+    mr_ensemble: bool = False
+    mr_alpha: float = 0.95
+    mr_burn_in: int = 0
+    seed: int = 0
+    device: str = "cuda"
+    reward_model_root: str = ""  # iql_eval.py:110: reward_model_path = f"{root}_{seed}"
+
+    def __post_init__(self):
+        self.name = f"{self.name}-{self.env}-{str(uuid.uuid4())[:8]}"
+        if self.checkpoints_path is not None:
+            self.checkpoints_path = os.path.join(self.checkpoints_path, self.name)
+        if self.reward_model_root and not self.reward_model_path:
+            self.reward_model_path = f"{self.reward_model_root}_{self.seed}"
+
+
+def _require_cuda(device) -> torch.device:
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError(f"iqlpref_b200 has no CPU path (device={device!r}); use a CUDA device")
+    if not torch.cuda.is_available():
+        raise RuntimeError("iqlpref_b200 needs a CUDA device (B200); none is visible")
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    _lib.load()
+    return dev
+
+
+def row_stride(state_dim: int, action_dim: int) -> int:
+    """Floats per packed replay row [obs|act|next_obs|rew|done|pad], 16-byte multiple."""
+    return (2 * state_dim + action_dim + 2 + 3) // 4 * 4
+
+
+def pack_rows(obs, act, rew, next_obs, done, stride: int) -> torch.Tensor:
+    """Pack the five reference tensors ([n,S],[n,A],[n]|[n,1],[n,S],[n]|[n,1]) into rows."""
+    n, s = obs.shape
+    a = act.shape[1]
+    out = torch.zeros((n, stride), dtype=torch.float32, device=obs.device)
+    out[:, :s] = obs
+    out[:, s:s + a] = act
+    out[:, s + a:2 * s + a] = next_obs
+    out[:, 2 * s + a] = rew.reshape(n)
+    out[:, 2 * s + a + 1] = done.reshape(n).to(torch.float32)
+    return out
+
+
+def soft_update(target: nn.Module, source: nn.Module, tau: float):
+    """iql.py:127-129 with the in-place Polyak kernel (one launch per parameter tensor)."""
+    lib = _lib.load()
+    for tp, sp in zip(target.parameters(), source.parameters()):
+        if not tp.is_cuda:
+            raise RuntimeError("soft_update: parameters must live on a CUDA device (no CPU path)")
+        if tp.data.is_contiguous() and sp.data.is_contiguous() and tp.data_ptr() % 16 == 0 and sp.data_ptr() % 16 == 0:
+            _lib.check(lib.iqlb_polyak(_lib.ptr(tp.data), _lib.ptr(sp.data), tp.numel(), float(tau),
+                                       _lib.stream_ptr(tp.device)), "iqlb_polyak")
+        else:  # unaligned view of a packed buffer: stage through an aligned copy
+            t = tp.data.contiguous().clone()
+            s = sp.data.contiguous().clone()
+            _lib.check(lib.iqlb_polyak(_lib.ptr(t), _lib.ptr(s), t.numel(), float(tau), _lib.stream_ptr(tp.device)),
+                       "iqlb_polyak")
+            tp.data.copy_(t)
+
+
+def asymmetric_l2_loss(u: torch.Tensor, tau: float) -> torch.Tensor:
+    """iql.py:404-405 (kept for API parity; the training step computes it in-kernel)."""
+    return torch.mean(torch.abs(tau - (u < 0).float()) * u ** 2)
+
+
+class ReplayBuffer:
+    """iql.py:164-226.  Storage is one packed fp32 table [buffer_size, row_stride] in HBM."""
+
+    def __init__(self, state_dim: int, action_dim: int, buffer_size: int, device: str = "cuda"):
+        self._device = _require_cuda(device)
+        self._state_dim, self._action_dim = state_dim, action_dim
+        self._buffer_size = buffer_size
+        self._pointer = 0
+        self._size = 0
+        self._stride = row_stride(state_dim, action_dim)
+        self._table = torch.zeros((buffer_size, self._stride), dtype=torch.float32, device=self._device)
+
+    # views with the reference's attribute names
+    @property
+    def _states(self):
+        return self._table[:, :self._state_dim]
+
+    @property
+    def _actions(self):
+        return self._table[:, self._state_dim:self._state_dim + self._action_dim]
+
+    @property
+    def _next_states(self):
+        s, a = self._state_dim, self._action_dim
+        return self._table[:, s + a:2 * s + a]
+
+    @property
+    def _rewards(self):
+        c = 2 * self._state_dim + self._action_dim
+        return self._table[:, c:c + 1]
+
+    @property
+    def _dones(self):
+        c = 2 * self._state_dim + self._action_dim + 1
+        return self._table[:, c:c + 1]
+
+    def _to_tensor(self, data: np.ndarray) -> torch.Tensor:
+        return torch.tensor(data, dtype=torch.float32, device=self._device)
+
+    def load_d4rl_dataset(self, data: Dict[str, np.ndarray]):
+        if self._size != 0:
+            raise ValueError("Trying to load data into non-empty replay buffer")
+        n = data["observations"].shape[0]
+        if n > self._buffer_size:
+            raise ValueError("Replay buffer is smaller than the dataset you are trying to load!")
+        self._states[:n] = self._to_tensor(data["observations"])
+        self._actions[:n] = self._to_tensor(data["actions"])
+        self._rewards[:n] = self._to_tensor(data["rewards"][..., None])
+        self._next_states[:n] = self._to_tensor(data["next_observations"])
+        self._dones[:n] = self._to_tensor(data["terminals"][..., None])
+        self._size += n
+        self._pointer = min(self._size, n)
+        print(f"Dataset size: {n}")
+
+    @property
+    def n_rows(self) -> int:
+        return min(self._size, self._pointer)
+
+    def split(self, rows: torch.Tensor) -> TensorBatch:
+        s, a = self._state_dim, self._action_dim
+        return [rows[:, :s], rows[:, s:s + a], rows[:, 2 * s + a:2 * s + a + 1], rows[:, s + a:2 * s + a],
+                rows[:, 2 * s + a + 1:2 * s + a + 2]]
+
+    def sample_rows(self, batch_size: int, return_indices: bool = False):
+        """Packed rows [batch, row_stride].  Draws from torch's CUDA generator state (seed, philox
+        offset) and advances it exactly like `torch.randint(0, n, (batch,), device=cuda)`."""
+        n = self.n_rows
+        if n <= 0:
+            raise RuntimeError("cannot sample from an empty replay buffer")
+        gen = torch.cuda.default_generators[self._device.index]
+        seed, offset = gen.initial_seed(), gen.get_offset()
+        rng = torch.tensor([[seed, offset]], dtype=torch.int64, device=self._device)
+        out = torch.empty((batch_size, self._stride), dtype=torch.float32, device=self._device)
+        idx = torch.empty((1, batch_size), dtype=torch.int64, device=self._device) if return_indices else None
+        lib = _lib.load()
+        _lib.check(lib.iqlb_replay_sample(_lib.ptr(self._table), n, self._stride, 2 * self._state_dim + self._action_dim,
+                                          None, None, _lib.ptr(rng), 1, batch_size, _lib.ptr(idx), _lib.ptr(out),
+                                          _lib.stream_ptr(self._device)), "iqlb_replay_sample")
+        gen.set_offset(offset + philox_offset_increment(batch_size, n, self._device))
+        return (out, idx[0]) if return_indices else out
+
+    def sample(self, batch_size: int) -> TensorBatch:
+        return self.split(self.sample_rows(batch_size))
+
+    def add_transition(self):
+        raise NotImplementedError
+
+
+def philox_offset_increment(batch: int, n: int, device) -> int:
+    """Generator advance of one torch.randint call (ATen DistributionTemplates.h:50-63)."""
+    props = torch.cuda.get_device_properties(device)
+    block = 256
+    grid = min(props.multi_processor_count * (props.max_threads_per_multi_processor // block),
+               (batch + block - 1) // block)
+    unroll = 2 if n >= (1 << 28) else 4
+    return ((batch - 1) // (block * grid * unroll) + 1) * 4
+
+
+# --------------------------------------------------------------------------------------------
+# Parameter containers (same module tree / state_dict keys as the reference)
+# --------------------------------------------------------------------------------------------
+class Squeeze(nn.Module):
+    def __init__(self, dim=-1):
+        super().__init__()
+        self.dim = dim
+
+    def forward(self, x):
+        return x.squeeze(dim=self.dim)
+
+
+class MLP(nn.Module):
+    def __init__(self, dims, activation_fn=nn.ReLU, output_activation_fn=None, squeeze_output=False, dropout=None):
+        super().__init__()
+        if len(dims) < 2:
+            raise ValueError("MLP requires at least two dims (input and output)")
+        mods: List[nn.Module] = []
+        for d_in, d_out in zip(dims[:-2], dims[1:-1]):
+            mods += [nn.Linear(d_in, d_out), activation_fn()]
+            if dropout is not None:
+                mods.append(nn.Dropout(dropout))
+        mods.append(nn.Linear(dims[-2], dims[-1]))
+        if output_activation_fn is not None:
+            mods.append(output_activation_fn())
+        if squeeze_output:
+            if dims[-1] != 1:
+                raise ValueError("Last dim must be 1 when squeezing")
+            mods.append(Squeeze(-1))
+        self.net = nn.Sequential(*mods)
+
+    def forward(self, x):
+        return self.net(x)
+
+    def linears(self) -> List[nn.Linear]:
+        return [m for m in self.net if isinstance(m, nn.Linear)]
+
+
+class GaussianPolicy(nn.Module):
+    def __init__(self, state_dim, act_dim, max_action, hidden_dim=256, n_hidden=2, dropout=None):
+        super().__init__()
+        self.net = MLP([state_dim, *([hidden_dim] * n_hidden), act_dim], output_activation_fn=nn.Tanh, dropout=dropout)
+        self.log_std = nn.Parameter(torch.zeros(act_dim, dtype=torch.float32))
+        self.max_action = max_action
+
+    def forward(self, obs):
+        return Normal(self.net(obs), torch.exp(self.log_std.clamp(LOG_STD_MIN, LOG_STD_MAX)))
+
+    @torch.inference_mode()
+    def act(self, state: np.ndarray, device: str = "cpu"):
+        state = torch.tensor(state.reshape(1, -1), device=device, dtype=torch.float32)
+        dist = self(state)
+        action = dist.mean if not self.training else dist.sample()
+        return torch.clamp(self.max_action * action, -self.max_action, self.max_action).cpu().data.numpy().flatten()
+
+
+class DeterministicPolicy(nn.Module):
+    def __init__(self, state_dim, act_dim, max_action, hidden_dim=256, n_hidden=2, dropout=None):
+        super().__init__()
+        self.net = MLP([state_dim, *([hidden_dim] * n_hidden), act_dim], output_activation_fn=nn.Tanh, dropout=dropout)
+        self.max_action = max_action
+
+    def forward(self, obs):
+        return self.net(obs)
+
+    @torch.inference_mode()
+    def act(self, state: np.ndarray, device: str = "cpu"):
+        state = torch.tensor(state.reshape(1, -1), device=device, dtype=torch.float32)
+        return torch.clamp(self(state) * self.max_action, -self.max_action, self.max_action).cpu().data.numpy().flatten()
+
+
+class TwinQ(nn.Module):
+    def __init__(self, state_dim, action_dim, hidden_dim=256, n_hidden=2):
+        super().__init__()
+        dims = [state_dim + action_dim, *([hidden_dim] * n_hidden), 1]
+        self.q1 = MLP(dims, squeeze_output=True)
+        self.q2 = MLP(dims, squeeze_output=True)
+
+    def both(self, state, action):
+        sa = torch.cat([state, action], 1)
+        return self.q1(sa), self.q2(sa)
+
+    def forward(self, state, action):
+        return torch.min(*self.both(state, action))
+
+
+class ValueFunction(nn.Module):
+    def __init__(self, state_dim, hidden_dim=256, n_hidden=2):
+        super().__init__()
+        self.v = MLP([state_dim, *([hidden_dim] * n_hidden), 1], squeeze_output=True)
+
+    def forward(self, state):
+        return self.v(state)
+
+
+def _mlp_linears(m: nn.Module) -> List[nn.Linear]:
+    return [x for x in m.net if isinstance(x, nn.Linear)]
+
+
+def _check_two_hidden(lins: Sequence[nn.Linear], what: str):
+    if len(lins) != 3:
+        raise ValueError(f"{what}: the B200 step is built for n_hidden=2 (3 Linear layers), got {len(lins)}")
+
+
+# --------------------------------------------------------------------------------------------
+# N independent agents
+# --------------------------------------------------------------------------------------------
+class BatchedIQL:
+    """N independent IQL agents (same network shapes, per-agent hyper-parameters, seeds and
+    reward labels) advanced together.  Agent i obeys the contract of the reference's
+    `ImplicitQLearning` (iql.py:546-688)."""
+
+    HP_KEYS = ("discount", "tau", "beta", "iql_tau", "vf_lr", "qf_lr", "actor_lr", "max_steps")
+
+    def __init__(self, state_dim: int, action_dim: int, n_agents: int, hidden_dim: int = 256, batch_size: int = 256,
+                 deterministic: bool = False, device: str = "cuda", precision: str = "fp32",
+                 hparams: Optional[Sequence[Dict[str, float]]] = None, seeds: Optional[Sequence[int]] = None):
+        self.device = _require_cuda(device)
+        self.lib = _lib.load()
+        self.S, self.A, self.H, self.B, self.N = state_dim, action_dim, hidden_dim, batch_size, n_agents
+        self.deterministic = bool(deterministic)
+        self.precision = {"fp32": 0, "bf16": 1}[precision]
+        self.R = row_stride(state_dim, action_dim)
+        p_all, p_q = C.c_int64(), C.c_int64()
+        _lib.check(self.lib.iqlb_param_count(state_dim, action_dim, hidden_dim, int(self.deterministic),
+                                             C.byref(p_all), C.byref(p_q)), "iqlb_param_count")
+        self.P, self.PQ = p_all.value, p_q.value
+        self.Pstride, self.PQstride = (self.P + 3) // 4 * 4, (self.PQ + 3) // 4 * 4
+        z = lambda *shape, dt=torch.float32: torch.zeros(shape, dtype=dt, device=self.device)
+        self.params, self.exp_avg, self.exp_avg_sq = z(n_agents, self.Pstride), z(n_agents, self.Pstride), z(n_agents, self.Pstride)
+        self.target = z(n_agents, self.PQstride)
+        self.hparams = z(n_agents, _lib.HP_STRIDE)
+        self.it = z(n_agents, dt=torch.int64)
+        self.actor_lr = z(n_agents, dt=torch.float64)
+        self.rng = z(n_agents, 2, dt=torch.int64)
+        self.losses, self.loss_sum = z(n_agents, 3), z(n_agents, 3)
+        defaults = dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.7, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4,
+                        max_steps=1_000_000)
+        hp_rows, lr0 = [], []
+        for i in range(n_agents):
+            hp = dict(defaults)
+            if hparams is not None:
+                hp.update(hparams[i])
+            hp_rows.append([float(hp[k]) for k in self.HP_KEYS])
+            lr0.append(float(hp["actor_lr"]))
+        self.hp_host = hp_rows
+        self.hparams.copy_(torch.tensor(hp_rows, dtype=torch.float32))
+        self.actor_lr.copy_(torch.tensor(lr0, dtype=torch.float64))
+        if seeds is not None:
+            self.rng[:, 0] = torch.tensor([int(s) for s in seeds], dtype=torch.int64)
+        desc = _lib.AgentsDesc(n_agents, state_dim, action_dim, hidden_dim, batch_size, int(self.deterministic),
+                               self.R, self.precision)
+        handle = C.c_void_p()
+        _lib.check(self.lib.iqlb_agents_create(C.byref(desc), _lib.ptr(self.params), _lib.ptr(self.exp_avg),
+                                               _lib.ptr(self.exp_avg_sq), _lib.ptr(self.target), _lib.ptr(self.hparams),
+                                               _lib.ptr(self.it), _lib.ptr(self.actor_lr), _lib.ptr(self.rng),
+                                               _lib.ptr(self.losses), _lib.ptr(self.loss_sum), C.byref(handle)),
+                   "iqlb_agents_create")
+        self._h = handle
+        self._replay = None
+        self._layout = self._make_layout()
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and getattr(self, "lib", None) is not None:
+            self.lib.iqlb_agents_destroy(h)
+            self._h = None
+
+    # ---- packed layout (mirrors Layout in csrc/iql_step.cuh) -------------------------------
+    def _make_layout(self):
+        S, A, H = self.S, self.A, self.H
+        lay, off = {}, 0
+        for net, d_in, d_out in (("q1", S + A, 1), ("q2", S + A, 1), ("v", S, 1), ("actor", S, A)):
+            for name, shape in (("w0", (H, d_in)), ("b0", (H,)), ("w1", (H, H)), ("b1", (H,)), ("w2", (d_out, H)),
+                                ("b2", (d_out,))):
+                n = int(np.prod(shape))
+                lay[f"{net}.{name}"] = (off, shape)
+                off += n
+        if not self.deterministic:
+            lay["log_std"] = (off, (A,))
+            off += A
+        assert off == self.P, (off, self.P)
+        return lay
+
+    def view(self, buf: torch.Tensor, agent: int, key: str) -> torch.Tensor:
+        off, shape = self._layout[key]
+        n = int(np.prod(shape))
+        return buf[agent, off:off + n].view(*shape)
+
+    # ---- adopting reference-shaped modules ----------------------------------------------------
+    def _module_tensors(self, qf, vf, actor):
+        out = {}
+        for net, mod in (("q1", qf.q1), ("q2", qf.q2), ("v", vf.v), ("actor", actor.net)):
+            lins = _mlp_linears(mod)
+            _check_two_hidden(lins, net)
+            for i, lin in enumerate(lins):
+                out[f"{net}.w{i}"] = lin.weight
+                out[f"{net}.b{i}"] = lin.bias
+        if not self.deterministic:
+            out["log_std"] = actor.log_std
+        return out
+
+    def adopt(self, agent: int, qf: nn.Module, vf: nn.Module, actor: nn.Module, bind: bool = True):
+        """Copy the modules' parameters into agent slot `agent` (target := qf, iql.py:565) and, if
+        `bind`, re-point the module parameters at the packed storage so `module.state_dict()`
+        always reflects the trained values."""
+        for m in list(actor.modules()):
+            if isinstance(m, nn.Dropout) and m.p > 0:
+                raise NotImplementedError("actor_dropout is not supported by the B200 step yet")
+        with torch.no_grad():
+            for key, prm in self._module_tensors(qf, vf, actor).items():
+                dst = self.view(self.params, agent, key)
+                if tuple(prm.shape) != tuple(dst.shape):
+                    raise ValueError(f"{key}: module shape {tuple(prm.shape)} != packed shape {tuple(dst.shape)}")
+                dst.copy_(prm.detach().to(self.device, torch.float32))
+                if bind:
+                    prm.data = dst
+            self.target[agent, :self.PQ] = self.params[agent, :self.PQ]
+        self._sync_shadow()
+
+    def _sync_shadow(self):
+        pass  # bf16 operand shadows are refreshed inside the library at the next step
+
+    # ---- stepping ---------------------------------------------------------------------------------
+    def attach_replay(self, buffer: ReplayBuffer, reward_cols: Optional[torch.Tensor] = None,
+                      reward_variant: Optional[torch.Tensor] = None, record_indices: bool = False):
+        if buffer._stride != self.R:
+            raise ValueError("replay buffer row layout does not match the agents")
+        self._replay = buffer
+        self._reward_cols, self._reward_variant = reward_cols, reward_variant
+        self.last_indices = (torch.empty((self.N, self.B), dtype=torch.int64, device=self.device)
+                             if record_indices else None)
+        _lib.check(self.lib.iqlb_agents_set_replay(self._h, _lib.ptr(buffer._table), buffer.n_rows,
+                                                   _lib.ptr(reward_cols), _lib.ptr(reward_variant),
+                                                   _lib.ptr(self.last_indices)), "iqlb_agents_set_replay")
+
+    def train(self, batch_rows: Optional[torch.Tensor] = None):
+        """Enqueue one update of every agent.  `batch_rows`: packed [N, B, row_stride] device rows,
+        or None to sample on device.  Losses land in `self.losses` ([N,3]) without a host sync."""
+        if batch_rows is not None:
+            if tuple(batch_rows.shape) != (self.N, self.B, self.R) or batch_rows.dtype != torch.float32:
+                raise ValueError(f"batch_rows must be float32 [{self.N},{self.B},{self.R}]")
+            batch_rows = batch_rows.contiguous()
+        _lib.check(self.lib.iqlb_agents_step(self._h, _lib.ptr(batch_rows), _lib.stream_ptr(self.device)),
+                   "iqlb_agents_step")
+
+    def train_host(self, host_rows: torch.Tensor, host_losses: torch.Tensor):
+        """Step with the batch in pinned host memory; returns after the losses are on the host."""
+        _lib.check(self.lib.iqlb_agents_step_host(self._h, _lib.ptr(host_rows), _lib.ptr(host_losses),
+                                                  _lib.stream_ptr(self.device)), "iqlb_agents_step_host")
+
+    def launches_per_step(self, sampled: bool) -> int:
+        return int(self.lib.iqlb_agents_launches_per_step(self._h, int(sampled)))
+
+    def debug_tensor(self, which: int) -> torch.Tensor:
+        nbytes = C.c_int64()
+        _lib.check(self.lib.iqlb_agents_debug_copy(self._h, which, None, C.byref(nbytes), None), "debug")
+        out = torch.empty(nbytes.value // 4, dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.iqlb_agents_debug_copy(self._h, which, _lib.ptr(out), C.byref(nbytes),
+                                                   _lib.stream_ptr(self.device)), "debug")
+        return out
+
+    # ---- export in the oracle's naming (tests) -----------------------------------------------------
+    def export(self, agent: int) -> Dict[str, np.ndarray]:
+        d = {}
+        for key in self._layout:
+            d[key] = self.view(self.params, agent, key).detach().cpu().numpy().copy()
+            if key.startswith("q1.") or key.startswith("q2."):
+                d["qt" + key[1:]] = self.view(self.target, agent, key).detach().cpu().numpy().copy()
+        return d
+
+
+class ImplicitQLearning:
+    """Drop-in for the reference trainer (iql.py:546-688), one agent on the batched engine."""
+
+    def __init__(self, max_action: float, actor: nn.Module, actor_optimizer: torch.optim.Optimizer,
+                 q_network: nn.Module, q_optimizer: torch.optim.Optimizer, v_network: nn.Module,
+                 v_optimizer: torch.optim.Optimizer, iql_tau: float = 0.7, beta: float = 3.0,
+                 max_steps: int = 1000000, discount: float = 0.99, tau: float = 0.005, device: str = "cuda",
+                 batch_size: int = 256, precision: str = "fp32"):
+        self.max_action = max_action
+        self.qf, self.vf, self.actor = q_network, v_network, actor
+        self.v_optimizer, self.q_optimizer, self.actor_optimizer = v_optimizer, q_optimizer, actor_optimizer
+        self.iql_tau, self.beta, self.discount, self.tau = iql_tau, beta, discount, tau
+        self.device = device
+        q_lins = _mlp_linears(q_network.q1)
+        _check_two_hidden(q_lins, "q_network")
+        a_lins = _mlp_linears(actor.net)
+        state_dim, hidden = a_lins[0].in_features, a_lins[0].out_features
+        action_dim = a_lins[-1].out_features
+        self._max_steps = int(max_steps)
+        hp = dict(discount=discount, tau=tau, beta=beta, iql_tau=iql_tau, vf_lr=v_optimizer.param_groups[0]["lr"],
+                  qf_lr=q_optimizer.param_groups[0]["lr"], actor_lr=actor_optimizer.param_groups[0]["lr"],
+                  max_steps=max_steps)
+        self._precision = precision
+        self._dims = (state_dim, action_dim, hidden)
+        self._hp = hp
+        self._engine: Optional[BatchedIQL] = None
+        self._batch_size = None
+        self.q_target = copy.deepcopy(self.qf).requires_grad_(False).to(device)
+        self.total_it = 0
+        self._build(batch_size)
+
+    def _build(self, batch_size: int):
+        s, a, h = self._dims
+        det = not hasattr(self.actor, "log_std")
+        eng = BatchedIQL(s, a, 1, hidden_dim=h, batch_size=batch_size, deterministic=det, device=self.device,
+                         precision=self._precision, hparams=[self._hp])
+        eng.adopt(0, self.qf, self.vf, self.actor, bind=True)
+        # q_target parameters become views of the packed target buffer
+        with torch.no_grad():
+            for net, mod in (("q1", self.q_target.q1), ("q2", self.q_target.q2)):
+                for i, lin in enumerate(_mlp_linears(mod)):
+                    for nm, prm in ((f"{net}.w{i}", lin.weight), (f"{net}.b{i}", lin.bias)):
+                        dst = eng.view(eng.target, 0, nm)
+                        dst.copy_(prm.detach().to(eng.device))
+                        prm.data = dst
+        if self._engine is not None:  # batch size changed: carry the optimizer state over
+            for name in ("exp_avg", "exp_avg_sq", "it", "actor_lr"):
+                getattr(eng, name).copy_(getattr(self._engine, name))
+        self._engine = eng
+        self._batch_size = batch_size
+
+    @property
+    def engine(self) -> BatchedIQL:
+        return self._engine
+
+    def train(self, batch: TensorBatch) -> Dict[str, float]:
+        self.total_it += 1
+        observations, actions, rewards, next_observations, dones = batch
+        if observations.shape[0] != self._batch_size:
+            self._build(int(observations.shape[0]))
+        if actions.shape[1] != self._dims[1]:
+            raise RuntimeError("Actions shape missmatch")
+        rows = pack_rows(observations, actions, rewards, next_observations, dones, self._engine.R)
+        self._engine.train(rows.unsqueeze(0))
+        v, q, a = self._engine.losses[0].tolist()  # the reference's three .item() syncs
+        return {"value_loss": v, "q_loss": q, "actor_loss": a}
+
+    # ---- checkpoint format of the reference (iql.py:664-688) ------------------------------------------
+    def _opt_state(self, opt: torch.optim.Optimizer, keys: Sequence[str], lr: float) -> Dict[str, Any]:
+        eng = self._engine
+        step = torch.tensor(float(int(eng.it[0].item())))
+        state = {}
+        for i, key in enumerate(keys):
+            state[i] = {"step": step.clone(), "exp_avg": eng.view(eng.exp_avg, 0, key).detach().clone(),
+                        "exp_avg_sq": eng.view(eng.exp_avg_sq, 0, key).detach().clone()}
+        sd = opt.state_dict()
+        if int(eng.it[0].item()) == 0:
+            state = {}
+        sd["state"] = state
+        sd["param_groups"][0]["lr"] = lr
+        return sd
+
+    def _keys(self, nets: Sequence[str]) -> List[str]:
+        keys = []
+        for net in nets:
+            for i in range(3):
+                keys += [f"{net}.w{i}", f"{net}.b{i}"]
+        return keys
+
+    def state_dict(self) -> Dict[str, Any]:
+        eng = self._engine
+        a_keys = self._keys(["actor"]) + ([] if eng.deterministic else ["log_std"])
+        lr_a = float(eng.actor_lr[0].item())
+        it = int(eng.it[0].item())
+        return {
+            "qf": self.qf.state_dict(),
+            "q_optimizer": self._opt_state(self.q_optimizer, self._keys(["q1", "q2"]), self._hp["qf_lr"]),
+            "vf": self.vf.state_dict(),
+            "v_optimizer": self._opt_state(self.v_optimizer, self._keys(["v"]), self._hp["vf_lr"]),
+            "actor": self.actor.state_dict(),
+            "actor_optimizer": self._opt_state(self.actor_optimizer, a_keys, lr_a),
+            "actor_lr_schedule": {"T_max": self._max_steps, "eta_min": 0.0, "base_lrs": [self._hp["actor_lr"]],
+                                  "last_epoch": it, "_step_count": it + 1, "_is_initial": False,
+                                  "_get_lr_called_within_step": False, "_last_lr": [lr_a]},
+            "total_it": self.total_it,
+        }
+
+    def load_state_dict(self, state_dict: Dict[str, Any]):
+        eng = self._engine
+        self.qf.load_state_dict(state_dict["qf"])
+        self.vf.load_state_dict(state_dict["vf"])
+        self.actor.load_state_dict(state_dict["actor"])
+        with torch.no_grad():  # iql.py:679: the target is re-created from qf on load
+            eng.target[0, :eng.PQ] = eng.params[0, :eng.PQ]
+        a_keys = self._keys(["actor"]) + ([] if eng.deterministic else ["log_std"])
+        step = 0
+        for sd, keys in ((state_dict["q_optimizer"], self._keys(["q1", "q2"])),
+                         (state_dict["v_optimizer"], self._keys(["v"])), (state_dict["actor_optimizer"], a_keys)):
+            for i, key in enumerate(keys):
+                st = sd["state"].get(i)
+                if st is None:
+                    continue
+                eng.view(eng.exp_avg, 0, key).copy_(st["exp_avg"].to(eng.device))
+                eng.view(eng.exp_avg_sq, 0, key).copy_(st["exp_avg_sq"].to(eng.device))
+                step = int(float(st["step"]))
+        eng.it.fill_(step)
+        eng.actor_lr.fill_(float(state_dict["actor_optimizer"]["param_groups"][0]["lr"]))
+        self.total_it = state_dict["total_it"]
+
+
+# the relabelling half of the reference module lives in relabel.py; re-exported for drop-in imports
+from .relabel import (  # noqa: E402,F401
+    RewardMLP, RewardPT, _build_mlp_reward_model, _discover_mr_snapshots, _mr_activations, _strip_compile_prefix,
+    cvar_stability_check, empirical_cvar, ensemble_predict, load_mlp_reward_model, load_pt_reward_model,
+    qlearning_dataset_bnn, qlearning_dataset_mr, qlearning_dataset_mr_ensemble, qlearning_dataset_pt)

@@ -1,0 +1,218 @@
+"""GPU parity: the IQL update (losses per step, parameters after K steps) against fixtures produced
+by the unmodified reference and against the CPU oracle.  Tolerance (fp32 mode): 1e-3 relative, as
+BASELINE.json's north_star states; observed agreement is ~1e-5."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import yaml
+
+from oracle.iql_oracle import IQLOracle, OracleHParams, nets_from_reference_modules
+from oracle.philox_oracle import cuda_randint_indices
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-3
+
+
+def _close(got, want, rtol=RTOL, atol=1e-5, what=""):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    err = np.abs(got - want)
+    tol = atol + rtol * np.abs(want)
+    assert (err <= tol).all(), f"{what}: max err {err.max():.3e} (max |want| {np.abs(want).max():.3e})"
+
+
+def _rows(biql, tab, idx, R):
+    i = torch.from_numpy(idx)
+    return biql.pack_rows(torch.from_numpy(tab["obs"])[i], torch.from_numpy(tab["act"])[i],
+                          torch.from_numpy(tab["rew"])[i], torch.from_numpy(tab["next_obs"])[i],
+                          torch.from_numpy(tab["done"])[i], R)
+
+
+@pytest.mark.parametrize("name,det", [("gauss", False), ("det", True)])
+def test_small_nets_full_tensors_vs_reference(golden_dir, name, det):
+    from iqlpref_b200 import iql as biql
+    d = np.load(os.path.join(golden_dir, f"iql_small_{name}_fp32.npz"))
+    hp = yaml.safe_load(str(d["hp"]))
+    S, A, H, B = 17, 6, 64, 64
+    qf, vf = biql.TwinQ(S, A, H), biql.ValueFunction(S, H)
+    actor = (biql.DeterministicPolicy if det else biql.GaussianPolicy)(S, A, 1.0, H)
+    for nm, mod in (("qf", qf), ("vf", vf), ("actor", actor)):
+        mod.load_state_dict({k[len("init." + nm) + 1:]: torch.from_numpy(d[k]) for k in d.files
+                             if k.startswith(f"init.{nm}.")})
+    eng = biql.BatchedIQL(S, A, 1, hidden_dim=H, batch_size=B, deterministic=det, hparams=[hp])
+    eng.adopt(0, qf, vf, actor)
+    tab = {k: d[f"table.{k}"] for k in ("obs", "act", "rew", "next_obs", "done")}
+    for k in range(d["idx"].shape[0]):
+        eng.train(_rows(biql, tab, d["idx"][k], eng.R).cuda().unsqueeze(0))
+        _close(eng.losses[0].cpu().numpy(), d["losses"][k], what=f"losses step {k}")
+    # modules were bound to the packed storage: their state_dict is the trained state
+    for nm, mod in (("qf", qf), ("vf", vf), ("actor", actor)):
+        for key, val in mod.state_dict().items():
+            _close(val.cpu().numpy(), d[f"final.{nm}.{key}"], atol=2e-6, what=f"{nm}.{key}")
+    e = eng.export(0)
+    _close(e["qt1.w1"], d["final.q_target.q1.net.2.weight"], atol=2e-6, what="target q1.w1")
+    _close(e["qt2.b2"], d["final.q_target.q2.net.4.bias"], atol=2e-6, what="target q2.b2")
+    assert int(eng.it[0].item()) == d["idx"].shape[0]
+    assert abs(float(eng.actor_lr[0].item()) - float(d["lr_final"])) < 1e-12
+
+
+CFGS = {"cfg1": (17, 6, False), "cfg2": (29, 8, False), "cfg4det": (45, 24, True)}
+
+
+def _build_cfg(biql, cfg, d, precision="fp32"):
+    S, A, det = CFGS[cfg]
+    hp = yaml.safe_load(str(d["hp"]))
+    torch.manual_seed(int(d["seed"]))
+    qf, vf = biql.TwinQ(S, A), biql.ValueFunction(S)
+    actor = (biql.DeterministicPolicy if det else biql.GaussianPolicy)(S, A, 1.0)
+    # the regenerated init must be the reference's init (same RNG consumption order)
+    for nm, mod in (("qf", qf), ("vf", vf), ("actor", actor)):
+        for key, val in mod.state_dict().items():
+            np.testing.assert_array_equal(val.numpy().reshape(-1)[::97], d[f"init.{nm}.{key}#sample"])
+    eng = biql.BatchedIQL(S, A, 1, batch_size=256, deterministic=det, hparams=[hp], precision=precision)
+    eng.adopt(0, qf, vf, actor)
+    n_rows = int(d["n_rows"])
+    rng = np.random.default_rng(int(d["seed"]) + 1000)  # same draws as oracle/gen_golden.py
+    tab = {"obs": rng.standard_normal((n_rows, S)).astype(np.float32),
+           "act": rng.uniform(-1, 1, (n_rows, A)).astype(np.float32),
+           "rew": (rng.standard_normal(n_rows) * 0.5 + 0.5).astype(np.float32),
+           "next_obs": rng.standard_normal((n_rows, S)).astype(np.float32),
+           "done": (rng.uniform(size=n_rows) < 0.05).astype(np.float32)}
+    return eng, (qf, vf, actor), tab
+
+
+@pytest.mark.parametrize("cfg", list(CFGS))
+def test_full_size_nets_vs_reference_fp32(golden_dir, cfg):
+    from iqlpref_b200 import iql as biql
+    d = np.load(os.path.join(golden_dir, f"iql_{cfg}_fp32.npz"))
+    eng, mods, tab = _build_cfg(biql, cfg, d)
+    for k in range(d["idx"].shape[0]):
+        eng.train(_rows(biql, tab, d["idx"][k], eng.R).cuda().unsqueeze(0))
+        _close(eng.losses[0].cpu().numpy(), d["losses"][k], what=f"{cfg} losses step {k}")
+    for nm, mod in zip(("qf", "vf", "actor"), mods):
+        for key, val in mod.state_dict().items():
+            v = val.cpu().numpy().reshape(-1)
+            _close(v[::97], d[f"final.{nm}.{key}#sample"], atol=2e-6, what=f"{cfg} {nm}.{key}")
+            _close(np.sqrt((v.astype(np.float64) ** 2).sum()), d[f"final.{nm}.{key}#l2"], rtol=1e-5, what="l2")
+
+
+def test_batched_agents_match_independent_oracles():
+    """N agents with different seeds / hyper-parameters in ONE launch sequence == N oracles."""
+    from iqlpref_b200 import iql as biql
+    S, A, H, B, N, K = 11, 3, 64, 128, 3, 6
+    hps = [dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.7, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4, max_steps=50),
+           dict(discount=0.95, tau=0.01, beta=10.0, iql_tau=0.9, vf_lr=1e-3, qf_lr=5e-4, actor_lr=1e-4, max_steps=4),
+           dict(discount=0.9, tau=0.05, beta=0.5, iql_tau=0.5, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-3, max_steps=1000)]
+    eng = biql.BatchedIQL(S, A, N, hidden_dim=H, batch_size=B, hparams=hps)
+    oracles = []
+    for a in range(N):
+        torch.manual_seed(100 + a)
+        qf, vf, actor = biql.TwinQ(S, A, H), biql.ValueFunction(S, H), biql.GaussianPolicy(S, A, 1.0, H)
+        with torch.no_grad():
+            actor.log_std.copy_(torch.tensor([0.3, -21.0, 2.5]))  # exercise the clamp (iql.py:473)
+        oracles.append(IQLOracle(*nets_from_reference_modules(qf, vf, actor), OracleHParams(**hps[a]), mode="fp32"))
+        eng.adopt(a, qf, vf, actor, bind=False)
+    rng = np.random.default_rng(5)
+    for k in range(K):
+        rows = []
+        for a in range(N):
+            obs = torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32)
+            act = torch.tensor(rng.uniform(-1, 1, (B, A)), dtype=torch.float32)
+            rew = torch.tensor(rng.standard_normal(B), dtype=torch.float32)
+            nobs = torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32)
+            done = torch.tensor((rng.uniform(size=B) < 0.2).astype(np.float32))
+            want = oracles[a].step(obs, act, rew, nobs, done)
+            rows.append(biql.pack_rows(obs, act, rew, nobs, done, eng.R))
+            oracles[a].last = [want["value_loss"], want["q_loss"], want["actor_loss"]]
+        eng.train(torch.stack(rows).cuda())
+        got = eng.losses.cpu().numpy()
+        for a in range(N):
+            _close(got[a], oracles[a].last, what=f"agent {a} step {k}")
+    for a in range(N):
+        e, o = eng.export(a), oracles[a].export()
+        for key in e:
+            _close(e[key], o[key], atol=2e-6, what=f"agent {a} {key}")
+        assert abs(float(eng.actor_lr[a].item()) - oracles[a].a_opt.lr) < 1e-12 * max(1.0, oracles[a].a_opt.lr)
+    s = eng.loss_sum.cpu().numpy()
+    assert np.isfinite(s).all() and (s[:, 1] > 0).all()
+
+
+def test_on_device_sampling_is_bit_exact_and_equals_explicit_batch():
+    from iqlpref_b200 import iql as biql
+    S, A, H, B, N, n = 17, 6, 64, 256, 2, 5000
+    rng = np.random.default_rng(9)
+    buf = biql.ReplayBuffer(S, A, n, "cuda")
+    buf.load_d4rl_dataset({"observations": rng.standard_normal((n, S)).astype(np.float32),
+                           "actions": rng.uniform(-1, 1, (n, A)).astype(np.float32),
+                           "rewards": rng.standard_normal(n).astype(np.float32),
+                           "next_observations": rng.standard_normal((n, S)).astype(np.float32),
+                           "terminals": rng.uniform(size=n) < 0.1})
+    engs = []
+    for _ in range(2):
+        eng = biql.BatchedIQL(S, A, N, hidden_dim=H, batch_size=B, seeds=[3, 4])
+        for a in range(N):
+            torch.manual_seed(50 + a)
+            eng.adopt(a, biql.TwinQ(S, A, H), biql.ValueFunction(S, H), biql.GaussianPolicy(S, A, 1.0, H), bind=False)
+        engs.append(eng)
+    sampled, explicit = engs
+    sampled.attach_replay(buf, record_indices=True)
+    for k in range(3):
+        sampled.train()  # on-device Philox sampling
+        idx = sampled.last_indices.cpu().numpy()
+        for a in range(N):
+            np.testing.assert_array_equal(idx[a], cuda_randint_indices(3 + a, 4 * k, n, B))
+        explicit.train(buf._table[sampled.last_indices])
+        assert torch.equal(sampled.losses, explicit.losses)
+    assert torch.equal(sampled.params, explicit.params)
+    assert sampled.rng[:, 1].tolist() == [12, 12]
+
+
+def test_implicit_q_learning_dropin_and_checkpoint_roundtrip():
+    from iqlpref_b200 import iql as biql
+    S, A, B = 17, 6, 256
+    torch.manual_seed(0)
+    qf, vf, actor = biql.TwinQ(S, A).cuda(), biql.ValueFunction(S).cuda(), biql.GaussianPolicy(S, A, 1.0).cuda()
+    mk = lambda m: torch.optim.Adam(m.parameters(), lr=3e-4)
+    orc = IQLOracle(*nets_from_reference_modules(qf.cpu(), vf.cpu(), actor.cpu()), OracleHParams(max_steps=100))
+    qf, vf, actor = qf.cuda(), vf.cuda(), actor.cuda()
+    tr = biql.ImplicitQLearning(1.0, actor, mk(actor), qf, mk(qf), vf, mk(vf), max_steps=100, device="cuda")
+    rng = np.random.default_rng(0)
+
+    def batch():
+        return [torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32),
+                torch.tensor(rng.uniform(-1, 1, (B, A)), dtype=torch.float32),
+                torch.tensor(rng.standard_normal((B, 1)), dtype=torch.float32),
+                torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32),
+                torch.tensor((rng.uniform(size=(B, 1)) < 0.1).astype(np.float32))]
+    for _ in range(3):
+        b = batch()
+        want = orc.step(b[0], b[1], b[2].squeeze(-1), b[3], b[4].squeeze(-1))
+        got = tr.train([t.cuda() for t in b])
+        assert set(got) == {"value_loss", "q_loss", "actor_loss"}
+        _close([got[k] for k in sorted(got)], [want[k] for k in sorted(want)], what="dropin losses")
+    assert tr.total_it == 3
+    _close(tr.qf.q1.net[2].weight.detach().cpu().numpy(), orc.export()["q1.w1"], atol=2e-6)
+    _close(tr.q_target.q2.net[0].weight.detach().cpu().numpy(), orc.export()["qt2.w0"], atol=2e-6)
+    sd = tr.state_dict()
+    assert set(sd) == {"qf", "q_optimizer", "vf", "v_optimizer", "actor", "actor_optimizer", "actor_lr_schedule", "total_it"}
+    assert float(sd["q_optimizer"]["state"][0]["step"]) == 3.0
+    # resume in a fresh trainer and continue: same trajectory as the uninterrupted oracle
+    torch.manual_seed(1)
+    qf2, vf2, actor2 = biql.TwinQ(S, A).cuda(), biql.ValueFunction(S).cuda(), biql.GaussianPolicy(S, A, 1.0).cuda()
+    tr2 = biql.ImplicitQLearning(1.0, actor2, mk(actor2), qf2, mk(qf2), vf2, mk(vf2), max_steps=100, device="cuda")
+    tr2.load_state_dict(sd)
+    assert tr2.total_it == 3
+    # iql.py:679 quirk: the target is re-created from qf on load
+    assert torch.equal(tr2.q_target.q1.net[0].weight, tr2.qf.q1.net[0].weight)
+    with pytest.raises(RuntimeError):
+        bad = batch()
+        bad[1] = bad[1][:, :3]
+        tr.train([t.cuda() for t in bad])
+
+
+def test_no_cpu_path():
+    from iqlpref_b200 import iql as biql
+    with pytest.raises(RuntimeError):
+        biql.BatchedIQL(3, 2, 1, device="cpu")

@@ -122,6 +122,16 @@ int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_l
 /* Number of kernels one iqlb_agents_step enqueues (for launch accounting). */
 int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled);
 
+/* Per-kernel timing of the step with CUDA events on the launching stream (bench.py's roofline leg).
+ * profile(h,1) zeroes the totals and makes every later step record one event per launch;
+ * profile_collect(h) waits for the last recorded step and adds its per-launch times to the totals
+ * (call it after each profiled step); profile_read returns kernel i's name, total ms and the number
+ * of collected steps (error once i >= number of launches in a step). */
+int iqlb_agents_profile(iqlb_agents* h, int32_t enable);
+int iqlb_agents_profile_collect(iqlb_agents* h);
+int iqlb_agents_profile_read(iqlb_agents* h, int32_t i, const char** host_name, double* host_ms_total,
+                             int32_t* host_steps);
+
 /* Debug/parity hook: copy an internal scratch tensor to dst (device).  which: 0 H1, 1 H2,
  * 2 head_out, 3 d_out, 4 dH2, 5 dH1, 6 grads, 7 batch.  Returns bytes via *nbytes if dst NULL. */
 int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, int64_t* nbytes, void* stream);

@@ -313,42 +313,75 @@ static int build_tasks(iqlb_agents* h) {
   return IQLB_OK;
 }
 
+// Launch bookkeeping: when profiling is on, an event is recorded after every launch of the step.
+struct Prof {
+  iqlb_agents* h; cudaStream_t st; int i = 0;
+  Prof(iqlb_agents* h_, cudaStream_t st_) : h(h_), st(st_) {
+    if (h->prof) cudaEventRecord(h->ev[0], st);
+  }
+  void mark(const char* name) {
+    if (h->prof && i < iqlb_agents::kMaxProf) {
+      h->prof_name[i] = name;
+      cudaEventRecord(h->ev[i + 1], st);
+    }
+    ++i;
+  }
+  void done() {
+    if (h->prof) h->prof_n = i < iqlb_agents::kMaxProf ? i : iqlb_agents::kMaxProf;
+    h->launches_last = i;
+  }
+};
+
 static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   const Layout& L = h->L;
   const int N = h->desc.n_agents;
   int rc;
+  Prof pf(h, st);
   if (sampled) {
     IQLB_REQUIRE(h->table != nullptr, "no replay table attached (iqlb_agents_set_replay)");
     rc = launch_gather(h->table, h->n_rows, L.R, 2 * L.S + L.A, h->reward_cols, h->reward_variant, h->rng, nullptr, N,
                        L.B, h->idx_out, h->batch, st);
     if (rc) return rc;
+    pf.mark("replay_gather");
   }
   if (h->desc.precision == 1) {
     if ((rc = bf16_step_gemms_fwd(h, st))) return rc;
+    pf.mark("bf16_fwd");
   } else {
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd0, N * kStreams, L.B, L.H, false, st))) return rc;
+    pf.mark("gemm_fwd_l0");
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd1, N * kStreams, L.B, L.H, false, st))) return rc;
+    pf.mark("gemm_fwd_l1");
   }
   head_fwd_kernel<<<dim3((L.B + 7) / 8, kStreams, N), 256, 0, st>>>(L, h->params, h->target, h->H2, h->head_out);
   IQLB_LAUNCH_CHECK();
+  pf.mark("head_fwd");
   const int lb = (L.B + 31) / 32 * 32;
   loss_kernel<<<N, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
                                 h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0);
   IQLB_LAUNCH_CHECK();
+  pf.mark("loss");
   head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
   IQLB_LAUNCH_CHECK();
+  pf.mark("head_bwd");
   if (h->desc.precision == 1) {
     if ((rc = bf16_step_gemms_bwd(h, st))) return rc;
+    pf.mark("bf16_bwd");
   } else {
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw1, N * kTrain, L.H, L.H, false, st))) return rc;
+    pf.mark("gemm_bwd_w1");
     if ((rc = launch_grouped_gemm(GEMM_BWD_DATA, h->t_bd1, N * kTrain, L.B, L.H, false, st))) return rc;
+    pf.mark("gemm_bwd_d1");
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw0, N * kTrain, L.H, L.Dq, true, st))) return rc;
+    pf.mark("gemm_bwd_w0");
   }
   const int64_t n4 = L.Pstride / 4;
   adam_polyak_kernel<<<dim3((unsigned)((n4 + 255) / 256), N), 256, 0, st>>>(
       L, (float4*)h->params, (float4*)h->exp_avg, (float4*)h->exp_avg_sq, (float4*)h->target, (const float4*)h->grads,
       h->scal, nullptr);
   IQLB_LAUNCH_CHECK();
+  pf.mark("adam_polyak");
+  pf.done();
   return IQLB_OK;
 }
 
@@ -415,6 +448,7 @@ extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
   bf16_destroy(h);
   cudaFree(h->batch); cudaFree(h->H1); cudaFree(h->H2); cudaFree(h->head_out); cudaFree(h->d_out);
   cudaFree(h->dH2); cudaFree(h->dH1); cudaFree(h->grads); cudaFree(h->scal);
+  for (int i = 0; i <= iqlb_agents::kMaxProf; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   cudaFree(h->t_fwd0); cudaFree(h->t_fwd1); cudaFree(h->t_bw1); cudaFree(h->t_bd1); cudaFree(h->t_bw0);
   delete h;
   return IQLB_OK;
@@ -457,9 +491,46 @@ extern "C" int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, fl
 
 extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled) {
   if (!h) return 0;
+  if (h->launches_last > 0) return h->launches_last;  // counted by the last step
   // gather + fwd0 + fwd1 + head_fwd + loss + head_bwd + bw1 + bd1 + bw0 + adam
-  const int gemms = 5;
-  return (sampled ? 1 : 0) + gemms + 4;
+  return (sampled ? 1 : 0) + 5 + 4;
+}
+
+extern "C" int iqlb_agents_profile(iqlb_agents* h, int32_t enable) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  if (enable && !h->ev[0]) {
+    for (int i = 0; i <= iqlb_agents::kMaxProf; ++i) IQLB_CUDA(cudaEventCreate(&h->ev[i]));
+  }
+  h->prof = enable != 0;
+  if (enable) {
+    for (int i = 0; i < iqlb_agents::kMaxProf; ++i) h->prof_ms[i] = 0.0;
+    h->prof_steps = 0;
+    h->prof_n = 0;
+  }
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_profile_collect(iqlb_agents* h) {
+  IQLB_REQUIRE(h != nullptr && h->prof, "profiling is off");
+  if (h->prof_n == 0) return IQLB_OK;
+  IQLB_CUDA(cudaEventSynchronize(h->ev[h->prof_n]));
+  for (int i = 0; i < h->prof_n; ++i) {
+    float ms = 0.f;
+    IQLB_CUDA(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+    h->prof_ms[i] += ms;
+  }
+  h->prof_steps += 1;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_profile_read(iqlb_agents* h, int32_t i, const char** host_name, double* host_ms_total,
+                                        int32_t* host_steps) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  IQLB_REQUIRE(i >= 0 && i < h->prof_n, "kernel index out of range");
+  if (host_name) *host_name = h->prof_name[i];
+  if (host_ms_total) *host_ms_total = h->prof_ms[i];
+  if (host_steps) *host_steps = h->prof_steps;
+  return IQLB_OK;
 }
 
 extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, int64_t* nbytes, void* stream) {

@@ -103,4 +103,12 @@ struct iqlb_agents {
   iqlb::StepScalars* scal = nullptr;
   iqlb::GemmTask *t_fwd0 = nullptr, *t_fwd1 = nullptr, *t_bw1 = nullptr, *t_bd1 = nullptr, *t_bw0 = nullptr;
   void* bf16_state = nullptr;  // precision==1 extension (tcgen05 path)
+  // per-kernel CUDA-event timing (iqlb_agents_profile): ev[i], ev[i+1] bracket launch i of a step
+  static constexpr int kMaxProf = 24;
+  bool prof = false;
+  cudaEvent_t ev[kMaxProf + 1] = {};
+  const char* prof_name[kMaxProf] = {};
+  double prof_ms[kMaxProf] = {};
+  int prof_n = 0, prof_steps = 0;
+  int launches_last = 0;
 };

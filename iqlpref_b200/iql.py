@@ -485,6 +485,22 @@ class BatchedIQL:
     def launches_per_step(self, sampled: bool) -> int:
         return int(self.lib.iqlb_agents_launches_per_step(self._h, int(sampled)))
 
+    # ---- per-kernel timing (CUDA events on the launching stream; used by bench.py) ----------------------
+    def profile(self, enable: bool):
+        _lib.check(self.lib.iqlb_agents_profile(self._h, int(bool(enable))), "iqlb_agents_profile")
+
+    def profile_collect(self):
+        _lib.check(self.lib.iqlb_agents_profile_collect(self._h), "iqlb_agents_profile_collect")
+
+    def profile_read(self) -> List[Dict[str, Any]]:
+        """[{"kernel": name, "ms_per_step": t}] for every launch of one step, in launch order."""
+        out, i = [], 0
+        name, ms, steps = C.c_char_p(), C.c_double(), C.c_int32()
+        while self.lib.iqlb_agents_profile_read(self._h, i, C.byref(name), C.byref(ms), C.byref(steps)) == 0:
+            out.append({"kernel": name.value.decode(), "ms_per_step": ms.value / max(steps.value, 1)})
+            i += 1
+        return out
+
     def debug_tensor(self, which: int) -> torch.Tensor:
         nbytes = C.c_int64()
         _lib.check(self.lib.iqlb_agents_debug_copy(self._h, which, None, C.byref(nbytes), None), "debug")

@@ -92,6 +92,10 @@ def ensemble_predict(members: Sequence[Sequence[Any]], X, reduce: str = "mean", 
     n = X.shape[0]
     n_tail = S if reduce == "mean" else cvar_n_tail(alpha, S)
     out = torch.empty(n, dtype=torch.float32, device=dev)
+    if n == 0:  # nothing to launch (an empty tensor has no device pointer)
+        res = [out] + ([torch.empty((S, 0), dtype=torch.float32, device=dev)] if return_preds else []) + \
+              ([torch.empty((S, 0), dtype=torch.uint8, device=dev)] if return_selection else [])
+        return res[0] if len(res) == 1 else tuple(res)
     preds = torch.empty((S, n), dtype=torch.float32, device=dev) if return_preds else None
     sel = torch.empty((S, n), dtype=torch.uint8, device=dev) if return_selection else None
     w_arr = (C.c_int32 * len(widths))(*widths)

@@ -189,6 +189,15 @@ int iqlb_relabel_pt(const iqlb_pt_desc* d, const float* weights, const float* ob
 int iqlb_pt_forward(const iqlb_pt_desc* d, const float* weights, const float* states, const float* actions,
                     const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out, void* stream);
 
+/* Diagnostic: one CTA computes D[128][n] (fp32, row-major) = A * B with tcgen05.mma from two bf16
+ * operand images (128-byte-swizzled column blocks of 64, see csrc/umma.cuh).  a_mn / b_mn select
+ * MN-major (1: image columns are the M/N index, starting at column a_off) or K-major (0: image rows
+ * are the M/N index, starting at row a_off); *_rows_total = rows of the whole image.  Used by
+ * tests/test_gpu_umma.py to pin the descriptors against numpy for every arrangement the step uses. */
+int iqlb_selftest_umma(const void* a_img, int64_t a_bytes, const void* b_img, int64_t b_bytes, int32_t a_mn,
+                       int32_t a_rows_total, int32_t a_off, int32_t b_mn, int32_t b_rows_total, int32_t b_off,
+                       int32_t n, int32_t ksteps, float* d_out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Host helper (plain C loop, no GPU): the keep-mask / episode-step scan every qlearning_dataset_*
  * starts with (iql.py:701-716, 1236-1253).  terminals/timeouts are host uint8[n]; timeouts may be

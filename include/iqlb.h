@@ -119,6 +119,10 @@ int iqlb_agents_step(iqlb_agents* h, const float* batch, void* stream);
  * losses[n_agents][3] into host_losses, then a stream synchronise (the reference's .item()). */
 int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_losses, void* stream);
 
+/* Tell the library that the caller wrote params/target directly (adopting modules, loading a
+ * checkpoint): precision 1 rebuilds the bf16 operand images of the weights; precision 0: no-op. */
+int iqlb_agents_refresh(iqlb_agents* h, void* stream);
+
 /* Number of kernels one iqlb_agents_step enqueues (for launch accounting). */
 int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled);
 

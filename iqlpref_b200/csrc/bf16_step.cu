@@ -1,9 +1,617 @@
-// bf16 tcgen05/TMEM path of the IQL step (precision == 1).  Placeholder until the UMMA kernels land.
+// bf16 tcgen05/TMEM path of the IQL step (precision == 1).
+// Replaces the 7 MLP forwards and 4 MLP backwards of ImplicitQLearning.train
+// (/root/reference/algorithms/offline/iql.py:581-637) with three tensor-core kernels:
+//
+//   bf16_fwd_kernel         (half-batch, stream, agent): X -> relu(X W0^T + b0) -> relu(H1 W1^T + b1)
+//                           -> head (W2, b2, tanh for the actor); keeps H1, H2 (bf16 images) and the
+//                           ReLU masks of the four trainable streams for the backward pass.
+//   bf16_bwd_data_kernel    (half-batch, net, agent): dH2 = (dz W2) * relu'(H2) on CUDA cores,
+//                           dH1 = (dH2 W1) * relu'(H1) on the tensor cores (W1 read MN-major).
+//   bf16_bwd_weight_kernel  (128 output features, net, agent): dW1 = dH2^T H1, dW0 = dH1^T X,
+//                           dW2 = dz^T H2, db1, db0 - all as MN-major x MN-major MMAs over the
+//                           batch dimension (bias gradients ride on a ones column of the dz image).
+//
+// All operands are bf16 "images" (umma.cuh): identical bytes in HBM and in shared memory, moved by
+// 1-D bulk copies.  Accumulation is fp32 in TMEM; parameters, Adam state and the Polyak target stay
+// fp32 (iql_step.cu), and the Adam kernel refreshes the bf16 weight images it just updated.
 #include "iql_step.cuh"
+#include "umma.cuh"
 
 namespace iqlb {
-int bf16_create(iqlb_agents*) { return fail(IQLB_ERR_UNSUPPORTED, "bf16 tcgen05 path not built yet%s", ""); }
-void bf16_destroy(iqlb_agents*) {}
-int bf16_step_gemms_fwd(iqlb_agents*, cudaStream_t) { return IQLB_ERR_UNSUPPORTED; }
-int bf16_step_gemms_bwd(iqlb_agents*, cudaStream_t) { return IQLB_ERR_UNSUPPORTED; }
+using namespace umma;
+
+// ------------------------------------------------------------------------------------------------
+// params/target fp32 -> bf16 weight images (after adopt / load_state_dict; Adam keeps them fresh)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) shadow_refresh_kernel(BfParams P, const float* __restrict__ params,
+                                                             const float* __restrict__ target) {
+  const Layout& L = P.L;
+  const int agent = blockIdx.y;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= L.off_logstd) return;
+  int net;
+  int64_t off;
+  if (!shadow_loc(L, P.KXB, e, net, off)) return;
+  uint8_t* w = P.wimg + (int64_t)agent * P.agent_w_bytes;
+  *reinterpret_cast<__nv_bfloat16*>(w + (int64_t)net * P.net_bytes + off) = __float2bfloat16_rn(params[(int64_t)agent * L.Pstride + e]);
+  if (e < L.PQ)
+    *reinterpret_cast<__nv_bfloat16*>(w + (int64_t)(net + 4) * P.net_bytes + off) =
+        __float2bfloat16_rn(target[(int64_t)agent * L.PQstride + e]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// packed fp32 batch rows -> bf16 input images  X_sa = [obs|act|0..], X_next = [next_obs|0..]
+// one thread per 16-byte chunk (8 columns)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __restrict__ batch) {
+  const Layout& L = P.L;
+  const int agent = blockIdx.y;
+  const int chunks_per_row = P.KXB * 8;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L.B * chunks_per_row) return;
+  const int b = i / chunks_per_row, ch = i % chunks_per_row;
+  const float* row = batch + ((int64_t)agent * L.B + b) * L.R;
+  uint32_t sa[4], nx[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int c = ch * 8 + 2 * q;
+    const float a0 = c < L.Dq ? row[c] : 0.f, a1 = c + 1 < L.Dq ? row[c + 1] : 0.f;
+    const float n0 = c < L.S ? row[L.Dq + c] : 0.f, n1 = c + 1 < L.S ? row[L.Dq + c + 1] : 0.f;
+    sa[q] = pack_bf16(a0, a1);
+    nx[q] = pack_bf16(n0, n1);
+  }
+  const int64_t off = image_off(L.B, b, ch * 8);
+  *reinterpret_cast<uint4*>(P.xsa + (int64_t)agent * P.x_bytes + off) = make_uint4(sa[0], sa[1], sa[2], sa[3]);
+  *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
+}
+
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+
+// store 8 consecutive columns (one 16-byte chunk) of tile row `row` into a tile image with 128 rows
+__device__ __forceinline__ void st_chunk(uint8_t* tile, int row, int col0, const float* v) {
+  const int off = (col0 >> 6) * 16384 + row * 128 + ((((col0 & 63) >> 3) ^ (row & 7)) << 4);
+  *reinterpret_cast<uint4*>(tile + off) =
+      make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Forward.  grid (B/128, 7 streams, agents), 128 threads, 1 CTA per SM.
+// Shared memory (H = 256): [W0 image KXB*32K | X tile KXB*16K | W1 ring (4-KXB)*32K | H tile 64K | ctrl]
+// W1 streams in as four 32 KB K-blocks; the last KXB of them land in the W0 region once layer 0
+// has been consumed.  TMEM: layer-0 accumulator in columns [0,256), layer-1 in [256,512).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const float* __restrict__ params,
+                                                          const float* __restrict__ target,
+                                                          float* __restrict__ head_out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const Layout& L = P.L;
+  const int half = blockIdx.x, s = blockIdx.y, agent = blockIdx.z;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int KXB = P.KXB, nring = 4 - KXB;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t oW0 = 0, oX = (uint32_t)KXB * 32768u, oRing = oX + (uint32_t)KXB * 16384u,
+                 oH = oRing + (uint32_t)nring * 32768u, oCtrl = oH + 65536u;
+  const uint32_t bar_l0 = sbase + oCtrl, bar_w1 = bar_l0 + 8, bar_mma0 = bar_l0 + 40, bar_mma1 = bar_l0 + 48;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 56);
+  const int net = net_of_stream(s), t = train_index(s);
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const uint8_t* wnet = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net * P.net_bytes;
+  const uint8_t* ximg = (s == 0 ? P.xnext : P.xsa) + (int64_t)agent * P.x_bytes;
+  const float* fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
+                                       : params + (int64_t)agent * L.Pstride + L.net_off(s);
+  auto chunk_off = [&](int c) -> uint32_t { return c < nring ? oRing + (uint32_t)c * 32768u : oW0 + (uint32_t)(c - nring) * 32768u; };
+
+  if (tid == 0) {
+    if (sbase & 1023u) __trap();
+    mbar_init(bar_l0, 1);
+    for (int c = 0; c < 4; ++c) mbar_init(bar_w1 + 8 * c, 1);
+    mbar_init(bar_mma0, 1);
+    mbar_init(bar_mma1, 1);
+    fence_barrier_init();
+    mbar_expect_tx(bar_l0, (uint32_t)KXB * (32768u + 16384u));
+    bulk_g2s(sbase + oW0, wnet, (uint32_t)KXB * 32768u, bar_l0);
+    for (int cb = 0; cb < KXB; ++cb)
+      bulk_g2s(sbase + oX + (uint32_t)cb * 16384u, ximg + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, 16384u, bar_l0);
+    for (int c = 0; c < nring; ++c) {
+      mbar_expect_tx(bar_w1 + 8 * c, 32768u);
+      bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
+    }
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(sbase + oCtrl + 56, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (tid == 0) {
+    mbar_wait(bar_l0, 0);
+    tc_fence_after();
+    gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oW0, L.H, 0), 256, (in + 15) / 16, false);
+    mma_commit(bar_mma0);
+  }
+  __syncwarp();
+  mbar_wait(bar_mma0, 0);
+  tc_fence_after();
+  if (tid == 0) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
+    for (int c = nring; c < 4; ++c) {
+      mbar_expect_tx(bar_w1 + 8 * c, 32768u);
+      bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
+    }
+  }
+  __syncwarp();
+  const int row = tid, brow = half * 128 + row;
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+  uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+  {  // epilogue 0: H1 = relu(acc + b0) -> bf16 tile (A operand of layer 1)
+    const float* b0 = fnet + L.b0(in);
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      float v[32];
+      tmem_ld32(lane_base + (uint32_t)c0, v);
+      tmem_ld_wait();
+      uint32_t m = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float x = fmaxf(v[j] + __ldg(b0 + c0 + j), 0.f);
+        v[j] = x;
+        m |= (x > 0.f ? 1u : 0u) << j;
+      }
+      if (m1) m1[c0 >> 5] = m;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
+    }
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  if (tid == 0) {
+    tc_fence_after();
+    if (t >= 0) {
+      uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+      for (int cb = 0; cb < 4; ++cb)
+        bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+      bulk_commit();
+    }
+    for (int kb = 0; kb < 4; ++kb) {
+      mbar_wait(bar_w1 + 8 * kb, 0);
+      tc_fence_after();
+      gemm_issue(tmem + 256, operand_k_major(sbase + oH + (uint32_t)kb * 16384u, 128, 0),
+                 operand_k_major(sbase + chunk_off(kb), L.H, 0), 256, 4, kb > 0);
+    }
+    mma_commit(bar_mma1);
+    if (t >= 0) bulk_wait_read0();  // the H1 tile must be out before epilogue 1 overwrites it with H2
+  }
+  __syncwarp();
+  mbar_wait(bar_mma1, 0);
+  tc_fence_after();
+  __syncthreads();
+  {  // epilogue 1: H2 = relu(acc + b1); head = H2 . W2 + b2
+    const float* b1 = fnet + L.b1(in);
+    const float* W2 = fnet + L.w2(in);
+    float acc[kOutMax];
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o) acc[o] = 0.f;
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      float v[32];
+      tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
+      tmem_ld_wait();
+      uint32_t m = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float x = fmaxf(v[j] + __ldg(b1 + c0 + j), 0.f);
+        v[j] = x;
+        m |= (x > 0.f ? 1u : 0u) << j;
+      }
+#pragma unroll
+      for (int o = 0; o < kOutMax; ++o) {
+        if (o < nout) {
+          const float* w = W2 + (int64_t)o * L.H + c0;
+          float a = acc[o];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) a = fmaf(v[j], __ldg(w + j), a);
+          acc[o] = a;
+        }
+      }
+      if (t >= 0) {
+        m2[c0 >> 5] = m;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
+      }
+    }
+    const float* b2 = fnet + L.b2(in, nout);
+    float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o) {
+      if (o < nout) {
+        const float z = acc[o] + __ldg(b2 + o);
+        if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
+        else ho[(int64_t)s * L.B + brow] = z;
+      }
+    }
+  }
+  if (t >= 0) {
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+      for (int cb = 0; cb < 4; ++cb)
+        bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+      bulk_commit();
+      bulk_wait_read0();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward, data gradients.  grid (B/128, 4 trainable nets, agents), 128 threads.
+// Shared memory: [dH2 tile 64K | W1 image 128K | 2 x 16K output staging | ctrl].
+// dH2[b,j] = relu'(H2[b,j]) * sum_o dz[b,o] W2[o,j] on CUDA cores (one row per thread), then
+// dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
+// each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
+                                                               const float* __restrict__ d_out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const Layout& L = P.L;
+  const int half = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
+  const int s = train_stream(t), net = net_of_stream(s);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
+  const uint32_t bar_w = sbase + oCtrl, bar_mma = bar_w + 32;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 64);
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const uint8_t* w1img = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net * P.net_bytes + P.w0_bytes;
+  const float* fnet = params + (int64_t)agent * L.Pstride + L.net_off(s);
+  const int64_t at = (int64_t)agent * kTrain + t;
+
+  if (tid == 0) {
+    if (sbase & 1023u) __trap();
+    for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
+    fence_barrier_init();
+    for (int ib = 0; ib < 4; ++ib) {
+      mbar_expect_tx(bar_w + 8 * ib, 32768u);
+      bulk_g2s(sbase + oW + (uint32_t)ib * 32768u, w1img + (int64_t)ib * 32768, 32768u, bar_w + 8 * ib);
+    }
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(sbase + oCtrl + 64, 256);
+  }
+  const int row = tid, brow = half * 128 + row;
+  {  // dH2 tile
+    const float* W2 = fnet + L.w2(in);
+    const float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
+    const int drow0 = (t == 3) ? 3 : t;
+    float dz[kOutMax];
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o) dz[o] = o < nout ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
+    const uint32_t* m2 = P.mask2 + (at * L.B + brow) * (L.H / 32);
+    for (int c0 = 0; c0 < 256; c0 += 8) {
+      const uint32_t m = m2[c0 >> 5] >> (c0 & 31);
+      float g[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = 0.f;
+#pragma unroll
+      for (int o = 0; o < kOutMax; ++o) {
+        if (o < nout) {
+          const float* w = W2 + (int64_t)o * L.H + c0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = fmaf(dz[o], __ldg(w + j), g[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = ((m >> j) & 1u) ? g[j] : 0.f;
+      st_chunk(smem + oA, row, c0, g);
+    }
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  if (tid == 0) {
+    uint8_t* dh2 = P.dh2 + at * P.h_bytes;
+    for (int cb = 0; cb < 4; ++cb)
+      bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
+    bulk_commit();
+    const Operand a = operand_k_major(sbase + oA, 128, 0);
+    for (int ib = 0; ib < 4; ++ib) {
+      mbar_wait(bar_w + 8 * ib, 0);
+      tc_fence_after();
+      gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
+      mma_commit(bar_mma + 8 * ib);
+    }
+  }
+  __syncwarp();
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t* m1 = P.mask1 + (at * L.B + brow) * (L.H / 32);
+  uint8_t* dh1 = P.dh1 + at * P.h_bytes;
+  for (int ib = 0; ib < 4; ++ib) {
+    if (ib >= 2) {  // staging slot ib&1 was handed to a bulk store two iterations ago
+      if (tid == 0) bulk_wait_read1();
+      __syncthreads();
+    }
+    mbar_wait(bar_mma + 8 * ib, 0);
+    tc_fence_after();
+    uint8_t* stage = smem + oStage + (ib & 1) * 16384;
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      float v[32];
+      tmem_ld32(lane_base + 64u * ib + 32u * hh, v);
+      tmem_ld_wait();
+      const uint32_t m = m1[ib * 2 + hh];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * hh + 8 * q, v + 8 * q);
+    }
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oStage + (uint32_t)(ib & 1) * 16384u, 16384u);
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait_read0();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward, weight gradients.  grid (H/128 output-feature tiles, 4 nets, agents), 128 threads.
+// Every product reduces over the batch (K = B), with both operands read MN-major from images whose
+// rows are batch rows.  blk = B*128 bytes = one 64-column block of a batch-row image.
+// Shared memory: [bufA 2 blk | bufB 4 blk | dz image 1 blk | ctrl]
+//   phase 1: bufA = dH2[:, tile], bufB = H1          -> dW1 tile (TMEM 0..255), db1 (col 352+out)
+//   phase 2: bufA = dH1[:, tile], bufB[0..] = X_sa   -> dW0 tile (TMEM 256..), db0 (col 384+out)
+//            bufB[2 blk..] = H2[:, tile]             -> dW2^T tile (TMEM 416 + o)
+// The dz image holds dz[b, 0..out) and a column of ones at `out`, so bias gradients are MMA columns.
+// Thread r of the CTA owns output feature 128*tile + r when draining TMEM into the fp32 gradients.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const Layout& L = P.L;
+  const int ot = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
+  const int s = train_stream(t);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t blk = (uint32_t)L.B * 128u;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t oA = 0, oB = 2 * blk, oZ = 6 * blk, oCtrl = 7 * blk;
+  const uint32_t bar_ld1 = sbase + oCtrl, bar_ld2 = bar_ld1 + 8, bar_ld3 = bar_ld1 + 16, bar_p1 = bar_ld1 + 24,
+                 bar_p2 = bar_ld1 + 32;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 40);
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const int64_t at = (int64_t)agent * kTrain + t;
+  const int ksteps = L.B / 16;
+  const int n0 = (in + 15) / 16 * 16;
+
+  if (tid == 0) {
+    if (sbase & 1023u) __trap();
+    for (int i = 0; i < 5; ++i) mbar_init(bar_ld1 + 8 * i, 1);
+    fence_barrier_init();
+    mbar_expect_tx(bar_ld1, 7 * blk);
+    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
+    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);
+    bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(sbase + oCtrl + 40, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
+  if (tid == 0) {
+    mbar_wait(bar_ld1, 0);
+    tc_fence_after();
+    const Operand a1 = operand_mn_major(sbase + oA, L.B, 0, 0);
+    gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
+    gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
+    mma_commit(bar_p1);
+  }
+  __syncwarp();
+  mbar_wait(bar_p1, 0);
+  tc_fence_after();
+  if (tid == 0) {  // phase-1 operands consumed: refill
+    mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
+    bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
+    bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
+    mbar_expect_tx(bar_ld3, 2 * blk);
+    bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
+  }
+  __syncwarp();
+  const int f = ot * 128 + tid;  // output feature owned by this thread
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  float* gnet = grads + (int64_t)agent * L.Pstride + L.net_off(s);
+  {  // drain dW1 row f and db1[f]
+    float* gw1 = gnet + L.w1(in) + (int64_t)f * L.H;
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(gw1) & 15) == 0;
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      float v[32];
+      tmem_ld32(lane_base + (uint32_t)c0, v);
+      tmem_ld_wait();
+      if (vec_ok) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(gw1 + c0 + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      } else {  // networks after Q1 start at odd float offsets in the packed parameter layout
+#pragma unroll
+        for (int j = 0; j < 32; ++j) gw1[c0 + j] = v[j];
+      }
+    }
+    float v[32];
+    tmem_ld32(lane_base + 352u, v);
+    tmem_ld_wait();
+    float db = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+    gnet[L.b1(in) + f] = db;
+  }
+  if (tid == 0) {
+    mbar_wait(bar_ld2, 0);
+    tc_fence_after();
+    const Operand a0 = operand_mn_major(sbase + oA, L.B, 0, 0);
+    gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
+    gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
+    mbar_wait(bar_ld3, 0);
+    tc_fence_after();
+    gemm_issue(tmem + 416, operand_mn_major(sbase + oB + 2 * blk, L.B, 0, 0), z, 32, ksteps, false);
+    mma_commit(bar_p2);
+  }
+  __syncwarp();
+  mbar_wait(bar_p2, 0);
+  tc_fence_after();
+  {  // drain dW0 row f, db0[f], dW2[:, f]
+    float* gw0 = gnet + L.w0() + (int64_t)f * in;
+    for (int c0 = 0; c0 < n0; c0 += 16) {
+      float v[16];
+      tmem_ld16(lane_base + 256u + (uint32_t)c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (c0 + j < in) gw0[c0 + j] = v[j];
+    }
+    float v[32];
+    tmem_ld32(lane_base + 384u, v);
+    tmem_ld_wait();
+    float db = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+    gnet[L.b0(in) + f] = db;
+    tmem_ld32(lane_base + 416u, v);
+    tmem_ld_wait();
+    float* gw2 = gnet + L.w2(in);
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o)
+      if (o < nout) gw2[(int64_t)o * L.H + f] = v[o];
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u; }
+static size_t bwd_data_smem() { return 65536u + 131072u + 32768u + 128u; }
+static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
+
+int bf16_create(iqlb_agents* h) {
+  const Layout& L = h->L;
+  IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
+  IQLB_REQUIRE(L.B == 128 || L.B == 256, "the tcgen05 path needs batch_size 128 or 256");
+  IQLB_REQUIRE(L.A <= kOutMax && L.Dq <= 128, "action_dim <= 24 and state_dim + action_dim <= 128");
+  Bf16State* st = new (std::nothrow) Bf16State();
+  if (!st) return fail(IQLB_ERR_NOMEM, "out of host memory%s", "");
+  h->bf16_state = st;
+  BfParams& P = st->P;
+  P.L = L;
+  P.KXB = (L.Dq + 63) / 64;
+  P.w0_bytes = (int64_t)P.KXB * L.H * 128;
+  P.net_bytes = P.w0_bytes + (int64_t)(L.H / 64) * L.H * 128;
+  P.agent_w_bytes = 6 * P.net_bytes;
+  P.x_bytes = (int64_t)P.KXB * L.B * 128;
+  P.h_bytes = (int64_t)(L.H / 64) * L.B * 128;
+  P.z_bytes = (int64_t)L.B * 128;
+  const int64_t N = h->desc.n_agents;
+  auto alloc = [&](void** p, int64_t bytes) -> int {
+    IQLB_CUDA(cudaMalloc(p, (size_t)bytes));
+    IQLB_CUDA(cudaMemset(*p, 0, (size_t)bytes));
+    return IQLB_OK;
+  };
+  int rc = IQLB_OK;
+  if (!rc) rc = alloc((void**)&P.wimg, N * P.agent_w_bytes);
+  if (!rc) rc = alloc((void**)&P.xsa, N * P.x_bytes);
+  if (!rc) rc = alloc((void**)&P.xnext, N * P.x_bytes);
+  if (!rc) rc = alloc((void**)&P.h1, N * kTrain * P.h_bytes);
+  if (!rc) rc = alloc((void**)&P.h2, N * kTrain * P.h_bytes);
+  if (!rc) rc = alloc((void**)&P.dh2, N * kTrain * P.h_bytes);
+  if (!rc) rc = alloc((void**)&P.dh1, N * kTrain * P.h_bytes);
+  if (!rc) rc = alloc((void**)&P.dz, N * kTrain * P.z_bytes);
+  if (!rc) rc = alloc((void**)&P.mask1, N * kTrain * L.B * (L.H / 32) * 4);
+  if (!rc) rc = alloc((void**)&P.mask2, N * kTrain * L.B * (L.H / 32) * 4);
+  if (rc) return rc;
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bwd_weight_smem(L.B)));
+  st->dirty = true;
+  return IQLB_OK;
+}
+
+void bf16_destroy(iqlb_agents* h) {
+  Bf16State* st = (Bf16State*)h->bf16_state;
+  if (!st) return;
+  BfParams& P = st->P;
+  cudaFree(P.wimg); cudaFree(P.xsa); cudaFree(P.xnext); cudaFree(P.h1); cudaFree(P.h2); cudaFree(P.dh2);
+  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2);
+  delete st;
+  h->bf16_state = nullptr;
+}
+
+const BfParams* bf16_params(const iqlb_agents* h) {
+  const Bf16State* st = (const Bf16State*)h->bf16_state;
+  return st ? &st->P : nullptr;
+}
+
+void bf16_mark_dirty(iqlb_agents* h) {
+  if (h->bf16_state) ((Bf16State*)h->bf16_state)->dirty = true;
+}
+
+int bf16_refresh(iqlb_agents* h, cudaStream_t stream) {
+  Bf16State* st = (Bf16State*)h->bf16_state;
+  IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
+  const Layout& L = h->L;
+  shadow_refresh_kernel<<<dim3((unsigned)((L.off_logstd + 255) / 256), h->desc.n_agents), 256, 0, stream>>>(
+      st->P, h->params, h->target);
+  IQLB_LAUNCH_CHECK();
+  st->dirty = false;
+  return IQLB_OK;
+}
+
+int bf16_step_gemms_fwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
+  Bf16State* st = (Bf16State*)h->bf16_state;
+  IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
+  const Layout& L = h->L;
+  const int N = h->desc.n_agents;
+  int rc;
+  if (st->dirty) {
+    if ((rc = bf16_refresh(h, stream))) return rc;
+    pf.mark("shadow_refresh");
+  }
+  pack_x_kernel<<<dim3((unsigned)((L.B * st->P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(st->P, h->batch);
+  IQLB_LAUNCH_CHECK();
+  pf.mark("pack_x");
+  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 128, fwd_smem(st->P.KXB), stream>>>(st->P, h->params, h->target,
+                                                                                     h->head_out);
+  IQLB_LAUNCH_CHECK();
+  pf.mark("bf16_fwd");
+  return IQLB_OK;
+}
+
+int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
+  Bf16State* st = (Bf16State*)h->bf16_state;
+  IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
+  const Layout& L = h->L;
+  const int N = h->desc.n_agents;
+  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 128, bwd_data_smem(), stream>>>(st->P, h->params, h->d_out);
+  IQLB_LAUNCH_CHECK();
+  pf.mark("bf16_bwd_data");
+  bf16_bwd_weight_kernel<<<dim3(L.H / 128, kTrain, N), 128, bwd_weight_smem(L.B), stream>>>(st->P, h->grads);
+  IQLB_LAUNCH_CHECK();
+  pf.mark("bf16_bwd_weight");
+  return IQLB_OK;
+}
+
 }  // namespace iqlb

@@ -17,8 +17,11 @@ int launch_gather(const float* table, int64_t n_rows, int row_stride, int reward
                   int64_t* idx_out, float* batch_out, cudaStream_t stream);
 int bf16_create(iqlb_agents* h);
 void bf16_destroy(iqlb_agents* h);
-int bf16_step_gemms_fwd(iqlb_agents* h, cudaStream_t stream);
-int bf16_step_gemms_bwd(iqlb_agents* h, cudaStream_t stream);
+int bf16_step_gemms_fwd(iqlb_agents* h, Prof& pf, cudaStream_t stream);
+int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream);
+const BfParams* bf16_params(const iqlb_agents* h);
+void bf16_mark_dirty(iqlb_agents* h);
+int bf16_refresh(iqlb_agents* h, cudaStream_t stream);
 
 // ------------------------------------------------------------------------------------------
 // Heads forward: out[o] = H2[b,:] . W2[o,:] + b2[o]   (N = 1 for V/Q, N = A (+tanh) for actor)
@@ -64,7 +67,8 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
                             const float* __restrict__ batch, const float* __restrict__ head_out,
                             float* __restrict__ d_out, float* __restrict__ grads, float* __restrict__ losses,
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
-                            uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng) {
+                            uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
+                            uint8_t* __restrict__ dzimg, int64_t z_bytes) {
   __shared__ float red[32];
   const int agent = blockIdx.x, b = threadIdx.x;
   const bool live = b < L.B;
@@ -92,12 +96,35 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
     dout[2 * L.B + b] = e2 * invB;
     w = fminf(expf(beta * adv), 100.0f);
   }
+  // bf16 path: the dz image (dz columns + a column of ones) feeds the weight-gradient MMAs, and the
+  // head bias gradients are reduced here (the fp32 path does both in head_bwd_kernel)
+  auto put_dz = [&](int t, int col, float v) {
+    *reinterpret_cast<__nv_bfloat16*>(dzimg + ((int64_t)agent * kTrain + t) * z_bytes + umma::image_off(L.B, b, col)) =
+        __float2bfloat16_rn(v);
+  };
+  if (dzimg != nullptr) {
+    float d0 = 0.f, d1 = 0.f, d2 = 0.f;
+    if (live) {
+      d0 = dout[0 * L.B + b]; d1 = dout[1 * L.B + b]; d2 = dout[2 * L.B + b];
+      put_dz(0, 0, d0); put_dz(0, 1, 1.0f);
+      put_dz(1, 0, d1); put_dz(1, 1, 1.0f);
+      put_dz(2, 0, d2); put_dz(2, 1, 1.0f);
+      put_dz(3, L.A, 1.0f);
+    }
+    const float s0 = block_sum(d0, red), s1 = block_sum(d1, red), s2 = block_sum(d2, red);
+    if (b == 0) {
+      float* g = grads + (int64_t)agent * L.Pstride;
+      g[L.off_v + L.b2(L.S, 1)] = s0;
+      g[L.off_q1 + L.b2(L.Dq, 1)] = s1;
+      g[L.off_q2 + L.b2(L.Dq, 1)] = s2;
+    }
+  }
   // actor: per-action terms; log_std gradient needs a block reduction per action
   const float* log_std = params + (int64_t)agent * L.Pstride + L.off_logstd;
   float* g_log_std = grads + (int64_t)agent * L.Pstride + L.off_logstd;
   float bc = 0.f;
   for (int a = 0; a < L.A; ++a) {
-    float gls = 0.f;
+    float gls = 0.f, dza = 0.f;
     if (live) {
       const float mu = ho[(int64_t)(6 + a) * L.B + b];
       const float act = row[L.S + a];
@@ -115,7 +142,13 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
         dmu = w * diff * inv_var * invB;
         gls = (ls_raw >= -20.0f && ls_raw <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
       }
-      dout[(int64_t)(3 + a) * L.B + b] = dmu * (1.0f - mu * mu);
+      dza = dmu * (1.0f - mu * mu);
+      dout[(int64_t)(3 + a) * L.B + b] = dza;
+      if (dzimg != nullptr) put_dz(3, a, dza);
+    }
+    if (dzimg != nullptr) {
+      const float sa = block_sum(dza, red);
+      if (b == 0) grads[(int64_t)agent * L.Pstride + L.off_a + L.b2(L.S, L.A) + a] = sa;
     }
     if (!L.deterministic) {
       const float tot = block_sum(gls, red);
@@ -213,8 +246,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __restrict__ params,
                                                           float4* __restrict__ exp_avg, float4* __restrict__ exp_avg_sq,
                                                           float4* __restrict__ target, const float4* __restrict__ grads,
-                                                          const StepScalars* __restrict__ scal,
-                                                          __nv_bfloat16* __restrict__ shadow /*unused here*/) {
+                                                          const StepScalars* __restrict__ scal, BfParams BP, int shadow) {
   const int agent = blockIdx.y;
   const int64_t n4 = L.Pstride / 4;
   const int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -238,6 +270,19 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __re
     mp[c] = mm;
     vp[c] = vv;
   }
+  uint8_t* wimg = shadow ? BP.wimg + (int64_t)agent * BP.agent_w_bytes : nullptr;
+  int snet[4];
+  int64_t soff[4];
+  if (shadow) {  // refresh the bf16 operand images of the weights just updated
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      snet[c] = -1;
+      if (shadow_loc(L, BP.KXB, e0 + c, snet[c], soff[c]))
+        *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)snet[c] * BP.net_bytes + soff[c]) = __float2bfloat16_rn(pp[c]);
+      else
+        snet[c] = -1;
+    }
+  }
   params[g4] = p;
   exp_avg[g4] = m;
   exp_avg_sq[g4] = v;
@@ -247,7 +292,11 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __re
     float* tp = &tg.x;
 #pragma unroll
     for (int c = 0; c < 4; ++c)
-      if (e0 + c < L.PQ) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);
+      if (e0 + c < L.PQ) {
+        tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);
+        if (shadow && snet[c] >= 0)
+          *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)(snet[c] + 4) * BP.net_bytes + soff[c]) = __float2bfloat16_rn(tp[c]);
+      }
     target[t4] = tg;
   }
 }
@@ -313,25 +362,6 @@ static int build_tasks(iqlb_agents* h) {
   return IQLB_OK;
 }
 
-// Launch bookkeeping: when profiling is on, an event is recorded after every launch of the step.
-struct Prof {
-  iqlb_agents* h; cudaStream_t st; int i = 0;
-  Prof(iqlb_agents* h_, cudaStream_t st_) : h(h_), st(st_) {
-    if (h->prof) cudaEventRecord(h->ev[0], st);
-  }
-  void mark(const char* name) {
-    if (h->prof && i < iqlb_agents::kMaxProf) {
-      h->prof_name[i] = name;
-      cudaEventRecord(h->ev[i + 1], st);
-    }
-    ++i;
-  }
-  void done() {
-    if (h->prof) h->prof_n = i < iqlb_agents::kMaxProf ? i : iqlb_agents::kMaxProf;
-    h->launches_last = i;
-  }
-};
-
 static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   const Layout& L = h->L;
   const int N = h->desc.n_agents;
@@ -344,30 +374,33 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
     if (rc) return rc;
     pf.mark("replay_gather");
   }
-  if (h->desc.precision == 1) {
-    if ((rc = bf16_step_gemms_fwd(h, st))) return rc;
-    pf.mark("bf16_fwd");
+  const bool bf = h->desc.precision == 1;
+  const BfParams* bp = bf16_params(h);
+  if (bf) {
+    if ((rc = bf16_step_gemms_fwd(h, pf, st))) return rc;
   } else {
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd0, N * kStreams, L.B, L.H, false, st))) return rc;
     pf.mark("gemm_fwd_l0");
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd1, N * kStreams, L.B, L.H, false, st))) return rc;
     pf.mark("gemm_fwd_l1");
   }
-  head_fwd_kernel<<<dim3((L.B + 7) / 8, kStreams, N), 256, 0, st>>>(L, h->params, h->target, h->H2, h->head_out);
-  IQLB_LAUNCH_CHECK();
-  pf.mark("head_fwd");
+  if (!bf) {
+    head_fwd_kernel<<<dim3((L.B + 7) / 8, kStreams, N), 256, 0, st>>>(L, h->params, h->target, h->H2, h->head_out);
+    IQLB_LAUNCH_CHECK();
+    pf.mark("head_fwd");
+  }
   const int lb = (L.B + 31) / 32 * 32;
   loss_kernel<<<N, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
-                                h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0);
+                                h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0,
+                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0);
   IQLB_LAUNCH_CHECK();
   pf.mark("loss");
-  head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
-  IQLB_LAUNCH_CHECK();
-  pf.mark("head_bwd");
-  if (h->desc.precision == 1) {
-    if ((rc = bf16_step_gemms_bwd(h, st))) return rc;
-    pf.mark("bf16_bwd");
+  if (bf) {
+    if ((rc = bf16_step_gemms_bwd(h, pf, st))) return rc;
   } else {
+    head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
+    IQLB_LAUNCH_CHECK();
+    pf.mark("head_bwd");
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw1, N * kTrain, L.H, L.H, false, st))) return rc;
     pf.mark("gemm_bwd_w1");
     if ((rc = launch_grouped_gemm(GEMM_BWD_DATA, h->t_bd1, N * kTrain, L.B, L.H, false, st))) return rc;
@@ -378,9 +411,9 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   const int64_t n4 = L.Pstride / 4;
   adam_polyak_kernel<<<dim3((unsigned)((n4 + 255) / 256), N), 256, 0, st>>>(
       L, (float4*)h->params, (float4*)h->exp_avg, (float4*)h->exp_avg_sq, (float4*)h->target, (const float4*)h->grads,
-      h->scal, nullptr);
+      h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0);
   IQLB_LAUNCH_CHECK();
-  pf.mark("adam_polyak");
+  pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   pf.done();
   return IQLB_OK;
 }
@@ -494,6 +527,12 @@ extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampl
   if (h->launches_last > 0) return h->launches_last;  // counted by the last step
   // gather + fwd0 + fwd1 + head_fwd + loss + head_bwd + bw1 + bd1 + bw0 + adam
   return (sampled ? 1 : 0) + 5 + 4;
+}
+
+extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  if (h->desc.precision == 1) return bf16_refresh(h, (cudaStream_t)stream);
+  return IQLB_OK;
 }
 
 extern "C" int iqlb_agents_profile(iqlb_agents* h, int32_t enable) {

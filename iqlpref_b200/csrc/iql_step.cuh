@@ -3,6 +3,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "umma.cuh"
 
 namespace iqlb {
 
@@ -79,6 +80,60 @@ struct StepScalars {  // per agent, written by the loss kernel, read by Adam
 int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
                         cudaStream_t stream);
 
+constexpr int kOutMax = 24;  // widest head handled in registers (actor action_dim)
+
+struct BfParams {
+  Layout L;
+  int KXB;                // 64-column blocks of the input images (ceil((S+A)/64))
+  int64_t w0_bytes;       // W0 image bytes  = KXB * H * 128
+  int64_t net_bytes;      // W0 + W1 images of one network
+  int64_t agent_w_bytes;  // 6 networks: Q1 Q2 V actor Qt1 Qt2
+  int64_t x_bytes;        // one input image [B x 64*KXB]
+  int64_t h_bytes;        // one activation image [B x H]
+  int64_t z_bytes;        // one dz image [B x 64]
+  uint8_t *wimg, *xsa, *xnext, *h1, *h2, *dh2, *dh1, *dz;
+  uint32_t *mask1, *mask2;  // [agent][train net][B][H/32]
+};
+
+struct Bf16State {
+  BfParams P;
+  bool dirty = true;
+};
+
+__host__ __device__ inline int net_of_stream(int s) {  // index into the weight images
+  switch (s) {
+    case 0: case 1: return 2;  // V
+    case 2: return 4;          // Q target 1
+    case 3: return 5;          // Q target 2
+    case 4: return 0;
+    case 5: return 1;
+    default: return 3;         // actor
+  }
+}
+__host__ __device__ inline int train_index(int s) { return s == 1 ? 0 : (s == 4 ? 1 : (s == 5 ? 2 : (s == 6 ? 3 : -1))); }
+
+// image location of parameter element e (offset inside one agent's packed parameters)
+__device__ __forceinline__ bool shadow_loc(const Layout& L, int KXB, int64_t e, int& net, int64_t& off) {
+  int n, in;
+  int64_t r;
+  if (e < L.off_q2) { n = 0; r = e; in = L.Dq; }
+  else if (e < L.off_v) { n = 1; r = e - L.off_q2; in = L.Dq; }
+  else if (e < L.off_a) { n = 2; r = e - L.off_v; in = L.S; }
+  else if (e < L.off_logstd) { n = 3; r = e - L.off_a; in = L.S; }
+  else return false;
+  const int64_t w0n = (int64_t)L.H * in;
+  if (r < w0n) {
+    off = umma::image_off(L.H, (int)(r / in), (int)(r % in));
+  } else {
+    r -= w0n + L.H;
+    if (r < 0 || r >= (int64_t)L.H * L.H) return false;
+    off = (int64_t)KXB * L.H * 128 + umma::image_off(L.H, (int)(r / L.H), (int)(r % L.H));
+  }
+  net = n;
+  return true;
+}
+
+
 }  // namespace iqlb
 
 struct iqlb_agents {
@@ -112,3 +167,24 @@ struct iqlb_agents {
   int prof_n = 0, prof_steps = 0;
   int launches_last = 0;
 };
+
+namespace iqlb {
+// Launch bookkeeping: when profiling is on, an event is recorded after every launch of the step.
+struct Prof {
+  iqlb_agents* h; cudaStream_t st; int i = 0;
+  Prof(iqlb_agents* h_, cudaStream_t st_) : h(h_), st(st_) {
+    if (h->prof) cudaEventRecord(h->ev[0], st);
+  }
+  void mark(const char* name) {
+    if (h->prof && i < iqlb_agents::kMaxProf) {
+      h->prof_name[i] = name;
+      cudaEventRecord(h->ev[i + 1], st);
+    }
+    ++i;
+  }
+  void done() {
+    if (h->prof) h->prof_n = i < iqlb_agents::kMaxProf ? i : iqlb_agents::kMaxProf;
+    h->launches_last = i;
+  }
+};
+}  // namespace iqlb

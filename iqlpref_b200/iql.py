@@ -452,7 +452,8 @@ class BatchedIQL:
         self._sync_shadow()
 
     def _sync_shadow(self):
-        pass  # bf16 operand shadows are refreshed inside the library at the next step
+        """params/target were written from Python: rebuild the bf16 operand images (precision bf16)."""
+        _lib.check(self.lib.iqlb_agents_refresh(self._h, _lib.stream_ptr(self.device)), "iqlb_agents_refresh")
 
     # ---- stepping ---------------------------------------------------------------------------------
     def attach_replay(self, buffer: ReplayBuffer, reward_cols: Optional[torch.Tensor] = None,
@@ -646,6 +647,7 @@ class ImplicitQLearning:
                 step = int(float(st["step"]))
         eng.it.fill_(step)
         eng.actor_lr.fill_(float(state_dict["actor_optimizer"]["param_groups"][0]["lr"]))
+        eng._sync_shadow()
         self.total_it = state_dict["total_it"]
 
 

@@ -75,22 +75,25 @@ __device__ __forceinline__ void st_chunk(uint8_t* tile, int row, int col0, const
 }
 
 // ------------------------------------------------------------------------------------------------
-// Forward.  grid (B/128, 7 streams, agents), 128 threads, 1 CTA per SM.
-// Shared memory (H = 256): [W0 image KXB*32K | X tile KXB*16K | W1 ring (4-KXB)*32K | H tile 64K | ctrl]
+// Forward.  grid (B/128, 7 streams, agents), 256 threads (warp w drains TMEM lane quarter w%4,
+// column half w/4), 1 CTA per SM.
+// Shared memory (H = 256): [W0 image KXB*32K | X tile KXB*16K | W1 ring (4-KXB)*32K | H tile 64K | ctrl | b0]
 // W1 streams in as four 32 KB K-blocks; the last KXB of them land in the W0 region once layer 0
-// has been consumed.  TMEM: layer-0 accumulator in columns [0,256), layer-1 in [256,512).
+// has been consumed, and b1 / W2 (fp32) take over the X region.  TMEM: layer-0 accumulator in
+// columns [0,256), layer-1 in [256,512).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const float* __restrict__ params,
+__global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const float* __restrict__ params,
                                                           const float* __restrict__ target,
                                                           float* __restrict__ head_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int half = blockIdx.x, s = blockIdx.y, agent = blockIdx.z;
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int quarter = warp & 3, chalf = warp >> 2;
   const int KXB = P.KXB, nring = 4 - KXB;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oW0 = 0, oX = (uint32_t)KXB * 32768u, oRing = oX + (uint32_t)KXB * 16384u,
-                 oH = oRing + (uint32_t)nring * 32768u, oCtrl = oH + 65536u;
+                 oH = oRing + (uint32_t)nring * 32768u, oCtrl = oH + 65536u, oB0 = oCtrl + 128u;
   const uint32_t bar_l0 = sbase + oCtrl, bar_w1 = bar_l0 + 8, bar_mma0 = bar_l0 + 40, bar_mma1 = bar_l0 + 48;
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 56);
   const int net = net_of_stream(s), t = train_index(s);
@@ -100,6 +103,9 @@ __global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const floa
   const float* fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
                                        : params + (int64_t)agent * L.Pstride + L.net_off(s);
   auto chunk_off = [&](int c) -> uint32_t { return c < nring ? oRing + (uint32_t)c * 32768u : oW0 + (uint32_t)(c - nring) * 32768u; };
+  float* sb0 = reinterpret_cast<float*>(smem + oB0);
+  float* sb1 = reinterpret_cast<float*>(smem + oX);   // valid after layer 0 has consumed X
+  float* sw2 = sb1 + 256;
 
   if (tid == 0) {
     if (sbase & 1023u) __trap();
@@ -117,10 +123,9 @@ __global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const floa
       bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
     }
   }
-  if (warp == 0) {
-    __syncwarp();
-    tmem_alloc(sbase + oCtrl + 56, 512);
-  }
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 56, 512);
+  sb0[tid] = __ldg(fnet + L.b0(in) + tid);
+  const float b1_pref = __ldg(fnet + L.b1(in) + tid);  // parked in a register until the X region is free
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -142,27 +147,30 @@ __global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const floa
     }
   }
   __syncwarp();
-  const int row = tid, brow = half * 128 + row;
-  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  sb1[tid] = b1_pref;
+  for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
+  const int row = quarter * 32 + lane, brow = half * 128 + row;
+  const int cbeg = chalf * 128;
+  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
   uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
-  {  // epilogue 0: H1 = relu(acc + b0) -> bf16 tile (A operand of layer 1)
-    const float* b0 = fnet + L.b0(in);
-    for (int c0 = 0; c0 < 256; c0 += 32) {
-      float v[32];
-      tmem_ld32(lane_base + (uint32_t)c0, v);
-      tmem_ld_wait();
-      uint32_t m = 0;
+  // epilogue 0: H1 = relu(acc + b0) -> bf16 tile (A operand of layer 1)
+  for (int c0 = cbeg; c0 < cbeg + 128; c0 += 32) {
+    float v[32];
+    tmem_ld32(lane_base + (uint32_t)c0, v);
+    tmem_ld_wait();
+    uint32_t m = 0;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float x = fmaxf(v[j] + __ldg(b0 + c0 + j), 0.f);
-        v[j] = x;
-        m |= (x > 0.f ? 1u : 0u) << j;
-      }
-      if (m1) m1[c0 >> 5] = m;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
+    for (int j4 = 0; j4 < 8; ++j4) {
+      const float4 bb = *reinterpret_cast<const float4*>(sb0 + c0 + 4 * j4);
+      const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
+      const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
+      v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
+      m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
     }
+    if (m1) m1[c0 >> 5] = m;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
   }
   fence_async_smem();
   tc_fence_before();
@@ -188,80 +196,102 @@ __global__ void __launch_bounds__(128, 1) bf16_fwd_kernel(BfParams P, const floa
   mbar_wait(bar_mma1, 0);
   tc_fence_after();
   __syncthreads();
-  {  // epilogue 1: H2 = relu(acc + b1); head = H2 . W2 + b2
-    const float* b1 = fnet + L.b1(in);
-    const float* W2 = fnet + L.w2(in);
-    float acc[kOutMax];
+  // epilogue 1: H2 = relu(acc + b1); head = H2 . W2 + b2 (two column halves per row, combined below)
+  float acc[kOutMax];
 #pragma unroll
-    for (int o = 0; o < kOutMax; ++o) acc[o] = 0.f;
-    for (int c0 = 0; c0 < 256; c0 += 32) {
-      float v[32];
-      tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
-      tmem_ld_wait();
-      uint32_t m = 0;
+  for (int o = 0; o < kOutMax; ++o) acc[o] = 0.f;
+  for (int c0 = cbeg; c0 < cbeg + 128; c0 += 32) {
+    float v[32];
+    tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
+    tmem_ld_wait();
+    uint32_t m = 0;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float x = fmaxf(v[j] + __ldg(b1 + c0 + j), 0.f);
-        v[j] = x;
-        m |= (x > 0.f ? 1u : 0u) << j;
+    for (int j4 = 0; j4 < 8; ++j4) {
+      const float4 bb = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * j4);
+      const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
+      const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
+      v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
+      m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
+    }
+    if (nout == 1) {
+      float a = acc[0];
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 w = *reinterpret_cast<const float4*>(sw2 + c0 + 4 * j4);
+        a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
+        a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
       }
+      acc[0] = a;
+    } else {
 #pragma unroll
       for (int o = 0; o < kOutMax; ++o) {
         if (o < nout) {
-          const float* w = W2 + (int64_t)o * L.H + c0;
+          const float* wr = sw2 + o * 256 + c0;
           float a = acc[o];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) a = fmaf(v[j], __ldg(w + j), a);
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
+            a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
+            a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
+          }
           acc[o] = a;
         }
       }
-      if (t >= 0) {
-        m2[c0 >> 5] = m;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
-      }
     }
+    if (t >= 0) {
+      m2[c0 >> 5] = m;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
+    }
+  }
+  // combine the two column halves through the (now idle) W1 ring
+  float* part = reinterpret_cast<float*>(smem + oRing);
+  if (chalf == 1) {
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o)
+      if (o < nout) part[o * 128 + row] = acc[o];
+  }
+  if (t >= 0) fence_async_smem();
+  __syncthreads();
+  if (chalf == 0) {
     const float* b2 = fnet + L.b2(in, nout);
     float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
 #pragma unroll
     for (int o = 0; o < kOutMax; ++o) {
       if (o < nout) {
-        const float z = acc[o] + __ldg(b2 + o);
+        const float z = acc[o] + part[o * 128 + row] + __ldg(b2 + o);
         if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
         else ho[(int64_t)s * L.B + brow] = z;
       }
     }
   }
-  if (t >= 0) {
-    fence_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-      uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
-      for (int cb = 0; cb < 4; ++cb)
-        bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
-      bulk_commit();
-      bulk_wait_read0();
-    }
+  if (t >= 0 && tid == 0) {
+    uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+    for (int cb = 0; cb < 4; ++cb)
+      bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+    bulk_commit();
+    bulk_wait_read0();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward, data gradients.  grid (B/128, 4 trainable nets, agents), 128 threads.
-// Shared memory: [dH2 tile 64K | W1 image 128K | 2 x 16K output staging | ctrl].
-// dH2[b,j] = relu'(H2[b,j]) * sum_o dz[b,o] W2[o,j] on CUDA cores (one row per thread), then
+// Backward, data gradients.  grid (B/128, 4 trainable nets, agents), 256 threads.
+// Shared memory: [dH2 tile 64K | W1 image 128K | 2 x 16K output staging (first: W2 fp32) | ctrl].
+// dH2[b,j] = relu'(H2[b,j]) * sum_o dz[b,o] W2[o,j] on CUDA cores (thread = row x column half), then
 // dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
 // each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
+__global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int half = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
   const int s = train_stream(t), net = net_of_stream(s);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int quarter = warp & 3, chalf = warp >> 2;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
   const uint32_t bar_w = sbase + oCtrl, bar_mma = bar_w + 32;
@@ -280,35 +310,57 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const
       bulk_g2s(sbase + oW + (uint32_t)ib * 32768u, w1img + (int64_t)ib * 32768, 32768u, bar_w + 8 * ib);
     }
   }
-  if (warp == 0) {
-    __syncwarp();
-    tmem_alloc(sbase + oCtrl + 64, 256);
-  }
-  const int row = tid, brow = half * 128 + row;
-  {  // dH2 tile
-    const float* W2 = fnet + L.w2(in);
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 64, 256);
+  float* sw2 = reinterpret_cast<float*>(smem + oStage);
+  for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
+  const int row = quarter * 32 + lane, brow = half * 128 + row;
+  const int cbeg = chalf * 128;
+  const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32) + chalf * 4;
+  const uint4 m2w = *reinterpret_cast<const uint4*>(m2p);
+  const uint32_t* m1p = P.mask1 + (at * L.B + brow) * (L.H / 32);
+  uint32_t m1w[4];
+#pragma unroll
+  for (int ib = 0; ib < 4; ++ib) m1w[ib] = m1p[ib * 2 + chalf];
+  float dz[kOutMax];
+  {
     const float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
     const int drow0 = (t == 3) ? 3 : t;
-    float dz[kOutMax];
 #pragma unroll
     for (int o = 0; o < kOutMax; ++o) dz[o] = o < nout ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
-    const uint32_t* m2 = P.mask2 + (at * L.B + brow) * (L.H / 32);
-    for (int c0 = 0; c0 < 256; c0 += 8) {
-      const uint32_t m = m2[c0 >> 5] >> (c0 & 31);
-      float g[8];
+  }
+  __syncthreads();
+  {  // dH2 tile: this thread's row, columns [cbeg, cbeg+128)
+    const uint32_t mw[4] = {m2w.x, m2w.y, m2w.z, m2w.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = 0.f;
+    for (int wq = 0; wq < 4; ++wq) {
+      const uint32_t mword = mw[wq];
 #pragma unroll
-      for (int o = 0; o < kOutMax; ++o) {
-        if (o < nout) {
-          const float* w = W2 + (int64_t)o * L.H + c0;
+      for (int cc = 0; cc < 32; cc += 8) {
+        const int c0 = cbeg + wq * 32 + cc;
+        float g[8];
+        if (nout == 1) {
+          const float4 w0 = *reinterpret_cast<const float4*>(sw2 + c0), w1 = *reinterpret_cast<const float4*>(sw2 + c0 + 4);
+          g[0] = dz[0] * w0.x; g[1] = dz[0] * w0.y; g[2] = dz[0] * w0.z; g[3] = dz[0] * w0.w;
+          g[4] = dz[0] * w1.x; g[5] = dz[0] * w1.y; g[6] = dz[0] * w1.z; g[7] = dz[0] * w1.w;
+        } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = fmaf(dz[o], __ldg(w + j), g[j]);
+          for (int j = 0; j < 8; ++j) g[j] = 0.f;
+#pragma unroll
+          for (int o = 0; o < kOutMax; ++o) {
+            if (o < nout) {
+              const float4 w0 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0),
+                           w1 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0 + 4);
+              g[0] = fmaf(dz[o], w0.x, g[0]); g[1] = fmaf(dz[o], w0.y, g[1]); g[2] = fmaf(dz[o], w0.z, g[2]);
+              g[3] = fmaf(dz[o], w0.w, g[3]); g[4] = fmaf(dz[o], w1.x, g[4]); g[5] = fmaf(dz[o], w1.y, g[5]);
+              g[6] = fmaf(dz[o], w1.z, g[6]); g[7] = fmaf(dz[o], w1.w, g[7]);
+            }
+          }
         }
-      }
+        const uint32_t m = mword >> cc;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = ((m >> j) & 1u) ? g[j] : 0.f;
-      st_chunk(smem + oA, row, c0, g);
+        for (int j = 0; j < 8; ++j) g[j] = ((m >> j) & 1u) ? g[j] : 0.f;
+        st_chunk(smem + oA, row, c0, g);
+      }
     }
   }
   fence_async_smem();
@@ -330,9 +382,9 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const
     }
   }
   __syncwarp();
-  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-  const uint32_t* m1 = P.mask1 + (at * L.B + brow) * (L.H / 32);
+  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   uint8_t* dh1 = P.dh1 + at * P.h_bytes;
+#pragma unroll
   for (int ib = 0; ib < 4; ++ib) {
     if (ib >= 2) {  // staging slot ib&1 was handed to a bulk store two iterations ago
       if (tid == 0) bulk_wait_read1();
@@ -341,17 +393,14 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const
     mbar_wait(bar_mma + 8 * ib, 0);
     tc_fence_after();
     uint8_t* stage = smem + oStage + (ib & 1) * 16384;
+    float v[32];
+    tmem_ld32(lane_base + 64u * ib + 32u * chalf, v);
+    tmem_ld_wait();
+    const uint32_t m = m1w[ib];
 #pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      float v[32];
-      tmem_ld32(lane_base + 64u * ib + 32u * hh, v);
-      tmem_ld_wait();
-      const uint32_t m = m1[ib * 2 + hh];
+    for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * hh + 8 * q, v + 8 * q);
-    }
+    for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * chalf + 8 * q, v + 8 * q);
     fence_async_smem();
     __syncthreads();
     if (tid == 0) {
@@ -362,7 +411,7 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const
   if (tid == 0) bulk_wait_read0();
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 256);
+  if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -376,12 +425,13 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_data_kernel(BfParams P, const
 // The dz image holds dz[b, 0..out) and a column of ones at `out`, so bias gradients are MMA columns.
 // Thread r of the CTA owns output feature 128*tile + r when draining TMEM into the fp32 gradients.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads) {
+__global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int ot = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
   const int s = train_stream(t);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int quarter = warp & 3, chalf = warp >> 2;
   const uint32_t blk = (uint32_t)L.B * 128u;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oB = 2 * blk, oZ = 6 * blk, oCtrl = 7 * blk;
@@ -402,10 +452,7 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
     bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);
     bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
   }
-  if (warp == 0) {
-    __syncwarp();
-    tmem_alloc(sbase + oCtrl + 40, 512);
-  }
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 40, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -430,13 +477,13 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
     bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
   }
   __syncwarp();
-  const int f = ot * 128 + tid;  // output feature owned by this thread
-  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  const int f = ot * 128 + quarter * 32 + lane;  // output feature owned by this thread (two threads per feature)
+  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   float* gnet = grads + (int64_t)agent * L.Pstride + L.net_off(s);
   {  // drain dW1 row f and db1[f]
     float* gw1 = gnet + L.w1(in) + (int64_t)f * L.H;
     const bool vec_ok = (reinterpret_cast<uintptr_t>(gw1) & 15) == 0;
-    for (int c0 = 0; c0 < 256; c0 += 32) {
+    for (int c0 = chalf * 128; c0 < chalf * 128 + 128; c0 += 32) {
       float v[32];
       tmem_ld32(lane_base + (uint32_t)c0, v);
       tmem_ld_wait();
@@ -449,13 +496,15 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
         for (int j = 0; j < 32; ++j) gw1[c0 + j] = v[j];
       }
     }
-    float v[32];
-    tmem_ld32(lane_base + 352u, v);
-    tmem_ld_wait();
-    float db = 0.f;
+    if (chalf == 0) {
+      float v[32];
+      tmem_ld32(lane_base + 352u, v);
+      tmem_ld_wait();
+      float db = 0.f;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
-    gnet[L.b1(in) + f] = db;
+      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+      gnet[L.b1(in) + f] = db;
+    }
   }
   if (tid == 0) {
     mbar_wait(bar_ld2, 0);
@@ -471,7 +520,7 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncwarp();
   mbar_wait(bar_p2, 0);
   tc_fence_after();
-  {  // drain dW0 row f, db0[f], dW2[:, f]
+  if (chalf == 0) {  // drain dW0 row f and db0[f]
     float* gw0 = gnet + L.w0() + (int64_t)f * in;
     for (int c0 = 0; c0 < n0; c0 += 16) {
       float v[16];
@@ -488,6 +537,8 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
 #pragma unroll
     for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
     gnet[L.b0(in) + f] = db;
+  } else {  // dW2[:, f]
+    float v[32];
     tmem_ld32(lane_base + 416u, v);
     tmem_ld_wait();
     float* gw2 = gnet + L.w2(in);
@@ -497,13 +548,13 @@ __global__ void __launch_bounds__(128, 1) bf16_bwd_weight_kernel(BfParams P, flo
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u; }
+static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u + 1024u; }
 static size_t bwd_data_smem() { return 65536u + 131072u + 32768u + 128u; }
 static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
 
@@ -512,6 +563,7 @@ int bf16_create(iqlb_agents* h) {
   IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
   IQLB_REQUIRE(L.B == 128 || L.B == 256, "the tcgen05 path needs batch_size 128 or 256");
   IQLB_REQUIRE(L.A <= kOutMax && L.Dq <= 128, "action_dim <= 24 and state_dim + action_dim <= 128");
+  IQLB_REQUIRE(1 + L.A <= 16 * ((L.Dq + 63) / 64), "action_dim too wide for the head staging area");
   Bf16State* st = new (std::nothrow) Bf16State();
   if (!st) return fail(IQLB_ERR_NOMEM, "out of host memory%s", "");
   h->bf16_state = st;
@@ -593,7 +645,7 @@ int bf16_step_gemms_fwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
   pack_x_kernel<<<dim3((unsigned)((L.B * st->P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(st->P, h->batch);
   IQLB_LAUNCH_CHECK();
   pf.mark("pack_x");
-  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 128, fwd_smem(st->P.KXB), stream>>>(st->P, h->params, h->target,
+  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(st->P.KXB), stream>>>(st->P, h->params, h->target,
                                                                                      h->head_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_fwd");
@@ -605,10 +657,10 @@ int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
   IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
   const Layout& L = h->L;
   const int N = h->desc.n_agents;
-  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 128, bwd_data_smem(), stream>>>(st->P, h->params, h->d_out);
+  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 256, bwd_data_smem(), stream>>>(st->P, h->params, h->d_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_bwd_data");
-  bf16_bwd_weight_kernel<<<dim3(L.H / 128, kTrain, N), 128, bwd_weight_smem(L.B), stream>>>(st->P, h->grads);
+  bf16_bwd_weight_kernel<<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(st->P, h->grads);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_bwd_weight");
   return IQLB_OK;

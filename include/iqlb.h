@@ -72,7 +72,8 @@ int iqlb_replay_gather(const float* table, int64_t n_rows, int32_t row_stride, i
  * Parameter packing (fp32, per agent, nn.Linear layout W[out,in] row-major then b[out]):
  *   Q1: W0[H,S+A] b0[H] W1[H,H] b1[H] W2[1,H] b2[1] | Q2: same | V: W0[H,S] ... W2[1,H] b2[1]
  *   | actor: W0[H,S] b0 W1 b1 W2[A,H] b2[A] | log_std[A] (Gaussian policy only)
- * iqlb_param_count() gives P (all) and PQ (Q1+Q2, = target size).
+ * Each network segment is zero-padded to a multiple of 8 floats (every network starts 32-byte
+ * aligned).  iqlb_param_count() gives P (all, padding included) and PQ (Q1+Q2 segments = target size).
  * --------------------------------------------------------------------------------------------- */
 typedef struct {
   int32_t n_agents;
@@ -95,7 +96,8 @@ int iqlb_param_count(int32_t state_dim, int32_t action_dim, int32_t hidden_dim, 
                      int64_t* p_all, int64_t* p_q);
 
 /* All arrays are caller-owned device memory that must outlive the handle:
- *   params, exp_avg, exp_avg_sq : float[n_agents][P]      target : float[n_agents][PQ]
+ *   params, exp_avg, exp_avg_sq : float[n_agents][P8]     target : float[n_agents][PQ8]
+ *                                 (row strides P8 / PQ8 = P / PQ rounded up to a multiple of 8, padding zero)
  *   hparams : float[n_agents][8]
  *   it      : int64[n_agents]   (ImplicitQLearning.total_it == every Adam `step`)
  *   actor_lr: double[n_agents]  (current CosineAnnealingLR value, recursive form)
@@ -135,6 +137,11 @@ int iqlb_agents_profile(iqlb_agents* h, int32_t enable);
 int iqlb_agents_profile_collect(iqlb_agents* h);
 int iqlb_agents_profile_read(iqlb_agents* h, int32_t i, const char** host_name, double* host_ms_total,
                              int32_t* host_steps);
+
+/* Debug/parity switch.  option 0: precision 1 runs Adam + Polyak inside the weight-gradient kernel
+ * (value 1, default) or materialises fp32 gradients and runs the stand-alone Adam kernel (value 0,
+ * so that iqlb_agents_debug_copy(which = 6) can be compared with the fp32 path). */
+int iqlb_agents_debug_option(iqlb_agents* h, int32_t option, int32_t value);
 
 /* Debug/parity hook: copy an internal scratch tensor to dst (device).  which: 0 H1, 1 H2,
  * 2 head_out, 3 d_out, 4 dH2, 5 dH1, 6 grads, 7 batch.  Returns bytes via *nbytes if dst NULL. */

@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward, weight gradients.  grid (H/128 output-feature tiles, 4 nets, agents), 128 threads.
+// Backward, weight gradients + optimizer.  grid (H/128 output-feature tiles, 4 nets, agents), 256 threads.
 // Every product reduces over the batch (K = B), with both operands read MN-major from images whose
 // rows are batch rows.  blk = B*128 bytes = one 64-column block of a batch-row image.
 // Shared memory: [bufA 2 blk | bufB 4 blk | dz image 1 blk | ctrl]
@@ -423,9 +423,45 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
 //   phase 2: bufA = dH1[:, tile], bufB[0..] = X_sa   -> dW0 tile (TMEM 256..), db0 (col 384+out)
 //            bufB[2 blk..] = H2[:, tile]             -> dW2^T tile (TMEM 416 + o)
 // The dz image holds dz[b, 0..out) and a column of ones at `out`, so bias gradients are MMA columns.
-// Thread r of the CTA owns output feature 128*tile + r when draining TMEM into the fp32 gradients.
+//
+// kFused: the gradient tile never leaves the SM.  It is transposed through shared memory (the upper
+// half of bufB, before H2 moves in) and consumed by Adam (torch _fused_adam math), the Polyak target
+// update (iql.py:127-129, Q nets) and the refresh of the bf16 weight images, all with 128-bit
+// row-contiguous accesses: HBM sees p, m, v (and target) exactly once per step and no gradient.
+// !kFused (debug/parity): gradients are written to `grads` for the stand-alone Adam kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads) {
+__device__ __forceinline__ void adam_update(float& p, float& m, float& v, float g, float ss, float bc2_sqrt) {
+  m = m + (1.0f - 0.9f) * (g - m);
+  v = 0.999f * v + (1.0f - 0.999f) * g * g;
+  const float denom = sqrtf(v) / bc2_sqrt + 1e-8f;
+  p = p - ss * (m / denom);
+}
+
+struct AdamPtrs {
+  float *p, *m, *v, *tgt;  // agent base pointers (tgt = nullptr for V / actor)
+  uint8_t *img, *timg;     // weight-image base of this network / of its target twin
+  float ss, bc2_sqrt, tau;
+};
+
+// one scalar parameter at packed offset e; img_off < 0: no bf16 image for this element
+__device__ __forceinline__ void adam_scalar(const AdamPtrs& A, int64_t e, float g, int64_t img_off) {
+  float p = A.p[e], m = A.m[e], v = A.v[e];
+  adam_update(p, m, v, g, A.ss, A.bc2_sqrt);
+  A.p[e] = p; A.m[e] = m; A.v[e] = v;
+  if (img_off >= 0) *reinterpret_cast<__nv_bfloat16*>(A.img + img_off) = __float2bfloat16_rn(p);
+  if (A.tgt) {
+    float tg = A.tgt[e];
+    tg = tg + A.tau * (p - tg);
+    A.tgt[e] = tg;
+    if (img_off >= 0) *reinterpret_cast<__nv_bfloat16*>(A.timg + img_off) = __float2bfloat16_rn(tg);
+  }
+}
+
+template <bool kFused>
+__global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads,
+                                                                 float* __restrict__ params, float* __restrict__ exp_avg,
+                                                                 float* __restrict__ exp_avg_sq, float* __restrict__ target,
+                                                                 const StepScalars* __restrict__ scal) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int ot = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
@@ -469,41 +505,107 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncwarp();
   mbar_wait(bar_p1, 0);
   tc_fence_after();
-  if (tid == 0) {  // phase-1 operands consumed: refill
+  if (tid == 0) {  // phase-1 operands consumed: refill (H2 follows once the staging area is free again)
     mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
     bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
     bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
-    mbar_expect_tx(bar_ld3, 2 * blk);
-    bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
   }
   __syncwarp();
-  const int f = ot * 128 + quarter * 32 + lane;  // output feature owned by this thread (two threads per feature)
+  const int trow = quarter * 32 + lane;  // tile row drained by this thread (two threads per row)
+  const int f = ot * 128 + trow;
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-  float* gnet = grads + (int64_t)agent * L.Pstride + L.net_off(s);
-  {  // drain dW1 row f and db1[f]
-    float* gw1 = gnet + L.w1(in) + (int64_t)f * L.H;
-    const bool vec_ok = (reinterpret_cast<uintptr_t>(gw1) & 15) == 0;
-    for (int c0 = chalf * 128; c0 < chalf * 128 + 128; c0 += 32) {
+  const int64_t noff = L.net_off(s);
+  float* gnet = grads + (int64_t)agent * L.Pstride + noff;
+  AdamPtrs A;
+  {
+    const StepScalars sc = scal[agent];
+    A.p = params + (int64_t)agent * L.Pstride;
+    A.m = exp_avg + (int64_t)agent * L.Pstride;
+    A.v = exp_avg_sq + (int64_t)agent * L.Pstride;
+    const bool is_q = (t == 1 || t == 2);
+    A.tgt = is_q ? target + (int64_t)agent * L.PQstride : nullptr;
+    A.img = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net_of_stream(s) * P.net_bytes;
+    A.timg = A.img + 4 * P.net_bytes;
+    A.ss = t == 0 ? sc.ss_v : (is_q ? sc.ss_q : sc.ss_a);
+    A.bc2_sqrt = sc.bc2_sqrt;
+    A.tau = sc.tau;
+  }
+  float* stg = reinterpret_cast<float*>(smem + oB + 2 * blk);  // 2 x [128 rows][64] fp32, float4 index ^ (row & 15)
+
+  {
+    // ---- dW1: four 64-column chunks, double-buffered through shared memory ----
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      float* sb = stg + (cc & 1) * (128 * 64);
       float v[32];
-      tmem_ld32(lane_base + (uint32_t)c0, v);
+      tmem_ld32(lane_base + (uint32_t)(cc * 64 + chalf * 32), v);
       tmem_ld_wait();
-      if (vec_ok) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<float4*>(gw1 + c0 + 4 * q) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-      } else {  // networks after Q1 start at odd float offsets in the packed parameter layout
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<float4*>(sb + trow * 64 + (((chalf * 8 + q) ^ (trow & 15)) << 2)) =
+            make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      __syncthreads();  // chunk cc staged (and every warp is done reading buffer cc&1 from chunk cc-2)
+      const int rr = lane >> 3, l8 = lane & 7;
+      if (!kFused) {  // row-contiguous 128-bit stores of the gradient tile (8 lanes cover 256 B of a row)
+        float* gw1 = gnet + L.w1(in) + (int64_t)(ot * 128) * L.H + cc * 64 + 8 * l8;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) gw1[c0 + j] = v[j];
+        for (int it = 0; it < 4; ++it) {
+          const int r = warp * 16 + it * 4 + rr;
+          const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
+          const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
+          *reinterpret_cast<float4*>(gw1 + (int64_t)r * L.H) = g0;
+          *reinterpret_cast<float4*>(gw1 + (int64_t)r * L.H + 4) = g1;
+        }
+        continue;
+      }
+      // all global loads of the four row groups are issued before the first use (the stores below
+      // would otherwise fence the next group's loads behind them)
+      float4 pq[4][2], mq[4][2], vq[4][2], tq[4][2];
+      int64_t eq[4];
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = warp * 16 + it * 4 + rr;
+        const int64_t e = noff + L.w1(in) + (int64_t)(ot * 128 + r) * L.H + cc * 64 + 8 * l8;
+        eq[it] = e;
+        pq[it][0] = *reinterpret_cast<const float4*>(A.p + e); pq[it][1] = *reinterpret_cast<const float4*>(A.p + e + 4);
+        mq[it][0] = *reinterpret_cast<const float4*>(A.m + e); mq[it][1] = *reinterpret_cast<const float4*>(A.m + e + 4);
+        vq[it][0] = *reinterpret_cast<const float4*>(A.v + e); vq[it][1] = *reinterpret_cast<const float4*>(A.v + e + 4);
+        if (A.tgt) { tq[it][0] = *reinterpret_cast<const float4*>(A.tgt + e); tq[it][1] = *reinterpret_cast<const float4*>(A.tgt + e + 4); }
+        else { tq[it][0] = make_float4(0, 0, 0, 0); tq[it][1] = tq[it][0]; }
+      }
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = warp * 16 + it * 4 + rr;
+        const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
+        const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
+        const int fr = ot * 128 + r, col = cc * 64 + 8 * l8;
+        const int64_t e = eq[it];
+        float4 &p0 = pq[it][0], &p1 = pq[it][1], &m0 = mq[it][0], &m1 = mq[it][1], &v0 = vq[it][0], &v1 = vq[it][1];
+        float4 &t0 = tq[it][0], &t1 = tq[it][1];
+        adam_update(p0.x, m0.x, v0.x, g0.x, A.ss, A.bc2_sqrt); adam_update(p0.y, m0.y, v0.y, g0.y, A.ss, A.bc2_sqrt);
+        adam_update(p0.z, m0.z, v0.z, g0.z, A.ss, A.bc2_sqrt); adam_update(p0.w, m0.w, v0.w, g0.w, A.ss, A.bc2_sqrt);
+        adam_update(p1.x, m1.x, v1.x, g1.x, A.ss, A.bc2_sqrt); adam_update(p1.y, m1.y, v1.y, g1.y, A.ss, A.bc2_sqrt);
+        adam_update(p1.z, m1.z, v1.z, g1.z, A.ss, A.bc2_sqrt); adam_update(p1.w, m1.w, v1.w, g1.w, A.ss, A.bc2_sqrt);
+        *reinterpret_cast<float4*>(A.p + e) = p0; *reinterpret_cast<float4*>(A.p + e + 4) = p1;
+        *reinterpret_cast<float4*>(A.m + e) = m0; *reinterpret_cast<float4*>(A.m + e + 4) = m1;
+        *reinterpret_cast<float4*>(A.v + e) = v0; *reinterpret_cast<float4*>(A.v + e + 4) = v1;
+        const int64_t ioff = P.w0_bytes + image_off(L.H, fr, col);
+        *reinterpret_cast<uint4*>(A.img + ioff) = make_uint4(pack_bf16(p0.x, p0.y), pack_bf16(p0.z, p0.w),
+                                                             pack_bf16(p1.x, p1.y), pack_bf16(p1.z, p1.w));
+        if (A.tgt) {
+          t0.x += A.tau * (p0.x - t0.x); t0.y += A.tau * (p0.y - t0.y); t0.z += A.tau * (p0.z - t0.z); t0.w += A.tau * (p0.w - t0.w);
+          t1.x += A.tau * (p1.x - t1.x); t1.y += A.tau * (p1.y - t1.y); t1.z += A.tau * (p1.z - t1.z); t1.w += A.tau * (p1.w - t1.w);
+          *reinterpret_cast<float4*>(A.tgt + e) = t0; *reinterpret_cast<float4*>(A.tgt + e + 4) = t1;
+          *reinterpret_cast<uint4*>(A.timg + ioff) = make_uint4(pack_bf16(t0.x, t0.y), pack_bf16(t0.z, t0.w),
+                                                                pack_bf16(t1.x, t1.y), pack_bf16(t1.z, t1.w));
+        }
       }
     }
-    if (chalf == 0) {
-      float v[32];
-      tmem_ld32(lane_base + 352u, v);
-      tmem_ld_wait();
-      float db = 0.f;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
-      gnet[L.b1(in) + f] = db;
+    fence_async_smem();
+    __syncthreads();  // staging area free: H2 may move in
+    if (tid == 0) {
+      mbar_expect_tx(bar_ld3, 2 * blk);
+      bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
     }
   }
   if (tid == 0) {
@@ -520,31 +622,106 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncwarp();
   mbar_wait(bar_p2, 0);
   tc_fence_after();
-  if (chalf == 0) {  // drain dW0 row f and db0[f]
-    float* gw0 = gnet + L.w0() + (int64_t)f * in;
-    for (int c0 = 0; c0 < n0; c0 += 16) {
-      float v[16];
-      tmem_ld16(lane_base + 256u + (uint32_t)c0, v);
+  {
+    // ---- everything else through shared memory in packed-parameter order:
+    //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
+    // each a contiguous, 16-byte aligned span of the parameter vector -> one flat float4 Adam pass
+    const int g1 = 128 * in, g2 = g1 + 128, g3 = g2 + 128, gtot = g3 + 128 * nout;
+    if (chalf == 0) {
+      for (int c0 = 0; c0 < n0; c0 += 16) {
+        float v[16];
+        tmem_ld16(lane_base + 256u + (uint32_t)c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (c0 + j < in) stg[trow * in + c0 + j] = v[j];
+      }
+      float v[32];
+      tmem_ld32(lane_base + 384u, v);
+      tmem_ld_wait();
+      float db = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+      stg[g2 + trow] = db;
+    } else {
+      float v[32];
+      tmem_ld32(lane_base + 352u, v);
+      tmem_ld_wait();
+      float db = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+      stg[g1 + trow] = db;
+      tmem_ld32(lane_base + 416u, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 16; ++j)
-        if (c0 + j < in) gw0[c0 + j] = v[j];
+      for (int o = 0; o < kOutMax; ++o)
+        if (o < nout) stg[g3 + o * 128 + trow] = v[o];
     }
-    float v[32];
-    tmem_ld32(lane_base + 384u, v);
-    tmem_ld_wait();
-    float db = 0.f;
+    __syncthreads();
+    const int64_t e_w0 = noff + L.w0() + (int64_t)ot * 128 * in, e_b1 = noff + L.b1(in) + ot * 128,
+                  e_b0 = noff + L.b0(in) + ot * 128, e_w2 = noff + L.w2(in) + ot * 128;
+    if (!kFused) {  // flat, 128-bit copy of the staged gradients into the gradient buffer
+      float* gagent = grads + (int64_t)agent * L.Pstride;
+      for (int i = tid * 4; i < gtot; i += 1024) {
+        int64_t e;
+        if (i < g1) e = e_w0 + i;
+        else if (i < g2) e = e_b1 + (i - g1);
+        else if (i < g3) e = e_b0 + (i - g2);
+        else e = e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
+        *reinterpret_cast<float4*>(gagent + e) = *reinterpret_cast<const float4*>(stg + i);
+      }
+    }
+    for (int i0 = tid * 4; kFused && i0 < gtot; i0 += 4096) {  // four float4 per thread in flight
+      float4 pq[4], mq[4], vq[4], tq[4];
+      int64_t eq[4];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
-    gnet[L.b0(in) + f] = db;
-  } else {  // dW2[:, f]
-    float v[32];
-    tmem_ld32(lane_base + 416u, v);
-    tmem_ld_wait();
-    float* gw2 = gnet + L.w2(in);
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 1024;
+        int64_t e = 0;
+        if (i < g1) e = e_w0 + i;
+        else if (i < g2) e = e_b1 + (i - g1);
+        else if (i < g3) e = e_b0 + (i - g2);
+        else if (i < gtot) e = e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
+        eq[u] = e;
+        if (i < gtot) {
+          pq[u] = *reinterpret_cast<const float4*>(A.p + e); mq[u] = *reinterpret_cast<const float4*>(A.m + e);
+          vq[u] = *reinterpret_cast<const float4*>(A.v + e);
+          tq[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
+        }
+      }
 #pragma unroll
-    for (int o = 0; o < kOutMax; ++o)
-      if (o < nout) gw2[(int64_t)o * L.H + f] = v[o];
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * 1024;
+        if (i >= gtot) continue;
+        const int64_t e = eq[u];
+        const float4 g = *reinterpret_cast<const float4*>(stg + i);
+        float4 &p = pq[u], &m = mq[u], &v = vq[u], &tg = tq[u];
+        adam_update(p.x, m.x, v.x, g.x, A.ss, A.bc2_sqrt); adam_update(p.y, m.y, v.y, g.y, A.ss, A.bc2_sqrt);
+        adam_update(p.z, m.z, v.z, g.z, A.ss, A.bc2_sqrt); adam_update(p.w, m.w, v.w, g.w, A.ss, A.bc2_sqrt);
+        *reinterpret_cast<float4*>(A.p + e) = p;
+        *reinterpret_cast<float4*>(A.m + e) = m;
+        *reinterpret_cast<float4*>(A.v + e) = v;
+        if (A.tgt) {
+          tg.x += A.tau * (p.x - tg.x); tg.y += A.tau * (p.y - tg.y); tg.z += A.tau * (p.z - tg.z); tg.w += A.tau * (p.w - tg.w);
+          *reinterpret_cast<float4*>(A.tgt + e) = tg;
+        }
+        if (i < g1) {  // W0 elements also live in the bf16 weight image
+          const float pv[4] = {p.x, p.y, p.z, p.w}, tv[4] = {tg.x, tg.y, tg.z, tg.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int r = (i + j) / in, c = (i + j) - r * in;
+            const int64_t ioff = image_off(L.H, ot * 128 + r, c);
+            *reinterpret_cast<__nv_bfloat16*>(A.img + ioff) = __float2bfloat16_rn(pv[j]);
+            if (A.tgt) *reinterpret_cast<__nv_bfloat16*>(A.timg + ioff) = __float2bfloat16_rn(tv[j]);
+          }
+        }
+      }
+    }
+    if (kFused && ot == 0) {  // head bias (and log_std): gradients were reduced by the loss kernel
+      if (tid < nout) adam_scalar(A, noff + L.b2(in, nout) + tid, gnet[L.b2(in, nout) + tid], -1);
+      if (t == 3 && !L.deterministic && tid >= 32 && tid < 32 + L.A)
+        adam_scalar(A, L.off_logstd + (tid - 32), grads[(int64_t)agent * L.Pstride + L.off_logstd + (tid - 32)], -1);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -596,7 +773,9 @@ int bf16_create(iqlb_agents* h) {
   if (rc) return rc;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bwd_weight_smem(L.B)));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)bwd_weight_smem(L.B)));
   st->dirty = true;
   return IQLB_OK;
@@ -660,9 +839,14 @@ int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
   bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 256, bwd_data_smem(), stream>>>(st->P, h->params, h->d_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_bwd_data");
-  bf16_bwd_weight_kernel<<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(st->P, h->grads);
+  if (h->fused_adam)
+    bf16_bwd_weight_kernel<true><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
+        st->P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
+  else
+    bf16_bwd_weight_kernel<false><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
+        st->P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
   IQLB_LAUNCH_CHECK();
-  pf.mark("bf16_bwd_weight");
+  pf.mark(h->fused_adam ? "bf16_bwd_weight_adam" : "bf16_bwd_weight");
   return IQLB_OK;
 }
 

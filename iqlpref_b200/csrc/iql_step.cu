@@ -243,25 +243,35 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 // agent, with the Polyak target update (iql.py:127-129,613) fused for the Q segment.
 // HBM-bound: 28 B read + 16 B written per parameter (+8 B per Q parameter for the target).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __restrict__ params,
-                                                          float4* __restrict__ exp_avg, float4* __restrict__ exp_avg_sq,
-                                                          float4* __restrict__ target, const float4* __restrict__ grads,
+__global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __restrict__ params,
+                                                          float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
+                                                          float* __restrict__ target, const float* __restrict__ grads,
                                                           const StepScalars* __restrict__ scal, BfParams BP, int shadow) {
+  // eight consecutive parameters per thread: network segments start on multiples of 8, so a group
+  // never straddles two optimizers, and inside W1 it is exactly one 16-byte chunk of the bf16 image
   const int agent = blockIdx.y;
-  const int64_t n4 = L.Pstride / 4;
-  const int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i4 >= n4) return;
+  const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (e0 >= L.Pstride) return;
   const StepScalars sc = scal[agent];
-  const int64_t g4 = (int64_t)agent * n4 + i4;
-  float4 p = params[g4], m = exp_avg[g4], v = exp_avg_sq[g4];
-  const float4 g = grads[g4];
-  float* pp = &p.x; float* mp = &m.x; float* vp = &v.x; const float* gp = &g.x;
-  const int64_t e0 = i4 * 4;
-  const int64_t v_begin = L.off_v, a_begin = L.off_a;
+  const int64_t g8 = (int64_t)agent * L.Pstride + e0;
+  float4 p[2], m[2], v[2], g[2], tg[2];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    const int64_t e = e0 + c;
-    const float ss = e < v_begin ? sc.ss_q : (e < a_begin ? sc.ss_v : sc.ss_a);
+  for (int h = 0; h < 2; ++h) {
+    p[h] = *reinterpret_cast<const float4*>(params + g8 + 4 * h);
+    m[h] = *reinterpret_cast<const float4*>(exp_avg + g8 + 4 * h);
+    v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g8 + 4 * h);
+    g[h] = *reinterpret_cast<const float4*>(grads + g8 + 4 * h);
+  }
+  const bool has_t = e0 < L.PQ;
+  const int64_t t8 = (int64_t)agent * L.PQstride + e0;
+  if (has_t) {
+    tg[0] = *reinterpret_cast<const float4*>(target + t8);
+    tg[1] = *reinterpret_cast<const float4*>(target + t8 + 4);
+  }
+  const float ss = e0 < L.off_v ? sc.ss_q : (e0 < L.off_a ? sc.ss_v : sc.ss_a);
+  float* pp = &p[0].x; float* mp = &m[0].x; float* vp = &v[0].x; const float* gp = &g[0].x; float* tp = &tg[0].x;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
     const float gg = gp[c];
     const float mm = mp[c] + (1.0f - 0.9f) * (gg - mp[c]);
     const float vv = 0.999f * vp[c] + (1.0f - 0.999f) * gg * gg;
@@ -269,35 +279,40 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float4* __re
     pp[c] = pp[c] - ss * (mm / denom);
     mp[c] = mm;
     vp[c] = vv;
+    if (has_t) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);  // Tensor.lerp_ (weight < 0.5), with the post-Adam qf
   }
-  uint8_t* wimg = shadow ? BP.wimg + (int64_t)agent * BP.agent_w_bytes : nullptr;
-  int snet[4];
-  int64_t soff[4];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    *reinterpret_cast<float4*>(params + g8 + 4 * h) = p[h];
+    *reinterpret_cast<float4*>(exp_avg + g8 + 4 * h) = m[h];
+    *reinterpret_cast<float4*>(exp_avg_sq + g8 + 4 * h) = v[h];
+  }
+  if (has_t) {
+    *reinterpret_cast<float4*>(target + t8) = tg[0];
+    *reinterpret_cast<float4*>(target + t8 + 4) = tg[1];
+  }
   if (shadow) {  // refresh the bf16 operand images of the weights just updated
+    uint8_t* wimg = BP.wimg + (int64_t)agent * BP.agent_w_bytes;
+    int net;
+    int64_t off;
+    if (shadow_loc(L, BP.KXB, e0, net, off) && off >= BP.w0_bytes) {  // W1: one aligned chunk
+      *reinterpret_cast<uint4*>(wimg + (int64_t)net * BP.net_bytes + off) =
+          make_uint4(umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]), umma::pack_bf16(pp[4], pp[5]),
+                     umma::pack_bf16(pp[6], pp[7]));
+      if (has_t)
+        *reinterpret_cast<uint4*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) =
+            make_uint4(umma::pack_bf16(tp[0], tp[1]), umma::pack_bf16(tp[2], tp[3]), umma::pack_bf16(tp[4], tp[5]),
+                       umma::pack_bf16(tp[6], tp[7]));
+    } else {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      snet[c] = -1;
-      if (shadow_loc(L, BP.KXB, e0 + c, snet[c], soff[c]))
-        *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)snet[c] * BP.net_bytes + soff[c]) = __float2bfloat16_rn(pp[c]);
-      else
-        snet[c] = -1;
-    }
-  }
-  params[g4] = p;
-  exp_avg[g4] = m;
-  exp_avg_sq[g4] = v;
-  if (e0 < L.PQ) {  // PQstride - PQ < 4 padding lanes stay zero (params there are zero)
-    const int64_t t4 = (int64_t)agent * (L.PQstride / 4) + i4;
-    float4 tg = target[t4];
-    float* tp = &tg.x;
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-      if (e0 + c < L.PQ) {
-        tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);
-        if (shadow && snet[c] >= 0)
-          *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)(snet[c] + 4) * BP.net_bytes + soff[c]) = __float2bfloat16_rn(tp[c]);
+      for (int c = 0; c < 8; ++c) {
+        if (shadow_loc(L, BP.KXB, e0 + c, net, off)) {
+          *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)net * BP.net_bytes + off) = __float2bfloat16_rn(pp[c]);
+          if (has_t)
+            *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) = __float2bfloat16_rn(tp[c]);
+        }
       }
-    target[t4] = tg;
+    }
   }
 }
 
@@ -408,12 +423,13 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw0, N * kTrain, L.H, L.Dq, true, st))) return rc;
     pf.mark("gemm_bwd_w0");
   }
-  const int64_t n4 = L.Pstride / 4;
-  adam_polyak_kernel<<<dim3((unsigned)((n4 + 255) / 256), N), 256, 0, st>>>(
-      L, (float4*)h->params, (float4*)h->exp_avg, (float4*)h->exp_avg_sq, (float4*)h->target, (const float4*)h->grads,
-      h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0);
-  IQLB_LAUNCH_CHECK();
-  pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
+  if (!(bf && h->fused_adam)) {
+    const int64_t n8 = L.Pstride / 8;
+    adam_polyak_kernel<<<dim3((unsigned)((n8 + 255) / 256), N), 256, 0, st>>>(
+        L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0);
+    IQLB_LAUNCH_CHECK();
+    pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
+  }
   pf.done();
   return IQLB_OK;
 }
@@ -532,6 +548,13 @@ extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampl
 extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   if (h->desc.precision == 1) return bf16_refresh(h, (cudaStream_t)stream);
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_debug_option(iqlb_agents* h, int32_t option, int32_t value) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  IQLB_REQUIRE(option == 0, "unknown option");
+  h->fused_adam = value != 0;
   return IQLB_OK;
 }
 

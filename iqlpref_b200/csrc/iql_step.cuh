@@ -23,16 +23,18 @@ struct Layout {
   __host__ __device__ static int64_t net_size(int in, int H, int out) {
     return (int64_t)H * in + H + (int64_t)H * H + H + (int64_t)out * H + out;
   }
+  __host__ __device__ static int64_t al8(int64_t n) { return (n + 7) / 8 * 8; }
   __host__ __device__ void init(int S_, int A_, int H_, int det, int R_, int B_) {
     S = S_; A = A_; H = H_; Dq = S_ + A_; R = R_; B = B_; deterministic = det;
     qnet = net_size(Dq, H, 1);
     vnet = net_size(S, H, 1);
     anet = net_size(S, H, A);
-    off_q1 = 0; off_q2 = qnet; off_v = 2 * qnet; off_a = off_v + vnet; off_logstd = off_a + anet;
-    PQ = 2 * qnet;
+    // every network starts on a 32-byte boundary, so rows of W1 are 128-bit addressable in all four
+    off_q1 = 0; off_q2 = al8(qnet); off_v = off_q2 + al8(qnet); off_a = off_v + al8(vnet); off_logstd = off_a + al8(anet);
+    PQ = off_v;
     P = off_logstd + (det ? 0 : A);
-    Pstride = (P + 3) / 4 * 4;
-    PQstride = (PQ + 3) / 4 * 4;
+    Pstride = al8(P);
+    PQstride = al8(PQ);
   }
   // offsets inside one network
   __host__ __device__ int64_t w0() const { return 0; }
@@ -158,6 +160,7 @@ struct iqlb_agents {
   iqlb::StepScalars* scal = nullptr;
   iqlb::GemmTask *t_fwd0 = nullptr, *t_fwd1 = nullptr, *t_bw1 = nullptr, *t_bd1 = nullptr, *t_bw0 = nullptr;
   void* bf16_state = nullptr;  // precision==1 extension (tcgen05 path)
+  bool fused_adam = false;     // precision==1: Adam/Polyak inside the weight-gradient kernel (debug option 0)
   // per-kernel CUDA-event timing (iqlb_agents_profile): ev[i], ev[i+1] bracket launch i of a step
   static constexpr int kMaxProf = 24;
   bool prof = false;

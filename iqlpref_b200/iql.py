@@ -358,7 +358,7 @@ class BatchedIQL:
         _lib.check(self.lib.iqlb_param_count(state_dim, action_dim, hidden_dim, int(self.deterministic),
                                              C.byref(p_all), C.byref(p_q)), "iqlb_param_count")
         self.P, self.PQ = p_all.value, p_q.value
-        self.Pstride, self.PQstride = (self.P + 3) // 4 * 4, (self.PQ + 3) // 4 * 4
+        self.Pstride, self.PQstride = (self.P + 7) // 8 * 8, (self.PQ + 7) // 8 * 8
         z = lambda *shape, dt=torch.float32: torch.zeros(shape, dtype=dt, device=self.device)
         self.params, self.exp_avg, self.exp_avg_sq = z(n_agents, self.Pstride), z(n_agents, self.Pstride), z(n_agents, self.Pstride)
         self.target = z(n_agents, self.PQstride)
@@ -409,6 +409,7 @@ class BatchedIQL:
                 n = int(np.prod(shape))
                 lay[f"{net}.{name}"] = (off, shape)
                 off += n
+            off = (off + 7) // 8 * 8  # every network segment is padded to 8 floats (Layout::init)
         if not self.deterministic:
             lay["log_std"] = (off, (A,))
             off += A
@@ -501,6 +502,9 @@ class BatchedIQL:
             out.append({"kernel": name.value.decode(), "ms_per_step": ms.value / max(steps.value, 1)})
             i += 1
         return out
+
+    def debug_option(self, option: int, value: int):
+        _lib.check(self.lib.iqlb_agents_debug_option(self._h, option, value), "iqlb_agents_debug_option")
 
     def debug_tensor(self, which: int) -> torch.Tensor:
         nbytes = C.c_int64()

@@ -32,13 +32,17 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_param_count_matches_reference_shapes(lib):
-    # 286 991 / 300 819 / 329 523 params per agent (Gaussian), Q = 144 386 / 151 554 / 167 938
+    # 286 991 / 300 819 / 329 523 params per agent (Gaussian), Q = 144 386 / 151 554 / 167 938;
+    # the packed layout pads each of the four network segments to a multiple of 8 floats
+    al8 = lambda n: (n + 7) // 8 * 8
     for (s, a), (p, pq) in {(17, 6): (286991, 144386), (29, 8): (300819, 151554), (45, 24): (329523, 167938)}.items():
+        qnet, vnet, anet = pq // 2, 256 * s + 256 + 65536 + 256 + 256 + 1, p - a - pq - (256 * s + 256 + 65536 + 256 + 256 + 1)
+        assert qnet * 2 == pq and anet == 256 * s + 256 + 65536 + 256 + 256 * a + a
         pa, pb = C.c_int64(), C.c_int64()
         assert lib.iqlb_param_count(s, a, 256, 0, C.byref(pa), C.byref(pb)) == 0
-        assert (pa.value, pb.value) == (p, pq)
+        assert (pa.value, pb.value) == (2 * al8(qnet) + al8(vnet) + al8(anet) + a, 2 * al8(qnet))
         assert lib.iqlb_param_count(s, a, 256, 1, C.byref(pa), C.byref(pb)) == 0
-        assert pa.value == p - a
+        assert pa.value == 2 * al8(qnet) + al8(vnet) + al8(anet)
     assert lib.iqlb_param_count(0, 1, 256, 0, None, None) == -1
     assert b"dims" in lib.iqlb_last_error()
 

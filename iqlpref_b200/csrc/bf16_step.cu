@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) shadow_refresh_kernel(BfParams P, const f
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __restrict__ batch) {
   const Layout& L = P.L;
-  const int agent = blockIdx.y;
+  const int agent = P.agent0 + blockIdx.y;
   const int chunks_per_row = P.KXB * 8;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= L.B * chunks_per_row) return;
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
                                                           float* __restrict__ head_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int half = blockIdx.x, s = blockIdx.y, agent = blockIdx.z;
+  const int half = blockIdx.x, s = blockIdx.y, agent = P.agent0 + blockIdx.z;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
   const int KXB = P.KXB, nring = 4 - KXB;
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int half = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
+  const int half = blockIdx.x, t = blockIdx.y, agent = P.agent0 + blockIdx.z;
   const int s = train_stream(t), net = net_of_stream(s);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
@@ -464,7 +464,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
                                                                  const StepScalars* __restrict__ scal) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int ot = blockIdx.x, t = blockIdx.y, agent = blockIdx.z;
+  const int ot = blockIdx.x, t = blockIdx.y, agent = P.agent0 + blockIdx.z;
   const int s = train_stream(t);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
@@ -746,6 +746,7 @@ int bf16_create(iqlb_agents* h) {
   h->bf16_state = st;
   BfParams& P = st->P;
   P.L = L;
+  P.agent0 = 0;
   P.KXB = (L.Dq + 63) / 64;
   P.w0_bytes = (int64_t)P.KXB * L.H * 128;
   P.net_bytes = P.w0_bytes + (int64_t)(L.H / 64) * L.H * 128;
@@ -811,40 +812,44 @@ int bf16_refresh(iqlb_agents* h, cudaStream_t stream) {
   return IQLB_OK;
 }
 
-int bf16_step_gemms_fwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
+int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream) {
   Bf16State* st = (Bf16State*)h->bf16_state;
   IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
   const Layout& L = h->L;
-  const int N = h->desc.n_agents;
+  const int N = n;
+  BfParams P = st->P;
+  P.agent0 = a0;
   int rc;
   if (st->dirty) {
     if ((rc = bf16_refresh(h, stream))) return rc;
     pf.mark("shadow_refresh");
   }
-  pack_x_kernel<<<dim3((unsigned)((L.B * st->P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(st->P, h->batch);
+  pack_x_kernel<<<dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(P, h->batch);
   IQLB_LAUNCH_CHECK();
   pf.mark("pack_x");
-  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(st->P.KXB), stream>>>(st->P, h->params, h->target,
+  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target,
                                                                                      h->head_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_fwd");
   return IQLB_OK;
 }
 
-int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream) {
+int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream) {
   Bf16State* st = (Bf16State*)h->bf16_state;
   IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
   const Layout& L = h->L;
-  const int N = h->desc.n_agents;
-  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 256, bwd_data_smem(), stream>>>(st->P, h->params, h->d_out);
+  const int N = n;
+  BfParams P = st->P;
+  P.agent0 = a0;
+  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 256, bwd_data_smem(), stream>>>(P, h->params, h->d_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_bwd_data");
   if (h->fused_adam)
     bf16_bwd_weight_kernel<true><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
-        st->P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
+        P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
   else
     bf16_bwd_weight_kernel<false><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
-        st->P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
+        P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
   IQLB_LAUNCH_CHECK();
   pf.mark(h->fused_adam ? "bf16_bwd_weight_adam" : "bf16_bwd_weight");
   return IQLB_OK;

@@ -7,6 +7,7 @@
 // Data dependences follow SURVEY.md 3.2: every forward reads start-of-step parameters; only the
 // Polyak update must see the post-Adam Q parameters, so it is fused into the Adam kernel.
 #include <new>
+#include <stdlib.h>
 
 #include "iql_step.cuh"
 
@@ -17,8 +18,8 @@ int launch_gather(const float* table, int64_t n_rows, int row_stride, int reward
                   int64_t* idx_out, float* batch_out, cudaStream_t stream);
 int bf16_create(iqlb_agents* h);
 void bf16_destroy(iqlb_agents* h);
-int bf16_step_gemms_fwd(iqlb_agents* h, Prof& pf, cudaStream_t stream);
-int bf16_step_gemms_bwd(iqlb_agents* h, Prof& pf, cudaStream_t stream);
+int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
+int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
 const BfParams* bf16_params(const iqlb_agents* h);
 void bf16_mark_dirty(iqlb_agents* h);
 int bf16_refresh(iqlb_agents* h, cudaStream_t stream);
@@ -68,9 +69,9 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
                             float* __restrict__ d_out, float* __restrict__ grads, float* __restrict__ losses,
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
                             uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
-                            uint8_t* __restrict__ dzimg, int64_t z_bytes) {
+                            uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0) {
   __shared__ float red[32];
-  const int agent = blockIdx.x, b = threadIdx.x;
+  const int agent = agent0 + blockIdx.x, b = threadIdx.x;
   const bool live = b < L.B;
   const float* hp = hparams + agent * IQLB_HP_STRIDE;
   const float discount = hp[0], beta = hp[2], iql_tau = hp[3];
@@ -246,10 +247,11 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __restrict__ params,
                                                           float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                           float* __restrict__ target, const float* __restrict__ grads,
-                                                          const StepScalars* __restrict__ scal, BfParams BP, int shadow) {
+                                                          const StepScalars* __restrict__ scal, BfParams BP, int shadow,
+                                                          int agent0) {
   // eight consecutive parameters per thread: network segments start on multiples of 8, so a group
   // never straddles two optimizers, and inside W1 it is exactly one 16-byte chunk of the bf16 image
-  const int agent = blockIdx.y;
+  const int agent = agent0 + blockIdx.y;
   const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (e0 >= L.Pstride) return;
   const StepScalars sc = scal[agent];
@@ -377,42 +379,42 @@ static int build_tasks(iqlb_agents* h) {
   return IQLB_OK;
 }
 
-static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
+// The launch chain of one update for agents [a0, a0+n) up to (not including) the optimizer.
+static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cudaStream_t st) {
   const Layout& L = h->L;
-  const int N = h->desc.n_agents;
+  const bool bf = h->desc.precision == 1;
+  const BfParams* bp = bf16_params(h);
   int rc;
-  Prof pf(h, st);
   if (sampled) {
     IQLB_REQUIRE(h->table != nullptr, "no replay table attached (iqlb_agents_set_replay)");
-    rc = launch_gather(h->table, h->n_rows, L.R, 2 * L.S + L.A, h->reward_cols, h->reward_variant, h->rng, nullptr, N,
-                       L.B, h->idx_out, h->batch, st);
+    rc = launch_gather(h->table, h->n_rows, L.R, 2 * L.S + L.A, h->reward_cols,
+                       h->reward_variant ? h->reward_variant + a0 : nullptr, h->rng + 2 * a0, nullptr, n, L.B,
+                       h->idx_out ? h->idx_out + (int64_t)a0 * L.B : nullptr, h->batch + (int64_t)a0 * L.B * L.R, st);
     if (rc) return rc;
     pf.mark("replay_gather");
   }
-  const bool bf = h->desc.precision == 1;
-  const BfParams* bp = bf16_params(h);
   if (bf) {
-    if ((rc = bf16_step_gemms_fwd(h, pf, st))) return rc;
+    if ((rc = bf16_step_gemms_fwd(h, a0, n, pf, st))) return rc;
   } else {
+    const int N = h->desc.n_agents;  // the fp32 parity path always runs all agents in one group
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd0, N * kStreams, L.B, L.H, false, st))) return rc;
     pf.mark("gemm_fwd_l0");
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd1, N * kStreams, L.B, L.H, false, st))) return rc;
     pf.mark("gemm_fwd_l1");
-  }
-  if (!bf) {
     head_fwd_kernel<<<dim3((L.B + 7) / 8, kStreams, N), 256, 0, st>>>(L, h->params, h->target, h->H2, h->head_out);
     IQLB_LAUNCH_CHECK();
     pf.mark("head_fwd");
   }
   const int lb = (L.B + 31) / 32 * 32;
-  loss_kernel<<<N, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
+  loss_kernel<<<n, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
                                 h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0,
-                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0);
+                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0, a0);
   IQLB_LAUNCH_CHECK();
   pf.mark("loss");
   if (bf) {
-    if ((rc = bf16_step_gemms_bwd(h, pf, st))) return rc;
+    if ((rc = bf16_step_gemms_bwd(h, a0, n, pf, st))) return rc;
   } else {
+    const int N = h->desc.n_agents;
     head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
     IQLB_LAUNCH_CHECK();
     pf.mark("head_bwd");
@@ -423,13 +425,47 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw0, N * kTrain, L.H, L.Dq, true, st))) return rc;
     pf.mark("gemm_bwd_w0");
   }
-  if (!(bf && h->fused_adam)) {
-    const int64_t n8 = L.Pstride / 8;
-    adam_polyak_kernel<<<dim3((unsigned)((n8 + 255) / 256), N), 256, 0, st>>>(
-        L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0);
-    IQLB_LAUNCH_CHECK();
-    pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
+  return IQLB_OK;
+}
+
+static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
+  const Layout& L = h->L;
+  const bool bf = h->desc.precision == 1;
+  if (bf && h->fused_adam) return IQLB_OK;
+  const BfParams* bp = bf16_params(h);
+  const int64_t n8 = L.Pstride / 8;
+  adam_polyak_kernel<<<dim3((unsigned)((n8 + 255) / 256), n), 256, 0, st>>>(
+      L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0, a0);
+  IQLB_LAUNCH_CHECK();
+  pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
+  return IQLB_OK;
+}
+
+// One update of every agent.  precision 1 with >= 32 agents splits the agents into groups: the
+// tensor-core chain of group g+1 (latency-bound, on the caller's stream) overlaps the HBM-bound Adam
+// kernel of group g (on an internal stream that is forked from and joined to the caller's stream
+// inside this call, so stream ordering for the caller is unchanged).  Profiling runs one group.
+static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
+  const int N = h->desc.n_agents;
+  int rc;
+  Prof pf(h, st);
+  int G = (h->desc.precision == 1 && !h->prof && !h->fused_adam) ? h->n_groups : 1;
+  if (G <= 1) {
+    if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
+    if ((rc = step_adam(h, 0, N, pf, st))) return rc;
+    pf.done();
+    return IQLB_OK;
   }
+  const int per = (N + G - 1) / G;
+  for (int g = 0, a0 = 0; a0 < N; ++g, a0 += per) {
+    const int n = a0 + per <= N ? per : N - a0;
+    if ((rc = step_chain(h, a0, n, sampled, pf, st))) return rc;
+    IQLB_CUDA(cudaEventRecord(h->ev_chain[g], st));
+    IQLB_CUDA(cudaStreamWaitEvent(h->side_stream, h->ev_chain[g], 0));
+    if ((rc = step_adam(h, a0, n, pf, h->side_stream))) return rc;
+  }
+  IQLB_CUDA(cudaEventRecord(h->ev_join, h->side_stream));
+  IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
   pf.done();
   return IQLB_OK;
 }
@@ -487,6 +523,20 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   if (!rc) rc = alloc((float**)&h->scal, N * (int64_t)(sizeof(StepScalars) / sizeof(float)));
   if (!rc) rc = build_tasks(h);
   if (!rc && d->precision == 1) rc = bf16_create(h);
+  if (!rc && d->precision == 1) {
+    const char* env = getenv("IQLB_GROUPS");
+    int G = env ? atoi(env) : 1;  // measured on B200: splitting 64 agents into groups is slower
+    if (G < 1) G = 1;
+    if (G > iqlb_agents::kMaxGroups) G = iqlb_agents::kMaxGroups;
+    if (G > d->n_agents) G = d->n_agents;
+    h->n_groups = G;
+    if (G > 1) {
+      if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaStreamCreate%s", "");
+      for (int g = 0; g < G && !rc; ++g)
+        if (cudaEventCreateWithFlags(&h->ev_chain[g], cudaEventDisableTiming) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaEventCreate%s", "");
+      if (!rc && cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaEventCreate%s", "");
+    }
+  }
   if (rc) { iqlb_agents_destroy(h); return rc; }
   *out = h;
   return IQLB_OK;
@@ -495,6 +545,9 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
 extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
   if (!h) return IQLB_OK;
   bf16_destroy(h);
+  if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
+  for (int g = 0; g < iqlb_agents::kMaxGroups; ++g) if (h->ev_chain[g]) cudaEventDestroy(h->ev_chain[g]);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   cudaFree(h->batch); cudaFree(h->H1); cudaFree(h->H2); cudaFree(h->head_out); cudaFree(h->d_out);
   cudaFree(h->dH2); cudaFree(h->dH1); cudaFree(h->grads); cudaFree(h->scal);
   for (int i = 0; i <= iqlb_agents::kMaxProf; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);

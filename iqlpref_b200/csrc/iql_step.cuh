@@ -87,6 +87,7 @@ constexpr int kOutMax = 24;  // widest head handled in registers (actor action_d
 struct BfParams {
   Layout L;
   int KXB;                // 64-column blocks of the input images (ceil((S+A)/64))
+  int agent0;             // first agent of this launch (agent groups are pipelined, iql_step.cu)
   int64_t w0_bytes;       // W0 image bytes  = KXB * H * 128
   int64_t net_bytes;      // W0 + W1 images of one network
   int64_t agent_w_bytes;  // 6 networks: Q1 Q2 V actor Qt1 Qt2
@@ -169,6 +170,13 @@ struct iqlb_agents {
   double prof_ms[kMaxProf] = {};
   int prof_n = 0, prof_steps = 0;
   int launches_last = 0;
+  // agent-group pipelining (precision 1): Adam of group g runs on side_stream while the tensor-core
+  // chain of group g+1 runs on the caller's stream
+  static constexpr int kMaxGroups = 8;
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_chain[kMaxGroups] = {};
+  cudaEvent_t ev_join = nullptr;
+  int n_groups = 1;
 };
 
 namespace iqlb {

@@ -58,15 +58,14 @@ __device__ __forceinline__ void store_tile(float (*s)[ROWS + 4], const float (&r
 }
 
 template <int MODE, int BN>
-__global__ void __launch_bounds__(256) grouped_gemm_kernel(const GemmTask* __restrict__ tasks) {
+__device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
   constexpr int TN = BN / 16;
   constexpr bool A_KC = (MODE != GEMM_BWD_WEIGHT);
-  constexpr bool B_KC = (MODE == GEMM_FWD);
-  const GemmTask t = tasks[blockIdx.y];
+  constexpr bool B_KC = (MODE == GEMM_FWD || MODE == GEMM_LINEAR);
   const int tiles_n = (t.N + BN - 1) / BN;
   const int tiles_m = (t.M + BM - 1) / BM;
-  if ((int)blockIdx.x >= tiles_m * tiles_n) return;
-  const int tm = blockIdx.x / tiles_n, tn = blockIdx.x % tiles_n;
+  if (tile >= tiles_m * tiles_n) return;
+  const int tm = tile / tiles_n, tn = tile % tiles_n;
   const int m0 = tm * BM, n0 = tn * BN;
 
   __shared__ __align__(16) float As[BK][BM + 4];
@@ -140,11 +139,47 @@ __global__ void __launch_bounds__(256) grouped_gemm_kernel(const GemmTask* __res
         v = (__ldg(t.mask + (int64_t)m * t.ldc + n) > 0.f) ? v : 0.f;
       } else if (MODE == GEMM_FWD_KN) {
         v = apply_act(t.act, fmaf(t.scale, v, __ldg(t.bias + n)));
+      } else if (MODE == GEMM_LINEAR) {  // nn.Linear: act(A W^T + bias) (+ residual, carried in t.mask)
+        v = apply_act(t.act, v + (t.bias ? __ldg(t.bias + n) : 0.f));
+        if (t.mask != nullptr) v += t.mask[(int64_t)m * t.ldc + n];
       }
       t.C[(int64_t)m * t.ldc + n] = v;
     }
     if (want_bsum && tx == 0) t.bias_grad[m] = asum[i];
   }
+}
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(256) grouped_gemm_kernel(const GemmTask* __restrict__ tasks) {
+  const GemmTask t = tasks[blockIdx.y];
+  gemm_body<MODE, BN>(t, (int)blockIdx.x);
+}
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(256) single_gemm_kernel(const GemmTask t) {
+  gemm_body<MODE, BN>(t, (int)blockIdx.x);
+}
+
+// One GEMM with the task passed by value (no device-side task array).
+int launch_gemm(GemmMode mode, const GemmTask& t, cudaStream_t stream) {
+  if (t.M <= 0 || t.N <= 0) return IQLB_OK;
+  const int tiles_m = (t.M + BM - 1) / BM;
+  const bool narrow = t.N <= 32;
+  const unsigned grid = (unsigned)(tiles_m * (narrow ? (t.N + 31) / 32 : (t.N + 127) / 128));
+  switch (mode) {
+    case GEMM_LINEAR:
+      if (narrow) single_gemm_kernel<GEMM_LINEAR, 32><<<grid, 256, 0, stream>>>(t);
+      else single_gemm_kernel<GEMM_LINEAR, 128><<<grid, 256, 0, stream>>>(t);
+      break;
+    case GEMM_FWD_KN:
+      if (narrow) single_gemm_kernel<GEMM_FWD_KN, 32><<<grid, 256, 0, stream>>>(t);
+      else single_gemm_kernel<GEMM_FWD_KN, 128><<<grid, 256, 0, stream>>>(t);
+      break;
+    default:
+      return fail(IQLB_ERR_UNSUPPORTED, "launch_gemm: unsupported mode%s", "");
+  }
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
 }
 
 template <int MODE>

@@ -73,12 +73,13 @@ struct GemmTask {
   int act;              // FWD_KN: IQLB_ACT_* id
 };
 
-enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3 };
+enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3, GEMM_LINEAR = 4 };
 
 struct StepScalars {  // per agent, written by the loss kernel, read by Adam
   float ss_q, ss_v, ss_a, bc2_sqrt, tau;
 };
 
+int launch_gemm(GemmMode mode, const GemmTask& t, cudaStream_t stream);
 int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
                         cudaStream_t stream);
 

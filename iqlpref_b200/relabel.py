@@ -356,15 +356,26 @@ def pt_windows_from_steps(ep_steps: np.ndarray, query_length: int):
 
 
 def pt_predict(r_model, obs_all: np.ndarray, act_all: np.ndarray, win_start: np.ndarray, seq_len: np.ndarray,
-               query_length: int, device=None) -> torch.Tensor:
+               query_length: int, device=None, dedupe: bool = True) -> torch.Tensor:
     """value[:, 0, -1, 0] of the preference transformer for every window (CUDA tensor [n])."""
     dev = _cuda_device(device if device is not None else next(r_model.parameters()).device)
     desc = pt_desc_from_model(r_model, query_length)
     weights = pack_pt_weights(r_model, desc).to(dev)
     obs = torch.as_tensor(obs_all, dtype=torch.float32).to(dev).contiguous()
     act = torch.as_tensor(act_all, dtype=torch.float32).to(dev).contiguous()
-    ws = torch.as_tensor(win_start, dtype=torch.int32).to(dev).contiguous()
-    sl = torch.as_tensor(seq_len, dtype=torch.int32).to(dev).contiguous()
+    # identical (start, length) windows give identical rewards: evaluate each distinct window once.
+    # (With the reference's episode-step-as-row-index behaviour, SURVEY F4, a 1M-row dataset has at
+    # most max_episode_steps distinct windows.)
+    pairs = np.stack([np.asarray(win_start, dtype=np.int64), np.asarray(seq_len, dtype=np.int64)], axis=1)
+    inverse = None
+    if dedupe and pairs.shape[0] > 1:
+        uniq, inverse = np.unique(pairs, axis=0, return_inverse=True)
+        if uniq.shape[0] < pairs.shape[0]:
+            win_start, seq_len = uniq[:, 0], uniq[:, 1]
+        else:
+            inverse = None
+    ws = torch.as_tensor(np.asarray(win_start), dtype=torch.int32).to(dev).contiguous()
+    sl = torch.as_tensor(np.asarray(seq_len), dtype=torch.int32).to(dev).contiguous()
     n = ws.shape[0]
     if n and int((ws.long() + sl.long()).max().item()) > obs.shape[0]:
         raise ValueError("a window reaches past the end of the dataset")
@@ -373,6 +384,8 @@ def pt_predict(r_model, obs_all: np.ndarray, act_all: np.ndarray, win_start: np.
     _lib.check(lib.iqlb_relabel_pt(C.byref(desc), _lib.ptr(weights), _lib.ptr(obs), _lib.ptr(act), obs.shape[0],
                                    _lib.ptr(ws), _lib.ptr(sl), n, _lib.ptr(out), _lib.stream_ptr(dev)),
                "iqlb_relabel_pt")
+    if inverse is not None:
+        out = out[torch.as_tensor(inverse.reshape(-1), dtype=torch.int64, device=dev)]
     return out
 
 

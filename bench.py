@@ -399,6 +399,10 @@ def run_cuda(args):
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
 
+    # the path's only training collective: logged loss rows of every rank (outside the timed region)
+    from iqlpref_b200 import sharding
+    all_losses = sharding.gather_losses(eng.losses, world * N)
+    assert tuple(all_losses.shape) == (world * N, 3) and bool(torch.isfinite(all_losses).all())
     if rank == 0:
         peaks = load_peaks()
         roof, table = kernel_roofline(prof, N, peaks)
@@ -438,7 +442,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--agents-per-gpu", type=int, default=64)
     ap.add_argument("--rows", type=int, default=1_000_000)
-    ap.add_argument("--precision", default=os.environ.get("IQLB_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("IQLB_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--cpu-steps", type=int, default=40)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     args = ap.parse_args()

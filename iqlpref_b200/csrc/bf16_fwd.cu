@@ -1,0 +1,312 @@
+// Persistent, warp-specialised forward kernel of the bf16 IQL step (one CTA per SM, tiles =
+// (agent, stream, half batch) taken round-robin).  Same arithmetic and outputs as bf16_fwd_kernel
+// (bf16_step.cu); what changes is the schedule:
+//
+//   warp 0  producer : bulk copies (X tile, b0 | W0 and the four W1 K-blocks through a 4-slot ring); b1, W2 by the epilogue
+//   warp 1  MMA      : tcgen05.mma issue; layer 1 starts on K-block kb as soon as the epilogue has
+//                      written H1 block kb, so the tensor core trails the epilogue by one block
+//   warps 2-9        : epilogue (2 warps per TMEM lane quarter, 32 of every 64 columns each)
+//
+// While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
+// MMA warp has issued its layer 0, so loads, both GEMMs, TMEM allocation and barrier set-up disappear
+// from the critical path: a tile costs roughly its two epilogues.
+// Used when the input image is one 64-column block (state_dim + action_dim <= 64) and action_dim <= 8.
+#include "iql_step.cuh"
+#include "umma.cuh"
+
+namespace iqlb {
+using namespace umma;
+
+namespace fwdp {
+// shared memory: H tile | 4-slot ring of 32 KB operand blocks (W0, then the four W1 K-blocks of a tile)
+//                | X tile | b0 (x2) | b1 + W2 | head partial sums | barriers
+constexpr uint32_t oH = 0, oRing = 65536, oX = 196608, oB0 = 212992, oBW = 215040, kBWBytes = 9216, oPart = 224256,
+                   oCtrl = 228352, kSmem = 228352 + 256;
+constexpr int kSlots = 4, kPerTile = 5;
+// barrier indices (8 bytes each) inside the control block
+enum { FULL_L0 = 0, MMA0 = 1, MMA1 = 2, FULL_R = 3, EMPTY_R = 7, HBLK = 11, ACC0_FREE = 15, ACC1_FREE = 16, FULL_BW = 17,
+       N_BARS = 18 };
+}  // namespace fwdp
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ void st_chunk128(uint8_t* tile, int row, int col0, const float* v) {
+  const int off = (col0 >> 6) * 16384 + row * 128 + ((((col0 & 63) >> 3) ^ (row & 7)) << 4);
+  *reinterpret_cast<uint4*>(tile + off) =
+      make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+
+__global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, const float* __restrict__ params,
+                                                                  const float* __restrict__ target,
+                                                                  float* __restrict__ head_out, int n_tiles) {
+  using namespace fwdp;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const Layout& L = P.L;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t bars = sbase + oCtrl;
+  auto bar = [&](int i) -> uint32_t { return bars + 8u * (uint32_t)i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 8 * N_BARS);
+
+  if (tid == 0) {
+    if (sbase & 1023u) __trap();
+    mbar_init(bar(FULL_L0), 1); mbar_init(bar(MMA0), 1); mbar_init(bar(MMA1), 1); mbar_init(bar(FULL_BW), 1);
+    for (int i = 0; i < kSlots; ++i) { mbar_init(bar(FULL_R + i), 1); mbar_init(bar(EMPTY_R + i), 1); }
+    for (int i = 0; i < 4; ++i) mbar_init(bar(HBLK + i), 8);
+    mbar_init(bar(ACC0_FREE), 8); mbar_init(bar(ACC1_FREE), 8);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 8 * N_BARS, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
+                       const float*& fnet) {
+    const int nh = L.B / 128;
+    half = tile % nh;
+    const int r = tile / nh;
+    s = r % kStreams;
+    agent = P.agent0 + r / kStreams;
+    wnet = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net_of_stream(s) * P.net_bytes;
+    ximg = (s == 0 ? P.xnext : P.xsa) + (int64_t)agent * P.x_bytes;
+    fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
+                            : params + (int64_t)agent * L.Pstride + L.net_off(s);
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      int c = 0;  // ring entries issued so far (5 per tile: W0, W1 block 0..3)
+      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        int agent, s, half;
+        const uint8_t *wnet, *ximg;
+        const float* fnet;
+        tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
+        const int in = L.in_dim(s);
+        if (it > 0) mbar_wait(bar(MMA0), (uint32_t)((it - 1) & 1));  // layer 0 of the previous tile has consumed X
+        mbar_expect_tx(bar(FULL_L0), 16384u + 1024u);
+        bulk_g2s(sbase + oX, ximg + (int64_t)half * 16384, 16384u, bar(FULL_L0));
+        bulk_g2s(sbase + oB0 + (uint32_t)(it & 1) * 1024u, fnet + L.b0(in), 1024u, bar(FULL_L0));
+        for (int e = 0; e < kPerTile; ++e, ++c) {
+          const int slot = c % kSlots, use = c / kSlots;
+          if (use > 0) mbar_wait(bar(EMPTY_R + slot), (uint32_t)((use - 1) & 1));
+          mbar_expect_tx(bar(FULL_R + slot), 32768u);
+          bulk_g2s(sbase + oRing + (uint32_t)slot * 32768u, e == 0 ? wnet : wnet + P.w0_bytes + (int64_t)(e - 1) * 32768, 32768u,
+                   bar(FULL_R + slot));
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      int c = 0;
+      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t ph = (uint32_t)(it & 1);
+        const int s = (tile / (L.B / 128)) % kStreams;
+        const int in = L.in_dim(s);
+        {
+          const int slot = c % kSlots, use = c / kSlots;
+          mbar_wait(bar(FULL_L0), ph);
+          mbar_wait(bar(FULL_R + slot), (uint32_t)(use & 1));
+          if (it > 0) mbar_wait(bar(ACC0_FREE), (uint32_t)((it - 1) & 1));
+          tc_fence_after();
+          gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oRing + (uint32_t)slot * 32768u, L.H, 0),
+                     256, (in + 15) / 16, false);
+          mma_commit(bar(EMPTY_R + slot));
+          mma_commit(bar(MMA0));
+          ++c;
+        }
+        for (int kb = 0; kb < 4; ++kb, ++c) {
+          const int slot = c % kSlots, use = c / kSlots;
+          mbar_wait(bar(HBLK + kb), ph);
+          mbar_wait(bar(FULL_R + slot), (uint32_t)(use & 1));
+          if (kb == 0 && it > 0) mbar_wait(bar(ACC1_FREE), (uint32_t)((it - 1) & 1));
+          tc_fence_after();
+          gemm_issue(tmem + 256, operand_k_major(sbase + oH + (uint32_t)kb * 16384u, 128, 0),
+                     operand_k_major(sbase + oRing + (uint32_t)slot * 32768u, L.H, 0), 256, 4, kb > 0);
+          mma_commit(bar(EMPTY_R + slot));
+        }
+        mma_commit(bar(MMA1));
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (256 threads)
+    const int et = tid - 64;
+    bool h1_store_pending = false;
+    const int quarter = warp & 3, chalf = (warp - 2) >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+    auto load_bw = [&](int tile) {  // b1 and W2 (fp32) of a tile into their single buffer
+      int agent, s, half;
+      const uint8_t *wnet, *ximg;
+      const float* fnet;
+      tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
+      const int in = L.in_dim(s), nout = L.out_dim(s);
+      mbar_expect_tx(bar(FULL_BW), 1024u + (uint32_t)nout * 1024u);
+      bulk_g2s(sbase + oBW, fnet + L.b1(in), 1024u, bar(FULL_BW));
+      bulk_g2s(sbase + oBW + 1024u, fnet + L.w2(in), (uint32_t)nout * 1024u, bar(FULL_BW));
+    };
+    if (et == 0 && (int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
+    for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = (uint32_t)(it & 1);
+      float* part = reinterpret_cast<float*>(smem + oPart);
+      const float* sb1 = reinterpret_cast<const float*>(smem + oBW);
+      const float* sw2 = sb1 + 256;
+      int agent, s, half;
+      const uint8_t *wnet, *ximg;
+      const float* fnet;
+      tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
+      const int in = L.in_dim(s), nout = L.out_dim(s), t = train_index(s);
+      const int brow = half * 128 + row;
+      const float* sb0 = reinterpret_cast<const float*>(smem + oB0 + (it & 1) * 1024);
+      uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+      uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+      // (b0 landed before layer 0 was issued; FULL_L0 itself may already be a phase ahead, so it is
+      //  not waited on here - MMA0 cannot run ahead of this warp because layer 0 waits for ACC0_FREE)
+      mbar_wait(bar(MMA0), ph);
+      tc_fence_after();
+      if (h1_store_pending) {  // the previous trainable tile's H1 image must have left the H tile
+        if (et == 0) bulk_wait_read0();
+        named_bar_sync(1, 256);
+        h1_store_pending = false;
+      }
+      // ---- epilogue 0: H1 = relu(acc0 + b0), block by block so that layer 1 can start behind us
+#pragma unroll 1
+      for (int blk = 0; blk < 4; ++blk) {
+        const int c0 = blk * 64 + chalf * 32;
+        float v[32];
+        tmem_ld32(lane_base + (uint32_t)c0, v);
+        tmem_ld_wait();
+        uint32_t m = 0;
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 bb = *reinterpret_cast<const float4*>(sb0 + c0 + 4 * j4);
+          const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
+          const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
+          v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
+          m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
+        }
+        if (m1) m1[c0 >> 5] = m;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) st_chunk128(smem + oH, row, c0 + 8 * q, v + 8 * q);
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(HBLK + blk));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(ACC0_FREE));
+      if (t >= 0) {
+        named_bar_sync(1, 256);
+        if (et == 0) {
+          uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+          for (int cb = 0; cb < 4; ++cb)
+            bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+          bulk_commit();
+        }
+        h1_store_pending = true;
+      }
+      mbar_wait(bar(FULL_BW), ph);
+      mbar_wait(bar(MMA1), ph);
+      tc_fence_after();
+      // ---- epilogue 1: H2 = relu(acc1 + b1); head = H2 . W2 + b2
+      float acc[8];
+#pragma unroll
+      for (int o = 0; o < 8; ++o) acc[o] = 0.f;
+      // image of H2 restricted to this half batch: block cb at cb*B*128, rows of this half at +half*16384
+      uint8_t* h2row = t >= 0 ? P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes + (int64_t)half * 16384 : nullptr;
+#pragma unroll 1
+      for (int blk = 0; blk < 4; ++blk) {
+        const int c0 = blk * 64 + chalf * 32;
+        float v[32];
+        tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
+        tmem_ld_wait();
+        uint32_t m = 0;
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 bb = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * j4);
+          const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
+          const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
+          v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
+          m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
+        }
+#pragma unroll
+        for (int o = 0; o < 8; ++o) {
+          if (o < nout) {
+            const float* wr = sw2 + o * 256 + c0;
+            float a = acc[o];
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
+              a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
+              a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
+            }
+            acc[o] = a;
+          }
+        }
+        if (t >= 0) {  // H2 goes straight from registers to its image in HBM (four 16-byte chunks of this row)
+          m2[c0 >> 5] = m;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {  // global image blocks hold all B rows: block stride B*128 bytes
+            const int col = c0 + 8 * q;
+            uint8_t* dst = h2row + (int64_t)(col >> 6) * L.B * 128 + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
+                                                        pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(ACC1_FREE));
+      if (chalf == 1) {
+#pragma unroll
+        for (int o = 0; o < 8; ++o)
+          if (o < nout) part[o * 128 + row] = acc[o];
+      }
+      named_bar_sync(1, 256);
+      if (et == 0 && tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);  // every warp is done with b1 / W2
+      if (chalf == 0) {
+        const float* b2 = fnet + L.b2(in, nout);
+        float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
+#pragma unroll
+        for (int o = 0; o < 8; ++o) {
+          if (o < nout) {
+            const float z = acc[o] + part[o * 128 + row] + __ldg(b2 + o);
+            if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
+            else ho[(int64_t)s * L.B + brow] = z;
+          }
+        }
+      }
+    }
+    if (h1_store_pending && et == 0) bulk_wait_read0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
+                            cudaStream_t stream) {
+  static int n_sm = 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    int dev = 0;
+    IQLB_CUDA(cudaGetDevice(&dev));
+    IQLB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwdp::kSmem));
+    attr_set = true;
+  }
+  const int n_tiles = n_agents * kStreams * (P.L.B / 128);
+  const int grid = n_tiles < n_sm ? n_tiles : n_sm;
+  bf16_fwd_persist_kernel<<<grid, 320, fwdp::kSmem, stream>>>(P, params, target, head_out, n_tiles);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+bool bf16_fwd_persist_ok(const BfParams& P) { return P.KXB == 1 && P.L.A <= 8 && P.L.H == 256; }
+
+}  // namespace iqlb

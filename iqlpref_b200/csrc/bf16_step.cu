@@ -15,6 +15,8 @@
 // 1-D bulk copies.  Accumulation is fp32 in TMEM; parameters, Adam state and the Polyak target stay
 // fp32 (iql_step.cu), and the Adam kernel refreshes the bf16 weight images it just updated.
 #include "iql_step.cuh"
+#include <stdlib.h>
+
 #include "umma.cuh"
 
 namespace iqlb {
@@ -735,6 +737,10 @@ static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u +
 static size_t bwd_data_smem() { return 65536u + 131072u + 32768u + 128u; }
 static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
 
+int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
+                            cudaStream_t stream);
+bool bf16_fwd_persist_ok(const BfParams& P);
+
 int bf16_create(iqlb_agents* h) {
   const Layout& L = h->L;
   IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
@@ -827,9 +833,13 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   pack_x_kernel<<<dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(P, h->batch);
   IQLB_LAUNCH_CHECK();
   pf.mark("pack_x");
-  bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target,
-                                                                                     h->head_out);
-  IQLB_LAUNCH_CHECK();
+  static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
+  if (persist_env && bf16_fwd_persist_ok(P)) {
+    if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream))) return rc;
+  } else {
+    bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
+    IQLB_LAUNCH_CHECK();
+  }
   pf.mark("bf16_fwd");
   return IQLB_OK;
 }

@@ -247,6 +247,8 @@ def build_workload(args, dev, rank):
         qf, vf, ac = biql.TwinQ(S_DIM, A_DIM), biql.ValueFunction(S_DIM), biql.GaussianPolicy(S_DIM, A_DIM, 1.0)
         eng.adopt(a, qf, vf, ac, bind=False)
     eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
+    if args.precision == "bf16":
+        eng.debug_option(0, int(args.fused_adam))
     return eng, buf, cols, variant, {"rows_per_s": rows / (relabel_ms * 1e-3), "ms": relabel_ms, "rows": rows,
                                      "model": "RewardMLP(37,1,[128]*3,relu)"}
 
@@ -268,9 +270,13 @@ def kernel_roofline(prof, n_agents, peaks):
     f_head = 2 * B * H * (6 + A) + 2 * 2 * B * H * (3 + A)
     work = {  # name -> (bound, algorithmic amount per agent: bytes for hbm, flops for tensor)
         "replay_gather": ("hbm", 2 * B * row),
+        "replay_gather_pack": ("hbm", 2 * B * row + 2 * B * 128),  # rows read + written, two bf16 images written
+        "pack_x": ("hbm", B * row + 2 * B * 128),
         "gemm_fwd_l0": ("tensor", f_l0), "gemm_fwd_l1": ("tensor", f_l1), "gemm_bwd_w1": ("tensor", f_bw1),
         "gemm_bwd_d1": ("tensor", f_bd1), "gemm_bwd_w0": ("tensor", f_bw0),
         "bf16_fwd": ("tensor", f_l0 + f_l1), "bf16_bwd": ("tensor", f_bw1 + f_bd1 + f_bw0),
+        "bf16_bwd_data": ("tensor", f_bd1), "bf16_bwd_weight": ("tensor", f_bw1 + f_bw0),
+        "bf16_bwd_weight_adam": ("hbm", 24 * p + 8 * pq + 2 * (p + pq)),
         "head_fwd": ("hbm", 7 * B * H * 4), "head_bwd": ("hbm", 4 * 2 * B * H * 4), "loss": ("hbm", B * row),
         "adam_polyak": ("hbm", 24 * p + 8 * pq + 4 * p),  # p,m,v r+w, target r+w, grads read
         "adam_polyak_shadow": ("hbm", 24 * p + 8 * pq + 4 * p + 2 * (p + pq)),
@@ -445,6 +451,8 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("IQLB_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--cpu-steps", type=int, default=40)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--fused-adam", type=int, default=int(os.environ.get("IQLB_FUSED_ADAM", "0")),
+                    help="1: Adam/Polyak inside the weight-gradient kernel (gradients never reach HBM)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -6,6 +6,7 @@
 //   warp 1  MMA      : tcgen05.mma issue; layer 1 starts on K-block kb as soon as the epilogue has
 //                      written H1 block kb, so the tensor core trails the epilogue by one block
 //   warps 2-9        : epilogue (2 warps per TMEM lane quarter, 32 of every 64 columns each)
+//                      H1 / H2 tiles are staged in shared memory and leave as bulk stores
 //
 // While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
 // MMA warp has issued its layer 0, so loads, both GEMMs, TMEM allocation and barrier set-up disappear
@@ -19,13 +20,19 @@ using namespace umma;
 
 namespace fwdp {
 // shared memory: H tile | 4-slot ring of 32 KB operand blocks (W0, then the four W1 K-blocks of a tile)
-//                | X tile | b0 (x2) | b1 + W2 | head partial sums | barriers
-constexpr uint32_t oH = 0, oRing = 65536, oX = 196608, oB0 = 212992, oBW = 215040, kBWBytes = 9216, oPart = 224256,
-                   oCtrl = 228352, kSmem = 228352 + 256;
+//                | X tile | b0 (x2) | b1 + W2 + b2 | head partial sums ((groups-1) x [8][128]) | barriers
+constexpr uint32_t oH = 0, oRing = 65536, kSlotBytes = 32768;
 constexpr int kSlots = 4, kPerTile = 5;
+constexpr int kEpiWarps = 8, kEpiThreads = kEpiWarps * 32, kThreads = 64 + kEpiThreads;
+constexpr int kGroups = kEpiWarps / 4, kPar = kGroups / 2;  // column-half x block-parity groups of epilogue warps
+constexpr uint32_t oX = oRing + kSlots * kSlotBytes, oB0 = oX + 16384, oBW = oB0 + 2048, kBWBytes = 9216 + 32,
+                   oPart = oBW + kBWBytes, kPartBytes = (kGroups - 1) * 8 * 128 * 4, oCtrl = oPart + kPartBytes,
+                   kSmem = oCtrl + 160;
+static_assert(kSmem <= 232448, "shared memory budget of one CTA (227 KB)");
 // barrier indices (8 bytes each) inside the control block
 enum { FULL_L0 = 0, MMA0 = 1, MMA1 = 2, FULL_R = 3, EMPTY_R = 7, HBLK = 11, ACC0_FREE = 15, ACC1_FREE = 16, FULL_BW = 17,
        N_BARS = 18 };
+static_assert(kSlots <= 4, "barrier indices reserve four ring slots");
 }  // namespace fwdp
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -38,9 +45,29 @@ __device__ __forceinline__ void st_chunk128(uint8_t* tile, int row, int col0, co
       make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
 
-__global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, const float* __restrict__ params,
-                                                                  const float* __restrict__ target,
-                                                                  float* __restrict__ head_out, int n_tiles) {
+// v = relu(v + bias[0..32)); returns the 32-bit ReLU mask (bit j = v[j] > 0) when kMask
+template <bool kMask>
+__device__ __forceinline__ uint32_t bias_relu32(float (&v)[32], const float* __restrict__ sb) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const float4 bb = *reinterpret_cast<const float4*>(sb + 4 * j4);
+    v[4 * j4] = fmaxf(v[4 * j4] + bb.x, 0.f);
+    v[4 * j4 + 1] = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
+    v[4 * j4 + 2] = fmaxf(v[4 * j4 + 2] + bb.z, 0.f);
+    v[4 * j4 + 3] = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
+  }
+  if (kMask) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (v[j] > 0.f) m |= 1u << j;
+  }
+  return m;
+}
+
+__global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfParams P, const float* __restrict__ params,
+                                                                             const float* __restrict__ target,
+                                                                             float* __restrict__ head_out, int n_tiles) {
   using namespace fwdp;
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
@@ -55,7 +82,7 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
     mbar_init(bar(FULL_L0), 1); mbar_init(bar(MMA0), 1); mbar_init(bar(MMA1), 1); mbar_init(bar(FULL_BW), 1);
     for (int i = 0; i < kSlots; ++i) { mbar_init(bar(FULL_R + i), 1); mbar_init(bar(EMPTY_R + i), 1); }
     for (int i = 0; i < 4; ++i) mbar_init(bar(HBLK + i), 8);
-    mbar_init(bar(ACC0_FREE), 8); mbar_init(bar(ACC1_FREE), 8);
+    mbar_init(bar(ACC0_FREE), kEpiWarps); mbar_init(bar(ACC1_FREE), kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 8 * N_BARS, 512);
@@ -63,6 +90,8 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const bool dbg = P.dbg != nullptr && blockIdx.x == 0;
+#define IQLB_TS(slot) do { if (dbg) P.dbg[(slot)] = (unsigned long long)clock64(); } while (0)
 
   auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
                        const float*& fnet) {
@@ -87,16 +116,26 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
         const float* fnet;
         tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
         const int in = L.in_dim(s);
+        if (tile + (int)gridDim.x < n_tiles) {  // next tile's operands start their trip HBM -> L2 one tile ahead
+          int a2, s2, h2;
+          const uint8_t *w2, *x2;
+          const float* f2;
+          tile_ptrs(tile + gridDim.x, a2, s2, h2, w2, x2, f2);
+          bulk_prefetch_l2(w2, (uint32_t)P.net_bytes);
+          bulk_prefetch_l2(x2 + (int64_t)h2 * 16384, 16384u);
+        }
         if (it > 0) mbar_wait(bar(MMA0), (uint32_t)((it - 1) & 1));  // layer 0 of the previous tile has consumed X
+        IQLB_TS(1024 + it * 8);
         mbar_expect_tx(bar(FULL_L0), 16384u + 1024u);
         bulk_g2s(sbase + oX, ximg + (int64_t)half * 16384, 16384u, bar(FULL_L0));
         bulk_g2s(sbase + oB0 + (uint32_t)(it & 1) * 1024u, fnet + L.b0(in), 1024u, bar(FULL_L0));
         for (int e = 0; e < kPerTile; ++e, ++c) {
           const int slot = c % kSlots, use = c / kSlots;
           if (use > 0) mbar_wait(bar(EMPTY_R + slot), (uint32_t)((use - 1) & 1));
-          mbar_expect_tx(bar(FULL_R + slot), 32768u);
-          bulk_g2s(sbase + oRing + (uint32_t)slot * 32768u, e == 0 ? wnet : wnet + P.w0_bytes + (int64_t)(e - 1) * 32768, 32768u,
-                   bar(FULL_R + slot));
+          IQLB_TS(1024 + it * 8 + 1 + e);
+          mbar_expect_tx(bar(FULL_R + slot), kSlotBytes);
+          bulk_g2s(sbase + oRing + (uint32_t)slot * kSlotBytes, e == 0 ? wnet : wnet + P.w0_bytes + (int64_t)(e - 1) * 32768,
+                   kSlotBytes, bar(FULL_R + slot));
         }
       }
     }
@@ -114,7 +153,8 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
           mbar_wait(bar(FULL_R + slot), (uint32_t)(use & 1));
           if (it > 0) mbar_wait(bar(ACC0_FREE), (uint32_t)((it - 1) & 1));
           tc_fence_after();
-          gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oRing + (uint32_t)slot * 32768u, L.H, 0),
+          IQLB_TS(512 + it * 8);
+          gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oRing + (uint32_t)slot * kSlotBytes, L.H, 0),
                      256, (in + 15) / 16, false);
           mma_commit(bar(EMPTY_R + slot));
           mma_commit(bar(MMA0));
@@ -126,18 +166,22 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
           mbar_wait(bar(FULL_R + slot), (uint32_t)(use & 1));
           if (kb == 0 && it > 0) mbar_wait(bar(ACC1_FREE), (uint32_t)((it - 1) & 1));
           tc_fence_after();
+          IQLB_TS(512 + it * 8 + 1 + kb);
           gemm_issue(tmem + 256, operand_k_major(sbase + oH + (uint32_t)kb * 16384u, 128, 0),
-                     operand_k_major(sbase + oRing + (uint32_t)slot * 32768u, L.H, 0), 256, 4, kb > 0);
+                     operand_k_major(sbase + oRing + (uint32_t)slot * kSlotBytes, L.H, 0), 256, 4, kb > 0);
           mma_commit(bar(EMPTY_R + slot));
         }
         mma_commit(bar(MMA1));
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (256 threads)
+    // ------------------------------------------------------------------ epilogue (16 warps)
+    // warp -> TMEM lane quarter (warp % 4, the hardware rule), column half of a 64-column block, and
+    // block parity: warps of parity p drain blocks p and p + 2, so blocks 0 and 1 finish together and
+    // layer 1 starts after half of epilogue 0
     const int et = tid - 64;
     bool h1_store_pending = false;
-    const int quarter = warp & 3, chalf = (warp - 2) >> 2;
+    const int quarter = warp & 3, grp = (warp - 2) >> 2, chalf = grp & 1, par = grp >> 1;  // par < kPar
     const int row = quarter * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     auto load_bw = [&](int tile) {  // b1 and W2 (fp32) of a tile into their single buffer
@@ -146,9 +190,12 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
       const float* fnet;
       tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
       const int in = L.in_dim(s), nout = L.out_dim(s);
-      mbar_expect_tx(bar(FULL_BW), 1024u + (uint32_t)nout * 1024u);
+      // W2 [nout][256] and b2 [nout] are adjacent in the parameter vector; network segments are padded to 32 bytes,
+      // so rounding b2 up to 16 bytes stays inside the segment
+      const uint32_t w2b2 = (uint32_t)nout * 1024u + (((uint32_t)nout * 4u + 15u) & ~15u);
+      mbar_expect_tx(bar(FULL_BW), 1024u + w2b2);
       bulk_g2s(sbase + oBW, fnet + L.b1(in), 1024u, bar(FULL_BW));
-      bulk_g2s(sbase + oBW + 1024u, fnet + L.w2(in), (uint32_t)nout * 1024u, bar(FULL_BW));
+      bulk_g2s(sbase + oBW + 1024u, fnet + L.w2(in), w2b2, bar(FULL_BW));
     };
     if (et == 0 && (int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
     for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
@@ -167,30 +214,24 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
       uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
       // (b0 landed before layer 0 was issued; FULL_L0 itself may already be a phase ahead, so it is
       //  not waited on here - MMA0 cannot run ahead of this warp because layer 0 waits for ACC0_FREE)
+      if (et == 0) IQLB_TS(it * 8);
       mbar_wait(bar(MMA0), ph);
       tc_fence_after();
-      if (h1_store_pending) {  // the previous trainable tile's H1 image must have left the H tile
+      if (et == 0) IQLB_TS(it * 8 + 1);
+      if (h1_store_pending) {  // the previous trainable tile's H2 image / masks must have left the staging tiles
         if (et == 0) bulk_wait_read0();
-        named_bar_sync(1, 256);
+        named_bar_sync(1, kEpiThreads);
         h1_store_pending = false;
       }
       // ---- epilogue 0: H1 = relu(acc0 + b0), block by block so that layer 1 can start behind us
 #pragma unroll 1
-      for (int blk = 0; blk < 4; ++blk) {
+      for (int blk = par; blk < 4; blk += kPar) {
         const int c0 = blk * 64 + chalf * 32;
         float v[32];
         tmem_ld32(lane_base + (uint32_t)c0, v);
         tmem_ld_wait();
-        uint32_t m = 0;
-#pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 bb = *reinterpret_cast<const float4*>(sb0 + c0 + 4 * j4);
-          const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
-          const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
-          v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
-          m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
-        }
-        if (m1) m1[c0 >> 5] = m;
+        if (t >= 0) m1[c0 >> 5] = bias_relu32<true>(v, sb0 + c0);
+        else bias_relu32<false>(v, sb0 + c0);
 #pragma unroll
         for (int q = 0; q < 4; ++q) st_chunk128(smem + oH, row, c0 + 8 * q, v + 8 * q);
         fence_async_smem();
@@ -200,86 +241,111 @@ __global__ void __launch_bounds__(320, 1) bf16_fwd_persist_kernel(BfParams P, co
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(ACC0_FREE));
+      if (et == 0) IQLB_TS(it * 8 + 2);
       if (t >= 0) {
-        named_bar_sync(1, 256);
+        named_bar_sync(1, kEpiThreads);
         if (et == 0) {
           uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
           for (int cb = 0; cb < 4; ++cb)
             bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
           bulk_commit();
         }
-        h1_store_pending = true;
       }
       mbar_wait(bar(FULL_BW), ph);
+      if (et == 0) IQLB_TS(it * 8 + 3);
       mbar_wait(bar(MMA1), ph);
       tc_fence_after();
+      if (et == 0) IQLB_TS(it * 8 + 4);
+      if (t >= 0) {  // H1 and its masks have left shared memory (issued a whole layer-1 GEMM ago): H2 may move in
+        if (et == 0) bulk_wait_read0();
+        named_bar_sync(1, kEpiThreads);
+      }
+      if (et == 0) IQLB_TS(it * 8 + 7);
       // ---- epilogue 1: H2 = relu(acc1 + b1); head = H2 . W2 + b2
       float acc[8];
 #pragma unroll
       for (int o = 0; o < 8; ++o) acc[o] = 0.f;
-      // image of H2 restricted to this half batch: block cb at cb*B*128, rows of this half at +half*16384
-      uint8_t* h2row = t >= 0 ? P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes + (int64_t)half * 16384 : nullptr;
 #pragma unroll 1
-      for (int blk = 0; blk < 4; ++blk) {
+      for (int blk = par; blk < 4; blk += kPar) {
         const int c0 = blk * 64 + chalf * 32;
         float v[32];
         tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
         tmem_ld_wait();
         uint32_t m = 0;
+        if (t >= 0) m = bias_relu32<true>(v, sb1 + c0);
+        else bias_relu32<false>(v, sb1 + c0);
+        if (nout == 1) {
+          float a = acc[0];
 #pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 bb = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * j4);
-          const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
-          const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
-          v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
-          m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
-        }
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 w = *reinterpret_cast<const float4*>(sw2 + c0 + 4 * j4);
+            a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
+            a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
+          }
+          acc[0] = a;
+        } else {
 #pragma unroll
-        for (int o = 0; o < 8; ++o) {
-          if (o < nout) {
-            const float* wr = sw2 + o * 256 + c0;
-            float a = acc[o];
+          for (int o = 0; o < 8; ++o) {
+            if (o < nout) {
+              const float* wr = sw2 + o * 256 + c0;
+              float a = acc[o];
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
-              a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
-              a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
+                a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
+                a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
+              }
+              acc[o] = a;
             }
-            acc[o] = a;
           }
         }
-        if (t >= 0) {  // H2 goes straight from registers to its image in HBM (four 16-byte chunks of this row)
+        if (t >= 0) {  // H2 is staged in the H tile (layer 1 has consumed H1) and leaves as one bulk store
           m2[c0 >> 5] = m;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {  // global image blocks hold all B rows: block stride B*128 bytes
-            const int col = c0 + 8 * q;
-            uint8_t* dst = h2row + (int64_t)(col >> 6) * L.B * 128 + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4);
-            *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
-                                                        pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
-          }
+          for (int q = 0; q < 4; ++q) st_chunk128(smem + oH, row, c0 + 8 * q, v + 8 * q);
         }
       }
+      if (t >= 0) fence_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(ACC1_FREE));
-      if (chalf == 1) {
+      if (et == 0) IQLB_TS(it * 8 + 5);
+      if (grp > 0) {
 #pragma unroll
         for (int o = 0; o < 8; ++o)
-          if (o < nout) part[o * 128 + row] = acc[o];
+          if (o < nout) part[((grp - 1) * 8 + o) * 128 + row] = acc[o];
       }
-      named_bar_sync(1, 256);
-      if (et == 0 && tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);  // every warp is done with b1 / W2
-      if (chalf == 0) {
-        const float* b2 = fnet + L.b2(in, nout);
+      const float b2v = lane < 8 ? sw2[nout * 256 + (lane < nout ? lane : 0)] : 0.f;  // before the bundle is reloaded
+      named_bar_sync(1, kEpiThreads);
+      if (et == 0) IQLB_TS(it * 8 + 6);
+      if (et == 0) {
+        if (tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);  // every warp is done with b1 / W2 / b2
+        IQLB_TS(1536 + it * 8);
+        if (t >= 0) {
+          uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+          for (int cb = 0; cb < 4; ++cb)
+            bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+          bulk_commit();
+        }
+      }
+      if (et == 0) IQLB_TS(1536 + it * 8 + 1);
+      h1_store_pending = t >= 0;
+      if (grp == 0) {
         float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
 #pragma unroll
         for (int o = 0; o < 8; ++o) {
           if (o < nout) {
-            const float z = acc[o] + part[o * 128 + row] + __ldg(b2 + o);
+            float z = acc[o];
+#pragma unroll
+            for (int g = 0; g < kGroups - 1; ++g) z += part[(g * 8 + o) * 128 + row];
+            z += __shfl_sync(0xffffffffu, b2v, o);
             if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
             else ho[(int64_t)s * L.B + brow] = z;
           }
         }
+        if (et == 0) IQLB_TS(1536 + it * 8 + 2);
+        // the partial sums are read before any warp can overwrite them: the next write to `part` follows
+        // the next tile's named barriers, which this warp joins only after these loads
       }
     }
     if (h1_store_pending && et == 0) bulk_wait_read0();
@@ -302,7 +368,7 @@ int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float*
   }
   const int n_tiles = n_agents * kStreams * (P.L.B / 128);
   const int grid = n_tiles < n_sm ? n_tiles : n_sm;
-  bf16_fwd_persist_kernel<<<grid, 320, fwdp::kSmem, stream>>>(P, params, target, head_out, n_tiles);
+  bf16_fwd_persist_kernel<<<grid, fwdp::kThreads, fwdp::kSmem, stream>>>(P, params, target, head_out, n_tiles);
   IQLB_LAUNCH_CHECK();
   return IQLB_OK;
 }

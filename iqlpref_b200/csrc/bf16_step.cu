@@ -67,6 +67,62 @@ __global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __
   *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
 }
 
+// ------------------------------------------------------------------------------------------------
+// ReplayBuffer.sample (iql.py:211-221) fused with the image packing: Philox index, 128-bit row gather,
+// fp32 batch rows (the loss kernel reads reward / done / action from them) and both bf16 input images
+// in one pass.  A CTA stages 256 / vec_per_row rows in shared memory.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) replay_gather_pack_kernel(
+    BfParams P, const float4* __restrict__ table, uint64_t n_rows, int vec_per_row, int rows_per_cta, int reward_col,
+    const float* __restrict__ reward_cols, const int32_t* __restrict__ reward_variant, const uint64_t* __restrict__ rng,
+    int64_t* __restrict__ idx_out, float4* __restrict__ batch_out) {
+  extern __shared__ __align__(16) float srow[];  // [rows_per_cta][R]
+  const Layout& L = P.L;
+  const int agent = P.agent0 + blockIdx.y;
+  const int t = threadIdx.x;
+  const int lb = t / vec_per_row, v = t - lb * vec_per_row;
+  const int b = blockIdx.x * rows_per_cta + lb;
+  if (lb < rows_per_cta && b < L.B) {
+    uint32_t r[4];
+    philox4(rng[2 * agent], (uint64_t)b, rng[2 * agent + 1], r);
+    const int64_t row = randint_from_philox(r, n_rows);
+    if (idx_out != nullptr && v == 0) idx_out[(int64_t)agent * L.B + b] = row;
+    float4 val = __ldg(table + row * vec_per_row + v);
+    if (reward_cols != nullptr && (reward_col >> 2) == v) {
+      const int variant = reward_variant ? reward_variant[agent] : 0;
+      const float rw = __ldg(reward_cols + (int64_t)variant * (int64_t)n_rows + row);
+      switch (reward_col & 3) {
+        case 0: val.x = rw; break;
+        case 1: val.y = rw; break;
+        case 2: val.z = rw; break;
+        default: val.w = rw; break;
+      }
+    }
+    batch_out[((int64_t)agent * L.B + b) * vec_per_row + v] = val;
+    *reinterpret_cast<float4*>(srow + lb * L.R + 4 * v) = val;
+  }
+  __syncthreads();
+  const int cpr = P.KXB * 8;
+  for (int i = t; i < rows_per_cta * cpr; i += 256) {
+    const int rb = i / cpr, ch = i - rb * cpr;
+    const int bb = blockIdx.x * rows_per_cta + rb;
+    if (bb >= L.B) break;
+    const float* row = srow + rb * L.R;
+    uint32_t sa[4], nx[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int c = ch * 8 + 2 * q;
+      const float a0 = c < L.Dq ? row[c] : 0.f, a1 = c + 1 < L.Dq ? row[c + 1] : 0.f;
+      const float n0 = c < L.S ? row[L.Dq + c] : 0.f, n1 = c + 1 < L.S ? row[L.Dq + c + 1] : 0.f;
+      sa[q] = pack_bf16(a0, a1);
+      nx[q] = pack_bf16(n0, n1);
+    }
+    const int64_t off = image_off(L.B, bb, ch * 8);
+    *reinterpret_cast<uint4*>(P.xsa + (int64_t)agent * P.x_bytes + off) = make_uint4(sa[0], sa[1], sa[2], sa[3]);
+    *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
+  }
+}
+
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 
 // store 8 consecutive columns (one 16-byte chunk) of tile row `row` into a tile image with 128 rows
@@ -490,11 +546,29 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);
     bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
   }
+  if (kFused && tid == 32) {
+    // the optimizer state of this tile starts its trip from HBM to L2 now, under the operand loads and the
+    // MMAs: p, m, v (and the Polyak target) rows of W1 and W0 that the Adam epilogue below streams
+    const int64_t noff_ = L.net_off(s);
+    const int64_t e1 = (int64_t)agent * L.Pstride + noff_ + L.w1(in) + (int64_t)ot * 128 * L.H;
+    const int64_t e0 = (int64_t)agent * L.Pstride + noff_ + (int64_t)ot * 128 * in;
+    const uint32_t b1 = 128u * (uint32_t)L.H * 4u, b0 = 128u * (uint32_t)in * 4u;
+    bulk_prefetch_l2(params + e1, b1); bulk_prefetch_l2(exp_avg + e1, b1); bulk_prefetch_l2(exp_avg_sq + e1, b1);
+    bulk_prefetch_l2(params + e0, b0); bulk_prefetch_l2(exp_avg + e0, b0); bulk_prefetch_l2(exp_avg_sq + e0, b0);
+    if (t == 1 || t == 2) {
+      const int64_t q1 = (int64_t)agent * L.PQstride + noff_ + L.w1(in) + (int64_t)ot * 128 * L.H;
+      const int64_t q0 = (int64_t)agent * L.PQstride + noff_ + (int64_t)ot * 128 * in;
+      bulk_prefetch_l2(target + q1, b1); bulk_prefetch_l2(target + q0, b0);
+    }
+  }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 40, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const bool dbgw = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && blockIdx.z == 0 && tid == 64;
+#define IQLB_TSW(slot) do { if (dbgw) P.dbg[2048 + (slot)] = (unsigned long long)clock64(); } while (0)
+  IQLB_TSW(0);
   const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
   if (tid == 0) {
     mbar_wait(bar_ld1, 0);
@@ -507,6 +581,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncwarp();
   mbar_wait(bar_p1, 0);
   tc_fence_after();
+  IQLB_TSW(1);
   if (tid == 0) {  // phase-1 operands consumed: refill (H2 follows once the staging area is free again)
     mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
     bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
@@ -535,6 +610,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   float* stg = reinterpret_cast<float*>(smem + oB + 2 * blk);  // 2 x [128 rows][64] fp32, float4 index ^ (row & 15)
 
   {
+    if (!kFused) {
     // ---- dW1: four 64-column chunks, double-buffered through shared memory ----
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
@@ -560,47 +636,68 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
         }
         continue;
       }
-      // all global loads of the four row groups are issued before the first use (the stores below
-      // would otherwise fence the next group's loads behind them)
-      float4 pq[4][2], mq[4][2], vq[4][2], tq[4][2];
-      int64_t eq[4];
+    }
+    }
+    if (kFused) {
+      // ---- dW1 with Adam: four chunks of 32 rows x 256 columns.  The two warps that own TMEM lane quarter
+      // qq stage chunk qq (fp32, 16-byte words XOR-swizzled by row) while all eight warps stream the previous
+      // chunk: every row is 1 KB of contiguous p / m / v / target, a chunk 32 KB, so HBM sees the same linear
+      // streams as the stand-alone Adam kernel (the L2 prefetch at the top of the kernel covers the latency).
+      auto write_chunk = [&](int qq) {
+        float* sb = stg + (qq & 1) * (32 * 256);
+#pragma unroll 1
+        for (int c4 = 0; c4 < 4; ++c4) {
+          const int c0 = chalf * 128 + c4 * 32;
+          float v[32];
+          tmem_ld32(lane_base + (uint32_t)c0, v);
+          tmem_ld_wait();
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int r = warp * 16 + it * 4 + rr;
-        const int64_t e = noff + L.w1(in) + (int64_t)(ot * 128 + r) * L.H + cc * 64 + 8 * l8;
-        eq[it] = e;
-        pq[it][0] = *reinterpret_cast<const float4*>(A.p + e); pq[it][1] = *reinterpret_cast<const float4*>(A.p + e + 4);
-        mq[it][0] = *reinterpret_cast<const float4*>(A.m + e); mq[it][1] = *reinterpret_cast<const float4*>(A.m + e + 4);
-        vq[it][0] = *reinterpret_cast<const float4*>(A.v + e); vq[it][1] = *reinterpret_cast<const float4*>(A.v + e + 4);
-        if (A.tgt) { tq[it][0] = *reinterpret_cast<const float4*>(A.tgt + e); tq[it][1] = *reinterpret_cast<const float4*>(A.tgt + e + 4); }
-        else { tq[it][0] = make_float4(0, 0, 0, 0); tq[it][1] = tq[it][0]; }
-      }
-#pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int r = warp * 16 + it * 4 + rr;
-        const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
-        const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
-        const int fr = ot * 128 + r, col = cc * 64 + 8 * l8;
-        const int64_t e = eq[it];
-        float4 &p0 = pq[it][0], &p1 = pq[it][1], &m0 = mq[it][0], &m1 = mq[it][1], &v0 = vq[it][0], &v1 = vq[it][1];
-        float4 &t0 = tq[it][0], &t1 = tq[it][1];
-        adam_update(p0.x, m0.x, v0.x, g0.x, A.ss, A.bc2_sqrt); adam_update(p0.y, m0.y, v0.y, g0.y, A.ss, A.bc2_sqrt);
-        adam_update(p0.z, m0.z, v0.z, g0.z, A.ss, A.bc2_sqrt); adam_update(p0.w, m0.w, v0.w, g0.w, A.ss, A.bc2_sqrt);
-        adam_update(p1.x, m1.x, v1.x, g1.x, A.ss, A.bc2_sqrt); adam_update(p1.y, m1.y, v1.y, g1.y, A.ss, A.bc2_sqrt);
-        adam_update(p1.z, m1.z, v1.z, g1.z, A.ss, A.bc2_sqrt); adam_update(p1.w, m1.w, v1.w, g1.w, A.ss, A.bc2_sqrt);
-        *reinterpret_cast<float4*>(A.p + e) = p0; *reinterpret_cast<float4*>(A.p + e + 4) = p1;
-        *reinterpret_cast<float4*>(A.m + e) = m0; *reinterpret_cast<float4*>(A.m + e + 4) = m1;
-        *reinterpret_cast<float4*>(A.v + e) = v0; *reinterpret_cast<float4*>(A.v + e + 4) = v1;
-        const int64_t ioff = P.w0_bytes + image_off(L.H, fr, col);
-        *reinterpret_cast<uint4*>(A.img + ioff) = make_uint4(pack_bf16(p0.x, p0.y), pack_bf16(p0.z, p0.w),
-                                                             pack_bf16(p1.x, p1.y), pack_bf16(p1.z, p1.w));
-        if (A.tgt) {
-          t0.x += A.tau * (p0.x - t0.x); t0.y += A.tau * (p0.y - t0.y); t0.z += A.tau * (p0.z - t0.z); t0.w += A.tau * (p0.w - t0.w);
-          t1.x += A.tau * (p1.x - t1.x); t1.y += A.tau * (p1.y - t1.y); t1.z += A.tau * (p1.z - t1.z); t1.w += A.tau * (p1.w - t1.w);
-          *reinterpret_cast<float4*>(A.tgt + e) = t0; *reinterpret_cast<float4*>(A.tgt + e + 4) = t1;
-          *reinterpret_cast<uint4*>(A.timg + ioff) = make_uint4(pack_bf16(t0.x, t0.y), pack_bf16(t0.z, t0.w),
-                                                                pack_bf16(t1.x, t1.y), pack_bf16(t1.z, t1.w));
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<float4*>(sb + lane * 256 + ((((c0 >> 2) + q) ^ (lane & 7)) << 2)) =
+                make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
         }
+      };
+      if (quarter == 0) write_chunk(0);
+      __syncthreads();
+      IQLB_TSW(2);
+#pragma unroll 1
+      for (int qq = 0; qq < 4; ++qq) {
+        if (qq < 3 && quarter == qq + 1) write_chunk(qq + 1);
+        const float* sb = stg + (qq & 1) * (32 * 256);
+        float4 pq[8], mq[8], vq[8], tq[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {  // row warp*4 + u/2 of the chunk, 16-byte word lane + 32*(u%2): 512 B per warp access
+          const int r = warp * 4 + (u >> 1), j = lane + 32 * (u & 1);
+          const int64_t e = noff + L.w1(in) + (int64_t)(ot * 128 + qq * 32 + r) * L.H + 4 * j;
+          pq[u] = *reinterpret_cast<const float4*>(A.p + e);
+          mq[u] = *reinterpret_cast<const float4*>(A.m + e);
+          vq[u] = *reinterpret_cast<const float4*>(A.v + e);
+          tq[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
+        }
+        IQLB_TSW(13 + qq);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int r = warp * 4 + (u >> 1), j = lane + 32 * (u & 1);
+          const int fr = ot * 128 + qq * 32 + r;
+          const int64_t e = noff + L.w1(in) + (int64_t)fr * L.H + 4 * j;
+          const float4 g = *reinterpret_cast<const float4*>(sb + r * 256 + ((j ^ (r & 7)) << 2));
+          float4 &p = pq[u], &m = mq[u], &v = vq[u], &tg = tq[u];
+          adam_update(p.x, m.x, v.x, g.x, A.ss, A.bc2_sqrt); adam_update(p.y, m.y, v.y, g.y, A.ss, A.bc2_sqrt);
+          adam_update(p.z, m.z, v.z, g.z, A.ss, A.bc2_sqrt); adam_update(p.w, m.w, v.w, g.w, A.ss, A.bc2_sqrt);
+          *reinterpret_cast<float4*>(A.p + e) = p;
+          *reinterpret_cast<float4*>(A.m + e) = m;
+          *reinterpret_cast<float4*>(A.v + e) = v;
+          const int64_t ioff = P.w0_bytes + image_off(L.H, fr, 4 * j);  // 4 bf16 = half a 16-byte image chunk
+          *reinterpret_cast<uint2*>(A.img + ioff) = make_uint2(pack_bf16(p.x, p.y), pack_bf16(p.z, p.w));
+          if (A.tgt) {
+            tg.x += A.tau * (p.x - tg.x); tg.y += A.tau * (p.y - tg.y); tg.z += A.tau * (p.z - tg.z); tg.w += A.tau * (p.w - tg.w);
+            *reinterpret_cast<float4*>(A.tgt + e) = tg;
+            *reinterpret_cast<uint2*>(A.timg + ioff) = make_uint2(pack_bf16(tg.x, tg.y), pack_bf16(tg.z, tg.w));
+          }
+        }
+        IQLB_TSW(8 + qq);
+        __syncthreads();  // chunk qq consumed, chunk qq+1 staged
+        IQLB_TSW(3 + qq);
       }
     }
     fence_async_smem();
@@ -624,6 +721,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncwarp();
   mbar_wait(bar_p2, 0);
   tc_fence_after();
+  IQLB_TSW(7);
   {
     // ---- everything else through shared memory in packed-parameter order:
     //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
@@ -725,6 +823,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
         adam_scalar(A, L.off_logstd + (tid - 32), grads[(int64_t)agent * L.Pstride + L.off_logstd + (tid - 32)], -1);
     }
   }
+  IQLB_TSW(12);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
@@ -744,7 +843,7 @@ bool bf16_fwd_persist_ok(const BfParams& P);
 int bf16_create(iqlb_agents* h) {
   const Layout& L = h->L;
   IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
-  IQLB_REQUIRE(L.B == 128 || L.B == 256, "the tcgen05 path needs batch_size 128 or 256");
+  IQLB_REQUIRE(L.B == 256, "the tcgen05 path is built for batch_size 256 (every reference config); use precision fp32 otherwise");
   IQLB_REQUIRE(L.A <= kOutMax && L.Dq <= 128, "action_dim <= 24 and state_dim + action_dim <= 128");
   IQLB_REQUIRE(1 + L.A <= 16 * ((L.Dq + 63) / 64), "action_dim too wide for the head staging area");
   Bf16State* st = new (std::nothrow) Bf16State();
@@ -777,6 +876,8 @@ int bf16_create(iqlb_agents* h) {
   if (!rc) rc = alloc((void**)&P.dz, N * kTrain * P.z_bytes);
   if (!rc) rc = alloc((void**)&P.mask1, N * kTrain * L.B * (L.H / 32) * 4);
   if (!rc) rc = alloc((void**)&P.mask2, N * kTrain * L.B * (L.H / 32) * 4);
+  P.dbg = nullptr;
+  if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
   if (rc) return rc;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
@@ -793,7 +894,7 @@ void bf16_destroy(iqlb_agents* h) {
   if (!st) return;
   BfParams& P = st->P;
   cudaFree(P.wimg); cudaFree(P.xsa); cudaFree(P.xnext); cudaFree(P.h1); cudaFree(P.h2); cudaFree(P.dh2);
-  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2);
+  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2); cudaFree(P.dbg);
   delete st;
   h->bf16_state = nullptr;
 }
@@ -818,7 +919,26 @@ int bf16_refresh(iqlb_agents* h, cudaStream_t stream) {
   return IQLB_OK;
 }
 
-int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream) {
+// sampled steps: Philox gather + image packing in one launch (replaces replay_gather + pack_x)
+int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream) {
+  Bf16State* st = (Bf16State*)h->bf16_state;
+  IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
+  const Layout& L = h->L;
+  IQLB_REQUIRE(h->table != nullptr, "no replay table attached (iqlb_agents_set_replay)");
+  BfParams P = st->P;
+  P.agent0 = a0;
+  const int vpr = L.R / 4;
+  IQLB_REQUIRE(vpr <= 256, "row_stride too wide");
+  const int rpc = 256 / vpr;
+  replay_gather_pack_kernel<<<dim3((unsigned)((L.B + rpc - 1) / rpc), n), 256, (size_t)rpc * L.R * 4, stream>>>(
+      P, (const float4*)h->table, (uint64_t)h->n_rows, vpr, rpc, 2 * L.S + L.A, h->reward_cols, h->reward_variant, h->rng,
+      h->idx_out, (float4*)h->batch);
+  IQLB_LAUNCH_CHECK();
+  pf.mark("replay_gather_pack");
+  return IQLB_OK;
+}
+
+int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream, bool packed) {
   Bf16State* st = (Bf16State*)h->bf16_state;
   IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
   const Layout& L = h->L;
@@ -830,9 +950,11 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
     if ((rc = bf16_refresh(h, stream))) return rc;
     pf.mark("shadow_refresh");
   }
-  pack_x_kernel<<<dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(P, h->batch);
-  IQLB_LAUNCH_CHECK();
-  pf.mark("pack_x");
+  if (!packed) {
+    pack_x_kernel<<<dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(P, h->batch);
+    IQLB_LAUNCH_CHECK();
+    pf.mark("pack_x");
+  }
   static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
   if (persist_env && bf16_fwd_persist_ok(P)) {
     if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream))) return rc;

@@ -18,7 +18,8 @@ int launch_gather(const float* table, int64_t n_rows, int row_stride, int reward
                   int64_t* idx_out, float* batch_out, cudaStream_t stream);
 int bf16_create(iqlb_agents* h);
 void bf16_destroy(iqlb_agents* h);
-int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
+int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream, bool packed);
+int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
 int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
 const BfParams* bf16_params(const iqlb_agents* h);
 void bf16_mark_dirty(iqlb_agents* h);
@@ -70,104 +71,121 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
                             uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
                             uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0) {
-  __shared__ float red[32];
+  // per-warp partial sums of every reduced quantity: 0 vl | 1 ql | 2 al | 3..5 head bias grads (V, Q1, Q2)
+  // | 6.. actor head bias grads [A] | 6+A.. log_std grads [A]; one block-wide pass at the end
+  constexpr int kNV = 6 + 2 * kOutMax;
+  __shared__ float red[32][kNV];
   const int agent = agent0 + blockIdx.x, b = threadIdx.x;
+  const int lane = b & 31, warp = b >> 5, nw = (blockDim.x + 31) >> 5;
   const bool live = b < L.B;
+  const bool bf = dzimg != nullptr;
   const float* hp = hparams + agent * IQLB_HP_STRIDE;
   const float discount = hp[0], beta = hp[2], iql_tau = hp[3];
   const float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
   float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
-  const float* row = batch + ((int64_t)agent * L.B + (live ? b : 0)) * L.R;
+  const int bb = live ? b : 0;
+  const float* row = batch + ((int64_t)agent * L.B + bb) * L.R;
   const float invB = 1.0f / (float)L.B;
+  const float* log_std = params + (int64_t)agent * L.Pstride + L.off_logstd;
 
-  float vl = 0.f, ql = 0.f, al = 0.f, w = 0.f;
+  // every global load of this thread is issued before the first use
+  const float nv = ho[0 * L.B + bb], v = ho[1 * L.B + bb], tq1 = ho[2 * L.B + bb], tq2 = ho[3 * L.B + bb];
+  const float q1 = ho[4 * L.B + bb], q2 = ho[5 * L.B + bb];
+  const float rew = row[2 * L.S + L.A], done = row[2 * L.S + L.A + 1];
+  float mu[kOutMax], act[kOutMax], lsr[kOutMax];
+#pragma unroll
+  for (int a = 0; a < kOutMax; ++a) {
+    mu[a] = a < L.A ? ho[(int64_t)(6 + a) * L.B + bb] : 0.f;
+    act[a] = a < L.A ? row[L.S + a] : 0.f;
+    lsr[a] = (a < L.A && !L.deterministic) ? log_std[a] : 0.f;
+  }
+
+  const float tq = fminf(tq1, tq2);
+  const float adv = tq - v;
+  const float wt = adv < 0.f ? fabsf(iql_tau - 1.0f) : fabsf(iql_tau);
+  const float y = rew + (1.0f - done) * discount * nv;
+  const float e1 = q1 - y, e2 = q2 - y;
+  const float w = fminf(expf(beta * adv), 100.0f);
+  const float d0 = live ? -2.0f * wt * adv * invB : 0.f;
+  const float d1 = live ? e1 * invB : 0.f, d2 = live ? e2 * invB : 0.f;
+  float vl = live ? wt * (adv * adv) : 0.f;
+  float ql = live ? e1 * e1 + e2 * e2 : 0.f;
   if (live) {
-    const float nv = ho[0 * L.B + b], v = ho[1 * L.B + b];
-    const float tq = fminf(ho[2 * L.B + b], ho[3 * L.B + b]);
-    const float q1 = ho[4 * L.B + b], q2 = ho[5 * L.B + b];
-    const float rew = row[2 * L.S + L.A], done = row[2 * L.S + L.A + 1];
-    const float adv = tq - v;
-    const float wt = adv < 0.f ? fabsf(iql_tau - 1.0f) : fabsf(iql_tau);
-    vl = wt * (adv * adv);
-    dout[0 * L.B + b] = -2.0f * wt * adv * invB;
-    const float y = rew + (1.0f - done) * discount * nv;
-    const float e1 = q1 - y, e2 = q2 - y;
-    ql = e1 * e1 + e2 * e2;
-    dout[1 * L.B + b] = e1 * invB;
-    dout[2 * L.B + b] = e2 * invB;
-    w = fminf(expf(beta * adv), 100.0f);
+    dout[0 * L.B + b] = d0;
+    dout[1 * L.B + b] = d1;
+    dout[2 * L.B + b] = d2;
   }
   // bf16 path: the dz image (dz columns + a column of ones) feeds the weight-gradient MMAs, and the
   // head bias gradients are reduced here (the fp32 path does both in head_bwd_kernel)
-  auto put_dz = [&](int t, int col, float v) {
+  auto put_dz = [&](int t, int col, float val) {
     *reinterpret_cast<__nv_bfloat16*>(dzimg + ((int64_t)agent * kTrain + t) * z_bytes + umma::image_off(L.B, b, col)) =
-        __float2bfloat16_rn(v);
+        __float2bfloat16_rn(val);
   };
-  if (dzimg != nullptr) {
-    float d0 = 0.f, d1 = 0.f, d2 = 0.f;
-    if (live) {
-      d0 = dout[0 * L.B + b]; d1 = dout[1 * L.B + b]; d2 = dout[2 * L.B + b];
-      put_dz(0, 0, d0); put_dz(0, 1, 1.0f);
-      put_dz(1, 0, d1); put_dz(1, 1, 1.0f);
-      put_dz(2, 0, d2); put_dz(2, 1, 1.0f);
-      put_dz(3, L.A, 1.0f);
-    }
-    const float s0 = block_sum(d0, red), s1 = block_sum(d1, red), s2 = block_sum(d2, red);
-    if (b == 0) {
-      float* g = grads + (int64_t)agent * L.Pstride;
-      g[L.off_v + L.b2(L.S, 1)] = s0;
-      g[L.off_q1 + L.b2(L.Dq, 1)] = s1;
-      g[L.off_q2 + L.b2(L.Dq, 1)] = s2;
-    }
+  if (bf && live) {
+    for (int t = 0; t < 3; ++t)  // columns 0 (dz) and 1 (ones) share one 32-bit word of the image
+      *reinterpret_cast<uint32_t*>(dzimg + ((int64_t)agent * kTrain + t) * z_bytes + umma::image_off(L.B, b, 0)) =
+          umma::pack_bf16(t == 0 ? d0 : (t == 1 ? d1 : d2), 1.0f);
+    put_dz(3, L.A, 1.0f);
   }
-  // actor: per-action terms; log_std gradient needs a block reduction per action
-  const float* log_std = params + (int64_t)agent * L.Pstride + L.off_logstd;
-  float* g_log_std = grads + (int64_t)agent * L.Pstride + L.off_logstd;
   float bc = 0.f;
-  for (int a = 0; a < L.A; ++a) {
-    float gls = 0.f, dza = 0.f;
-    if (live) {
-      const float mu = ho[(int64_t)(6 + a) * L.B + b];
-      const float act = row[L.S + a];
-      const float diff = mu - act;
-      float dmu;
-      if (L.deterministic) {
-        bc += diff * diff;
-        dmu = 2.0f * w * diff * invB;
-      } else {
-        const float ls_raw = log_std[a];
-        const float ls = fminf(fmaxf(ls_raw, -20.0f), 2.0f);
-        const float sigma = expf(ls);
-        const float inv_var = 1.0f / (sigma * sigma);
-        bc += 0.5f * diff * diff * inv_var + ls + 0.91893853320467274178f;
-        dmu = w * diff * inv_var * invB;
-        gls = (ls_raw >= -20.0f && ls_raw <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
+#pragma unroll
+  for (int a = 0; a < kOutMax; ++a) {
+    if (a < L.A) {  // uniform
+      float gls = 0.f, dza = 0.f;
+      if (live) {
+        const float diff = mu[a] - act[a];
+        float dmu;
+        if (L.deterministic) {
+          bc += diff * diff;
+          dmu = 2.0f * w * diff * invB;
+        } else {
+          const float ls = fminf(fmaxf(lsr[a], -20.0f), 2.0f);
+          const float sigma = expf(ls);
+          const float inv_var = 1.0f / (sigma * sigma);
+          bc += 0.5f * diff * diff * inv_var + ls + 0.91893853320467274178f;
+          dmu = w * diff * inv_var * invB;
+          gls = (lsr[a] >= -20.0f && lsr[a] <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
+        }
+        dza = dmu * (1.0f - mu[a] * mu[a]);
+        dout[(int64_t)(3 + a) * L.B + b] = dza;
+        if (bf) put_dz(3, a, dza);
       }
-      dza = dmu * (1.0f - mu * mu);
-      dout[(int64_t)(3 + a) * L.B + b] = dza;
-      if (dzimg != nullptr) put_dz(3, a, dza);
-    }
-    if (dzimg != nullptr) {
-      const float sa = block_sum(dza, red);
-      if (b == 0) grads[(int64_t)agent * L.Pstride + L.off_a + L.b2(L.S, L.A) + a] = sa;
-    }
-    if (!L.deterministic) {
-      const float tot = block_sum(gls, red);
-      if (b == 0) g_log_std[a] = tot;
+      const float sa = warp_sum(dza), sg = warp_sum(gls);
+      if (lane == 0) { red[warp][6 + a] = sa; red[warp][6 + L.A + a] = sg; }
     }
   }
-  al = w * bc;
-  const float vls = block_sum(vl, red);
-  const float qls = block_sum(ql, red);
-  const float als = block_sum(al, red);
-  if (b == 0) {
-    const float value_loss = vls * invB, q_loss = qls * invB * 0.5f, actor_loss = als * invB;
-    losses[agent * 3 + 0] = value_loss;
-    losses[agent * 3 + 1] = q_loss;
-    losses[agent * 3 + 2] = actor_loss;
-    loss_sum[agent * 3 + 0] += value_loss;
-    loss_sum[agent * 3 + 1] += q_loss;
-    loss_sum[agent * 3 + 2] += actor_loss;
+  const float al = live ? w * bc : 0.f;
+  {
+    const float s0 = warp_sum(vl), s1 = warp_sum(ql), s2 = warp_sum(al);
+    const float s3 = warp_sum(d0), s4 = warp_sum(d1), s5 = warp_sum(d2);
+    if (lane == 0) {
+      red[warp][0] = s0; red[warp][1] = s1; red[warp][2] = s2; red[warp][3] = s3; red[warp][4] = s4; red[warp][5] = s5;
+    }
+  }
+  __syncthreads();
+  const int nvals = 6 + 2 * L.A;
+  for (int j = b; j < nvals; j += blockDim.x) {  // thread j adds the per-warp partials of quantity j in warp order
+    float tot = 0.f;
+    for (int wi = 0; wi < nw; ++wi) tot += red[wi][j];
+    float* g = grads + (int64_t)agent * L.Pstride;
+    if (j == 0) {
+      const float value_loss = tot * invB;
+      losses[agent * 3 + 0] = value_loss; loss_sum[agent * 3 + 0] += value_loss;
+    } else if (j == 1) {
+      const float q_loss = tot * invB * 0.5f;
+      losses[agent * 3 + 1] = q_loss; loss_sum[agent * 3 + 1] += q_loss;
+    } else if (j == 2) {
+      const float actor_loss = tot * invB;
+      losses[agent * 3 + 2] = actor_loss; loss_sum[agent * 3 + 2] += actor_loss;
+    } else if (j < 6) {
+      if (bf) g[(j == 3 ? L.off_v + L.b2(L.S, 1) : (j == 4 ? L.off_q1 : L.off_q2) + L.b2(L.Dq, 1))] = tot;
+    } else if (j < 6 + L.A) {
+      if (bf) g[L.off_a + L.b2(L.S, L.A) + (j - 6)] = tot;
+    } else if (!L.deterministic) {
+      g[L.off_logstd + (j - 6 - L.A)] = tot;
+    }
+  }
+  if (b == 32 || (blockDim.x <= 32 && b == 0)) {
     // Adam step scalars of THIS step (torch optim/adam.py:529-547) and scheduler/rng advance.
     const long long t = it[agent] + 1;
     const double bc1 = 1.0 - pow(0.9, (double)t), bc2 = 1.0 - pow(0.999, (double)t);
@@ -249,69 +267,67 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
                                                           float* __restrict__ target, const float* __restrict__ grads,
                                                           const StepScalars* __restrict__ scal, BfParams BP, int shadow,
                                                           int agent0) {
-  // eight consecutive parameters per thread: network segments start on multiples of 8, so a group
-  // never straddles two optimizers, and inside W1 it is exactly one 16-byte chunk of the bf16 image
+  // A CTA owns 2048 consecutive parameters of one agent; thread t handles the 16-byte words t and t + 256 of
+  // that span, so every warp access is 512 contiguous bytes per array.  Network segments start on multiples of
+  // 8 floats: a word never straddles two optimizers, and inside W1 it is half of a 16-byte chunk of the image.
   const int agent = agent0 + blockIdx.y;
-  const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
-  if (e0 >= L.Pstride) return;
   const StepScalars sc = scal[agent];
-  const int64_t g8 = (int64_t)agent * L.Pstride + e0;
   float4 p[2], m[2], v[2], g[2], tg[2];
+  int64_t e[2];
+  bool live[2], has_t[2];
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
-    p[h] = *reinterpret_cast<const float4*>(params + g8 + 4 * h);
-    m[h] = *reinterpret_cast<const float4*>(exp_avg + g8 + 4 * h);
-    v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g8 + 4 * h);
-    g[h] = *reinterpret_cast<const float4*>(grads + g8 + 4 * h);
-  }
-  const bool has_t = e0 < L.PQ;
-  const int64_t t8 = (int64_t)agent * L.PQstride + e0;
-  if (has_t) {
-    tg[0] = *reinterpret_cast<const float4*>(target + t8);
-    tg[1] = *reinterpret_cast<const float4*>(target + t8 + 4);
-  }
-  const float ss = e0 < L.off_v ? sc.ss_q : (e0 < L.off_a ? sc.ss_v : sc.ss_a);
-  float* pp = &p[0].x; float* mp = &m[0].x; float* vp = &v[0].x; const float* gp = &g[0].x; float* tp = &tg[0].x;
-#pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    const float gg = gp[c];
-    const float mm = mp[c] + (1.0f - 0.9f) * (gg - mp[c]);
-    const float vv = 0.999f * vp[c] + (1.0f - 0.999f) * gg * gg;
-    const float denom = sqrtf(vv) / sc.bc2_sqrt + 1e-8f;
-    pp[c] = pp[c] - ss * (mm / denom);
-    mp[c] = mm;
-    vp[c] = vv;
-    if (has_t) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);  // Tensor.lerp_ (weight < 0.5), with the post-Adam qf
+    e[h] = ((int64_t)blockIdx.x * 512 + threadIdx.x + 256 * h) * 4;
+    live[h] = e[h] < L.Pstride;
+    has_t[h] = e[h] < L.PQ;
+    if (live[h]) {
+      const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
+      p[h] = *reinterpret_cast<const float4*>(params + g4);
+      m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
+      v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
+      g[h] = *reinterpret_cast<const float4*>(grads + g4);
+      if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
+    }
   }
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
-    *reinterpret_cast<float4*>(params + g8 + 4 * h) = p[h];
-    *reinterpret_cast<float4*>(exp_avg + g8 + 4 * h) = m[h];
-    *reinterpret_cast<float4*>(exp_avg_sq + g8 + 4 * h) = v[h];
-  }
-  if (has_t) {
-    *reinterpret_cast<float4*>(target + t8) = tg[0];
-    *reinterpret_cast<float4*>(target + t8 + 4) = tg[1];
-  }
-  if (shadow) {  // refresh the bf16 operand images of the weights just updated
-    uint8_t* wimg = BP.wimg + (int64_t)agent * BP.agent_w_bytes;
-    int net;
-    int64_t off;
-    if (shadow_loc(L, BP.KXB, e0, net, off) && off >= BP.w0_bytes) {  // W1: one aligned chunk
-      *reinterpret_cast<uint4*>(wimg + (int64_t)net * BP.net_bytes + off) =
-          make_uint4(umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]), umma::pack_bf16(pp[4], pp[5]),
-                     umma::pack_bf16(pp[6], pp[7]));
-      if (has_t)
-        *reinterpret_cast<uint4*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) =
-            make_uint4(umma::pack_bf16(tp[0], tp[1]), umma::pack_bf16(tp[2], tp[3]), umma::pack_bf16(tp[4], tp[5]),
-                       umma::pack_bf16(tp[6], tp[7]));
-    } else {
+    if (!live[h]) continue;
+    const float ss = e[h] < L.off_v ? sc.ss_q : (e[h] < L.off_a ? sc.ss_v : sc.ss_a);
+    float* pp = &p[h].x; float* mp = &m[h].x; float* vp = &v[h].x; const float* gp = &g[h].x; float* tp = &tg[h].x;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        if (shadow_loc(L, BP.KXB, e0 + c, net, off)) {
-          *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)net * BP.net_bytes + off) = __float2bfloat16_rn(pp[c]);
-          if (has_t)
-            *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) = __float2bfloat16_rn(tp[c]);
+    for (int c = 0; c < 4; ++c) {
+      const float gg = gp[c];
+      const float mm = mp[c] + (1.0f - 0.9f) * (gg - mp[c]);
+      const float vv = 0.999f * vp[c] + (1.0f - 0.999f) * gg * gg;
+      const float denom = sqrtf(vv) / sc.bc2_sqrt + 1e-8f;
+      pp[c] = pp[c] - ss * (mm / denom);
+      mp[c] = mm;
+      vp[c] = vv;
+      if (has_t[h]) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);  // Tensor.lerp_ (weight < 0.5), with the post-Adam qf
+    }
+    const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
+    *reinterpret_cast<float4*>(params + g4) = p[h];
+    *reinterpret_cast<float4*>(exp_avg + g4) = m[h];
+    *reinterpret_cast<float4*>(exp_avg_sq + g4) = v[h];
+    if (has_t[h]) *reinterpret_cast<float4*>(target + (int64_t)agent * L.PQstride + e[h]) = tg[h];
+    if (shadow) {  // refresh the bf16 operand images of the weights just updated
+      uint8_t* wimg = BP.wimg + (int64_t)agent * BP.agent_w_bytes;
+      int net;
+      int64_t off;
+      if (shadow_loc(L, BP.KXB, e[h], net, off) && off >= BP.w0_bytes) {  // W1: four columns of one image chunk
+        *reinterpret_cast<uint2*>(wimg + (int64_t)net * BP.net_bytes + off) =
+            make_uint2(umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]));
+        if (has_t[h])
+          *reinterpret_cast<uint2*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) =
+              make_uint2(umma::pack_bf16(tp[0], tp[1]), umma::pack_bf16(tp[2], tp[3]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (shadow_loc(L, BP.KXB, e[h] + c, net, off)) {
+            *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)net * BP.net_bytes + off) = __float2bfloat16_rn(pp[c]);
+            if (has_t[h])
+              *reinterpret_cast<__nv_bfloat16*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) = __float2bfloat16_rn(tp[c]);
+          }
         }
       }
     }
@@ -385,7 +401,9 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   const bool bf = h->desc.precision == 1;
   const BfParams* bp = bf16_params(h);
   int rc;
-  if (sampled) {
+  if (sampled && bf) {
+    if ((rc = bf16_gather_pack(h, a0, n, pf, st))) return rc;
+  } else if (sampled) {
     IQLB_REQUIRE(h->table != nullptr, "no replay table attached (iqlb_agents_set_replay)");
     rc = launch_gather(h->table, h->n_rows, L.R, 2 * L.S + L.A, h->reward_cols,
                        h->reward_variant ? h->reward_variant + a0 : nullptr, h->rng + 2 * a0, nullptr, n, L.B,
@@ -394,7 +412,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
     pf.mark("replay_gather");
   }
   if (bf) {
-    if ((rc = bf16_step_gemms_fwd(h, a0, n, pf, st))) return rc;
+    if ((rc = bf16_step_gemms_fwd(h, a0, n, pf, st, sampled))) return rc;
   } else {
     const int N = h->desc.n_agents;  // the fp32 parity path always runs all agents in one group
     if ((rc = launch_grouped_gemm(GEMM_FWD, h->t_fwd0, N * kStreams, L.B, L.H, false, st))) return rc;
@@ -433,8 +451,7 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
   const bool bf = h->desc.precision == 1;
   if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
-  const int64_t n8 = L.Pstride / 8;
-  adam_polyak_kernel<<<dim3((unsigned)((n8 + 255) / 256), n), 256, 0, st>>>(
+  adam_polyak_kernel<<<dim3((unsigned)((L.Pstride + 2047) / 2048), n), 256, 0, st>>>(
       L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0, a0);
   IQLB_LAUNCH_CHECK();
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
@@ -492,6 +509,7 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
                "null state buffer");
   IQLB_REQUIRE(d->n_agents > 0 && d->state_dim > 0 && d->action_dim > 0 && d->hidden_dim > 0, "dims");
   IQLB_REQUIRE(d->batch_size > 0 && d->batch_size <= 1024, "batch_size in [1, 1024]");
+  IQLB_REQUIRE(d->action_dim <= kOutMax, "action_dim <= 24 (widest D4RL action space in the reference configs)");
   IQLB_REQUIRE(d->row_stride % 4 == 0 && d->row_stride >= 2 * d->state_dim + d->action_dim + 2,
                "row_stride must hold obs|act|next_obs|rew|done and be a multiple of 4");
   IQLB_REQUIRE(d->precision == 0 || d->precision == 1, "precision must be 0 (fp32) or 1 (bf16 tcgen05)");
@@ -663,6 +681,7 @@ extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, 
     case 5: src = h->dH1; n = N * kTrain * BH; break;
     case 6: src = h->grads; n = N * L.Pstride; break;
     case 7: src = h->batch; n = N * L.B * L.R; break;
+    case 8: src = bf16_params(h) ? (const float*)bf16_params(h)->dbg : nullptr; n = src ? 8192 : 0; break;
     default: return fail(IQLB_ERR_INVALID, "unknown debug tensor%s", "");
   }
   if (nbytes) *nbytes = n * (int64_t)sizeof(float);

@@ -97,6 +97,7 @@ struct BfParams {
   int64_t z_bytes;        // one dz image [B x 64]
   uint8_t *wimg, *xsa, *xnext, *h1, *h2, *dh2, *dh1, *dz;
   uint32_t *mask1, *mask2;  // [agent][train net][B][H/32]
+  unsigned long long* dbg;  // IQLB_TIMELINE=1: clock64 stamps of CTA 0 (kernel timelines, debug tensor 8)
 };
 
 struct Bf16State {

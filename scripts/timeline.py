@@ -1,0 +1,42 @@
+#!/usr/bin/env python
+"""Per-tile clock64 timeline of CTA 0 of the persistent forward kernel (IQLB_TIMELINE=1)."""
+import os, sys, argparse
+os.environ["IQLB_TIMELINE"] = "1"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import bench
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--agents-per-gpu", type=int, default=64)
+ap.add_argument("--rows", type=int, default=1_000_000)
+ap.add_argument("--precision", default="bf16")
+ap.add_argument("--fused-adam", type=int, default=0)
+args = ap.parse_args()
+dev = torch.device("cuda", 0)
+torch.cuda.set_device(0)
+eng, buf, cols, variant, _ = bench.build_workload(args, dev, 0)
+if args.fused_adam:
+    eng.debug_option(0, 1)
+for _ in range(5):
+    eng.train(None)
+torch.cuda.synchronize()
+ts = eng.debug_tensor(8).view(torch.int64).cpu().numpy()
+def show(name, base, n):
+    print(name)
+    t0 = ts[0]
+    for it in range(8):
+        r = ts[base + it * 8: base + it * 8 + n]
+        if r[0] == 0:
+            break
+        print(f"  it{it}: " + " ".join(f"{int(x - t0):7d}" for x in r))
+show("epilogue: start, MMA0 ok, epi0 end, BW ok, MMA1 ok, epi1 end, barrier, pre-epi1 barrier", 0, 8)
+show("tile end: load_bw issued, stores issued, heads written", 1536, 3)
+show("mma: L0 issue, kb0..kb3 issue", 512, 5)
+show("producer: X issue, ring e0..e4 issue", 1024, 6)
+
+w = ts[2048:2048 + 24]
+if w[0]:
+    names = ["start", "p1 done", "chunk0 staged", "c0 sync", "c1 sync", "c2 sync", "c3 sync", "p2 done", "c0 adam", "c1 adam", "c2 adam",
+             "c3 adam", "end", "c0 loads issued", "c1 loads", "c2 loads", "c3 loads"]
+    print("bwd_weight (fused) CTA (0,1,0): " + ", ".join(f"{n}={int(x - w[0])}" for n, x in zip(names, w) if x))

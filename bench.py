@@ -279,7 +279,7 @@ def kernel_roofline(prof, n_agents, peaks):
         "bf16_bwd_weight_adam": ("hbm", 24 * p + 8 * pq + 2 * (p + pq)),
         "head_fwd": ("hbm", 7 * B * H * 4), "head_bwd": ("hbm", 4 * 2 * B * H * 4), "loss": ("hbm", B * row),
         "adam_polyak": ("hbm", 24 * p + 8 * pq + 4 * p),  # p,m,v r+w, target r+w, grads read
-        "adam_polyak_shadow": ("hbm", 24 * p + 8 * pq + 4 * p + 2 * (p + pq)),
+        "adam_polyak_shadow": ("hbm", 24 * p + 8 * pq + 2 * p + 2 * (p + pq)),  # p,m,v r+w, target r+w, bf16 grads read, bf16 images written
     }
     table, top = [], None
     for k in prof:

@@ -359,14 +359,25 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
   const float* fnet = params + (int64_t)agent * L.Pstride + L.net_off(s);
   const int64_t at = (int64_t)agent * kTrain + t;
 
+  const bool dbgd = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && blockIdx.z == 0 && tid == 64;
+#define IQLB_TSD(slot) do { if (dbgd) P.dbg[2560 + (slot)] = (unsigned long long)clock64(); } while (0)
+  IQLB_TSD(0);
   if (tid == 0) {
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
     fence_barrier_init();
+    // the TMA engine keeps only a few tens of KB in flight per SM: ask L2 for the whole image first, so the
+    // copies below trail a DRAM fetch that runs at full rate instead of paying one DRAM latency per piece
+    if (P.opt_pf1 == 1) bulk_prefetch_l2(w1img, 131072u);
     for (int ib = 0; ib < 4; ++ib) {
       mbar_expect_tx(bar_w + 8 * ib, 32768u);
       bulk_g2s(sbase + oW + (uint32_t)ib * 32768u, w1img + (int64_t)ib * 32768, 32768u, bar_w + 8 * ib);
     }
+  }
+  if (P.opt_pf1 == 2) {  // every thread asks L2 for four 128-byte lines of the W1 image (LSU path, full memory parallelism)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(w1img + ((int64_t)(k * 256 + tid) << 7)));
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 64, 256);
   float* sw2 = reinterpret_cast<float*>(smem + oStage);
@@ -386,13 +397,15 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
 #pragma unroll
     for (int o = 0; o < kOutMax; ++o) dz[o] = o < nout ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
   }
+  IQLB_TSD(1);
   __syncthreads();
+  IQLB_TSD(2);
   {  // dH2 tile: this thread's row, columns [cbeg, cbeg+128)
-    const uint32_t mw[4] = {m2w.x, m2w.y, m2w.z, m2w.w};
-#pragma unroll
+    // (not unrolled: sixteen copies of the 24-output body would not fit the instruction cache)
+#pragma unroll 1
     for (int wq = 0; wq < 4; ++wq) {
-      const uint32_t mword = mw[wq];
-#pragma unroll
+      const uint32_t mword = wq == 0 ? m2w.x : (wq == 1 ? m2w.y : (wq == 2 ? m2w.z : m2w.w));
+#pragma unroll 1
       for (int cc = 0; cc < 32; cc += 8) {
         const int c0 = cbeg + wq * 32 + cc;
         float g[8];
@@ -421,10 +434,12 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
       }
     }
   }
+  IQLB_TSD(3);
   fence_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
   if (tid == 0) {
     uint8_t* dh2 = P.dh2 + at * P.h_bytes;
@@ -450,6 +465,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
     }
     mbar_wait(bar_mma + 8 * ib, 0);
     tc_fence_after();
+    IQLB_TSD(5 + ib);
     uint8_t* stage = smem + oStage + (ib & 1) * 16384;
     float v[32];
     tmem_ld32(lane_base + 64u * ib + 32u * chalf, v);
@@ -466,6 +482,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
       bulk_commit();
     }
   }
+  IQLB_TSD(9);
   if (tid == 0) bulk_wait_read0();
   tc_fence_before();
   __syncthreads();
@@ -545,6 +562,10 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
     bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);
     bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
+    if (P.opt_pf2) {  // phase-2 operands: L2 prefetch behind the phase-1 copies (a whole phase of lead time)
+      bulk_prefetch_l2(P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
+      bulk_prefetch_l2(P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
+    }
   }
   if (kFused && tid == 32) {
     // the optimizer state of this tile starts its trip from HBM to L2 now, under the operand loads and the
@@ -625,14 +646,14 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
       __syncthreads();  // chunk cc staged (and every warp is done reading buffer cc&1 from chunk cc-2)
       const int rr = lane >> 3, l8 = lane & 7;
       if (!kFused) {  // row-contiguous 128-bit stores of the gradient tile (8 lanes cover 256 B of a row)
-        float* gw1 = gnet + L.w1(in) + (int64_t)(ot * 128) * L.H + cc * 64 + 8 * l8;
+        __nv_bfloat16* gw1 = P.gradh + (int64_t)agent * L.Pstride + noff + L.w1(in) + (int64_t)(ot * 128) * L.H + cc * 64 + 8 * l8;
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
+        for (int it = 0; it < 4; ++it) {  // bf16, as the reference's autocast weight-gradient GEMM emits them
           const int r = warp * 16 + it * 4 + rr;
           const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
           const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
-          *reinterpret_cast<float4*>(gw1 + (int64_t)r * L.H) = g0;
-          *reinterpret_cast<float4*>(gw1 + (int64_t)r * L.H + 4) = g1;
+          *reinterpret_cast<uint4*>(gw1 + (int64_t)r * L.H) =
+              make_uint4(pack_bf16(g0.x, g0.y), pack_bf16(g0.z, g0.w), pack_bf16(g1.x, g1.y), pack_bf16(g1.z, g1.w));
         }
         continue;
       }
@@ -719,6 +740,36 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     mma_commit(bar_p2);
   }
   __syncwarp();
+  // Everything of the second drain that does not depend on the MMAs is done while they run: the head-bias /
+  // log_std update (gradients come from the loss kernel) and the optimizer-state loads of the flat pass.
+  const int g1 = 128 * in, g2 = g1 + 128, g3 = g2 + 128, gtot = g3 + 128 * nout;
+  const int64_t e_w0 = noff + L.w0() + (int64_t)ot * 128 * in, e_b1 = noff + L.b1(in) + ot * 128,
+                e_b0 = noff + L.b0(in) + ot * 128, e_w2 = noff + L.w2(in) + ot * 128;
+  auto flat_elem = [&](int i) -> int64_t {  // packed-parameter offset of staged gradient word i (see G0..G3 below)
+    if (i < g1) return e_w0 + i;
+    if (i < g2) return e_b1 + (i - g1);
+    if (i < g3) return e_b0 + (i - g2);
+    return e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
+  };
+  constexpr int kU = 6;  // 16-byte words per thread and array in flight (covers in <= 40 in one pass)
+  float4 pq2[kU], mq2[kU], vq2[kU], tq2[kU];
+  if (kFused) {
+    if (ot == 0) {  // head bias (and log_std)
+      if (tid < nout) adam_scalar(A, noff + L.b2(in, nout) + tid, gnet[L.b2(in, nout) + tid], -1);
+      if (t == 3 && !L.deterministic && tid >= 32 && tid < 32 + L.A)
+        adam_scalar(A, L.off_logstd + (tid - 32), grads[(int64_t)agent * L.Pstride + L.off_logstd + (tid - 32)], -1);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int i = tid * 4 + u * 1024;
+      if (i < gtot) {
+        const int64_t e = flat_elem(i);
+        pq2[u] = *reinterpret_cast<const float4*>(A.p + e); mq2[u] = *reinterpret_cast<const float4*>(A.m + e);
+        vq2[u] = *reinterpret_cast<const float4*>(A.v + e);
+        tq2[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
+      }
+    }
+  }
   mbar_wait(bar_p2, 0);
   tc_fence_after();
   IQLB_TSW(7);
@@ -726,7 +777,6 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     // ---- everything else through shared memory in packed-parameter order:
     //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
     // each a contiguous, 16-byte aligned span of the parameter vector -> one flat float4 Adam pass
-    const int g1 = 128 * in, g2 = g1 + 128, g3 = g2 + 128, gtot = g3 + 128 * nout;
     if (chalf == 0) {
       for (int c0 = 0; c0 < n0; c0 += 16) {
         float v[16];
@@ -758,44 +808,33 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
         if (o < nout) stg[g3 + o * 128 + trow] = v[o];
     }
     __syncthreads();
-    const int64_t e_w0 = noff + L.w0() + (int64_t)ot * 128 * in, e_b1 = noff + L.b1(in) + ot * 128,
-                  e_b0 = noff + L.b0(in) + ot * 128, e_w2 = noff + L.w2(in) + ot * 128;
     if (!kFused) {  // flat, 128-bit copy of the staged gradients into the gradient buffer
-      float* gagent = grads + (int64_t)agent * L.Pstride;
+      __nv_bfloat16* gagent = P.gradh + (int64_t)agent * L.Pstride;
       for (int i = tid * 4; i < gtot; i += 1024) {
-        int64_t e;
-        if (i < g1) e = e_w0 + i;
-        else if (i < g2) e = e_b1 + (i - g1);
-        else if (i < g3) e = e_b0 + (i - g2);
-        else e = e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
-        *reinterpret_cast<float4*>(gagent + e) = *reinterpret_cast<const float4*>(stg + i);
+        const float4 g = *reinterpret_cast<const float4*>(stg + i);
+        *reinterpret_cast<uint2*>(gagent + flat_elem(i)) = make_uint2(pack_bf16(g.x, g.y), pack_bf16(g.z, g.w));
       }
     }
-    for (int i0 = tid * 4; kFused && i0 < gtot; i0 += 4096) {  // four float4 per thread in flight
-      float4 pq[4], mq[4], vq[4], tq[4];
-      int64_t eq[4];
+    for (int i0 = tid * 4; kFused && i0 < gtot; i0 += 1024 * kU) {
+      if (i0 != tid * 4) {  // wider first layers: later passes load here
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * 1024;
-        int64_t e = 0;
-        if (i < g1) e = e_w0 + i;
-        else if (i < g2) e = e_b1 + (i - g1);
-        else if (i < g3) e = e_b0 + (i - g2);
-        else if (i < gtot) e = e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
-        eq[u] = e;
-        if (i < gtot) {
-          pq[u] = *reinterpret_cast<const float4*>(A.p + e); mq[u] = *reinterpret_cast<const float4*>(A.m + e);
-          vq[u] = *reinterpret_cast<const float4*>(A.v + e);
-          tq[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
+        for (int u = 0; u < kU; ++u) {
+          const int i = i0 + u * 1024;
+          if (i < gtot) {
+            const int64_t e = flat_elem(i);
+            pq2[u] = *reinterpret_cast<const float4*>(A.p + e); mq2[u] = *reinterpret_cast<const float4*>(A.m + e);
+            vq2[u] = *reinterpret_cast<const float4*>(A.v + e);
+            tq2[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
+          }
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kU; ++u) {
         const int i = i0 + u * 1024;
         if (i >= gtot) continue;
-        const int64_t e = eq[u];
+        const int64_t e = flat_elem(i);
         const float4 g = *reinterpret_cast<const float4*>(stg + i);
-        float4 &p = pq[u], &m = mq[u], &v = vq[u], &tg = tq[u];
+        float4 &p = pq2[u], &m = mq2[u], &v = vq2[u], &tg = tq2[u];
         adam_update(p.x, m.x, v.x, g.x, A.ss, A.bc2_sqrt); adam_update(p.y, m.y, v.y, g.y, A.ss, A.bc2_sqrt);
         adam_update(p.z, m.z, v.z, g.z, A.ss, A.bc2_sqrt); adam_update(p.w, m.w, v.w, g.w, A.ss, A.bc2_sqrt);
         *reinterpret_cast<float4*>(A.p + e) = p;
@@ -816,11 +855,6 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
           }
         }
       }
-    }
-    if (kFused && ot == 0) {  // head bias (and log_std): gradients were reduced by the loss kernel
-      if (tid < nout) adam_scalar(A, noff + L.b2(in, nout) + tid, gnet[L.b2(in, nout) + tid], -1);
-      if (t == 3 && !L.deterministic && tid >= 32 && tid < 32 + L.A)
-        adam_scalar(A, L.off_logstd + (tid - 32), grads[(int64_t)agent * L.Pstride + L.off_logstd + (tid - 32)], -1);
     }
   }
   IQLB_TSW(12);
@@ -876,7 +910,10 @@ int bf16_create(iqlb_agents* h) {
   if (!rc) rc = alloc((void**)&P.dz, N * kTrain * P.z_bytes);
   if (!rc) rc = alloc((void**)&P.mask1, N * kTrain * L.B * (L.H / 32) * 4);
   if (!rc) rc = alloc((void**)&P.mask2, N * kTrain * L.B * (L.H / 32) * 4);
+  if (!rc) rc = alloc((void**)&P.gradh, N * L.Pstride * 2);
   P.dbg = nullptr;
+  auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
+  P.opt_pf1 = envi("IQLB_PF1", 1); P.opt_pf2 = envi("IQLB_PF2", 1); P.opt_pf3 = envi("IQLB_PF3", 0);
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
   if (rc) return rc;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
@@ -894,7 +931,7 @@ void bf16_destroy(iqlb_agents* h) {
   if (!st) return;
   BfParams& P = st->P;
   cudaFree(P.wimg); cudaFree(P.xsa); cudaFree(P.xnext); cudaFree(P.h1); cudaFree(P.h2); cudaFree(P.dh2);
-  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2); cudaFree(P.dbg);
+  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2); cudaFree(P.gradh); cudaFree(P.dbg);
   delete st;
   h->bf16_state = nullptr;
 }

@@ -70,7 +70,11 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
                             float* __restrict__ d_out, float* __restrict__ grads, float* __restrict__ losses,
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
                             uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
-                            uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0) {
+                            uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0, unsigned long long* dbg,
+                            const uint8_t* __restrict__ wimg, int64_t agent_w_bytes, int64_t net_bytes,
+                            __nv_bfloat16* __restrict__ gradh) {
+#define IQLB_TSL(slot) do { if (dbg && blockIdx.x == 0) dbg[3072 + (slot)] = (unsigned long long)clock64(); } while (0)
+  if (threadIdx.x == 0) IQLB_TSL(0);
   // per-warp partial sums of every reduced quantity: 0 vl | 1 ql | 2 al | 3..5 head bias grads (V, Q1, Q2)
   // | 6.. actor head bias grads [A] | 6+A.. log_std grads [A]; one block-wide pass at the end
   constexpr int kNV = 6 + 2 * kOutMax;
@@ -81,6 +85,33 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
   const bool bf = dzimg != nullptr;
   const float* hp = hparams + agent * IQLB_HP_STRIDE;
   const float discount = hp[0], beta = hp[2], iql_tau = hp[3];
+  // per-agent bookkeeping (fp64 pow / cos: a long dependent chain).  When the launch carries an extra warp
+  // beyond the batch rows, its first lane does this at once, under the loss arithmetic of the other warps.
+  const bool extra_warp = (int)blockDim.x >= ((L.B + 31) / 32) * 32 + 32;
+  auto bookkeeping = [&]() {
+    IQLB_TSL(5);
+    // Adam step scalars of THIS step (torch optim/adam.py:529-547) and scheduler/rng advance.
+    const long long t = it[agent] + 1;
+    const double bc1 = 1.0 - pow(0.9, (double)t), bc2 = 1.0 - pow(0.999, (double)t);
+    const double lr_a = actor_lr[agent];
+    StepScalars sc;
+    sc.ss_v = (float)((double)hp[4] / bc1);
+    sc.ss_q = (float)((double)hp[5] / bc1);
+    sc.ss_a = (float)(lr_a / bc1);
+    sc.bc2_sqrt = (float)sqrt(bc2);
+    sc.tau = hp[1];
+    scal[agent] = sc;
+    it[agent] = t;
+    actor_lr[agent] = cosine_next(lr_a, (double)hp[6], t, (long long)hp[7]);
+    if (advance_rng) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
+    IQLB_TSL(6);
+  };
+  if (wimg != nullptr && b < 4) {
+    // the data-gradient kernel that follows reads W1 of the four trainable networks (images 0..3 of the agent):
+    // start their trip HBM -> L2 now, while this latency-bound kernel runs
+    umma::bulk_prefetch_l2(wimg + (int64_t)agent * agent_w_bytes + (int64_t)b * net_bytes, (uint32_t)net_bytes);
+  }
+  if (extra_warp && b == (int)blockDim.x - 32) bookkeeping();
   const float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
   float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
   const int bb = live ? b : 0;
@@ -102,6 +133,7 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
 
   const float tq = fminf(tq1, tq2);
   const float adv = tq - v;
+  if (threadIdx.x == 0) IQLB_TSL(1);
   const float wt = adv < 0.f ? fabsf(iql_tau - 1.0f) : fabsf(iql_tau);
   const float y = rew + (1.0f - done) * discount * nv;
   const float e1 = q1 - y, e2 = q2 - y;
@@ -128,30 +160,48 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
     put_dz(3, L.A, 1.0f);
   }
   float bc = 0.f;
+  // phase A: per-action terms in registers (no cross-lane traffic); phase B: warp sums of eight actions at a
+  // time, level by level, so the 16 shuffle chains of a group overlap instead of running one after another
+  float dzs[kOutMax], gss[kOutMax];
 #pragma unroll
   for (int a = 0; a < kOutMax; ++a) {
-    if (a < L.A) {  // uniform
-      float gls = 0.f, dza = 0.f;
-      if (live) {
-        const float diff = mu[a] - act[a];
-        float dmu;
-        if (L.deterministic) {
-          bc += diff * diff;
-          dmu = 2.0f * w * diff * invB;
-        } else {
-          const float ls = fminf(fmaxf(lsr[a], -20.0f), 2.0f);
-          const float sigma = expf(ls);
-          const float inv_var = 1.0f / (sigma * sigma);
-          bc += 0.5f * diff * diff * inv_var + ls + 0.91893853320467274178f;
-          dmu = w * diff * inv_var * invB;
-          gls = (lsr[a] >= -20.0f && lsr[a] <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
-        }
-        dza = dmu * (1.0f - mu[a] * mu[a]);
-        dout[(int64_t)(3 + a) * L.B + b] = dza;
-        if (bf) put_dz(3, a, dza);
+    float gls = 0.f, dza = 0.f;
+    if (live && a < L.A) {
+      const float diff = mu[a] - act[a];
+      float dmu;
+      if (L.deterministic) {
+        bc += diff * diff;
+        dmu = 2.0f * w * diff * invB;
+      } else {
+        const float ls = fminf(fmaxf(lsr[a], -20.0f), 2.0f);
+        const float sigma = expf(ls);
+        const float inv_var = 1.0f / (sigma * sigma);
+        bc += 0.5f * diff * diff * inv_var + ls + 0.91893853320467274178f;
+        dmu = w * diff * inv_var * invB;
+        gls = (lsr[a] >= -20.0f && lsr[a] <= 2.0f) ? w * (1.0f - diff * diff * inv_var) * invB : 0.f;
       }
-      const float sa = warp_sum(dza), sg = warp_sum(gls);
-      if (lane == 0) { red[warp][6 + a] = sa; red[warp][6 + L.A + a] = sg; }
+      dza = dmu * (1.0f - mu[a] * mu[a]);
+      dout[(int64_t)(3 + a) * L.B + b] = dza;
+      if (bf) put_dz(3, a, dza);
+    }
+    dzs[a] = dza; gss[a] = gls;
+  }
+#pragma unroll
+  for (int a0 = 0; a0 < kOutMax; a0 += 8) {
+    if (a0 < L.A) {  // uniform
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          dzs[a0 + k] += __shfl_xor_sync(0xffffffffu, dzs[a0 + k], o);
+          gss[a0 + k] += __shfl_xor_sync(0xffffffffu, gss[a0 + k], o);
+        }
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (a0 + k < L.A) { red[warp][6 + a0 + k] = dzs[a0 + k]; red[warp][6 + L.A + a0 + k] = gss[a0 + k]; }
+      }
     }
   }
   const float al = live ? w * bc : 0.f;
@@ -162,7 +212,9 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
       red[warp][0] = s0; red[warp][1] = s1; red[warp][2] = s2; red[warp][3] = s3; red[warp][4] = s4; red[warp][5] = s5;
     }
   }
+  if (threadIdx.x == 0) IQLB_TSL(2);
   __syncthreads();
+  if (threadIdx.x == 0) IQLB_TSL(3);
   const int nvals = 6 + 2 * L.A;
   for (int j = b; j < nvals; j += blockDim.x) {  // thread j adds the per-warp partials of quantity j in warp order
     float tot = 0.f;
@@ -177,30 +229,19 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
     } else if (j == 2) {
       const float actor_loss = tot * invB;
       losses[agent * 3 + 2] = actor_loss; loss_sum[agent * 3 + 2] += actor_loss;
-    } else if (j < 6) {
-      if (bf) g[(j == 3 ? L.off_v + L.b2(L.S, 1) : (j == 4 ? L.off_q1 : L.off_q2) + L.b2(L.Dq, 1))] = tot;
-    } else if (j < 6 + L.A) {
-      if (bf) g[L.off_a + L.b2(L.S, L.A) + (j - 6)] = tot;
-    } else if (!L.deterministic) {
-      g[L.off_logstd + (j - 6 - L.A)] = tot;
+    } else {
+      int64_t e = -1;
+      if (j < 6) { if (bf) e = (j == 3 ? L.off_v + L.b2(L.S, 1) : (j == 4 ? L.off_q1 : L.off_q2) + L.b2(L.Dq, 1)); }
+      else if (j < 6 + L.A) { if (bf) e = L.off_a + L.b2(L.S, L.A) + (j - 6); }
+      else if (!L.deterministic) e = L.off_logstd + (j - 6 - L.A);
+      if (e >= 0) {
+        g[e] = tot;
+        if (gradh != nullptr) gradh[(int64_t)agent * L.Pstride + e] = __float2bfloat16_rn(tot);
+      }
     }
   }
-  if (b == 32 || (blockDim.x <= 32 && b == 0)) {
-    // Adam step scalars of THIS step (torch optim/adam.py:529-547) and scheduler/rng advance.
-    const long long t = it[agent] + 1;
-    const double bc1 = 1.0 - pow(0.9, (double)t), bc2 = 1.0 - pow(0.999, (double)t);
-    const double lr_a = actor_lr[agent];
-    StepScalars sc;
-    sc.ss_v = (float)((double)hp[4] / bc1);
-    sc.ss_q = (float)((double)hp[5] / bc1);
-    sc.ss_a = (float)(lr_a / bc1);
-    sc.bc2_sqrt = (float)sqrt(bc2);
-    sc.tau = hp[1];
-    scal[agent] = sc;
-    it[agent] = t;
-    actor_lr[agent] = cosine_next(lr_a, (double)hp[6], t, (long long)hp[7]);
-    if (advance_rng) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
-  }
+  if (threadIdx.x == 0) IQLB_TSL(4);
+  if (!extra_warp && (b == 32 || (blockDim.x <= 32 && b == 0))) bookkeeping();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -272,6 +313,8 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
   // 8 floats: a word never straddles two optimizers, and inside W1 it is half of a 16-byte chunk of the image.
   const int agent = agent0 + blockIdx.y;
   const StepScalars sc = scal[agent];
+  const bool hint = (shadow & 2) != 0;  // stream the optimizer state through L2 (evict_first), keep the images (evict_last)
+  const uint64_t pol_s = l2_policy_evict_first(), pol_k = l2_policy_evict_last();
   float4 p[2], m[2], v[2], g[2], tg[2];
   int64_t e[2];
   bool live[2], has_t[2];
@@ -282,11 +325,27 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
     has_t[h] = e[h] < L.PQ;
     if (live[h]) {
       const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
-      p[h] = *reinterpret_cast<const float4*>(params + g4);
-      m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
-      v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
-      g[h] = *reinterpret_cast<const float4*>(grads + g4);
-      if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
+      if (shadow & 1) {  // bf16 path: gradients arrive in bf16
+        p[h] = *reinterpret_cast<const float4*>(params + g4);
+        m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
+        v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
+        const uint2 gh = *reinterpret_cast<const uint2*>(BP.gradh + g4);
+        g[h] = make_float4(__uint_as_float(gh.x << 16), __uint_as_float(gh.x & 0xffff0000u), __uint_as_float(gh.y << 16),
+                           __uint_as_float(gh.y & 0xffff0000u));
+        if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
+      } else if (hint) {
+        p[h] = ld_f4_hint(params + g4, pol_s);
+        m[h] = ld_f4_hint(exp_avg + g4, pol_s);
+        v[h] = ld_f4_hint(exp_avg_sq + g4, pol_s);
+        g[h] = ld_f4_hint(grads + g4, pol_s);
+        if (has_t[h]) tg[h] = ld_f4_hint(target + (int64_t)agent * L.PQstride + e[h], pol_s);
+      } else {
+        p[h] = *reinterpret_cast<const float4*>(params + g4);
+        m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
+        v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
+        g[h] = *reinterpret_cast<const float4*>(grads + g4);
+        if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
+      }
     }
   }
 #pragma unroll
@@ -306,20 +365,34 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
       if (has_t[h]) tp[c] = tp[c] + sc.tau * (pp[c] - tp[c]);  // Tensor.lerp_ (weight < 0.5), with the post-Adam qf
     }
     const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
-    *reinterpret_cast<float4*>(params + g4) = p[h];
-    *reinterpret_cast<float4*>(exp_avg + g4) = m[h];
-    *reinterpret_cast<float4*>(exp_avg_sq + g4) = v[h];
-    if (has_t[h]) *reinterpret_cast<float4*>(target + (int64_t)agent * L.PQstride + e[h]) = tg[h];
-    if (shadow) {  // refresh the bf16 operand images of the weights just updated
+    if (hint) {
+      st_f4_hint(params + g4, p[h], pol_s);
+      st_f4_hint(exp_avg + g4, m[h], pol_s);
+      st_f4_hint(exp_avg_sq + g4, v[h], pol_s);
+      if (has_t[h]) st_f4_hint(target + (int64_t)agent * L.PQstride + e[h], tg[h], pol_s);
+    } else {
+      *reinterpret_cast<float4*>(params + g4) = p[h];
+      *reinterpret_cast<float4*>(exp_avg + g4) = m[h];
+      *reinterpret_cast<float4*>(exp_avg_sq + g4) = v[h];
+      if (has_t[h]) *reinterpret_cast<float4*>(target + (int64_t)agent * L.PQstride + e[h]) = tg[h];
+    }
+    if (shadow & 1) {  // refresh the bf16 operand images of the weights just updated
       uint8_t* wimg = BP.wimg + (int64_t)agent * BP.agent_w_bytes;
       int net;
       int64_t off;
       if (shadow_loc(L, BP.KXB, e[h], net, off) && off >= BP.w0_bytes) {  // W1: four columns of one image chunk
-        *reinterpret_cast<uint2*>(wimg + (int64_t)net * BP.net_bytes + off) =
-            make_uint2(umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]));
-        if (has_t[h])
-          *reinterpret_cast<uint2*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) =
-              make_uint2(umma::pack_bf16(tp[0], tp[1]), umma::pack_bf16(tp[2], tp[3]));
+        if (hint) {
+          st_u2_hint(wimg + (int64_t)net * BP.net_bytes + off, umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]), pol_k);
+          if (has_t[h])
+            st_u2_hint(wimg + (int64_t)(net + 4) * BP.net_bytes + off, umma::pack_bf16(tp[0], tp[1]),
+                       umma::pack_bf16(tp[2], tp[3]), pol_k);
+        } else {
+          *reinterpret_cast<uint2*>(wimg + (int64_t)net * BP.net_bytes + off) =
+              make_uint2(umma::pack_bf16(pp[0], pp[1]), umma::pack_bf16(pp[2], pp[3]));
+          if (has_t[h])
+            *reinterpret_cast<uint2*>(wimg + (int64_t)(net + 4) * BP.net_bytes + off) =
+                make_uint2(umma::pack_bf16(tp[0], tp[1]), umma::pack_bf16(tp[2], tp[3]));
+        }
       } else {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -332,6 +405,11 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
       }
     }
   }
+}
+
+__global__ void bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = __bfloat162float(src[i]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -423,10 +501,13 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
     IQLB_LAUNCH_CHECK();
     pf.mark("head_fwd");
   }
-  const int lb = (L.B + 31) / 32 * 32;
+  int lb = (L.B + 31) / 32 * 32;
+  if (lb + 32 <= 1024) lb += 32;  // bookkeeping warp
   loss_kernel<<<n, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
                                 h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0,
-                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0, a0);
+                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0, a0, bf ? bp->dbg : nullptr,
+                                (bf && bp->opt_pf3) ? bp->wimg : nullptr, bf ? bp->agent_w_bytes : 0, bf ? bp->net_bytes : 0,
+                                bf ? bp->gradh : nullptr);
   IQLB_LAUNCH_CHECK();
   pf.mark("loss");
   if (bf) {
@@ -451,8 +532,9 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
   const bool bf = h->desc.precision == 1;
   if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
+  static const bool l2hint = getenv("IQLB_L2HINT") && atoi(getenv("IQLB_L2HINT")) != 0;  // measured: no gain on B200
   adam_polyak_kernel<<<dim3((unsigned)((L.Pstride + 2047) / 2048), n), 256, 0, st>>>(
-      L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, bf ? 1 : 0, a0);
+      L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, (bf ? 1 : 0) | (l2hint ? 2 : 0), a0);
   IQLB_LAUNCH_CHECK();
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
@@ -679,7 +761,18 @@ extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, 
     case 3: src = h->d_out; n = N * L.dout_rows() * L.B; break;
     case 4: src = h->dH2; n = N * kTrain * BH; break;
     case 5: src = h->dH1; n = N * kTrain * BH; break;
-    case 6: src = h->grads; n = N * L.Pstride; break;
+    case 6:
+      n = N * L.Pstride;
+      if (h->desc.precision == 1 && !h->fused_adam && bf16_params(h)) {
+        if (nbytes) *nbytes = n * (int64_t)sizeof(float);
+        if (dst) {
+          bf16_to_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(bf16_params(h)->gradh, (float*)dst, n);
+          IQLB_LAUNCH_CHECK();
+        }
+        return IQLB_OK;
+      }
+      src = h->grads;
+      break;
     case 7: src = h->batch; n = N * L.B * L.R; break;
     case 8: src = bf16_params(h) ? (const float*)bf16_params(h)->dbg : nullptr; n = src ? 8192 : 0; break;
     default: return fail(IQLB_ERR_INVALID, "unknown debug tensor%s", "");

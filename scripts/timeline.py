@@ -40,3 +40,11 @@ if w[0]:
     names = ["start", "p1 done", "chunk0 staged", "c0 sync", "c1 sync", "c2 sync", "c3 sync", "p2 done", "c0 adam", "c1 adam", "c2 adam",
              "c3 adam", "end", "c0 loads issued", "c1 loads", "c2 loads", "c3 loads"]
     print("bwd_weight (fused) CTA (0,1,0): " + ", ".join(f"{n}={int(x - w[0])}" for n, x in zip(names, w) if x))
+
+l = ts[3072:3072 + 8]
+if l[0]:
+    print("loss CTA 0: " + ", ".join(f"{n}={int(x - l[0])}" for n, x in zip(["start", "loads done", "loop done", "sync", "sums written", "scalars start", "scalars end"], l) if x))
+
+d = ts[2560:2560 + 12]
+if d[0]:
+    print("bwd_data CTA (0,1,0): " + ", ".join(f"{n}={int(x - d[0])}" for n, x in zip(["start", "loads in regs", "sync", "dH2 tile done", "sync2", "mma0", "mma1", "mma2", "mma3", "drained"], d) if x))

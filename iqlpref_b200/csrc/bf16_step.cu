@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
 // dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
 // each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
+__global__ void __launch_bounds__(288, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
@@ -380,27 +380,31 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
       asm volatile("prefetch.global.L2 [%0];" ::"l"(w1img + ((int64_t)(k * 256 + tid) << 7)));
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 64, 256);
+  // warps 0-7 compute and drain; warp 8 (one lane) issues the dH2 store and the MMAs, so the drain of block ib
+  // overlaps the issue of block ib+1 instead of waiting for the issuing thread's warp
+  const bool worker = warp < 8;
   float* sw2 = reinterpret_cast<float*>(smem + oStage);
-  for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
+  if (worker)
+    for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
   const int row = quarter * 32 + lane, brow = half * 128 + row;
   const int cbeg = chalf * 128;
   const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32) + chalf * 4;
-  const uint4 m2w = *reinterpret_cast<const uint4*>(m2p);
+  const uint4 m2w = worker ? *reinterpret_cast<const uint4*>(m2p) : make_uint4(0, 0, 0, 0);
   const uint32_t* m1p = P.mask1 + (at * L.B + brow) * (L.H / 32);
   uint32_t m1w[4];
 #pragma unroll
-  for (int ib = 0; ib < 4; ++ib) m1w[ib] = m1p[ib * 2 + chalf];
+  for (int ib = 0; ib < 4; ++ib) m1w[ib] = worker ? m1p[ib * 2 + chalf] : 0u;
   float dz[kOutMax];
   {
     const float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
     const int drow0 = (t == 3) ? 3 : t;
 #pragma unroll
-    for (int o = 0; o < kOutMax; ++o) dz[o] = o < nout ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
+    for (int o = 0; o < kOutMax; ++o) dz[o] = (worker && o < nout) ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
   }
   IQLB_TSD(1);
   __syncthreads();
   IQLB_TSD(2);
-  {  // dH2 tile: this thread's row, columns [cbeg, cbeg+128)
+  if (worker) {  // dH2 tile: this thread's row, columns [cbeg, cbeg+128)
     // (not unrolled: sixteen copies of the 24-output body would not fit the instruction cache)
 #pragma unroll 1
     for (int wq = 0; wq < 4; ++wq) {
@@ -441,7 +445,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
   tc_fence_after();
   IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
-  if (tid == 0) {
+  if (tid == 256) {
     uint8_t* dh2 = P.dh2 + at * P.h_bytes;
     for (int cb = 0; cb < 4; ++cb)
       bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
@@ -453,20 +457,17 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
       gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
       mma_commit(bar_mma + 8 * ib);
     }
+    bulk_wait_read0();  // the dH2 tile has left shared memory before this CTA retires
   }
   __syncwarp();
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   uint8_t* dh1 = P.dh1 + at * P.h_bytes;
 #pragma unroll
-  for (int ib = 0; ib < 4; ++ib) {
-    if (ib >= 2) {  // staging slot ib&1 was handed to a bulk store two iterations ago
-      if (tid == 0) bulk_wait_read1();
-      __syncthreads();
-    }
+  for (int ib = 0; worker && ib < 4; ++ib) {
     mbar_wait(bar_mma + 8 * ib, 0);
     tc_fence_after();
     IQLB_TSD(5 + ib);
-    uint8_t* stage = smem + oStage + (ib & 1) * 16384;
+    uint8_t* stage = smem + oW + ib * 32768;  // W1 block ib has been consumed by MMA ib: its space stages dH1 block ib
     float v[32];
     tmem_ld32(lane_base + 64u * ib + 32u * chalf, v);
     tmem_ld_wait();
@@ -476,9 +477,9 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_data_kernel(BfParams P, const
 #pragma unroll
     for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * chalf + 8 * q, v + 8 * q);
     fence_async_smem();
-    __syncthreads();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     if (tid == 0) {
-      bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oStage + (uint32_t)(ib & 1) * 16384u, 16384u);
+      bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oW + (uint32_t)ib * 32768u, 16384u);
       bulk_commit();
     }
   }
@@ -913,7 +914,7 @@ int bf16_create(iqlb_agents* h) {
   if (!rc) rc = alloc((void**)&P.gradh, N * L.Pstride * 2);
   P.dbg = nullptr;
   auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
-  P.opt_pf1 = envi("IQLB_PF1", 1); P.opt_pf2 = envi("IQLB_PF2", 1); P.opt_pf3 = envi("IQLB_PF3", 0);
+  P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
   if (rc) return rc;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
@@ -1010,7 +1011,7 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   const int N = n;
   BfParams P = st->P;
   P.agent0 = a0;
-  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 256, bwd_data_smem(), stream>>>(P, h->params, h->d_out);
+  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 288, bwd_data_smem(), stream>>>(P, h->params, h->d_out);
   IQLB_LAUNCH_CHECK();
   pf.mark("bf16_bwd_data");
   if (h->fused_adam)

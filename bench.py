@@ -295,8 +295,35 @@ def kernel_roofline(prof, n_agents, peaks):
         if top is None or e["ms_per_step"] > top["ms_per_step"]:
             top = e
     roof = {"bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
-            "frac": top["frac"], "traffic": None, "kernel": top["kernel"], "peak_source": peaks["source"]}
+            "frac": top["frac"], "traffic": ncu_traffic(top["kernel"]), "kernel": top["kernel"], "peak_source": peaks["source"],
+            "traffic_source": "profiles/r01_bf16_ncu_full.json (dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+                              "64 agents)",
+            "algorithmic_per_launch": work.get(top["kernel"], ("", 0))[1] * n_agents}
     return roof, table
+
+
+NCU_NAMES = {"adam_polyak_shadow": "adam_polyak_kernel", "adam_polyak": "adam_polyak_kernel", "bf16_fwd": "bf16_fwd_persist_kernel",
+             "bf16_bwd_data": "bf16_bwd_data_kernel", "bf16_bwd_weight": "bf16_bwd_weight_kernel", "loss": "loss_kernel",
+             "replay_gather_pack": "replay_gather_pack_kernel"}
+
+
+def ncu_traffic(kernel):
+    """DRAM bytes per launch (read + write) of `kernel` from the committed `ncu --set full` capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_bf16_ncu_full.json")) as f:
+            prof = json.load(f)
+        want = NCU_NAMES.get(kernel, kernel)
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        for k in prof["kernels"]:
+            if want in k["kernel"]:
+                tot = 0.0
+                for key in ("dram_read", "dram_write"):
+                    val, unit = k[key].split()
+                    tot += float(val) * scale[unit]
+                return tot
+    except Exception:  # noqa: BLE001
+        pass
+    return None
 
 
 def load_peaks():
@@ -403,7 +430,24 @@ def run_cuda(args):
     e1.record(stream)
     torch.cuda.synchronize(dev)
     barrier()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    ms_e2e_sync = max_over_ranks(e0.elapsed_time(e1))
+    # pipelined host feed (losses returned with one step of lag; H2D of step k+1 under update k)
+    for i in range(W):
+        eng.train_host_pipelined(host_rows[i % ring], host_losses)
+    eng.train_host_pipelined(None, host_losses)
+    torch.cuda.synchronize(dev)
+    barrier()
+    t_w0 = time.perf_counter()
+    e0.record(stream)
+    for i in range(K):
+        eng.train_host_pipelined(host_rows[i % ring], host_losses)
+    eng.train_host_pipelined(None, host_losses)  # flush: losses of the last update are on the host
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    t_w1 = time.perf_counter()
+    barrier()
+    ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), (t_w1 - t_w0) * 1e3))
+    assert torch.isfinite(host_losses).all()
 
     # the path's only training collective: logged loss rows of every rank (outside the timed region)
     from iqlpref_b200 import sharding
@@ -424,7 +468,10 @@ def run_cuda(args):
                 "clocks": clocks,
                 "e2e": {"value": world * N * K / (ms_e2e * 1e-3), "unit": UNIT,
                         "h2d_bytes_per_step": world * N * BATCH * eng.R * 4, "d2h_bytes_per_step": world * N * 3 * 4,
-                        "api": "iqlb_agents_step_host (pinned host rows -> H2D -> update -> D2H losses -> sync)"},
+                        "api": "iqlb_agents_step_host_pipelined (every step: pinned host rows -> H2D on a copy stream -> "
+                               "update -> D2H losses, returned with one step of lag; wall clock incl. final flush)",
+                        "blocking_api_value": world * N * K / (ms_e2e_sync * 1e-3),
+                        "blocking_api": "iqlb_agents_step_host (H2D -> update -> D2H losses -> sync, every step)"},
                 "gpu_launches": launches,
                 "roofline": roof,
                 "kernels": table,

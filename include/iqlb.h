@@ -121,6 +121,14 @@ int iqlb_agents_step(iqlb_agents* h, const float* batch, void* stream);
  * losses[n_agents][3] into host_losses, then a stream synchronise (the reference's .item()). */
 int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_losses, void* stream);
 
+/* Pipelined host feed for training loops that log with one step of lag (the reference averages losses over
+ * log_freq = 250 steps, iql.py:1537-1544).  Call k copies host_batch (pinned) to the device on an internal copy
+ * stream, enqueues update k on `stream`, and returns the losses[n_agents][3] of update k-1 (zeros for k = 0)
+ * after waiting for that update only - so the H2D copy of step k+1 runs under update k.  host_batch of call k
+ * must stay untouched until call k+1 has returned.  host_batch == NULL: no new update, returns the losses of
+ * the last one (flush). */
+int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host_batch, float* host_losses_prev, void* stream);
+
 /* Tell the library that the caller wrote params/target directly (adopting modules, loading a
  * checkpoint): precision 1 rebuilds the bf16 operand images of the weights; precision 0: no-op. */
 int iqlb_agents_refresh(iqlb_agents* h, void* stream);

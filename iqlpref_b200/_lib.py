@@ -43,6 +43,7 @@ _SIGNATURES = {
     "iqlb_agents_set_replay": ([_P, _P, C.c_int64, _P, _P, _P], C.c_int),
     "iqlb_agents_step": ([_P, _P, _P], C.c_int),
     "iqlb_agents_step_host": ([_P, _P, _P, _P], C.c_int),
+    "iqlb_agents_step_host_pipelined": ([_P, _P, _P, _P], C.c_int),
     "iqlb_agents_refresh": ([_P, _P], C.c_int),
     "iqlb_agents_launches_per_step": ([_P, C.c_int32], C.c_int),
     "iqlb_agents_profile": ([_P, C.c_int32], C.c_int),

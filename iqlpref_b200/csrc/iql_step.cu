@@ -648,6 +648,16 @@ extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
   if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
   for (int g = 0; g < iqlb_agents::kMaxGroups; ++g) if (h->ev_chain[g]) cudaEventDestroy(h->ev_chain[g]);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->copy_stream) {
+    cudaStreamSynchronize(h->copy_stream);
+    cudaStreamDestroy(h->copy_stream);
+    for (int i = 0; i < 2; ++i) {
+      if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
+      if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+      cudaFree(h->stage[i]);
+      if (h->host_loss[i]) cudaFreeHost(h->host_loss[i]);
+    }
+  }
   cudaFree(h->batch); cudaFree(h->H1); cudaFree(h->H2); cudaFree(h->head_out); cudaFree(h->d_out);
   cudaFree(h->dH2); cudaFree(h->dH1); cudaFree(h->grads); cudaFree(h->scal);
   for (int i = 0; i <= iqlb_agents::kMaxProf; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -688,6 +698,47 @@ extern "C" int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, fl
   IQLB_CUDA(cudaMemcpyAsync(host_losses, h->losses, (size_t)h->desc.n_agents * 3 * sizeof(float),
                             cudaMemcpyDeviceToHost, st));
   IQLB_CUDA(cudaStreamSynchronize(st));
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host_batch, float* host_losses_prev,
+                                               void* stream) {
+  IQLB_REQUIRE(h && host_losses_prev, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const Layout& L = h->L;
+  const size_t bytes = (size_t)h->desc.n_agents * L.B * L.R * sizeof(float);
+  const size_t lbytes = (size_t)h->desc.n_agents * 3 * sizeof(float);
+  if (!h->copy_stream) {
+    IQLB_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      IQLB_CUDA(cudaEventCreateWithFlags(&h->ev_h2d[i], cudaEventDisableTiming));
+      IQLB_CUDA(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+      IQLB_CUDA(cudaMalloc((void**)&h->stage[i], bytes));
+      IQLB_CUDA(cudaMallocHost((void**)&h->host_loss[i], lbytes));
+    }
+  }
+  const int s = (int)(h->pipe_k & 1);
+  if (host_batch != nullptr) {
+    // stage[s] was last read by step k-2, whose completion the previous call waited for
+    IQLB_CUDA(cudaMemcpyAsync(h->stage[s], host_batch, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+    IQLB_CUDA(cudaEventRecord(h->ev_h2d[s], h->copy_stream));
+    IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_h2d[s], 0));
+    IQLB_CUDA(cudaMemcpyAsync(h->batch, h->stage[s], bytes, cudaMemcpyDeviceToDevice, st));
+    int rc = step_device(h, false, st);
+    if (rc) return rc;
+    IQLB_CUDA(cudaMemcpyAsync(h->host_loss[s], h->losses, lbytes, cudaMemcpyDeviceToHost, st));
+    IQLB_CUDA(cudaEventRecord(h->ev_done[s], st));
+  }
+  const bool flush = host_batch == nullptr;
+  const long long prev = flush ? h->pipe_k - 1 : h->pipe_k - 1;  // the step whose losses are returned
+  if (prev >= 0) {
+    const int ps = (int)(prev & 1);
+    IQLB_CUDA(cudaEventSynchronize(h->ev_done[ps]));
+    memcpy(host_losses_prev, h->host_loss[ps], lbytes);
+  } else {
+    memset(host_losses_prev, 0, lbytes);
+  }
+  if (!flush) h->pipe_k += 1;
   return IQLB_OK;
 }
 

@@ -181,6 +181,12 @@ struct iqlb_agents {
   cudaEvent_t ev_chain[kMaxGroups] = {};
   cudaEvent_t ev_join = nullptr;
   int n_groups = 1;
+  // pipelined host feed (iqlb_agents_step_host_pipelined): H2D of step k+1 on copy_stream under the update of step k
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_h2d[2] = {}, ev_done[2] = {};
+  float* stage[2] = {};
+  float* host_loss[2] = {};  // pinned
+  long long pipe_k = 0;
 };
 
 namespace iqlb {

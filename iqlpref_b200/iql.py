@@ -484,6 +484,13 @@ class BatchedIQL:
         _lib.check(self.lib.iqlb_agents_step_host(self._h, _lib.ptr(host_rows), _lib.ptr(host_losses),
                                                   _lib.stream_ptr(self.device)), "iqlb_agents_step_host")
 
+    def train_host_pipelined(self, host_rows: Optional[torch.Tensor], host_losses_prev: torch.Tensor):
+        """Pipelined host feed: enqueue the update on `host_rows` (pinned; None = flush) and return the losses of
+        the PREVIOUS update in `host_losses_prev`; the H2D copy of the next call overlaps this update."""
+        _lib.check(self.lib.iqlb_agents_step_host_pipelined(self._h, _lib.ptr(host_rows) if host_rows is not None else None,
+                                                            _lib.ptr(host_losses_prev), _lib.stream_ptr(self.device)),
+                   "iqlb_agents_step_host_pipelined")
+
     def launches_per_step(self, sampled: bool) -> int:
         return int(self.lib.iqlb_agents_launches_per_step(self._h, int(sampled)))
 

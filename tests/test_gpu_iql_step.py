@@ -223,3 +223,37 @@ def test_no_cpu_path():
     from iqlpref_b200 import iql as biql
     with pytest.raises(RuntimeError):
         biql.BatchedIQL(3, 2, 1, device="cpu")
+
+
+@pytest.mark.gpu
+def test_host_feed_pipelined_matches_blocking():
+    """iqlb_agents_step_host_pipelined = iqlb_agents_step_host with the losses delivered one call later."""
+    import torch
+    from iqlpref_b200 import iql as biql
+    S, A, B, N, K = 11, 3, 64, 3, 5
+    hp = dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.7, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4, max_steps=1000)
+    engs = []
+    for _ in range(2):
+        eng = biql.BatchedIQL(S, A, N, hidden_dim=64, batch_size=B, device="cuda:0", hparams=[hp] * N)
+        for a in range(N):
+            torch.manual_seed(a)
+            eng.adopt(a, biql.TwinQ(S, A, 64), biql.ValueFunction(S, 64), biql.GaussianPolicy(S, A, 1.0, 64))
+        engs.append(eng)
+    g = torch.Generator().manual_seed(0)
+    rows = [torch.randn((N, B, engs[0].R), generator=g).pin_memory() for _ in range(K)]
+    for r in rows:
+        r[:, :, 2 * S + A + 1] = (r[:, :, 2 * S + A + 1] > 1.0).float()
+    want, got = [], []
+    hl = torch.empty((N, 3)).pin_memory()
+    for r in rows:
+        engs[0].train_host(r, hl)
+        want.append(hl.clone())
+    for r in rows:
+        engs[1].train_host_pipelined(r, hl)
+        got.append(hl.clone())
+    engs[1].train_host_pipelined(None, hl)
+    got.append(hl.clone())
+    assert torch.equal(got[0], torch.zeros_like(got[0]))
+    for k in range(K):
+        assert torch.equal(got[k + 1], want[k]), k
+    assert torch.equal(engs[0].params, engs[1].params)

@@ -106,6 +106,17 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
                             : params + (int64_t)agent * L.Pstride + L.net_off(s);
   };
 
+  // PDL: the weight images (Adam of the previous step) are older than the immediate predecessor (the gather):
+  // the first tile's weights start towards L2 before this grid waits for the gather's input images
+  if (tid == 0 && (int)blockIdx.x < n_tiles) {
+    int a0, s0, h0;
+    const uint8_t *w0p, *x0p;
+    const float* f0p;
+    tile_ptrs(blockIdx.x, a0, s0, h0, w0p, x0p, f0p);
+    bulk_prefetch_l2(w0p, (uint32_t)P.net_bytes);
+  }
+  pdl_wait();
+  pdl_launch();
   if (warp == 0) {
     // ------------------------------------------------------------------ producer
     if (lane == 0) {
@@ -356,7 +367,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
 }
 
 int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, bool pdl) {
   static int n_sm = 0;
   static bool attr_set = false;
   if (!attr_set) {
@@ -368,8 +379,8 @@ int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float*
   }
   const int n_tiles = n_agents * kStreams * (P.L.B / 128);
   const int grid = n_tiles < n_sm ? n_tiles : n_sm;
-  bf16_fwd_persist_kernel<<<grid, fwdp::kThreads, fwdp::kSmem, stream>>>(P, params, target, head_out, n_tiles);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(bf16_fwd_persist_kernel, dim3(grid), dim3(fwdp::kThreads), fwdp::kSmem, stream, pdl, P, params, target,
+                       head_out, n_tiles));
   return IQLB_OK;
 }
 

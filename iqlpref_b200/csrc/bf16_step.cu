@@ -77,6 +77,8 @@ __global__ void __launch_bounds__(256) replay_gather_pack_kernel(
     const float* __restrict__ reward_cols, const int32_t* __restrict__ reward_variant, const uint64_t* __restrict__ rng,
     int64_t* __restrict__ idx_out, float4* __restrict__ batch_out) {
   extern __shared__ __align__(16) float srow[];  // [rows_per_cta][R]
+  pdl_wait();  // first kernel of a step: the previous step's Adam (launched before it) must be complete
+  pdl_launch();
   const Layout& L = P.L;
   const int agent = P.agent0 + blockIdx.y;
   const int t = threadIdx.x;
@@ -394,6 +396,9 @@ __global__ void __launch_bounds__(288, 1) bf16_bwd_data_kernel(BfParams P, const
   uint32_t m1w[4];
 #pragma unroll
   for (int ib = 0; ib < 4; ++ib) m1w[ib] = worker ? m1p[ib * 2 + chalf] : 0u;
+  // everything above reads the forward kernel's and Adam's outputs only; dz comes from the loss kernel
+  pdl_wait();
+  pdl_launch();
   float dz[kOutMax];
   {
     const float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
@@ -560,9 +565,10 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     for (int i = 0; i < 5; ++i) mbar_init(bar_ld1 + 8 * i, 1);
     fence_barrier_init();
     mbar_expect_tx(bar_ld1, 7 * blk);
-    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
-    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);
+    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward / loss outputs: before the PDL wait
     bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
+    pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
+    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
     if (P.opt_pf2) {  // phase-2 operands: L2 prefetch behind the phase-1 copies (a whole phase of lead time)
       bulk_prefetch_l2(P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
       bulk_prefetch_l2(P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
@@ -584,6 +590,8 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
     }
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 40, 512);
+  pdl_wait();
+  pdl_launch();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -872,7 +880,7 @@ static size_t bwd_data_smem() { return 65536u + 131072u + 32768u + 128u; }
 static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
 
 int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
-                            cudaStream_t stream);
+                            cudaStream_t stream, bool pdl);
 bool bf16_fwd_persist_ok(const BfParams& P);
 
 int bf16_create(iqlb_agents* h) {
@@ -968,10 +976,9 @@ int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t strea
   const int vpr = L.R / 4;
   IQLB_REQUIRE(vpr <= 256, "row_stride too wide");
   const int rpc = 256 / vpr;
-  replay_gather_pack_kernel<<<dim3((unsigned)((L.B + rpc - 1) / rpc), n), 256, (size_t)rpc * L.R * 4, stream>>>(
-      P, (const float4*)h->table, (uint64_t)h->n_rows, vpr, rpc, 2 * L.S + L.A, h->reward_cols, h->reward_variant, h->rng,
-      h->idx_out, (float4*)h->batch);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(replay_gather_pack_kernel, dim3((unsigned)((L.B + rpc - 1) / rpc), n), dim3(256), (size_t)rpc * L.R * 4,
+                       stream, pdl_enabled(1) && !h->prof, P, (const float4*)h->table, (uint64_t)h->n_rows, vpr, rpc,
+                       2 * L.S + L.A, h->reward_cols, h->reward_variant, (const uint64_t*)h->rng, h->idx_out, (float4*)h->batch));
   pf.mark("replay_gather_pack");
   return IQLB_OK;
 }
@@ -995,7 +1002,7 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   }
   static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
   if (persist_env && bf16_fwd_persist_ok(P)) {
-    if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream))) return rc;
+    if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream, pdl_enabled(2) && !h->prof))) return rc;
   } else {
     bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
     IQLB_LAUNCH_CHECK();
@@ -1011,16 +1018,13 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   const int N = n;
   BfParams P = st->P;
   P.agent0 = a0;
-  bf16_bwd_data_kernel<<<dim3(L.B / 128, kTrain, N), 288, bwd_data_smem(), stream>>>(P, h->params, h->d_out);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(288), bwd_data_smem(), stream,
+                       pdl_enabled(8) && !h->prof, P,
+                       (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");
-  if (h->fused_adam)
-    bf16_bwd_weight_kernel<true><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
-        P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
-  else
-    bf16_bwd_weight_kernel<false><<<dim3(L.H / 128, kTrain, N), 256, bwd_weight_smem(L.B), stream>>>(
-        P, h->grads, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->scal);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(h->fused_adam ? bf16_bwd_weight_kernel<true> : bf16_bwd_weight_kernel<false>, dim3(L.H / 128, kTrain, N),
+                       dim3(256), bwd_weight_smem(L.B), stream, pdl_enabled(16) && !h->prof, P, h->grads, h->params, h->exp_avg, h->exp_avg_sq,
+                       h->target, (const StepScalars*)h->scal));
   pf.mark(h->fused_adam ? "bf16_bwd_weight_adam" : "bf16_bwd_weight");
   return IQLB_OK;
 }

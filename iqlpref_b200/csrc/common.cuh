@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/iqlb.h"
@@ -101,6 +102,34 @@ __device__ __forceinline__ void st_f4_hint(float* ptr, const float4& v, uint64_t
 }
 __device__ __forceinline__ void st_u2_hint(void* ptr, uint32_t a, uint32_t b, uint64_t pol) {
   asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(ptr), "r"(a), "r"(b), "l"(pol) : "memory");
+}
+#endif
+
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------------
+// Every kernel of the bf16 step is launched with programmatic stream serialization: its CTAs may start while
+// the previous kernel's last wave is still running, do the part of their prologue that does not touch the
+// previous kernel's outputs (barrier / TMEM set-up, weight loads, bookkeeping), then pdl_wait() until the
+// previous grid has completed and flushed.  pdl_launch() comes AFTER the wait in every kernel, so at most
+// two adjacent kernels overlap and anything older than the immediate predecessor is complete.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+// IQLB_PDL: bit mask of kernels launched with the attribute (1 gather, 2 forward, 4 loss, 8 data gradient,
+// 16 weight gradient, 32 Adam)
+inline bool pdl_enabled(int bit) {
+  static const int mask = getenv("IQLB_PDL") ? atoi(getenv("IQLB_PDL")) : 27;  // measured on B200: loss and Adam lose with it
+  return (mask & bit) != 0;
 }
 #endif
 

@@ -119,17 +119,21 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
   const float invB = 1.0f / (float)L.B;
   const float* log_std = params + (int64_t)agent * L.Pstride + L.off_logstd;
 
-  // every global load of this thread is issued before the first use
-  const float nv = ho[0 * L.B + bb], v = ho[1 * L.B + bb], tq1 = ho[2 * L.B + bb], tq2 = ho[3 * L.B + bb];
-  const float q1 = ho[4 * L.B + bb], q2 = ho[5 * L.B + bb];
+  // every global load of this thread is issued before the first use; what the forward kernel (the PDL
+  // predecessor) wrote - head_out - is loaded after the wait, batch rows / log_std / bookkeeping before it
   const float rew = row[2 * L.S + L.A], done = row[2 * L.S + L.A + 1];
   float mu[kOutMax], act[kOutMax], lsr[kOutMax];
 #pragma unroll
   for (int a = 0; a < kOutMax; ++a) {
-    mu[a] = a < L.A ? ho[(int64_t)(6 + a) * L.B + bb] : 0.f;
     act[a] = a < L.A ? row[L.S + a] : 0.f;
     lsr[a] = (a < L.A && !L.deterministic) ? log_std[a] : 0.f;
   }
+  pdl_wait();
+  pdl_launch();
+  const float nv = ho[0 * L.B + bb], v = ho[1 * L.B + bb], tq1 = ho[2 * L.B + bb], tq2 = ho[3 * L.B + bb];
+  const float q1 = ho[4 * L.B + bb], q2 = ho[5 * L.B + bb];
+#pragma unroll
+  for (int a = 0; a < kOutMax; ++a) mu[a] = a < L.A ? ho[(int64_t)(6 + a) * L.B + bb] : 0.f;
 
   const float tq = fminf(tq1, tq2);
   const float adv = tq - v;
@@ -319,33 +323,37 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
   int64_t e[2];
   bool live[2], has_t[2];
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
+  for (int h = 0; h < 2; ++h) {  // optimizer state: not written by the weight-gradient kernel (the PDL predecessor)
     e[h] = ((int64_t)blockIdx.x * 512 + threadIdx.x + 256 * h) * 4;
     live[h] = e[h] < L.Pstride;
     has_t[h] = e[h] < L.PQ;
     if (live[h]) {
       const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
-      if (shadow & 1) {  // bf16 path: gradients arrive in bf16
-        p[h] = *reinterpret_cast<const float4*>(params + g4);
-        m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
-        v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
-        const uint2 gh = *reinterpret_cast<const uint2*>(BP.gradh + g4);
-        g[h] = make_float4(__uint_as_float(gh.x << 16), __uint_as_float(gh.x & 0xffff0000u), __uint_as_float(gh.y << 16),
-                           __uint_as_float(gh.y & 0xffff0000u));
-        if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
-      } else if (hint) {
+      if (hint) {
         p[h] = ld_f4_hint(params + g4, pol_s);
         m[h] = ld_f4_hint(exp_avg + g4, pol_s);
         v[h] = ld_f4_hint(exp_avg_sq + g4, pol_s);
-        g[h] = ld_f4_hint(grads + g4, pol_s);
         if (has_t[h]) tg[h] = ld_f4_hint(target + (int64_t)agent * L.PQstride + e[h], pol_s);
       } else {
         p[h] = *reinterpret_cast<const float4*>(params + g4);
         m[h] = *reinterpret_cast<const float4*>(exp_avg + g4);
         v[h] = *reinterpret_cast<const float4*>(exp_avg_sq + g4);
-        g[h] = *reinterpret_cast<const float4*>(grads + g4);
         if (has_t[h]) tg[h] = *reinterpret_cast<const float4*>(target + (int64_t)agent * L.PQstride + e[h]);
       }
+    }
+  }
+  pdl_wait();
+  pdl_launch();
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {  // gradients of this step
+    if (!live[h]) continue;
+    const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
+    if (shadow & 1) {  // bf16 path: gradients arrive in bf16
+      const uint2 gh = *reinterpret_cast<const uint2*>(BP.gradh + g4);
+      g[h] = make_float4(__uint_as_float(gh.x << 16), __uint_as_float(gh.x & 0xffff0000u), __uint_as_float(gh.y << 16),
+                         __uint_as_float(gh.y & 0xffff0000u));
+    } else {
+      g[h] = *reinterpret_cast<const float4*>(grads + g4);
     }
   }
 #pragma unroll
@@ -503,12 +511,13 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   }
   int lb = (L.B + 31) / 32 * 32;
   if (lb + 32 <= 1024) lb += 32;  // bookkeeping warp
-  loss_kernel<<<n, lb, 0, st>>>(L, h->params, h->hparams, h->batch, h->head_out, h->d_out, h->grads, h->losses,
-                                h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0,
-                                bf ? bp->dz : nullptr, bf ? bp->z_bytes : 0, a0, bf ? bp->dbg : nullptr,
-                                (bf && bp->opt_pf3) ? bp->wimg : nullptr, bf ? bp->agent_w_bytes : 0, bf ? bp->net_bytes : 0,
-                                bf ? bp->gradh : nullptr);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(loss_kernel, dim3(n), dim3(lb), 0, st, bf && pdl_enabled(4) && !h->prof, L, (const float*)h->params,
+                       h->hparams, (const float*)h->batch, (const float*)h->head_out, h->d_out, h->grads, h->losses,
+                       h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0, bf ? bp->dz : (uint8_t*)nullptr,
+                       bf ? bp->z_bytes : (int64_t)0, a0, bf ? bp->dbg : (unsigned long long*)nullptr,
+                       (bf && bp->opt_pf3) ? (const uint8_t*)bp->wimg : (const uint8_t*)nullptr,
+                       bf ? bp->agent_w_bytes : (int64_t)0, bf ? bp->net_bytes : (int64_t)0,
+                       bf ? bp->gradh : (__nv_bfloat16*)nullptr));
   pf.mark("loss");
   if (bf) {
     if ((rc = bf16_step_gemms_bwd(h, a0, n, pf, st))) return rc;
@@ -533,9 +542,10 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
   if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
   static const bool l2hint = getenv("IQLB_L2HINT") && atoi(getenv("IQLB_L2HINT")) != 0;  // measured: no gain on B200
-  adam_polyak_kernel<<<dim3((unsigned)((L.Pstride + 2047) / 2048), n), 256, 0, st>>>(
-      L, h->params, h->exp_avg, h->exp_avg_sq, h->target, h->grads, h->scal, bf ? *bp : BfParams{}, (bf ? 1 : 0) | (l2hint ? 2 : 0), a0);
-  IQLB_LAUNCH_CHECK();
+  IQLB_CUDA(launch_pdl(adam_polyak_kernel, dim3((unsigned)((L.Pstride + 2047) / 2048), n), dim3(256), 0, st,
+                       bf && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
+                       (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
+                       (bf ? 1 : 0) | (l2hint ? 2 : 0), a0));
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
 }

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libiqlb.so")
+LIB_PATH = os.environ.get("IQLB_LIB") or os.path.join(_HERE, "csrc", "libiqlb.so")
 
 HP_STRIDE = 8
 

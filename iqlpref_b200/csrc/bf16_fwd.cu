@@ -6,7 +6,8 @@
 //   warp 1  MMA      : tcgen05.mma issue; layer 1 starts on K-block kb as soon as the epilogue has
 //                      written H1 block kb, so the tensor core trails the epilogue by one block
 //   warps 2-9        : epilogue (2 warps per TMEM lane quarter, 32 of every 64 columns each)
-//                      H1 / H2 tiles are staged in shared memory and leave as bulk stores
+//   warp 10          : stores: H1 / H2 tiles staged in shared memory leave as bulk stores (one commit group per
+//                      64-column block, so H2 block b moves in as soon as H1 block b has left), b1 | W2 | b2 loads
 //
 // While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
 // MMA warp has issued its layer 0, so loads, both GEMMs, TMEM allocation and barrier set-up disappear
@@ -23,15 +24,15 @@ namespace fwdp {
 //                | X tile | b0 (x2) | b1 + W2 + b2 | head partial sums ((groups-1) x [8][128]) | barriers
 constexpr uint32_t oH = 0, oRing = 65536, kSlotBytes = 32768;
 constexpr int kSlots = 4, kPerTile = 5;
-constexpr int kEpiWarps = 8, kEpiThreads = kEpiWarps * 32, kThreads = 64 + kEpiThreads;
+constexpr int kEpiWarps = 8, kEpiThreads = kEpiWarps * 32, kAuxWarp = 2 + kEpiWarps, kThreads = 64 + kEpiThreads + 32;
 constexpr int kGroups = kEpiWarps / 4, kPar = kGroups / 2;  // column-half x block-parity groups of epilogue warps
 constexpr uint32_t oX = oRing + kSlots * kSlotBytes, oB0 = oX + 16384, oBW = oB0 + 2048, kBWBytes = 9216 + 32,
                    oPart = oBW + kBWBytes, kPartBytes = (kGroups - 1) * 8 * 128 * 4, oCtrl = oPart + kPartBytes,
-                   kSmem = oCtrl + 160;
+                   kSmem = oCtrl + 256;
 static_assert(kSmem <= 232448, "shared memory budget of one CTA (227 KB)");
 // barrier indices (8 bytes each) inside the control block
 enum { FULL_L0 = 0, MMA0 = 1, MMA1 = 2, FULL_R = 3, EMPTY_R = 7, HBLK = 11, ACC0_FREE = 15, ACC1_FREE = 16, FULL_BW = 17,
-       N_BARS = 18 };
+       EPI0_DONE = 18, EPI1_DONE = 19, H1_OUT = 20 /* ..23: H1 block b has left the H tile */, H2_OUT = 24 /* ..27 */, N_BARS = 28 };
 static_assert(kSlots <= 4, "barrier indices reserve four ring slots");
 }  // namespace fwdp
 
@@ -83,6 +84,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     for (int i = 0; i < kSlots; ++i) { mbar_init(bar(FULL_R + i), 1); mbar_init(bar(EMPTY_R + i), 1); }
     for (int i = 0; i < 4; ++i) mbar_init(bar(HBLK + i), 8);
     mbar_init(bar(ACC0_FREE), kEpiWarps); mbar_init(bar(ACC1_FREE), kEpiWarps);
+    mbar_init(bar(EPI0_DONE), kEpiWarps); mbar_init(bar(EPI1_DONE), 1);
+    for (int i = 0; i < 4; ++i) { mbar_init(bar(H1_OUT + i), 1); mbar_init(bar(H2_OUT + i), 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 8 * N_BARS, 512);
@@ -106,6 +109,19 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
                             : params + (int64_t)agent * L.Pstride + L.net_off(s);
   };
 
+  auto load_bw = [&](int tile) {  // b1 and W2 (fp32) of a tile into their single buffer
+    int agent, s, half;
+    const uint8_t *wnet, *ximg;
+    const float* fnet;
+    tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
+    const int in = L.in_dim(s), nout = L.out_dim(s);
+    // W2 [nout][256] and b2 [nout] are adjacent in the parameter vector; network segments are padded to 32 bytes,
+    // so rounding b2 up to 16 bytes stays inside the segment
+    const uint32_t w2b2 = (uint32_t)nout * 1024u + (((uint32_t)nout * 4u + 15u) & ~15u);
+    mbar_expect_tx(bar(FULL_BW), 1024u + w2b2);
+    bulk_g2s(sbase + oBW, fnet + L.b1(in), 1024u, bar(FULL_BW));
+    bulk_g2s(sbase + oBW + 1024u, fnet + L.w2(in), w2b2, bar(FULL_BW));
+  };
   // PDL: the weight images (Adam of the previous step) are older than the immediate predecessor (the gather):
   // the first tile's weights start towards L2 before this grid waits for the gather's input images
   if (tid == 0 && (int)blockIdx.x < n_tiles) {
@@ -185,30 +201,17 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         mma_commit(bar(MMA1));
       }
     }
-  } else {
-    // ------------------------------------------------------------------ epilogue (16 warps)
+  } else if (warp < kAuxWarp) {
+    // ------------------------------------------------------------------ epilogue
     // warp -> TMEM lane quarter (warp % 4, the hardware rule), column half of a 64-column block, and
     // block parity: warps of parity p drain blocks p and p + 2, so blocks 0 and 1 finish together and
     // layer 1 starts after half of epilogue 0
     const int et = tid - 64;
     bool h1_store_pending = false;
+    int ntrain = 0;  // trainable tiles finished by this CTA (phase of the H1_OUT / H2_OUT barriers)
     const int quarter = warp & 3, grp = (warp - 2) >> 2, chalf = grp & 1, par = grp >> 1;  // par < kPar
     const int row = quarter * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-    auto load_bw = [&](int tile) {  // b1 and W2 (fp32) of a tile into their single buffer
-      int agent, s, half;
-      const uint8_t *wnet, *ximg;
-      const float* fnet;
-      tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
-      const int in = L.in_dim(s), nout = L.out_dim(s);
-      // W2 [nout][256] and b2 [nout] are adjacent in the parameter vector; network segments are padded to 32 bytes,
-      // so rounding b2 up to 16 bytes stays inside the segment
-      const uint32_t w2b2 = (uint32_t)nout * 1024u + (((uint32_t)nout * 4u + 15u) & ~15u);
-      mbar_expect_tx(bar(FULL_BW), 1024u + w2b2);
-      bulk_g2s(sbase + oBW, fnet + L.b1(in), 1024u, bar(FULL_BW));
-      bulk_g2s(sbase + oBW + 1024u, fnet + L.w2(in), w2b2, bar(FULL_BW));
-    };
-    if (et == 0 && (int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
     for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const uint32_t ph = (uint32_t)(it & 1);
       float* part = reinterpret_cast<float*>(smem + oPart);
@@ -229,17 +232,13 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       mbar_wait(bar(MMA0), ph);
       tc_fence_after();
       if (et == 0) IQLB_TS(it * 8 + 1);
-      if (h1_store_pending) {  // the previous trainable tile's H2 image / masks must have left the staging tiles
-        if (et == 0) bulk_wait_read0();
-        named_bar_sync(1, kEpiThreads);
-        h1_store_pending = false;
-      }
       // ---- epilogue 0: H1 = relu(acc0 + b0), block by block so that layer 1 can start behind us
 #pragma unroll 1
       for (int blk = par; blk < 4; blk += kPar) {
         const int c0 = blk * 64 + chalf * 32;
         float v[32];
         tmem_ld32(lane_base + (uint32_t)c0, v);
+        if (h1_store_pending) mbar_wait(bar(H2_OUT + blk), (uint32_t)((ntrain - 1) & 1));  // previous tile's H2 block has left
         tmem_ld_wait();
         if (t >= 0) m1[c0 >> 5] = bias_relu32<true>(v, sb0 + c0);
         else bias_relu32<false>(v, sb0 + c0);
@@ -253,24 +252,12 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(ACC0_FREE));
       if (et == 0) IQLB_TS(it * 8 + 2);
-      if (t >= 0) {
-        named_bar_sync(1, kEpiThreads);
-        if (et == 0) {
-          uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
-          for (int cb = 0; cb < 4; ++cb)
-            bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
-          bulk_commit();
-        }
-      }
+      if (lane == 0) mbar_arrive(bar(EPI0_DONE));  // every H1 block of this warp is written and fenced: the store warp takes over
       mbar_wait(bar(FULL_BW), ph);
       if (et == 0) IQLB_TS(it * 8 + 3);
       mbar_wait(bar(MMA1), ph);
       tc_fence_after();
       if (et == 0) IQLB_TS(it * 8 + 4);
-      if (t >= 0) {  // H1 and its masks have left shared memory (issued a whole layer-1 GEMM ago): H2 may move in
-        if (et == 0) bulk_wait_read0();
-        named_bar_sync(1, kEpiThreads);
-      }
       if (et == 0) IQLB_TS(it * 8 + 7);
       // ---- epilogue 1: H2 = relu(acc1 + b1); head = H2 . W2 + b2
       float acc[8];
@@ -281,6 +268,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         const int c0 = blk * 64 + chalf * 32;
         float v[32];
         tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
+        if (t >= 0) mbar_wait(bar(H1_OUT + blk), (uint32_t)(ntrain & 1));  // H1 block blk has left: H2 block blk may move in
         tmem_ld_wait();
         uint32_t m = 0;
         if (t >= 0) m = bias_relu32<true>(v, sb1 + c0);
@@ -329,18 +317,9 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       const float b2v = lane < 8 ? sw2[nout * 256 + (lane < nout ? lane : 0)] : 0.f;  // before the bundle is reloaded
       named_bar_sync(1, kEpiThreads);
       if (et == 0) IQLB_TS(it * 8 + 6);
-      if (et == 0) {
-        if (tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);  // every warp is done with b1 / W2 / b2
-        IQLB_TS(1536 + it * 8);
-        if (t >= 0) {
-          uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
-          for (int cb = 0; cb < 4; ++cb)
-            bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
-          bulk_commit();
-        }
-      }
-      if (et == 0) IQLB_TS(1536 + it * 8 + 1);
+      if (et == 0) mbar_arrive(bar(EPI1_DONE));  // H2 staged, b1 / W2 / b2 consumed: the store warp stores and reloads
       h1_store_pending = t >= 0;
+      if (t >= 0) ++ntrain;
       if (grp == 0) {
         float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
 #pragma unroll
@@ -355,11 +334,51 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
           }
         }
         if (et == 0) IQLB_TS(1536 + it * 8 + 2);
-        // the partial sums are read before any warp can overwrite them: the next write to `part` follows
-        // the next tile's named barriers, which this warp joins only after these loads
+        // the partial sums are read before any warp can overwrite them: the next write to `part` follows the
+        // next tile's layer-1 GEMM, which needs the H1 blocks that this warp writes only after these loads
       }
     }
-    if (h1_store_pending && et == 0) bulk_wait_read0();
+  } else {
+    // ------------------------------------------------------------------ store warp
+    if (lane == 0) {
+      if ((int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
+      int ntr = 0;
+      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t ph = (uint32_t)(it & 1);
+        int agent, s, half;
+        const uint8_t *wnet, *ximg;
+        const float* fnet;
+        tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
+        const int t = train_index(s);
+        mbar_wait(bar(EPI0_DONE), ph);
+        if (t >= 0) {  // H1: one commit group per 64-column block, released to epilogue 1 block by block
+          uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+          for (int cb = 0; cb < 4; ++cb) {
+            bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+            bulk_commit();
+          }
+          asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory"); mbar_arrive(bar(H1_OUT + 0));
+          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); mbar_arrive(bar(H1_OUT + 1));
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); mbar_arrive(bar(H1_OUT + 2));
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); mbar_arrive(bar(H1_OUT + 3));
+        }
+        mbar_wait(bar(EPI1_DONE), ph);
+        if (tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);
+        if (t >= 0) {
+          uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
+          for (int cb = 0; cb < 4; ++cb) {
+            bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
+            bulk_commit();
+          }
+          asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory"); mbar_arrive(bar(H2_OUT + 0));
+          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); mbar_arrive(bar(H2_OUT + 1));
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); mbar_arrive(bar(H2_OUT + 2));
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); mbar_arrive(bar(H2_OUT + 3));
+          ++ntr;
+        }
+      }
+      bulk_wait0();
+    }
   }
   tc_fence_before();
   __syncthreads();

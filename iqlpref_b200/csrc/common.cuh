@@ -22,7 +22,7 @@ inline int fail(int code, const char* fmt, const char* a = "", long long b = 0) 
   do {                                                                                      \
     cudaError_t e__ = (expr);                                                               \
     if (e__ != cudaSuccess) {                                                               \
-      snprintf(iqlb::g_err, sizeof(iqlb::g_err), "%s failed: %s (%s:%d)", #expr,            \
+      snprintf(iqlb::g_err, sizeof(iqlb::g_err), "%.300s failed: %s (%s:%d)", #expr,            \
                cudaGetErrorString(e__), __FILE__, __LINE__);                                \
       return IQLB_ERR_CUDA;                                                                 \
     }                                                                                       \

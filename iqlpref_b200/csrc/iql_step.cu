@@ -307,6 +307,9 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 // agent, with the Polyak target update (iql.py:127-129,613) fused for the Q segment.
 // HBM-bound: 28 B read + 16 B written per parameter (+8 B per Q parameter for the target).
 // ------------------------------------------------------------------------------------------
+#ifndef IQLB_ADAM_SLOTS
+#define IQLB_ADAM_SLOTS 1
+#endif
 __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __restrict__ params,
                                                           float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                           float* __restrict__ target, const float* __restrict__ grads,
@@ -319,12 +322,13 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
   const StepScalars sc = scal[agent];
   const bool hint = (shadow & 2) != 0;  // stream the optimizer state through L2 (evict_first), keep the images (evict_last)
   const uint64_t pol_s = l2_policy_evict_first(), pol_k = l2_policy_evict_last();
-  float4 p[2], m[2], v[2], g[2], tg[2];
-  int64_t e[2];
-  bool live[2], has_t[2];
+  constexpr int kS = IQLB_ADAM_SLOTS;  // 16-byte words per thread and array
+  float4 p[kS], m[kS], v[kS], g[kS], tg[kS];
+  int64_t e[kS];
+  bool live[kS], has_t[kS];
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {  // optimizer state: not written by the weight-gradient kernel (the PDL predecessor)
-    e[h] = ((int64_t)blockIdx.x * 512 + threadIdx.x + 256 * h) * 4;
+  for (int h = 0; h < kS; ++h) {  // optimizer state: not written by the weight-gradient kernel (the PDL predecessor)
+    e[h] = ((int64_t)blockIdx.x * (256 * kS) + threadIdx.x + 256 * h) * 4;
     live[h] = e[h] < L.Pstride;
     has_t[h] = e[h] < L.PQ;
     if (live[h]) {
@@ -345,7 +349,7 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
   pdl_wait();
   pdl_launch();
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {  // gradients of this step
+  for (int h = 0; h < kS; ++h) {  // gradients of this step
     if (!live[h]) continue;
     const int64_t g4 = (int64_t)agent * L.Pstride + e[h];
     if (shadow & 1) {  // bf16 path: gradients arrive in bf16
@@ -357,7 +361,7 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
     }
   }
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
+  for (int h = 0; h < kS; ++h) {
     if (!live[h]) continue;
     const float ss = e[h] < L.off_v ? sc.ss_q : (e[h] < L.off_a ? sc.ss_v : sc.ss_a);
     float* pp = &p[h].x; float* mp = &m[h].x; float* vp = &v[h].x; const float* gp = &g[h].x; float* tp = &tg[h].x;
@@ -542,7 +546,7 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
   if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
   static const bool l2hint = getenv("IQLB_L2HINT") && atoi(getenv("IQLB_L2HINT")) != 0;  // measured: no gain on B200
-  IQLB_CUDA(launch_pdl(adam_polyak_kernel, dim3((unsigned)((L.Pstride + 2047) / 2048), n), dim3(256), 0, st,
+  IQLB_CUDA(launch_pdl(adam_polyak_kernel, dim3((unsigned)((L.Pstride + 1024 * IQLB_ADAM_SLOTS - 1) / (1024 * IQLB_ADAM_SLOTS)), n), dim3(256), 0, st,
                        bf && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
                        (bf ? 1 : 0) | (l2hint ? 2 : 0), a0));

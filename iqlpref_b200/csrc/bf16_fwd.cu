@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
 
   auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
                        const float*& fnet) {
+    if (P.rev) tile = n_tiles - 1 - tile;
     const int nh = L.B / 128;
     half = tile % nh;
     const int r = tile / nh;
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       int c = 0;
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
-        const int s = (tile / (L.B / 128)) % kStreams;
+        const int s = ((P.rev ? n_tiles - 1 - tile : tile) / (L.B / 128)) % kStreams;
         const int in = L.in_dim(s);
         {
           const int slot = c % kSlots, use = c / kSlots;

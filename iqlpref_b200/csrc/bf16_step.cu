@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(288, 1) bf16_bwd_data_kernel(BfParams P, const
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int half = blockIdx.x, t = blockIdx.y, agent = P.agent0 + blockIdx.z;
+  const int half = blockIdx.x, t = blockIdx.y, agent = P.agent0 + (P.rev ? (int)(gridDim.z - 1 - blockIdx.z) : (int)blockIdx.z);
   const int s = train_stream(t), net = net_of_stream(s);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
@@ -545,7 +545,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
                                                                  const StepScalars* __restrict__ scal) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int ot = blockIdx.x, t = blockIdx.y, agent = P.agent0 + blockIdx.z;
+  const int ot = blockIdx.x, t = blockIdx.y, agent = P.agent0 + (P.rev ? (int)(gridDim.z - 1 - blockIdx.z) : (int)blockIdx.z);
   const int s = train_stream(t);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
@@ -921,6 +921,7 @@ int bf16_create(iqlb_agents* h) {
   if (!rc) rc = alloc((void**)&P.mask2, N * kTrain * L.B * (L.H / 32) * 4);
   if (!rc) rc = alloc((void**)&P.gradh, N * L.Pstride * 2);
   P.dbg = nullptr;
+  P.rev = 0;
   auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
   P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
@@ -990,6 +991,7 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   const int N = n;
   BfParams P = st->P;
   P.agent0 = a0;
+  P.rev = h->zig == 1;
   int rc;
   if (st->dirty) {
     if ((rc = bf16_refresh(h, stream))) return rc;
@@ -1018,10 +1020,12 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   const int N = n;
   BfParams P = st->P;
   P.agent0 = a0;
+  P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
   IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(288), bwd_data_smem(), stream,
                        pdl_enabled(8) && !h->prof, P,
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");
+  if (h->zig >= 0) P.rev ^= 1;
   IQLB_CUDA(launch_pdl(h->fused_adam ? bf16_bwd_weight_kernel<true> : bf16_bwd_weight_kernel<false>, dim3(L.H / 128, kTrain, N),
                        dim3(256), bwd_weight_smem(L.B), stream, pdl_enabled(16) && !h->prof, P, h->grads, h->params, h->exp_avg, h->exp_avg_sq,
                        h->target, (const StepScalars*)h->scal));

@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
   // A CTA owns 2048 consecutive parameters of one agent; thread t handles the 16-byte words t and t + 256 of
   // that span, so every warp access is 512 contiguous bytes per array.  Network segments start on multiples of
   // 8 floats: a word never straddles two optimizers, and inside W1 it is half of a 16-byte chunk of the image.
-  const int agent = agent0 + blockIdx.y;
+  const int agent = agent0 + ((shadow & 4) ? (int)(gridDim.y - 1 - blockIdx.y) : (int)blockIdx.y);
   const StepScalars sc = scal[agent];
   const bool hint = (shadow & 2) != 0;  // stream the optimizer state through L2 (evict_first), keep the images (evict_last)
   const uint64_t pol_s = l2_policy_evict_first(), pol_k = l2_policy_evict_last();
@@ -549,7 +549,7 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
   IQLB_CUDA(launch_pdl(adam_polyak_kernel, dim3((unsigned)((L.Pstride + 1024 * IQLB_ADAM_SLOTS - 1) / (1024 * IQLB_ADAM_SLOTS)), n), dim3(256), 0, st,
                        bf && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
-                       (bf ? 1 : 0) | (l2hint ? 2 : 0), a0));
+                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0));
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
 }
@@ -567,6 +567,7 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
     if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
     if ((rc = step_adam(h, 0, N, pf, st))) return rc;
     pf.done();
+    if (h->zig >= 0 && h->desc.precision == 1) h->zig ^= 1;
     return IQLB_OK;
   }
   const int per = (N + G - 1) / G;
@@ -637,6 +638,7 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   if (!rc) rc = alloc((float**)&h->scal, N * (int64_t)(sizeof(StepScalars) / sizeof(float)));
   if (!rc) rc = build_tasks(h);
   if (!rc && d->precision == 1) rc = bf16_create(h);
+  h->zig = (getenv("IQLB_ZIGZAG") && atoi(getenv("IQLB_ZIGZAG")) == 0) ? -1 : 0;
   if (!rc && d->precision == 1) {
     const char* env = getenv("IQLB_GROUPS");
     int G = env ? atoi(env) : 1;  // measured on B200: splitting 64 agents into groups is slower

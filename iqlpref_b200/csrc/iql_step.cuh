@@ -89,6 +89,7 @@ struct BfParams {
   Layout L;
   int KXB;                // 64-column blocks of the input images (ceil((S+A)/64))
   int agent0;             // first agent of this launch (agent groups are pipelined, iql_step.cu)
+  int rev;                // 1: this launch walks its agents from the last to the first (L2 zig-zag, iql_step.cu)
   int64_t w0_bytes;       // W0 image bytes  = KXB * H * 128
   int64_t net_bytes;      // W0 + W1 images of one network
   int64_t agent_w_bytes;  // 6 networks: Q1 Q2 V actor Qt1 Qt2
@@ -187,6 +188,9 @@ struct iqlb_agents {
   float* stage[2] = {};
   float* host_loss[2] = {};  // pinned
   long long pipe_k = 0;
+  // L2 zig-zag: consecutive kernels walk the agents in opposite directions, so a consumer starts with what its
+  // producer wrote last (still in L2); the direction flips every step (IQLB_ZIGZAG=0 turns it off)
+  int zig = 0;
 };
 
 namespace iqlb {

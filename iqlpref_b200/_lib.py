@@ -50,6 +50,7 @@ _SIGNATURES = {
     "iqlb_agents_profile_collect": ([_P], C.c_int),
     "iqlb_agents_profile_read": ([_P, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_int32)], C.c_int),
     "iqlb_agents_debug_option": ([_P, C.c_int32, C.c_int32], C.c_int),
+    "iqlb_agents_set_actor_dropout": ([_P, C.c_float], C.c_int),
     "iqlb_agents_debug_copy": ([_P, C.c_int32, _P, C.POINTER(C.c_int64), _P], C.c_int),
     "iqlb_polyak": ([_P, _P, C.c_int64, C.c_float, _P], C.c_int),
     "iqlb_relabel_mlp": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.c_int32,

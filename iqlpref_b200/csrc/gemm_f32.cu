@@ -121,10 +121,13 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
     __syncthreads();
   }
 
+  uint64_t drop_seed = 0, drop_ctr = 0;
+  if (MODE == GEMM_FWD && t.drop_thresh != 0) { drop_seed = *t.drop_rng; drop_ctr = (uint64_t)(*t.drop_it) * 4ull; }
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int m = m0 + (i < 4 ? ty * 4 + i : BM / 2 + ty * 4 + (i - 4));
     if (m >= t.M) continue;
+    uint32_t dr[4] = {0, 0, 0, 0};
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
       int n;
@@ -135,8 +138,14 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
       if (MODE == GEMM_FWD) {
         v += __ldg(t.bias + n);
         v = v > 0.f ? v : 0.f;
+        if (t.drop_thresh != 0) {
+          const int64_t e = (int64_t)m * t.N + n;
+          if ((j & 3) == 0 || (n & 3) == 0 || TN != 8)  // columns come in aligned groups of four: one Philox call per group
+            philox4(drop_seed, ((uint64_t)(t.drop_layer + 1) << 32) | (uint64_t)(e >> 2), drop_ctr, dr);
+          v = dr[n & 3] >= t.drop_thresh ? v * t.drop_scale : 0.f;
+        }
       } else if (MODE == GEMM_BWD_DATA) {
-        v = (__ldg(t.mask + (int64_t)m * t.ldc + n) > 0.f) ? v : 0.f;
+        v = (__ldg(t.mask + (int64_t)m * t.ldc + n) > 0.f) ? v * t.scale : 0.f;
       } else if (MODE == GEMM_FWD_KN) {
         v = apply_act(t.act, fmaf(t.scale, v, __ldg(t.bias + n)));
       } else if (MODE == GEMM_LINEAR) {  // nn.Linear: act(A W^T + bias) (+ residual, carried in t.mask)

@@ -65,7 +65,8 @@ __device__ __forceinline__ double cosine_next(double lr, double base_lr, long lo
   return (1.0 + cos(kPi * (double)epoch / (double)t_max)) / (1.0 + cos(kPi * (double)(epoch - 1) / (double)t_max)) * lr;
 }
 
-__global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __restrict__ params, const float* __restrict__ hparams,
+template <int kMaxThreads>
+__global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float* __restrict__ params, const float* __restrict__ hparams,
                             const float* __restrict__ batch, const float* __restrict__ head_out,
                             float* __restrict__ d_out, float* __restrict__ grads, float* __restrict__ losses,
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
@@ -121,19 +122,31 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
 
   // every global load of this thread is issued before the first use; what the forward kernel (the PDL
   // predecessor) wrote - head_out - is loaded after the wait, batch rows / log_std / bookkeeping before it
-  const float rew = row[2 * L.S + L.A], done = row[2 * L.S + L.A + 1];
+  const float rew = __ldg(row + 2 * L.S + L.A), done = __ldg(row + 2 * L.S + L.A + 1);
   float mu[kOutMax], act[kOutMax], lsr[kOutMax];
+  // (unconditional loads on clamped indices, through volatile asm: the compiler would otherwise sink each
+  //  predicated load to its first use inside the action loop and pay one memory latency per action)
+  auto ldg = [](const float* p) { float x; asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(x) : "l"(p)); return x; };
+  auto ldv = [](const float* p) { float x; asm volatile("ld.global.f32 %0, [%1];" : "=f"(x) : "l"(p)); return x; };
+  const int amax = L.A - 1;
 #pragma unroll
   for (int a = 0; a < kOutMax; ++a) {
-    act[a] = a < L.A ? row[L.S + a] : 0.f;
-    lsr[a] = (a < L.A && !L.deterministic) ? log_std[a] : 0.f;
+    if (a < 8 || a < L.A) {  // uniform; the first eight always (antmaze / halfcheetah never branch)
+      act[a] = ldg(row + L.S + (a < amax ? a : amax));
+      lsr[a] = L.deterministic ? 0.f : ldg(log_std + (a < amax ? a : amax));
+    } else {
+      act[a] = 0.f; lsr[a] = 0.f;
+    }
   }
   pdl_wait();
   pdl_launch();
-  const float nv = ho[0 * L.B + bb], v = ho[1 * L.B + bb], tq1 = ho[2 * L.B + bb], tq2 = ho[3 * L.B + bb];
-  const float q1 = ho[4 * L.B + bb], q2 = ho[5 * L.B + bb];
+  const float nv = ldv(ho + 0 * L.B + bb), v = ldv(ho + 1 * L.B + bb), tq1 = ldv(ho + 2 * L.B + bb), tq2 = ldv(ho + 3 * L.B + bb);
+  const float q1 = ldv(ho + 4 * L.B + bb), q2 = ldv(ho + 5 * L.B + bb);
 #pragma unroll
-  for (int a = 0; a < kOutMax; ++a) mu[a] = a < L.A ? ho[(int64_t)(6 + a) * L.B + bb] : 0.f;
+  for (int a = 0; a < kOutMax; ++a) {
+    if (a < 8 || a < L.A) mu[a] = ldv(ho + (int64_t)(6 + (a < amax ? a : amax)) * L.B + bb);
+    else mu[a] = 0.f;
+  }
 
   const float tq = fminf(tq1, tq2);
   const float adv = tq - v;
@@ -226,13 +239,13 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
     float* g = grads + (int64_t)agent * L.Pstride;
     if (j == 0) {
       const float value_loss = tot * invB;
-      losses[agent * 3 + 0] = value_loss; loss_sum[agent * 3 + 0] += value_loss;
+      losses[agent * 3 + 0] = value_loss; atomicAdd(loss_sum + agent * 3 + 0, value_loss);  // one writer: a fire-and-forget add
     } else if (j == 1) {
       const float q_loss = tot * invB * 0.5f;
-      losses[agent * 3 + 1] = q_loss; loss_sum[agent * 3 + 1] += q_loss;
+      losses[agent * 3 + 1] = q_loss; atomicAdd(loss_sum + agent * 3 + 1, q_loss);  // one writer: a fire-and-forget add
     } else if (j == 2) {
       const float actor_loss = tot * invB;
-      losses[agent * 3 + 2] = actor_loss; loss_sum[agent * 3 + 2] += actor_loss;
+      losses[agent * 3 + 2] = actor_loss; atomicAdd(loss_sum + agent * 3 + 2, actor_loss);  // one writer: a fire-and-forget add
     } else {
       int64_t e = -1;
       if (j < 6) { if (bf) e = (j == 3 ? L.off_v + L.b2(L.S, 1) : (j == 4 ? L.off_q1 : L.off_q2) + L.b2(L.Dq, 1)); }
@@ -255,7 +268,7 @@ __global__ void __launch_bounds__(1024) loss_kernel(Layout L, const float* __res
 __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __restrict__ params,
                                                        const float* __restrict__ H2,
                                                        const float* __restrict__ d_out, float* __restrict__ dH2,
-                                                       float* __restrict__ grads) {
+                                                       float* __restrict__ grads, float actor_drop_scale) {
   const int agent = blockIdx.y, t = blockIdx.x, s = train_stream(t);
   const int in = L.in_dim(s), nout = L.out_dim(s);
   const int64_t noff = L.net_off(s);
@@ -288,7 +301,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
             g = fmaf(d, w2[oo], g);
           }
         }
-        dh2[(int64_t)b * L.H + j] = last ? (h > 0.f ? g : 0.f) : g;
+        dh2[(int64_t)b * L.H + j] = last ? (h > 0.f ? (t == 3 ? g * actor_drop_scale : g) : 0.f) : g;
       }
 #pragma unroll
       for (int oo = 0; oo < 8; ++oo)
@@ -428,6 +441,11 @@ __global__ void bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ src, float*
 static int build_tasks(iqlb_agents* h) {
   const Layout& L = h->L;
   const int N = h->desc.n_agents;
+  cudaFree(h->t_fwd0); cudaFree(h->t_fwd1); cudaFree(h->t_bw1); cudaFree(h->t_bd1); cudaFree(h->t_bw0);
+  h->t_fwd0 = h->t_fwd1 = h->t_bw1 = h->t_bd1 = h->t_bw0 = nullptr;
+  const bool drop = h->drop_p > 0.f;
+  const uint32_t drop_thresh = drop ? (uint32_t)((double)h->drop_p * 4294967296.0) : 0u;
+  const float drop_scale = drop ? 1.0f / (1.0f - h->drop_p) : 1.0f;
   std::vector<GemmTask> f0((size_t)N * kStreams), f1((size_t)N * kStreams), bw1((size_t)N * kTrain),
       bd1((size_t)N * kTrain), bw0((size_t)N * kTrain);
   for (int a = 0; a < N; ++a) {
@@ -444,10 +462,12 @@ static int build_tasks(iqlb_agents* h) {
       t.A = X + (s == 0 ? L.S + L.A : 0); t.lda = L.R;
       t.Bm = net + L.w0(); t.ldb = in; t.bias = net + L.b0(in);
       t.C = h1; t.ldc = L.H; t.M = L.B; t.N = L.H; t.K = in;
+      if (drop && s == 6) { t.drop_thresh = drop_thresh; t.drop_scale = drop_scale; t.drop_layer = 0; t.drop_rng = h->rng + 2 * a; t.drop_it = h->it + a; }
       f0[(size_t)a * kStreams + s] = t;
       GemmTask u{};
       u.A = h1; u.lda = L.H; u.Bm = net + L.w1(in); u.ldb = L.H; u.bias = net + L.b1(in);
       u.C = h2; u.ldc = L.H; u.M = L.B; u.N = L.H; u.K = L.H;
+      if (drop && s == 6) { u.drop_thresh = drop_thresh; u.drop_scale = drop_scale; u.drop_layer = 1; u.drop_rng = h->rng + 2 * a; u.drop_it = h->it + a; }
       f1[(size_t)a * kStreams + s] = u;
     }
     for (int tt = 0; tt < kTrain; ++tt) {
@@ -464,6 +484,7 @@ static int build_tasks(iqlb_agents* h) {
       GemmTask d1{};  // dH1 = (dH2 W1) * relu'(H1)
       d1.A = dh2; d1.lda = L.H; d1.Bm = net + L.w1(in); d1.ldb = L.H; d1.C = dh1; d1.ldc = L.H;
       d1.mask = h1; d1.M = L.B; d1.N = L.H; d1.K = L.H;
+      d1.scale = (drop && tt == 3) ? drop_scale : 1.0f;
       bd1[(size_t)a * kTrain + tt] = d1;
       GemmTask w0{};  // dW0[H,in] = dH1^T X ; db0
       w0.A = dh1; w0.lda = L.H; w0.Bm = X; w0.ldb = L.R; w0.C = gnet + L.w0(); w0.ldc = in;
@@ -515,7 +536,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   }
   int lb = (L.B + 31) / 32 * 32;
   if (lb + 32 <= 1024) lb += 32;  // bookkeeping warp
-  IQLB_CUDA(launch_pdl(loss_kernel, dim3(n), dim3(lb), 0, st, bf && pdl_enabled(4) && !h->prof, L, (const float*)h->params,
+  IQLB_CUDA(launch_pdl(lb <= 320 ? loss_kernel<320> : loss_kernel<1024>, dim3(n), dim3(lb), 0, st, bf && pdl_enabled(4) && !h->prof, L, (const float*)h->params,
                        h->hparams, (const float*)h->batch, (const float*)h->head_out, h->d_out, h->grads, h->losses,
                        h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0, bf ? bp->dz : (uint8_t*)nullptr,
                        bf ? bp->z_bytes : (int64_t)0, a0, bf ? bp->dbg : (unsigned long long*)nullptr,
@@ -527,7 +548,8 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
     if ((rc = bf16_step_gemms_bwd(h, a0, n, pf, st))) return rc;
   } else {
     const int N = h->desc.n_agents;
-    head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads);
+    head_bwd_kernel<<<dim3(kTrain, N), 256, 0, st>>>(L, h->params, h->H2, h->d_out, h->dH2, h->grads,
+                                                     h->drop_p > 0.f ? 1.0f / (1.0f - h->drop_p) : 1.0f);
     IQLB_LAUNCH_CHECK();
     pf.mark("head_bwd");
     if ((rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->t_bw1, N * kTrain, L.H, L.H, false, st))) return rc;
@@ -769,6 +791,14 @@ extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   if (h->desc.precision == 1) return bf16_refresh(h, (cudaStream_t)stream);
   return IQLB_OK;
+}
+
+extern "C" int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  IQLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
+  IQLB_REQUIRE(h->desc.precision == 0 || p == 0.f, "actor dropout runs on the fp32 path (precision 0)");
+  h->drop_p = p;
+  return build_tasks(h);
 }
 
 extern "C" int iqlb_agents_debug_option(iqlb_agents* h, int32_t option, int32_t value) {

@@ -69,8 +69,16 @@ struct GemmTask {
   const float* mask;    // BWD_DATA: relu mask source (same shape/ld as C)
   float* bias_grad;     // BWD_WEIGHT: column sums of A
   int M, N, K, lda, ldb, ldc;
-  float scale;          // FWD_KN: act(scale * acc + bias)
+  float scale;          // FWD_KN: act(scale * acc + bias); BWD_DATA: gradient scale (1, or 1/(1-p) through a dropout)
   int act;              // FWD_KN: IQLB_ACT_* id
+  // FWD with actor dropout (iql.py:437-438, nn.Dropout after every hidden ReLU of the actor): element (m, n) is kept
+  // when word (n & 3) of Philox4x32-10(key = rng seed of the agent, subsequence = (layer+1) << 32 | (m*N + n) / 4,
+  // counter = Adam step of the agent) is >= drop_thresh; kept values are scaled by drop_scale = 1/(1-p)
+  uint32_t drop_thresh;  // 0: no dropout
+  float drop_scale;
+  int drop_layer;
+  const uint64_t* drop_rng;  // &rng[2 * agent] (seed)
+  const int64_t* drop_it;    // &it[agent]
 };
 
 enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3, GEMM_LINEAR = 4 };
@@ -166,6 +174,7 @@ struct iqlb_agents {
   iqlb::StepScalars* scal = nullptr;
   iqlb::GemmTask *t_fwd0 = nullptr, *t_fwd1 = nullptr, *t_bw1 = nullptr, *t_bd1 = nullptr, *t_bw0 = nullptr;
   void* bf16_state = nullptr;  // precision==1 extension (tcgen05 path)
+  float drop_p = 0.f;          // actor dropout probability (precision 0 only)
   bool fused_adam = false;     // precision==1: Adam/Polyak inside the weight-gradient kernel (debug option 0)
   // per-kernel CUDA-event timing (iqlb_agents_profile): ev[i], ev[i+1] bracket launch i of a step
   static constexpr int kMaxProf = 24;

@@ -14,6 +14,7 @@ the arithmetic runs in libiqlb.so (hand-written sm_100a CUDA, include/iqlb.h).
 There is no CPU path: constructing any of the compute classes without CUDA + libiqlb.so raises.
 """
 import copy
+import warnings
 import ctypes as C
 import math
 import os
@@ -347,7 +348,8 @@ class BatchedIQL:
 
     def __init__(self, state_dim: int, action_dim: int, n_agents: int, hidden_dim: int = 256, batch_size: int = 256,
                  deterministic: bool = False, device: str = "cuda", precision: str = "fp32",
-                 hparams: Optional[Sequence[Dict[str, float]]] = None, seeds: Optional[Sequence[int]] = None):
+                 hparams: Optional[Sequence[Dict[str, float]]] = None, seeds: Optional[Sequence[int]] = None,
+                 actor_dropout: Optional[float] = None):
         self.device = _require_cuda(device)
         self.lib = _lib.load()
         self.S, self.A, self.H, self.B, self.N = state_dim, action_dim, hidden_dim, batch_size, n_agents
@@ -392,6 +394,12 @@ class BatchedIQL:
         self._h = handle
         self._replay = None
         self._layout = self._make_layout()
+        self.actor_dropout = float(actor_dropout or 0.0)
+        if self.actor_dropout > 0.0:
+            if self.precision != 0:
+                raise NotImplementedError("actor_dropout runs on precision='fp32' (the tcgen05 path has no dropout yet)")
+            _lib.check(self.lib.iqlb_agents_set_actor_dropout(self._h, C.c_float(self.actor_dropout)),
+                       "iqlb_agents_set_actor_dropout")
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -439,8 +447,9 @@ class BatchedIQL:
         `bind`, re-point the module parameters at the packed storage so `module.state_dict()`
         always reflects the trained values."""
         for m in list(actor.modules()):
-            if isinstance(m, nn.Dropout) and m.p > 0:
-                raise NotImplementedError("actor_dropout is not supported by the B200 step yet")
+            if isinstance(m, nn.Dropout) and m.p > 0 and abs(m.p - self.actor_dropout) > 1e-12:
+                raise ValueError(f"the actor uses Dropout({m.p}) but the engine was built with actor_dropout="
+                                 f"{self.actor_dropout}: pass actor_dropout={m.p} (precision='fp32')")
         with torch.no_grad():
             for key, prm in self._module_tensors(qf, vf, actor).items():
                 dst = self.view(self.params, agent, key)
@@ -565,8 +574,13 @@ class ImplicitQLearning:
     def _build(self, batch_size: int):
         s, a, h = self._dims
         det = not hasattr(self.actor, "log_std")
+        drop = max([m.p for m in self.actor.modules() if isinstance(m, nn.Dropout)] or [0.0])
+        precision = self._precision
+        if drop > 0 and precision != "fp32":
+            warnings.warn("actor dropout runs on the fp32 path: precision='fp32' is used for this trainer", RuntimeWarning)
+            precision = "fp32"
         eng = BatchedIQL(s, a, 1, hidden_dim=h, batch_size=batch_size, deterministic=det, device=self.device,
-                         precision=self._precision, hparams=[self._hp])
+                         precision=precision, hparams=[self._hp], actor_dropout=drop or None)
         eng.adopt(0, self.qf, self.vf, self.actor, bind=True)
         # q_target parameters become views of the packed target buffer
         with torch.no_grad():

@@ -257,3 +257,67 @@ def test_host_feed_pipelined_matches_blocking():
     for k in range(K):
         assert torch.equal(got[k + 1], want[k]), k
     assert torch.equal(engs[0].params, engs[1].params)
+
+
+def _dropout_masks(seed: int, step: int, B: int, H: int, p: float):
+    """The keep masks iqlb_agents_set_actor_dropout documents (include/iqlb.h), rebuilt with the numpy Philox."""
+    import torch
+    from oracle.philox_oracle import philox4x32_10
+    thresh = np.uint64(int(np.float64(np.float32(p)) * 4294967296.0))
+    masks = []
+    for layer in range(2):
+        e4 = np.arange(B * H // 4, dtype=np.uint64)
+        ctr = np.stack([np.full_like(e4, step & 0xFFFFFFFF), np.full_like(e4, step >> 32), e4 & np.uint64(0xFFFFFFFF),
+                        np.full_like(e4, layer + 1)], axis=-1)
+        key = np.empty((e4.size, 2), dtype=np.uint64)
+        key[:, 0], key[:, 1] = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+        r = philox4x32_10(ctr, key).astype(np.uint64).reshape(B, H)
+        keep = (r >= thresh).astype(np.float32) / (1.0 - np.float32(p))
+        masks.append(torch.from_numpy(keep.astype(np.float32)))
+    return masks
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("det", [False, True])
+def test_actor_dropout_matches_oracle_with_injected_masks(det):
+    """pen / adroit configs (actor_dropout 0.1, iql.py:437-438): the CUDA step with its documented Philox masks equals
+    the oracle fed the same masks (the reference's own mask stream cannot be mirrored)."""
+    import torch
+    from iqlpref_b200 import iql as biql
+    from oracle.iql_oracle import IQLOracle, OracleHParams, nets_from_reference_modules
+    S, A, H, B, p, seed = 45, 24, 64, 128, 0.1, 1234
+    hp = dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.8, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4, max_steps=1000)
+    torch.manual_seed(3)
+    qf, vf = biql.TwinQ(S, A, H), biql.ValueFunction(S, H)
+    actor = (biql.DeterministicPolicy if det else biql.GaussianPolicy)(S, A, 1.0, H, dropout=p)
+    orc = IQLOracle(*nets_from_reference_modules(qf, vf, actor), OracleHParams(deterministic=det, **hp), mode="fp32")
+    eng = biql.BatchedIQL(S, A, 1, hidden_dim=H, batch_size=B, deterministic=det, device="cuda:0", hparams=[hp], seeds=[seed],
+                          actor_dropout=p)
+    eng.adopt(0, qf, vf, actor, bind=False)
+    rng = np.random.default_rng(5)
+    kept = []
+    for step in range(4):
+        obs = torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32)
+        act = torch.tensor(rng.uniform(-1, 1, (B, A)), dtype=torch.float32)
+        rew = torch.tensor(rng.standard_normal(B), dtype=torch.float32)
+        nobs = torch.tensor(rng.standard_normal((B, S)), dtype=torch.float32)
+        done = torch.tensor((rng.uniform(size=B) < 0.1).astype(np.float32))
+        masks = _dropout_masks(seed, step, B, H, p)
+        kept.append(float((masks[0] > 0).float().mean()))
+        want = orc.step(obs, act, rew, nobs, done, dropout_masks=masks)
+        eng.train(biql.pack_rows(obs, act, rew, nobs, done, eng.R).cuda().unsqueeze(0))
+        got = eng.losses[0].tolist()
+        ref = [want["value_loss"], want["q_loss"], want["actor_loss"]]
+        assert np.allclose(got, ref, rtol=1e-3, atol=1e-6), (step, got, ref)
+    assert 0.85 < np.mean(kept) < 0.95
+    exp, ref = eng.export(0), orc.export()
+    for k in ("actor.w0", "actor.w1", "actor.w2", "actor.b0"):
+        scale = np.abs(ref[k]).max()
+        assert np.abs(exp[k] - ref[k]).max() <= 1e-3 * scale, k
+
+
+@pytest.mark.gpu
+def test_actor_dropout_needs_fp32_path():
+    from iqlpref_b200 import iql as biql
+    with pytest.raises(NotImplementedError):
+        biql.BatchedIQL(29, 8, 1, batch_size=256, device="cuda:0", precision="bf16", actor_dropout=0.1)

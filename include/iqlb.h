@@ -189,6 +189,19 @@ int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in,
                      int32_t activation, int32_t n_tail, float* out, float* preds_out, uint8_t* sel_out,
                      void* stream);
 
+/* Same with an explicit arithmetic mode for the hidden layers:
+ *   IQLB_RELABEL_FP32       fp32 FFMA GEMMs (any shape; the 1e-6 parity mode)
+ *   IQLB_RELABEL_SPLIT_BF16 tcgen05 tensor cores, every product as x_hi*W_hi + x_lo*W_hi + x_hi*W_lo with fp32
+ *                           accumulation (~1e-5 relative per layer); d_in <= 128, equal hidden widths of 64 or
+ *                           128, depth <= 3 - IQLB_ERR_UNSUPPORTED otherwise
+ *   IQLB_RELABEL_AUTO       split-bf16 where it applies, fp32 elsewhere (what iqlb_relabel_mlp does)
+ * The member selection (CVaR tail) is exact given the predictions in every mode. */
+enum { IQLB_RELABEL_AUTO = -1, IQLB_RELABEL_FP32 = 0, IQLB_RELABEL_SPLIT_BF16 = 1 };
+int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in,
+                       const float* weights, int32_t n_members, const int32_t* host_widths, int32_t depth,
+                       int32_t activation, int32_t n_tail, int32_t precision, float* out, float* preds_out,
+                       uint8_t* sel_out, void* stream);
+
 /* Preference transformer (optbnn/bnn/nets/pref_trans.py:230-325) evaluated on the windows that
  * qlearning_dataset_pt builds (iql.py:1264-1292) and reduced to value[:,0,-1,0].
  *   obs[n_data][S], act[n_data][A]      : the dataset

@@ -38,6 +38,24 @@ inline int fail(int code, const char* fmt, const char* a = "", long long b = 0) 
     }                                                                                       \
   } while (0)
 
+// RewardMLP activations (optbnn/bnn/nets/mlp.py:45-48), ids of include/iqlb.h
+#ifdef __CUDACC__
+__device__ __forceinline__ float apply_act(int act, float x) {
+  switch (act) {
+    case IQLB_ACT_RELU: return x > 0.f ? x : 0.f;
+    case IQLB_ACT_TANH: return tanhf(x);
+    case IQLB_ACT_COS: return cosf(x);
+    case IQLB_ACT_SIN: return sinf(x);
+    case IQLB_ACT_LINEAR: return x;
+    case IQLB_ACT_RBF: return expf(-x * x);
+    case IQLB_ACT_SWISH: return x * (1.0f / (1.0f + expf(-x)));
+    case IQLB_ACT_SOFTPLUS: return x > 20.f ? x : log1pf(expf(x));
+    case IQLB_ACT_LEAKY_RELU: return x > 0.f ? x : 0.01f * x;
+    default: return x;
+  }
+}
+#endif
+
 // ---- Philox4x32-10 exactly as cuRAND's curand_Philox4x32_10 (curand_philox4x32_x.h) ----------
 __host__ __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
 #ifdef __CUDA_ARCH__

@@ -9,21 +9,6 @@
 
 namespace iqlb {
 
-__device__ __forceinline__ float apply_act(int act, float x) {
-  switch (act) {
-    case IQLB_ACT_RELU: return x > 0.f ? x : 0.f;
-    case IQLB_ACT_TANH: return tanhf(x);
-    case IQLB_ACT_COS: return cosf(x);
-    case IQLB_ACT_SIN: return sinf(x);
-    case IQLB_ACT_LINEAR: return x;
-    case IQLB_ACT_RBF: return expf(-x * x);
-    case IQLB_ACT_SWISH: return x * (1.0f / (1.0f + expf(-x)));
-    case IQLB_ACT_SOFTPLUS: return x > 20.f ? x : log1pf(expf(x));
-    case IQLB_ACT_LEAKY_RELU: return x > 0.f ? x : 0.01f * x;
-    default: return x;
-  }
-}
-
 constexpr int BM = 128;
 constexpr int BK = 8;
 constexpr int TM = 8;

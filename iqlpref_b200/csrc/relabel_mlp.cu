@@ -10,6 +10,13 @@
 
 namespace iqlb {
 
+struct RelabelTc;  // relabel_mlp_tc.cu
+bool relabel_mlp_tc_supported(int d_in, const int32_t* widths, int depth);
+int relabel_tc_begin(RelabelTc** ctx, int ldx, int d_in, const float* weights, int S, const int32_t* widths, int depth,
+                     int activation, cudaStream_t st);
+int relabel_tc_forward(RelabelTc* c, const float* x, int64_t rows, float* preds, int64_t pred_stride, cudaStream_t st);
+void relabel_tc_end(RelabelTc* c, cudaStream_t st);
+
 // preds[s, i] = scale * H[s, i, :] . Wout[s, :] + bout[s]     (one warp per (row, member))
 __global__ void __launch_bounds__(256) mlp_out_kernel(const float* __restrict__ Hbuf, int64_t h_member_stride, int ldh,
                                                       int width, const float* __restrict__ weights,
@@ -78,17 +85,64 @@ __global__ void __launch_bounds__(256) cvar_select_kernel(const float* __restric
 
 using namespace iqlb;
 
-extern "C" int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in, const float* weights,
-                                int32_t n_members, const int32_t* host_widths, int32_t depth, int32_t activation,
-                                int32_t n_tail, float* out, float* preds_out, uint8_t* sel_out, void* stream) {
+// Tensor-core path (relabel_mlp_tc.cu): member predictions by split-bf16 tcgen05 MMAs, then the same selection.
+static int relabel_mlp_tensor(const float* x, int64_t n_rows, int ldx, int d_in, const float* weights, int S,
+                              const int32_t* widths, int depth, int activation, int n_tail, float* out,
+                              float* preds_out, uint8_t* sel_out, cudaStream_t st) {
+  RelabelTc* ctx = nullptr;
+  int rc = relabel_tc_begin(&ctx, ldx, d_in, weights, S, widths, depth, activation, st);
+  if (rc) return rc;
+  const bool direct = S == 1 && !sel_out && !preds_out;  // a single model: its prediction is the result
+  int64_t chunk = n_rows < (1ll << 30) ? n_rows : (1ll << 30);
+  float* scratch = nullptr;
+  if (!direct && !preds_out) {
+    int64_t c = (int64_t)(512ll << 20) / ((int64_t)S * (int64_t)sizeof(float));
+    c = c / 256 * 256;
+    if (c < 256) c = 256;
+    if (c < chunk) chunk = c;
+    cudaError_t e = cudaMallocAsync((void**)&scratch, (size_t)S * (size_t)chunk * sizeof(float), st);
+    if (e != cudaSuccess) {
+      relabel_tc_end(ctx, st);
+      return fail(IQLB_ERR_NOMEM, "relabel scratch: %s", cudaGetErrorString(e));
+    }
+  }
+  for (int64_t r0 = 0; r0 < n_rows && rc == IQLB_OK; r0 += chunk) {
+    const int64_t rows = n_rows - r0 < chunk ? n_rows - r0 : chunk;
+    float* preds = preds_out ? preds_out + r0 : (direct ? out + r0 : scratch);
+    const int64_t pstride = (preds_out || direct) ? n_rows : chunk;
+    rc = relabel_tc_forward(ctx, x + r0 * ldx, rows, preds, pstride, st);
+    if (rc == IQLB_OK && !direct) {
+      cvar_select_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(preds, pstride, S, n_tail, (int)rows, out + r0,
+                                                                        sel_out ? sel_out + r0 : nullptr, n_rows);
+      if (cudaGetLastError() != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cvar_select_kernel launch failed%s", "");
+    }
+  }
+  if (scratch) cudaFreeAsync(scratch, st);
+  relabel_tc_end(ctx, st);
+  return rc;
+}
+
+extern "C" int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in, const float* weights,
+                                  int32_t n_members, const int32_t* host_widths, int32_t depth, int32_t activation,
+                                  int32_t n_tail, int32_t precision, float* out, float* preds_out, uint8_t* sel_out,
+                                  void* stream) {
   IQLB_REQUIRE(x && weights && host_widths && out, "null pointer");
   IQLB_REQUIRE(n_rows >= 0 && d_in > 0 && ldx >= d_in, "row shape");
   IQLB_REQUIRE(n_members > 0 && depth > 0 && depth <= 16, "ensemble shape");
   IQLB_REQUIRE(n_tail >= 1 && n_tail <= n_members, "n_tail must be in [1, S]");
   IQLB_REQUIRE(activation >= IQLB_ACT_RELU && activation <= IQLB_ACT_LEAKY_RELU, "activation id");
+  IQLB_REQUIRE(precision >= IQLB_RELABEL_AUTO && precision <= IQLB_RELABEL_SPLIT_BF16, "precision id");
   if (n_rows == 0) return IQLB_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const int S = n_members;
+  const bool tc_ok = relabel_mlp_tc_supported(d_in, host_widths, depth);
+  if (precision == IQLB_RELABEL_SPLIT_BF16 && !tc_ok) {
+    snprintf(g_err, sizeof(g_err), "tensor-core relabel covers d_in <= 128, equal hidden widths of 64 or 128, depth <= 3");
+    return IQLB_ERR_UNSUPPORTED;
+  }
+  if (precision != IQLB_RELABEL_FP32 && tc_ok)
+    return relabel_mlp_tensor(x, n_rows, ldx, d_in, weights, S, host_widths, depth, activation, n_tail, out, preds_out,
+                              sel_out, st);
   // member parameter offsets
   std::vector<int64_t> offW(depth + 1), offB(depth + 1);
   int64_t pm = 0;
@@ -164,6 +218,13 @@ extern "C" int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int
   cleanup();
 #undef RL_CUDA
   return IQLB_OK;
+}
+
+extern "C" int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in, const float* weights,
+                                int32_t n_members, const int32_t* host_widths, int32_t depth, int32_t activation,
+                                int32_t n_tail, float* out, float* preds_out, uint8_t* sel_out, void* stream) {
+  return iqlb_relabel_mlp_p(x, n_rows, ldx, d_in, weights, n_members, host_widths, depth, activation, n_tail,
+                            IQLB_RELABEL_AUTO, out, preds_out, sel_out, stream);
 }
 
 extern "C" int iqlb_keep_mask_scan(const uint8_t* terminals, const uint8_t* timeouts, int64_t n,

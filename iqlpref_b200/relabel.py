@@ -55,24 +55,23 @@ def cvar_n_tail(alpha: float, n_total: int) -> int:
     return max(1, int(np.floor((1.0 - alpha) * n_total)))  # iql.py:937,1148
 
 
-def ensemble_predict(members: Sequence[Sequence[Any]], X, reduce: str = "mean", alpha: float = 0.0,
-                     activation: str = "relu", device="cuda", return_preds: bool = False,
-                     return_selection: bool = False):
-    """Evaluate S reward MLPs on X [n, d_in] and reduce over members.
+RELABEL_PRECISIONS = {"auto": -1, "fp32": 0, "split_bf16": 1}  # include/iqlb.h IQLB_RELABEL_*
 
-    members: S parameter lists [W0, b0, ..., Wout, bout] (numpy or torch; W stored (n_in, n_out) as
-    in `RewardMLP.state_dict()` / the BNN `sampled_weights` tuples).  reduce: "mean" or "cvar"
-    (mean of the worst floor((1-alpha)*S) members, at least one).  Returns a float32 CUDA tensor [n]
-    (plus `preds` [S, n] and/or the uint8 tail-membership mask [S, n] when asked)."""
+
+class PackedMembers:
+    """S reward MLPs flattened into the [S, PM] fp32 device matrix `iqlb_relabel_mlp` reads (pack once, relabel
+    many times: `ensemble_predict(pack_members(...), X)` skips the host-side flattening and the upload)."""
+
+    def __init__(self, weights: torch.Tensor, d_in: int, widths: List[int]):
+        self.weights, self.d_in, self.widths = weights, d_in, widths
+
+    def __len__(self):
+        return int(self.weights.shape[0])
+
+
+def pack_members(members: Sequence[Sequence[Any]], device="cuda") -> PackedMembers:
     dev = _cuda_device(device)
-    if reduce not in ("mean", "cvar"):
-        raise ValueError(f"reduce must be 'mean' or 'cvar', got {reduce!r}")
-    if reduce == "cvar" and not (0.0 <= alpha < 1.0):
-        raise ValueError(f"alpha must be in [0, 1), got {alpha!r}")
-    if activation not in _lib.ACTIVATIONS:
-        raise ValueError(f"unknown activation {activation!r}")
-    S = len(members)
-    if S == 0:
+    if len(members) == 0:
         raise ValueError("empty ensemble")
     first = [np.asarray(w.detach().cpu() if torch.is_tensor(w) else w) for w in members[0]]
     d_in = int(first[0].shape[0])
@@ -84,11 +83,37 @@ def ensemble_predict(members: Sequence[Sequence[Any]], X, reduce: str = "mean", 
         parts = [(w.detach().to("cpu", torch.float32).reshape(-1) if torch.is_tensor(w)
                   else torch.from_numpy(np.ascontiguousarray(np.asarray(w, dtype=np.float32)).reshape(-1))) for w in m]
         flat.append(torch.cat(parts))
-    weights = torch.stack(flat).to(dev)
+    return PackedMembers(torch.stack(flat).to(dev), d_in, widths)
+
+
+def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
+                     activation: str = "relu", device="cuda", return_preds: bool = False,
+                     return_selection: bool = False, precision: str = "auto"):
+    """Evaluate S reward MLPs on X [n, d_in] and reduce over members.
+
+    members: S parameter lists [W0, b0, ..., Wout, bout] (numpy or torch; W stored (n_in, n_out) as
+    in `RewardMLP.state_dict()` / the BNN `sampled_weights` tuples) or a `PackedMembers`.  reduce: "mean" or
+    "cvar" (mean of the worst floor((1-alpha)*S) members, at least one).  precision: "fp32" (FFMA GEMMs),
+    "split_bf16" (tcgen05, x_hi*W_hi + x_lo*W_hi + x_hi*W_lo; d_in <= 128, hidden [64|128] x <= 3) or "auto"
+    (tensor cores where the shape allows).  X may be a row-strided view (stride(1) == 1) of a wider table.
+    Returns a float32 CUDA tensor [n] (plus `preds` [S, n] and/or the uint8 tail-membership mask [S, n])."""
+    dev = _cuda_device(device)
+    if precision not in RELABEL_PRECISIONS:
+        raise ValueError(f"precision must be one of {sorted(RELABEL_PRECISIONS)}, got {precision!r}")
+    if reduce not in ("mean", "cvar"):
+        raise ValueError(f"reduce must be 'mean' or 'cvar', got {reduce!r}")
+    if reduce == "cvar" and not (0.0 <= alpha < 1.0):
+        raise ValueError(f"alpha must be in [0, 1), got {alpha!r}")
+    if activation not in _lib.ACTIVATIONS:
+        raise ValueError(f"unknown activation {activation!r}")
+    packed = members if isinstance(members, PackedMembers) else pack_members(members, dev)
+    S, d_in, widths, weights = len(packed), packed.d_in, packed.widths, packed.weights
     X = torch.as_tensor(X, dtype=torch.float32)
-    X = X.to(dev).contiguous()
+    X = X.to(dev)
     if X.ndim != 2 or X.shape[1] != d_in:
         raise ValueError(f"X must be [n, {d_in}]")
+    if X.shape[0] > 1 and (X.stride(1) != 1 or X.stride(0) < d_in):
+        X = X.contiguous()
     n = X.shape[0]
     n_tail = S if reduce == "mean" else cvar_n_tail(alpha, S)
     out = torch.empty(n, dtype=torch.float32, device=dev)
@@ -100,9 +125,11 @@ def ensemble_predict(members: Sequence[Sequence[Any]], X, reduce: str = "mean", 
     sel = torch.empty((S, n), dtype=torch.uint8, device=dev) if return_selection else None
     w_arr = (C.c_int32 * len(widths))(*widths)
     lib = _lib.load()
-    _lib.check(lib.iqlb_relabel_mlp(_lib.ptr(X), n, X.stride(0), d_in, _lib.ptr(weights), S, w_arr, len(widths),
-                                    _lib.ACTIVATIONS[activation], n_tail, _lib.ptr(out), _lib.ptr(preds),
-                                    _lib.ptr(sel), _lib.stream_ptr(dev)), "iqlb_relabel_mlp")
+    ldx = X.stride(0) if n > 1 else d_in
+    _lib.check(lib.iqlb_relabel_mlp_p(_lib.ptr(X), n, ldx, d_in, _lib.ptr(weights), S, w_arr, len(widths),
+                                      _lib.ACTIVATIONS[activation], n_tail, RELABEL_PRECISIONS[precision],
+                                      _lib.ptr(out), _lib.ptr(preds), _lib.ptr(sel), _lib.stream_ptr(dev)),
+               "iqlb_relabel_mlp_p")
     res = [out]
     if return_preds:
         res.append(preds)

@@ -152,3 +152,74 @@ def test_relabel_large_ragged_rows():
         ensemble_predict(members, np.zeros((4, 36), np.float32), "mean")
     with pytest.raises(ValueError):
         ensemble_predict(members, np.zeros((4, 37), np.float32), "cvar", alpha=1.0)
+
+
+def _members(rng, d_in, w, depth, S, bias=True):
+    out = []
+    for _ in range(S):
+        m, n_in = [], d_in
+        for _l in range(depth):
+            m += [rng.standard_normal((n_in, w)).astype(np.float32),
+                  (rng.standard_normal(w) if bias else np.zeros(w)).astype(np.float32)]
+            n_in = w
+        m += [rng.standard_normal((w, 1)).astype(np.float32), rng.standard_normal(1).astype(np.float32)]
+        out.append(m)
+    return out
+
+
+# split-bf16 tolerance: each product carries ~2^-18..2^-16 relative error (three bf16 MMAs, fp32 accumulation), so a
+# prediction is within 1e-3 relative of the reference, with an absolute floor of 1e-4 of the prediction scale.
+def _assert_split_bf16_close(got, want):
+    np.testing.assert_allclose(got, want, rtol=1e-3, atol=1e-4 * max(1.0, float(np.abs(want).max())))
+
+
+@pytest.mark.parametrize("d_in,w,depth,S,act,n", [
+    (37, 128, 3, 1, "relu", 1000),      # antmaze q_mlp (BASELINE configs[1])
+    (37, 128, 3, 1, "relu", 70_001),    # ragged, more tiles than SMs
+    (37, 128, 3, 7, "relu", 40_000),    # ensemble, every CTA streams all members (weight slots reloaded)
+    (69, 64, 3, 200, "relu", 300),      # pen-human BNN: members split across CTAs, 2-3 members per CTA
+    (69, 128, 3, 10, "tanh", 5000),     # pen-human snapshot ensemble, generic activation
+    (128, 128, 2, 3, "swish", 513),
+    (16, 64, 1, 3, "relu", 257),
+    (5, 64, 2, 1, "leaky_relu", 1),
+])
+def test_tensor_core_relabel_matches_oracle_and_fp32_path(d_in, w, depth, S, act, n):
+    from iqlpref_b200.relabel import ensemble_predict, pack_members
+    rng = np.random.default_rng(d_in * 1000 + w + S)
+    members = _members(rng, d_in, w, depth, S)
+    x = rng.standard_normal((n, d_in)).astype(np.float32)
+    packed = pack_members(members)
+    out_t, preds_t = ensemble_predict(packed, x, "cvar", 0.5, act, return_preds=True, precision="split_bf16")
+    out_f, preds_f = ensemble_predict(packed, x, "cvar", 0.5, act, return_preds=True, precision="fp32")
+    preds_t, preds_f = preds_t.cpu().numpy(), preds_f.cpu().numpy()
+    _assert_split_bf16_close(preds_t, preds_f)
+    for s in list(range(min(S, 3))) + [S - 1]:
+        _assert_split_bf16_close(preds_t[s], ro.reward_mlp_forward(x, members[s], act)[:, 0])
+    # the reduction is exact given the predictions, whatever produced them
+    np.testing.assert_allclose(out_t.cpu().numpy(), ro.cvar_reduce(preds_t, 0.5), rtol=1e-5, atol=1e-6)
+    # without the side outputs (scratch predictions, or the single-model direct write) the result is the same
+    out_only = ensemble_predict(packed, x, "cvar", 0.5, act, precision="split_bf16")
+    np.testing.assert_array_equal(out_only.cpu().numpy(), out_t.cpu().numpy())
+
+
+def test_tensor_core_relabel_reads_row_strided_tables():
+    """The relabel reads [obs|act] straight out of the packed replay table (row stride 68 floats)."""
+    from iqlpref_b200.relabel import ensemble_predict
+    rng = np.random.default_rng(11)
+    members = _members(rng, 37, 128, 3, 1)
+    table = torch.from_numpy(rng.standard_normal((3000, 68)).astype(np.float32)).cuda()
+    for view in (table[:, :37], table[:, 1:38]):  # 16-byte aligned rows and not
+        got = ensemble_predict(members, view, "mean", precision="split_bf16").cpu().numpy()
+        _assert_split_bf16_close(got, ro.reward_mlp_forward(view.cpu().numpy(), members[0], "relu")[:, 0])
+
+
+def test_tensor_core_relabel_refuses_other_shapes():
+    from iqlpref_b200.relabel import ensemble_predict
+    rng = np.random.default_rng(12)
+    x = rng.standard_normal((64, 37)).astype(np.float32)
+    with pytest.raises(RuntimeError):
+        ensemble_predict(_members(rng, 37, 96, 2, 1), x, "mean", precision="split_bf16")
+    got = ensemble_predict(_members(np.random.default_rng(12), 37, 96, 2, 1), x[:, :37], "mean", precision="auto")
+    assert got.shape == (64,)
+    with pytest.raises(ValueError):
+        ensemble_predict(_members(rng, 37, 128, 2, 1), x, "mean", precision="tf32")

@@ -202,6 +202,10 @@ int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in
                        int32_t activation, int32_t n_tail, int32_t precision, float* out, float* preds_out,
                        uint8_t* sel_out, void* stream);
 
+/* Debug: CTA 0 of the following tensor-core relabel launches records clock64 stamps into buf (device memory,
+ * >= 5*512 uint64; scripts/relabel_timeline.py decodes them).  NULL switches the recording off. */
+int iqlb_relabel_debug_timeline(unsigned long long* buf);
+
 /* Preference transformer (optbnn/bnn/nets/pref_trans.py:230-325) evaluated on the windows that
  * qlearning_dataset_pt builds (iql.py:1264-1292) and reduced to value[:,0,-1,0].
  *   obs[n_data][S], act[n_data][A]      : the dataset

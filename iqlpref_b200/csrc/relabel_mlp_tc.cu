@@ -15,10 +15,14 @@
 //   TMEM, per subtile p: [ACC w cols fp32 | A_hi AW cols | A_lo AW cols],  AW = max(w, K0)/2
 //   SMEM: the hi/lo weight images of all layers of ONE member (K-major UMMA images, 1-D bulk copies),
 //         resident for a single model, streamed layer slot by layer slot for ensembles; 2 bias bundles.
-//   warp 0: weight / bias producer      warp 1: MMA issuer
-//   warps 2-5: epilogue of subtile 0    warps 6-9: epilogue of subtile 1
+//   warp 0: weight / bias producer (+ L2 prefetch of the next tile's rows)      warp 1: MMA issuer
+//   warps 2-9: epilogue of subtile 0, warps 10-17: subtile 1 (two warps per TMEM lane quarter, one per column half)
 // The two subtiles ping-pong: while the epilogue warps of one drain layer l, the tensor core runs layer l
 // (or l+1) of the other.  The width->1 output layer is a dot product in the last epilogue.
+// Measured (clock64 timeline, scripts/relabel_timeline.py): a 128x128x16 MMA with A from TMEM retires every ~110
+// clocks; TMEM loads/stores of the epilogue warps queue behind the MMAs in flight (a tcgen05.st + wait::st costs
+// ~1 k clocks while a 24-MMA batch runs), so variants with fewer, fatter epilogue threads or register prefetch of
+// the next rows were slower than this one.
 #include <vector>
 
 #include "common.cuh"
@@ -29,7 +33,7 @@ using namespace umma;
 
 namespace rtc {
 constexpr int kMaxDepth = 3;
-constexpr int kThreads = 320;
+constexpr int kThreads = 576;  // producer, MMA issuer, 2 x 8 epilogue warps
 enum { W_FULL = 0, W_EMPTY = kMaxDepth, B_FULL = 2 * kMaxDepth, B_EMPTY = B_FULL + 2, A_READY = B_EMPTY + 2,
        ACC_READY = A_READY + 2, N_BARS = ACC_READY + 2 };
 }  // namespace rtc
@@ -51,6 +55,7 @@ struct RtcParams {
   int aw;                  // TMEM columns of one A image (hi or lo)
   float scale0, scale_h, scale_out;  // 1/sqrt(n_in) of layer 0, hidden layers, output layer
   float* preds;            // [S][pred_stride]
+  unsigned long long* dbg; // optional clock64 timeline of CTA 0 (iqlb_relabel_debug_timeline)
   int64_t pred_stride;
 };
 
@@ -109,8 +114,12 @@ __device__ __forceinline__ void split32(const float (&v)[32], uint32_t (&hi)[16]
   }
 }
 
-template <bool kRelu>
-__global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const RtcParams P) {
+__device__ __forceinline__ void rtc_stamp(const RtcParams& P, int role, int idx) {
+  if (P.dbg != nullptr && blockIdx.x == 0 && idx < 512) P.dbg[role * 512 + idx] = (unsigned long long)clock64();
+}
+
+template <bool kRelu, int kW>
+__global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
   using namespace rtc;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -118,15 +127,17 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
   const uint32_t oBun = P.slot_off[P.depth - 1] + P.slot_bytes[P.depth - 1];
   const uint32_t oBar = oBun + 2 * P.bundle_bytes;
   const uint32_t oTmem = oBar + N_BARS * 8;
+  const uint32_t oRed = oTmem + 16;  // 256 partial dot products
   auto bar = [&](int i) { return base + oBar + 8u * (uint32_t)i; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int w = P.w, depth = P.depth;
+  constexpr int w = kW;
+  const int depth = P.depth;
 
   if (threadIdx.x == 0) {
     for (int l = 0; l < kMaxDepth; ++l) { mbar_init(bar(W_FULL + l), 1); mbar_init(bar(W_EMPTY + l), 1); }
     for (int q = 0; q < 2; ++q) {
-      mbar_init(bar(B_FULL + q), 1); mbar_init(bar(B_EMPTY + q), 256);
-      mbar_init(bar(A_READY + q), 128); mbar_init(bar(ACC_READY + q), 1);
+      mbar_init(bar(B_FULL + q), 1); mbar_init(bar(B_EMPTY + q), 512);
+      mbar_init(bar(A_READY + q), 256); mbar_init(bar(ACC_READY + q), 1);
     }
     fence_barrier_init();
   }
@@ -148,9 +159,19 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
 
   if (warp == 0) {
     if (lane == 0) {
+      const bool x_aligned = (P.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 15) == 0);
       for (int i = 0; i < n_it; ++i) {
         const uint8_t* mb = P.wimg + (int64_t)(s0 + i % nm) * P.member_bytes;
         const int q = i & 1;
+        if (i % nm == 0 && x_aligned) {  // dataset rows of the NEXT tile: HBM -> L2 while this one computes
+          const int64_t r_next = ((int64_t)tile0 + (int64_t)(i / nm + 1) * P.ctas_per_ms) * 256;
+          if (r_next < P.rows) {
+            const int64_t nr = P.rows - r_next < 256 ? P.rows - r_next : 256;
+            const char* src = reinterpret_cast<const char*>(P.x + r_next * P.ldx);
+            const int64_t bytes = (nr * P.ldx * 4) & ~15ll;
+            for (int64_t o = 0; o < bytes; o += 16384) bulk_prefetch_l2(src + o, (uint32_t)(bytes - o < 16384 ? bytes - o : 16384));
+          }
+        }
         if (i >= 2) mbar_wait(bar(B_EMPTY + q), (uint32_t)(((i >> 1) - 1) & 1));
         mbar_expect_tx(bar(B_FULL + q), P.bundle_bytes);
         bulk_g2s(base + oBun + q * P.bundle_bytes, mb + P.bundle_off, P.bundle_bytes, bar(B_FULL + q));
@@ -179,6 +200,7 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
             mbar_wait(bar(A_READY + p), na[p] & 1);
             ++na[p];
             tc_fence_after();
+            rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2);
             const uint32_t acc = tmem + p * PC, ah = acc + w, al = ah + P.aw;
             uint32_t accum = 0;
 #pragma unroll 1
@@ -192,24 +214,30 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
               }
             }
             mma_commit(bar(ACC_READY + p));
+            rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2 + 1);
           }
           if (reload && i + 1 < n_it) mma_commit(bar(W_EMPTY + l));
         }
       }
     }
   } else {
-    const int p = (warp - 2) >> 2, quarter = warp & 3;
+    // 16 epilogue warps: subtile p, TMEM lane quarter (= warp % 4, the lanes a warp may touch), column half
+    const int ew = warp - 2, p = ew >> 3, quarter = warp & 3, half = (ew & 7) >> 2;
     const uint32_t acc = tmem + ((uint32_t)(quarter * 32) << 16) + p * PC, ah = acc + w, al = ah + P.aw;
     const bool vec = (P.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 15) == 0);
     const int k0r32 = (P.d_in + 31) / 32 * 32;
+    const int hc = w / 2, col0 = half * hc;  // this thread's accumulator columns [col0, col0 + hc)
+    float* red = reinterpret_cast<float*>(gbase + oRed) + p * 128 + quarter * 32 + lane;
+    const bool stamper = quarter == 0 && lane == 0;
     uint32_t nacc = 0;
     for (int i = 0; i < n_it; ++i) {
       const int tile = tile0 + (i / nm) * P.ctas_per_ms, s = s0 + i % nm;
       const int64_t row = (int64_t)tile * 256 + p * 128 + quarter * 32 + lane;
       const bool valid = row < P.rows;
       const float* xr = P.x + (valid ? row : 0) * P.ldx;
-      // layer-0 operand: dataset row -> hi/lo bf16 in tensor memory
-      for (int c0 = 0; c0 < k0r32; c0 += 32) {
+      if (stamper) rtc_stamp(P, 1 + p + 2 * half, (i * 4) * 2);
+      // layer-0 operand: dataset row -> hi/lo bf16 in tensor memory (32-column chunks alternate between the halves)
+      for (int c0 = half * 32; c0 < k0r32; c0 += 64) {
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
@@ -238,6 +266,7 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(bar(A_READY + p));
+      if (stamper) rtc_stamp(P, 1 + p + 2 * half, (i * 4) * 2 + 1);
       const int q = i & 1;
       mbar_wait(bar(B_FULL + q), (uint32_t)((i >> 1) & 1));
       const float* bun = reinterpret_cast<const float*>(gbase + oBun + q * P.bundle_bytes);
@@ -245,10 +274,11 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
         mbar_wait(bar(ACC_READY + p), nacc & 1);
         ++nacc;
         tc_fence_after();
+        if (stamper) rtc_stamp(P, 1 + p + 2 * half, (i * 4 + l + 1) * 2);
         const float scale = l == 0 ? P.scale0 : P.scale_h;
         const float* b = bun + l * w;
         if (l < depth - 1) {
-          for (int c = 0; c < w; c += 32) {
+          for (int c = col0; c < col0 + hc; c += 32) {
             float v[32];
             tmem_ld32(acc + (uint32_t)c, v);
             tmem_ld_wait();
@@ -268,10 +298,11 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
           tmem_st_wait();
           tc_fence_before();
           mbar_arrive(bar(A_READY + p));
+          if (stamper) rtc_stamp(P, 1 + p + 2 * half, (i * 4 + l + 1) * 2 + 1);
         } else {
           const float* wo = bun + depth * w;
           float dot = 0.f;
-          for (int c = 0; c < w; c += 32) {
+          for (int c = col0; c < col0 + hc; c += 32) {
             float v[32];
             tmem_ld32(acc + (uint32_t)c, v);
             tmem_ld_wait();
@@ -289,7 +320,11 @@ __global__ void __launch_bounds__(rtc::kThreads, 1) relabel_mlp_tc_kernel(const 
               dot = fmaf(h2, w4.z, dot); dot = fmaf(h3, w4.w, dot);
             }
           }
-          if (valid) P.preds[(int64_t)s * P.pred_stride + row] = fmaf(P.scale_out, dot, wo[w]);
+          // the two column halves of a row meet in shared memory (named barrier of the subtile's 256 threads)
+          if (half == 1) *red = dot;
+          asm volatile("bar.sync %0, 256;" ::"r"(1 + p) : "memory");
+          if (half == 0 && valid) P.preds[(int64_t)s * P.pred_stride + row] = fmaf(P.scale_out, dot + *red, wo[w]);
+          if (stamper) rtc_stamp(P, 1 + p + 2 * half, (i * 4 + l + 1) * 2 + 1);
         }
       }
       mbar_arrive(bar(B_EMPTY + q));
@@ -309,15 +344,18 @@ bool relabel_mlp_tc_supported(int d_in, const int32_t* widths, int depth) {
     if (widths[l] != w) return false;
   size_t smem = 0;
   for (int l = 0; l < depth; ++l) smem += 2u * (size_t)(((l == 0 ? d_in : w) + 63) / 64) * w * 128u;
-  smem += 2u * (size_t)(depth * w + w + 4) * 4u + rtc::N_BARS * 8 + 16 + 1024;
+  smem += 2u * (size_t)(depth * w + w + 4) * 4u + rtc::N_BARS * 8 + 16 + 1024 + 1024;
   return smem <= 227u * 1024u;
 }
+
+unsigned long long* g_rtc_dbg = nullptr;
 
 struct RelabelTc {
   RtcParams P;
   size_t smem;
   int n_sm;
   bool relu;
+  void (*kern)(const RtcParams);
   uint8_t* wimg;
 };
 
@@ -349,16 +387,16 @@ int relabel_tc_begin(RelabelTc** ctx, int ldx, int d_in, const float* weights, i
   P.scale0 = 1.0f / sqrtf((float)d_in);
   P.scale_h = 1.0f / sqrtf((float)w);
   P.scale_out = P.scale_h;
-  c->smem = (size_t)off + 2u * P.bundle_bytes + rtc::N_BARS * 8 + 16 + 1024;
+  c->smem = (size_t)off + 2u * P.bundle_bytes + rtc::N_BARS * 8 + 16 + 1024 + 1024;
   c->relu = activation == IQLB_ACT_RELU;
   c->wimg = nullptr;
   int dev = 0;
   c->n_sm = 148;
   cudaError_t e = cudaGetDevice(&dev);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c->n_sm, cudaDevAttrMultiProcessorCount, dev);
-  if (e == cudaSuccess)
-    e = c->relu ? cudaFuncSetAttribute(relabel_mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem)
-                : cudaFuncSetAttribute(relabel_mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem);
+  c->kern = c->relu ? (w == 128 ? relabel_mlp_tc_kernel<true, 128> : relabel_mlp_tc_kernel<true, 64>)
+                    : (w == 128 ? relabel_mlp_tc_kernel<false, 128> : relabel_mlp_tc_kernel<false, 64>);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(c->kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem);
   if (e == cudaSuccess) e = cudaMallocAsync((void**)&c->wimg, (size_t)S * (size_t)P.member_bytes, st);
   if (e == cudaSuccess) {
     P.wimg = c->wimg;
@@ -377,12 +415,12 @@ int relabel_tc_begin(RelabelTc** ctx, int ldx, int d_in, const float* weights, i
 // preds[s * pred_stride + i] = member s on row i of x[rows][ldx]
 int relabel_tc_forward(RelabelTc* c, const float* x, int64_t rows, float* preds, int64_t pred_stride, cudaStream_t st) {
   RtcParams P = c->P;
+  P.dbg = g_rtc_dbg;
   P.x = x; P.rows = rows; P.preds = preds; P.pred_stride = pred_stride;
   P.n_tiles = (int)((rows + 255) / 256);
   if (P.n_tiles >= c->n_sm) { P.n_ms = 1; P.ctas_per_ms = c->n_sm; }
   else { P.n_ms = c->n_sm / P.n_tiles; if (P.n_ms > P.S) P.n_ms = P.S; P.ctas_per_ms = P.n_tiles; }
-  if (c->relu) relabel_mlp_tc_kernel<true><<<P.n_ms * P.ctas_per_ms, rtc::kThreads, c->smem, st>>>(P);
-  else relabel_mlp_tc_kernel<false><<<P.n_ms * P.ctas_per_ms, rtc::kThreads, c->smem, st>>>(P);
+  c->kern<<<P.n_ms * P.ctas_per_ms, rtc::kThreads, c->smem, st>>>(P);
   IQLB_LAUNCH_CHECK();
   return IQLB_OK;
 }
@@ -394,3 +432,10 @@ void relabel_tc_end(RelabelTc* c, cudaStream_t st) {
 }
 
 }  // namespace iqlb
+
+// Debug: CTA 0 of the next tensor-core relabel launches writes clock64 stamps into buf (device, >= 5*512 u64;
+// role 0 = MMA issuer, 1..4 = first epilogue thread of subtile 0/1, column half 0/1); NULL switches it off.
+extern "C" int iqlb_relabel_debug_timeline(unsigned long long* buf) {
+  iqlb::g_rtc_dbg = buf;
+  return IQLB_OK;
+}

@@ -136,8 +136,13 @@ int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host_batch, flo
  * generator, which cannot be mirrored: parity is tested by injecting this mask into the oracle. */
 int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p);
 
-/* Tell the library that the caller wrote params/target directly (adopting modules, loading a
- * checkpoint): precision 1 rebuilds the bf16 operand images of the weights; precision 0: no-op. */
+/* Tell the library that the caller wrote params/target/it/rng directly (adopting modules, loading a
+ * checkpoint, reseeding): precision 1 rebuilds the bf16 operand images of the weights and drops the
+ * look-ahead batch; precision 0: no-op.
+ * Look-ahead sampling (precision 1, on-device sampling, no idx_out; opt-in with IQLB_PRESAMPLE=1): the
+ * gather of step t+1 is enqueued on an internal stream under the optimizer kernel of step t, after the
+ * RNG offset of step t has been advanced, so the index stream is unchanged; an explicit-batch step,
+ * iqlb_agents_set_replay or this call discards it. */
 int iqlb_agents_refresh(iqlb_agents* h, void* stream);
 
 /* Number of kernels one iqlb_agents_step enqueues (for launch accounting). */

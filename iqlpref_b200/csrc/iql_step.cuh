@@ -200,6 +200,13 @@ struct iqlb_agents {
   // L2 zig-zag: consecutive kernels walk the agents in opposite directions, so a consumer starts with what its
   // producer wrote last (still in L2); the direction flips every step (IQLB_ZIGZAG=0 turns it off)
   int zig = 0;
+  // look-ahead sampling (precision 1): the Philox gather + packing of step t+1 runs on pre_stream under the
+  // HBM-bound optimizer kernel of step t (its consumers of step t - loss, forward, weight gradients - are done and
+  // the RNG offset has been advanced by then).  pre_valid: h->batch / the X images already hold the next batch.
+  cudaStream_t pre_stream = nullptr;
+  cudaEvent_t ev_pre_fork = nullptr, ev_pre_join = nullptr;
+  bool pre_valid = false;
+  int presample = 0;
 };
 
 namespace iqlb {

@@ -125,3 +125,43 @@ def test_bf16_sampled_step_and_shadow_refresh():
     eng._sync_shadow()
     eng.train(None)
     assert torch.equal(l1, eng.losses)
+
+
+def test_bf16_lookahead_sampling_changes_nothing(monkeypatch):
+    """The gather of step t+1 running under the optimizer kernel of step t must leave losses, parameters and RNG
+    offsets bit-identical to the in-order schedule, also across an explicit-batch step and a table swap."""
+    from iqlpref_b200 import iql as biql
+    S, A, N = 29, 8, 4
+    buf = biql.ReplayBuffer(S, A, 7000)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    buf._table[:, :2 * S + A + 2] = torch.randn((7000, 2 * S + A + 2), generator=g, device="cuda")
+    buf._table[:, 2 * S + A + 1] = 0
+    buf._size = buf._pointer = 7000
+    buf2 = biql.ReplayBuffer(S, A, 3000)
+    buf2._table[:, :2 * S + A + 2] = torch.randn((3000, 2 * S + A + 2), generator=g, device="cuda")
+    buf2._table[:, 2 * S + A + 1] = 0
+    buf2._size = buf2._pointer = 3000
+    rng = np.random.default_rng(2)
+    rows = torch.stack([biql.pack_rows(*_batch(rng, 256, S, A), buf._stride) for _ in range(N)]).cuda()
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("IQLB_PRESAMPLE", mode)
+        eng = biql.BatchedIQL(S, A, N, batch_size=256, hparams=[HP] * N, precision="bf16", seeds=[7, 8, 9, 10])
+        for a in range(N):
+            torch.manual_seed(20 + a)
+            eng.adopt(a, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0), bind=False)
+        eng.attach_replay(buf)
+        trace = []
+        for k in range(9):
+            if k == 4:
+                eng.train(rows)          # explicit batch between sampled steps
+            else:
+                if k == 6:
+                    eng.attach_replay(buf2)  # table swap with a look-ahead batch pending
+                eng.train(None)
+            trace.append(eng.losses.clone())
+        torch.cuda.synchronize()
+        out[mode] = (torch.stack(trace), eng.params.clone(), eng.rng.clone())
+    for x, y in zip(out["0"], out["1"]):
+        assert torch.equal(x, y)
+    assert out["1"][2][:, 1].tolist() == [32] * N  # eight sampled steps, four Philox draws each

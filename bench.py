@@ -206,7 +206,7 @@ def build_workload(args, dev, rank):
     import numpy as np
     import torch
     from iqlpref_b200 import iql as biql
-    from iqlpref_b200.relabel import ensemble_predict
+    from iqlpref_b200.relabel import ensemble_predict, pack_members
     from iqlpref_b200.reward_models.q_mlp import MLP as RewardMLP, member_weights
     N, rows = args.agents_per_gpu, args.rows
     g = torch.Generator(device=dev)
@@ -224,14 +224,27 @@ def build_workload(args, dev, rank):
     torch.manual_seed(0)
     rm = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
     x = t[:, :S_DIM + A_DIM]
-    ensemble_predict([member_weights(rm)], x[:4096], "mean", device=dev)  # warm-up
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize(dev)
-    e0.record()
-    r_hat = ensemble_predict([member_weights(rm)], x, "mean", device=dev)
-    e1.record()
-    torch.cuda.synchronize(dev)
-    relabel_ms = e0.elapsed_time(e1)
+    packed = pack_members([member_weights(rm)], dev)  # x is a row-strided view of the replay table: no copy
+    relabel = {"rows": rows, "model": "RewardMLP(37,1,[128]*3,relu)", "table_row_bytes": R * 4}
+    flops = rows * 2.0 * ((S_DIM + A_DIM) * 128 + 2 * 128 * 128 + 128)
+    for prec, reps in (("split_bf16", 5), ("fp32", 1)):
+        ensemble_predict(packed, x[:4096], "mean", device=dev, precision=prec)  # warm-up
+        ensemble_predict(packed, x, "mean", device=dev, precision=prec)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(reps):
+            r_hat = ensemble_predict(packed, x, "mean", device=dev, precision=prec)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1) / reps
+        relabel[prec] = {"ms": ms, "rows_per_s": rows / (ms * 1e-3), "tflops_fp32_equiv": flops / (ms * 1e-3) / 1e12,
+                         "table_GBps": rows * R * 4 / (ms * 1e-3) / 1e9}
+    relabel["rows_per_s"] = relabel["split_bf16"]["rows_per_s"]
+    relabel["ms"] = relabel["split_bf16"]["ms"]
+    # split-bf16 issues three bf16 MMAs per product: the tensor-pipe work is 3x the fp32-equivalent flops
+    relabel["bf16_mma_tflops"] = 3.0 * relabel["split_bf16"]["tflops_fp32_equiv"]
+    r_hat = ensemble_predict(packed, x, "mean", device=dev, precision="split_bf16")
     # reward columns standing in for normalize_reward 0..7 (iql.py:363-401): affine maps of the relabelled reward
     r = r_hat
     span = (r.max() - r.min()).clamp_min(1e-6)
@@ -249,8 +262,7 @@ def build_workload(args, dev, rank):
     eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
     if args.precision == "bf16":
         eng.debug_option(0, int(args.fused_adam))
-    return eng, buf, cols, variant, {"rows_per_s": rows / (relabel_ms * 1e-3), "ms": relabel_ms, "rows": rows,
-                                     "model": "RewardMLP(37,1,[128]*3,relu)"}
+    return eng, buf, cols, variant, relabel
 
 
 KERNEL_WORK = None  # filled per precision in kernel_roofline()
@@ -479,6 +491,10 @@ def run_cuda(args):
                                   "hbm_frac": bytes_per_update() * per_gpu / 1e9 / peaks["hbm"],
                                   "flops_per_update": flops_per_update(), "bytes_per_update": bytes_per_update()},
                 "relabel": relabel}
+        relabel["roofline"] = {"bound": "tensor", "achieved": relabel["bf16_mma_tflops"], "peak": peaks["tensor_burst"],
+                               "unit": "TFLOP/s", "frac": relabel["bf16_mma_tflops"] / peaks["tensor_burst"],
+                               "hbm_frac": relabel["split_bf16"]["table_GBps"] / peaks["hbm"],
+                               "note": "whole iqlb_relabel_mlp_p call (weight-image prep + kernel), timed alone: burst peak"}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         print(json.dumps(line), flush=True)

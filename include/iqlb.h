@@ -246,6 +246,11 @@ int iqlb_selftest_umma(const void* a_img, int64_t a_bytes, const void* b_img, in
                        int32_t a_rows_total, int32_t a_off, int32_t b_mn, int32_t b_rows_total, int32_t b_off,
                        int32_t n, int32_t ksteps, float* d_out, void* stream);
 
+/* Tensor-pipe issue-rate probe: `count` back-to-back 128 x n x 16 bf16 MMAs into one accumulator, A from shared
+ * memory (a_from_tmem = 0) or from tensor memory (1).  clocks_out (device, 2 x uint64): SM clocks spent issuing,
+ * and from the first issue to the completion of the last MMA. */
+int iqlb_selftest_mma_rate(int32_t a_from_tmem, int32_t n, int32_t count, unsigned long long* clocks_out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Host helper (plain C loop, no GPU): the keep-mask / episode-step scan every qlearning_dataset_*
  * starts with (iql.py:701-716, 1236-1253).  terminals/timeouts are host uint8[n]; timeouts may be

@@ -63,6 +63,7 @@ _SIGNATURES = {
     "iqlb_pt_forward": ([C.POINTER(PTDesc), _P, _P, _P, _P, _P, C.c_int64, _P, _P], C.c_int),
     "iqlb_selftest_umma": ([_P, C.c_int64, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, _P, _P], C.c_int),
+    "iqlb_selftest_mma_rate": ([C.c_int32, C.c_int32, C.c_int32, _P, _P], C.c_int),
     "iqlb_keep_mask_scan": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P], C.c_int),
 }
 

@@ -15,8 +15,8 @@
 //   TMEM, per subtile p: [ACC w cols fp32 | A_hi AW cols | A_lo AW cols],  AW = max(w, K0)/2
 //   SMEM: the hi/lo weight images of all layers of ONE member (K-major UMMA images, 1-D bulk copies),
 //         resident for a single model, streamed layer slot by layer slot for ensembles; 2 bias bundles.
-//   warp 0: weight / bias producer (+ L2 prefetch of the next tile's rows)      warp 1: MMA issuer
-//   warps 2-9: epilogue of subtile 0, warps 10-17: subtile 1 (two warps per TMEM lane quarter, one per column half)
+//   warp 0: weight / bias producer (+ L2 prefetch of the next tile's rows)      warps 1, 2: MMA issuers of subtile 0, 1
+//   warps 4-11: epilogue of subtile 0, warps 12-19: subtile 1 (two warps per TMEM lane quarter, one per column half)
 // The two subtiles ping-pong: while the epilogue warps of one drain layer l, the tensor core runs layer l
 // (or l+1) of the other.  The width->1 output layer is a dot product in the last epilogue.
 // Measured (clock64 timeline, scripts/relabel_timeline.py): a 128x128x16 MMA with A from TMEM retires every ~110
@@ -33,7 +33,7 @@ using namespace umma;
 
 namespace rtc {
 constexpr int kMaxDepth = 3;
-constexpr int kThreads = 576;  // producer, MMA issuer, 2 x 8 epilogue warps
+constexpr int kThreads = 640;  // producer, 2 MMA issuers, spare, 2 x 8 epilogue warps
 enum { W_FULL = 0, W_EMPTY = kMaxDepth, B_FULL = 2 * kMaxDepth, B_EMPTY = B_FULL + 2, A_READY = B_EMPTY + 2,
        ACC_READY = A_READY + 2, N_BARS = ACC_READY + 2 };
 }  // namespace rtc
@@ -53,6 +53,7 @@ struct RtcParams {
   uint32_t bundle_off, bundle_bytes;    // floats: b_0 .. b_{depth-1} (w each) | wout (w) | bout, 0, 0, 0
   int ksteps0;             // ceil(d_in / 16)
   int aw;                  // TMEM columns of one A image (hi or lo)
+  int skew_clocks;         // start-up delay of the second subtile's MMA issuer
   float scale0, scale_h, scale_out;  // 1/sqrt(n_in) of layer 0, hidden layers, output layer
   float* preds;            // [S][pred_stride]
   unsigned long long* dbg; // optional clock64 timeline of CTA 0 (iqlb_relabel_debug_timeline)
@@ -134,7 +135,7 @@ __global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
   const int depth = P.depth;
 
   if (threadIdx.x == 0) {
-    for (int l = 0; l < kMaxDepth; ++l) { mbar_init(bar(W_FULL + l), 1); mbar_init(bar(W_EMPTY + l), 1); }
+    for (int l = 0; l < kMaxDepth; ++l) { mbar_init(bar(W_FULL + l), 1); mbar_init(bar(W_EMPTY + l), 2); }
     for (int q = 0; q < 2; ++q) {
       mbar_init(bar(B_FULL + q), 1); mbar_init(bar(B_EMPTY + q), 512);
       mbar_init(bar(A_READY + q), 256); mbar_init(bar(ACC_READY + q), 1);
@@ -187,42 +188,56 @@ __global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 || warp == 2) {
+    // One MMA issuer per subtile.  A single thread issues a 128 x N x 16 MMA only every ~105-120 clocks whatever N
+    // is (scripts/mma_rate.py): at N = 128 one issuer reaches 55 % of the tensor pipe, two reach 92 %.
     if (lane == 0) {
+      const int p = warp - 1;
       const uint32_t idesc = instr_desc_bf16(w, 0, 0);
-      uint32_t na[2] = {0, 0};
+      const uint32_t acc = tmem + p * PC, ah = acc + w, al = ah + P.aw;
+      uint32_t na = 0;
+      if (p == 1 && n_it > 0) {
+        // stagger the subtiles by about half a layer, so that one is in its epilogue while the other is in the
+        // tensor pipe (started together they stay in lockstep: MMAs overlap MMAs and epilogues overlap epilogues)
+        mbar_wait(bar(ACC_READY + 0), 0);
+        const long long t0 = clock64();
+        while (clock64() - t0 < P.skew_clocks) {
+        }
+      }
       for (int i = 0; i < n_it; ++i) {
         for (int l = 0; l < depth; ++l) {
           if (reload || i == 0) mbar_wait(bar(W_FULL + l), reload ? (uint32_t)(i & 1) : 0u);
           const int ks = l == 0 ? P.ksteps0 : w / 16;
-          const uint32_t bhi = base + P.slot_off[l], blo = bhi + P.slot_bytes[l] / 2;
-          for (int p = 0; p < 2; ++p) {
-            mbar_wait(bar(A_READY + p), na[p] & 1);
-            ++na[p];
-            tc_fence_after();
-            rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2);
-            const uint32_t acc = tmem + p * PC, ah = acc + w, al = ah + P.aw;
-            uint32_t accum = 0;
+          const uint64_t bhi = smem_desc(base + P.slot_off[l], 16, 1024);
+          const uint64_t blo = smem_desc(base + P.slot_off[l] + P.slot_bytes[l] / 2, 16, 1024);
+          mbar_wait(bar(A_READY + p), na & 1);
+          ++na;
+          tc_fence_after();
+          rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2);
+          uint32_t accum = 0;
 #pragma unroll 1
-            for (int term = 0; term < 3; ++term) {
-              const uint32_t a = term == 1 ? al : ah, b = term == 2 ? blo : bhi;
-#pragma unroll 4
-              for (int k = 0; k < ks; ++k) {
-                mma_bf16_ts(acc, a + 8u * k, smem_desc(b + (uint32_t)(k >> 2) * (uint32_t)w * 128u + (uint32_t)(k & 3) * 32u, 16, 1024),
-                            idesc, accum);
-                accum = 1;
-              }
+          for (int term = 0; term < 3; ++term) {
+            const uint32_t a = term == 1 ? al : ah;
+            const uint64_t b = term == 2 ? blo : bhi;
+#pragma unroll 8
+            for (int k = 0; k < ks; ++k) {
+              // the descriptor's start-address field is (address >> 4): advancing it is one 64-bit add
+              mma_bf16_ts(acc, a + 8u * k, b + (uint64_t)(((uint32_t)(k >> 2) * (uint32_t)w * 128u + (uint32_t)(k & 3) * 32u) >> 4),
+                          idesc, accum);
+              accum = 1;
             }
-            mma_commit(bar(ACC_READY + p));
-            rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2 + 1);
           }
+          mma_commit(bar(ACC_READY + p));
+          rtc_stamp(P, 0, ((i * 3 + l) * 2 + p) * 2 + 1);
           if (reload && i + 1 < n_it) mma_commit(bar(W_EMPTY + l));
         }
       }
     }
+  } else if (warp == 3) {
+    // spare warp: keeps the epilogue warps aligned to the TMEM lane quarters (quarter = warp % 4)
   } else {
     // 16 epilogue warps: subtile p, TMEM lane quarter (= warp % 4, the lanes a warp may touch), column half
-    const int ew = warp - 2, p = ew >> 3, quarter = warp & 3, half = (ew & 7) >> 2;
+    const int ew = warp - 4, p = ew >> 3, quarter = warp & 3, half = (ew & 7) >> 2;
     const uint32_t acc = tmem + ((uint32_t)(quarter * 32) << 16) + p * PC, ah = acc + w, al = ah + P.aw;
     const bool vec = (P.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 15) == 0);
     const int k0r32 = (P.d_in + 31) / 32 * 32;
@@ -387,6 +402,7 @@ int relabel_tc_begin(RelabelTc** ctx, int ldx, int d_in, const float* weights, i
   P.scale0 = 1.0f / sqrtf((float)d_in);
   P.scale_h = 1.0f / sqrtf((float)w);
   P.scale_out = P.scale_h;
+  P.skew_clocks = getenv("IQLB_RELABEL_SKEW") ? atoi(getenv("IQLB_RELABEL_SKEW")) : 1200;
   c->smem = (size_t)off + 2u * P.bundle_bytes + rtc::N_BARS * 8 + 16 + 1024 + 1024;
   c->relu = activation == IQLB_ACT_RELU;
   c->wimg = nullptr;

@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
 // dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
 // each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(288, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
+__global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
@@ -450,19 +450,25 @@ __global__ void __launch_bounds__(288, 1) bf16_bwd_data_kernel(BfParams P, const
   tc_fence_after();
   IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
-  if (tid == 256) {
-    uint8_t* dh2 = P.dh2 + at * P.h_bytes;
-    for (int cb = 0; cb < 4; ++cb)
-      bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
-    bulk_commit();
+  if (tid == 256 || tid == 288) {
+    // two issuing threads (even / odd blocks): one thread gets an MMA out only every ~105-120 clocks whatever N is
+    // (scripts/mma_rate.py), which at N = 64 is a quarter of the tensor pipe's rate
+    const int first = tid == 256 ? 0 : (P.opt_issuers == 2 ? 1 : 4);
+    const int step = P.opt_issuers == 2 ? 2 : 1;
+    if (tid == 256) {
+      uint8_t* dh2 = P.dh2 + at * P.h_bytes;
+      for (int cb = 0; cb < 4; ++cb)
+        bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
+      bulk_commit();
+    }
     const Operand a = operand_k_major(sbase + oA, 128, 0);
-    for (int ib = 0; ib < 4; ++ib) {
+    for (int ib = first; ib < 4; ib += step) {
       mbar_wait(bar_w + 8 * ib, 0);
       tc_fence_after();
       gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
       mma_commit(bar_mma + 8 * ib);
     }
-    bulk_wait_read0();  // the dH2 tile has left shared memory before this CTA retires
+    if (tid == 256) bulk_wait_read0();  // the dH2 tile has left shared memory before this CTA retires
   }
   __syncwarp();
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -559,10 +565,15 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   const int64_t at = (int64_t)agent * kTrain + t;
   const int ksteps = L.B / 16;
   const int n0 = (in + 15) / 16 * 16;
+  // One thread issues an MMA only every ~105-120 clocks whatever N is (scripts/mma_rate.py), so the narrow products
+  // (bias columns, dW2, dW0) cost as much issue time as the 256-wide one: lane 0 of warps 0-2 issue them side by side.
+  const bool multi = P.opt_issuers == 2;
 
   if (tid == 0) {
     if (sbase & 1023u) __trap();
-    for (int i = 0; i < 5; ++i) mbar_init(bar_ld1 + 8 * i, 1);
+    for (int i = 0; i < 3; ++i) mbar_init(bar_ld1 + 8 * i, 1);
+    mbar_init(bar_p1, multi ? 2 : 1);  // one arrival per issuing thread
+    mbar_init(bar_p2, multi ? 3 : 1);
     fence_barrier_init();
     mbar_expect_tx(bar_ld1, 7 * blk);
     bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward / loss outputs: before the PDL wait
@@ -600,12 +611,12 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
 #define IQLB_TSW(slot) do { if (dbgw) P.dbg[2048 + (slot)] = (unsigned long long)clock64(); } while (0)
   IQLB_TSW(0);
   const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
-  if (tid == 0) {
+  if (tid == 0 || (multi && tid == 32)) {
     mbar_wait(bar_ld1, 0);
     tc_fence_after();
     const Operand a1 = operand_mn_major(sbase + oA, L.B, 0, 0);
-    gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
-    gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
+    if (tid == 0) gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
+    if (tid == 32 || !multi) gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
     mma_commit(bar_p1);
   }
   __syncwarp();
@@ -737,15 +748,19 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
       bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
     }
   }
-  if (tid == 0) {
-    mbar_wait(bar_ld2, 0);
-    tc_fence_after();
-    const Operand a0 = operand_mn_major(sbase + oA, L.B, 0, 0);
-    gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
-    gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
-    mbar_wait(bar_ld3, 0);
-    tc_fence_after();
-    gemm_issue(tmem + 416, operand_mn_major(sbase + oB + 2 * blk, L.B, 0, 0), z, 32, ksteps, false);
+  if (tid == 0 || (multi && (tid == 32 || tid == 64))) {
+    if (tid != 64) {
+      mbar_wait(bar_ld2, 0);
+      tc_fence_after();
+      const Operand a0 = operand_mn_major(sbase + oA, L.B, 0, 0);
+      if (tid == 0) gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
+      if (tid == 32 || !multi) gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
+    }
+    if (tid == 64 || !multi) {
+      mbar_wait(bar_ld3, 0);
+      tc_fence_after();
+      gemm_issue(tmem + 416, operand_mn_major(sbase + oB + 2 * blk, L.B, 0, 0), z, 32, ksteps, false);
+    }
     mma_commit(bar_p2);
   }
   __syncwarp();
@@ -923,6 +938,7 @@ int bf16_create(iqlb_agents* h) {
   P.dbg = nullptr;
   P.rev = 0;
   auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
+  P.opt_issuers = envi("IQLB_ISSUERS", 2);
   P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
   if (rc) return rc;
@@ -1021,7 +1037,7 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   BfParams P = st->P;
   P.agent0 = a0;
   P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
-  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(288), bwd_data_smem(), stream,
+  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(320), bwd_data_smem(), stream,
                        pdl_enabled(8) && !h->prof, P,
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");

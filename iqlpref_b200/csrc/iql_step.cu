@@ -60,9 +60,16 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(Layout L, const float* __
 //   value_loss (iql.py:404-405,587-588), q_loss (:604-606), actor_loss (:622-632)
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ double cosine_next(double lr, double base_lr, long long epoch, long long t_max) {
-  const double kPi = 3.14159265358979323846;
-  if ((epoch - 1 - t_max) % (2 * t_max) == 0) return lr + base_lr * (1.0 - cos(kPi / (double)t_max)) / 2.0;
-  return (1.0 + cos(kPi * (double)epoch / (double)t_max)) / (1.0 + cos(kPi * (double)(epoch - 1) / (double)t_max)) * lr;
+  // cospi(x) = cos(pi x) without the rounding of pi * x; 32-bit remainder when the counters fit (they do: max_steps
+  // and the step counter are < 2^31 in every reference config), 64-bit otherwise
+  bool restart;
+  if (epoch < 0x7fffffffll && t_max < 0x3fffffffll && epoch - 1 - t_max >= 0)
+    restart = (uint32_t)(epoch - 1 - t_max) % (2u * (uint32_t)t_max) == 0u;
+  else
+    restart = (epoch - 1 - t_max) % (2 * t_max) == 0;
+  const double inv_t = 1.0 / (double)t_max;
+  if (restart) return lr + base_lr * (1.0 - cospi(inv_t)) / 2.0;
+  return (1.0 + cospi((double)epoch * inv_t)) / (1.0 + cospi((double)(epoch - 1) * inv_t)) * lr;
 }
 
 template <int kMaxThreads>
@@ -93,7 +100,10 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
     IQLB_TSL(5);
     // Adam step scalars of THIS step (torch optim/adam.py:529-547) and scheduler/rng advance.
     const long long t = it[agent] + 1;
-    const double bc1 = 1.0 - pow(0.9, (double)t), bc2 = 1.0 - pow(0.999, (double)t);
+    // beta^t as exp(t ln beta): one fp64 exp instead of a pow (a third of the dependent chain); the result differs
+    // from Python's beta ** t by ~1e-15 relative, far below the fp32 step sizes it ends up in
+    const double bc1 = 1.0 - exp((double)t * -0.10536051565782628234);   // ln 0.9
+    const double bc2 = 1.0 - exp((double)t * -0.00100050033358353350);   // ln 0.999
     const double lr_a = actor_lr[agent];
     StepScalars sc;
     sc.ss_v = (float)((double)hp[4] / bc1);
@@ -104,7 +114,7 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
     scal[agent] = sc;
     it[agent] = t;
     actor_lr[agent] = cosine_next(lr_a, (double)hp[6], t, (long long)hp[7]);
-    if (advance_rng) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
+    if (advance_rng & 1) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
     IQLB_TSL(6);
   };
   if (wimg != nullptr && b < 4) {

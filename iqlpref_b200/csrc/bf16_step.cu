@@ -348,7 +348,19 @@ __global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const
                                                                const float* __restrict__ d_out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int half = blockIdx.x, t = blockIdx.y, agent = P.agent0 + (P.rev ? (int)(gridDim.z - 1 - blockIdx.z) : (int)blockIdx.z);
+  // Longest tiles first: the actor's dH2 = dz W2 has out_dim columns of dz per row (8-24) against one for V / Q, and
+  // its CTAs run ~14.5 us against ~8 us - launched in (agent, net) order they end up as the kernel's tail
+  // (per-SM CTA timeline, scripts/timeline.py).  CTAs are scheduled in linear block order: actor tiles take the front.
+  const int cta_lin = (int)blockIdx.x + 2 * ((int)blockIdx.y + kTrain * (int)blockIdx.z);
+  const int n_ag = (int)gridDim.z;
+  int half, t, aidx;
+  if (P.opt_lpt) {
+    if (cta_lin < 2 * n_ag) { half = cta_lin & 1; t = 3; aidx = cta_lin >> 1; }
+    else { const int r = cta_lin - 2 * n_ag; half = r & 1; t = (r >> 1) % 3; aidx = (r >> 1) / 3; }
+  } else {
+    half = blockIdx.x; t = blockIdx.y; aidx = blockIdx.z;
+  }
+  const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
   const int s = train_stream(t), net = net_of_stream(s);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int quarter = warp & 3, chalf = warp >> 2;
@@ -361,9 +373,15 @@ __global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const
   const float* fnet = params + (int64_t)agent * L.Pstride + L.net_off(s);
   const int64_t at = (int64_t)agent * kTrain + t;
 
-  const bool dbgd = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && blockIdx.z == 0 && tid == 64;
+  const bool dbgd = P.dbg != nullptr && half == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
 #define IQLB_TSD(slot) do { if (dbgd) P.dbg[2560 + (slot)] = (unsigned long long)clock64(); } while (0)
   IQLB_TSD(0);
+  if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {  // (SM, start) of every CTA: scripts/timeline.py --waves
+    unsigned smid; unsigned long long gt;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + cta_lin * 3] = smid; P.dbg[4096 + cta_lin * 3 + 1] = gt;
+  }
   if (tid == 0) {
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
@@ -496,6 +514,11 @@ __global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const
   }
   IQLB_TSD(9);
   if (tid == 0) bulk_wait_read0();
+  if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + cta_lin * 3 + 2] = gt;
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 256);
@@ -607,7 +630,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const bool dbgw = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && blockIdx.z == 0 && tid == 64;
+  const bool dbgw = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && (int)blockIdx.z == P.dbg_z && tid == 64;
 #define IQLB_TSW(slot) do { if (dbgw) P.dbg[2048 + (slot)] = (unsigned long long)clock64(); } while (0)
   IQLB_TSW(0);
   const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
@@ -939,8 +962,10 @@ int bf16_create(iqlb_agents* h) {
   P.rev = 0;
   auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
   P.opt_issuers = envi("IQLB_ISSUERS", 2);
+  P.opt_lpt = envi("IQLB_LPT", 1);
+  P.dbg_z = envi("IQLB_DBG_Z", 0);  // which agent's CTA records the clock64 timeline
   P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
-  if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 4096 * 8);
+  if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 8192 * 8);
   if (rc) return rc;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));

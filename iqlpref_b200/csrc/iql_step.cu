@@ -922,7 +922,7 @@ extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, 
       src = h->grads;
       break;
     case 7: src = h->batch; n = N * L.B * L.R; break;
-    case 8: src = bf16_params(h) ? (const float*)bf16_params(h)->dbg : nullptr; n = src ? 8192 : 0; break;
+    case 8: src = bf16_params(h) ? (const float*)bf16_params(h)->dbg : nullptr; n = src ? 16384 : 0; break;
     default: return fail(IQLB_ERR_INVALID, "unknown debug tensor%s", "");
   }
   if (nbytes) *nbytes = n * (int64_t)sizeof(float);

@@ -48,3 +48,24 @@ if l[0]:
 d = ts[2560:2560 + 12]
 if d[0]:
     print("bwd_data CTA (0,1,0): " + ", ".join(f"{n}={int(x - d[0])}" for n, x in zip(["start", "loads in regs", "sync", "dH2 tile done", "sync2", "mma0", "mma1", "mma2", "mma3", "drained"], d) if x))
+
+import collections
+wv = ts[4096:4096 + 3 * 512].reshape(512, 3)
+if wv[:, 1].any():
+    by_sm = collections.defaultdict(list)
+    for sm, a, b in wv:
+        if a:
+            by_sm[int(sm)].append((int(a), int(b)))
+    t0 = min(a for v in by_sm.values() for a, _ in v)
+    print("bwd_data CTAs per SM (globaltimer ns from the first CTA start): [start, end] ...")
+    for sm in sorted(by_sm)[:6] + sorted(by_sm)[-2:]:
+        print(f"  SM {sm:3d}: " + "  ".join(f"[{a - t0:6d},{b - t0:6d}]" for a, b in sorted(by_sm[sm])))
+    dur = [b - a for v in by_sm.values() for a, b in v]
+    ends = max(b for v in by_sm.values() for _, b in v)
+    gaps = []
+    for v in by_sm.values():
+        v = sorted(v)
+        gaps += [v[i + 1][0] - v[i][1] for i in range(len(v) - 1)]
+    import numpy as np
+    print(f"  CTA duration ns: median {np.median(dur):.0f}, max {max(dur)}; gap between CTAs on an SM: median {np.median(gaps):.0f};"
+          f" kernel span {ends - t0} ns; CTAs per SM: {collections.Counter(len(v) for v in by_sm.values())}")

@@ -443,14 +443,22 @@ __global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const
         } else {
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = 0.f;
+          // groups of eight outputs behind a uniform branch: an 8-action actor issues one group, not three
+          // (predicated-off instructions still take issue slots)
 #pragma unroll
-          for (int o = 0; o < kOutMax; ++o) {
-            if (o < nout) {
-              const float4 w0 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0),
-                           w1 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0 + 4);
-              g[0] = fmaf(dz[o], w0.x, g[0]); g[1] = fmaf(dz[o], w0.y, g[1]); g[2] = fmaf(dz[o], w0.z, g[2]);
-              g[3] = fmaf(dz[o], w0.w, g[3]); g[4] = fmaf(dz[o], w1.x, g[4]); g[5] = fmaf(dz[o], w1.y, g[5]);
-              g[6] = fmaf(dz[o], w1.z, g[6]); g[7] = fmaf(dz[o], w1.w, g[7]);
+          for (int ob = 0; ob < kOutMax; ob += 8) {
+            if (ob < nout) {
+#pragma unroll
+              for (int oo = 0; oo < 8; ++oo) {
+                const int o = ob + oo;
+                if (oo == 0 || o < nout) {
+                  const float4 w0 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0),
+                               w1 = *reinterpret_cast<const float4*>(sw2 + o * 256 + c0 + 4);
+                  g[0] = fmaf(dz[o], w0.x, g[0]); g[1] = fmaf(dz[o], w0.y, g[1]); g[2] = fmaf(dz[o], w0.z, g[2]);
+                  g[3] = fmaf(dz[o], w0.w, g[3]); g[4] = fmaf(dz[o], w1.x, g[4]); g[5] = fmaf(dz[o], w1.y, g[5]);
+                  g[6] = fmaf(dz[o], w1.z, g[6]); g[7] = fmaf(dz[o], w1.w, g[7]);
+                }
+              }
             }
           }
         }

@@ -641,6 +641,13 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   const bool dbgw = P.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 1 && (int)blockIdx.z == P.dbg_z && tid == 64;
 #define IQLB_TSW(slot) do { if (dbgw) P.dbg[2048 + (slot)] = (unsigned long long)clock64(); } while (0)
   IQLB_TSW(0);
+  const int wlin = (int)blockIdx.x + 2 * ((int)blockIdx.y + kTrain * (int)blockIdx.z);
+  if (P.dbg != nullptr && tid == 0 && wlin < 512) {  // (SM, start) of every CTA: scripts/timeline.py
+    unsigned smid; unsigned long long gt;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + 1536 + wlin * 4] = smid; P.dbg[4096 + 1536 + wlin * 4 + 1] = gt; P.dbg[4096 + 1536 + wlin * 4 + 3] = (unsigned)t;
+  }
   const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
   if (tid == 0 || (multi && tid == 32)) {
     mbar_wait(bar_ld1, 0);
@@ -915,6 +922,11 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
   IQLB_TSW(12);
   tc_fence_before();
   __syncthreads();
+  if (P.dbg != nullptr && tid == 0 && wlin < 512) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + 1536 + wlin * 4 + 2] = gt;
+  }
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 

@@ -69,3 +69,19 @@ if wv[:, 1].any():
     import numpy as np
     print(f"  CTA duration ns: median {np.median(dur):.0f}, max {max(dur)}; gap between CTAs on an SM: median {np.median(gaps):.0f};"
           f" kernel span {ends - t0} ns; CTAs per SM: {collections.Counter(len(v) for v in by_sm.values())}")
+
+ww = ts[4096 + 1536:4096 + 1536 + 4 * 512].reshape(512, 4)
+if ww[:, 1].any():
+    by_sm = collections.defaultdict(list)
+    for sm, a, b, net in ww:
+        if a:
+            by_sm[int(sm)].append((int(a), int(b), int(net)))
+    t0 = min(a for v in by_sm.values() for a, _, _ in v)
+    print("bwd_weight CTAs per SM: [start, end, net] ...")
+    for sm in sorted(by_sm)[:6]:
+        print(f"  SM {sm:3d}: " + "  ".join(f"[{a - t0:6d},{b - t0:6d},{n}]" for a, b, n in sorted(by_sm[sm])))
+    for net in range(4):
+        d = [b - a for v in by_sm.values() for a, b, n in v if n == net]
+        print(f"  net {net}: median CTA duration {np.median(d):.0f} ns (max {max(d)})")
+    ends = max(b for v in by_sm.values() for _, b, _ in v)
+    print(f"  kernel span {ends - t0} ns; CTAs per SM: {collections.Counter(len(v) for v in by_sm.values())}")

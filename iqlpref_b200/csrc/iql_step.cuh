@@ -106,6 +106,7 @@ struct BfParams {
   int64_t z_bytes;        // one dz image [B x 64]
   uint8_t *wimg, *xsa, *xnext, *h1, *h2, *dh2, *dh1, *dz;
   uint32_t *mask1, *mask2;  // [agent][train net][B][H/32]
+  uint32_t* bwd_flags;      // [agent][4] data-gradient tiles published to the weight-gradient CTAs of a merged launch
   __nv_bfloat16* gradh;     // [agent][Pstride] gradients of the step in bf16 (what the reference's autocast GEMMs emit)
   int opt_lpt;            // data-gradient kernel: actor tiles (the longest) first (IQLB_LPT)
   int dbg_z;              // timeline: blockIdx.z of the recording CTA

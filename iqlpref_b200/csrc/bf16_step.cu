@@ -1149,7 +1149,7 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   // hand-off: a producer must wait for its bulk stores to COMPLETE (not just to leave shared memory) before it raises
   // the flag, and a consumer pays an acquire load + fence before its first operand copy - the gap between CTAs on an
   // SM grows from 1.1 to 2-2.9 us (scripts/timeline.py).  Opt-in (IQLB_BWD_MERGED=1).
-  static const bool merged_env = getenv("IQLB_BWD_MERGED") && atoi(getenv("IQLB_BWD_MERGED")) != 0;
+  const bool merged_env = getenv("IQLB_BWD_MERGED") && atoi(getenv("IQLB_BWD_MERGED")) != 0;
   if (merged_env && !h->prof && !h->fused_adam && P.bwd_flags != nullptr && a0 == 0 && N == h->desc.n_agents) {
     const size_t smem = bwd_data_smem() > bwd_weight_smem(L.B) ? bwd_data_smem() : bwd_weight_smem(L.B);
     IQLB_CUDA(launch_pdl(bf16_bwd_merged_kernel, dim3(16 * N), dim3(320), smem, stream, pdl_enabled(8), P,

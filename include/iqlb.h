@@ -207,6 +207,30 @@ int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in
                        int32_t activation, int32_t n_tail, int32_t precision, float* out, float* preds_out,
                        uint8_t* sel_out, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * (6) Dataset preparation on the device (between the relabel and the replay buffer).
+ * --------------------------------------------------------------------------------------------- */
+
+/* return_reward_range (iql.py:344-360): episodes end at a terminal or after max_episode_steps rows; returns are
+ * summed in double in the reference's order.  min_max (device, 2 doubles) = min / max over the COMPLETED episodes;
+ * trj_lens (device, nullable, float[n]) = length of the episode each row belongs to (the trailing unfinished
+ * episode reports its current length, as the reference does).  All pointers are device pointers. */
+int iqlb_reward_range(const float* rewards, const uint8_t* terminals, int64_t n, int32_t max_episode_steps,
+                      double* min_max, float* trj_lens, void* stream);
+
+/* modify_reward (iql.py:363-401), in place on rewards[n] with numpy's op sequence and dtypes.
+ * env_kind 0: halfcheetah / hopper / walker2d; 1: antmaze with normalize_reward 0..7 (other environments are not
+ * touched by the reference: do not call). */
+int iqlb_modify_reward(float* rewards, const uint8_t* terminals, int64_t n, int32_t env_kind,
+                       int32_t normalize_reward, int32_t max_episode_steps, void* stream);
+
+/* compute_mean_std (iql.py:132-135): mean[dim], std[dim] = population std + eps over states[n][dim] (row stride
+ * ld floats), accumulated in double.  normalize_states (iql.py:138-139): in place (x - mean) / std. */
+int iqlb_state_mean_std(const float* states, int64_t n, int32_t dim, int32_t ld, float eps, float* mean, float* std,
+                        void* stream);
+int iqlb_normalize_states(float* states, int64_t n, int32_t dim, int32_t ld, const float* mean, const float* std,
+                          void* stream);
+
 /* Debug: CTA 0 of the following tensor-core relabel launches records clock64 stamps into buf (device memory,
  * >= 5*512 uint64; scripts/relabel_timeline.py decodes them).  NULL switches the recording off. */
 int iqlb_relabel_debug_timeline(unsigned long long* buf);

@@ -64,6 +64,10 @@ _SIGNATURES = {
     "iqlb_selftest_umma": ([_P, C.c_int64, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, _P, _P], C.c_int),
     "iqlb_selftest_mma_rate": ([C.c_int32, C.c_int32, C.c_int32, _P, _P], C.c_int),
+    "iqlb_reward_range": ([_P, _P, C.c_int64, C.c_int32, _P, _P, _P], C.c_int),
+    "iqlb_modify_reward": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P], C.c_int),
+    "iqlb_state_mean_std": ([_P, C.c_int64, C.c_int32, C.c_int32, C.c_float, _P, _P, _P], C.c_int),
+    "iqlb_normalize_states": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_keep_mask_scan": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P], C.c_int),
 }
 

@@ -676,6 +676,10 @@ class ImplicitQLearning:
         self.total_it = state_dict["total_it"]
 
 
+# dataset preparation (iql.py:132-139, 344-401) runs on the GPU; same names and signatures as the reference
+from .dataset_prep import (  # noqa: E402,F401
+    compute_mean_std, modify_reward, normalize_states, return_reward_range)
+
 # the relabelling half of the reference module lives in relabel.py; re-exported for drop-in imports
 from .relabel import (  # noqa: E402,F401
     RewardMLP, RewardPT, _build_mlp_reward_model, _discover_mr_snapshots, _mr_activations, _strip_compile_prefix,

@@ -136,6 +136,13 @@ int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host_batch, flo
  * generator, which cannot be mirrored: parity is tested by injecting this mask into the oracle. */
 int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p);
 
+/* Batched policy inference for evaluation (GaussianPolicy.act / DeterministicPolicy.act in eval mode, iql.py:476-482,
+ * 506-514, called from eval_actor :304-319): actions[a][i][:] = clamp(max_action * tanh(actor_a(states_a[i])), +-max_action)
+ * for every agent, fp32.  states: device, agent a reads n_rows x state_dim floats at states + a * agent_stride
+ * (agent_stride 0: all agents evaluate the same rows); actions: device [n_agents][n_rows][action_dim]. */
+int iqlb_agents_act(iqlb_agents* h, const float* states, int64_t agent_stride, int32_t n_rows, float max_action,
+                    float* actions, void* stream);
+
 /* Tell the library that the caller wrote params/target/it/rng directly (adopting modules, loading a
  * checkpoint, reseeding): precision 1 rebuilds the bf16 operand images of the weights and drops the
  * look-ahead batch; precision 0: no-op.

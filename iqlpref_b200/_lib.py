@@ -52,6 +52,7 @@ _SIGNATURES = {
     "iqlb_agents_debug_option": ([_P, C.c_int32, C.c_int32], C.c_int),
     "iqlb_agents_set_actor_dropout": ([_P, C.c_float], C.c_int),
     "iqlb_agents_debug_copy": ([_P, C.c_int32, _P, C.POINTER(C.c_int64), _P], C.c_int),
+    "iqlb_agents_act": ([_P, _P, C.c_int64, C.c_int32, C.c_float, _P, _P], C.c_int),
     "iqlb_polyak": ([_P, _P, C.c_int64, C.c_float, _P], C.c_int),
     "iqlb_relabel_mlp": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.c_int32,
                           C.c_int32, C.c_int32, _P, _P, _P, _P], C.c_int),

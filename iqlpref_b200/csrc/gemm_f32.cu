@@ -196,6 +196,7 @@ int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int
     case GEMM_FWD: return launch_mode<GEMM_FWD>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
     case GEMM_BWD_DATA: return launch_mode<GEMM_BWD_DATA>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
     case GEMM_FWD_KN: return launch_mode<GEMM_FWD_KN>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
+    case GEMM_LINEAR: return launch_mode<GEMM_LINEAR>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
     default: return launch_mode<GEMM_BWD_WEIGHT>(d_tasks, n_tasks, maxM, maxN, narrow_n, stream);
   }
 }

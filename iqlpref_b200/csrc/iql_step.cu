@@ -844,6 +844,60 @@ extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   return IQLB_OK;
 }
 
+// max_action * tanh-head output, clamped (GaussianPolicy.act / DeterministicPolicy.act, iql.py:476-482, 506-514)
+__global__ void __launch_bounds__(256) act_scale_clamp_kernel(float* __restrict__ a, int64_t n, float max_action) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = fminf(fmaxf(max_action * a[i], -max_action), max_action);
+}
+
+// Batched deterministic policy inference, the device half of eval_actor (iql.py:304-319): every agent's actor in eval
+// mode (no dropout) on its own block of states (or on one shared block), fp32 like the reference's evaluation.
+extern "C" int iqlb_agents_act(iqlb_agents* h, const float* states, int64_t agent_stride, int32_t n_rows,
+                               float max_action, float* actions, void* stream) {
+  IQLB_REQUIRE(h && states && actions, "null pointer");
+  IQLB_REQUIRE(n_rows >= 0 && agent_stride >= 0, "shape");
+  if (n_rows == 0) return IQLB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const Layout& L = h->L;
+  const int N = h->desc.n_agents;
+  float* hid = nullptr;       // H1 | H2, [N][n_rows][H] each
+  GemmTask* d_tasks = nullptr;
+  const int64_t hn = (int64_t)N * n_rows * L.H;
+  IQLB_CUDA(cudaMallocAsync((void**)&hid, (size_t)(2 * hn) * sizeof(float), st));
+  cudaError_t e = cudaMallocAsync((void**)&d_tasks, (size_t)(3 * N) * sizeof(GemmTask), st);
+  if (e != cudaSuccess) { cudaFreeAsync(hid, st); return fail(IQLB_ERR_NOMEM, "iqlb_agents_act: %s", cudaGetErrorString(e)); }
+  std::vector<GemmTask> tasks((size_t)3 * N);
+  for (int a = 0; a < N; ++a) {
+    const float* net = h->params + (int64_t)a * L.Pstride + L.off_a;
+    float* h1 = hid + (int64_t)a * n_rows * L.H;
+    float* h2 = hid + hn + (int64_t)a * n_rows * L.H;
+    GemmTask t{};
+    t.M = n_rows; t.scale = 1.f;
+    t.A = states + (int64_t)a * agent_stride; t.lda = L.S; t.Bm = net + L.w0(); t.ldb = L.S; t.bias = net + L.b0(L.S);
+    t.C = h1; t.ldc = L.H; t.N = L.H; t.K = L.S; t.act = IQLB_ACT_RELU;
+    tasks[a] = t;
+    t.A = h1; t.lda = L.H; t.Bm = net + L.w1(L.S); t.ldb = L.H; t.bias = net + L.b1(L.S); t.C = h2; t.K = L.H;
+    tasks[N + a] = t;
+    t.A = h2; t.Bm = net + L.w2(L.S); t.bias = net + L.b2(L.S, L.A); t.C = actions + (int64_t)a * n_rows * L.A;
+    t.ldc = L.A; t.N = L.A; t.act = IQLB_ACT_TANH;
+    tasks[2 * N + a] = t;
+  }
+  // (synchronous copy of a few KB: an evaluation call, not the training path)
+  e = cudaMemcpy(d_tasks, tasks.data(), tasks.size() * sizeof(GemmTask), cudaMemcpyHostToDevice);
+  int rc = e == cudaSuccess ? IQLB_OK : fail(IQLB_ERR_CUDA, "iqlb_agents_act: %s", cudaGetErrorString(e));
+  if (!rc) rc = launch_grouped_gemm(GEMM_LINEAR, d_tasks, N, n_rows, L.H, false, st);
+  if (!rc) rc = launch_grouped_gemm(GEMM_LINEAR, d_tasks + N, N, n_rows, L.H, false, st);
+  if (!rc) rc = launch_grouped_gemm(GEMM_LINEAR, d_tasks + 2 * N, N, n_rows, L.A, true, st);
+  if (!rc) {
+    const int64_t tot = (int64_t)N * n_rows * L.A;
+    act_scale_clamp_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(actions, tot, max_action);
+    if (cudaGetLastError() != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "act_scale_clamp_kernel launch failed%s", "");
+  }
+  cudaFreeAsync(hid, st);
+  cudaFreeAsync(d_tasks, st);
+  return rc;
+}
+
 extern "C" int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   IQLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");

@@ -488,6 +488,25 @@ class BatchedIQL:
         _lib.check(self.lib.iqlb_agents_step(self._h, _lib.ptr(batch_rows), _lib.stream_ptr(self.device)),
                    "iqlb_agents_step")
 
+    @torch.no_grad()
+    def act(self, states, max_action: float = 1.0) -> torch.Tensor:
+        """Deterministic actions of every agent's policy in eval mode (GaussianPolicy.act / DeterministicPolicy.act,
+        iql.py:476-482, 506-514; the device half of eval_actor :304-319): clamp(max_action * tanh(actor(s))).
+        `states`: [n, state_dim] (all agents evaluate the same rows) or [n_agents, n, state_dim]; returns
+        float32 [n_agents, n, action_dim] on the device, fp32 arithmetic like the reference's evaluation."""
+        x = torch.as_tensor(states, dtype=torch.float32).to(self.device).contiguous()
+        if x.ndim == 1:
+            x = x.reshape(1, -1)
+        if x.shape[-1] != self.S or x.ndim not in (2, 3) or (x.ndim == 3 and x.shape[0] != self.N):
+            raise ValueError(f"states must be [n, {self.S}] or [{self.N}, n, {self.S}]")
+        n = x.shape[-2]
+        out = torch.empty((self.N, n, self.A), dtype=torch.float32, device=self.device)
+        if n:
+            stride = 0 if x.ndim == 2 else n * self.S
+            _lib.check(self.lib.iqlb_agents_act(self._h, _lib.ptr(x), stride, n, float(max_action), _lib.ptr(out),
+                                                _lib.stream_ptr(self.device)), "iqlb_agents_act")
+        return out
+
     def train_host(self, host_rows: torch.Tensor, host_losses: torch.Tensor):
         """Step with the batch in pinned host memory; returns after the losses are on the host."""
         _lib.check(self.lib.iqlb_agents_step_host(self._h, _lib.ptr(host_rows), _lib.ptr(host_losses),

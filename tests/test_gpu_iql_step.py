@@ -321,3 +321,35 @@ def test_actor_dropout_needs_fp32_path():
     from iqlpref_b200 import iql as biql
     with pytest.raises(NotImplementedError):
         biql.BatchedIQL(29, 8, 1, batch_size=256, device="cuda:0", precision="bf16", actor_dropout=0.1)
+
+
+@pytest.mark.parametrize("det", [False, True])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_batched_policy_inference_matches_the_modules(det, precision):
+    """BatchedIQL.act = the reference policies' act() in eval mode (iql.py:476-482, 506-514), for every agent at once."""
+    from iqlpref_b200 import iql as biql
+    S, A, N, H = 29, 8, 3, 256
+    eng = biql.BatchedIQL(S, A, N, hidden_dim=H, batch_size=256, deterministic=det, precision=precision)
+    actors = []
+    for a in range(N):
+        torch.manual_seed(70 + a)
+        actor = (biql.DeterministicPolicy if det else biql.GaussianPolicy)(S, A, 2.5, H)
+        actors.append(actor)
+        eng.adopt(a, biql.TwinQ(S, A, H), biql.ValueFunction(S, H), actor, bind=False)
+    rng = np.random.default_rng(3)
+    shared = torch.tensor(rng.standard_normal((77, S)) * 3, dtype=torch.float32)
+    per_agent = torch.tensor(rng.standard_normal((N, 130, S)) * 3, dtype=torch.float32)
+    got_s, got_p = eng.act(shared, 2.5).cpu(), eng.act(per_agent, 2.5).cpu()
+    assert got_s.shape == (N, 77, A) and got_p.shape == (N, 130, A)
+    for a, actor in enumerate(actors):
+        actor.eval()
+        with torch.no_grad():
+            for x, got in ((shared, got_s[a]), (per_agent[a], got_p[a])):
+                out = actor(x)
+                mean = out if det else out.mean
+                want = torch.clamp(2.5 * mean, -2.5, 2.5)
+                torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(got_s[a, 5].numpy(), actor.act(shared[5].numpy(), "cpu"), rtol=1e-4, atol=1e-5)
+    assert eng.act(torch.zeros((0, S))).shape == (N, 0, A)
+    with pytest.raises(ValueError):
+        eng.act(torch.zeros((4, S + 1)))

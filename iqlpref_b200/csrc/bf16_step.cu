@@ -50,7 +50,11 @@ __global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __
   const int agent = P.agent0 + blockIdx.y;
   const int chunks_per_row = P.KXB * 8;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= L.B * chunks_per_row) return;
+  // Programmatic launch: nothing here depends on the predecessor (the previous step's Adam kernel) - the input images'
+  // readers finished before it started - so the packing runs under its tail; the wait sits at the END, so that this
+  // grid's completion still implies the predecessor's for the forward kernel (which reads the weight images).
+  pdl_launch();
+  if (i >= L.B * chunks_per_row) { pdl_wait(); return; }
   const int b = i / chunks_per_row, ch = i % chunks_per_row;
   const float* row = batch + ((int64_t)agent * L.B + b) * L.R;
   uint32_t sa[4], nx[4];
@@ -65,6 +69,7 @@ __global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __
   const int64_t off = image_off(L.B, b, ch * 8);
   *reinterpret_cast<uint4*>(P.xsa + (int64_t)agent * P.x_bytes + off) = make_uint4(sa[0], sa[1], sa[2], sa[3]);
   *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
+  pdl_wait();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1122,8 +1127,8 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
     pf.mark("shadow_refresh");
   }
   if (!packed) {
-    pack_x_kernel<<<dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), 256, 0, stream>>>(P, h->batch);
-    IQLB_LAUNCH_CHECK();
+    IQLB_CUDA(launch_pdl(pack_x_kernel, dim3((unsigned)((L.B * P.KXB * 8 + 255) / 256), N), dim3(256), 0, stream,
+                         pdl_enabled(1) && !h->prof, P, h->batch_src ? h->batch_src : (const float*)h->batch));
     pf.mark("pack_x");
   }
   static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
                             uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
                             uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0, unsigned long long* dbg,
                             const uint8_t* __restrict__ wimg, int64_t agent_w_bytes, int64_t net_bytes,
-                            __nv_bfloat16* __restrict__ gradh) {
+                            __nv_bfloat16* __restrict__ gradh, float* __restrict__ losses_snap) {
 #define IQLB_TSL(slot) do { if (dbg && blockIdx.x == 0) dbg[3072 + (slot)] = (unsigned long long)clock64(); } while (0)
   if (threadIdx.x == 0) IQLB_TSL(0);
   // per-warp partial sums of every reduced quantity: 0 vl | 1 ql | 2 al | 3..5 head bias grads (V, Q1, Q2)
@@ -249,13 +249,13 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
     float* g = grads + (int64_t)agent * L.Pstride;
     if (j == 0) {
       const float value_loss = tot * invB;
-      losses[agent * 3 + 0] = value_loss; atomicAdd(loss_sum + agent * 3 + 0, value_loss);  // one writer: a fire-and-forget add
+      losses[agent * 3 + 0] = value_loss; if (losses_snap) losses_snap[agent * 3 + 0] = value_loss; atomicAdd(loss_sum + agent * 3 + 0, value_loss);  // one writer: a fire-and-forget add
     } else if (j == 1) {
       const float q_loss = tot * invB * 0.5f;
-      losses[agent * 3 + 1] = q_loss; atomicAdd(loss_sum + agent * 3 + 1, q_loss);  // one writer: a fire-and-forget add
+      losses[agent * 3 + 1] = q_loss; if (losses_snap) losses_snap[agent * 3 + 1] = q_loss; atomicAdd(loss_sum + agent * 3 + 1, q_loss);  // one writer: a fire-and-forget add
     } else if (j == 2) {
       const float actor_loss = tot * invB;
-      losses[agent * 3 + 2] = actor_loss; atomicAdd(loss_sum + agent * 3 + 2, actor_loss);  // one writer: a fire-and-forget add
+      losses[agent * 3 + 2] = actor_loss; if (losses_snap) losses_snap[agent * 3 + 2] = actor_loss; atomicAdd(loss_sum + agent * 3 + 2, actor_loss);  // one writer: a fire-and-forget add
     } else {
       int64_t e = -1;
       if (j < 6) { if (bf) e = (j == 3 ? L.off_v + L.b2(L.S, 1) : (j == 4 ? L.off_q1 : L.off_q2) + L.b2(L.Dq, 1)); }
@@ -551,12 +551,12 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   int lb = (L.B + 31) / 32 * 32;
   if (lb + 32 <= 1024) lb += 32;  // bookkeeping warp
   IQLB_CUDA(launch_pdl(lb <= 320 ? loss_kernel<320> : loss_kernel<1024>, dim3(n), dim3(lb), 0, st, bf && pdl_enabled(4) && !h->prof, L, (const float*)h->params,
-                       h->hparams, (const float*)h->batch, (const float*)h->head_out, h->d_out, h->grads, h->losses,
+                       h->hparams, (const float*)((bf && h->batch_src) ? h->batch_src : h->batch), (const float*)h->head_out, h->d_out, h->grads, h->losses,
                        h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0, bf ? bp->dz : (uint8_t*)nullptr,
                        bf ? bp->z_bytes : (int64_t)0, a0, bf ? bp->dbg : (unsigned long long*)nullptr,
                        (bf && bp->opt_pf3) ? (const uint8_t*)bp->wimg : (const uint8_t*)nullptr,
                        bf ? bp->agent_w_bytes : (int64_t)0, bf ? bp->net_bytes : (int64_t)0,
-                       bf ? bp->gradh : (__nv_bfloat16*)nullptr));
+                       bf ? bp->gradh : (__nv_bfloat16*)nullptr, h->loss_snap_cur));
   pf.mark("loss");
   if (bf) {
     if ((rc = bf16_step_gemms_bwd(h, a0, n, pf, st))) return rc;
@@ -732,10 +732,13 @@ extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
   if (h->copy_stream) {
     cudaStreamSynchronize(h->copy_stream);
     cudaStreamDestroy(h->copy_stream);
+    if (h->d2h_stream) { cudaStreamSynchronize(h->d2h_stream); cudaStreamDestroy(h->d2h_stream); }
     for (int i = 0; i < 2; ++i) {
       if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
       if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+      if (h->ev_step[i]) cudaEventDestroy(h->ev_step[i]);
       cudaFree(h->stage[i]);
+      cudaFree(h->loss_snap[i]);
       if (h->host_loss[i]) cudaFreeHost(h->host_loss[i]);
     }
   }
@@ -795,10 +798,13 @@ extern "C" int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host
   const size_t lbytes = (size_t)h->desc.n_agents * 3 * sizeof(float);
   if (!h->copy_stream) {
     IQLB_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    IQLB_CUDA(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 2; ++i) {
       IQLB_CUDA(cudaEventCreateWithFlags(&h->ev_h2d[i], cudaEventDisableTiming));
       IQLB_CUDA(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+      IQLB_CUDA(cudaEventCreateWithFlags(&h->ev_step[i], cudaEventDisableTiming));
       IQLB_CUDA(cudaMalloc((void**)&h->stage[i], bytes));
+      IQLB_CUDA(cudaMalloc((void**)&h->loss_snap[i], lbytes));
       IQLB_CUDA(cudaMallocHost((void**)&h->host_loss[i], lbytes));
     }
   }
@@ -808,11 +814,22 @@ extern "C" int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host
     IQLB_CUDA(cudaMemcpyAsync(h->stage[s], host_batch, bytes, cudaMemcpyHostToDevice, h->copy_stream));
     IQLB_CUDA(cudaEventRecord(h->ev_h2d[s], h->copy_stream));
     IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_h2d[s], 0));
-    IQLB_CUDA(cudaMemcpyAsync(h->batch, h->stage[s], bytes, cudaMemcpyDeviceToDevice, st));
+    // precision 1 reads the staged rows in place (the packing and the loss kernel take the pointer); the fp32 path's
+    // GEMM tasks are bound to h->batch
+    if (h->desc.precision == 1) h->batch_src = h->stage[s];
+    else IQLB_CUDA(cudaMemcpyAsync(h->batch, h->stage[s], bytes, cudaMemcpyDeviceToDevice, st));
+    h->loss_snap_cur = h->loss_snap[s];
     int rc = step_device(h, false, st);
+    h->batch_src = nullptr;
+    h->loss_snap_cur = nullptr;
     if (rc) return rc;
-    IQLB_CUDA(cudaMemcpyAsync(h->host_loss[s], h->losses, lbytes, cudaMemcpyDeviceToHost, st));
-    IQLB_CUDA(cudaEventRecord(h->ev_done[s], st));
+    // the losses leave on the copy stream, so that the caller's stream carries kernels only (a copy node between the
+    // optimizer kernel and the next step's first kernel would serialise their hand-over)
+    // (read from the per-parity snapshot the loss kernel wrote: `losses` itself is rewritten by the next step)
+    IQLB_CUDA(cudaEventRecord(h->ev_step[s], st));
+    IQLB_CUDA(cudaStreamWaitEvent(h->d2h_stream, h->ev_step[s], 0));
+    IQLB_CUDA(cudaMemcpyAsync(h->host_loss[s], h->loss_snap[s], lbytes, cudaMemcpyDeviceToHost, h->d2h_stream));
+    IQLB_CUDA(cudaEventRecord(h->ev_done[s], h->d2h_stream));
   }
   const bool flush = host_batch == nullptr;
   const long long prev = flush ? h->pipe_k - 1 : h->pipe_k - 1;  // the step whose losses are returned

@@ -198,11 +198,16 @@ struct iqlb_agents {
   // pipelined host feed (iqlb_agents_step_host_pipelined): H2D of step k+1 on copy_stream under the update of step k
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {}, ev_done[2] = {};
+  cudaStream_t d2h_stream = nullptr;  // loss read-back
+  float* loss_snap[2] = {};           // per-parity device copy of the step's losses, written by the loss kernel
+  float* loss_snap_cur = nullptr;
+  cudaEvent_t ev_step[2] = {};  // step k enqueued on the caller's stream (the loss read-back waits for it)
   float* stage[2] = {};
   float* host_loss[2] = {};  // pinned
   long long pipe_k = 0;
   // L2 zig-zag: consecutive kernels walk the agents in opposite directions, so a consumer starts with what its
   // producer wrote last (still in L2); the direction flips every step (IQLB_ZIGZAG=0 turns it off)
+  const float* batch_src = nullptr;  // explicit-batch step reads its rows from here instead of `batch` (pipelined host feed, precision 1)
   int zig = 0;
   // look-ahead sampling (precision 1): the Philox gather + packing of step t+1 runs on pre_stream under the
   // HBM-bound optimizer kernel of step t (its consumers of step t - loss, forward, weight gradients - are done and

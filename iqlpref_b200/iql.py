@@ -20,7 +20,7 @@ import math
 import os
 import uuid
 from dataclasses import dataclass
-from typing import Any, Dict, List, Optional, Sequence
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -339,6 +339,21 @@ def _check_two_hidden(lins: Sequence[nn.Linear], what: str):
 # --------------------------------------------------------------------------------------------
 # N independent agents
 # --------------------------------------------------------------------------------------------
+def _strip_compile_prefix_key(key: str) -> str:
+    """`torch.compile`d modules (iql.py:1523-1527) prefix their state_dict keys with `_orig_mod.`."""
+    return key[len("_orig_mod."):] if key.startswith("_orig_mod.") else key
+
+
+def _to_cpu(obj):
+    if isinstance(obj, torch.Tensor):
+        return obj.detach().cpu()
+    if isinstance(obj, dict):
+        return {k: _to_cpu(v) for k, v in obj.items()}
+    if isinstance(obj, list):
+        return [_to_cpu(v) for v in obj]
+    return obj
+
+
 class BatchedIQL:
     """N independent IQL agents (same network shapes, per-agent hyper-parameters, seeds and
     reward labels) advanced together.  Agent i obeys the contract of the reference's
@@ -549,6 +564,110 @@ class BatchedIQL:
                                                    _lib.stream_ptr(self.device)), "debug")
         return out
 
+    # ---- the reference's checkpoint format, agent by agent (iql.py:664-688, 1519-1521, 1557-1561) ------
+    def checkpoint_keys(self, part: str) -> List[Tuple[str, str]]:
+        """(packed key, state_dict name) of `part` in {"qf", "vf", "actor"}, in `nn.Module.parameters()` order -
+        the order torch's optimizer state is indexed by.  The Gaussian policy registers `log_std` before its
+        MLP (iql.py:464-465), so `log_std` is parameter 0 of the actor optimizer."""
+        nets = {"qf": (("q1", "q1.net"), ("q2", "q2.net")), "vf": (("v", "v.net"),), "actor": (("actor", "net.net"),)}[part]
+        out = [("log_std", "log_std")] if part == "actor" and not self.deterministic else []
+        for net, prefix in nets:
+            for i in range(3):
+                out += [(f"{net}.w{i}", f"{prefix}.{2 * i}.weight"), (f"{net}.b{i}", f"{prefix}.{2 * i}.bias")]
+        return out
+
+    def _optimizer_state_dict(self, agent: int, part: str, lr: float, step: int, fused: Optional[bool]) -> Dict[str, Any]:
+        keys = self.checkpoint_keys(part)
+        # param_groups as the installed torch writes them for Adam(params, lr=lr[, fused=True]) (iql.py:1481-1491)
+        dummy = [nn.Parameter(torch.zeros(1)) for _ in keys]
+        sd = torch.optim.Adam(dummy, lr=lr).state_dict()
+        sd["param_groups"][0]["fused"] = fused
+        state = {}
+        if step > 0:
+            for i, (key, _) in enumerate(keys):
+                state[i] = {"step": torch.tensor(float(step)),
+                            "exp_avg": self.view(self.exp_avg, agent, key).detach().clone(),
+                            "exp_avg_sq": self.view(self.exp_avg_sq, agent, key).detach().clone()}
+        sd["state"] = state
+        return sd
+
+    def agent_state_dict(self, agent: int, total_it: Optional[int] = None, fused: Optional[bool] = True) -> Dict[str, Any]:
+        """What `ImplicitQLearning.state_dict()` of the reference returns for agent `agent` (iql.py:664-674): the
+        three module state_dicts, the three `torch.optim.Adam` state_dicts (state indexed in parameter order), the
+        `CosineAnnealingLR` state_dict and `total_it`.  The reference's `load_state_dict` accepts it unchanged."""
+        hp = dict(zip(self.HP_KEYS, self.hp_host[agent]))
+        it = int(self.it[agent].item())
+        lr_a = float(self.actor_lr[agent].item())
+        mod = lambda part: {name: self.view(self.params, agent, key).detach().clone()
+                            for key, name in self.checkpoint_keys(part)}
+        a_opt = self._optimizer_state_dict(agent, "actor", lr_a, it, fused)
+        a_opt["param_groups"][0]["initial_lr"] = hp["actor_lr"]  # added by the scheduler (lr_scheduler.py, _initial_step)
+        return {
+            "qf": mod("qf"),
+            "q_optimizer": self._optimizer_state_dict(agent, "qf", hp["qf_lr"], it, fused),
+            "vf": mod("vf"),
+            "v_optimizer": self._optimizer_state_dict(agent, "vf", hp["vf_lr"], it, fused),
+            "actor": mod("actor"),
+            "actor_optimizer": a_opt,
+            "actor_lr_schedule": {"T_max": int(hp["max_steps"]), "eta_min": 0.0, "base_lrs": [hp["actor_lr"]],
+                                  "last_epoch": it, "_step_count": it + 1, "_is_initial": False,
+                                  "_get_lr_called_within_step": False, "_last_lr": [lr_a]},
+            "total_it": it if total_it is None else int(total_it),
+        }
+
+    def load_agent_state_dict(self, agent: int, state_dict: Dict[str, Any], sync: bool = True) -> int:
+        """Resume agent `agent` from a checkpoint of the reference (or of `agent_state_dict`): parameters, Adam
+        moments and step, the scheduled actor lr; the target becomes a copy of qf, as iql.py:679 does on load.
+        Returns the checkpoint's `total_it`."""
+        parts = (("qf", "q_optimizer"), ("vf", "v_optimizer"), ("actor", "actor_optimizer"))
+        mods = {}
+        for part, _ in parts:  # validate everything before the first write
+            mods[part] = mod = {_strip_compile_prefix_key(k): v for k, v in state_dict[part].items()}
+            missing = [name for _, name in self.checkpoint_keys(part) if name not in mod]
+            if missing:
+                raise KeyError(f"checkpoint['{part}'] lacks {missing}")
+            for key, name in self.checkpoint_keys(part):
+                want = tuple(self.view(self.params, agent, key).shape)
+                if tuple(mod[name].shape) != want:
+                    raise ValueError(f"{part}.{name}: checkpoint shape {tuple(mod[name].shape)} != {want}")
+        with torch.no_grad():
+            step = 0
+            for part, opt in parts:
+                mod = mods[part]
+                for i, (key, name) in enumerate(self.checkpoint_keys(part)):
+                    self.view(self.params, agent, key).copy_(mod[name].to(self.device, torch.float32))
+                    st = state_dict[opt]["state"].get(i)
+                    m, v = self.view(self.exp_avg, agent, key), self.view(self.exp_avg_sq, agent, key)
+                    if st is None:
+                        m.zero_(); v.zero_()
+                    else:
+                        m.copy_(st["exp_avg"].to(self.device, torch.float32))
+                        v.copy_(st["exp_avg_sq"].to(self.device, torch.float32))
+                        step = int(float(st["step"]))
+            self.target[agent, :self.PQ] = self.params[agent, :self.PQ]
+            self.it[agent] = step
+            self.actor_lr[agent] = float(state_dict["actor_optimizer"]["param_groups"][0]["lr"])
+        if sync:
+            self._sync_shadow()
+        return int(state_dict["total_it"])
+
+    def save_checkpoints(self, paths: Sequence[str], total_it: Optional[int] = None):
+        """One reference-format file per agent (`torch.save(trainer.state_dict(), checkpoint_{t}.pt)`, iql.py:1557-1561);
+        `paths[i]` is agent i's file."""
+        if len(paths) != self.N:
+            raise ValueError(f"{self.N} agents need {self.N} paths")
+        for a, p in enumerate(paths):
+            sd = self.agent_state_dict(a, total_it)
+            torch.save(_to_cpu(sd), p)
+
+    def load_checkpoints(self, paths: Sequence[str]) -> List[int]:
+        if len(paths) != self.N:
+            raise ValueError(f"{self.N} agents need {self.N} paths")
+        its = [self.load_agent_state_dict(a, torch.load(p, map_location="cpu", weights_only=False), sync=False)
+               for a, p in enumerate(paths)]
+        self._sync_shadow()
+        return its
+
     # ---- export in the oracle's naming (tests) -----------------------------------------------------
     def export(self, agent: int) -> Dict[str, np.ndarray]:
         d = {}
@@ -646,25 +765,21 @@ class ImplicitQLearning:
         sd["param_groups"][0]["lr"] = lr
         return sd
 
-    def _keys(self, nets: Sequence[str]) -> List[str]:
-        keys = []
-        for net in nets:
-            for i in range(3):
-                keys += [f"{net}.w{i}", f"{net}.b{i}"]
-        return keys
+    def _keys(self, part: str) -> List[str]:
+        """Packed keys of `part` in optimizer (= `parameters()`) order: `log_std` leads the Gaussian actor."""
+        return [key for key, _ in self._engine.checkpoint_keys(part)]
 
     def state_dict(self) -> Dict[str, Any]:
         eng = self._engine
-        a_keys = self._keys(["actor"]) + ([] if eng.deterministic else ["log_std"])
         lr_a = float(eng.actor_lr[0].item())
         it = int(eng.it[0].item())
         return {
             "qf": self.qf.state_dict(),
-            "q_optimizer": self._opt_state(self.q_optimizer, self._keys(["q1", "q2"]), self._hp["qf_lr"]),
+            "q_optimizer": self._opt_state(self.q_optimizer, self._keys("qf"), self._hp["qf_lr"]),
             "vf": self.vf.state_dict(),
-            "v_optimizer": self._opt_state(self.v_optimizer, self._keys(["v"]), self._hp["vf_lr"]),
+            "v_optimizer": self._opt_state(self.v_optimizer, self._keys("vf"), self._hp["vf_lr"]),
             "actor": self.actor.state_dict(),
-            "actor_optimizer": self._opt_state(self.actor_optimizer, a_keys, lr_a),
+            "actor_optimizer": self._opt_state(self.actor_optimizer, self._keys("actor"), lr_a),
             "actor_lr_schedule": {"T_max": self._max_steps, "eta_min": 0.0, "base_lrs": [self._hp["actor_lr"]],
                                   "last_epoch": it, "_step_count": it + 1, "_is_initial": False,
                                   "_get_lr_called_within_step": False, "_last_lr": [lr_a]},
@@ -672,27 +787,9 @@ class ImplicitQLearning:
         }
 
     def load_state_dict(self, state_dict: Dict[str, Any]):
-        eng = self._engine
-        self.qf.load_state_dict(state_dict["qf"])
-        self.vf.load_state_dict(state_dict["vf"])
-        self.actor.load_state_dict(state_dict["actor"])
-        with torch.no_grad():  # iql.py:679: the target is re-created from qf on load
-            eng.target[0, :eng.PQ] = eng.params[0, :eng.PQ]
-        a_keys = self._keys(["actor"]) + ([] if eng.deterministic else ["log_std"])
-        step = 0
-        for sd, keys in ((state_dict["q_optimizer"], self._keys(["q1", "q2"])),
-                         (state_dict["v_optimizer"], self._keys(["v"])), (state_dict["actor_optimizer"], a_keys)):
-            for i, key in enumerate(keys):
-                st = sd["state"].get(i)
-                if st is None:
-                    continue
-                eng.view(eng.exp_avg, 0, key).copy_(st["exp_avg"].to(eng.device))
-                eng.view(eng.exp_avg_sq, 0, key).copy_(st["exp_avg_sq"].to(eng.device))
-                step = int(float(st["step"]))
-        eng.it.fill_(step)
-        eng.actor_lr.fill_(float(state_dict["actor_optimizer"]["param_groups"][0]["lr"]))
-        eng._sync_shadow()
-        self.total_it = state_dict["total_it"]
+        """iql.py:676-688 (the target is re-created from qf on load, :679).  The module parameters are views of the
+        packed storage, so loading agent slot 0 updates `self.qf / vf / actor / q_target` in place."""
+        self.total_it = self._engine.load_agent_state_dict(0, state_dict)
 
 
 # dataset preparation (iql.py:132-139, 344-401) runs on the GPU; same names and signatures as the reference

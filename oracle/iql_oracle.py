@@ -129,9 +129,10 @@ class IQLOracle:
             self.log_std = log_std.detach().clone().float().requires_grad_(True)
         self.v_params = _flat(self.v)
         self.q_params = _flat(self.q1) + _flat(self.q2)
-        # GaussianPolicy registers net.* then log_std?  No: `self.net` is assigned before
-        # `self.log_std` (iql.py:463-468), so parameters() yields net params then log_std.
-        self.a_params = _flat(self.actor) + ([self.log_std] if self.log_std is not None else [])
+        # nn.Module.parameters() yields a module's own parameters before its children's, so torch's actor optimizer
+        # sees log_std first (iql.py:463-468); Adam treats tensors independently, the order matters only for the
+        # checkpoint's state indices (load_checkpoint below)
+        self.a_params = ([self.log_std] if self.log_std is not None else []) + _flat(self.actor)
         self.v_opt = _Adam(self.v_params, hp.vf_lr)
         self.q_opt = _Adam(self.q_params, hp.qf_lr)
         self.a_opt = _Adam(self.a_params, hp.actor_lr)
@@ -192,6 +193,34 @@ class IQLOracle:
             self.sched_epoch += 1
             self.a_opt.lr = cosine_lr_next(self.a_opt.lr, hp.actor_lr, self.sched_epoch, hp.max_steps)
         return out
+
+    # -- resume -------------------------------------------------------------------------
+    @torch.no_grad()
+    def load_checkpoint(self, sd: Dict) -> None:
+        """ImplicitQLearning.load_state_dict (iql.py:676-688) on the file the training loop writes
+        (`torch.save(trainer.state_dict(), ...)`, :1557-1561): modules, Adam moments and step (state index =
+        position in `parameters()`), the scheduler's epoch and the lr it left in the actor optimizer; the target
+        is re-created from qf (:679)."""
+        mods = (("qf", (("q1.net", self.q1), ("q2.net", self.q2))), ("vf", (("v.net", self.v),)),
+                ("actor", (("net.net", self.actor),)))
+        for part, nets in mods:
+            for prefix, net in nets:
+                for i, (w, b) in enumerate(net):
+                    w.copy_(sd[part][f"{prefix}.{2 * i}.weight"])
+                    b.copy_(sd[part][f"{prefix}.{2 * i}.bias"])
+        if self.log_std is not None:
+            self.log_std.copy_(sd["actor"]["log_std"])
+        for opt, key in ((self.q_opt, "q_optimizer"), (self.v_opt, "v_optimizer"), (self.a_opt, "actor_optimizer")):
+            for i in range(len(opt.params)):
+                st = sd[key]["state"][i]
+                opt.exp_avg[i].copy_(st["exp_avg"])
+                opt.exp_avg_sq[i].copy_(st["exp_avg_sq"])
+                opt.step_count = int(float(st["step"]))
+            opt.lr = float(sd[key]["param_groups"][0]["lr"])
+        self.qt1 = [(w.detach().clone(), b.detach().clone()) for w, b in self.q1]
+        self.qt2 = [(w.detach().clone(), b.detach().clone()) for w, b in self.q2]
+        self.sched_epoch = int(sd["actor_lr_schedule"]["last_epoch"])
+        self.total_it = int(sd["total_it"])
 
     # -- export -------------------------------------------------------------------------
     def export(self) -> Dict[str, np.ndarray]:

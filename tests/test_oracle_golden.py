@@ -155,3 +155,42 @@ def test_empirical_cvar(rel):
     s = rel["cvar.samples"]
     got = [ro.cvar_reduce(s[:, None], a)[0] for a in (0.0, 0.5, 0.9, 0.95, 0.99)]
     np.testing.assert_allclose(got, rel["cvar.values"], rtol=1e-6)
+
+
+# ---- checkpoint format (iql.py:664-688): the oracle resumes from the reference's own file ---------------------
+def test_oracle_resumes_from_the_reference_checkpoint(golden_dir):
+    import yaml
+    from oracle.iql_oracle import IQLOracle, OracleHParams
+    d = np.load(os.path.join(golden_dir, "iql_small_ckpt_resume.npz"))
+    sd = torch.load(os.path.join(golden_dir, "iql_small_ckpt.pt"), map_location="cpu", weights_only=False)
+    hp = yaml.safe_load(str(d["hp"]))
+    S, A, H = 17, 6, 64
+    z = lambda o, i: (torch.zeros(o, i), torch.zeros(o))
+    net = lambda i, o: [z(H, i), z(H, H), z(o, H)]
+    orc = IQLOracle(net(S + A, 1), net(S + A, 1), net(S, 1), net(S, A), torch.zeros(A), OracleHParams(**hp), mode="fp32")
+    orc.load_checkpoint(sd)
+    assert orc.total_it == int(d["k_saved"]) and orc.a_opt.step_count == int(d["k_saved"])
+    t = {n: torch.from_numpy(d[f"table.{n}"]) for n in ("obs", "act", "rew", "next_obs", "done")}
+    for k in range(int(d["k_saved"]), d["idx"].shape[0]):
+        i = torch.from_numpy(d["idx"][k])
+        out = orc.step(t["obs"][i], t["act"][i], t["rew"][i], t["next_obs"][i], t["done"][i])
+        np.testing.assert_allclose([out["value_loss"], out["q_loss"], out["actor_loss"]], d["losses"][k], rtol=1e-5)
+    e = orc.export()
+    np.testing.assert_allclose(e["q1.w1"], d["final.qf.q1.net.2.weight"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(e["qt2.w0"], d["final.q_target.q2.net.0.weight"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(e["log_std"], d["final.actor.log_std"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(orc.a_opt.exp_avg[0].numpy(), d["final.actor_optimizer.0.exp_avg"], rtol=1e-4, atol=1e-9)
+    assert abs(orc.a_opt.lr - float(d["lr_final"])) < 1e-15
+
+
+def test_mirror_modules_enumerate_parameters_like_the_reference_checkpoint(golden_dir):
+    """The optimizer state of a checkpoint is indexed by position in `parameters()`: the host mirror's modules must
+    enumerate names in the order the reference's file holds them (`log_std` first for the Gaussian policy)."""
+    from iqlpref_b200 import iql as biql
+    sd = torch.load(os.path.join(golden_dir, "iql_small_ckpt.pt"), map_location="cpu", weights_only=False)
+    mods = {"qf": biql.TwinQ(17, 6, 64), "vf": biql.ValueFunction(17, 64), "actor": biql.GaussianPolicy(17, 6, 1.0, 64)}
+    for part, opt in (("qf", "q_optimizer"), ("vf", "v_optimizer"), ("actor", "actor_optimizer")):
+        names = [n for n, _ in mods[part].named_parameters()]
+        assert names == list(sd[part])
+        for i, (n, prm) in enumerate(mods[part].named_parameters()):
+            assert tuple(sd[opt]["state"][i]["exp_avg"].shape) == tuple(prm.shape) == tuple(sd[part][n].shape)

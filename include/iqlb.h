@@ -268,6 +268,39 @@ int iqlb_relabel_pt(const iqlb_pt_desc* d, const float* weights, const float* ob
 int iqlb_pt_forward(const iqlb_pt_desc* d, const float* weights, const float* states, const float* actions,
                     const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * MR preference-model training step: replaces MRTrainer.train / .evaluation
+ * (gp_reward-priors/optbnn/training/training.py:27-72, 74-114) with bt_pool_logit
+ * (optbnn/utils/util.py:356-364), RewardMLP (optbnn/bnn/nets/mlp.py:73-111) and
+ * torch.optim.Adam(net.parameters(), lr) (scripts_mr/run_mr_training.py:105).
+ *   params / exp_avg / exp_avg_sq : device float[PM] in the member layout of iqlb_relabel_mlp
+ *       (W0[d_in][w0] b0[w0] ... Wout[w_last][1] bout[1]); owned by the caller, updated in place
+ *   states{1,2} [B][T][S], actions{1,2} [B][T][A], mask{1,2} [B][T] (0/1), labels [B][2] : device fp32
+ *   out2 (device float[2], nullable): mean soft-label cross entropy, accuracy (argmax of pooled
+ *       logits vs argmax of labels)
+ *   grad_out (nullable): device float[PM], the gradient the step used
+ *   adam_step : 1 for the first step (the value of Adam's `step` after this update)
+ *   pool_mean : 1 = bt_pool "mean" (masked mean), 0 = "sum"
+ * A call with lr == 0 and exp_avg == NULL computes loss and gradients only.  No host sync, except on
+ * the first call for a new row count (the weight-gradient task table is rebuilt).
+ * --------------------------------------------------------------------------------------------- */
+typedef struct iqlb_mr_trainer iqlb_mr_trainer;
+int iqlb_mr_create(int32_t d_in, const int32_t* host_widths, int32_t depth, int32_t activation,
+                   int32_t pool_mean, int64_t max_rows /* 2*B*T */, iqlb_mr_trainer** out);
+int iqlb_mr_destroy(iqlb_mr_trainer* h);
+int iqlb_mr_param_count(const iqlb_mr_trainer* h, int64_t* n_params);
+int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
+                       const float* states1, const float* actions1, const float* mask1,
+                       const float* states2, const float* actions2, const float* mask2,
+                       const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                       float beta1, float beta2, float eps, int64_t adam_step, float* out2,
+                       float* grad_out, void* stream);
+/* MRTrainer.evaluation: forward + loss/accuracy only; pred_out (nullable) float[2*B*T] per-row rewards */
+int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float* states1, const float* actions1,
+                 const float* mask1, const float* states2, const float* actions2, const float* mask2,
+                 const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float* out2,
+                 float* pred_out, void* stream);
+
 /* Diagnostic: one CTA computes D[128][n] (fp32, row-major) = A * B with tcgen05.mma from two bf16
  * operand images (128-byte-swizzled column blocks of 64, see csrc/umma.cuh).  a_mn / b_mn select
  * MN-major (1: image columns are the M/N index, starting at column a_off) or K-major (0: image rows

@@ -69,6 +69,12 @@ _SIGNATURES = {
     "iqlb_modify_reward": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P], C.c_int),
     "iqlb_state_mean_std": ([_P, C.c_int64, C.c_int32, C.c_int32, C.c_float, _P, _P, _P], C.c_int),
     "iqlb_normalize_states": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
+    "iqlb_mr_create": ([C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(_P)], C.c_int),
+    "iqlb_mr_destroy": ([_P], C.c_int),
+    "iqlb_mr_param_count": ([_P, C.POINTER(C.c_int64)], C.c_int),
+    "iqlb_mr_train_step": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                            C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64, _P, _P, _P], C.c_int),
+    "iqlb_mr_eval": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_keep_mask_scan": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P], C.c_int),
 }
 

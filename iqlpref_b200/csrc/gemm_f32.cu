@@ -132,7 +132,9 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
       } else if (MODE == GEMM_BWD_DATA) {
         v = (__ldg(t.mask + (int64_t)m * t.ldc + n) > 0.f) ? v * t.scale : 0.f;
       } else if (MODE == GEMM_FWD_KN) {
-        v = apply_act(t.act, fmaf(t.scale, v, __ldg(t.bias + n)));
+        v = fmaf(t.scale, v, __ldg(t.bias + n));
+        if (t.pre != nullptr) t.pre[(int64_t)m * t.ldc + n] = v;
+        v = apply_act(t.act, v);
       } else if (MODE == GEMM_LINEAR) {  // nn.Linear: act(A W^T + bias) (+ residual, carried in t.mask)
         v = apply_act(t.act, v + (t.bias ? __ldg(t.bias + n) : 0.f));
         if (t.mask != nullptr) v += t.mask[(int64_t)m * t.ldc + n];

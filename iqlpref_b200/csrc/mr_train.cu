@@ -1,0 +1,432 @@
+// Bradley-Terry preference-model training step of the MR reward model:
+//   MRTrainer.train / .evaluation   gp_reward-priors/optbnn/training/training.py:27-72, 74-114
+//   bt_pool_logit                   gp_reward-priors/optbnn/utils/util.py:356-364
+//   RewardMLP forward               gp_reward-priors/optbnn/bnn/nets/mlp.py:73-111, layers/linear.py:34-47
+//   optimizer                       torch.optim.Adam(net.parameters(), lr) (scripts_mr/run_mr_training.py:105)
+// One call = forward over the 2*B*T rows of both segments, masked pooling, soft-label cross entropy, backward
+// and Adam, all on the caller's stream, no host synchronisation.  fp32 FFMA GEMMs (the reference trains in fp32,
+// no autocast).  Weight gradients are split over row chunks (one CTA per chunk and tile) and summed in a fixed
+// order by the kernel that also applies Adam, so a step is deterministic.
+#include <vector>
+
+#include "iql_step.cuh"
+
+namespace iqlb {
+
+__device__ __forceinline__ float act_grad(int act, float z) {
+  switch (act) {
+    case IQLB_ACT_RELU: return z > 0.f ? 1.f : 0.f;
+    case IQLB_ACT_TANH: { const float t = tanhf(z); return 1.f - t * t; }
+    case IQLB_ACT_COS: return -sinf(z);
+    case IQLB_ACT_SIN: return cosf(z);
+    case IQLB_ACT_LINEAR: return 1.f;
+    case IQLB_ACT_RBF: return -2.f * z * expf(-z * z);
+    case IQLB_ACT_SWISH: { const float s = 1.0f / (1.0f + expf(-z)); return s * (1.f + z * (1.f - s)); }
+    case IQLB_ACT_SOFTPLUS: return z > 20.f ? 1.f : 1.0f / (1.0f + expf(-z));
+    case IQLB_ACT_LEAKY_RELU: return z > 0.f ? 1.f : 0.01f;
+    default: return 1.f;
+  }
+}
+
+// X[(seg*B + b)*T + t] = cat(states_seg[b,t,:], actions_seg[b,t,:])   (training.py:47-54)
+__global__ void mr_pack_kernel(const float* __restrict__ s1, const float* __restrict__ a1,
+                               const float* __restrict__ s2, const float* __restrict__ a2, int64_t BT, int S, int A,
+                               float* __restrict__ X) {
+  const int D = S + A;
+  const int64_t total = 2 * BT * D;
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = e / D;
+    const int c = (int)(e % D);
+    const int seg = row >= BT;
+    const int64_t r = row - (seg ? BT : 0);
+    const float* s = seg ? s2 : s1;
+    const float* a = seg ? a2 : a1;
+    X[e] = c < S ? __ldg(s + r * S + c) : __ldg(a + r * A + (c - S));
+  }
+}
+
+// pred[m] = scale * <H[m,:], w_out> + b_out, one warp per row
+__global__ void mr_head_kernel(const float* __restrict__ H, int ld, int w, const float* __restrict__ w_out,
+                               const float* __restrict__ b_out, float scale, int64_t M, float* __restrict__ pred) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (row >= M) return;
+  float acc = 0.f;
+  for (int k = lane; k < w; k += 32) acc = fmaf(__ldg(H + row * ld + k), __ldg(w_out + k), acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) pred[row] = fmaf(scale, acc, __ldg(b_out));
+}
+
+// Masked pooling, soft-label cross entropy (mean over pairs), accuracy, and the gradient of the loss with
+// respect to every per-row prediction.  One block; thread b walks its pair's T rows of both segments.
+//   rowgrad[m] = dL/dpred[m] = dlogit[b, seg] * mask[b, t] / n[b, seg]   (0 where pred*mask is NaN: nansum)
+__global__ void __launch_bounds__(256) mr_loss_kernel(const float* __restrict__ pred, const float* __restrict__ m1,
+                                                      const float* __restrict__ m2, const float* __restrict__ labels,
+                                                      int B, int T, int pool_mean, float* __restrict__ rowgrad,
+                                                      float* __restrict__ out2) {
+  __shared__ float s_loss[256], s_acc[256];
+  float loss = 0.f, acc = 0.f;
+  const int64_t BT = (int64_t)B * T;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float logit[2], ninv[2];
+#pragma unroll
+    for (int seg = 0; seg < 2; ++seg) {
+      const float* mk = (seg ? m2 : m1) + (int64_t)b * T;
+      const float* pr = pred + seg * BT + (int64_t)b * T;
+      float s = 0.f, n = 0.f;
+      for (int t = 0; t < T; ++t) {
+        const float m = __ldg(mk + t), v = pr[t] * m;
+        if (!isnan(v)) s += v;
+        if (!isnan(m)) n += m;
+      }
+      n = pool_mean ? fmaxf(n, 1.0f) : 1.0f;
+      logit[seg] = s / n;
+      ninv[seg] = 1.0f / n;
+    }
+    const float y0 = __ldg(labels + 2 * b), y1 = __ldg(labels + 2 * b + 1);
+    const float mx = fmaxf(logit[0], logit[1]);
+    const float e0 = expf(logit[0] - mx), e1 = expf(logit[1] - mx);
+    const float lse = mx + logf(e0 + e1);
+    loss += -(y0 * (logit[0] - lse) + y1 * (logit[1] - lse));
+    // torch.argmax returns the first maximal index
+    const int pc = logit[1] > logit[0] ? 1 : 0, tc = y1 > y0 ? 1 : 0;
+    acc += (pc == tc) ? 1.f : 0.f;
+    if (rowgrad != nullptr) {
+      const float ys = y0 + y1, inv = 1.0f / (e0 + e1), invB = 1.0f / (float)B;
+      const float dl[2] = {(e0 * inv * ys - y0) * invB, (e1 * inv * ys - y1) * invB};
+#pragma unroll
+      for (int seg = 0; seg < 2; ++seg) {
+        const float* mk = (seg ? m2 : m1) + (int64_t)b * T;
+        const float* pr = pred + seg * BT + (int64_t)b * T;
+        float* rg = rowgrad + seg * BT + (int64_t)b * T;
+        for (int t = 0; t < T; ++t) {
+          const float m = __ldg(mk + t);
+          rg[t] = isnan(pr[t] * m) ? 0.f : dl[seg] * m * ninv[seg];
+        }
+      }
+    }
+  }
+  s_loss[threadIdx.x] = loss; s_acc[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_acc[threadIdx.x] += s_acc[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out2[0] = s_loss[0] / (float)B; out2[1] = s_acc[0] / (float)B; }
+}
+
+// dZ[m,k] = rowgrad[m] * w_out[k] * scale * act'(Z[m,k])   (back through the output layer and the last activation)
+__global__ void mr_head_bwd_kernel(const float* __restrict__ rowgrad, const float* __restrict__ w_out, float scale,
+                                   const float* __restrict__ Z, int ld, int w, int64_t M, int act,
+                                   float* __restrict__ dZ) {
+  const int64_t total = M * w;
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = e / w;
+    const int k = (int)(e % w);
+    dZ[m * ld + k] = rowgrad[m] * __ldg(w_out + k) * scale * act_grad(act, Z[m * ld + k]);
+  }
+}
+
+// G[m,k] = scale * G[m,k] * act'(Z[m,k])   (in place: dH -> dZ of the layer below)
+__global__ void mr_act_bwd_kernel(float* __restrict__ G, const float* __restrict__ Z, int ld, int w, int64_t M,
+                                  float scale, int act) {
+  const int64_t total = M * w;
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = e / w;
+    const int k = (int)(e % w);
+    G[m * ld + k] = scale * G[m * ld + k] * act_grad(act, Z[m * ld + k]);
+  }
+}
+
+// Column sums of one row chunk per block: dst[c*plen + j] = sum_{m in chunk c} rs[m] * X[m, j]  (rs == null: 1);
+// with rs_sum the extra column j == ncols receives sum_m rs[m].
+__global__ void __launch_bounds__(128) mr_colsum_kernel(const float* __restrict__ X, int ld, int ncols,
+                                                        const float* __restrict__ rs, int rs_sum, int64_t M,
+                                                        int chunk_rows, float* __restrict__ dst, int64_t plen) {
+  const int64_t r0 = (int64_t)blockIdx.x * chunk_rows;
+  const int64_t r1 = r0 + chunk_rows < M ? r0 + chunk_rows : M;
+  float* d = dst + (int64_t)blockIdx.x * plen;
+  for (int j = threadIdx.x; j < ncols + (rs_sum ? 1 : 0); j += blockDim.x) {
+    float acc = 0.f;
+    if (j < ncols) {
+      for (int64_t m = r0; m < r1; ++m) acc = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], acc);
+    } else {
+      for (int64_t m = r0; m < r1; ++m) acc += rs[m];
+    }
+    d[j] = acc;
+  }
+}
+
+// g[e] = (e < n_w ? wscale : 1) * sum_c partial[c*plen + e], then torch.optim.Adam on element e
+// (optim/adam.py: exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2*v + (1-b2) g^2; p -= step_size * m / (sqrt(v)/sqrt(bc2) + eps)).
+__global__ void mr_reduce_adam_kernel(const float* __restrict__ partial, int n_chunks, int64_t plen, int64_t n_w,
+                                      float wscale, float* __restrict__ p, float* __restrict__ m,
+                                      float* __restrict__ v, float* __restrict__ grad_out, float beta1, float beta2,
+                                      float eps, float step_size, float bc2_sqrt) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= plen) return;
+  float g = 0.f;
+  for (int c = 0; c < n_chunks; ++c) g += partial[(int64_t)c * plen + e];
+  if (e < n_w) g *= wscale;
+  if (grad_out != nullptr) grad_out[e] = g;
+  if (p == nullptr) return;
+  float mm = m[e], vv = v[e];
+  mm = mm + (g - mm) * (1.0f - beta1);
+  vv = beta2 * vv + (1.0f - beta2) * g * g;
+  m[e] = mm; v[e] = vv;
+  const float denom = sqrtf(vv) / bc2_sqrt + eps;
+  p[e] = p[e] - step_size * (mm / denom);
+}
+
+}  // namespace iqlb
+
+using namespace iqlb;
+
+struct iqlb_mr_trainer {
+  int d_in = 0, depth = 0, act = 0, pool_mean = 1, maxw = 0;
+  std::vector<int> widths;
+  std::vector<int64_t> offW, offB;  // depth + 1 entries (last = output layer)
+  int64_t pm = 0, max_rows = 0, max_plen = 0;
+  int max_chunks = 0;
+  float *X = nullptr, *pred = nullptr, *rowgrad = nullptr, *partial = nullptr, *G0 = nullptr, *G1 = nullptr;
+  float* out2 = nullptr;
+  std::vector<float*> Z, H;
+  GemmTask* d_tasks = nullptr;  // [depth][max_chunks] weight-gradient tasks
+  int64_t tasks_rows = -1;      // row count the device task array was built for
+};
+
+static void mr_free(iqlb_mr_trainer* h) {
+  if (!h) return;
+  cudaFree(h->X); cudaFree(h->pred); cudaFree(h->rowgrad); cudaFree(h->partial); cudaFree(h->G0); cudaFree(h->G1);
+  cudaFree(h->out2); cudaFree(h->d_tasks);
+  for (float* p : h->Z) cudaFree(p);
+  for (float* p : h->H) cudaFree(p);
+  delete h;
+}
+
+static constexpr int kMrMaxChunks = 296;  // two one-CTA waves of weight-gradient tiles on 148 SMs
+
+extern "C" int iqlb_mr_create(int32_t d_in, const int32_t* host_widths, int32_t depth, int32_t activation,
+                              int32_t pool_mean, int64_t max_rows, iqlb_mr_trainer** out) {
+  IQLB_REQUIRE(out != nullptr, "null out");
+  IQLB_REQUIRE(d_in > 0 && depth >= 1 && depth <= 16 && host_widths != nullptr, "network shape");
+  IQLB_REQUIRE(activation >= IQLB_ACT_RELU && activation <= IQLB_ACT_LEAKY_RELU, "activation id");
+  IQLB_REQUIRE(max_rows > 0 && max_rows % 2 == 0, "max_rows = 2 * pairs * segment length");
+  auto* h = new iqlb_mr_trainer();
+  h->d_in = d_in; h->depth = depth; h->act = activation; h->pool_mean = pool_mean ? 1 : 0; h->max_rows = max_rows;
+  int prev = d_in;
+  for (int l = 0; l < depth; ++l) {
+    if (host_widths[l] <= 0) { delete h; return fail(IQLB_ERR_INVALID, "invalid argument: hidden width%s", ""); }
+    h->widths.push_back(host_widths[l]);
+    h->offW.push_back(h->pm); h->pm += (int64_t)prev * host_widths[l];
+    h->offB.push_back(h->pm); h->pm += host_widths[l];
+    const int64_t plen = (int64_t)prev * host_widths[l] + host_widths[l];
+    if (plen > h->max_plen) h->max_plen = plen;
+    prev = host_widths[l];
+    if (prev > h->maxw) h->maxw = prev;
+  }
+  h->offW.push_back(h->pm); h->pm += prev;
+  h->offB.push_back(h->pm); h->pm += 1;
+  h->max_chunks = kMrMaxChunks;
+#define MR_ALLOC(ptr, n)                                                                          \
+  do {                                                                                            \
+    if (cudaMalloc((void**)&(ptr), (size_t)(n) * sizeof(float)) != cudaSuccess) {                 \
+      cudaGetLastError(); mr_free(h);                                                             \
+      return fail(IQLB_ERR_NOMEM, "iqlb_mr_create: device allocation failed%s", "");              \
+    }                                                                                             \
+  } while (0)
+  MR_ALLOC(h->X, max_rows * d_in);
+  MR_ALLOC(h->pred, max_rows);
+  MR_ALLOC(h->rowgrad, max_rows);
+  MR_ALLOC(h->partial, (int64_t)h->max_chunks * h->max_plen);
+  MR_ALLOC(h->G0, max_rows * h->maxw);
+  MR_ALLOC(h->G1, max_rows * h->maxw);
+  MR_ALLOC(h->out2, 2);
+  h->Z.assign(depth, nullptr); h->H.assign(depth, nullptr);
+  for (int l = 0; l < depth; ++l) { MR_ALLOC(h->Z[l], max_rows * h->widths[l]); MR_ALLOC(h->H[l], max_rows * h->widths[l]); }
+#undef MR_ALLOC
+  if (cudaMalloc((void**)&h->d_tasks, (size_t)depth * h->max_chunks * sizeof(GemmTask)) != cudaSuccess) {
+    cudaGetLastError(); mr_free(h);
+    return fail(IQLB_ERR_NOMEM, "iqlb_mr_create: device allocation failed%s", "");
+  }
+  *out = h;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_mr_destroy(iqlb_mr_trainer* h) {
+  if (h) cudaDeviceSynchronize();
+  mr_free(h);
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_mr_param_count(const iqlb_mr_trainer* h, int64_t* n_params) {
+  IQLB_REQUIRE(h != nullptr && n_params != nullptr, "null argument");
+  *n_params = h->pm;
+  return IQLB_OK;
+}
+
+static int mr_forward(iqlb_mr_trainer* h, const float* params, const float* s1, const float* a1, const float* s2,
+                      const float* a2, int B, int T, int S, int A, bool keep_pre, cudaStream_t st) {
+  const int64_t BT = (int64_t)B * T, M = 2 * BT;
+  {
+    const int64_t total = M * h->d_in;
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    mr_pack_kernel<<<blocks, 256, 0, st>>>(s1, a1, s2, a2, BT, S, A, h->X);
+    IQLB_LAUNCH_CHECK();
+  }
+  int prev = h->d_in;
+  const float* src = h->X;
+  for (int l = 0; l < h->depth; ++l) {
+    const int w = h->widths[l];
+    GemmTask t{};
+    t.A = src; t.lda = prev;
+    t.Bm = params + h->offW[l]; t.ldb = w;
+    t.bias = params + h->offB[l];
+    t.C = h->H[l]; t.ldc = w;
+    t.pre = keep_pre ? h->Z[l] : nullptr;
+    t.M = (int)M; t.N = w; t.K = prev;
+    t.scale = 1.0f / sqrtf((float)prev);
+    t.act = h->act;
+    const int rc = launch_gemm(GEMM_FWD_KN, t, st);
+    if (rc) return rc;
+    src = h->H[l]; prev = w;
+  }
+  mr_head_kernel<<<(unsigned)((M * 32 + 255) / 256), 256, 0, st>>>(src, prev, prev, params + h->offW[h->depth],
+                                                                  params + h->offB[h->depth],
+                                                                  1.0f / sqrtf((float)prev), M, h->pred);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+static int mr_check_batch(const iqlb_mr_trainer* h, const void* params, const void* s1, const void* a1,
+                          const void* m1, const void* s2, const void* a2, const void* m2, const void* labels,
+                          int B, int T, int S, int A) {
+  IQLB_REQUIRE(h != nullptr, "null trainer");
+  IQLB_REQUIRE(params && s1 && a1 && m1 && s2 && a2 && m2 && labels, "null pointer");
+  IQLB_REQUIRE(B > 0 && T > 0 && S > 0 && A >= 0, "batch shape");
+  IQLB_REQUIRE(S + A == h->d_in, "state_dim + action_dim must equal the network input width");
+  IQLB_REQUIRE(2ll * B * T <= h->max_rows, "batch larger than max_rows given to iqlb_mr_create");
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float* states1, const float* actions1,
+                            const float* mask1, const float* states2, const float* actions2, const float* mask2,
+                            const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float* out2,
+                            float* pred_out, void* stream) {
+  int rc = mr_check_batch(h, params, states1, actions1, mask1, states2, actions2, mask2, labels, B, T, S, A);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, false, st);
+  if (rc) return rc;
+  mr_loss_kernel<<<1, 256, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, nullptr, out2 ? out2 : h->out2);
+  IQLB_LAUNCH_CHECK();
+  if (pred_out) IQLB_CUDA(cudaMemcpyAsync(pred_out, h->pred, (size_t)2 * B * T * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
+                                  const float* states1, const float* actions1, const float* mask1,
+                                  const float* states2, const float* actions2, const float* mask2,
+                                  const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                                  float beta1, float beta2, float eps, int64_t adam_step, float* out2,
+                                  float* grad_out, void* stream) {
+  int rc = mr_check_batch(h, params, states1, actions1, mask1, states2, actions2, mask2, labels, B, T, S, A);
+  if (rc) return rc;
+  IQLB_REQUIRE((exp_avg != nullptr && exp_avg_sq != nullptr) || lr == 0.f, "null optimizer state");
+  IQLB_REQUIRE(adam_step >= 1, "adam_step counts from 1 (the step being taken)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t M = 2ll * B * T;
+  const int L = h->depth;
+  rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, true, st);
+  if (rc) return rc;
+  mr_loss_kernel<<<1, 256, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, h->rowgrad,
+                                    out2 ? out2 : h->out2);
+  IQLB_LAUNCH_CHECK();
+
+  // row chunks of the split weight-gradient reductions
+  int n_chunks = (int)((M + 127) / 128);
+  if (n_chunks > h->max_chunks) n_chunks = h->max_chunks;
+  int chunk_rows = (int)((M + n_chunks - 1) / n_chunks);
+  chunk_rows = (chunk_rows + 7) / 8 * 8;
+  n_chunks = (int)((M + chunk_rows - 1) / chunk_rows);
+
+  if (h->tasks_rows != M) {
+    std::vector<GemmTask> tasks((size_t)L * h->max_chunks);
+    int prev = h->d_in;
+    for (int l = 0; l < L; ++l) {
+      const int w = h->widths[l];
+      const float* below = l == 0 ? h->X : h->H[l - 1];
+      const float* dz = ((L - 1 - l) % 2 == 0) ? h->G0 : h->G1;
+      const int64_t plen = (int64_t)prev * w + w;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int64_t r0 = (int64_t)c * chunk_rows;
+        GemmTask t{};
+        t.A = below + r0 * prev; t.lda = prev;      // A[k, m'] : rows of the layer input
+        t.Bm = dz + r0 * w; t.ldb = w;              // X[k, n'] : rows of dZ
+        t.C = h->partial + (int64_t)c * plen; t.ldc = w;
+        t.M = prev; t.N = w; t.K = (int)((M - r0 < chunk_rows) ? (M - r0) : chunk_rows);
+        tasks[(size_t)l * h->max_chunks + c] = t;
+      }
+      prev = w;
+    }
+    // the previous task array may still be in use by launches of an earlier step on this stream
+    IQLB_CUDA(cudaStreamSynchronize(st));
+    IQLB_CUDA(cudaMemcpy(h->d_tasks, tasks.data(), tasks.size() * sizeof(GemmTask), cudaMemcpyHostToDevice));
+    h->tasks_rows = M;
+  }
+
+  const double bc1 = 1.0 - pow((double)beta1, (double)adam_step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)adam_step);
+  const float step_size = (float)((double)lr / bc1), bc2_sqrt = (float)sqrt(bc2);
+  const bool apply = lr != 0.f || exp_avg != nullptr;
+  auto reduce_adam = [&](int64_t off, int64_t plen, int64_t n_w, float wscale) -> int {
+    mr_reduce_adam_kernel<<<(unsigned)((plen + 255) / 256), 256, 0, st>>>(
+        h->partial, n_chunks, plen, n_w, wscale, apply ? params + off : nullptr, apply ? exp_avg + off : nullptr,
+        apply ? exp_avg_sq + off : nullptr, grad_out ? grad_out + off : nullptr, beta1, beta2, eps, step_size,
+        bc2_sqrt);
+    IQLB_LAUNCH_CHECK();
+    return IQLB_OK;
+  };
+  const int ew_blocks = 148 * 8;
+
+  // output layer: dZ of the last hidden layer first (it reads w_out before Adam rewrites it)
+  const int wl = h->widths[L - 1];
+  const float out_scale = 1.0f / sqrtf((float)wl);
+  mr_head_bwd_kernel<<<ew_blocks, 256, 0, st>>>(h->rowgrad, params + h->offW[L], out_scale, h->Z[L - 1], wl, wl, M,
+                                                h->act, h->G0);
+  IQLB_LAUNCH_CHECK();
+  mr_colsum_kernel<<<n_chunks, 128, 0, st>>>(h->H[L - 1], wl, wl, h->rowgrad, 1, M, chunk_rows, h->partial, wl + 1);
+  IQLB_LAUNCH_CHECK();
+  rc = reduce_adam(h->offW[L], wl + 1, wl, out_scale);
+  if (rc) return rc;
+
+  for (int l = L - 1; l >= 0; --l) {
+    const int w = h->widths[l];
+    const int prev = l == 0 ? h->d_in : h->widths[l - 1];
+    float* dz = ((L - 1 - l) % 2 == 0) ? h->G0 : h->G1;
+    float* other = ((L - 1 - l) % 2 == 0) ? h->G1 : h->G0;
+    const int64_t plen = (int64_t)prev * w + w;
+    rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, w <= 32, st);
+    if (rc) return rc;
+    mr_colsum_kernel<<<n_chunks, 128, 0, st>>>(dz, w, w, nullptr, 0, M, chunk_rows, h->partial + (int64_t)prev * w,
+                                               plen);
+    IQLB_LAUNCH_CHECK();
+    if (l > 0) {
+      GemmTask t{};  // dH[m, k_in] = sum_n dZ[m, n] W[k_in, n]
+      t.A = dz; t.lda = w;
+      t.Bm = params + h->offW[l]; t.ldb = w;
+      t.C = other; t.ldc = prev;
+      t.M = (int)M; t.N = prev; t.K = w;
+      t.act = IQLB_ACT_LINEAR;
+      rc = launch_gemm(GEMM_LINEAR, t, st);
+      if (rc) return rc;
+      mr_act_bwd_kernel<<<ew_blocks, 256, 0, st>>>(other, h->Z[l - 1], prev, prev, M, 1.0f / sqrtf((float)prev),
+                                                   h->act);
+      IQLB_LAUNCH_CHECK();
+    }
+    rc = reduce_adam(h->offW[l], plen, (int64_t)prev * w, 1.0f / sqrtf((float)prev));
+    if (rc) return rc;
+  }
+  return IQLB_OK;
+}

@@ -1,0 +1,179 @@
+"""`MRTrainer` of /root/reference/gp_reward-priors/optbnn/training/training.py:11-129 behind the same surface
+(`MRTrainer(net, opt, num_datapoints, device, bt_pool)`, `.train(batch) -> {"training_loss", "training_acc"}`,
+`.evaluation(batch) -> {"eval_loss", "eval_acc"}`, `.state_dict()`, `.load_state_dict()`), SURVEY.md §8f-1.
+
+The whole step - forward over both segments, `bt_pool_logit` (optbnn/utils/util.py:356-364), soft-label cross
+entropy, backward, `torch.optim.Adam` - is `iqlb_mr_train_step` in libiqlb.so (`csrc/mr_train.cu`).  The network's
+parameters become views of one flat fp32 device buffer in the member layout the relabel kernels read
+(`W0 b0 ... Wout bout`, W stored (n_in, n_out)), so a trained net goes to `ensemble_predict` / `qlearning_dataset_mr`
+without a copy and `net.state_dict()` / `checkpoint_{epoch}.pt` files keep the reference's keys.  Adam's moments live
+in two more flat buffers and are exposed through `opt.state` as views in the reference's format.  No CPU path.
+"""
+import ctypes as C
+from typing import Any, Dict, List, Sequence
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+TensorBatch = List[torch.Tensor]
+
+
+def _linears(net) -> List[nn.Module]:
+    net = getattr(net, "_orig_mod", net)
+    return list(net.layers) + [net.output_layer]
+
+
+class MRTrainer:
+    def __init__(self, net: nn.Module, opt: torch.optim.Optimizer, num_datapoints: int, device: str = "cuda",
+                 bt_pool: str = "mean", max_rows: int = 0):
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("iqlpref_b200 has no CPU path: MRTrainer runs on a CUDA device")
+        if bt_pool not in ("mean", "sum"):
+            raise ValueError(f"bt_pool_logit: mode must be 'sum' or 'mean', got {bt_pool!r}")
+        if not isinstance(opt, torch.optim.Adam) or isinstance(opt, torch.optim.AdamW):
+            raise NotImplementedError("MRTrainer: torch.optim.Adam only (scripts_mr/run_mr_training.py:105)")
+        g = opt.param_groups[0]
+        if len(opt.param_groups) != 1 or g.get("weight_decay", 0) != 0 or g.get("amsgrad", False) or g.get("maximize", False):
+            raise NotImplementedError("MRTrainer: one parameter group, no weight decay / amsgrad / maximize")
+        self.net, self.opt, self.device, self.bt_pool, self.num_datapoints = net, opt, dev, bt_pool, num_datapoints
+        lins = _linears(net)
+        from .relabel import _activation_name
+        self.activation = _activation_name(getattr(net, "_orig_mod", net))
+        if lins[-1].W.shape[1] != 1:
+            raise ValueError("reward MLP must have output_dim == 1")
+        self.d_in = int(lins[0].W.shape[0])
+        self.widths = [int(l.W.shape[1]) for l in lins[:-1]]
+        params = [p for l in lins for p in (l.W, l.b)]
+        if [id(p) for p in params] != [id(p) for p in g["params"]]:
+            raise ValueError("MRTrainer: the optimizer must hold net.parameters() in order")
+        # one flat buffer; the module's parameters become views of it
+        self.flat = torch.cat([p.detach().to(dev, torch.float32).reshape(-1) for p in params]).contiguous()
+        self.exp_avg = torch.zeros_like(self.flat)
+        self.exp_avg_sq = torch.zeros_like(self.flat)
+        self._slices = []
+        off = 0
+        for p in params:
+            n = p.numel()
+            self._slices.append((off, n, tuple(p.shape)))
+            p.data = self.flat[off:off + n].view(p.shape)
+            off += n
+        self._params = params
+        self.step_count = 0
+        self._handle = None
+        self._max_rows = int(max_rows)
+        self._out2 = torch.zeros(2, dtype=torch.float32, device=dev)
+        self._adopt_optimizer_state()
+
+    # ---------------------------------------------------------------- native handle
+    def _ensure(self, rows: int):
+        lib = _lib.load()
+        if self._handle is not None and rows <= self._max_rows:
+            return lib
+        if self._handle is not None:
+            lib.iqlb_mr_destroy(self._handle)
+            self._handle = None
+        self._max_rows = max(rows, self._max_rows)
+        h = C.c_void_p()
+        widths = (C.c_int32 * len(self.widths))(*self.widths)
+        with torch.cuda.device(self.device):
+            _lib.check(lib.iqlb_mr_create(self.d_in, widths, len(self.widths), _lib.ACTIVATIONS[self.activation],
+                                          1 if self.bt_pool == "mean" else 0, self._max_rows, C.byref(h)),
+                       "iqlb_mr_create")
+        n = C.c_int64()
+        _lib.check(lib.iqlb_mr_param_count(h, C.byref(n)), "iqlb_mr_param_count")
+        assert n.value == self.flat.numel()
+        self._handle = h
+        return lib
+
+    def __del__(self):
+        try:
+            if self._handle is not None:
+                _lib.load().iqlb_mr_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+    def _unpack(self, batch: TensorBatch):
+        s1, a1, _, m1, s2, a2, _, m2, labels = batch
+        if s1.dim() != 3 or a1.dim() != 3:
+            raise ValueError("states / actions must be [B, T, dim]")
+        B, T, S = s1.shape
+        A = a1.shape[2]
+        prep = lambda t: t.to(self.device, torch.float32).contiguous()
+        ts = [prep(t) for t in (s1, a1, m1, s2, a2, m2, labels)]
+        if ts[3].shape != (B, T, S) or ts[4].shape != (B, T, A) or ts[2].shape != (B, T) or ts[5].shape != (B, T) \
+                or ts[6].shape != (B, 2):
+            raise ValueError("inconsistent preference batch shapes")
+        if S + A != self.d_in:
+            raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({2 * B * T}x{S + A} and {self.d_in}x{self.widths[0]})")
+        return ts, int(B), int(T), int(S), int(A)
+
+    # ---------------------------------------------------------------- training.py:27-72
+    def train(self, batch: TensorBatch, return_grad: bool = False) -> Dict[str, float]:
+        ts, B, T, S, A = self._unpack(batch)
+        if not self.net.training:
+            self.net.train()
+        lib = self._ensure(2 * B * T)
+        g = self.opt.param_groups[0]
+        grad = torch.empty_like(self.flat) if return_grad else None
+        self.step_count += 1
+        with torch.cuda.device(self.device):
+            _lib.check(lib.iqlb_mr_train_step(self._handle, _lib.ptr(self.flat), _lib.ptr(self.exp_avg),
+                                              _lib.ptr(self.exp_avg_sq), *[_lib.ptr(t) for t in ts], B, T, S, A,
+                                              float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]),
+                                              float(g["eps"]), self.step_count, _lib.ptr(self._out2), _lib.ptr(grad),
+                                              _lib.stream_ptr(self.device)), "iqlb_mr_train_step")
+        loss, acc = self._out2.tolist()  # the reference's loss.item() sync (training.py:65-70)
+        log = {"training_loss": loss, "training_acc": acc}
+        if return_grad:
+            log["grad"] = grad
+        return log
+
+    # ---------------------------------------------------------------- training.py:74-114
+    def evaluation(self, batch: TensorBatch) -> Dict[str, float]:
+        ts, B, T, S, A = self._unpack(batch)
+        if self.net.training:
+            self.net.eval()
+        lib = self._ensure(2 * B * T)
+        with torch.cuda.device(self.device):
+            _lib.check(lib.iqlb_mr_eval(self._handle, _lib.ptr(self.flat), *[_lib.ptr(t) for t in ts], B, T, S, A,
+                                        _lib.ptr(self._out2), None, _lib.stream_ptr(self.device)), "iqlb_mr_eval")
+        loss, acc = self._out2.tolist()
+        return {"eval_loss": loss, "eval_acc": acc}
+
+    def member(self) -> List[torch.Tensor]:
+        """[W0, b0, ..., Wout, bout] views for `ensemble_predict` / snapshot ensembles (no copy)."""
+        return [p.detach() for p in self._params]
+
+    # ---------------------------------------------------------------- optimizer state in the reference's format
+    def _publish_optimizer_state(self):
+        for p, (off, n, shape) in zip(self._params, self._slices):
+            self.opt.state[p] = {"step": torch.tensor(float(self.step_count)),
+                                 "exp_avg": self.exp_avg[off:off + n].view(shape),
+                                 "exp_avg_sq": self.exp_avg_sq[off:off + n].view(shape)}
+
+    def _adopt_optimizer_state(self):
+        steps = set()
+        for p, (off, n, shape) in zip(self._params, self._slices):
+            st = self.opt.state.get(p)
+            if not st:
+                continue
+            self.exp_avg[off:off + n].copy_(st["exp_avg"].to(self.device, torch.float32).reshape(-1))
+            self.exp_avg_sq[off:off + n].copy_(st["exp_avg_sq"].to(self.device, torch.float32).reshape(-1))
+            steps.add(int(float(st["step"])))
+        if len(steps) > 1:
+            raise ValueError("MRTrainer: parameters with different Adam step counts")
+        if steps:
+            self.step_count = steps.pop()
+
+    def state_dict(self) -> Dict[str, Any]:  # training.py:116-120
+        self._publish_optimizer_state()
+        return {"net": self.net.state_dict(), "optimizer": self.opt.state_dict()}
+
+    def load_state_dict(self, state_dict: Dict[str, Any]):  # training.py:122-124
+        self.net.load_state_dict(state_dict["net"])  # copies into the views of the flat buffer
+        self.opt.load_state_dict(state_dict["optimizer"])
+        self._adopt_optimizer_state()

@@ -1,0 +1,180 @@
+"""GPU parity of the MR preference-model training step: `iqlpref_b200.mr_training.MRTrainer`
+(`iqlb_mr_train_step` / `iqlb_mr_eval`) against fixtures written by the unmodified reference `MRTrainer`
+(gp_reward-priors/optbnn/training/training.py:27-114; tests/golden/mr_train.npz, oracle/gen_golden_mr.py) and
+against the numpy oracle on fresh seeded batches for every activation, both pooling modes, ragged / empty masks,
+NaN rewards and the production batch shape.  Tolerances: loss 1e-4 relative, gradients 1e-3 relative to the tensor's
+largest entry, accuracy exact, parameters after K Adam steps 3e-5 absolute except elements whose gradient is rounding
+noise (Adam moves those by ~lr per step in either direction; at most 2 %, bounded by 2*K*lr)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.gen_golden_mr import CASES, load_case
+from oracle.mr_train_oracle import MRTrainerOracle, mr_loss_and_grads, synth_batch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def golden(golden_dir):
+    return np.load(os.path.join(golden_dir, "mr_train.npz"))
+
+
+def make_trainer(weights, act, pool, lr=3e-4):
+    from iqlpref_b200.mr_training import MRTrainer
+    from iqlpref_b200.reward_models.q_mlp import MLP
+    d_in = weights[0].shape[0]
+    widths = [w.shape[1] for w in weights[0:-2:2]]
+    net = MLP(d_in, 1, widths, act)
+    with torch.no_grad():
+        for p, w in zip(net.parameters(), weights):
+            p.copy_(torch.from_numpy(np.asarray(w)).reshape(p.shape))
+    opt = torch.optim.Adam(net.parameters(), lr=lr)
+    return MRTrainer(net, opt, num_datapoints=1, device="cuda", bt_pool=pool), net, opt
+
+
+def tb(batch):
+    return [torch.from_numpy(np.asarray(x)) for x in batch]
+
+
+def split(flat, weights):
+    out, off = [], 0
+    flat = flat.detach().cpu().numpy()
+    for w in weights:
+        out.append(flat[off:off + w.size].reshape(w.shape)); off += w.size
+    return out
+
+
+def assert_grads_close(got, want, rel=1e-3):
+    for g, gr in zip(got, want):
+        gr = np.asarray(gr).reshape(g.shape)
+        np.testing.assert_allclose(g, gr, rtol=0, atol=rel * max(float(np.abs(gr).max()), 1e-6))
+
+
+def assert_params_close(got, want, K, lr=3e-4):
+    for w, wr in zip(got, want):
+        d = np.abs(np.asarray(w).reshape(-1) - np.asarray(wr).reshape(-1))
+        assert d.max() <= 2 * K * lr
+        assert np.sum(d > 3e-5) <= max(1, 0.02 * d.size)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_reference_fixture(golden, name):
+    c = load_case(golden, name)
+    tr, net, opt = make_trainer(c["w0"], c["act"], c["pool"])
+    for k in range(c["K"]):
+        log = tr.train(tb(c["batches"][k]), return_grad=(k == 0))
+        assert log["training_loss"] == pytest.approx(c["loss"][k], rel=1e-4)
+        assert log["training_acc"] == pytest.approx(c["acc"][k], abs=1e-6)
+        if k == 0:
+            assert_grads_close(split(log["grad"], c["w0"]), c["g0"])
+    ev = tr.evaluation(tb(c["batches"][c["K"]]))
+    assert ev["eval_loss"] == pytest.approx(c["eval"][0], rel=1e-4)
+    assert ev["eval_acc"] == pytest.approx(c["eval"][1], abs=1e-6)
+    assert_params_close([p.detach().cpu().numpy() for p in net.parameters()], c["wK"], c["K"])
+    sd = tr.state_dict()
+    assert set(sd) == {"net", "optimizer"}
+    st = sd["optimizer"]["state"]
+    assert len(st) == len(c["w0"]) and float(st[0]["step"]) == c["K"]
+    for i, (mr, vr) in enumerate(zip(c["mK"], c["vK"])):
+        m = st[i]["exp_avg"].cpu().numpy(); v = st[i]["exp_avg_sq"].cpu().numpy()
+        assert m.shape == mr.shape
+        np.testing.assert_allclose(m, mr, rtol=2e-3, atol=2e-6 * max(1.0, float(np.abs(mr).max())))
+        np.testing.assert_allclose(v, vr, rtol=4e-3, atol=1e-9)
+
+
+@pytest.mark.parametrize("act", ["relu", "tanh", "cos", "sin", "linear", "rbf", "swish", "softplus", "leaky_relu"])
+@pytest.mark.parametrize("pool", ["mean", "sum"])
+def test_gradients_every_activation(act, pool):
+    rng = np.random.default_rng(sum(map(ord, act + pool)))
+    S, A, B, T = 7, 3, 33, 9
+    widths = [40, 24, 16]
+    dims = [S + A] + widths + [1]
+    weights = []
+    for i in range(len(dims) - 1):
+        weights += [rng.standard_normal((dims[i], dims[i + 1])).astype(np.float32),
+                    (0.1 * rng.standard_normal(dims[i + 1])).astype(np.float32)]
+    batch = synth_batch(rng, B, T, S, A)
+    batch[3][0, :] = 0.0  # a segment with an empty mask: n clamps to 1 (util.py:363)
+    loss, acc, grads = mr_loss_and_grads(weights, batch, act, pool)
+    tr, net, _ = make_trainer(weights, act, pool)
+    log = tr.train(tb(batch), return_grad=True)
+    assert log["training_loss"] == pytest.approx(loss, rel=1e-4)
+    assert log["training_acc"] == pytest.approx(acc, abs=1e-6)
+    assert_grads_close(split(log["grad"], weights), grads)
+
+
+def test_nan_rewards_are_skipped_like_nansum():
+    rng = np.random.default_rng(5)
+    S, A, B, T = 4, 2, 8, 6
+    weights = [rng.standard_normal((6, 16)).astype(np.float32), np.zeros(16, np.float32),
+               rng.standard_normal((16, 1)).astype(np.float32), np.zeros(1, np.float32)]
+    batch = synth_batch(rng, B, T, S, A, ragged=False)
+    batch[0][2, 3, :] = np.nan  # one row of segment 1 predicts NaN
+    tr, _, _ = make_trainer(weights, "relu", "mean")
+    ev = tr.evaluation(tb(batch))
+    assert np.isfinite(ev["eval_loss"])
+    from oracle.mr_train_oracle import ce_loss_acc, mr_forward
+    logits, _ = mr_forward(weights, batch, "relu", "mean")
+    loss, acc, _ = ce_loss_acc(logits, batch[8])
+    assert ev["eval_loss"] == pytest.approx(loss, rel=1e-4) and ev["eval_acc"] == pytest.approx(acc, abs=1e-6)
+
+
+def test_production_shape_against_oracle_trajectory():
+    """antmaze MR shape (37 -> 128 x 3 -> 1), batch 256 x 25-step segments (12 800 rows, > one chunk per SM wave)."""
+    rng = np.random.default_rng(21)
+    S, A, B, T, K = 29, 8, 256, 25, 3
+    dims = [S + A, 128, 128, 128, 1]
+    weights = []
+    for i in range(4):
+        weights += [rng.standard_normal((dims[i], dims[i + 1])).astype(np.float32), np.zeros(dims[i + 1], np.float32)]
+    orc = MRTrainerOracle(weights, "relu")
+    tr, net, _ = make_trainer(weights, "relu", "mean")
+    for k in range(K):
+        batch = synth_batch(rng, B, T, S, A)
+        want = orc.train(batch)
+        got = tr.train(tb(batch))
+        assert got["training_loss"] == pytest.approx(want["training_loss"], rel=2e-4)
+        assert abs(got["training_acc"] - want["training_acc"]) <= 1.5 / B  # a pair with |logit0 - logit1| ~ 1e-7
+    assert_params_close([p.detach().cpu().numpy() for p in net.parameters()], orc.weights, K)
+
+
+def test_trained_net_feeds_the_relabel_path_and_checkpoints_round_trip(tmp_path):
+    from iqlpref_b200.relabel import ensemble_predict
+    rng = np.random.default_rng(3)
+    S, A, B, T = 5, 2, 12, 4
+    weights = [rng.standard_normal((7, 64)).astype(np.float32), np.zeros(64, np.float32),
+               rng.standard_normal((64, 1)).astype(np.float32), np.zeros(1, np.float32)]
+    tr, net, opt = make_trainer(weights, "tanh", "mean")
+    b0, b1 = synth_batch(rng, B, T, S, A), synth_batch(rng, B, T, S, A)
+    tr.train(tb(b0))
+    torch.save(tr.state_dict(), tmp_path / "checkpoint_0.pt")  # run_mr_training.py:147-151
+    after1 = tr.train(tb(b1))
+    x = torch.from_numpy(rng.standard_normal((50, 7)).astype(np.float32)).cuda()
+    r_direct = ensemble_predict([tr.member()], x, "mean", activation="tanh", precision="fp32")
+    assert torch.equal(r_direct, net(x).reshape(-1))
+    # resume from the file in a fresh trainer: identical continuation
+    tr2, net2, _ = make_trainer(weights, "tanh", "mean")
+    tr2.load_state_dict(torch.load(tmp_path / "checkpoint_0.pt", weights_only=False))
+    assert tr2.step_count == 1
+    again = tr2.train(tb(b1))
+    assert again == after1
+    for p, q in zip(net.parameters(), net2.parameters()):
+        assert torch.equal(p, q)
+
+
+def test_errors():
+    from iqlpref_b200.mr_training import MRTrainer
+    from iqlpref_b200.reward_models.q_mlp import MLP
+    net = MLP(6, 1, [8], "relu")
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    with pytest.raises(ValueError):
+        MRTrainer(net, opt, 1, device="cuda", bt_pool="median")
+    with pytest.raises(RuntimeError):
+        MRTrainer(net, opt, 1, device="cpu")
+    tr = MRTrainer(net, opt, 1, device="cuda")
+    bad = synth_batch(np.random.default_rng(0), 2, 3, 5, 2)  # 7 inputs for a 6-input net
+    with pytest.raises(RuntimeError):
+        tr.train(tb(bad))

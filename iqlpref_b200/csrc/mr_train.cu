@@ -59,61 +59,72 @@ __global__ void mr_head_kernel(const float* __restrict__ H, int ld, int w, const
 }
 
 // Masked pooling, soft-label cross entropy (mean over pairs), accuracy, and the gradient of the loss with
-// respect to every per-row prediction.  One block; thread b walks its pair's T rows of both segments.
+// respect to every per-row prediction.  One 64-thread block per pair: warp `seg` pools its segment (coalesced over
+// t, warp-shuffle sums), thread 0 forms the pair's loss, the two warps write
 //   rowgrad[m] = dL/dpred[m] = dlogit[b, seg] * mask[b, t] / n[b, seg]   (0 where pred*mask is NaN: nansum)
-__global__ void __launch_bounds__(256) mr_loss_kernel(const float* __restrict__ pred, const float* __restrict__ m1,
-                                                      const float* __restrict__ m2, const float* __restrict__ labels,
-                                                      int B, int T, int pool_mean, float* __restrict__ rowgrad,
-                                                      float* __restrict__ out2) {
-  __shared__ float s_loss[256], s_acc[256];
-  float loss = 0.f, acc = 0.f;
+// and the last block to finish sums the per-pair terms in a fixed order (deterministic mean).
+__global__ void __launch_bounds__(64) mr_loss_kernel(const float* __restrict__ pred, const float* __restrict__ m1,
+                                                     const float* __restrict__ m2, const float* __restrict__ labels,
+                                                     int B, int T, int pool_mean, float* __restrict__ rowgrad,
+                                                     float* __restrict__ pair_out, unsigned int* __restrict__ counter,
+                                                     float* __restrict__ out2) {
+  __shared__ float s_logit[2], s_ninv[2], s_dl[2];
+  __shared__ bool s_last;
+  const int b = blockIdx.x, seg = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t BT = (int64_t)B * T;
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
-    float logit[2], ninv[2];
+  const float* mk = (seg ? m2 : m1) + (int64_t)b * T;
+  const float* pr = pred + seg * BT + (int64_t)b * T;
+  float s = 0.f, n = 0.f;
+  for (int t = lane; t < T; t += 32) {
+    const float m = __ldg(mk + t), v = pr[t] * m;
+    if (!isnan(v)) s += v;
+    if (!isnan(m)) n += m;
+  }
 #pragma unroll
-    for (int seg = 0; seg < 2; ++seg) {
-      const float* mk = (seg ? m2 : m1) + (int64_t)b * T;
-      const float* pr = pred + seg * BT + (int64_t)b * T;
-      float s = 0.f, n = 0.f;
-      for (int t = 0; t < T; ++t) {
-        const float m = __ldg(mk + t), v = pr[t] * m;
-        if (!isnan(v)) s += v;
-        if (!isnan(m)) n += m;
-      }
-      n = pool_mean ? fmaxf(n, 1.0f) : 1.0f;
-      logit[seg] = s / n;
-      ninv[seg] = 1.0f / n;
-    }
+  for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); n += __shfl_xor_sync(0xffffffffu, n, o); }
+  if (lane == 0) {
+    n = pool_mean ? fmaxf(n, 1.0f) : 1.0f;
+    s_logit[seg] = s / n;
+    s_ninv[seg] = 1.0f / n;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float l0 = s_logit[0], l1 = s_logit[1];
     const float y0 = __ldg(labels + 2 * b), y1 = __ldg(labels + 2 * b + 1);
-    const float mx = fmaxf(logit[0], logit[1]);
-    const float e0 = expf(logit[0] - mx), e1 = expf(logit[1] - mx);
+    const float mx = fmaxf(l0, l1);
+    const float e0 = expf(l0 - mx), e1 = expf(l1 - mx);
     const float lse = mx + logf(e0 + e1);
-    loss += -(y0 * (logit[0] - lse) + y1 * (logit[1] - lse));
     // torch.argmax returns the first maximal index
-    const int pc = logit[1] > logit[0] ? 1 : 0, tc = y1 > y0 ? 1 : 0;
-    acc += (pc == tc) ? 1.f : 0.f;
-    if (rowgrad != nullptr) {
-      const float ys = y0 + y1, inv = 1.0f / (e0 + e1), invB = 1.0f / (float)B;
-      const float dl[2] = {(e0 * inv * ys - y0) * invB, (e1 * inv * ys - y1) * invB};
-#pragma unroll
-      for (int seg = 0; seg < 2; ++seg) {
-        const float* mk = (seg ? m2 : m1) + (int64_t)b * T;
-        const float* pr = pred + seg * BT + (int64_t)b * T;
-        float* rg = rowgrad + seg * BT + (int64_t)b * T;
-        for (int t = 0; t < T; ++t) {
-          const float m = __ldg(mk + t);
-          rg[t] = isnan(pr[t] * m) ? 0.f : dl[seg] * m * ninv[seg];
-        }
-      }
+    const int pc = l1 > l0 ? 1 : 0, tc = y1 > y0 ? 1 : 0;
+    pair_out[2 * b] = -(y0 * (l0 - lse) + y1 * (l1 - lse));
+    pair_out[2 * b + 1] = (pc == tc) ? 1.f : 0.f;
+    const float ys = y0 + y1, inv = 1.0f / (e0 + e1), invB = 1.0f / (float)B;
+    s_dl[0] = (e0 * inv * ys - y0) * invB;
+    s_dl[1] = (e1 * inv * ys - y1) * invB;
+    __threadfence();
+    s_last = atomicAdd(counter, 1u) == (unsigned)(B - 1);
+  }
+  __syncthreads();
+  if (rowgrad != nullptr) {
+    float* rg = rowgrad + seg * BT + (int64_t)b * T;
+    const float c = s_dl[seg] * s_ninv[seg];
+    for (int t = lane; t < T; t += 32) {
+      const float m = __ldg(mk + t);
+      rg[t] = isnan(pr[t] * m) ? 0.f : c * m;
     }
   }
-  s_loss[threadIdx.x] = loss; s_acc[threadIdx.x] = acc;
+  if (!s_last) return;
+  __threadfence();
+  __shared__ float r_loss[64], r_acc[64];
+  float loss = 0.f, acc = 0.f;
+  for (int i = threadIdx.x; i < B; i += 64) { loss += __ldcg(pair_out + 2 * i); acc += __ldcg(pair_out + 2 * i + 1); }
+  r_loss[threadIdx.x] = loss; r_acc[threadIdx.x] = acc;
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if ((int)threadIdx.x < o) { s_loss[threadIdx.x] += s_loss[threadIdx.x + o]; s_acc[threadIdx.x] += s_acc[threadIdx.x + o]; }
+  for (int o = 32; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) { r_loss[threadIdx.x] += r_loss[threadIdx.x + o]; r_acc[threadIdx.x] += r_acc[threadIdx.x + o]; }
     __syncthreads();
   }
-  if (threadIdx.x == 0) { out2[0] = s_loss[0] / (float)B; out2[1] = s_acc[0] / (float)B; }
+  if (threadIdx.x == 0) { out2[0] = r_loss[0] / (float)B; out2[1] = r_acc[0] / (float)B; *counter = 0u; }
 }
 
 // dZ[m,k] = rowgrad[m] * w_out[k] * scale * act'(Z[m,k])   (back through the output layer and the last activation)
@@ -148,13 +159,20 @@ __global__ void __launch_bounds__(128) mr_colsum_kernel(const float* __restrict_
   const int64_t r1 = r0 + chunk_rows < M ? r0 + chunk_rows : M;
   float* d = dst + (int64_t)blockIdx.x * plen;
   for (int j = threadIdx.x; j < ncols + (rs_sum ? 1 : 0); j += blockDim.x) {
-    float acc = 0.f;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four rows in flight
     if (j < ncols) {
-      for (int64_t m = r0; m < r1; ++m) acc = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], acc);
+      int64_t m = r0;
+      for (; m + 3 < r1; m += 4) {
+        a0 = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], a0);
+        a1 = fmaf(rs ? rs[m + 1] : 1.f, X[(m + 1) * ld + j], a1);
+        a2 = fmaf(rs ? rs[m + 2] : 1.f, X[(m + 2) * ld + j], a2);
+        a3 = fmaf(rs ? rs[m + 3] : 1.f, X[(m + 3) * ld + j], a3);
+      }
+      for (; m < r1; ++m) a0 = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], a0);
     } else {
-      for (int64_t m = r0; m < r1; ++m) acc += rs[m];
+      for (int64_t m = r0; m < r1; ++m) a0 += rs[m];
     }
-    d[j] = acc;
+    d[j] = (a0 + a1) + (a2 + a3);
   }
 }
 
@@ -166,8 +184,16 @@ __global__ void mr_reduce_adam_kernel(const float* __restrict__ partial, int n_c
                                       float eps, float step_size, float bc2_sqrt) {
   const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (e >= plen) return;
-  float g = 0.f;
-  for (int c = 0; c < n_chunks; ++c) g += partial[(int64_t)c * plen + e];
+  float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;  // four chunks in flight, fixed order
+  int c = 0;
+  for (; c + 3 < n_chunks; c += 4) {
+    g0 += partial[(int64_t)c * plen + e];
+    g1 += partial[(int64_t)(c + 1) * plen + e];
+    g2 += partial[(int64_t)(c + 2) * plen + e];
+    g3 += partial[(int64_t)(c + 3) * plen + e];
+  }
+  for (; c < n_chunks; ++c) g0 += partial[(int64_t)c * plen + e];
+  float g = (g0 + g1) + (g2 + g3);
   if (e < n_w) g *= wscale;
   if (grad_out != nullptr) grad_out[e] = g;
   if (p == nullptr) return;
@@ -191,6 +217,8 @@ struct iqlb_mr_trainer {
   int max_chunks = 0;
   float *X = nullptr, *pred = nullptr, *rowgrad = nullptr, *partial = nullptr, *G0 = nullptr, *G1 = nullptr;
   float* out2 = nullptr;
+  float* pair_out = nullptr;        // [max_rows] per-pair loss / accuracy terms
+  unsigned int* counter = nullptr;  // blocks of the loss kernel that have finished (reset by the last one)
   std::vector<float*> Z, H;
   GemmTask* d_tasks = nullptr;  // [depth][max_chunks] weight-gradient tasks
   int64_t tasks_rows = -1;      // row count the device task array was built for
@@ -199,7 +227,7 @@ struct iqlb_mr_trainer {
 static void mr_free(iqlb_mr_trainer* h) {
   if (!h) return;
   cudaFree(h->X); cudaFree(h->pred); cudaFree(h->rowgrad); cudaFree(h->partial); cudaFree(h->G0); cudaFree(h->G1);
-  cudaFree(h->out2); cudaFree(h->d_tasks);
+  cudaFree(h->out2); cudaFree(h->d_tasks); cudaFree(h->pair_out); cudaFree(h->counter);
   for (float* p : h->Z) cudaFree(p);
   for (float* p : h->H) cudaFree(p);
   delete h;
@@ -243,6 +271,9 @@ extern "C" int iqlb_mr_create(int32_t d_in, const int32_t* host_widths, int32_t 
   MR_ALLOC(h->G0, max_rows * h->maxw);
   MR_ALLOC(h->G1, max_rows * h->maxw);
   MR_ALLOC(h->out2, 2);
+  MR_ALLOC(h->pair_out, max_rows);
+  MR_ALLOC(h->counter, 1);
+  cudaMemset(h->counter, 0, sizeof(unsigned int));
   h->Z.assign(depth, nullptr); h->H.assign(depth, nullptr);
   for (int l = 0; l < depth; ++l) { MR_ALLOC(h->Z[l], max_rows * h->widths[l]); MR_ALLOC(h->H[l], max_rows * h->widths[l]); }
 #undef MR_ALLOC
@@ -319,7 +350,8 @@ extern "C" int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float
   cudaStream_t st = (cudaStream_t)stream;
   rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, false, st);
   if (rc) return rc;
-  mr_loss_kernel<<<1, 256, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, nullptr, out2 ? out2 : h->out2);
+  mr_loss_kernel<<<B, 64, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, nullptr, h->pair_out, h->counter,
+                                   out2 ? out2 : h->out2);
   IQLB_LAUNCH_CHECK();
   if (pred_out) IQLB_CUDA(cudaMemcpyAsync(pred_out, h->pred, (size_t)2 * B * T * sizeof(float), cudaMemcpyDeviceToDevice, st));
   return IQLB_OK;
@@ -340,8 +372,8 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
   const int L = h->depth;
   rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, true, st);
   if (rc) return rc;
-  mr_loss_kernel<<<1, 256, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, h->rowgrad,
-                                    out2 ? out2 : h->out2);
+  mr_loss_kernel<<<B, 64, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, h->rowgrad, h->pair_out,
+                                   h->counter, out2 ? out2 : h->out2);
   IQLB_LAUNCH_CHECK();
 
   // row chunks of the split weight-gradient reductions

@@ -19,8 +19,10 @@ from iqlpref_b200.mr_training import MRTrainer  # noqa: E402
 from iqlpref_b200.reward_models.q_mlp import MLP  # noqa: E402
 from oracle.mr_train_oracle import MRTrainerOracle, synth_batch  # noqa: E402  (CPU baseline leg only)
 
-CASES = [("antmaze_T25", 29, 8, [128] * 3, 256, 25), ("antmaze_T100", 29, 8, [128] * 3, 256, 100),
+CASES_ALL = [("antmaze_T25", 29, 8, [128] * 3, 256, 25), ("antmaze_T100", 29, 8, [128] * 3, 256, 100),
          ("pen_T100_w256", 45, 24, [256] * 3, 256, 100)]
+_only = os.environ.get("MR_CASES")
+CASES = [c for c in CASES_ALL if not _only or c[0] in _only.split(",")]
 
 
 def main():

@@ -3,7 +3,7 @@
 (gp_reward-priors/optbnn/training/training.py:27-114; tests/golden/mr_train.npz, oracle/gen_golden_mr.py) and
 against the numpy oracle on fresh seeded batches for every activation, both pooling modes, ragged / empty masks,
 NaN rewards and the production batch shape.  Tolerances: loss 1e-4 relative, gradients 1e-3 relative to the tensor's
-largest entry, accuracy exact, parameters after K Adam steps 3e-5 absolute except elements whose gradient is rounding
+largest entry (floored at 1e-2 of the whole gradient's largest entry), accuracy exact, parameters after K Adam steps 3e-5 absolute except elements whose gradient is rounding
 noise (Adam moves those by ~lr per step in either direction; at most 2 %, bounded by 2*K*lr)."""
 import os
 
@@ -48,9 +48,12 @@ def split(flat, weights):
 
 
 def assert_grads_close(got, want, rel=1e-3):
+    # per tensor, relative to its largest entry - with a floor at 1e-2 of the whole gradient's largest entry: the
+    # output bias has a Bradley-Terry gradient of exactly 0 in real arithmetic, so both sides hold rounding noise there
+    floor = 1e-2 * max(float(np.abs(np.asarray(gr)).max()) for gr in want)
     for g, gr in zip(got, want):
         gr = np.asarray(gr).reshape(g.shape)
-        np.testing.assert_allclose(g, gr, rtol=0, atol=rel * max(float(np.abs(gr).max()), 1e-6))
+        np.testing.assert_allclose(g, gr, rtol=0, atol=rel * max(float(np.abs(gr).max()), floor))
 
 
 def assert_params_close(got, want, K, lr=3e-4):
@@ -153,7 +156,7 @@ def test_trained_net_feeds_the_relabel_path_and_checkpoints_round_trip(tmp_path)
     torch.save(tr.state_dict(), tmp_path / "checkpoint_0.pt")  # run_mr_training.py:147-151
     after1 = tr.train(tb(b1))
     x = torch.from_numpy(rng.standard_normal((50, 7)).astype(np.float32)).cuda()
-    r_direct = ensemble_predict([tr.member()], x, "mean", activation="tanh", precision="fp32")
+    r_direct = ensemble_predict([tr.member()], x, "mean", activation="tanh")
     assert torch.equal(r_direct, net(x).reshape(-1))
     # resume from the file in a fresh trainer: identical continuation
     tr2, net2, _ = make_trainer(weights, "tanh", "mean")

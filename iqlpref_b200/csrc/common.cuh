@@ -54,6 +54,21 @@ __device__ __forceinline__ float apply_act(int act, float x) {
     default: return x;
   }
 }
+// d act / dz at pre-activation z (backward pass of the reward-MLP trainer)
+__device__ __forceinline__ float act_grad(int act, float z) {
+  switch (act) {
+    case IQLB_ACT_RELU: return z > 0.f ? 1.f : 0.f;
+    case IQLB_ACT_TANH: { const float t = tanhf(z); return 1.f - t * t; }
+    case IQLB_ACT_COS: return -sinf(z);
+    case IQLB_ACT_SIN: return cosf(z);
+    case IQLB_ACT_LINEAR: return 1.f;
+    case IQLB_ACT_RBF: return -2.f * z * expf(-z * z);
+    case IQLB_ACT_SWISH: { const float s = 1.0f / (1.0f + expf(-z)); return s * (1.f + z * (1.f - s)); }
+    case IQLB_ACT_SOFTPLUS: return z > 20.f ? 1.f : 1.0f / (1.0f + expf(-z));
+    case IQLB_ACT_LEAKY_RELU: return z > 0.f ? 1.f : 0.01f;
+    default: return 1.f;
+  }
+}
 #endif
 
 // ---- Philox4x32-10 exactly as cuRAND's curand_Philox4x32_10 (curand_philox4x32_x.h) ----------

@@ -3,7 +3,8 @@
 //   FWD        C[m,n] = relu(sum_k A[m,k] * W[n,k] + bias[n])        (nn.Linear forward)
 //   BWD_DATA   C[m,n] = mask[m,n] > 0 ? sum_k A[m,k] * W[k,n] : 0     (dX = dY W, through ReLU)
 //   BWD_WEIGHT C[m,n] = sum_k A[k,m] * X[k,n];  bias_grad[m] = sum_k A[k,m]   (dW = dY^T X, db)
-//   FWD_KN     C[m,n] = act(scale * sum_k A[m,k] * W[k,n] + bias[n])   (RewardMLP scaled Linear)
+//   FWD_KN     C[m,n] = act(scale * sum_k A[m,k] * W[k,n] + bias[n])   (RewardMLP scaled Linear; pre-activation kept in t.pre)
+//   LINEAR     C[m,n] = act(sum_k A[m,k] * W[n,k] + bias[n]) (+ residual); with t.pre: scale * acc * act'(pre[m,n])
 // 128 x BN tile, BK = 8, 256 threads, 8 x TN outputs per thread, register-prefetched.
 #include "iql_step.cuh"
 
@@ -106,6 +107,47 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
     __syncthreads();
   }
 
+  // full-width tiles of the row-major outputs: 128-bit stores (a warp writes two 256-byte row segments per instruction)
+  if constexpr (TN == 8 && (MODE == GEMM_FWD_KN || MODE == GEMM_LINEAR)) {
+    auto al16 = [](const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    if (n0 + BN <= t.N && (t.ldc & 3) == 0 && al16(t.C) && al16(t.pre) && al16(t.mask) && al16(t.bias)) {
+#pragma unroll
+      for (int i = 0; i < TM; ++i) {
+        const int m = m0 + (i < 4 ? ty * 4 + i : BM / 2 + ty * 4 + (i - 4));
+        if (m >= t.M) continue;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int n = n0 + h * (BN / 2) + tx * 4;
+          const int64_t o = (int64_t)m * t.ldc + n;
+          float v[4] = {acc[i][h * 4], acc[i][h * 4 + 1], acc[i][h * 4 + 2], acc[i][h * 4 + 3]};
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (t.bias != nullptr) b4 = __ldg(reinterpret_cast<const float4*>(t.bias + n));
+          const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+          if (MODE == GEMM_FWD_KN) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = fmaf(t.scale, v[j], b[j]);
+            if (t.pre != nullptr) *reinterpret_cast<float4*>(t.pre + o) = make_float4(v[0], v[1], v[2], v[3]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = apply_act(t.act, v[j]);
+          } else if (t.pre != nullptr) {  // data gradient through the activation below: scale * acc * act'(z)
+            const float4 z4 = *reinterpret_cast<const float4*>(t.pre + o);
+            const float z[4] = {z4.x, z4.y, z4.z, z4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = t.scale * v[j] * act_grad(t.act, z[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = apply_act(t.act, v[j] + b[j]);
+            if (t.mask != nullptr) {
+              const float4 r4 = *reinterpret_cast<const float4*>(t.mask + o);
+              v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
+            }
+          }
+          *reinterpret_cast<float4*>(t.C + o) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+      return;
+    }
+  }
   uint64_t drop_seed = 0, drop_ctr = 0;
   if (MODE == GEMM_FWD && t.drop_thresh != 0) { drop_seed = *t.drop_rng; drop_ctr = (uint64_t)(*t.drop_it) * 4ull; }
 #pragma unroll
@@ -135,6 +177,8 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
         v = fmaf(t.scale, v, __ldg(t.bias + n));
         if (t.pre != nullptr) t.pre[(int64_t)m * t.ldc + n] = v;
         v = apply_act(t.act, v);
+      } else if (MODE == GEMM_LINEAR && t.pre != nullptr) {  // scale * (A W^T) * act'(pre): back through an activation
+        v = t.scale * v * act_grad(t.act, t.pre[(int64_t)m * t.ldc + n]);
       } else if (MODE == GEMM_LINEAR) {  // nn.Linear: act(A W^T + bias) (+ residual, carried in t.mask)
         v = apply_act(t.act, v + (t.bias ? __ldg(t.bias + n) : 0.f));
         if (t.mask != nullptr) v += t.mask[(int64_t)m * t.ldc + n];

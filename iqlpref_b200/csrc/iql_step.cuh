@@ -79,7 +79,8 @@ struct GemmTask {
   int drop_layer;
   const uint64_t* drop_rng;  // &rng[2 * agent] (seed)
   const int64_t* drop_it;    // &it[agent]
-  float* pre;                // FWD_KN (nullable): pre-activation scale * acc + bias, same shape/ld as C (kept for the backward pass)
+  float* pre;                // FWD_KN (nullable): pre-activation scale * acc + bias, same shape/ld as C (kept for the backward pass);
+                             // LINEAR (nullable): read instead - C = scale * acc * act'(pre) (data gradient through an activation)
 };
 
 enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3, GEMM_LINEAR = 4 };

@@ -13,21 +13,6 @@
 
 namespace iqlb {
 
-__device__ __forceinline__ float act_grad(int act, float z) {
-  switch (act) {
-    case IQLB_ACT_RELU: return z > 0.f ? 1.f : 0.f;
-    case IQLB_ACT_TANH: { const float t = tanhf(z); return 1.f - t * t; }
-    case IQLB_ACT_COS: return -sinf(z);
-    case IQLB_ACT_SIN: return cosf(z);
-    case IQLB_ACT_LINEAR: return 1.f;
-    case IQLB_ACT_RBF: return -2.f * z * expf(-z * z);
-    case IQLB_ACT_SWISH: { const float s = 1.0f / (1.0f + expf(-z)); return s * (1.f + z * (1.f - s)); }
-    case IQLB_ACT_SOFTPLUS: return z > 20.f ? 1.f : 1.0f / (1.0f + expf(-z));
-    case IQLB_ACT_LEAKY_RELU: return z > 0.f ? 1.f : 0.01f;
-    default: return 1.f;
-  }
-}
-
 // X[(seg*B + b)*T + t] = cat(states_seg[b,t,:], actions_seg[b,t,:])   (training.py:47-54)
 __global__ void mr_pack_kernel(const float* __restrict__ s1, const float* __restrict__ a1,
                                const float* __restrict__ s2, const float* __restrict__ a2, int64_t BT, int S, int A,
@@ -136,17 +121,6 @@ __global__ void mr_head_bwd_kernel(const float* __restrict__ rowgrad, const floa
     const int64_t m = e / w;
     const int k = (int)(e % w);
     dZ[m * ld + k] = rowgrad[m] * __ldg(w_out + k) * scale * act_grad(act, Z[m * ld + k]);
-  }
-}
-
-// G[m,k] = scale * G[m,k] * act'(Z[m,k])   (in place: dH -> dZ of the layer below)
-__global__ void mr_act_bwd_kernel(float* __restrict__ G, const float* __restrict__ Z, int ld, int w, int64_t M,
-                                  float scale, int act) {
-  const int64_t total = M * w;
-  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t m = e / w;
-    const int k = (int)(e % w);
-    G[m * ld + k] = scale * G[m * ld + k] * act_grad(act, Z[m * ld + k]);
   }
 }
 
@@ -445,17 +419,16 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
                                                plen);
     IQLB_LAUNCH_CHECK();
     if (l > 0) {
-      GemmTask t{};  // dH[m, k_in] = sum_n dZ[m, n] W[k_in, n]
+      GemmTask t{};  // dH[m, k_in] = sum_n dZ[m, n] W[k_in, n], through the activation of the layer below
       t.A = dz; t.lda = w;
       t.Bm = params + h->offW[l]; t.ldb = w;
       t.C = other; t.ldc = prev;
       t.M = (int)M; t.N = prev; t.K = w;
-      t.act = IQLB_ACT_LINEAR;
+      t.pre = h->Z[l - 1];                    // epilogue: dZ of the layer below = scale * dH * act'(Z)
+      t.scale = 1.0f / sqrtf((float)prev);
+      t.act = h->act;
       rc = launch_gemm(GEMM_LINEAR, t, st);
       if (rc) return rc;
-      mr_act_bwd_kernel<<<ew_blocks, 256, 0, st>>>(other, h->Z[l - 1], prev, prev, M, 1.0f / sqrtf((float)prev),
-                                                   h->act);
-      IQLB_LAUNCH_CHECK();
     }
     rc = reduce_adam(h->offW[l], plen, (int64_t)prev * w, 1.0f / sqrtf((float)prev));
     if (rc) return rc;

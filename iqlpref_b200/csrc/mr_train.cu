@@ -133,14 +133,15 @@ __global__ void __launch_bounds__(128) mr_colsum_kernel(const float* __restrict_
   const int64_t r1 = r0 + chunk_rows < M ? r0 + chunk_rows : M;
   float* d = dst + (int64_t)blockIdx.x * plen;
   for (int j = threadIdx.x; j < ncols + (rs_sum ? 1 : 0); j += blockDim.x) {
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four rows in flight
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     if (j < ncols) {
       int64_t m = r0;
-      for (; m + 3 < r1; m += 4) {
-        a0 = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], a0);
-        a1 = fmaf(rs ? rs[m + 1] : 1.f, X[(m + 1) * ld + j], a1);
-        a2 = fmaf(rs ? rs[m + 2] : 1.f, X[(m + 2) * ld + j], a2);
-        a3 = fmaf(rs ? rs[m + 3] : 1.f, X[(m + 3) * ld + j], a3);
+      for (; m + 7 < r1; m += 8) {  // eight rows in flight per thread
+        float x[8], r[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { x[u] = X[(m + u) * ld + j]; r[u] = rs ? rs[m + u] : 1.f; }
+        a0 = fmaf(r[0], x[0], a0); a1 = fmaf(r[1], x[1], a1); a2 = fmaf(r[2], x[2], a2); a3 = fmaf(r[3], x[3], a3);
+        a0 = fmaf(r[4], x[4], a0); a1 = fmaf(r[5], x[5], a1); a2 = fmaf(r[6], x[6], a2); a3 = fmaf(r[7], x[7], a3);
       }
       for (; m < r1; ++m) a0 = fmaf(rs ? rs[m] : 1.f, X[m * ld + j], a0);
     } else {
@@ -152,22 +153,33 @@ __global__ void __launch_bounds__(128) mr_colsum_kernel(const float* __restrict_
 
 // g[e] = (e < n_w ? wscale : 1) * sum_c partial[c*plen + e], then torch.optim.Adam on element e
 // (optim/adam.py: exp_avg.lerp_(g, 1-b1); exp_avg_sq = b2*v + (1-b2) g^2; p -= step_size * m / (sqrt(v)/sqrt(bc2) + eps)).
-__global__ void mr_reduce_adam_kernel(const float* __restrict__ partial, int n_chunks, int64_t plen, int64_t n_w,
-                                      float wscale, float* __restrict__ p, float* __restrict__ m,
-                                      float* __restrict__ v, float* __restrict__ grad_out, float beta1, float beta2,
-                                      float eps, float step_size, float bc2_sqrt) {
-  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (e >= plen) return;
-  float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;  // four chunks in flight, fixed order
-  int c = 0;
-  for (; c + 3 < n_chunks; c += 4) {
-    g0 += partial[(int64_t)c * plen + e];
-    g1 += partial[(int64_t)(c + 1) * plen + e];
-    g2 += partial[(int64_t)(c + 2) * plen + e];
-    g3 += partial[(int64_t)(c + 3) * plen + e];
+__global__ void __launch_bounds__(256) mr_reduce_adam_kernel(const float* __restrict__ partial, int n_chunks,
+                                                             int64_t plen, int64_t n_w, float wscale,
+                                                             float* __restrict__ p, float* __restrict__ m,
+                                                             float* __restrict__ v, float* __restrict__ grad_out,
+                                                             float beta1, float beta2, float eps, float step_size,
+                                                             float bc2_sqrt) {
+  // 64 elements x 4 chunk groups per block: group q sums chunks q, q+4, ... (eight loads in flight), then the four group sums
+  // are added in a fixed order
+  __shared__ float s_part[4][64];
+  const int ex = threadIdx.x & 63, q = threadIdx.x >> 6;
+  const int64_t e = blockIdx.x * 64ll + ex;
+  float g0 = 0.f, g1 = 0.f;
+  if (e < plen) {
+    int c = q;
+    for (; c + 28 < n_chunks; c += 32) {  // eight loads in flight per thread
+      float t[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) t[u] = partial[(int64_t)(c + 4 * u) * plen + e];
+      g0 += (t[0] + t[2]) + (t[4] + t[6]);
+      g1 += (t[1] + t[3]) + (t[5] + t[7]);
+    }
+    for (; c < n_chunks; c += 4) g0 += partial[(int64_t)c * plen + e];
   }
-  for (; c < n_chunks; ++c) g0 += partial[(int64_t)c * plen + e];
-  float g = (g0 + g1) + (g2 + g3);
+  s_part[q][ex] = g0 + g1;
+  __syncthreads();
+  if (q != 0 || e >= plen) return;
+  float g = (s_part[0][ex] + s_part[1][ex]) + (s_part[2][ex] + s_part[3][ex]);
   if (e < n_w) g *= wscale;
   if (grad_out != nullptr) grad_out[e] = g;
   if (p == nullptr) return;
@@ -387,7 +399,7 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
   const float step_size = (float)((double)lr / bc1), bc2_sqrt = (float)sqrt(bc2);
   const bool apply = lr != 0.f || exp_avg != nullptr;
   auto reduce_adam = [&](int64_t off, int64_t plen, int64_t n_w, float wscale) -> int {
-    mr_reduce_adam_kernel<<<(unsigned)((plen + 255) / 256), 256, 0, st>>>(
+    mr_reduce_adam_kernel<<<(unsigned)((plen + 63) / 64), 256, 0, st>>>(
         h->partial, n_chunks, plen, n_w, wscale, apply ? params + off : nullptr, apply ? exp_avg + off : nullptr,
         apply ? exp_avg_sq + off : nullptr, grad_out ? grad_out + off : nullptr, beta1, beta2, eps, step_size,
         bc2_sqrt);

@@ -4,9 +4,11 @@
 //   RewardMLP forward               gp_reward-priors/optbnn/bnn/nets/mlp.py:73-111, layers/linear.py:34-47
 //   optimizer                       torch.optim.Adam(net.parameters(), lr) (scripts_mr/run_mr_training.py:105)
 // One call = forward over the 2*B*T rows of both segments, masked pooling, soft-label cross entropy, backward
-// and Adam, all on the caller's stream, no host synchronisation.  fp32 FFMA GEMMs (the reference trains in fp32,
+// and Adam, ordered on the caller's stream (weight-gradient partials fork to a side stream and join back), no host
+// synchronisation.  fp32 FFMA GEMMs (the reference trains in fp32,
 // no autocast).  Weight gradients are split over row chunks (one CTA per chunk and tile) and summed in a fixed
 // order by the kernel that also applies Adam, so a step is deterministic.
+#include <cstdlib>
 #include <vector>
 
 #include "iql_step.cuh"
@@ -208,6 +210,11 @@ struct iqlb_mr_trainer {
   std::vector<float*> Z, H;
   GemmTask* d_tasks = nullptr;  // [depth][max_chunks] weight-gradient tasks
   int64_t tasks_rows = -1;      // row count the device task array was built for
+  // the weight-gradient partials of a layer and its data-gradient GEMM both read dZ and nothing of each other: the
+  // partials run on a side stream (fork / join by events, capturable) and fill the idle tail of the GEMM's last wave
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool overlap = true;  // IQLB_MR_OVERLAP=0: everything on the caller's stream
 };
 
 static void mr_free(iqlb_mr_trainer* h) {
@@ -216,6 +223,9 @@ static void mr_free(iqlb_mr_trainer* h) {
   cudaFree(h->out2); cudaFree(h->d_tasks); cudaFree(h->pair_out); cudaFree(h->counter);
   for (float* p : h->Z) cudaFree(p);
   for (float* p : h->H) cudaFree(p);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   delete h;
 }
 
@@ -266,6 +276,14 @@ extern "C" int iqlb_mr_create(int32_t d_in, const int32_t* host_widths, int32_t 
   if (cudaMalloc((void**)&h->d_tasks, (size_t)depth * h->max_chunks * sizeof(GemmTask)) != cudaSuccess) {
     cudaGetLastError(); mr_free(h);
     return fail(IQLB_ERR_NOMEM, "iqlb_mr_create: device allocation failed%s", "");
+  }
+  const char* ov = getenv("IQLB_MR_OVERLAP");
+  h->overlap = !(ov && ov[0] == '0');
+  if (h->overlap && (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess ||
+                     cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+                     cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess)) {
+    cudaGetLastError(); mr_free(h);
+    return fail(IQLB_ERR_CUDA, "iqlb_mr_create: stream / event creation failed%s", "");
   }
   *out = h;
   return IQLB_OK;
@@ -425,11 +443,19 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
     float* dz = ((L - 1 - l) % 2 == 0) ? h->G0 : h->G1;
     float* other = ((L - 1 - l) % 2 == 0) ? h->G1 : h->G0;
     const int64_t plen = (int64_t)prev * w + w;
-    rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, w <= 32, st);
+    // the partial buffer is free again (the previous reduce on `st` has been enqueued) and dZ of this layer is ready
+    const bool fork = h->overlap && l > 0;
+    cudaStream_t ws = fork ? h->side : st;
+    if (fork) {
+      IQLB_CUDA(cudaEventRecord(h->ev_fork, st));
+      IQLB_CUDA(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    }
+    rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, w <= 32, ws);
     if (rc) return rc;
-    mr_colsum_kernel<<<n_chunks, 128, 0, st>>>(dz, w, w, nullptr, 0, M, chunk_rows, h->partial + (int64_t)prev * w,
+    mr_colsum_kernel<<<n_chunks, 128, 0, ws>>>(dz, w, w, nullptr, 0, M, chunk_rows, h->partial + (int64_t)prev * w,
                                                plen);
     IQLB_LAUNCH_CHECK();
+    if (fork) IQLB_CUDA(cudaEventRecord(h->ev_join, h->side));
     if (l > 0) {
       GemmTask t{};  // dH[m, k_in] = sum_n dZ[m, n] W[k_in, n], through the activation of the layer below
       t.A = dz; t.lda = w;
@@ -442,6 +468,7 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
       rc = launch_gemm(GEMM_LINEAR, t, st);
       if (rc) return rc;
     }
+    if (fork) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
     rc = reduce_adam(h->offW[l], plen, (int64_t)prev * w, 1.0f / sqrtf((float)prev));
     if (rc) return rc;
   }

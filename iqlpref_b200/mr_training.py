@@ -177,3 +177,73 @@ class MRTrainer:
         self.net.load_state_dict(state_dict["net"])  # copies into the views of the flat buffer
         self.opt.load_state_dict(state_dict["optimizer"])
         self._adopt_optimizer_state()
+
+
+def fit_mr(model: MRTrainer, training_batches, val_batches, epochs: int, eval_every: int = 5,
+           checkpoints_path: str = None, criteria_key: str = "acc", activations: str = None, log=None):
+    """The epoch loop of `scripts_mr/run_mr_training.py:117-215` around `MRTrainer`: epoch 0 evaluates only, every
+    `eval_every` epochs the validation pass runs and `checkpoint_{epoch}.pt` is written (the snapshot ensemble that
+    `qlearning_dataset_mr_ensemble` reads), `best_model.pt` follows the reference's criteria ("acc": higher accuracy,
+    ties broken by lower loss; "loss": the mirror image).  `training_batches` / `val_batches` are re-iterable
+    collections of 9-tensor batches (a `DataLoader` over `Pref_H5Dataset`, or a list).  With `activations` given, a
+    `config.yaml` holding it is written beside the snapshots (what `_mr_activations`, iql.py:1339-1342, reads).
+    Returns the per-epoch metric dicts (what the reference sends to wandb)."""
+    import os
+
+    import numpy as np
+    if criteria_key not in ("acc", "loss"):
+        raise ValueError(f"criteria_key must be 'acc' or 'loss', got {criteria_key!r}")
+    if checkpoints_path is not None:
+        os.makedirs(checkpoints_path, exist_ok=True)
+        if activations is not None:
+            import yaml
+            with open(os.path.join(checkpoints_path, "config.yaml"), "w") as f:
+                yaml.safe_dump({"activations": activations}, f)
+
+    def save(name):
+        if checkpoints_path is not None:
+            torch.save(model.state_dict(), os.path.join(checkpoints_path, name))
+
+    c_best_epoch, best_acc, best_loss = 0, -np.inf, np.inf
+    history = []
+    for epoch in range(epochs + 1):
+        metrics = {"training_loss": [], "training_acc": [], "best_epoch": c_best_epoch, "eval_loss": [], "eval_acc": [],
+                   f"eval_{criteria_key}_best": best_acc if criteria_key == "acc" else best_loss}
+        if epoch:
+            for batch in training_batches:
+                for key, val in model.train(batch).items():
+                    metrics[key].append(val)
+        else:
+            metrics["training_loss"] = np.nan
+        if epoch % eval_every == 0:
+            for batch in val_batches:
+                for key, val in model.evaluation(batch).items():
+                    metrics[key].append(val)
+            loss, acc = np.mean(metrics["eval_loss"]), np.mean(metrics["eval_acc"])
+            save(f"checkpoint_{epoch}.pt")
+            first, second = (acc, -loss) if criteria_key == "acc" else (-loss, acc)
+            best_first, best_second = (best_acc, -best_loss) if criteria_key == "acc" else (-best_loss, best_acc)
+            if first > best_first or (first == best_first and second > best_second):
+                c_best_epoch = epoch
+                metrics["best_epoch"] = c_best_epoch
+                save("best_model.pt")
+            if first > best_first:  # run_mr_training.py:153-205: each branch updates only what it compared
+                best_acc, best_loss = (acc, min(loss, best_loss)) if criteria_key == "acc" else (max(acc, best_acc), loss)
+            elif first == best_first:
+                if second > best_second:
+                    if criteria_key == "acc":
+                        best_loss = loss
+                    else:
+                        best_acc = acc
+            else:
+                if criteria_key == "acc":
+                    best_loss = min(loss, best_loss)
+                else:
+                    best_acc = max(acc, best_acc)
+            metrics[f"eval_{criteria_key}_best"] = best_acc if criteria_key == "acc" else best_loss
+        metrics = {k: (float(np.mean(v)) if isinstance(v, list) else v) for k, v in metrics.items()
+                   if not (isinstance(v, list) and not len(v))}
+        history.append(metrics)
+        if log is not None:
+            log(metrics, epoch)
+    return history

@@ -181,3 +181,44 @@ def test_errors():
     bad = synth_batch(np.random.default_rng(0), 2, 3, 5, 2)  # 7 inputs for a 6-input net
     with pytest.raises(RuntimeError):
         tr.train(tb(bad))
+
+
+def test_fit_loop_emits_the_snapshot_ensemble_the_relabel_reads(tmp_path):
+    """run_mr_training.py:117-215 -> checkpoint_{epoch}.pt / best_model.pt -> qlearning_dataset_mr_ensemble (iql.py:1085)."""
+    from iqlpref_b200.mr_training import fit_mr
+    from iqlpref_b200.relabel import _discover_mr_snapshots, ensemble_predict, qlearning_dataset_mr_ensemble, _state_to_member
+    rng = np.random.default_rng(8)
+    S, A, B, T = 6, 2, 16, 5
+    weights = [rng.standard_normal((8, 64)).astype(np.float32), np.zeros(64, np.float32),
+               rng.standard_normal((64, 64)).astype(np.float32), np.zeros(64, np.float32),
+               rng.standard_normal((64, 1)).astype(np.float32), np.zeros(1, np.float32)]
+    tr, net, _ = make_trainer(weights, "tanh", "mean", lr=1e-2)
+    train_b = [tb(synth_batch(rng, B, T, S, A)) for _ in range(3)]
+    val_b = [tb(synth_batch(rng, B, T, S, A)) for _ in range(2)]
+    ckpt_dir = str(tmp_path / "mr")
+    hist = fit_mr(tr, train_b, val_b, epochs=6, eval_every=2, checkpoints_path=ckpt_dir, criteria_key="loss",
+                  activations="tanh")
+    assert len(hist) == 7 and np.isnan(hist[0]["training_loss"]) and "eval_loss" in hist[0] and "eval_loss" not in hist[1]
+    assert hist[3]["training_loss"] < hist[1]["training_loss"]  # it learns the training pairs
+    paths = _discover_mr_snapshots(ckpt_dir, burn_in=2)
+    assert [os.path.basename(p) for p in paths] == ["checkpoint_2.pt", "checkpoint_4.pt", "checkpoint_6.pt"]
+    assert os.path.isfile(os.path.join(ckpt_dir, "best_model.pt"))
+    best = torch.load(os.path.join(ckpt_dir, "best_model.pt"), weights_only=False)
+    assert set(best) == {"net", "optimizer"} and "layers.linear_1.W" in best["net"]
+    # the emitted directory is a valid input of the ensemble relabel; its rewards are the CVaR over the snapshots
+    n = 40
+    ds = {"observations": rng.standard_normal((n, S)).astype(np.float32),
+          "actions": rng.uniform(-1, 1, (n, A)).astype(np.float32),
+          "rewards": np.zeros(n, np.float32), "terminals": np.zeros(n, bool), "timeouts": np.zeros(n, bool)}
+
+    class Env:
+        _max_episode_steps = 1000
+    with pytest.warns(RuntimeWarning):  # three snapshots: thin tail
+        out = qlearning_dataset_mr_ensemble(Env(), ckpt_dir, alpha=0.5, burn_in=2, device="cuda", dataset=ds)
+    members = [_state_to_member(torch.load(p, weights_only=False)["net"]) for p in paths]
+    x = torch.from_numpy(np.concatenate([ds["observations"][:-1], ds["actions"][:-1]], 1)).cuda()
+    want = ensemble_predict(members, x, "cvar", 0.5, activation="tanh").cpu().numpy()
+    np.testing.assert_allclose(out["rewards"].reshape(-1), want, rtol=1e-6, atol=1e-7)
+    # the last snapshot is the trainer's current net
+    for w, p in zip(members[-1], net.parameters()):
+        assert torch.equal(w.cuda(), p.detach())

@@ -54,8 +54,9 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
   const int tm = tile / tiles_n, tn = tile % tiles_n;
   const int m0 = tm * BM, n0 = tn * BN;
 
-  __shared__ __align__(16) float As[BK][BM + 4];
-  __shared__ __align__(16) float Bs[BK][BN + 4];
+  // two stages: the tile of step k+1 is written while step k is being read, one barrier per step
+  __shared__ __align__(16) float As2[2][BK][BM + 4];
+  __shared__ __align__(16) float Bs2[2][BK][BN + 4];
 
   const int ty = threadIdx.x / 16, tx = threadIdx.x % 16;
   float acc[TM][TN];
@@ -72,11 +73,15 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
   load_tile<B_KC, BN>(t.Bm, t.ldb, n0, t.N, 0, t.K, rb);
   const bool want_bsum = (MODE == GEMM_BWD_WEIGHT) && tn == 0 && t.bias_grad != nullptr;
 
-  for (int k0 = 0; k0 < t.K; k0 += BK) {
-    store_tile<A_KC, BM>(As, ra);
-    store_tile<B_KC, BN>(Bs, rb);
-    __syncthreads();
-    if (k0 + BK < t.K) {
+  store_tile<A_KC, BM>(As2[0], ra);
+  store_tile<B_KC, BN>(Bs2[0], rb);
+  __syncthreads();
+  int stage = 0;
+  for (int k0 = 0; k0 < t.K; k0 += BK, stage ^= 1) {
+    float (*As)[BM + 4] = As2[stage];
+    float (*Bs)[BN + 4] = Bs2[stage];
+    const bool more = k0 + BK < t.K;
+    if (more) {
       load_tile<A_KC, BM>(t.A, t.lda, m0, t.M, k0 + BK, t.K, ra);
       load_tile<B_KC, BN>(t.Bm, t.ldb, n0, t.N, k0 + BK, t.K, rb);
     }
@@ -103,6 +108,10 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
 #pragma unroll
         for (int i = 0; i < TM; ++i) asum[i] += a[i];
       }
+    }
+    if (more) {  // the other stage was last read before the previous barrier
+      store_tile<A_KC, BM>(As2[stage ^ 1], ra);
+      store_tile<B_KC, BN>(Bs2[stage ^ 1], rb);
     }
     __syncthreads();
   }
@@ -190,13 +199,13 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
 }
 
 template <int MODE, int BN>
-__global__ void __launch_bounds__(256) grouped_gemm_kernel(const GemmTask* __restrict__ tasks) {
+__global__ void __launch_bounds__(256, 2) grouped_gemm_kernel(const GemmTask* __restrict__ tasks) {
   const GemmTask t = tasks[blockIdx.y];
   gemm_body<MODE, BN>(t, (int)blockIdx.x);
 }
 
 template <int MODE, int BN>
-__global__ void __launch_bounds__(256) single_gemm_kernel(const GemmTask t) {
+__global__ void __launch_bounds__(256, 2) single_gemm_kernel(const GemmTask t) {
   gemm_body<MODE, BN>(t, (int)blockIdx.x);
 }
 

@@ -112,7 +112,9 @@ class MRTrainer:
         return ts, int(B), int(T), int(S), int(A)
 
     # ---------------------------------------------------------------- training.py:27-72
-    def train(self, batch: TensorBatch, return_grad: bool = False) -> Dict[str, float]:
+    def train(self, batch: TensorBatch, return_grad: bool = False, sync: bool = True) -> Dict[str, float]:
+        """`sync=False` skips the reference's per-step `loss.item()`: the log holds 0-dim CUDA tensors (a snapshot of
+        this step's loss / accuracy) and the host runs ahead of the device."""
         ts, B, T, S, A = self._unpack(batch)
         if not self.net.training:
             self.net.train()
@@ -126,7 +128,11 @@ class MRTrainer:
                                               float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]),
                                               float(g["eps"]), self.step_count, _lib.ptr(self._out2), _lib.ptr(grad),
                                               _lib.stream_ptr(self.device)), "iqlb_mr_train_step")
-        loss, acc = self._out2.tolist()  # the reference's loss.item() sync (training.py:65-70)
+        if sync:
+            loss, acc = self._out2.tolist()  # the reference's loss.item() sync (training.py:65-70)
+        else:
+            snap = self._out2.clone()
+            loss, acc = snap[0], snap[1]
         log = {"training_loss": loss, "training_acc": acc}
         if return_grad:
             log["grad"] = grad

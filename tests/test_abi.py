@@ -81,3 +81,23 @@ def test_host_mirror_surface():
     assert cvar_n_tail(0.9, 40) == 3 and cvar_n_tail(0.9, 10) == 1 and cvar_n_tail(0.0, 7) == 7
     st, sl = pt_windows_from_steps(np.array([0, 5, 9, 10, 57]), 10)
     assert st.tolist() == [0, 0, 0, 1, 48] and sl.tolist() == [1, 6, 10, 10, 10]
+
+
+def test_mr_trainer_host_surface():
+    """MRTrainer mirror (training.py:11-129): argument checks that need no GPU; there is no CPU path."""
+    import torch
+    from iqlpref_b200.mr_training import MRTrainer, fit_mr
+    from iqlpref_b200.reward_models.q_mlp import MLP
+    net = MLP(6, 1, [8, 8], "relu")
+    opt = torch.optim.Adam(net.parameters(), lr=3e-4)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        MRTrainer(net, opt, num_datapoints=10, device="cpu")
+    with pytest.raises(ValueError, match="bt_pool_logit"):
+        MRTrainer(net, opt, num_datapoints=10, device="cuda", bt_pool="median")
+    with pytest.raises(NotImplementedError):
+        MRTrainer(net, torch.optim.SGD(net.parameters(), lr=0.1), num_datapoints=10, device="cuda")
+    with pytest.raises(NotImplementedError):
+        MRTrainer(net, torch.optim.Adam(net.parameters(), lr=1e-3, weight_decay=0.1), num_datapoints=10, device="cuda")
+    with pytest.raises(ValueError, match="criteria_key"):
+        fit_mr(None, [], [], epochs=1, criteria_key="f1")
+    assert list(net.state_dict())[:4] == ["layers.0.W", "layers.0.b", "layers.linear_1.W", "layers.linear_1.b"]

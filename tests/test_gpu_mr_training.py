@@ -159,6 +159,11 @@ def test_trained_net_feeds_the_relabel_path_and_checkpoints_round_trip(tmp_path)
     r_direct = ensemble_predict([tr.member()], x, "mean", activation="tanh")
     assert torch.equal(r_direct, net(x).reshape(-1))
     # resume from the file in a fresh trainer: identical continuation
+    # sync=False: same step, the log holds device scalars
+    tr3, net3, _ = make_trainer(weights, "tanh", "mean")
+    tr3.train(tb(b0), sync=False)
+    lazy = tr3.train([t.cuda() for t in tb(b1)], sync=False)
+    assert torch.is_tensor(lazy["training_loss"]) and float(lazy["training_loss"]) == after1["training_loss"]
     tr2, net2, _ = make_trainer(weights, "tanh", "mean")
     tr2.load_state_dict(torch.load(tmp_path / "checkpoint_0.pt", weights_only=False))
     assert tr2.step_count == 1

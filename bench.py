@@ -360,7 +360,22 @@ def run_cuda(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL writes its debug lines (the version banner at NCCL_DEBUG=VERSION) to stdout by default; stdout carries
+        # exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # ... and at NCCL_DEBUG=VERSION / WARN it ignores NCCL_DEBUG_FILE: point fd 1 at stderr while the communicator
+        # is created (eager with device_id; the barrier covers a lazy one)
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
 
     def barrier():
         if world > 1:

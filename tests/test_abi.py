@@ -101,3 +101,16 @@ def test_mr_trainer_host_surface():
     with pytest.raises(ValueError, match="criteria_key"):
         fit_mr(None, [], [], epochs=1, criteria_key="f1")
     assert list(net.state_dict())[:4] == ["layers.0.W", "layers.0.b", "layers.linear_1.W", "layers.linear_1.b"]
+
+
+def test_mr_entry_points_reject_bad_arguments_without_touching_the_gpu(lib):
+    h = C.c_void_p()
+    widths = (C.c_int32 * 2)(8, 8)
+    assert lib.iqlb_mr_create(0, widths, 2, 0, 1, 64, C.byref(h)) == -1 and b"network shape" in lib.iqlb_last_error()
+    assert lib.iqlb_mr_create(6, widths, 2, 99, 1, 64, C.byref(h)) == -1 and b"activation" in lib.iqlb_last_error()
+    assert lib.iqlb_mr_create(6, widths, 2, 0, 1, 63, C.byref(h)) == -1 and b"max_rows" in lib.iqlb_last_error()
+    assert lib.iqlb_mr_create(6, widths, 2, 0, 1, 64, None) == -1
+    assert lib.iqlb_mr_param_count(None, None) == -1
+    assert lib.iqlb_mr_train_step(None, *([None] * 10), 1, 1, 1, 1, 0.0, 0.9, 0.999, 1e-8, 1, None, None, None) == -1
+    assert lib.iqlb_mr_eval(None, *([None] * 8), 1, 1, 1, 1, None, None, None) == -1
+    assert lib.iqlb_mr_destroy(None) == 0

@@ -338,7 +338,8 @@ static int mr_check_batch(const iqlb_mr_trainer* h, const void* params, const vo
                           const void* m1, const void* s2, const void* a2, const void* m2, const void* labels,
                           int B, int T, int S, int A) {
   IQLB_REQUIRE(h != nullptr, "null trainer");
-  IQLB_REQUIRE(params && s1 && a1 && m1 && s2 && a2 && m2 && labels, "null pointer");
+  IQLB_REQUIRE(params && s1 && m1 && s2 && m2 && labels, "null pointer");
+  IQLB_REQUIRE((a1 && a2) || A == 0, "null actions with action_dim > 0");
   IQLB_REQUIRE(B > 0 && T > 0 && S > 0 && A >= 0, "batch shape");
   IQLB_REQUIRE(S + A == h->d_in, "state_dim + action_dim must equal the network input width");
   IQLB_REQUIRE(2ll * B * T <= h->max_rows, "batch larger than max_rows given to iqlb_mr_create");

@@ -2,13 +2,17 @@
 """Headline benchmark: IQL updates/sec (B=256, summed over batched agents) on N B200s.
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K --warmup W   # CPU reference arm (oracle port)
+    python bench.py --impl reference --gpus N --steps K --warmup W   # CPU arm: the unmodified reference (baseline/_ref)
+    python bench.py --gpus N --scaling strong --agents-total 64      # BASELINE configs[4]: 64 agents split over N GPUs
 
 Workload (BASELINE.json configs[1]): synthetic antmaze-large-diverse-shaped
 replay data (1M rows, 29 obs, 8 act), batch 256, 2x256 MLPs, Gaussian actor, `--agents-per-gpu`
 independent IQL agents (seeds x normalize_reward variants, one reward column per variant) per GPU.
 One "step" = one `sample()+train()` of every agent.  Agents never communicate, so ranks share no
-data-path collective ("scaling": "weak": agents per GPU fixed).
+data-path collective ("scaling": "weak": agents per GPU fixed; `--scaling strong` fixes the total instead).
+The line also carries: `cpu_baseline` (the reference's own iql.py on the host cores, same workload, plus
+configs[0] as written under `configs0`), `reference_cuda` (the same stock-PyTorch code on this GPU, 1 agent),
+`roofline` of the dominant kernel with SURVEY 8(d)'s algorithmic bytes, and `relabel` (configs[1..3] passes).
 
 One JSON line on stdout (rank 0).  Everything else goes to stderr.
 """
@@ -124,31 +128,76 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU reference arm: the oracle port of iql.py's sample()+train() (bf16 autocast as shipped), one
-# single-threaded process per host core (the reference's own parallel model is one process per agent)
+# CPU reference arm.  The UNMODIFIED reference (`ReplayBuffer.sample()` + `ImplicitQLearning.train()` of
+# algorithms/offline/iql.py, bf16 autocast as shipped, eager) imported from /root/reference or from its
+# git-ignored, shipped copy baseline/_ref (oracle/make_ref.py): `kind: "reference"`.  Its own parallel model is one
+# OS process per agent (tr_sweeps/launch.sh:82-92), so the arm runs one single-threaded process per host core, each
+# owning its share of the agents and its own replay buffer.  If the reference cannot be imported the oracle port
+# (oracle/iql_oracle.py) runs instead and the line says `kind: "port"`.
 # ------------------------------------------------------------------------------------------------
-def _cpu_worker(wid, n_agents, rows, warmup, steps, barrier, out_q):
+def synth_dataset(rows, S, A, seed):
+    """The synthetic D4RL-shaped table of SURVEY 8d (cfg1 / cfg2), as the dict `load_d4rl_dataset` takes."""
     import numpy as np
-    import torch
-    torch.set_num_threads(1)
-    from oracle.iql_oracle import IQLOracle, OracleHParams, nets_from_reference_modules
-    from iqlpref_b200 import iql as biql
-    rng = np.random.default_rng(1000 + wid)
-    tab = [torch.from_numpy(rng.standard_normal((rows, S_DIM), dtype=np.float32)),
-           torch.from_numpy(rng.uniform(-1, 1, (rows, A_DIM)).astype(np.float32)),
-           torch.from_numpy((rng.uniform(size=rows) < 1e-3).astype(np.float32)),
-           torch.from_numpy(rng.standard_normal((rows, S_DIM), dtype=np.float32)),
-           torch.zeros(rows)]
-    agents = []
-    for a in range(n_agents):
-        torch.manual_seed(wid * 100 + a)
-        qf, vf, ac = biql.TwinQ(S_DIM, A_DIM), biql.ValueFunction(S_DIM), biql.GaussianPolicy(S_DIM, A_DIM, 1.0)
-        agents.append(IQLOracle(*nets_from_reference_modules(qf, vf, ac), OracleHParams(**HP), mode="autocast"))
+    rng = np.random.default_rng(seed)
+    rew = (rng.uniform(size=rows) < 1e-3).astype(np.float32)
+    return {"observations": rng.standard_normal((rows, S), dtype=np.float32),
+            "actions": rng.uniform(-1, 1, (rows, A)).astype(np.float32),
+            "rewards": rew, "next_observations": rng.standard_normal((rows, S), dtype=np.float32),
+            "terminals": rew > 0}
 
-    def one_step():
-        for ag in agents:
-            idx = torch.randint(0, rows, (BATCH,))  # ReplayBuffer.sample, iql.py:211-221
-            ag.step(*[t[idx] for t in tab])
+
+def reference_usable():
+    try:
+        from oracle.ref_import import reference_available
+        return bool(reference_available())
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def build_reference_agent(ref, S, A, hp, seed, device, deterministic=False):
+    """Networks, optimizers and trainer exactly as the reference's train() builds them (iql.py:1467-1515)."""
+    import torch
+    torch.manual_seed(seed)
+    qf, vf = ref.TwinQ(S, A).to(device), ref.ValueFunction(S).to(device)
+    actor = (ref.DeterministicPolicy if deterministic else ref.GaussianPolicy)(S, A, 1.0).to(device)
+    kw = {"fused": True} if str(device).startswith("cuda") else {}
+    v_opt = torch.optim.Adam(vf.parameters(), lr=hp["vf_lr"], **kw)
+    q_opt = torch.optim.Adam(qf.parameters(), lr=hp["qf_lr"], **kw)
+    a_opt = torch.optim.Adam(actor.parameters(), lr=hp["actor_lr"], **kw)
+    return ref.ImplicitQLearning(1.0, actor, a_opt, qf, q_opt, vf, v_opt, iql_tau=hp["iql_tau"], beta=hp["beta"],
+                                 max_steps=hp["max_steps"], discount=hp["discount"], tau=hp["tau"], device=str(device))
+
+
+def _cpu_worker(wid, n_agents, rows, warmup, steps, barrier, out_q, use_ref, S, A, hp, threads):
+    sys.stdout = sys.stderr  # the reference prints ("Dataset size: ..."); stdout carries exactly one JSON line
+    import torch
+    torch.set_num_threads(threads)
+    ds = synth_dataset(rows, S, A, 1000 + wid)
+    if use_ref:
+        from oracle.ref_import import load_reference_iql
+        ref = load_reference_iql()
+        buf = ref.ReplayBuffer(S, A, rows, "cpu")
+        buf.load_d4rl_dataset(ds)
+        agents = [build_reference_agent(ref, S, A, hp, wid * 100 + a, "cpu") for a in range(n_agents)]
+
+        def one_step():
+            for tr in agents:
+                tr.train(buf.sample(BATCH))  # iql.py:1535-1536
+    else:
+        from oracle.iql_oracle import IQLOracle, OracleHParams, nets_from_reference_modules
+        from iqlpref_b200 import iql as biql
+        tab = [torch.from_numpy(ds["observations"]), torch.from_numpy(ds["actions"]), torch.from_numpy(ds["rewards"]),
+               torch.from_numpy(ds["next_observations"]), torch.from_numpy(ds["terminals"].astype("float32"))]
+        agents = []
+        for a in range(n_agents):
+            torch.manual_seed(wid * 100 + a)
+            qf, vf, ac = biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0)
+            agents.append(IQLOracle(*nets_from_reference_modules(qf, vf, ac), OracleHParams(**hp), mode="autocast"))
+
+        def one_step():
+            for ag in agents:
+                idx = torch.randint(0, rows, (BATCH,))  # ReplayBuffer.sample, iql.py:211-221
+                ag.step(*[t[idx] for t in tab])
     for _ in range(warmup):
         one_step()
     barrier.wait()
@@ -160,15 +209,19 @@ def _cpu_worker(wid, n_agents, rows, warmup, steps, barrier, out_q):
     out_q.put((wid, t0, t1))
 
 
-def cpu_reference(steps, warmup, total_agents, rows=200_000, procs=None):
-    """Returns (updates_per_s, ms_per_step, cores_used, description)."""
+def cpu_reference(steps, warmup, total_agents, rows, procs=None, S=S_DIM, A=A_DIM, hp=None, threads=1):
+    """One `sample()+train()` of every agent per step, `procs` processes x `threads` torch threads.
+    Returns a dict: updates/s, ms per step, cores used, kind, description."""
     import multiprocessing as mp
+    hp = hp or HP
     cores = len(os.sched_getaffinity(0))
     procs = procs or max(1, min(cores, total_agents))
     per = max(1, total_agents // procs)
+    use_ref = reference_usable()
     ctx = mp.get_context("spawn")
     barrier, q = ctx.Barrier(procs), ctx.Queue()
-    ps = [ctx.Process(target=_cpu_worker, args=(w, per, rows, warmup, steps, barrier, q)) for w in range(procs)]
+    ps = [ctx.Process(target=_cpu_worker, args=(w, per, rows, warmup, steps, barrier, q, use_ref, S, A, hp, threads))
+          for w in range(procs)]
     for p in ps:
         p.start()
     res = [q.get() for _ in ps]
@@ -176,24 +229,62 @@ def cpu_reference(steps, warmup, total_agents, rows=200_000, procs=None):
         p.join()
     t0, t1 = min(r[1] for r in res), max(r[2] for r in res)
     n_upd = procs * per * steps
-    desc = (f"oracle port of iql.py sample()+train() (bf16 autocast as shipped, eager), {procs} single-thread processes x "
-            f"{per} agents, {steps} steps after {warmup} warm-up, {rows}-row tables; {cores} host cores visible")
-    return n_upd / (t1 - t0), (t1 - t0) / steps * 1e3, procs, desc, procs * per
+    what = ("the unmodified reference (algorithms/offline/iql.py ReplayBuffer.sample + ImplicitQLearning.train, bf16 "
+            "autocast as shipped, eager)" if use_ref else
+            "oracle port of iql.py sample()+train() (bf16 autocast as shipped, eager; the reference was not importable)")
+    desc = (f"{what}: {procs} process(es) x {threads} thread(s) x {per} agent(s), {steps} steps after {warmup} warm-up, "
+            f"{rows}-row replay buffer per process, obs {S} / act {A}; {cores} host cores visible")
+    return {"value": n_upd / (t1 - t0), "ms_per_step": (t1 - t0) / steps * 1e3, "cores": procs * threads,
+            "kind": "reference" if use_ref else "port", "sample": desc, "agents": procs * per}
+
+
+def cpu_cfg1_sweep(rows, steps=60, warmup=10):
+    """BASELINE.json configs[0] as written: halfcheetah-shaped (17 obs, 6 act), `rows` rows, ONE seed, the reference's
+    iql.py on the CPU; torch thread counts swept, best reported (SURVEY 8d 'CPU baseline timing')."""
+    cores = len(os.sched_getaffinity(0))
+    hp1 = dict(HP, beta=3.0, iql_tau=0.7)  # configs/offline/iql/halfcheetah/medium_v2.yaml
+    table, best = [], None
+    th = 1
+    while th <= cores:
+        r = cpu_reference(steps, warmup, 1, rows, procs=1, S=17, A=6, hp=hp1, threads=th)
+        table.append({"threads": th, "updates_per_s": r["value"]})
+        if best is None or r["value"] > best["value"]:
+            best = dict(r, threads=th)
+        th *= 2
+    return {"value": best["value"], "unit": UNIT, "cores": best["threads"], "kind": best["kind"],
+            "workload": f"configs[0]: IQL offline/iql.py on synthetic halfcheetah-medium-v2-shaped data ({rows} x 17 obs, "
+                        f"6 act), batch {BATCH}, 2x{HID} MLPs, 1 seed, CPU", "thread_sweep": table}
+
+
+def common_config(args, world):
+    """The `config` object both arms print (identical for the same flags, so the two lines are comparable)."""
+    n = agents_per_gpu(args, world)
+    return {"workload": workload_name(n, args.rows), "agents_per_gpu": n, "agents_total": n * world,
+            "batch_size": BATCH, "rows": args.rows, "obs_dim": S_DIM, "act_dim": A_DIM, "hidden": HID,
+            "precision": "bf16" if args.precision == "bf16" else "fp32", "scaling_mode": args.scaling}
+
+
+def agents_per_gpu(args, world):
+    if args.scaling == "strong":
+        if args.agents_total % world:
+            raise SystemExit(f"--agents-total {args.agents_total} is not divisible by {world} GPUs")
+        return args.agents_total // world
+    return args.agents_per_gpu
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    total = args.agents_per_gpu
-    ups, ms, procs, desc, n_agents = cpu_reference(args.steps, args.warmup, total)
-    line = {"impl": "reference", "metric": METRIC, "value": ups, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(args.agents_per_gpu, args.rows), "agents_in_sample": n_agents,
-                       "batch_size": BATCH},
-            "cpu_baseline": {"value": ups, "unit": UNIT, "cores": procs, "kind": "port", "sample": desc},
-            "e2e": {"value": ups, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    r = cpu_reference(args.steps, args.warmup, agents_per_gpu(args, world), args.rows)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": common_config(args, world),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+                             "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
@@ -202,13 +293,115 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # the CUDA arm
 # ------------------------------------------------------------------------------------------------
-def build_workload(args, dev, rank):
+def time_gpu(fn, reps, dev):
+    """Average milliseconds of `fn()` over `reps` back-to-back calls, CUDA events on the current stream, after the
+    caller's warm-up; nothing but the calls sits between the two events."""
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    return e0.elapsed_time(e1) / reps
+
+
+def mlp_flops_per_row(d_in, w, depth):
+    return 2.0 * (d_in * w + (depth - 1) * w * w + w)
+
+
+def bench_relabel(args, dev, table, R, peaks):
+    """Relabel passes of BASELINE configs[1], [2], [3] on synthetic data: rows/s and roofline fractions.  Every entry is
+    timed over >= 10 (the single model: 50) repetitions of the library call with pre-packed weights and preallocated
+    outputs, CUDA events around the calls only."""
     import numpy as np
     import torch
-    from iqlpref_b200 import iql as biql
-    from iqlpref_b200.relabel import ensemble_predict, pack_members
+    from iqlpref_b200.relabel import ensemble_predict, pack_members, pt_predict
+    from iqlpref_b200.reward_models.pref_transformer import PT
     from iqlpref_b200.reward_models.q_mlp import MLP as RewardMLP, member_weights
-    N, rows = args.agents_per_gpu, args.rows
+    rows = table.shape[0]
+    d_in = S_DIM + A_DIM
+    out = {}
+    x = table[:, :d_in]  # row-strided view of the replay table: read in place, no copy
+    buf = torch.empty(rows, dtype=torch.float32, device=dev)
+
+    def entry(name, fn, reps, n_rows, S, flops_row, bytes_row, note):
+        for _ in range(3):
+            fn()
+        ms = [time_gpu(fn, reps, dev) for _ in range(3)]  # three runs: they must agree
+        sec = min(ms) * 1e-3
+        fl = n_rows * S * flops_row
+        out[name] = {"ms": min(ms), "ms_runs": ms, "reps": reps, "rows": n_rows, "members": S,
+                     "rows_per_s": n_rows / sec, "member_rows_per_s": n_rows * S / sec,
+                     "flops_per_member_row": flops_row, "tflops_fp32_equiv": fl / sec / 1e12,
+                     "tensor_frac_bf16_mma": 3.0 * fl / sec / 1e12 / peaks["tensor_burst"],
+                     "hbm_GBps": n_rows * bytes_row / sec / 1e9, "hbm_frac": n_rows * bytes_row / sec / 1e9 / peaks["hbm"],
+                     "note": note}
+
+    # configs[1]: q_mlp RewardMLP(37, 1, [128]*3, relu), random init, the whole replay table
+    torch.manual_seed(0)
+    rm = RewardMLP(d_in, 1, [128, 128, 128], "relu")
+    packed1 = pack_members([member_weights(rm)], dev)
+    fr = mlp_flops_per_row(d_in, 128, 3)
+    entry("mlp", lambda: ensemble_predict(packed1, x, "mean", device=dev, precision="split_bf16", out=buf), 50, rows, 1, fr,
+          R * 4 + 4, "single model, split-bf16 tcgen05 (3 bf16 MMAs per product): compute-bound at ~830 flop/B, so the "
+          "70 %-of-HBM target of north_star does not apply (DESIGN.md); tensor_frac is against the burst peak")
+    out["mlp_fp32"] = {"ms": min(time_gpu(lambda: ensemble_predict(packed1, x, "mean", device=dev, precision="fp32", out=buf),
+                                          3, dev) for _ in range(2))}
+    r_hat = ensemble_predict(packed1, x, "mean", device=dev, precision="split_bf16").clone()
+    # configs[3] shapes (SURVEY 8d cfg4): snapshot ensembles with CVaR
+    rng = np.random.default_rng(0)
+
+    def members(S, d, w):
+        ms = []
+        for _ in range(S):
+            m, n_in = [], d
+            for _l in range(3):
+                m += [rng.standard_normal((n_in, w)).astype(np.float32), (rng.standard_normal(w) * 0.1).astype(np.float32)]
+                n_in = w
+            ms.append(m + [rng.standard_normal((w, 1)).astype(np.float32), np.zeros(1, np.float32)])
+        return pack_members(ms, dev)
+    p10 = members(10, d_in, 128)
+    entry("ens10_cvar", lambda: ensemble_predict(p10, x, "cvar", 0.9, device=dev, out=buf), 10, rows, 10, fr, R * 4 + 4,
+          "10 MR snapshots x the whole table, CVaR alpha 0.9 (n_tail 1), selection in the reduction kernel")
+    n_pen = 5000
+    xp = torch.randn((n_pen, 69), device=dev)
+    bufp = torch.empty(n_pen, dtype=torch.float32, device=dev)
+    p981 = members(981, 69, 128)
+    entry("ens981_pen", lambda: ensemble_predict(p981, xp, "cvar", 0.95, device=dev, out=bufp), 10, n_pen, 981,
+          mlp_flops_per_row(69, 128, 3), 69 * 4 + 4, "pen-human: 981 MR snapshots RewardMLP(69,1,[128]*3) x 5000 rows, CVaR 0.95")
+    # configs[2]: preference transformer E=256, L=1, q=100 (scripts_pt/antmaze_large_diverse_pt_antmaze_eval.yaml)
+    torch.manual_seed(0)
+    pt = PT(state_dim=S_DIM, action_dim=A_DIM, max_episode_steps=1000, embd_dim=256, pref_attn_embd_dim=256, num_heads=4,
+            intermediate_dim=1024, num_layers=1, max_pos=2048, eps=0.1).to(dev).eval()
+    n_win = args.pt_windows
+    q = 100
+    obs_all = table[:, :S_DIM].contiguous()
+    act_all = table[:, S_DIM:d_in].contiguous()
+    start = np.arange(n_win, dtype=np.int32) * 7 % (rows - q)
+    seq = np.full(n_win, q, dtype=np.int32)
+    seq[::10] = 1 + np.arange(len(seq[::10])) % q  # 10 % left-padded windows
+    fn_pt = lambda: pt_predict(pt, obs_all, act_all, start, seq, q, device=dev, dedupe=False)
+    fn_pt()
+    ms = [time_gpu(fn_pt, 3, dev) for _ in range(2)]
+    sec = min(ms) * 1e-3
+    fl_min, fl_full = 55e6, 384e6  # SURVEY 8d: last-token-only minimum / full forward, per window (E=256, L=1, q=100)
+    out["pt"] = {"ms": min(ms), "ms_runs": ms, "distinct_windows": n_win, "windows_per_s": n_win / sec,
+                 "flops_per_window_counted": fl_min, "tflops": n_win * fl_min / sec / 1e12,
+                 "tensor_frac": n_win * fl_min / sec / 1e12 / peaks["tensor_burst"],
+                 "tensor_frac_full_forward_count": n_win * fl_full / sec / 1e12 / peaks["tensor_burst"],
+                 "note": "RewardPT(29, 8, E=256, heads 4, I=1024, L=1), query_length 100, every window distinct (with the "
+                         "reference's episode-step-as-row-index behaviour, SURVEY F4, a 1M-row dataset has <= 1000 distinct "
+                         "windows: its whole relabel is n_windows=1000 of these); includes the host-side window upload"}
+    out["rows_per_s"] = out["mlp"]["rows_per_s"]
+    return out, r_hat
+
+
+def build_workload(args, dev, rank, world):
+    import torch
+    from iqlpref_b200 import iql as biql
+    N, rows = agents_per_gpu(args, world), args.rows
     g = torch.Generator(device=dev)
     g.manual_seed(0)  # the dataset is the same on every rank (replicated, SURVEY 8e)
     buf = biql.ReplayBuffer(S_DIM, A_DIM, rows, device=str(dev))
@@ -220,31 +413,8 @@ def build_workload(args, dev, rank):
     sparse = (torch.rand(rows, generator=g, device=dev) < 1e-3).float()
     t[:, 2 * S_DIM + A_DIM + 1] = sparse  # terminals = goal reached
     buf._size = buf._pointer = rows
-    # q_mlp relabel of the whole dataset (configs[1]): RewardMLP(37, 1, [128]*3, relu), random init
-    torch.manual_seed(0)
-    rm = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
-    x = t[:, :S_DIM + A_DIM]
-    packed = pack_members([member_weights(rm)], dev)  # x is a row-strided view of the replay table: no copy
-    relabel = {"rows": rows, "model": "RewardMLP(37,1,[128]*3,relu)", "table_row_bytes": R * 4}
-    flops = rows * 2.0 * ((S_DIM + A_DIM) * 128 + 2 * 128 * 128 + 128)
-    for prec, reps in (("split_bf16", 5), ("fp32", 1)):
-        ensemble_predict(packed, x[:4096], "mean", device=dev, precision=prec)  # warm-up
-        ensemble_predict(packed, x, "mean", device=dev, precision=prec)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize(dev)
-        e0.record()
-        for _ in range(reps):
-            r_hat = ensemble_predict(packed, x, "mean", device=dev, precision=prec)
-        e1.record()
-        torch.cuda.synchronize(dev)
-        ms = e0.elapsed_time(e1) / reps
-        relabel[prec] = {"ms": ms, "rows_per_s": rows / (ms * 1e-3), "tflops_fp32_equiv": flops / (ms * 1e-3) / 1e12,
-                         "table_GBps": rows * R * 4 / (ms * 1e-3) / 1e9}
-    relabel["rows_per_s"] = relabel["split_bf16"]["rows_per_s"]
-    relabel["ms"] = relabel["split_bf16"]["ms"]
-    # split-bf16 issues three bf16 MMAs per product: the tensor-pipe work is 3x the fp32-equivalent flops
-    relabel["bf16_mma_tflops"] = 3.0 * relabel["split_bf16"]["tflops_fp32_equiv"]
-    r_hat = ensemble_predict(packed, x, "mean", device=dev, precision="split_bf16")
+    # q_mlp relabel of the whole dataset (configs[1]) + the other relabel passes (rank 0 reports them)
+    relabel, r_hat = bench_relabel(args, dev, t, R, load_peaks())
     # reward columns standing in for normalize_reward 0..7 (iql.py:363-401): affine maps of the relabelled reward
     r = r_hat
     span = (r.max() - r.min()).clamp_min(1e-6)
@@ -263,6 +433,37 @@ def build_workload(args, dev, rank):
     if args.precision == "bf16":
         eng.debug_option(0, int(args.fused_adam))
     return eng, buf, cols, variant, relabel
+
+
+def reference_cuda(args, dev, steps=200, warmup=20):
+    """The "same box, stock PyTorch" bar: the unmodified reference's sample() + train() on THIS GPU, one
+    agent, eager (the reference wraps its nets in torch.compile, iql.py:1523-1527; Inductor is not exercised here),
+    fused Adam and three .item() syncs per step as shipped."""
+    import torch
+    from oracle.ref_import import load_reference_iql
+    saved = sys.stdout
+    sys.stdout = sys.stderr
+    try:
+        ref = load_reference_iql()
+        buf = ref.ReplayBuffer(S_DIM, A_DIM, args.rows, str(dev))
+        buf.load_d4rl_dataset(synth_dataset(args.rows, S_DIM, A_DIM, 0))
+        tr = build_reference_agent(ref, S_DIM, A_DIM, HP, 1, str(dev))
+        for _ in range(warmup):
+            tr.train(buf.sample(BATCH))
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            tr.train(buf.sample(BATCH))
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+    finally:
+        sys.stdout = saved
+    del buf, tr
+    torch.cuda.empty_cache()
+    return {"value": steps / dt, "unit": UNIT, "agents": 1, "ms_per_step": dt / steps * 1e3,
+            "what": "unmodified reference iql.py (ReplayBuffer.sample + ImplicitQLearning.train, bf16 autocast, "
+                    f"Adam(fused=True), eager) on the same B200, 1 agent, {steps} steps after {warmup} warm-up, wall clock "
+                    "around the loop (its .item() calls synchronise every step)"}
 
 
 KERNEL_WORK = None  # filled per precision in kernel_roofline()
@@ -288,11 +489,16 @@ def kernel_roofline(prof, n_agents, peaks):
         "gemm_bwd_d1": ("tensor", f_bd1), "gemm_bwd_w0": ("tensor", f_bw0),
         "bf16_fwd": ("tensor", f_l0 + f_l1), "bf16_bwd": ("tensor", f_bw1 + f_bd1 + f_bw0),
         "bf16_bwd_data": ("tensor", f_bd1), "bf16_bwd_weight": ("tensor", f_bw1 + f_bw0),
-        "bf16_bwd_weight_adam": ("hbm", 24 * p + 8 * pq + 2 * (p + pq)),
+        "bf16_bwd_weight_adam": ("hbm", 24 * p + 8 * pq),
         "head_fwd": ("hbm", 7 * B * H * 4), "head_bwd": ("hbm", 4 * 2 * B * H * 4), "loss": ("hbm", B * row),
-        "adam_polyak": ("hbm", 24 * p + 8 * pq + 4 * p),  # p,m,v r+w, target r+w, grads read
-        "adam_polyak_shadow": ("hbm", 24 * p + 8 * pq + 2 * p + 2 * (p + pq)),  # p,m,v r+w, target r+w, bf16 grads read, bf16 images written
+        # ALGORITHMIC bytes of the optimizer = p, m, v read + written (24 B/param) and the Polyak
+        # target read + written (8 B/target param); nothing else
+        "adam_polyak": ("hbm", 24 * p + 8 * pq),
+        "adam_polyak_shadow": ("hbm", 24 * p + 8 * pq),
     }
+    # bytes this IMPLEMENTATION moves on top of the algorithm (not credited in `frac`): the gradient read (fp32, or
+    # bf16 on the tcgen05 path) and, on the tcgen05 path, the refreshed bf16 weight images
+    extra = {"adam_polyak": 4 * p, "adam_polyak_shadow": 2 * p + 2 * (p + pq), "bf16_bwd_weight_adam": 2 * (p + pq)}
     table, top = [], None
     for k in prof:
         bound, amount = work.get(k["kernel"], ("hbm", 0))
@@ -303,6 +509,9 @@ def kernel_roofline(prof, n_agents, peaks):
             ach, peak, unit = amount * n_agents / sec / 1e12 if sec > 0 else 0.0, peaks["tensor"], "TFLOP/s"
         e = {"kernel": k["kernel"], "ms_per_step": k["ms_per_step"], "bound": bound, "achieved": ach, "peak": peak,
              "unit": unit, "frac": ach / peak if peak else None}
+        if k["kernel"] in extra and sec > 0:
+            e["design_extra_bytes"] = extra[k["kernel"]] * n_agents
+            e["frac_incl_design_extra"] = (amount + extra[k["kernel"]]) * n_agents / sec / 1e9 / peak
         table.append(e)
         if top is None or e["ms_per_step"] > top["ms_per_step"]:
             top = e
@@ -310,7 +519,11 @@ def kernel_roofline(prof, n_agents, peaks):
             "frac": top["frac"], "traffic": ncu_traffic(top["kernel"]), "kernel": top["kernel"], "peak_source": peaks["source"],
             "traffic_source": "profiles/r01_bf16_ncu_full.json (dram__bytes_read.sum + dram__bytes_write.sum per launch, "
                               "64 agents)",
-            "algorithmic_per_launch": work.get(top["kernel"], ("", 0))[1] * n_agents}
+            "algorithmic_per_launch": work.get(top["kernel"], ("", 0))[1] * n_agents,
+            "algorithmic_definition": "SURVEY 8(d): 24 B/param (p, m, v read + write) + 8 B/target param (Polyak read + "
+                                      "write); gradient reads and bf16 weight-image writes are design_extra_bytes",
+            "design_extra_bytes": top.get("design_extra_bytes", 0),
+            "frac_incl_design_extra": top.get("frac_incl_design_extra")}
     return roof, table
 
 
@@ -391,12 +604,21 @@ def run_cuda(args):
     cpu_base = None
     if rank == 0 and world == 1 and not args.skip_cpu_baseline:
         t0 = time.perf_counter()
-        ups, ms, procs, desc, _ = cpu_reference(args.cpu_steps, 3, args.agents_per_gpu)
-        cpu_base = {"value": ups, "unit": UNIT, "cores": procs, "kind": "port", "sample": desc}
-        log(f"cpu_baseline: {ups:.1f} updates/s on {procs} cores ({time.perf_counter() - t0:.1f}s)")
+        r = cpu_reference(args.cpu_steps, 3, agents_per_gpu(args, world), args.rows)
+        cpu_base = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+        log(f"cpu_baseline: {r['value']:.1f} updates/s on {r['cores']} cores, kind {r['kind']} ({time.perf_counter() - t0:.1f}s)")
+        if not args.skip_cfg1:
+            t0 = time.perf_counter()
+            cpu_base["configs0"] = cpu_cfg1_sweep(args.rows)
+            log(f"cpu configs[0]: {cpu_base['configs0']['value']:.1f} updates/s with {cpu_base['configs0']['cores']} thread(s) "
+                f"({time.perf_counter() - t0:.1f}s)")
+    ref_cuda = None
+    if rank == 0 and world == 1 and not args.skip_reference_cuda and reference_usable():
+        ref_cuda = reference_cuda(args, dev)
+        log(f"reference_cuda: {ref_cuda['value']:.1f} updates/s (stock PyTorch eager, 1 agent)")
 
-    eng, buf, cols, variant, relabel = build_workload(args, dev, rank)
-    N, K, W = args.agents_per_gpu, args.steps, args.warmup
+    eng, buf, cols, variant, relabel = build_workload(args, dev, rank, world)
+    N, K, W = agents_per_gpu(args, world), args.steps, args.warmup
     stream = torch.cuda.current_stream(dev)
     for _ in range(W):
         eng.train(None)
@@ -486,12 +708,14 @@ def run_cuda(args):
         ups = world * N * K / (ms_total * 1e-3)
         per_gpu = ups / world
         line = {"metric": METRIC, "value": ups, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
                 "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
-                "config": {"workload": workload_name(N, args.rows), "agents_per_gpu": N, "batch_size": BATCH,
-                           "precision": args.precision, "sampling": "on-device Philox gather inside the timed region",
-                           "l2": f"inputs larger than L2: {N * (3 * eng.Pstride + eng.PQstride) * 4 / 1e6:.0f} MB of "
-                                 f"agent state + {args.rows * eng.R * 4 / 1e6:.0f} MB replay table per GPU vs 126 MB L2"},
+                "config": common_config(args, world),
+                "notes": {"sampling": "on-device Philox gather inside the timed region",
+                          "l2": f"inputs larger than L2: {N * (3 * eng.Pstride + eng.PQstride) * 4 / 1e6:.0f} MB of "
+                                f"agent state + {args.rows * eng.R * 4 / 1e6:.0f} MB replay table per GPU vs 126 MB L2"
+                                + ("" if N >= 32 else " (state of this few agents fits L2: the replay table is the "
+                                                      "larger-than-L2 input)")},
                 "clocks": clocks,
                 "e2e": {"value": world * N * K / (ms_e2e * 1e-3), "unit": UNIT,
                         "h2d_bytes_per_step": world * N * BATCH * eng.R * 4, "d2h_bytes_per_step": world * N * 3 * 4,
@@ -506,12 +730,15 @@ def run_cuda(args):
                                   "hbm_frac": bytes_per_update() * per_gpu / 1e9 / peaks["hbm"],
                                   "flops_per_update": flops_per_update(), "bytes_per_update": bytes_per_update()},
                 "relabel": relabel}
-        relabel["roofline"] = {"bound": "tensor", "achieved": relabel["bf16_mma_tflops"], "peak": peaks["tensor_burst"],
-                               "unit": "TFLOP/s", "frac": relabel["bf16_mma_tflops"] / peaks["tensor_burst"],
-                               "hbm_frac": relabel["split_bf16"]["table_GBps"] / peaks["hbm"],
-                               "note": "whole iqlb_relabel_mlp_p call (weight-image prep + kernel), timed alone: burst peak"}
+        relabel["roofline"] = {"bound": "tensor", "achieved": 3.0 * relabel["mlp"]["tflops_fp32_equiv"],
+                               "peak": peaks["tensor_burst"], "unit": "TFLOP/s", "frac": relabel["mlp"]["tensor_frac_bf16_mma"],
+                               "hbm_frac": relabel["mlp"]["hbm_frac"],
+                               "note": "single-model relabel, whole iqlb_relabel_mlp_p call (weight-image prep + kernel), "
+                                       "timed alone: burst peak; split-bf16 issues three bf16 MMAs per product"}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
+        if ref_cuda is not None:
+            line["reference_cuda"] = ref_cuda
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -529,6 +756,13 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("IQLB_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--cpu-steps", type=int, default=40)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-cfg1", action="store_true", help="skip the configs[0] CPU thread sweep")
+    ap.add_argument("--skip-reference-cuda", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --agents-per-gpu agents on every GPU; strong: --agents-total agents split over the GPUs "
+                         "(BASELINE.json configs[4]: 64 agents sharded across 8 GPUs)")
+    ap.add_argument("--agents-total", type=int, default=64)
+    ap.add_argument("--pt-windows", type=int, default=4096)
     ap.add_argument("--fused-adam", type=int, default=int(os.environ.get("IQLB_FUSED_ADAM", "0")),
                     help="1: Adam/Polyak inside the weight-gradient kernel (gradients never reach HBM)")
     args = ap.parse_args()

@@ -109,6 +109,26 @@ def check(rc: int, what: str = ""):
         raise IqlbError(f"{what}: iqlb error {rc}: {msg}")
 
 
+def on_device(fn):
+    """Method decorator: run with `self.device` as the current CUDA device.  The library allocates its scratch on, and
+    launches on, the CURRENT device, while the buffers and the stream it is handed belong to `self.device`; without
+    this a caller using device="cuda:1" and no prior torch.cuda.set_device would mix devices."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *a, **k):
+        import torch
+        with torch.cuda.device(self.device):
+            return fn(self, *a, **k)
+    return wrapper
+
+
+def device_ctx(device):
+    """`with device_ctx(dev):` for free functions (same purpose as `on_device`)."""
+    import torch
+    return torch.cuda.device(device)
+
+
 def ptr(t):
     """Raw device/host pointer of a torch tensor (None -> NULL)."""
     return None if t is None else C.c_void_p(t.data_ptr())

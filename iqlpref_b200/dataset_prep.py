@@ -35,8 +35,9 @@ def return_reward_range_device(rewards: torch.Tensor, terminals: torch.Tensor, m
     min_max = torch.empty(2, dtype=torch.float64, device=dev)
     trj = torch.empty(n, dtype=torch.float32, device=dev) if want_lengths else None
     lib = _lib.load()
-    _lib.check(lib.iqlb_reward_range(_lib.ptr(rewards), _lib.ptr(terminals), n, int(max_episode_steps),
-                                     _lib.ptr(min_max), _lib.ptr(trj), _lib.stream_ptr(dev)), "iqlb_reward_range")
+    with _lib.device_ctx(dev):
+        _lib.check(lib.iqlb_reward_range(_lib.ptr(rewards), _lib.ptr(terminals), n, int(max_episode_steps),
+                                         _lib.ptr(min_max), _lib.ptr(trj), _lib.stream_ptr(dev)), "iqlb_reward_range")
     return min_max, trj
 
 
@@ -62,8 +63,10 @@ def modify_reward_device(rewards: torch.Tensor, terminals: torch.Tensor, env_nam
     else:
         return rewards
     lib = _lib.load()
-    _lib.check(lib.iqlb_modify_reward(_lib.ptr(rewards), _lib.ptr(terminals), rewards.numel(), kind, int(normalize_reward),
-                                      int(max_episode_steps), _lib.stream_ptr(rewards.device)), "iqlb_modify_reward")
+    with _lib.device_ctx(rewards.device):
+        _lib.check(lib.iqlb_modify_reward(_lib.ptr(rewards), _lib.ptr(terminals), rewards.numel(), kind,
+                                          int(normalize_reward), int(max_episode_steps),
+                                          _lib.stream_ptr(rewards.device)), "iqlb_modify_reward")
     return rewards
 
 
@@ -86,8 +89,9 @@ def compute_mean_std_device(states: torch.Tensor, eps: float) -> Tuple[torch.Ten
     mean = torch.empty(dim, dtype=torch.float32, device=states.device)
     std = torch.empty(dim, dtype=torch.float32, device=states.device)
     lib = _lib.load()
-    _lib.check(lib.iqlb_state_mean_std(_lib.ptr(states), n, dim, states.stride(0), float(eps), _lib.ptr(mean),
-                                       _lib.ptr(std), _lib.stream_ptr(states.device)), "iqlb_state_mean_std")
+    with _lib.device_ctx(states.device):
+        _lib.check(lib.iqlb_state_mean_std(_lib.ptr(states), n, dim, states.stride(0), float(eps), _lib.ptr(mean),
+                                           _lib.ptr(std), _lib.stream_ptr(states.device)), "iqlb_state_mean_std")
     return mean, std
 
 
@@ -102,10 +106,11 @@ def normalize_states_device(states: torch.Tensor, mean: torch.Tensor, std: torch
     """In place (states - mean) / std on a float32 CUDA tensor [n, dim] (row-strided views allowed)."""
     n, dim = states.shape
     lib = _lib.load()
-    _lib.check(lib.iqlb_normalize_states(_lib.ptr(states), n, dim, states.stride(0) if n > 1 else dim,
-                                         _lib.ptr(mean.to(states.device, torch.float32).contiguous()),
-                                         _lib.ptr(std.to(states.device, torch.float32).contiguous()),
-                                         _lib.stream_ptr(states.device)), "iqlb_normalize_states")
+    with _lib.device_ctx(states.device):
+        _lib.check(lib.iqlb_normalize_states(_lib.ptr(states), n, dim, states.stride(0) if n > 1 else dim,
+                                             _lib.ptr(mean.to(states.device, torch.float32).contiguous()),
+                                             _lib.ptr(std.to(states.device, torch.float32).contiguous()),
+                                             _lib.stream_ptr(states.device)), "iqlb_normalize_states")
     return states
 
 

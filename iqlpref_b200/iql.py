@@ -118,15 +118,16 @@ def soft_update(target: nn.Module, source: nn.Module, tau: float):
     for tp, sp in zip(target.parameters(), source.parameters()):
         if not tp.is_cuda:
             raise RuntimeError("soft_update: parameters must live on a CUDA device (no CPU path)")
-        if tp.data.is_contiguous() and sp.data.is_contiguous() and tp.data_ptr() % 16 == 0 and sp.data_ptr() % 16 == 0:
-            _lib.check(lib.iqlb_polyak(_lib.ptr(tp.data), _lib.ptr(sp.data), tp.numel(), float(tau),
-                                       _lib.stream_ptr(tp.device)), "iqlb_polyak")
-        else:  # unaligned view of a packed buffer: stage through an aligned copy
-            t = tp.data.contiguous().clone()
-            s = sp.data.contiguous().clone()
-            _lib.check(lib.iqlb_polyak(_lib.ptr(t), _lib.ptr(s), t.numel(), float(tau), _lib.stream_ptr(tp.device)),
-                       "iqlb_polyak")
-            tp.data.copy_(t)
+        with _lib.device_ctx(tp.device):
+            if tp.data.is_contiguous() and sp.data.is_contiguous() and tp.data_ptr() % 16 == 0 and sp.data_ptr() % 16 == 0:
+                _lib.check(lib.iqlb_polyak(_lib.ptr(tp.data), _lib.ptr(sp.data), tp.numel(), float(tau),
+                                           _lib.stream_ptr(tp.device)), "iqlb_polyak")
+            else:  # unaligned view of a packed buffer: stage through an aligned copy
+                t = tp.data.contiguous().clone()
+                s = sp.data.contiguous().clone()
+                _lib.check(lib.iqlb_polyak(_lib.ptr(t), _lib.ptr(s), t.numel(), float(tau), _lib.stream_ptr(tp.device)),
+                           "iqlb_polyak")
+                tp.data.copy_(t)
 
 
 def asymmetric_l2_loss(u: torch.Tensor, tau: float) -> torch.Tensor:
@@ -209,9 +210,11 @@ class ReplayBuffer:
         out = torch.empty((batch_size, self._stride), dtype=torch.float32, device=self._device)
         idx = torch.empty((1, batch_size), dtype=torch.int64, device=self._device) if return_indices else None
         lib = _lib.load()
-        _lib.check(lib.iqlb_replay_sample(_lib.ptr(self._table), n, self._stride, 2 * self._state_dim + self._action_dim,
-                                          None, None, _lib.ptr(rng), 1, batch_size, _lib.ptr(idx), _lib.ptr(out),
-                                          _lib.stream_ptr(self._device)), "iqlb_replay_sample")
+        with _lib.device_ctx(self._device):
+            _lib.check(lib.iqlb_replay_sample(_lib.ptr(self._table), n, self._stride,
+                                              2 * self._state_dim + self._action_dim, None, None, _lib.ptr(rng), 1,
+                                              batch_size, _lib.ptr(idx), _lib.ptr(out), _lib.stream_ptr(self._device)),
+                       "iqlb_replay_sample")
         gen.set_offset(offset + philox_offset_increment(batch_size, n, self._device))
         return (out, idx[0]) if return_indices else out
 
@@ -401,20 +404,26 @@ class BatchedIQL:
         desc = _lib.AgentsDesc(n_agents, state_dim, action_dim, hidden_dim, batch_size, int(self.deterministic),
                                self.R, self.precision)
         handle = C.c_void_p()
-        _lib.check(self.lib.iqlb_agents_create(C.byref(desc), _lib.ptr(self.params), _lib.ptr(self.exp_avg),
-                                               _lib.ptr(self.exp_avg_sq), _lib.ptr(self.target), _lib.ptr(self.hparams),
-                                               _lib.ptr(self.it), _lib.ptr(self.actor_lr), _lib.ptr(self.rng),
-                                               _lib.ptr(self.losses), _lib.ptr(self.loss_sum), C.byref(handle)),
-                   "iqlb_agents_create")
+        with _lib.device_ctx(self.device):  # the library allocates its scratch on the current device
+            _lib.check(self.lib.iqlb_agents_create(C.byref(desc), _lib.ptr(self.params), _lib.ptr(self.exp_avg),
+                                                   _lib.ptr(self.exp_avg_sq), _lib.ptr(self.target), _lib.ptr(self.hparams),
+                                                   _lib.ptr(self.it), _lib.ptr(self.actor_lr), _lib.ptr(self.rng),
+                                                   _lib.ptr(self.losses), _lib.ptr(self.loss_sum), C.byref(handle)),
+                       "iqlb_agents_create")
         self._h = handle
         self._replay = None
         self._layout = self._make_layout()
         self.actor_dropout = float(actor_dropout or 0.0)
+        # the reference's MLP inserts nn.Dropout after every hidden ReLU whenever `dropout is not None` (iql.py:436-437),
+        # which moves the actor's Linear layers to net.net.0 / 3 / 6 in its state_dict (adopt() re-derives this from
+        # the module it is given)
+        self._actor_lin_idx = (0, 3, 6) if actor_dropout is not None else (0, 2, 4)
         if self.actor_dropout > 0.0:
             if self.precision != 0:
                 raise NotImplementedError("actor_dropout runs on precision='fp32' (the tcgen05 path has no dropout yet)")
-            _lib.check(self.lib.iqlb_agents_set_actor_dropout(self._h, C.c_float(self.actor_dropout)),
-                       "iqlb_agents_set_actor_dropout")
+            with _lib.device_ctx(self.device):
+                _lib.check(self.lib.iqlb_agents_set_actor_dropout(self._h, C.c_float(self.actor_dropout)),
+                           "iqlb_agents_set_actor_dropout")
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -465,6 +474,9 @@ class BatchedIQL:
             if isinstance(m, nn.Dropout) and m.p > 0 and abs(m.p - self.actor_dropout) > 1e-12:
                 raise ValueError(f"the actor uses Dropout({m.p}) but the engine was built with actor_dropout="
                                  f"{self.actor_dropout}: pass actor_dropout={m.p} (precision='fp32')")
+        lin_idx = tuple(i for i, m in enumerate(actor.net.net) if isinstance(m, nn.Linear))
+        if len(lin_idx) == 3:
+            self._actor_lin_idx = lin_idx  # state_dict names of the actor's Linear layers (0/2/4, or 0/3/6 with Dropout)
         with torch.no_grad():
             for key, prm in self._module_tensors(qf, vf, actor).items():
                 dst = self.view(self.params, agent, key)
@@ -476,11 +488,13 @@ class BatchedIQL:
             self.target[agent, :self.PQ] = self.params[agent, :self.PQ]
         self._sync_shadow()
 
+    @_lib.on_device
     def _sync_shadow(self):
         """params/target were written from Python: rebuild the bf16 operand images (precision bf16)."""
         _lib.check(self.lib.iqlb_agents_refresh(self._h, _lib.stream_ptr(self.device)), "iqlb_agents_refresh")
 
     # ---- stepping ---------------------------------------------------------------------------------
+    @_lib.on_device
     def attach_replay(self, buffer: ReplayBuffer, reward_cols: Optional[torch.Tensor] = None,
                       reward_variant: Optional[torch.Tensor] = None, record_indices: bool = False):
         if buffer._stride != self.R:
@@ -493,6 +507,7 @@ class BatchedIQL:
                                                    _lib.ptr(reward_cols), _lib.ptr(reward_variant),
                                                    _lib.ptr(self.last_indices)), "iqlb_agents_set_replay")
 
+    @_lib.on_device
     def train(self, batch_rows: Optional[torch.Tensor] = None):
         """Enqueue one update of every agent.  `batch_rows`: packed [N, B, row_stride] device rows,
         or None to sample on device.  Losses land in `self.losses` ([N,3]) without a host sync."""
@@ -503,6 +518,7 @@ class BatchedIQL:
         _lib.check(self.lib.iqlb_agents_step(self._h, _lib.ptr(batch_rows), _lib.stream_ptr(self.device)),
                    "iqlb_agents_step")
 
+    @_lib.on_device
     @torch.no_grad()
     def act(self, states, max_action: float = 1.0) -> torch.Tensor:
         """Deterministic actions of every agent's policy in eval mode (GaussianPolicy.act / DeterministicPolicy.act,
@@ -522,11 +538,13 @@ class BatchedIQL:
                                                 _lib.stream_ptr(self.device)), "iqlb_agents_act")
         return out
 
+    @_lib.on_device
     def train_host(self, host_rows: torch.Tensor, host_losses: torch.Tensor):
         """Step with the batch in pinned host memory; returns after the losses are on the host."""
         _lib.check(self.lib.iqlb_agents_step_host(self._h, _lib.ptr(host_rows), _lib.ptr(host_losses),
                                                   _lib.stream_ptr(self.device)), "iqlb_agents_step_host")
 
+    @_lib.on_device
     def train_host_pipelined(self, host_rows: Optional[torch.Tensor], host_losses_prev: torch.Tensor):
         """Pipelined host feed: enqueue the update on `host_rows` (pinned; None = flush) and return the losses of
         the PREVIOUS update in `host_losses_prev`; the H2D copy of the next call overlaps this update."""
@@ -534,16 +552,26 @@ class BatchedIQL:
                                                             _lib.ptr(host_losses_prev), _lib.stream_ptr(self.device)),
                    "iqlb_agents_step_host_pipelined")
 
+    def sync(self):
+        """Make everything the engine has enqueued visible to the caller's stream (see `iqlb_agents_sync`)."""
+        fn = getattr(self.lib, "iqlb_agents_sync", None)
+        if fn is not None:
+            with _lib.device_ctx(self.device):
+                _lib.check(fn(self._h, _lib.stream_ptr(self.device)), "iqlb_agents_sync")
+
     def launches_per_step(self, sampled: bool) -> int:
         return int(self.lib.iqlb_agents_launches_per_step(self._h, int(sampled)))
 
     # ---- per-kernel timing (CUDA events on the launching stream; used by bench.py) ----------------------
+    @_lib.on_device
     def profile(self, enable: bool):
         _lib.check(self.lib.iqlb_agents_profile(self._h, int(bool(enable))), "iqlb_agents_profile")
 
+    @_lib.on_device
     def profile_collect(self):
         _lib.check(self.lib.iqlb_agents_profile_collect(self._h), "iqlb_agents_profile_collect")
 
+    @_lib.on_device
     def profile_read(self) -> List[Dict[str, Any]]:
         """[{"kernel": name, "ms_per_step": t}] for every launch of one step, in launch order."""
         out, i = [], 0
@@ -553,9 +581,11 @@ class BatchedIQL:
             i += 1
         return out
 
+    @_lib.on_device
     def debug_option(self, option: int, value: int):
         _lib.check(self.lib.iqlb_agents_debug_option(self._h, option, value), "iqlb_agents_debug_option")
 
+    @_lib.on_device
     def debug_tensor(self, which: int) -> torch.Tensor:
         nbytes = C.c_int64()
         _lib.check(self.lib.iqlb_agents_debug_copy(self._h, which, None, C.byref(nbytes), None), "debug")
@@ -572,8 +602,9 @@ class BatchedIQL:
         nets = {"qf": (("q1", "q1.net"), ("q2", "q2.net")), "vf": (("v", "v.net"),), "actor": (("actor", "net.net"),)}[part]
         out = [("log_std", "log_std")] if part == "actor" and not self.deterministic else []
         for net, prefix in nets:
+            idx = self._actor_lin_idx if net == "actor" else (0, 2, 4)
             for i in range(3):
-                out += [(f"{net}.w{i}", f"{prefix}.{2 * i}.weight"), (f"{net}.b{i}", f"{prefix}.{2 * i}.bias")]
+                out += [(f"{net}.w{i}", f"{prefix}.{idx[i]}.weight"), (f"{net}.b{i}", f"{prefix}.{idx[i]}.bias")]
         return out
 
     def _optimizer_state_dict(self, agent: int, part: str, lr: float, step: int, fused: Optional[bool]) -> Dict[str, Any]:
@@ -623,6 +654,14 @@ class BatchedIQL:
         mods = {}
         for part, _ in parts:  # validate everything before the first write
             mods[part] = mod = {_strip_compile_prefix_key(k): v for k, v in state_dict[part].items()}
+            if part == "actor":
+                # nn.Dropout modules have no parameters but shift the Sequential indices: renumber the checkpoint's
+                # three Linear layers (sorted by index) onto this engine's naming
+                found = sorted({int(k.split(".")[2]) for k in mod if k.startswith("net.net.") and k.endswith(".weight")})
+                if len(found) == 3 and tuple(found) != tuple(self._actor_lin_idx):
+                    ren = {f"net.net.{a}.": f"net.net.{b}." for a, b in zip(found, self._actor_lin_idx)}
+                    mods[part] = mod = {next((ren[p] + k[len(p):] for p in ren if k.startswith(p)), k): v
+                                        for k, v in mod.items()}
             missing = [name for _, name in self.checkpoint_keys(part) if name not in mod]
             if missing:
                 raise KeyError(f"checkpoint['{part}'] lacks {missing}")
@@ -678,6 +717,49 @@ class BatchedIQL:
         return d
 
 
+class _ActorLRSchedule:
+    """`ImplicitQLearning.actor_lr_schedule` (iql.py:571: `CosineAnnealingLR(actor_optimizer, max_steps)`).  The
+    schedule itself advances inside the step kernel (recursive form, torch lr_scheduler.py:1449-1455, one `.step()`
+    per `train()` like iql.py:637); this object exposes the scheduler's read / checkpoint surface over the engine's
+    `actor_lr[agent]` and `it[agent]`: `get_last_lr()`, `last_epoch`, `T_max`, `eta_min`, `base_lrs`, `state_dict()`,
+    `load_state_dict()`.  The actor optimizer's `param_groups[0]["lr"]` is kept in step with it."""
+
+    def __init__(self, trainer: "ImplicitQLearning", agent: int = 0):
+        self._tr, self._agent = trainer, agent
+        self.eta_min = 0.0
+
+    @property
+    def T_max(self) -> int:
+        return self._tr._max_steps
+
+    @property
+    def base_lrs(self) -> List[float]:
+        return [float(self._tr._hp["actor_lr"])]
+
+    @property
+    def last_epoch(self) -> int:
+        return int(self._tr._engine.it[self._agent].item())
+
+    def get_last_lr(self) -> List[float]:
+        return [float(self._tr._engine.actor_lr[self._agent].item())]
+
+    def step(self):
+        raise RuntimeError("the cosine schedule is advanced by train() inside the fused step (iql.py:637); "
+                           "stepping it separately would advance it twice")
+
+    def state_dict(self) -> Dict[str, Any]:
+        it = self.last_epoch
+        return {"T_max": self.T_max, "eta_min": 0.0, "base_lrs": self.base_lrs, "last_epoch": it,
+                "_step_count": it + 1, "_is_initial": False, "_get_lr_called_within_step": False,
+                "_last_lr": self.get_last_lr()}
+
+    def load_state_dict(self, sd: Dict[str, Any]):
+        eng = self._tr._engine
+        eng.sync()
+        eng.actor_lr[self._agent] = float(sd["_last_lr"][0])
+        self._tr.actor_optimizer.param_groups[0]["lr"] = float(sd["_last_lr"][0])
+
+
 class ImplicitQLearning:
     """Drop-in for the reference trainer (iql.py:546-688), one agent on the batched engine."""
 
@@ -706,6 +788,7 @@ class ImplicitQLearning:
         self._engine: Optional[BatchedIQL] = None
         self._batch_size = None
         self.q_target = copy.deepcopy(self.qf).requires_grad_(False).to(device)
+        self.actor_lr_schedule = _ActorLRSchedule(self)  # iql.py:571
         self.total_it = 0
         self._build(batch_size)
 
@@ -780,9 +863,7 @@ class ImplicitQLearning:
             "v_optimizer": self._opt_state(self.v_optimizer, self._keys("vf"), self._hp["vf_lr"]),
             "actor": self.actor.state_dict(),
             "actor_optimizer": self._opt_state(self.actor_optimizer, self._keys("actor"), lr_a),
-            "actor_lr_schedule": {"T_max": self._max_steps, "eta_min": 0.0, "base_lrs": [self._hp["actor_lr"]],
-                                  "last_epoch": it, "_step_count": it + 1, "_is_initial": False,
-                                  "_get_lr_called_within_step": False, "_last_lr": [lr_a]},
+            "actor_lr_schedule": self.actor_lr_schedule.state_dict(),
             "total_it": self.total_it,
         }
 

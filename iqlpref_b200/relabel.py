@@ -88,7 +88,7 @@ def pack_members(members: Sequence[Sequence[Any]], device="cuda") -> PackedMembe
 
 def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
                      activation: str = "relu", device="cuda", return_preds: bool = False,
-                     return_selection: bool = False, precision: str = "auto"):
+                     return_selection: bool = False, precision: str = "auto", out: Optional[torch.Tensor] = None):
     """Evaluate S reward MLPs on X [n, d_in] and reduce over members.
 
     members: S parameter lists [W0, b0, ..., Wout, bout] (numpy or torch; W stored (n_in, n_out) as
@@ -96,6 +96,7 @@ def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
     "cvar" (mean of the worst floor((1-alpha)*S) members, at least one).  precision: "fp32" (FFMA GEMMs),
     "split_bf16" (tcgen05, x_hi*W_hi + x_lo*W_hi + x_hi*W_lo; d_in <= 128, hidden [64|128] x <= 3) or "auto"
     (tensor cores where the shape allows).  X may be a row-strided view (stride(1) == 1) of a wider table.
+    `out`: optional preallocated float32 CUDA tensor [n] to write into (repeated relabels without allocation).
     Returns a float32 CUDA tensor [n] (plus `preds` [S, n] and/or the uint8 tail-membership mask [S, n])."""
     dev = _cuda_device(device)
     if precision not in RELABEL_PRECISIONS:
@@ -116,7 +117,10 @@ def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
         X = X.contiguous()
     n = X.shape[0]
     n_tail = S if reduce == "mean" else cvar_n_tail(alpha, S)
-    out = torch.empty(n, dtype=torch.float32, device=dev)
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+    elif tuple(out.shape) != (n,) or out.dtype != torch.float32 or out.device != X.device or not out.is_contiguous():
+        raise ValueError(f"out must be a contiguous float32 tensor [{n}] on {X.device}")
     if n == 0:  # nothing to launch (an empty tensor has no device pointer)
         res = [out] + ([torch.empty((S, 0), dtype=torch.float32, device=dev)] if return_preds else []) + \
               ([torch.empty((S, 0), dtype=torch.uint8, device=dev)] if return_selection else [])
@@ -126,10 +130,11 @@ def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
     w_arr = (C.c_int32 * len(widths))(*widths)
     lib = _lib.load()
     ldx = X.stride(0) if n > 1 else d_in
-    _lib.check(lib.iqlb_relabel_mlp_p(_lib.ptr(X), n, ldx, d_in, _lib.ptr(weights), S, w_arr, len(widths),
-                                      _lib.ACTIVATIONS[activation], n_tail, RELABEL_PRECISIONS[precision],
-                                      _lib.ptr(out), _lib.ptr(preds), _lib.ptr(sel), _lib.stream_ptr(dev)),
-               "iqlb_relabel_mlp_p")
+    with _lib.device_ctx(dev):
+        _lib.check(lib.iqlb_relabel_mlp_p(_lib.ptr(X), n, ldx, d_in, _lib.ptr(weights), S, w_arr, len(widths),
+                                          _lib.ACTIVATIONS[activation], n_tail, RELABEL_PRECISIONS[precision],
+                                          _lib.ptr(out), _lib.ptr(preds), _lib.ptr(sel), _lib.stream_ptr(dev)),
+                   "iqlb_relabel_mlp_p")
     res = [out]
     if return_preds:
         res.append(preds)
@@ -408,9 +413,10 @@ def pt_predict(r_model, obs_all: np.ndarray, act_all: np.ndarray, win_start: np.
         raise ValueError("a window reaches past the end of the dataset")
     out = torch.empty(n, dtype=torch.float32, device=dev)
     lib = _lib.load()
-    _lib.check(lib.iqlb_relabel_pt(C.byref(desc), _lib.ptr(weights), _lib.ptr(obs), _lib.ptr(act), obs.shape[0],
-                                   _lib.ptr(ws), _lib.ptr(sl), n, _lib.ptr(out), _lib.stream_ptr(dev)),
-               "iqlb_relabel_pt")
+    with _lib.device_ctx(dev):
+        _lib.check(lib.iqlb_relabel_pt(C.byref(desc), _lib.ptr(weights), _lib.ptr(obs), _lib.ptr(act), obs.shape[0],
+                                       _lib.ptr(ws), _lib.ptr(sl), n, _lib.ptr(out), _lib.stream_ptr(dev)),
+                   "iqlb_relabel_pt")
     if inverse is not None:
         out = out[torch.as_tensor(inverse.reshape(-1), dtype=torch.int64, device=dev)]
     return out

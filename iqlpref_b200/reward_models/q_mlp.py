@@ -66,8 +66,14 @@ class Q_MLP(MLP):
 
 def member_weights(model) -> List[torch.Tensor]:
     """[W0, b0, ..., Wout, bout] of a reward MLP (ours or the reference's optbnn MLP)."""
+    # the kernels evaluate act(X @ (W / sqrt(n_in)) + b) with no normalisation layer (layers/linear.py:43-47,
+    # mlp.py:73-92 with norm_layer=None): a reference MLP built any other way would be relabelled with wrong rewards
+    if getattr(model, "norm_layer", None) is not None:
+        raise NotImplementedError("reward MLPs with a norm_layer are not supported by the relabel kernels")
     out = []
     for lin in list(model.layers) + [model.output_layer]:
+        if getattr(lin, "scaled_variance", True) is False:
+            raise NotImplementedError("reward MLPs with scaled_variance=False are not supported by the relabel kernels")
         out += [lin.W.detach(), lin.b.detach()]
     if out[-2].shape[1] != 1:
         raise ValueError("reward MLP must have output_dim == 1")

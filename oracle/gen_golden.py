@@ -43,12 +43,14 @@ def flat_modules(qf, vf, actor):
     d = {}
     for name, mod in (("qf", qf), ("vf", vf), ("actor", actor)):
         for k, v in mod.state_dict().items():
-            d[f"{name}.{k}"] = v.detach().numpy().copy()
+            d[f"{name}.{k}"] = v.detach().cpu().numpy().copy()
     return d
 
 
-def run_reference_steps(ref, S, A, H, B, K, n_rows, seed, mode, deterministic, hp):
-    """Build reference nets exactly like iql.py:1467-1491 and run K steps on fixed indices."""
+def run_reference_steps(ref, S, A, H, B, K, n_rows, seed, mode, deterministic, hp, device="cpu"):
+    """Build reference nets exactly like iql.py:1467-1491 and run K steps on fixed indices.  `device="cuda"`
+    (scripts/gen_cuda_golden.py, on the GPU box) follows the reference's CUDA set-up: modules moved to the device
+    after their CPU initialisation, `Adam(fused=True)` (iql.py:1470-1491)."""
     rng = np.random.default_rng(seed + 1000)
     table = {
         "obs": rng.standard_normal((n_rows, S)).astype(np.float32),
@@ -63,17 +65,18 @@ def run_reference_steps(ref, S, A, H, B, K, n_rows, seed, mode, deterministic, h
     vf = ref.ValueFunction(S, H)
     actor = (ref.DeterministicPolicy if deterministic else ref.GaussianPolicy)(S, A, 1.0, H)
     init = flat_modules(qf, vf, actor)
-    v_opt = torch.optim.Adam(vf.parameters(), lr=hp["vf_lr"])
-    q_opt = torch.optim.Adam(qf.parameters(), lr=hp["qf_lr"])
-    a_opt = torch.optim.Adam(actor.parameters(), lr=hp["actor_lr"])
+    qf, vf, actor = qf.to(device), vf.to(device), actor.to(device)
+    kw = {"fused": True} if str(device).startswith("cuda") else {}
+    v_opt = torch.optim.Adam(vf.parameters(), lr=hp["vf_lr"], **kw)
+    q_opt = torch.optim.Adam(qf.parameters(), lr=hp["qf_lr"], **kw)
+    a_opt = torch.optim.Adam(actor.parameters(), lr=hp["actor_lr"], **kw)
     tr = ref.ImplicitQLearning(1.0, actor, a_opt, qf, q_opt, vf, v_opt, iql_tau=hp["iql_tau"], beta=hp["beta"],
-                               max_steps=hp["max_steps"], discount=hp["discount"], tau=hp["tau"], device="cpu")
+                               max_steps=hp["max_steps"], discount=hp["discount"], tau=hp["tau"], device=str(device))
     losses = np.zeros((K, 3), dtype=np.float64)
+    dtab = {k: torch.from_numpy(v).to(device) for k, v in table.items()}
     for k in range(K):
-        i = torch.from_numpy(idx[k])
-        batch = [torch.from_numpy(table["obs"])[i], torch.from_numpy(table["act"])[i],
-                 torch.from_numpy(table["rew"])[i, None], torch.from_numpy(table["next_obs"])[i],
-                 torch.from_numpy(table["done"])[i, None]]
+        i = torch.from_numpy(idx[k]).to(device)
+        batch = [dtab["obs"][i], dtab["act"][i], dtab["rew"][i, None], dtab["next_obs"][i], dtab["done"][i, None]]
         if mode == "autocast":
             ld = tr.train(batch)  # as shipped: bf16 autocast, iql.py:650
         else:  # fp32 statement of the same step (algorithms/minari/iql.py:466-488)
@@ -88,7 +91,7 @@ def run_reference_steps(ref, S, A, H, B, K, n_rows, seed, mode, deterministic, h
         losses[k] = (ld["value_loss"], ld["q_loss"], ld["actor_loss"])
     final = flat_modules(qf, vf, actor)
     for k_, v_ in tr.q_target.state_dict().items():
-        final[f"q_target.{k_}"] = v_.detach().numpy().copy()
+        final[f"q_target.{k_}"] = v_.detach().cpu().numpy().copy()
     lr_final = a_opt.param_groups[0]["lr"]
     return table, idx, init, final, losses, lr_final
 

@@ -4,6 +4,8 @@ TEST INFRASTRUCTURE.  Run here (needs /root/reference):  python -m oracle.gen_go
 
   tests/golden/iql_small_ckpt.pt          what the reference's training loop writes as checkpoint_{t}.pt
                                           (iql.py:1557-1561 -> ImplicitQLearning.state_dict :664-674) after 4 updates
+  tests/golden/iql_small_ckpt_dropout.pt  the same file for an actor built with actor_dropout=0.1 (Linear layers at
+                                          net.net.0 / 3 / 6), after 2 updates
   tests/golden/iql_small_ckpt_resume.npz  the replay rows / indices of those updates, and what the reference does
                                           when a FRESH trainer loads that file (iql.py:1519-1521, :676-688) and
                                           runs 3 more updates: losses, parameters, target, Adam moments, actor lr
@@ -26,10 +28,10 @@ S, A, H, B, K1, K2, N_ROWS = 17, 6, 64, 64, 4, 3, 300
 HP = dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.7, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4, max_steps=50)
 
 
-def make_trainer(ref, seed):
+def make_trainer(ref, seed, dropout=None):
     """Networks and optimizers as iql.py:1467-1491 builds them (non-fused Adam: CPU)."""
     torch.manual_seed(seed)
-    qf, vf, actor = ref.TwinQ(S, A, H), ref.ValueFunction(S, H), ref.GaussianPolicy(S, A, 1.0, H)
+    qf, vf, actor = ref.TwinQ(S, A, H), ref.ValueFunction(S, H), ref.GaussianPolicy(S, A, 1.0, H, dropout=dropout)
     v_opt = torch.optim.Adam(vf.parameters(), lr=HP["vf_lr"])
     q_opt = torch.optim.Adam(qf.parameters(), lr=HP["qf_lr"])
     a_opt = torch.optim.Adam(actor.parameters(), lr=HP["actor_lr"])
@@ -88,7 +90,13 @@ def main():
              lr_final=np.array(sd2["actor_optimizer"]["param_groups"][0]["lr"]), total_it=np.array(sd2["total_it"]),
              sched_last_epoch=np.array(sd2["actor_lr_schedule"]["last_epoch"]),
              **{f"init.{k}": v for k, v in init.items()}, **{f"final.{k}": v for k, v in final.items()})
-    for f in ("iql_small_ckpt.pt", "iql_small_ckpt_resume.npz"):
+    # an actor with nn.Dropout (pen / door configs, actor_dropout: 0.1): its Linear layers sit at net.net.0 / 3 / 6
+    # (iql.py:436-437).  Two updates (the masks come from torch's CPU generator: only the FORMAT is pinned here).
+    tr3 = make_trainer(ref, seed=5, dropout=0.1)
+    for k in range(2):
+        step_fp32(tr3, table, idx[k])
+    torch.save(tr3.state_dict(), os.path.join(OUT, "iql_small_ckpt_dropout.pt"))
+    for f in ("iql_small_ckpt.pt", "iql_small_ckpt_resume.npz", "iql_small_ckpt_dropout.pt"):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 
 

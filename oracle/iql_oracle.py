@@ -18,8 +18,9 @@ the same step, and the 1e-3 parity target) and `autocast` (bf16 autocast as ship
 Parity pinning: the reference ships NO tests or golden vectors for this path
 (SURVEY.md §4).  This oracle is pinned against outputs of the reference itself, generated
 in the authoring container by `oracle/gen_golden.py` and committed under `tests/golden/`
-(`tests/test_oracle_golden.py`), and - when /root/reference is present - directly against
-the imported reference (`tests/test_oracle_vs_reference.py`).
+(`tests/test_oracle_golden.py`: per-step losses and final parameters of both modes, small and
+full-size nets), and - where the reference can be imported (`/root/reference`, or the
+`baseline/_ref` copy) - directly against it on fresh inputs (`tests/test_oracle_vs_reference.py`).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / `--impl reference` leg
 may import this module.

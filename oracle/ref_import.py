@@ -1,9 +1,11 @@
 """Import the UNMODIFIED reference (`/root/reference`) in the authoring container.
 
-TEST INFRASTRUCTURE ONLY.  Used by `oracle/gen_golden.py` (fixture generation) and by
-CPU tests that pin the oracle restatement against the real reference when
-`/root/reference` exists.  Nothing on the product path, and nothing that runs on the
-GPU box, may import this module (the reference does not travel).
+TEST / BENCH INFRASTRUCTURE ONLY.  Used by `oracle/gen_golden.py` (fixture generation), by tests
+that pin the oracle restatement and the CUDA path against the real reference, and by
+`bench.py --impl reference` / `reference_cuda`.  Nothing on the product path may import this
+module.  On the GPU box `/root/reference` does not exist: the copy of the hot-path files under
+`baseline/_ref/` (oracle/make_ref.py; git-ignored, shipped) is used when present, and every
+caller falls back to the committed fixtures / the oracle port when it is not.
 
 The reference imports third-party modules that are absent here (d4rl, gym, pyrallis,
 h5py, matplotlib, prettytable, seaborn).  None of them is touched by the hot path, so
@@ -15,7 +17,19 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("IQLPREF_REFERENCE_ROOT", "/root/reference")
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _find_root() -> str:
+    """`/root/reference` in the authoring container; on the GPU box the git-ignored copy of the hot-path files that
+    `oracle/make_ref.py` placed under `baseline/_ref/` (it ships with the snapshot, the reference itself does not)."""
+    for root in (os.environ.get("IQLPREF_REFERENCE_ROOT"), "/root/reference", os.path.join(_REPO, "baseline", "_ref")):
+        if root and os.path.isfile(os.path.join(root, "algorithms/offline/iql.py")):
+            return root
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def reference_available() -> bool:

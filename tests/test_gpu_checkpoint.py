@@ -189,3 +189,85 @@ def test_per_agent_files_round_trip(tmp_path, precision):
     bad["vf"].pop("v.net.2.bias")
     with pytest.raises(KeyError):
         second.load_agent_state_dict(0, bad)
+
+
+def test_actor_with_dropout_keeps_the_reference_key_names(golden_dir, tmp_path):
+    """The reference's MLP inserts nn.Dropout after every hidden ReLU when `dropout is not None` (iql.py:436-437), so the
+    actor's Linear layers are net.net.0 / 3 / 6 in its state_dict (pen / door configs, actor_dropout: 0.1).
+    `tests/golden/iql_small_ckpt_dropout.pt` was written by the unmodified reference with such an actor."""
+    from iqlpref_b200 import iql as biql
+    sd = torch.load(os.path.join(golden_dir, "iql_small_ckpt_dropout.pt"), map_location="cpu", weights_only=False)
+    assert list(sd["actor"]) == ["log_std"] + [f"net.net.{i}.{p}" for i in (0, 3, 6) for p in ("weight", "bias")]
+    hp = dict(discount=0.99, tau=0.005, beta=3.0, iql_tau=0.7, vf_lr=3e-4, qf_lr=3e-4, actor_lr=3e-4, max_steps=50)
+    eng = biql.BatchedIQL(S, A, 2, hidden_dim=H, batch_size=B, hparams=[hp, hp], actor_dropout=0.1)
+    assert eng.load_agent_state_dict(1, sd) == 2
+    e = eng.export(1)
+    np.testing.assert_array_equal(e["actor.w1"], sd["actor"]["net.net.3.weight"].numpy())
+    np.testing.assert_array_equal(e["actor.b2"], sd["actor"]["net.net.6.bias"].numpy())
+    np.testing.assert_array_equal(eng.view(eng.exp_avg, 1, "actor.w2").cpu().numpy(),
+                                  sd["actor_optimizer"]["state"][5]["exp_avg"].numpy())  # log_std, w0, b0, w1, b1, w2
+    out = eng.agent_state_dict(1, fused=None)
+    assert list(out["actor"]) == list(sd["actor"])  # names and order as the reference writes them
+    for k, v in sd["actor"].items():
+        assert torch.equal(out["actor"][k].cpu(), v)
+    for i, st in sd["actor_optimizer"]["state"].items():
+        assert torch.equal(out["actor_optimizer"]["state"][i]["exp_avg_sq"].cpu(), st["exp_avg_sq"])
+    # save -> load round trip of the engine's own files, and an engine WITHOUT dropout modules reads the same file
+    # (nn.Dropout has no parameters: only the numbering differs)
+    paths = [str(tmp_path / f"a{a}.pt") for a in range(2)]
+    eng.save_checkpoints(paths, total_it=2)
+    assert list(torch.load(paths[1], weights_only=False)["actor"]) == list(sd["actor"])
+    eng2 = biql.BatchedIQL(S, A, 2, hidden_dim=H, batch_size=B, hparams=[hp, hp], actor_dropout=0.1)
+    eng2.load_checkpoints(paths)
+    assert torch.equal(eng2.params[1], eng.params[1]) and torch.equal(eng2.exp_avg[1], eng.exp_avg[1])
+    plain = biql.BatchedIQL(S, A, 1, hidden_dim=H, batch_size=B, hparams=[hp])
+    plain.load_agent_state_dict(0, sd)
+    assert torch.equal(plain.params[0], eng.params[1])
+    assert list(plain.agent_state_dict(0)["actor"])[1] == "net.net.0.weight" and "net.net.2.weight" in plain.agent_state_dict(0)["actor"]
+    # the drop-in trainer around a reference-shaped actor with Dropout: load, state_dict, same names
+    torch.manual_seed(0)
+    qf, vf = biql.TwinQ(S, A, H).cuda(), biql.ValueFunction(S, H).cuda()
+    actor = biql.GaussianPolicy(S, A, 1.0, H, dropout=0.1).cuda()
+    mk = lambda m, lr: torch.optim.Adam(m.parameters(), lr=lr)
+    tr = biql.ImplicitQLearning(1.0, actor, mk(actor, 3e-4), qf, mk(qf, 3e-4), vf, mk(vf, 3e-4), max_steps=50,
+                                device="cuda", batch_size=B)
+    assert list(tr.state_dict()["actor"]) == list(sd["actor"])  # the advisor's case: the trainer's own state_dict loads
+    tr.load_state_dict(tr.state_dict())
+    tr.load_state_dict(sd)
+    assert tr.total_it == 2
+    assert torch.equal(tr.actor.net.net[3].weight.cpu(), sd["actor"]["net.net.3.weight"])
+    got = tr.state_dict()
+    assert list(got["actor"]) == list(sd["actor"])
+    assert torch.equal(got["actor_optimizer"]["state"][3]["exp_avg"].cpu(), sd["actor_optimizer"]["state"][3]["exp_avg"])
+
+
+def test_actor_lr_schedule_attribute(golden_dir):
+    """`trainer.actor_lr_schedule` (iql.py:571): get_last_lr / state_dict / load_state_dict over the in-kernel schedule."""
+    from iqlpref_b200 import iql as biql
+    d, sd, hp = _fixtures(golden_dir)
+    qf, vf, actor = (m.cuda() for m in _modules(biql, d))
+    mk = lambda m, lr: torch.optim.Adam(m.parameters(), lr=lr)
+    tr = biql.ImplicitQLearning(1.0, actor, mk(actor, hp["actor_lr"]), qf, mk(qf, hp["qf_lr"]), vf, mk(vf, hp["vf_lr"]),
+                                iql_tau=hp["iql_tau"], beta=hp["beta"], max_steps=hp["max_steps"],
+                                discount=hp["discount"], tau=hp["tau"], device="cuda", batch_size=B)
+    sch = tr.actor_lr_schedule
+    assert sch.get_last_lr() == [hp["actor_lr"]] and sch.last_epoch == 0 and sch.T_max == hp["max_steps"]
+    t = {n: torch.from_numpy(d[f"table.{n}"]) for n in ("obs", "act", "rew", "next_obs", "done")}
+    for k in range(int(d["k_saved"])):
+        i = torch.from_numpy(d["idx"][k])
+        tr.train([t["obs"][i].cuda(), t["act"][i].cuda(), t["rew"][i, None].cuda(), t["next_obs"][i].cuda(),
+                  t["done"][i, None].cuda()])
+    assert sch.last_epoch == int(d["k_saved"])
+    assert abs(sch.get_last_lr()[0] - float(d["lr_saved"])) < 1e-15  # the reference's scheduler after the same steps
+    want = sd["actor_lr_schedule"]
+    got = sch.state_dict()
+    assert set(got) == set(want)
+    for key, val in want.items():
+        if key == "_last_lr":
+            assert abs(got[key][0] - val[0]) < 1e-15
+        else:
+            assert got[key] == val, key
+    sch.load_state_dict(dict(want, _last_lr=[1.25e-4]))
+    assert sch.get_last_lr() == [1.25e-4] and tr.actor_optimizer.param_groups[0]["lr"] == 1.25e-4
+    with pytest.raises(RuntimeError):
+        sch.step()

@@ -353,3 +353,47 @@ def test_batched_policy_inference_matches_the_modules(det, precision):
     assert eng.act(torch.zeros((0, S))).shape == (N, 0, A)
     with pytest.raises(ValueError):
         eng.act(torch.zeros((4, S + 1)))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_agents_are_bit_identical_however_they_are_sharded(precision):
+    """agents are independent, so agent i of a 4-agent engine, of a 2 + 2 split (what two ranks of
+    `sharding.shard_agents` hold) and of a 1 + 3 split must produce the same bits - losses every step, parameters,
+    Adam state, target and RNG offset at the end - with on-device sampling."""
+    from iqlpref_b200 import iql as biql
+    from iqlpref_b200 import sharding
+    S, A, N, K = 29, 8, 4, 6
+    hps = [dict(discount=0.99, tau=0.005, beta=3.0 + a, iql_tau=0.7 + 0.05 * a, vf_lr=3e-4, qf_lr=3e-4,
+                actor_lr=3e-4, max_steps=100 + a) for a in range(N)]
+    buf = biql.ReplayBuffer(S, A, 6000)
+    g = torch.Generator(device="cuda").manual_seed(4)
+    buf._table[:, :2 * S + A + 2] = torch.randn((6000, 2 * S + A + 2), generator=g, device="cuda")
+    buf._table[:, 2 * S + A + 1] = (buf._table[:, 2 * S + A + 1] > 1.3).float()
+    buf._size = buf._pointer = 6000
+    cols = torch.randn((3, 6000), generator=g, device="cuda").contiguous()
+
+    def run(agent_ids):
+        n = len(agent_ids)
+        eng = biql.BatchedIQL(S, A, n, batch_size=256, hparams=[hps[a] for a in agent_ids], precision=precision,
+                              seeds=[11 + a for a in agent_ids])
+        for j, a in enumerate(agent_ids):
+            torch.manual_seed(50 + a)
+            eng.adopt(j, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0), bind=False)
+        variant = torch.tensor([a % 3 for a in agent_ids], dtype=torch.int32, device="cuda")
+        eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
+        trace = []
+        for _ in range(K):
+            eng.train(None)
+            trace.append(eng.losses.clone())
+        eng.sync()
+        torch.cuda.synchronize()
+        return torch.stack(trace, 1), eng  # [n, K, 3]
+
+    whole, e_all = run(list(range(N)))
+    for split in ([range(*sharding.shard_bounds(N, r, 2)) for r in range(2)], [range(0, 1), range(1, 4)]):
+        for ids in split:
+            ids = list(ids)
+            part, e = run(ids)
+            assert torch.equal(part, whole[ids]), (precision, ids)
+            for name in ("params", "exp_avg", "exp_avg_sq", "target", "it", "actor_lr", "rng"):
+                assert torch.equal(getattr(e, name), getattr(e_all, name)[ids]), (precision, ids, name)

@@ -223,3 +223,108 @@ def test_tensor_core_relabel_refuses_other_shapes():
     assert got.shape == (64,)
     with pytest.raises(ValueError):
         ensemble_predict(_members(rng, 37, 128, 2, 1), x, "mean", precision="tf32")
+
+
+# ------------------------------------------------------------------------------------------------
+# CVaR tail membership against the REFERENCE's fp32 predictions, default precision included
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("precision,rel_tol", [("auto", 4e-5), ("fp32", 4e-6)])
+@pytest.mark.parametrize("alpha", [0.5, 0.9, 0.95])
+@pytest.mark.parametrize("S", [40, 981])
+def test_cvar_tail_membership_vs_reference_fp32_predictions(golden_dir, S, alpha, precision, rel_tol):
+    """`tests/golden/cvar_ref.npz` holds the all_preds matrix the unmodified reference RewardMLP computes in fp32 on the
+    CPU (oracle/gen_golden_cvar.py).  The reference's tail set of a row is `np.argpartition(all_preds, kth, axis=0)
+    [:n_tail]` (iql.py:1009-1011, 1185-1187).  The CUDA path selects from its own predictions (default precision "auto" =
+    split-bf16 on the tensor cores, ~1e-5 of the prediction scale; "fp32" = FFMA), so membership must be IDENTICAL
+    wherever the reference separates the n_tail-th and (n_tail+1)-th smallest member by more than twice the arithmetic
+    tolerance, and may differ only for members that close to the threshold (the tie-tolerant criterion of SURVEY H6)."""
+    from iqlpref_b200.relabel import cvar_n_tail, ensemble_predict
+    from oracle.gen_golden_cvar import members_from_seed, rows_from_seed
+    ref = np.load(os.path.join(golden_dir, "cvar_ref.npz"))[f"preds.S{S}"]
+    x = rows_from_seed()
+    out, preds, sel = ensemble_predict(members_from_seed(S, seed=S), x, "cvar", alpha, "relu", return_preds=True,
+                                       return_selection=True, precision=precision)
+    preds, sel, out = preds.cpu().numpy(), sel.cpu().numpy().astype(bool), out.cpu().numpy()
+    n_tail = cvar_n_tail(alpha, S)
+    assert n_tail == max(1, int(np.floor((1.0 - alpha) * S)))
+    kth = min(n_tail, S - 1)
+    ref_sel = np.zeros_like(sel)
+    np.put_along_axis(ref_sel, np.argpartition(ref, kth, axis=0)[:n_tail], True, axis=0)
+    tol = rel_tol * float(np.abs(ref).max())
+    err = float(np.abs(preds - ref).max())
+    srt = np.sort(ref, axis=0)
+    clear = (srt[n_tail] - srt[n_tail - 1]) > 2 * tol
+    diff = sel != ref_sel
+    print(f"S={S} alpha={alpha} {precision}: max |pred - ref| = {err:.2e} (tol {tol:.2e}); rows with a clear threshold "
+          f"{int(clear.sum())}/{clear.size}; rows whose tail set differs {int(diff.any(axis=0).sum())}")
+    assert err <= tol
+    assert (sel.sum(axis=0) == n_tail).all()
+    assert clear.mean() > 0.4
+    np.testing.assert_array_equal(sel[:, clear], ref_sel[:, clear])
+    # where membership differs, the member sits within the tolerance band around the reference's threshold
+    thr = 0.5 * (srt[n_tail] + srt[n_tail - 1])
+    assert (np.abs(ref - thr[None, :])[diff] <= 2 * tol).all()
+    want = np.partition(ref, kth, axis=0)[:n_tail].mean(axis=0)
+    np.testing.assert_allclose(out, want, rtol=0, atol=2 * tol)
+
+
+def test_empirical_cvar_matches_the_reference(rel):
+    """product `empirical_cvar` (iql.py:735-763) against values written by the reference function (relabel.npz)."""
+    from iqlpref_b200.iql import empirical_cvar
+    got = [empirical_cvar(rel["cvar.samples"], a) for a in (0.0, 0.5, 0.9, 0.95, 0.99)]
+    np.testing.assert_allclose(got, rel["cvar.values"], rtol=1e-6)
+    assert abs(got[0] - float(rel["cvar.samples"].mean())) < 1e-6  # alpha = 0 is the plain mean (docstring :751-752)
+    for bad in (-0.1, 1.0, 1.5):
+        with pytest.raises(ValueError):
+            empirical_cvar(rel["cvar.samples"], bad)
+
+
+@pytest.mark.parametrize("compiled", [False, True])
+def test_load_mlp_reward_model(rel, tmp_path, compiled):
+    """`load_mlp_reward_model` (iql.py:1345-1353): best_model.pt["net"] + config.yaml "activations"; dims inferred from
+    the shapes (:1326-1336); `_orig_mod.` prefixes of a torch.compile'd model stripped (:1312-1323)."""
+    from iqlpref_b200.iql import load_mlp_reward_model, qlearning_dataset_mr
+    from iqlpref_b200.reward_models import MLP
+    m = MLP(37, 1, [32, 48, 32], "tanh")
+    sd = {k: torch.from_numpy(rel[f"mlp.tanh.w{i}"]) for i, k in enumerate(m.state_dict())}
+    if compiled:
+        sd = {"_orig_mod." + k: v for k, v in sd.items()}
+    torch.save({"net": sd, "optimizer": {}}, tmp_path / "best_model.pt")
+    (tmp_path / "config.yaml").write_text(yaml.safe_dump({"activations": "tanh", "hidden_dims": [1, 2, 3]}))
+    model = load_mlp_reward_model(str(tmp_path), "cuda")
+    assert not model.training and model.hidden_dims == [32, 48, 32] and model.input_dim == 37
+    assert model.activation_name == "tanh" and next(model.parameters()).is_cuda
+    y = model(torch.from_numpy(rel["mlp.x"]).cuda())
+    np.testing.assert_allclose(y.cpu().numpy(), rel["mlp.tanh.y"], rtol=1e-3, atol=1e-5)
+    # config.yaml without "activations" means relu (iql.py:1339-1342)
+    m2 = MLP(37, 1, [32, 32, 32], "relu")
+    torch.save({"net": {k: torch.from_numpy(rel[f"mr.w{i}"]) for i, k in enumerate(m2.state_dict())}},
+               tmp_path / "best_model.pt")
+    (tmp_path / "config.yaml").write_text("lr: 0.001\n")
+    model = load_mlp_reward_model(str(tmp_path), "cuda")
+    assert model.activation_name == "relu"
+    out = qlearning_dataset_mr(FakeEnv(), model, dataset=_ds(rel, "ds_t"))
+    np.testing.assert_allclose(out["rewards"], rel["mr.ds_t.toe0.rewards"], rtol=1e-3, atol=1e-5)
+    with pytest.raises(FileNotFoundError):
+        load_mlp_reward_model(str(tmp_path / "nowhere"), "cuda")
+
+
+@pytest.mark.parametrize("L", [1, 2])
+def test_load_pt_reward_model(rel, tmp_path, L):
+    """`load_pt_reward_model` (iql.py:1356-1390): every dimension inferred from the state-dict shapes, heads / eps /
+    intermediate_dim from config.yaml; the loaded model relabels like the reference's."""
+    from iqlpref_b200.iql import load_pt_reward_model, qlearning_dataset_pt
+    pre = f"pt{L}."
+    sd = {k[len(pre):]: torch.from_numpy(rel[k]) for k in rel.files
+          if k.startswith(pre) and ".fw." not in k and ".ds_" not in k}
+    max_pos = 64
+    for l in range(L):  # the reference's state_dict carries the causal buffer (its shape gives max_pos, :1386)
+        sd[f"gpt.layers.{l}.attention.causal_bias"] = torch.triu(torch.full((max_pos, max_pos), float("-inf")),
+                                                                 diagonal=1).view(1, 1, max_pos, max_pos)
+    torch.save({"net": {"_orig_mod." + k: v for k, v in sd.items()}}, tmp_path / "best_model.pt")
+    (tmp_path / "config.yaml").write_text(yaml.safe_dump({"num_heads": 4, "intermediate_dim": 64, "model_eps": 0.1}))
+    model = load_pt_reward_model(str(tmp_path), "cuda")
+    assert not model.training and model.num_layers == L and model.embd_dim == 32 and model.pref_attn_embd_dim == 32
+    assert model.timestep_embed.weight.shape[0] == 61 and abs(model.stacked_layer_norm.eps - 0.1) < 1e-12
+    out = qlearning_dataset_pt(FakeEnv(), model, query_length=10, dataset=_ds(rel, "ds_t"))
+    np.testing.assert_allclose(out["rewards"], rel[f"pt{L}.ds_t.rewards"], rtol=1e-3, atol=1e-5)

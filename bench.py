@@ -414,7 +414,15 @@ def build_workload(args, dev, rank, world):
     t[:, 2 * S_DIM + A_DIM + 1] = sparse  # terminals = goal reached
     buf._size = buf._pointer = rows
     # q_mlp relabel of the whole dataset (configs[1]) + the other relabel passes (rank 0 reports them)
-    relabel, r_hat = bench_relabel(args, dev, t, R, load_peaks())
+    if getattr(args, "skip_relabel", False):  # kernel experiments: only the reward columns are needed
+        from iqlpref_b200.relabel import ensemble_predict, pack_members
+        from iqlpref_b200.reward_models.q_mlp import MLP as RewardMLP, member_weights
+        torch.manual_seed(0)
+        rm = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
+        r_hat = ensemble_predict(pack_members([member_weights(rm)], dev), t[:, :S_DIM + A_DIM], "mean", device=dev)
+        relabel = {"skipped": True}
+    else:
+        relabel, r_hat = bench_relabel(args, dev, t, R, load_peaks())
     # reward columns standing in for normalize_reward 0..7 (iql.py:363-401): affine maps of the relabelled reward
     r = r_hat
     span = (r.max() - r.min()).clamp_min(1e-6)
@@ -432,6 +440,7 @@ def build_workload(args, dev, rank, world):
     eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
     if args.precision == "bf16":
         eng.debug_option(0, int(args.fused_adam))
+    eng.set_overlap(bool(args.overlap))  # training-loop mode: the last group's optimizer runs under the next update
     return eng, buf, cols, variant, relabel
 
 
@@ -633,6 +642,7 @@ def run_cuda(args):
     e0.record(stream)
     for _ in range(K):
         eng.train(None)
+    eng.sync()  # the optimizer of the last agent group (internal stream) is inside the timed region
     e1.record(stream)
     torch.cuda.synchronize(dev)
     t_host1 = time.perf_counter()
@@ -676,6 +686,7 @@ def run_cuda(args):
     e0.record(stream)
     for i in range(K):
         eng.train_host(host_rows[i % ring], host_losses)
+    eng.sync()
     e1.record(stream)
     torch.cuda.synchronize(dev)
     barrier()
@@ -691,6 +702,7 @@ def run_cuda(args):
     for i in range(K):
         eng.train_host_pipelined(host_rows[i % ring], host_losses)
     eng.train_host_pipelined(None, host_losses)  # flush: losses of the last update are on the host
+    eng.sync()
     e1.record(stream)
     torch.cuda.synchronize(dev)
     t_w1 = time.perf_counter()
@@ -730,11 +742,12 @@ def run_cuda(args):
                                   "hbm_frac": bytes_per_update() * per_gpu / 1e9 / peaks["hbm"],
                                   "flops_per_update": flops_per_update(), "bytes_per_update": bytes_per_update()},
                 "relabel": relabel}
-        relabel["roofline"] = {"bound": "tensor", "achieved": 3.0 * relabel["mlp"]["tflops_fp32_equiv"],
-                               "peak": peaks["tensor_burst"], "unit": "TFLOP/s", "frac": relabel["mlp"]["tensor_frac_bf16_mma"],
-                               "hbm_frac": relabel["mlp"]["hbm_frac"],
-                               "note": "single-model relabel, whole iqlb_relabel_mlp_p call (weight-image prep + kernel), "
-                                       "timed alone: burst peak; split-bf16 issues three bf16 MMAs per product"}
+        if "mlp" in relabel:
+            relabel["roofline"] = {"bound": "tensor", "achieved": 3.0 * relabel["mlp"]["tflops_fp32_equiv"],
+                                   "peak": peaks["tensor_burst"], "unit": "TFLOP/s",
+                                   "frac": relabel["mlp"]["tensor_frac_bf16_mma"], "hbm_frac": relabel["mlp"]["hbm_frac"],
+                                   "note": "single-model relabel, whole iqlb_relabel_mlp_p call (weight-image prep + "
+                                           "kernel), timed alone: burst peak; split-bf16 issues three bf16 MMAs per product"}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         if ref_cuda is not None:
@@ -763,6 +776,9 @@ def main():
                          "(BASELINE.json configs[4]: 64 agents sharded across 8 GPUs)")
     ap.add_argument("--agents-total", type=int, default=64)
     ap.add_argument("--pt-windows", type=int, default=4096)
+    ap.add_argument("--skip-relabel", action="store_true", help="skip the relabel benchmarks (kernel experiments)")
+    ap.add_argument("--overlap", type=int, default=int(os.environ.get("IQLB_OVERLAP_ARG", "1")),
+                    help="1: iqlb_agents_set_overlap (deferred join of the optimizer stream, synced before the clock stops)")
     ap.add_argument("--fused-adam", type=int, default=int(os.environ.get("IQLB_FUSED_ADAM", "0")),
                     help="1: Adam/Polyak inside the weight-gradient kernel (gradients never reach HBM)")
     args = ap.parse_args()

@@ -152,6 +152,19 @@ int iqlb_agents_act(iqlb_agents* h, const float* states, int64_t agent_stride, i
  * iqlb_agents_set_replay or this call discards it. */
 int iqlb_agents_refresh(iqlb_agents* h, void* stream);
 
+/* Optimizer overlap (precision 1, opt-in with IQLB_GROUPS=2; with the default single agent group both calls are no-ops -
+ * on B200 the overlapped schedule measured slower than the serial one).  The HBM-bound Adam +
+ * Polyak kernel of agent group g runs on an internal low-priority stream, as a residency-bounded persistent grid, UNDER the
+ * latency-bound tensor-core kernels of the next group on the caller's stream: agents are independent (the reference runs
+ * one OS process per agent, tr_sweeps/launch.sh:82-92), so group g's update t+1 needs only group g's optimizer of update t.
+ * Default (overlap 0): every step call ends with the caller's stream waiting for the internal one - ordinary stream
+ * semantics.  iqlb_agents_set_overlap(h, 1, stream) defers that join to the next step, so the last group's optimizer also
+ * overlaps the first group's next update; the caller must then call iqlb_agents_sync(h, stream) before reading or writing
+ * params / exp_avg / exp_avg_sq / target on `stream` (losses, loss_sum, it, actor_lr and rng are written on the caller's
+ * stream and need no sync; refresh, act, debug_copy and destroy join by themselves).  Arithmetic is unchanged. */
+int iqlb_agents_set_overlap(iqlb_agents* h, int32_t enable, void* stream);
+int iqlb_agents_sync(iqlb_agents* h, void* stream);
+
 /* Number of kernels one iqlb_agents_step enqueues (for launch accounting). */
 int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled);
 

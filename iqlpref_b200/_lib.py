@@ -45,6 +45,8 @@ _SIGNATURES = {
     "iqlb_agents_step_host": ([_P, _P, _P, _P], C.c_int),
     "iqlb_agents_step_host_pipelined": ([_P, _P, _P, _P], C.c_int),
     "iqlb_agents_refresh": ([_P, _P], C.c_int),
+    "iqlb_agents_set_overlap": ([_P, C.c_int32, _P], C.c_int),
+    "iqlb_agents_sync": ([_P, _P], C.c_int),
     "iqlb_agents_launches_per_step": ([_P, C.c_int32], C.c_int),
     "iqlb_agents_profile": ([_P, C.c_int32], C.c_int),
     "iqlb_agents_profile_collect": ([_P], C.c_int),

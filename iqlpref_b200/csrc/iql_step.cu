@@ -333,25 +333,36 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 #ifndef IQLB_ADAM_SLOTS
 #define IQLB_ADAM_SLOTS 1
 #endif
-__global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __restrict__ params,
+// One CTA owns `256 * IQLB_ADAM_SLOTS` 16-byte words (a "chunk") of one agent's parameter vector at a time and walks
+// chunks blockIdx.x, blockIdx.x + gridDim.x, ... of the launch (agent-major order).  Two launch shapes:
+//   * one chunk per CTA (gridDim.x == n_chunks): the stand-alone optimizer pass, every SM at full occupancy;
+//   * a RESIDENCY-BOUNDED persistent grid (gridDim.x == k * SMs, k small): the optimizer of agent group g runs on a side
+//     stream UNDER the tensor-core kernels of group g+1 (iql_step.cu step_device).  Those kernels keep one CTA per SM
+//     with ~39 K registers and all of shared memory; a 256-thread CTA of this kernel needs no shared memory and
+//     <= 48 registers per thread (launch bound: 5 CTAs per SM), so two of them fit beside it on every SM and stream HBM while the GEMM CTA waits on
+//     its own latencies.  An unbounded grid would instead fill every SM's thread slots and lock the GEMM kernels out.
+template <bool kPersist>
+__global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layout L, float* __restrict__ params,
                                                           float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                           float* __restrict__ target, const float* __restrict__ grads,
                                                           const StepScalars* __restrict__ scal, BfParams BP, int shadow,
-                                                          int agent0) {
-  // A CTA owns 2048 consecutive parameters of one agent; thread t handles the 16-byte words t and t + 256 of
-  // that span, so every warp access is 512 contiguous bytes per array.  Network segments start on multiples of
-  // 8 floats: a word never straddles two optimizers, and inside W1 it is half of a 16-byte chunk of the image.
-  const int agent = agent0 + ((shadow & 4) ? (int)(gridDim.y - 1 - blockIdx.y) : (int)blockIdx.y);
-  const StepScalars sc = scal[agent];
+                                                          int agent0, int n_agents_launch, int chunks_per_agent) {
+  // Thread t handles the 16-byte words t (and t + 256, ...) of the chunk, so every warp access is 512 contiguous bytes per
+  // array.  Network segments start on multiples of 8 floats: a word never straddles two optimizers, and inside W1 it
+  // is half of a 16-byte chunk of the image.
   const bool hint = (shadow & 2) != 0;  // stream the optimizer state through L2 (evict_first), keep the images (evict_last)
   const uint64_t pol_s = l2_policy_evict_first(), pol_k = l2_policy_evict_last();
   constexpr int kS = IQLB_ADAM_SLOTS;  // 16-byte words per thread and array
+  auto body = [&](const int chunk, const bool first) {
+  const int aidx = chunk / chunks_per_agent, cblk = chunk - aidx * chunks_per_agent;
+  const int agent = agent0 + ((shadow & 4) ? n_agents_launch - 1 - aidx : aidx);
+  const StepScalars sc = scal[agent];
   float4 p[kS], m[kS], v[kS], g[kS], tg[kS];
   int64_t e[kS];
   bool live[kS], has_t[kS];
 #pragma unroll
   for (int h = 0; h < kS; ++h) {  // optimizer state: not written by the weight-gradient kernel (the PDL predecessor)
-    e[h] = ((int64_t)blockIdx.x * (256 * kS) + threadIdx.x + 256 * h) * 4;
+    e[h] = ((int64_t)cblk * (256 * kS) + threadIdx.x + 256 * h) * 4;
     live[h] = e[h] < L.Pstride;
     has_t[h] = e[h] < L.PQ;
     if (live[h]) {
@@ -369,8 +380,10 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
       }
     }
   }
-  pdl_wait();
-  pdl_launch();
+  if (first) {
+    pdl_wait();
+    pdl_launch();
+  }
 #pragma unroll
   for (int h = 0; h < kS; ++h) {  // gradients of this step
     if (!live[h]) continue;
@@ -439,6 +452,17 @@ __global__ void __launch_bounds__(256) adam_polyak_kernel(Layout L, float* __res
         }
       }
     }
+  }
+  };
+  if (kPersist) {
+    const int n_chunks = n_agents_launch * chunks_per_agent;
+    bool first = true;
+    for (int chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+      body(chunk, first);
+      first = false;
+    }
+  } else {
+    body((int)blockIdx.x, true);
   }
 }
 
@@ -576,24 +600,47 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   return IQLB_OK;
 }
 
-static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st) {
+static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded) {
   const Layout& L = h->L;
   const bool bf = h->desc.precision == 1;
   if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
-  static const bool l2hint = getenv("IQLB_L2HINT") && atoi(getenv("IQLB_L2HINT")) != 0;  // measured: no gain on B200
-  IQLB_CUDA(launch_pdl(adam_polyak_kernel, dim3((unsigned)((L.Pstride + 1024 * IQLB_ADAM_SLOTS - 1) / (1024 * IQLB_ADAM_SLOTS)), n), dim3(256), 0, st,
-                       bf && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
+  static const int l2hint_env = getenv("IQLB_L2HINT") ? atoi(getenv("IQLB_L2HINT")) : -1;
+  // bounded (under the next group's tensor-core kernels): the optimizer state streams through L2 with evict_first so that
+  // it does not push the other group's activations (written by one kernel, read by the next) out to HBM
+  const bool l2hint = l2hint_env >= 0 ? l2hint_env != 0 : bounded;
+  const int cpa = (int)((L.Pstride + 1024 * IQLB_ADAM_SLOTS - 1) / (1024 * IQLB_ADAM_SLOTS));
+  const int n_chunks = cpa * n;
+  int grid = n_chunks;
+  if (bounded && h->n_sm > 0 && h->adam_ctas_per_sm > 0 && grid > h->n_sm * h->adam_ctas_per_sm) grid = h->n_sm * h->adam_ctas_per_sm;
+  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)grid), dim3(256), 0, st,
+                       bf && !bounded && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
-                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0));
+                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa));
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
 }
 
-// One update of every agent.  precision 1 with >= 32 agents splits the agents into groups: the
-// tensor-core chain of group g+1 (latency-bound, on the caller's stream) overlaps the HBM-bound Adam
-// kernel of group g (on an internal stream that is forked from and joined to the caller's stream
-// inside this call, so stream ordering for the caller is unchanged).  Profiling runs one group.
+// The caller's stream waits for every optimizer launch still running on the side stream.
+static int join_groups(iqlb_agents* h, cudaStream_t st) {
+  for (int g = 0; g < iqlb_agents::kMaxGroups; ++g) {
+    if (h->adam_pending[g]) {
+      IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_adam[g], 0));
+      h->adam_pending[g] = false;
+    }
+  }
+  return IQLB_OK;
+}
+
+// One update of every agent.
+// precision 1 with >= 2 agent groups (opt-in, IQLB_GROUPS; one group by default): the HBM-bound optimizer of group g runs on
+// an internal low-priority stream as a residency-bounded persistent grid (adam_polyak_kernel) UNDER the latency-bound
+// tensor-core chain of the next group on the caller's stream - agents are independent, so group g's chain of step t+1
+// needs only group g's optimizer of step t.  Default: the caller's stream joins the side stream at the end of every call
+// (stream semantics unchanged: chain(A), [Adam(A) || chain(B)], Adam(B)).  With iqlb_agents_set_overlap(h, 1) the join
+// is deferred, so Adam(B) of step t also overlaps chain(A) of step t+1; the caller must then call iqlb_agents_sync
+// before touching params / exp_avg / exp_avg_sq / target (losses, it, rng and actor_lr are written on the caller's
+// stream and need no sync).  Profiling runs one group.
 static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   const int N = h->desc.n_agents;
   int rc;
@@ -604,6 +651,7 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
     h->pre_valid = false;
   }
   if (G <= 1) {
+    if ((rc = join_groups(h, st))) return rc;  // (a profiled or fused-Adam step after overlapped ones)
     if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
     if (sampled && h->desc.precision == 1 && h->presample && !h->prof && h->idx_out == nullptr) {
       if (!h->pre_stream) {
@@ -621,22 +669,47 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
       h->pre_valid = true;
       pf.mark("replay_gather_pack(next step)");
     }
-    if ((rc = step_adam(h, 0, N, pf, st))) return rc;
+    if ((rc = step_adam(h, 0, N, pf, st, false))) return rc;
     pf.done();
     if (h->zig >= 0 && h->desc.precision == 1) h->zig ^= 1;
     return IQLB_OK;
   }
   const int per = (N + G - 1) / G;
+  static const bool tl = getenv("IQLB_GROUP_TL") && atoi(getenv("IQLB_GROUP_TL")) != 0;  // debug: per-step group timeline
+  static cudaEvent_t tl_start = nullptr;
+  if (tl) {
+    if (!tl_start) cudaEventCreate(&tl_start);
+    cudaEventRecord(tl_start, st);
+  }
   for (int g = 0, a0 = 0; a0 < N; ++g, a0 += per) {
     const int n = a0 + per <= N ? per : N - a0;
+    if (h->adam_pending[g]) {  // this group's optimizer of the previous step (deferred join)
+      IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_adam[g], 0));
+      h->adam_pending[g] = false;
+    }
     if ((rc = step_chain(h, a0, n, sampled, pf, st))) return rc;
     IQLB_CUDA(cudaEventRecord(h->ev_chain[g], st));
     IQLB_CUDA(cudaStreamWaitEvent(h->side_stream, h->ev_chain[g], 0));
-    if ((rc = step_adam(h, a0, n, pf, h->side_stream))) return rc;
+    if ((rc = step_adam(h, a0, n, pf, h->side_stream, true))) return rc;
+    IQLB_CUDA(cudaEventRecord(h->ev_adam[g], h->side_stream));
+    h->adam_pending[g] = true;
   }
-  IQLB_CUDA(cudaEventRecord(h->ev_join, h->side_stream));
-  IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
+  if (tl) {  // synchronises: shows the schedule inside ONE step (no cross-step overlap while this is on)
+    static int n_print = 0;
+    cudaStreamSynchronize(h->side_stream);
+    cudaStreamSynchronize(st);
+    if (n_print++ % 20 == 15) {
+      for (int g = 0; g < G; ++g) {
+        float tc = 0.f, ta = 0.f;
+        cudaEventElapsedTime(&tc, tl_start, h->ev_chain[g]);
+        cudaEventElapsedTime(&ta, tl_start, h->ev_adam[g]);
+        fprintf(stderr, "[group timeline] group %d: chain done at %.1f us, optimizer done at %.1f us\n", g, tc * 1e3, ta * 1e3);
+      }
+    }
+  }
+  if (!h->overlap && (rc = join_groups(h, st))) return rc;
   pf.done();
+  if (h->zig >= 0) h->zig ^= 1;
   return IQLB_OK;
 }
 
@@ -700,16 +773,31 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   h->presample = (getenv("IQLB_PRESAMPLE") && atoi(getenv("IQLB_PRESAMPLE")) != 0) ? 1 : 0;
   if (!rc && d->precision == 1) {
     const char* env = getenv("IQLB_GROUPS");
-    int G = env ? atoi(env) : 1;  // measured on B200: splitting 64 agents into groups is slower
+    // Opt-in (IQLB_GROUPS=2): measured on B200 with 64 agents, two groups are SLOWER than one (313-370 vs 260 us per
+    // step, profiles/r02_overlap_ab.jsonl).  The group timeline shows why: a 32-agent chain alone takes 96 us and its
+    // optimizer 65 us, but run together they take 150 us and 113 us - the latency-bound tensor-core kernels see every
+    // operand load queue behind the optimizer's saturated HBM stream, and two half-size chains (2 x 96 us) cost 53 us
+    // more than one full-size chain (139 us) to begin with.
+    int G = env ? atoi(env) : 1;
     if (G < 1) G = 1;
     if (G > iqlb_agents::kMaxGroups) G = iqlb_agents::kMaxGroups;
     if (G > d->n_agents) G = d->n_agents;
     h->n_groups = G;
-    if (G > 1) {
-      if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaStreamCreate%s", "");
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      rc = fail(IQLB_ERR_CUDA, "cudaDeviceGetAttribute%s", "");
+    h->adam_ctas_per_sm = getenv("IQLB_ADAM_CTAS") ? atoi(getenv("IQLB_ADAM_CTAS")) : 2;
+    h->overlap = (getenv("IQLB_OVERLAP") && atoi(getenv("IQLB_OVERLAP")) != 0) ? 1 : 0;
+    if (G > 1 && !rc) {
+      int prio_lo = 0, prio_hi = 0;  // lowest priority: tensor-core CTAs of the caller's stream are placed first
+      if (cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi) != cudaSuccess ||
+          cudaStreamCreateWithPriority(&h->side_stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess)
+        rc = fail(IQLB_ERR_CUDA, "cudaStreamCreate%s", "");
+      const unsigned evf = (getenv("IQLB_GROUP_TL") && atoi(getenv("IQLB_GROUP_TL")) != 0) ? cudaEventDefault : cudaEventDisableTiming;
       for (int g = 0; g < G && !rc; ++g)
-        if (cudaEventCreateWithFlags(&h->ev_chain[g], cudaEventDisableTiming) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaEventCreate%s", "");
-      if (!rc && cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cudaEventCreate%s", "");
+        if (cudaEventCreateWithFlags(&h->ev_chain[g], evf) != cudaSuccess ||
+            cudaEventCreateWithFlags(&h->ev_adam[g], evf) != cudaSuccess)
+          rc = fail(IQLB_ERR_CUDA, "cudaEventCreate%s", "");
     }
   }
   if (rc) { iqlb_agents_destroy(h); return rc; }
@@ -727,8 +815,10 @@ extern "C" int iqlb_agents_destroy(iqlb_agents* h) {
     cudaEventDestroy(h->ev_pre_fork);
     cudaEventDestroy(h->ev_pre_join);
   }
-  for (int g = 0; g < iqlb_agents::kMaxGroups; ++g) if (h->ev_chain[g]) cudaEventDestroy(h->ev_chain[g]);
-  if (h->ev_join) cudaEventDestroy(h->ev_join);
+  for (int g = 0; g < iqlb_agents::kMaxGroups; ++g) {
+    if (h->ev_chain[g]) cudaEventDestroy(h->ev_chain[g]);
+    if (h->ev_adam[g]) cudaEventDestroy(h->ev_adam[g]);
+  }
   if (h->copy_stream) {
     cudaStreamSynchronize(h->copy_stream);
     cudaStreamDestroy(h->copy_stream);
@@ -844,6 +934,17 @@ extern "C" int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host
   return IQLB_OK;
 }
 
+extern "C" int iqlb_agents_sync(iqlb_agents* h, void* stream) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  return join_groups(h, (cudaStream_t)stream);
+}
+
+extern "C" int iqlb_agents_set_overlap(iqlb_agents* h, int32_t enable, void* stream) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  h->overlap = enable ? 1 : 0;
+  return enable ? IQLB_OK : join_groups(h, (cudaStream_t)stream);
+}
+
 extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampled) {
   if (!h) return 0;
   if (h->launches_last > 0) return h->launches_last;  // counted by the last step
@@ -853,6 +954,7 @@ extern "C" int iqlb_agents_launches_per_step(const iqlb_agents* h, int32_t sampl
 
 extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
+  { int rcj = join_groups(h, (cudaStream_t)stream); if (rcj) return rcj; }
   if (h->pre_valid) {  // caller-owned state (parameters, RNG offsets) changed: the look-ahead batch is stale
     IQLB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_pre_join, 0));
     h->pre_valid = false;
@@ -875,6 +977,7 @@ extern "C" int iqlb_agents_act(iqlb_agents* h, const float* states, int64_t agen
   IQLB_REQUIRE(n_rows >= 0 && agent_stride >= 0, "shape");
   if (n_rows == 0) return IQLB_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  { int rcj = join_groups(h, st); if (rcj) return rcj; }
   const Layout& L = h->L;
   const int N = h->desc.n_agents;
   float* hid = nullptr;       // H1 | H2, [N][n_rows][H] each
@@ -969,6 +1072,7 @@ extern "C" int iqlb_agents_profile_read(iqlb_agents* h, int32_t i, const char** 
 
 extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, int64_t* nbytes, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
+  if (dst) { int rcj = join_groups(h, (cudaStream_t)stream); if (rcj) return rcj; }
   const Layout& L = h->L;
   const int64_t N = h->desc.n_agents, BH = (int64_t)L.B * L.H;
   const float* src = nullptr;

@@ -195,8 +195,12 @@ struct iqlb_agents {
   static constexpr int kMaxGroups = 8;
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_chain[kMaxGroups] = {};
-  cudaEvent_t ev_join = nullptr;
+  cudaEvent_t ev_adam[kMaxGroups] = {};     // optimizer of group g done (side stream)
+  bool adam_pending[kMaxGroups] = {};       // ... and not yet waited for by the caller's stream
   int n_groups = 1;
+  int overlap = 0;           // 1: the join with the side stream is deferred to the next step / iqlb_agents_sync
+  int n_sm = 0;
+  int adam_ctas_per_sm = 2;  // residency bound of the optimizer grid when it runs under tensor-core kernels
   // pipelined host feed (iqlb_agents_step_host_pipelined): H2D of step k+1 on copy_stream under the update of step k
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {}, ev_done[2] = {};

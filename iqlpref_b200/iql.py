@@ -470,6 +470,7 @@ class BatchedIQL:
         """Copy the modules' parameters into agent slot `agent` (target := qf, iql.py:565) and, if
         `bind`, re-point the module parameters at the packed storage so `module.state_dict()`
         always reflects the trained values."""
+        self.sync()
         for m in list(actor.modules()):
             if isinstance(m, nn.Dropout) and m.p > 0 and abs(m.p - self.actor_dropout) > 1e-12:
                 raise ValueError(f"the actor uses Dropout({m.p}) but the engine was built with actor_dropout="
@@ -552,12 +553,19 @@ class BatchedIQL:
                                                             _lib.ptr(host_losses_prev), _lib.stream_ptr(self.device)),
                    "iqlb_agents_step_host_pipelined")
 
+    @_lib.on_device
     def sync(self):
-        """Make everything the engine has enqueued visible to the caller's stream (see `iqlb_agents_sync`)."""
-        fn = getattr(self.lib, "iqlb_agents_sync", None)
-        if fn is not None:
-            with _lib.device_ctx(self.device):
-                _lib.check(fn(self._h, _lib.stream_ptr(self.device)), "iqlb_agents_sync")
+        """Make the optimizer work the engine runs on its internal stream visible to the current stream (needed only
+        after `set_overlap(True)`, before touching `params / exp_avg / exp_avg_sq / target`; see `iqlb_agents_sync`)."""
+        _lib.check(self.lib.iqlb_agents_sync(self._h, _lib.stream_ptr(self.device)), "iqlb_agents_sync")
+
+    @_lib.on_device
+    def set_overlap(self, enable: bool):
+        """Training-loop mode (precision "bf16"): the optimizer of the last agent group keeps running under the first
+        group's NEXT update instead of being joined at the end of every `train()` call.  Losses are unaffected; call
+        `sync()` before reading parameters or optimizer state.  Checkpoint / export helpers of this class do."""
+        _lib.check(self.lib.iqlb_agents_set_overlap(self._h, int(bool(enable)), _lib.stream_ptr(self.device)),
+                   "iqlb_agents_set_overlap")
 
     def launches_per_step(self, sampled: bool) -> int:
         return int(self.lib.iqlb_agents_launches_per_step(self._h, int(sampled)))
@@ -626,6 +634,7 @@ class BatchedIQL:
         """What `ImplicitQLearning.state_dict()` of the reference returns for agent `agent` (iql.py:664-674): the
         three module state_dicts, the three `torch.optim.Adam` state_dicts (state indexed in parameter order), the
         `CosineAnnealingLR` state_dict and `total_it`.  The reference's `load_state_dict` accepts it unchanged."""
+        self.sync()
         hp = dict(zip(self.HP_KEYS, self.hp_host[agent]))
         it = int(self.it[agent].item())
         lr_a = float(self.actor_lr[agent].item())
@@ -650,6 +659,7 @@ class BatchedIQL:
         """Resume agent `agent` from a checkpoint of the reference (or of `agent_state_dict`): parameters, Adam
         moments and step, the scheduled actor lr; the target becomes a copy of qf, as iql.py:679 does on load.
         Returns the checkpoint's `total_it`."""
+        self.sync()
         parts = (("qf", "q_optimizer"), ("vf", "v_optimizer"), ("actor", "actor_optimizer"))
         mods = {}
         for part, _ in parts:  # validate everything before the first write
@@ -709,6 +719,7 @@ class BatchedIQL:
 
     # ---- export in the oracle's naming (tests) -----------------------------------------------------
     def export(self, agent: int) -> Dict[str, np.ndarray]:
+        self.sync()
         d = {}
         for key in self._layout:
             d[key] = self.view(self.params, agent, key).detach().cpu().numpy().copy()

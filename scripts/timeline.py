@@ -13,9 +13,10 @@ ap.add_argument("--rows", type=int, default=1_000_000)
 ap.add_argument("--precision", default="bf16")
 ap.add_argument("--fused-adam", type=int, default=0)
 args = ap.parse_args()
+args.scaling, args.agents_total, args.pt_windows, args.overlap, args.skip_relabel = "weak", 64, 0, 0, True
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
-eng, buf, cols, variant, _ = bench.build_workload(args, dev, 0)
+eng, buf, cols, variant, _ = bench.build_workload(args, dev, 0, 1)
 if args.fused_adam:
     eng.debug_option(0, 1)
 for _ in range(5):

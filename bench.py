@@ -40,7 +40,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+ACTOR_DROPOUT = None
+WORKLOAD = "cfg2"
+
+
+def set_workload(name):
+    """cfg2 = BASELINE.json configs[1] (antmaze-large-diverse-shaped, the headline); cfg4 = the IQL leg of configs[3]
+    (pen-human-shaped: 45 obs, 24 act, actor_dropout 0.1, configs/offline/iql/pen/human_v1.yaml)."""
+    global S_DIM, A_DIM, HP, ACTOR_DROPOUT, WORKLOAD
+    WORKLOAD = name
+    if name == "cfg4":
+        S_DIM, A_DIM, ACTOR_DROPOUT = 45, 24, 0.1
+        HP = dict(HP, beta=3.0, iql_tau=0.8)
+
+
 def workload_name(agents_per_gpu, rows):
+    if WORKLOAD == "cfg4":
+        return (f"configs[3] (IQL leg): IQL on synthetic pen-human-shaped data ({rows} rows, {S_DIM} obs, {A_DIM} act), "
+                f"batch {BATCH}, 2x{HID} MLPs, Gaussian actor with actor_dropout {ACTOR_DROPOUT}, {agents_per_gpu} "
+                f"independent agents per GPU (seeds x {N_VARIANTS} reward columns)")
     return (f"configs[1]: IQL on synthetic antmaze-large-diverse-shaped data ({rows} rows, {S_DIM} obs, {A_DIM} act), "
             f"batch {BATCH}, 2x{HID} MLPs, Gaussian actor, q_mlp-relabelled rewards, {agents_per_gpu} independent agents "
             f"per GPU (seeds x {N_VARIANTS} normalize_reward columns)")
@@ -49,7 +67,9 @@ def workload_name(agents_per_gpu, rows):
 # ------------------------------------------------------------------------------------------------
 # algorithmic work per agent-update (restated in DESIGN.md)
 # ------------------------------------------------------------------------------------------------
-def flops_per_update(S=S_DIM, A=A_DIM, H=HID, B=BATCH):
+def flops_per_update(S=None, A=None, H=HID, B=BATCH):
+    S, A = S or S_DIM, A or A_DIM
+
     def fwd(i, o):
         return 2 * B * (i * H + H * H + H * o)
 
@@ -60,15 +80,17 @@ def flops_per_update(S=S_DIM, A=A_DIM, H=HID, B=BATCH):
     return f + b
 
 
-def param_counts(S=S_DIM, A=A_DIM, H=HID, gaussian=True):
+def param_counts(S=None, A=None, H=HID, gaussian=True):
+    S, A = S or S_DIM, A or A_DIM
     net = lambda i, o: H * i + H + H * H + H + o * H + o
     pq = 2 * net(S + A, 1)
     p = pq + net(S, 1) + net(S, A) + (A if gaussian else 0)
     return p, pq
 
 
-def bytes_per_update(S=S_DIM, A=A_DIM, B=BATCH):
+def bytes_per_update(S=None, A=None, B=BATCH):
     """fp32 state streamed once: p,m,v read+write (24 B/param), target read+write (8 B/param), batch rows once."""
+    S, A = S or S_DIM, A or A_DIM
     p, pq = param_counts(S, A)
     row = (2 * S + A + 2) * 4
     return 24 * p + 8 * pq + B * row
@@ -419,7 +441,7 @@ def build_workload(args, dev, rank, world):
         from iqlpref_b200.reward_models.q_mlp import MLP as RewardMLP, member_weights
         torch.manual_seed(0)
         rm = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
-        r_hat = ensemble_predict(pack_members([member_weights(rm)], dev), t[:, :S_DIM + A_DIM], "mean", device=dev)
+        r_hat = ensemble_predict(pack_members([member_weights(rm)], dev), t[:, :S_DIM + A_DIM], "mean", device=dev).clone()
         relabel = {"skipped": True}
     else:
         relabel, r_hat = bench_relabel(args, dev, t, R, load_peaks())
@@ -432,10 +454,11 @@ def build_workload(args, dev, rank, world):
     variant = (torch.arange(N, device=dev, dtype=torch.int32) % N_VARIANTS).contiguous()
     seeds = [1 + rank * N + a for a in range(N)]
     eng = biql.BatchedIQL(S_DIM, A_DIM, N, hidden_dim=HID, batch_size=BATCH, device=str(dev), precision=args.precision,
-                          hparams=[HP] * N, seeds=seeds)
+                          hparams=[HP] * N, seeds=seeds, actor_dropout=ACTOR_DROPOUT)
     for a in range(N):
         torch.manual_seed(seeds[a])
-        qf, vf, ac = biql.TwinQ(S_DIM, A_DIM), biql.ValueFunction(S_DIM), biql.GaussianPolicy(S_DIM, A_DIM, 1.0)
+        qf, vf = biql.TwinQ(S_DIM, A_DIM), biql.ValueFunction(S_DIM)
+        ac = biql.GaussianPolicy(S_DIM, A_DIM, 1.0, dropout=ACTOR_DROPOUT)
         eng.adopt(a, qf, vf, ac, bind=False)
     eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
     if args.precision == "bf16":
@@ -781,7 +804,13 @@ def main():
                     help="1: iqlb_agents_set_overlap (deferred join of the optimizer stream, synced before the clock stops)")
     ap.add_argument("--fused-adam", type=int, default=int(os.environ.get("IQLB_FUSED_ADAM", "0")),
                     help="1: Adam/Polyak inside the weight-gradient kernel (gradients never reach HBM)")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
+                    help="cfg2: antmaze-shaped headline (configs[1]); cfg4: pen-human-shaped IQL leg of configs[3] "
+                         "(45 obs / 24 act, actor_dropout 0.1) - relabel benchmarks and the CPU legs are skipped")
     args = ap.parse_args()
+    set_workload(args.workload)
+    if args.workload == "cfg4":
+        args.skip_relabel = args.skip_cpu_baseline = args.skip_reference_cuda = True
     if args.impl == "reference":
         return run_reference(args)
     if args.gpus > 1 and "WORLD_SIZE" not in os.environ:

@@ -130,7 +130,7 @@ int iqlb_agents_step_host(iqlb_agents* h, const float* host_batch, float* host_l
 int iqlb_agents_step_host_pipelined(iqlb_agents* h, const float* host_batch, float* host_losses_prev, void* stream);
 
 /* Actor dropout (nn.Dropout(p) after every hidden ReLU of the policy MLP, iql.py:437-438, 459, 492; the adroit /
- * pen configs use p = 0.1).  fp32 path only.  The keep mask of element (row m, unit n) of hidden layer l at Adam
+ * pen configs use p = 0.1).  Both precisions.  The keep mask of element (row m, unit n) of hidden layer l at Adam
  * step t of agent a is word (n & 3) of Philox4x32-10(key = rng[a].seed, subsequence = (l+1) << 32 | (m*H + n) / 4,
  * counter = t) >= p * 2^32; kept activations are scaled by 1/(1-p).  The reference draws its masks from torch's CUDA
  * generator, which cannot be mirrored: parity is tested by injecting this mask into the oracle. */

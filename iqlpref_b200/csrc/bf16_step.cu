@@ -147,6 +147,9 @@ __device__ __forceinline__ void st_chunk(uint8_t* tile, int row, int col0, const
 // has been consumed, and b1 / W2 (fp32) take over the X region.  TMEM: layer-0 accumulator in
 // columns [0,256), layer-1 in [256,512).
 // ------------------------------------------------------------------------------------------------
+// kDrop: actor dropout (pen / adroit configs): the keep mask is applied to the actor stream's hidden activations
+// after the ReLU, and the stored bit masks become relu' AND keep, so the backward pass needs only the 1/(1-p) factor.
+template <bool kDrop>
 __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const float* __restrict__ params,
                                                           const float* __restrict__ target,
                                                           float* __restrict__ head_out) {
@@ -219,6 +222,8 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
   uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+  const bool drop = kDrop && s == 6 && P.drop_thresh != 0;
+  const uint64_t drop_seed = drop ? P.drop_rng[2 * agent] : 0ull, drop_step = drop ? (uint64_t)P.drop_it[agent] : 0ull;
   // epilogue 0: H1 = relu(acc + b0) -> bf16 tile (A operand of layer 1)
   for (int c0 = cbeg; c0 < cbeg + 128; c0 += 32) {
     float v[32];
@@ -232,6 +237,12 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
       const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
       v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
       m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
+    }
+    if (kDrop && drop) {
+      dropout32(v, drop_seed, drop_step, 0, brow, L.H, c0, P.drop_thresh, P.drop_scale);
+      m = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
     }
     if (m1) m1[c0 >> 5] = m;
 #pragma unroll
@@ -277,6 +288,12 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
       const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
       v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
       m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
+    }
+    if (kDrop && drop) {
+      dropout32(v, drop_seed, drop_step, 1, brow, L.H, c0, P.drop_thresh, P.drop_scale);
+      m = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
     }
     if (nout == 1) {
       float a = acc[0];
@@ -379,6 +396,9 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   const float* fnet = params + (int64_t)agent * L.Pstride + L.net_off(s);
   const int64_t at = (int64_t)agent * kTrain + t;
 
+  // actor dropout: both hidden layers' gradients pass through a kept-and-scaled mask (the stored bit masks already are
+  // relu' AND keep); exactly 1 when dropout is off
+  const float gscale = (t == 3 && P.drop_thresh != 0) ? P.drop_scale : 1.0f;
   const bool dbgd = P.dbg != nullptr && half == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
 #define IQLB_TSD(slot) do { if (dbgd) P.dbg[2560 + (slot)] = (unsigned long long)clock64(); } while (0)
   IQLB_TSD(0);
@@ -471,6 +491,10 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
         const uint32_t m = mword >> cc;
 #pragma unroll
         for (int j = 0; j < 8; ++j) g[j] = ((m >> j) & 1u) ? g[j] : 0.f;
+        if (gscale != 1.0f) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] *= gscale;
+        }
         st_chunk(smem + oA, row, c0, g);
       }
     }
@@ -517,6 +541,10 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     const uint32_t m = m1w[ib];
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
+    if (gscale != 1.0f) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= gscale;
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * chalf + 8 * q, v + 8 * q);
     fence_async_smem();
@@ -1053,7 +1081,9 @@ int bf16_create(iqlb_agents* h) {
   P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 8192 * 8);
   if (rc) return rc;
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
+  P.drop_thresh = 0; P.drop_scale = 1.0f; P.drop_rng = h->rng; P.drop_it = h->it;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)bwd_weight_smem(L.B)));
@@ -1113,6 +1143,15 @@ int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t strea
   return IQLB_OK;
 }
 
+// actor dropout parameters of this launch (iqlb_agents_set_actor_dropout)
+static void bf16_set_dropout(const iqlb_agents* h, BfParams& P) {
+  const bool on = h->drop_p > 0.f;
+  P.drop_thresh = on ? (uint32_t)((double)h->drop_p * 4294967296.0) : 0u;
+  P.drop_scale = on ? 1.0f / (1.0f - h->drop_p) : 1.0f;
+  P.drop_rng = h->rng;
+  P.drop_it = h->it;
+}
+
 int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream, bool packed) {
   Bf16State* st = (Bf16State*)h->bf16_state;
   IQLB_REQUIRE(st != nullptr, "not a bf16 handle");
@@ -1132,10 +1171,14 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
     pf.mark("pack_x");
   }
   static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
-  if (persist_env && bf16_fwd_persist_ok(P)) {
+  bf16_set_dropout(h, P);
+  if (persist_env && bf16_fwd_persist_ok(P) && P.drop_thresh == 0) {
     if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream, pdl_enabled(2) && !h->prof))) return rc;
+  } else if (P.drop_thresh != 0) {
+    bf16_fwd_kernel<true><<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
+    IQLB_LAUNCH_CHECK();
   } else {
-    bf16_fwd_kernel<<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
+    bf16_fwd_kernel<false><<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
     IQLB_LAUNCH_CHECK();
   }
   pf.mark("bf16_fwd");
@@ -1149,6 +1192,7 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   const int N = n;
   BfParams P = st->P;
   P.agent0 = a0;
+  bf16_set_dropout(h, P);
   P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
   // Measured on B200 (64 agents): 259.7 vs 259.0 us per step.  The round saved (6.9 instead of 4 + 4) is eaten by the
   // hand-off: a producer must wait for its bulk stores to COMPLETE (not just to leave shared memory) before it raises

@@ -1021,8 +1021,7 @@ extern "C" int iqlb_agents_act(iqlb_agents* h, const float* states, int64_t agen
 extern "C" int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   IQLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
-  IQLB_REQUIRE(h->desc.precision == 0 || p == 0.f, "actor dropout runs on the fp32 path (precision 0)");
-  h->drop_p = p;
+  h->drop_p = p;  // precision 1 reads it at every launch (bf16_step.cu bf16_set_dropout)
   return build_tasks(h);
 }
 

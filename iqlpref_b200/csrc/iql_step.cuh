@@ -110,6 +110,11 @@ struct BfParams {
   uint32_t *mask1, *mask2;  // [agent][train net][B][H/32]
   uint32_t* bwd_flags;      // [agent][4] data-gradient tiles published to the weight-gradient CTAs of a merged launch
   __nv_bfloat16* gradh;     // [agent][Pstride] gradients of the step in bf16 (what the reference's autocast GEMMs emit)
+  // actor dropout (iql.py:436-437; include/iqlb.h iqlb_agents_set_actor_dropout): 0 = off
+  uint32_t drop_thresh;   // keep an element when its Philox word >= drop_thresh (= p * 2^32)
+  float drop_scale;       // 1 / (1 - p); 1 when off
+  const uint64_t* drop_rng;  // rng[2 * agent] = seed (Philox key)
+  const int64_t* drop_it;    // it[agent] = Adam steps done so far (Philox counter)
   int opt_lpt;            // data-gradient kernel: actor tiles (the longest) first (IQLB_LPT)
   int dbg_z;              // timeline: blockIdx.z of the recording CTA
   int opt_issuers;        // MMA-issuing threads of the gradient kernels (IQLB_ISSUERS, 1 or 2)
@@ -133,6 +138,23 @@ __host__ __device__ inline int net_of_stream(int s) {  // index into the weight 
   }
 }
 __host__ __device__ inline int train_index(int s) { return s == 1 ? 0 : (s == 4 ? 1 : (s == 5 ? 2 : (s == 6 ? 3 : -1))); }
+
+#ifdef __CUDACC__
+// Actor dropout on 32 consecutive hidden units [c0, c0 + 32) of batch row `brow` of hidden layer `layer` (0 or 1):
+// element (m, n) is kept when word (n & 3) of Philox4x32-10(key = seed, subsequence = (layer + 1) << 32 | (m * H + n) / 4,
+// counter = step) is >= thresh, and kept values are scaled by 1 / (1 - p) - the mask documented in include/iqlb.h, the
+// same one the fp32 path draws (gemm_f32.cu) and tests/test_gpu_iql_step.py rebuilds with the numpy Philox.
+__device__ __forceinline__ void dropout32(float (&v)[32], uint64_t seed, uint64_t step, int layer, int brow, int H, int c0,
+                                          uint32_t thresh, float scale) {
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    uint32_t r[4];
+    philox4(seed, ((uint64_t)(layer + 1) << 32) | (uint64_t)(((int64_t)brow * H + c0 + 4 * j4) >> 2), step * 4ull, r);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[4 * j4 + k] = r[k] >= thresh ? v[4 * j4 + k] * scale : 0.f;
+  }
+}
+#endif
 
 // image location of parameter element e (offset inside one agent's packed parameters)
 __device__ __forceinline__ bool shadow_loc(const Layout& L, int KXB, int64_t e, int& net, int64_t& off) {

@@ -419,8 +419,6 @@ class BatchedIQL:
         # the module it is given)
         self._actor_lin_idx = (0, 3, 6) if actor_dropout is not None else (0, 2, 4)
         if self.actor_dropout > 0.0:
-            if self.precision != 0:
-                raise NotImplementedError("actor_dropout runs on precision='fp32' (the tcgen05 path has no dropout yet)")
             with _lib.device_ctx(self.device):
                 _lib.check(self.lib.iqlb_agents_set_actor_dropout(self._h, C.c_float(self.actor_dropout)),
                            "iqlb_agents_set_actor_dropout")
@@ -474,7 +472,7 @@ class BatchedIQL:
         for m in list(actor.modules()):
             if isinstance(m, nn.Dropout) and m.p > 0 and abs(m.p - self.actor_dropout) > 1e-12:
                 raise ValueError(f"the actor uses Dropout({m.p}) but the engine was built with actor_dropout="
-                                 f"{self.actor_dropout}: pass actor_dropout={m.p} (precision='fp32')")
+                                 f"{self.actor_dropout}: pass actor_dropout={m.p}")
         lin_idx = tuple(i for i, m in enumerate(actor.net.net) if isinstance(m, nn.Linear))
         if len(lin_idx) == 3:
             self._actor_lin_idx = lin_idx  # state_dict names of the actor's Linear layers (0/2/4, or 0/3/6 with Dropout)
@@ -808,9 +806,6 @@ class ImplicitQLearning:
         det = not hasattr(self.actor, "log_std")
         drop = max([m.p for m in self.actor.modules() if isinstance(m, nn.Dropout)] or [0.0])
         precision = self._precision
-        if drop > 0 and precision != "fp32":
-            warnings.warn("actor dropout runs on the fp32 path: precision='fp32' is used for this trainer", RuntimeWarning)
-            precision = "fp32"
         eng = BatchedIQL(s, a, 1, hidden_dim=h, batch_size=batch_size, deterministic=det, device=self.device,
                          precision=precision, hparams=[self._hp], actor_dropout=drop or None)
         eng.adopt(0, self.qf, self.vf, self.actor, bind=True)

@@ -323,6 +323,13 @@ int iqlb_selftest_umma(const void* a_img, int64_t a_bytes, const void* b_img, in
                        int32_t a_rows_total, int32_t a_off, int32_t b_mn, int32_t b_rows_total, int32_t b_off,
                        int32_t n, int32_t ksteps, float* d_out, void* stream);
 
+/* Diagnostic: one fp32 GEMM through the library's dispatcher.  kn_layout 0: C = act(A W^T + bias) (+ residual), W [n][k]
+ * (nn.Linear); 1: C = act(scale * A W + bias), W [k][n] (RewardMLP's scaled Linear).  allow_tc 1 lets shapes of at least
+ * 128 x 64 x 16 run on the tensor cores in split-bf16 arithmetic (csrc/gemm_tc.cu; ~1e-5 relative), 0 forces fp32 FFMA. */
+int iqlb_selftest_gemm(int32_t kn_layout, const float* a, int32_t lda, const float* w, int32_t ldw, const float* bias,
+                       const float* residual, float* c, int32_t ldc, int32_t m, int32_t n, int32_t k, int32_t activation,
+                       float scale, int32_t allow_tc, void* stream);
+
 /* Tensor-pipe issue-rate probe: `count` back-to-back 128 x n x 16 bf16 MMAs into one accumulator, A from shared
  * memory (a_from_tmem = 0) or from tensor memory (1).  clocks_out (device, 2 x uint64): SM clocks spent issuing,
  * and from the first issue to the completion of the last MMA. */

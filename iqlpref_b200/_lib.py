@@ -66,6 +66,8 @@ _SIGNATURES = {
     "iqlb_pt_forward": ([C.POINTER(PTDesc), _P, _P, _P, _P, _P, C.c_int64, _P, _P], C.c_int),
     "iqlb_selftest_umma": ([_P, C.c_int64, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, _P, _P], C.c_int),
+    "iqlb_selftest_gemm": ([C.c_int32, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                            C.c_int32, C.c_float, C.c_int32, _P], C.c_int),
     "iqlb_selftest_mma_rate": ([C.c_int32, C.c_int32, C.c_int32, _P, _P], C.c_int),
     "iqlb_reward_range": ([_P, _P, C.c_int64, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_modify_reward": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P], C.c_int),

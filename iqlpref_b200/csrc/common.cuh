@@ -71,6 +71,25 @@ __device__ __forceinline__ float act_grad(int act, float z) {
 }
 #endif
 
+#ifdef __CUDACC__
+// GEMM epilogues evaluate an activation per output element, 32-64 elements per thread, fully unrolled: with the switch
+// inlined at every element (cosf / sinf / tanhf bring their slow paths along) a kernel grows to 20-80 thousand
+// instructions and every element's path through it misses the instruction cache - the tensor-core GEMM spent 60 of its 75
+// thousand clocks per tile there.  The two activations the hot paths use stay inline; the rest is ONE out-of-line copy.
+static __device__ __noinline__ float apply_act_call(int act, float x) { return apply_act(act, x); }
+static __device__ __noinline__ float act_grad_call(int act, float z) { return act_grad(act, z); }
+__device__ __forceinline__ float apply_act_lean(int act, float x) {
+  if (act == IQLB_ACT_RELU) return x > 0.f ? x : 0.f;
+  if (act == IQLB_ACT_LINEAR) return x;
+  return apply_act_call(act, x);
+}
+__device__ __forceinline__ float act_grad_lean(int act, float z) {
+  if (act == IQLB_ACT_RELU) return z > 0.f ? 1.f : 0.f;
+  if (act == IQLB_ACT_LINEAR) return 1.f;
+  return act_grad_call(act, z);
+}
+#endif
+
 // ---- Philox4x32-10 exactly as cuRAND's curand_Philox4x32_10 (curand_philox4x32_x.h) ----------
 __host__ __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
 #ifdef __CUDA_ARCH__

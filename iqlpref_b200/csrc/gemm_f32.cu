@@ -137,15 +137,15 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
             for (int j = 0; j < 4; ++j) v[j] = fmaf(t.scale, v[j], b[j]);
             if (t.pre != nullptr) *reinterpret_cast<float4*>(t.pre + o) = make_float4(v[0], v[1], v[2], v[3]);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = apply_act(t.act, v[j]);
+            for (int j = 0; j < 4; ++j) v[j] = apply_act_lean(t.act, v[j]);
           } else if (t.pre != nullptr) {  // data gradient through the activation below: scale * acc * act'(z)
             const float4 z4 = *reinterpret_cast<const float4*>(t.pre + o);
             const float z[4] = {z4.x, z4.y, z4.z, z4.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = t.scale * v[j] * act_grad(t.act, z[j]);
+            for (int j = 0; j < 4; ++j) v[j] = t.scale * v[j] * act_grad_lean(t.act, z[j]);
           } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = apply_act(t.act, v[j] + b[j]);
+            for (int j = 0; j < 4; ++j) v[j] = apply_act_lean(t.act, v[j] + b[j]);
             if (t.mask != nullptr) {
               const float4 r4 = *reinterpret_cast<const float4*>(t.mask + o);
               v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
@@ -185,11 +185,11 @@ __device__ __forceinline__ void gemm_body(const GemmTask& t, int tile) {
       } else if (MODE == GEMM_FWD_KN) {
         v = fmaf(t.scale, v, __ldg(t.bias + n));
         if (t.pre != nullptr) t.pre[(int64_t)m * t.ldc + n] = v;
-        v = apply_act(t.act, v);
+        v = apply_act_lean(t.act, v);
       } else if (MODE == GEMM_LINEAR && t.pre != nullptr) {  // scale * (A W^T) * act'(pre): back through an activation
-        v = t.scale * v * act_grad(t.act, t.pre[(int64_t)m * t.ldc + n]);
+        v = t.scale * v * act_grad_lean(t.act, t.pre[(int64_t)m * t.ldc + n]);
       } else if (MODE == GEMM_LINEAR) {  // nn.Linear: act(A W^T + bias) (+ residual, carried in t.mask)
-        v = apply_act(t.act, v + (t.bias ? __ldg(t.bias + n) : 0.f));
+        v = apply_act_lean(t.act, v + (t.bias ? __ldg(t.bias + n) : 0.f));
         if (t.mask != nullptr) v += t.mask[(int64_t)m * t.ldc + n];
       }
       t.C[(int64_t)m * t.ldc + n] = v;
@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(256, 2) single_gemm_kernel(const GemmTask t) {
 // One GEMM with the task passed by value (no device-side task array).
 int launch_gemm(GemmMode mode, const GemmTask& t, cudaStream_t stream) {
   if (t.M <= 0 || t.N <= 0) return IQLB_OK;
+  if (gemm_tc_eligible(mode, t)) return launch_gemm_tc(mode, t, stream);
   const int tiles_m = (t.M + BM - 1) / BM;
   const bool narrow = t.N <= 32;
   const unsigned grid = (unsigned)(tiles_m * (narrow ? (t.N + 31) / 32 : (t.N + 127) / 128));

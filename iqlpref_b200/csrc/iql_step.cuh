@@ -81,6 +81,9 @@ struct GemmTask {
   const int64_t* drop_it;    // &it[agent]
   float* pre;                // FWD_KN (nullable): pre-activation scale * acc + bias, same shape/ld as C (kept for the backward pass);
                              // LINEAR (nullable): read instead - C = scale * acc * act'(pre) (data gradient through an activation)
+  unsigned long long* dbg;   // gemm_tc.cu: CTA 0 records clock64 stamps here (diagnostics; nullptr otherwise)
+  int allow_tc;              // 1: launch_gemm may run this task on the tensor cores in split-bf16 arithmetic (gemm_tc.cu,
+                             // ~1e-5 relative) when the shape is worth a 128 x 128 tile; 0: fp32 FFMA always
 };
 
 enum GemmMode { GEMM_FWD = 0, GEMM_BWD_DATA = 1, GEMM_BWD_WEIGHT = 2, GEMM_FWD_KN = 3, GEMM_LINEAR = 4 };
@@ -90,6 +93,8 @@ struct StepScalars {  // per agent, written by the loss kernel, read by Adam
 };
 
 int launch_gemm(GemmMode mode, const GemmTask& t, cudaStream_t stream);
+bool gemm_tc_eligible(GemmMode mode, const GemmTask& t);
+int launch_gemm_tc(GemmMode mode, const GemmTask& t, cudaStream_t stream);
 int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
                         cudaStream_t stream);
 

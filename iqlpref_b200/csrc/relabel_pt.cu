@@ -74,55 +74,81 @@ __global__ void __launch_bounds__(256) pt_embed_kernel(PtOff P, const float* __r
                                                        const int32_t* __restrict__ win_start, const int32_t* __restrict__ seq_len,
                                                        const int32_t* __restrict__ timesteps, const float* __restrict__ attn_mask,
                                                        int64_t win0, int n_win, float* __restrict__ x, float* __restrict__ maskbuf) {
-  extern __shared__ float sh[];  // per warp: S + A floats
+  // Persistent CTAs; the two embedding matrices live in shared memory TRANSPOSED ([in][E]), so lane `l` reads output
+  // feature l + 32 c of input i at consecutive addresses (the row-major weights read through __ldg cost 32 cache lines
+  // per warp instruction: 3.5 ms of an 8.6 ms relabel of 4096 windows).
+  extern __shared__ float sh[];  // WsT [S][E] | WaT [A][E] | per warp: S + A floats
+  float* WsT = sh;
+  float* WaT = WsT + (size_t)P.S * P.E;
+  float* stage = WaT + (size_t)P.A * P.E;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t tp = (int64_t)blockIdx.x * 8 + warp;  // (window, position) index inside the chunk
-  if (tp >= (int64_t)n_win * P.T) return;
-  const int wl = (int)(tp / P.T), t = (int)(tp % P.T);
-  const int64_t wg = win0 + wl;
-  const float* sp = nullptr;
-  const float* ap = nullptr;
-  int ts = 0;
-  float m = 0.f;
-  if (gather) {
-    const int sl = seq_len[wg], pad = P.T - sl;
-    if (t >= pad) {
-      const int64_t row = (int64_t)win_start[wg] + (t - pad);
-      sp = obs + row * P.S; ap = act + row * P.A; ts = t - pad; m = 1.f;
-    }
-  } else {
-    sp = obs + (wg * P.T + t) * P.S; ap = act + (wg * P.T + t) * P.A;
-    ts = timesteps[wg * P.T + t]; m = attn_mask[wg * P.T + t];
+  for (int i = threadIdx.x; i < P.S * P.E; i += blockDim.x) {
+    const int e = i / P.S, k = i - e * P.S;  // read row-major [E][S] coalesced, write transposed
+    WsT[(size_t)k * P.E + e] = __ldg(w + P.sw + i);
   }
-  float* ss = sh + warp * (P.S + P.A);
+  for (int i = threadIdx.x; i < P.A * P.E; i += blockDim.x) {
+    const int e = i / P.A, k = i - e * P.A;
+    WaT[(size_t)k * P.E + e] = __ldg(w + P.aw + i);
+  }
+  __syncthreads();
+  float* ss = stage + warp * (P.S + P.A);
   float* sa = ss + P.S;
-  for (int i = lane; i < P.S; i += 32) ss[i] = sp ? sp[i] : 0.f;
-  for (int i = lane; i < P.A; i += 32) sa[i] = ap ? ap[i] : 0.f;
-  __syncwarp();
   const int per = P.E / 32;
-  const float* te = w + P.temb + (int64_t)ts * P.E;
-  float es[kPtMaxPerLane], ea[kPtMaxPerLane];
-#pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c) {
-    if (c < per) {
-      const int e = lane + 32 * c;
-      const float* ws = w + P.sw + (int64_t)e * P.S;
-      const float* wa = w + P.aw + (int64_t)e * P.A;
-      float a0 = 0.f, a1 = 0.f;
-      for (int i = 0; i < P.S; ++i) a0 = fmaf(ss[i], __ldg(ws + i), a0);
-      for (int i = 0; i < P.A; ++i) a1 = fmaf(sa[i], __ldg(wa + i), a1);
-      const float tv = __ldg(te + e);
-      es[c] = a0 + __ldg(w + P.sb + e) + tv;
-      ea[c] = a1 + __ldg(w + P.ab + e) + tv;
+  const int64_t n_pairs = (int64_t)n_win * P.T;
+  for (int64_t tp = (int64_t)blockIdx.x * 8 + warp; tp < n_pairs; tp += (int64_t)gridDim.x * 8) {
+    const int wl = (int)(tp / P.T), t = (int)(tp % P.T);
+    const int64_t wg = win0 + wl;
+    const float* sp = nullptr;
+    const float* ap = nullptr;
+    int ts = 0;
+    float m = 0.f;
+    if (gather) {
+      const int sl = seq_len[wg], pad = P.T - sl;
+      if (t >= pad) {
+        const int64_t row = (int64_t)win_start[wg] + (t - pad);
+        sp = obs + row * P.S; ap = act + row * P.A; ts = t - pad; m = 1.f;
+      }
+    } else {
+      sp = obs + (wg * P.T + t) * P.S; ap = act + (wg * P.T + t) * P.A;
+      ts = timesteps[wg * P.T + t]; m = attn_mask[wg * P.T + t];
     }
-  }
-  warp_layer_norm(es, per, P.E, P.eps, w + P.slg, w + P.slb, lane);
-  warp_layer_norm(ea, per, P.E, P.eps, w + P.slg, w + P.slb, lane);
-  float* xs = x + ((int64_t)wl * 2 * P.T + 2 * t) * P.E;
+    __syncwarp();
+    for (int i = lane; i < P.S; i += 32) ss[i] = sp ? sp[i] : 0.f;
+    for (int i = lane; i < P.A; i += 32) sa[i] = ap ? ap[i] : 0.f;
+    __syncwarp();
+    const float* te = w + P.temb + (int64_t)ts * P.E;
+    float es[kPtMaxPerLane], ea[kPtMaxPerLane];
 #pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c)
-    if (c < per) { xs[lane + 32 * c] = es[c]; xs[P.E + lane + 32 * c] = ea[c]; }
-  if (lane == 0) maskbuf[(int64_t)wl * P.T + t] = m;
+    for (int c = 0; c < kPtMaxPerLane; ++c) { es[c] = 0.f; ea[c] = 0.f; }
+    for (int i = 0; i < P.S; ++i) {
+      const float sv = ss[i];
+      const float* wr = WsT + (size_t)i * P.E + lane;
+#pragma unroll
+      for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) es[c] = fmaf(sv, wr[32 * c], es[c]);
+    }
+    for (int i = 0; i < P.A; ++i) {
+      const float av = sa[i];
+      const float* wr = WaT + (size_t)i * P.E + lane;
+#pragma unroll
+      for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) ea[c] = fmaf(av, wr[32 * c], ea[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < kPtMaxPerLane; ++c) {
+      if (c < per) {
+        const int e = lane + 32 * c;
+        const float tv = __ldg(te + e);
+        es[c] = es[c] + __ldg(w + P.sb + e) + tv;
+        ea[c] = ea[c] + __ldg(w + P.ab + e) + tv;
+      }
+    }
+    warp_layer_norm(es, per, P.E, P.eps, w + P.slg, w + P.slb, lane);
+    warp_layer_norm(ea, per, P.E, P.eps, w + P.slg, w + P.slb, lane);
+    float* xs = x + ((int64_t)wl * 2 * P.T + 2 * t) * P.E;
+#pragma unroll
+    for (int c = 0; c < kPtMaxPerLane; ++c)
+      if (c < per) { xs[lane + 32 * c] = es[c]; xs[P.E + lane + 32 * c] = ea[c]; }
+    if (lane == 0) maskbuf[(int64_t)wl * P.T + t] = m;
+  }
 }
 
 // y[r] = LN(x[r * in_stride .. + E))  (rows may be strided: the last token of every window)
@@ -307,6 +333,7 @@ static int pt_linear(const float* A, int64_t lda, const float* W, const float* b
   GemmTask t{};
   t.A = A; t.lda = (int)lda; t.Bm = W; t.ldb = K; t.bias = bias; t.C = C; t.ldc = N; t.mask = residual;
   t.M = M; t.N = N; t.K = K; t.act = relu ? IQLB_ACT_RELU : IQLB_ACT_LINEAR; t.scale = 1.f;
+  t.allow_tc = 1;  // split-bf16 on the tensor cores for the token-level GEMMs (~1e-5 relative; the relabel bar is 1e-3)
   return launch_gemm(GEMM_LINEAR, t, st);
 }
 
@@ -339,29 +366,52 @@ static int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float
   if (chunk > n) chunk = n;
   const int64_t Mt = chunk * T2;
   float *x = nullptr, *hbuf = nullptr, *big = nullptr, *maskbuf = nullptr, *xl = nullptr, *hl = nullptr, *ql = nullptr, *midl = nullptr;
+  // stream-ordered scratch from the device's default memory pool: after the first call the pool keeps the blocks, so a
+  // relabel call neither synchronises nor pays cudaMalloc (the release threshold is raised once)
+  static bool pool_set = false;
+  if (!pool_set) {
+    int dev = 0;
+    cudaMemPool_t pool = nullptr;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      uint64_t keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    pool_set = true;
+  }
   auto cleanup = [&]() {
-    cudaStreamSynchronize(st);
-    cudaFree(x); cudaFree(hbuf); cudaFree(big); cudaFree(maskbuf); cudaFree(xl); cudaFree(hl); cudaFree(ql); cudaFree(midl);
+    float* bufs[8] = {x, hbuf, big, maskbuf, xl, hl, ql, midl};
+    for (float* b : bufs) if (b) cudaFreeAsync(b, st);
   };
 #define PT_CUDA(e) do { cudaError_t e__ = (e); if (e__ != cudaSuccess) { snprintf(g_err, sizeof(g_err), "%s: %s", #e, cudaGetErrorString(e__)); cleanup(); return IQLB_ERR_CUDA; } } while (0)
 #define PT_RC(e) do { int r__ = (e); if (r__) { cleanup(); return r__; } } while (0)
-  PT_CUDA(cudaMalloc((void**)&x, (size_t)Mt * E * sizeof(float)));
-  PT_CUDA(cudaMalloc((void**)&hbuf, (size_t)Mt * E * sizeof(float)));
-  PT_CUDA(cudaMalloc((void**)&big, (size_t)Mt * big_cols * sizeof(float)));
-  PT_CUDA(cudaMalloc((void**)&maskbuf, (size_t)chunk * P.T * sizeof(float)));
+  PT_CUDA(cudaMallocAsync((void**)&x, (size_t)Mt * E * sizeof(float), st));
+  PT_CUDA(cudaMallocAsync((void**)&hbuf, (size_t)Mt * E * sizeof(float), st));
+  PT_CUDA(cudaMallocAsync((void**)&big, (size_t)Mt * big_cols * sizeof(float), st));
+  PT_CUDA(cudaMallocAsync((void**)&maskbuf, (size_t)chunk * P.T * sizeof(float), st));
   if (!all_tokens) {
-    PT_CUDA(cudaMalloc((void**)&xl, (size_t)chunk * E * sizeof(float)));
-    PT_CUDA(cudaMalloc((void**)&hl, (size_t)chunk * E * sizeof(float)));
-    PT_CUDA(cudaMalloc((void**)&ql, (size_t)chunk * E * sizeof(float)));
-    PT_CUDA(cudaMalloc((void**)&midl, (size_t)chunk * I * sizeof(float)));
+    PT_CUDA(cudaMallocAsync((void**)&xl, (size_t)chunk * E * sizeof(float), st));
+    PT_CUDA(cudaMallocAsync((void**)&hl, (size_t)chunk * E * sizeof(float), st));
+    PT_CUDA(cudaMallocAsync((void**)&ql, (size_t)chunk * E * sizeof(float), st));
+    PT_CUDA(cudaMallocAsync((void**)&midl, (size_t)chunk * I * sizeof(float), st));
   }
+  const size_t embed_smem = ((size_t)(P.S + P.A) * E + 8 * (P.S + P.A)) * sizeof(float);
+  int n_sm = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+  }
+  PT_CUDA(cudaFuncSetAttribute(pt_embed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)embed_smem));
   const size_t attn_smem = ((size_t)2 * T2 * (dh + 1) + 8 * dh + 8 * T2) * sizeof(float);
   PT_CUDA(cudaFuncSetAttribute(pt_attn_full_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem));
   for (int64_t w0 = 0; w0 < n; w0 += chunk) {
     const int nw = (int)(n - w0 < chunk ? n - w0 : chunk);
     const int64_t mt = (int64_t)nw * T2;
-    pt_embed_kernel<<<(unsigned)(((int64_t)nw * P.T + 7) / 8), 256, 8 * (P.S + P.A) * sizeof(float), st>>>(
-        P, w, gather, obs, act, win_start, seq_len, timesteps, attn_mask, w0, nw, x, maskbuf);
+    {
+      const int64_t want = ((int64_t)nw * P.T + 7) / 8;
+      const unsigned grid = (unsigned)(want < 4 * n_sm ? want : 4 * n_sm);  // persistent: the weights are staged once per CTA
+      pt_embed_kernel<<<grid, 256, embed_smem, st>>>(P, w, gather, obs, act, win_start, seq_len, timesteps, attn_mask, w0,
+                                                     nw, x, maskbuf);
+    }
     PT_CUDA(cudaGetLastError());
     for (int l = 0; l < P.L; ++l) {
       const float* lw = w + P.layer0 + (int64_t)l * P.layer_stride;

@@ -17,7 +17,7 @@ import yaml
 
 from . import _lib
 from .reward_models.pref_transformer import PT as RewardPT
-from .reward_models.pref_transformer import pack_pt_weights, pt_desc_from_model
+from .reward_models.pref_transformer import packed_pt_weights, pt_desc_from_model
 from .reward_models.q_mlp import MLP as RewardMLP
 from .reward_models.q_mlp import member_weights
 
@@ -392,7 +392,7 @@ def pt_predict(r_model, obs_all: np.ndarray, act_all: np.ndarray, win_start: np.
     """value[:, 0, -1, 0] of the preference transformer for every window (CUDA tensor [n])."""
     dev = _cuda_device(device if device is not None else next(r_model.parameters()).device)
     desc = pt_desc_from_model(r_model, query_length)
-    weights = pack_pt_weights(r_model, desc).to(dev)
+    weights = packed_pt_weights(r_model, desc, dev)
     obs = torch.as_tensor(obs_all, dtype=torch.float32).to(dev).contiguous()
     act = torch.as_tensor(act_all, dtype=torch.float32).to(dev).contiguous()
     # identical (start, length) windows give identical rewards: evaluate each distinct window once.

@@ -75,7 +75,7 @@ class PT(nn.Module):
             raise RuntimeError("PT.forward runs on the GPU only (no CPU path)")
         b, t, _ = states.shape
         desc = pt_desc_from_model(self, t)
-        weights = pack_pt_weights(self, desc).to(dev)
+        weights = packed_pt_weights(self, desc, dev)
         st = states.to(torch.float32).contiguous()
         ac = actions.to(torch.float32).contiguous()
         ts = timesteps.to(torch.int32).contiguous()
@@ -99,6 +99,21 @@ def pt_desc_from_model(model, query_len: int) -> "_lib.PTDesc":
                        sd["gpt.layers.0.mlp.in_linear.weight"].shape[0], layers,
                        (sd["pref_linear.weight"].shape[0] - 1) // 2, sd["timestep_embed.weight"].shape[0], query_len,
                        float(model.stacked_layer_norm.eps))
+
+
+def packed_pt_weights(model, desc, device) -> torch.Tensor:
+    """`pack_pt_weights(model, desc)` on `device`, cached on the module until one of its parameters changes (the relabel
+    calls the model thousands of times with the same weights; packing goes through the host)."""
+    key = (str(device), desc.query_len) + tuple((p.data_ptr(), p._version) for p in model.parameters())
+    cached = getattr(model, "_iqlb_packed", None)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    w = pack_pt_weights(model, desc).to(device)
+    try:
+        object.__setattr__(model, "_iqlb_packed", (key, w))
+    except Exception:  # noqa: BLE001
+        pass
+    return w
 
 
 def pack_pt_weights(model, desc) -> torch.Tensor:

@@ -301,6 +301,9 @@ typedef struct iqlb_mr_trainer iqlb_mr_trainer;
 int iqlb_mr_create(int32_t d_in, const int32_t* host_widths, int32_t depth, int32_t activation,
                    int32_t pool_mean, int64_t max_rows /* 2*B*T */, iqlb_mr_trainer** out);
 int iqlb_mr_destroy(iqlb_mr_trainer* h);
+/* Arithmetic of the step's GEMMs (forward, data gradients, weight-gradient partials): 0 = fp32 FFMA (default), 1 = the
+ * tensor cores in split-bf16 (csrc/gemm_tc.cu: x_hi*w_hi + x_lo*w_hi + x_hi*w_lo, fp32 accumulation, ~1e-5 relative). */
+int iqlb_mr_set_precision(iqlb_mr_trainer* h, int32_t precision);
 int iqlb_mr_param_count(const iqlb_mr_trainer* h, int64_t* n_params);
 int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
                        const float* states1, const float* actions1, const float* mask1,

@@ -75,6 +75,7 @@ _SIGNATURES = {
     "iqlb_normalize_states": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_mr_create": ([C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(_P)], C.c_int),
     "iqlb_mr_destroy": ([_P], C.c_int),
+    "iqlb_mr_set_precision": ([_P, C.c_int32], C.c_int),
     "iqlb_mr_param_count": ([_P, C.POINTER(C.c_int64)], C.c_int),
     "iqlb_mr_train_step": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64, _P, _P, _P], C.c_int),

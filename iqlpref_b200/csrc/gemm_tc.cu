@@ -8,6 +8,8 @@
 //   LINEAR   C[m,n] = act(sum_k A[m,k] * W[n,k] + bias[n]) (+ residual)      W stored [N][K] (nn.Linear)
 //            with t.pre:  C[m,n] = scale * acc * act'(pre[m,n])               (data gradient through an activation)
 //   FWD_KN   C[m,n] = act(scale * sum_k A[m,k] * W[k,n] + bias[n])            W stored [K][N]; pre-activation kept in t.pre
+//   BWD_WEIGHT C[m,n] = sum_k A[k,m] * X[k,n]                                 dW = (layer input)^T dZ over the rows k
+//            (both operands read MN-major; the caller splits the rows over tasks and sums the partial tiles)
 //
 // One CTA = one 128 x 128 output tile.  K is walked in blocks of 64: all 256 threads load the fp32 tiles (128-bit loads,
 // the next block's loads are issued before the current block is converted), split them into hi / lo bf16 and write the
@@ -54,19 +56,21 @@ __device__ __forceinline__ void load8(const float* __restrict__ p, int valid, bo
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
+__device__ __forceinline__ void gemm_tc_body(const GemmTask& t, const int tile) {
   using namespace gtc;
-  constexpr bool B_KN = (MODE == GEMM_FWD_KN);
+  constexpr bool B_KN = (MODE == GEMM_FWD_KN || MODE == GEMM_BWD_WEIGHT);
+  constexpr bool A_MN = (MODE == GEMM_BWD_WEIGHT);
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar_empty = sbase + oCtrl, bar_done = bar_empty + 8 * kStages;
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 8 * kStages + 8);
   const int tiles_n = (t.N + BN - 1) / BN;
-  const int tm = blockIdx.x / tiles_n, tn = blockIdx.x % tiles_n;
+  if (tile >= ((t.M + BM - 1) / BM) * tiles_n) return;  // grouped launches size the grid for the largest task
+  const int tm = tile / tiles_n, tn = tile % tiles_n;
   const int m0 = tm * BM, n0 = tn * BN;
   const int nkb = (t.K + BK - 1) / BK;
-  const bool dbg = t.dbg != nullptr && blockIdx.x == gridDim.x / 2 && tid == 64;
+  const bool dbg = t.dbg != nullptr && tile == (int)gridDim.x / 2 && tid == 64;
 #define GTC_TS(i) do { if (dbg) t.dbg[(i)] = (unsigned long long)clock64(); } while (0)
   GTC_TS(0);
 
@@ -91,11 +95,16 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int q = tid + 256 * i;
-      {  // A[m][k], k contiguous: row r, chunk c
+      if (!A_MN) {  // A[m][k], k contiguous: row r, chunk c
         const int r = q >> 3, c = q & 7;
         const int gm = m0 + r, gk = k0 + 8 * c;
         const int valid = gm < t.M ? min(8, t.K - gk) : 0;
         load8(t.A + (int64_t)gm * t.lda + gk, valid, fastA, ra[i]);
+      } else {      // A[k][m], m contiguous
+        const int kk = q >> 4, cm = q & 15;
+        const int gk = k0 + kk, gm = m0 + 8 * cm;
+        const int valid = gk < t.K ? min(8, t.M - gm) : 0;
+        load8(t.A + (int64_t)gk * t.lda + gm, valid, fastA, ra[i]);
       }
       if (!B_KN) {  // W[n][k], k contiguous
         const int r = q >> 3, c = q & 7;
@@ -117,8 +126,14 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
       const int q = tid + 256 * i;
       uint4 hi, lo;
       {
-        const int r = q >> 3, c = q & 7;
-        const uint32_t off = (uint32_t)r * 128u + (uint32_t)((c ^ (r & 7)) << 4);
+        uint32_t off;
+        if (!A_MN) {
+          const int r = q >> 3, c = q & 7;
+          off = (uint32_t)r * 128u + (uint32_t)((c ^ (r & 7)) << 4);
+        } else {
+          const int kk = q >> 4, cm = q & 15;
+          off = (uint32_t)(cm >> 3) * (64u * 128u) + (uint32_t)kk * 128u + (uint32_t)(((cm & 7) ^ (kk & 7)) << 4);
+        }
         split8(ra[i], hi, lo);
         *reinterpret_cast<uint4*>(st + off) = hi;
         *reinterpret_cast<uint4*>(st + kImg + off) = lo;
@@ -152,7 +167,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
     if (tid == 0) {
       tc_fence_after();
       const uint32_t st = sbase + (uint32_t)slot * kStageBytes;
-      const Operand a_hi = operand_k_major(st, 128, 0), a_lo = operand_k_major(st + kImg, 128, 0);
+      const Operand a_hi = A_MN ? operand_mn_major(st, 64, 0, 0) : operand_k_major(st, 128, 0);
+      const Operand a_lo = A_MN ? operand_mn_major(st + kImg, 64, 0, 0) : operand_k_major(st + kImg, 128, 0);
       const Operand b_hi = B_KN ? operand_mn_major(st + 2 * kImg, 64, 0, 0) : operand_k_major(st + 2 * kImg, 128, 0);
       const Operand b_lo = B_KN ? operand_mn_major(st + 3 * kImg, 64, 0, 0) : operand_k_major(st + 3 * kImg, 128, 0);
       const int ks = min(BK, t.K - kb * BK);
@@ -176,7 +192,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
   //     and the residual / pre-activation reads and the output stores are 512 contiguous bytes per warp instruction.
   //     (One thread per output ROW wrote 32 scattered 16-byte pieces per instruction: 11 us of a 14 us tile.)
   constexpr int kLd = 132;
-  float* tile = reinterpret_cast<float*>(smem);
+  float* ctile = reinterpret_cast<float*>(smem);
   {
     const int quarter = warp & 3, chalf = warp >> 2;
     const int r = quarter * 32 + lane;
@@ -189,7 +205,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
       tmem_ld_wait();
 #pragma unroll
       for (int j4 = 0; j4 < 8; ++j4)
-        *reinterpret_cast<float4*>(tile + r * kLd + c0 + 4 * j4) = make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+        *reinterpret_cast<float4*>(ctile + r * kLd + c0 + 4 * j4) = make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
     }
   }
   tc_fence_before();
@@ -199,12 +215,12 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
     const bool cvec = (t.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(t.C) & 15) == 0) && nb + 4 <= t.N;
     float bias4[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) bias4[j] = (t.bias != nullptr && nb + j < t.N) ? __ldg(t.bias + nb + j) : 0.f;
+    for (int j = 0; j < 4; ++j) bias4[j] = (MODE != GEMM_BWD_WEIGHT && t.bias != nullptr && nb + j < t.N) ? __ldg(t.bias + nb + j) : 0.f;
     const int act = t.act;
     for (int r = warp; r < BM; r += 8) {
       const int m = m0 + r;
       if (m >= t.M) break;
-      const float4 a4 = *reinterpret_cast<const float4*>(tile + r * kLd + 4 * lane);
+      const float4 a4 = *reinterpret_cast<const float4*>(ctile + r * kLd + 4 * lane);
       float x[4] = {a4.x, a4.y, a4.z, a4.w};
       const int64_t o = (int64_t)m * t.ldc + nb;
       float side[4] = {0.f, 0.f, 0.f, 0.f};  // residual (LINEAR) or pre-activation (LINEAR with t.pre)
@@ -218,7 +234,9 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (MODE == GEMM_FWD_KN) {
+        if (MODE == GEMM_BWD_WEIGHT) {
+          // plain partial sum
+        } else if (MODE == GEMM_FWD_KN) {
           x[j] = fmaf(t.scale, x[j], bias4[j]);
         } else if (t.pre != nullptr) {
           x[j] = t.scale * x[j] * act_grad_lean(act, side[j]);
@@ -251,6 +269,20 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
   GTC_TS(17);
 }
 
+template <int MODE>
+__global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const GemmTask t) {
+  gemm_tc_body<MODE>(t, (int)blockIdx.x);
+}
+
+// one launch over a device-resident task array (blockIdx.y = task)
+template <int MODE>
+__global__ void __launch_bounds__(256, 1) gemm_tc_grouped_kernel(const GemmTask* __restrict__ tasks) {
+  __shared__ GemmTask t;
+  if (threadIdx.x == 0) t = tasks[blockIdx.y];
+  __syncthreads();
+  gemm_tc_body<MODE>(t, (int)blockIdx.x);
+}
+
 // Shapes worth a 128 x 128 tensor-core tile; anything else stays on the FFMA kernel.
 bool gemm_tc_eligible(GemmMode mode, const GemmTask& t) {
   static const bool off = getenv("IQLB_GEMM_TC") && atoi(getenv("IQLB_GEMM_TC")) == 0;
@@ -270,6 +302,20 @@ int launch_gemm_tc(GemmMode mode, const GemmTask& t, cudaStream_t stream) {
   const unsigned grid = (unsigned)(((t.M + gtc::BM - 1) / gtc::BM) * ((t.N + gtc::BN - 1) / gtc::BN));
   if (mode == GEMM_LINEAR) gemm_tc_kernel<GEMM_LINEAR><<<grid, 256, gtc::kSmem, stream>>>(t);
   else gemm_tc_kernel<GEMM_FWD_KN><<<grid, 256, gtc::kSmem, stream>>>(t);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+// Weight-gradient partials of the reward-model trainers: tasks[i] is one row chunk, every task has the same M x N.
+int launch_grouped_gemm_tc_bwd_weight(const GemmTask* d_tasks, int n_tasks, int M, int N, cudaStream_t stream) {
+  static bool attr = false;
+  if (!attr) {
+    IQLB_CUDA(cudaFuncSetAttribute(gemm_tc_grouped_kernel<GEMM_BWD_WEIGHT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)gtc::kSmem));
+    attr = true;
+  }
+  const dim3 grid((unsigned)(((M + gtc::BM - 1) / gtc::BM) * ((N + gtc::BN - 1) / gtc::BN)), (unsigned)n_tasks);
+  gemm_tc_grouped_kernel<GEMM_BWD_WEIGHT><<<grid, 256, gtc::kSmem, stream>>>(d_tasks);
   IQLB_LAUNCH_CHECK();
   return IQLB_OK;
 }

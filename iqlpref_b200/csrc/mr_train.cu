@@ -215,6 +215,7 @@ struct iqlb_mr_trainer {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;  // IQLB_MR_OVERLAP=0: everything on the caller's stream
+  int tc = 0;           // iqlb_mr_set_precision: 1 = the seven GEMMs of a step run on the tensor cores in split-bf16
 };
 
 static void mr_free(iqlb_mr_trainer* h) {
@@ -295,6 +296,13 @@ extern "C" int iqlb_mr_destroy(iqlb_mr_trainer* h) {
   return IQLB_OK;
 }
 
+extern "C" int iqlb_mr_set_precision(iqlb_mr_trainer* h, int32_t precision) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  IQLB_REQUIRE(precision == 0 || precision == 1, "precision must be 0 (fp32 FFMA) or 1 (split-bf16 tcgen05)");
+  h->tc = precision;
+  return IQLB_OK;
+}
+
 extern "C" int iqlb_mr_param_count(const iqlb_mr_trainer* h, int64_t* n_params) {
   IQLB_REQUIRE(h != nullptr && n_params != nullptr, "null argument");
   *n_params = h->pm;
@@ -323,6 +331,7 @@ static int mr_forward(iqlb_mr_trainer* h, const float* params, const float* s1, 
     t.M = (int)M; t.N = w; t.K = prev;
     t.scale = 1.0f / sqrtf((float)prev);
     t.act = h->act;
+    t.allow_tc = h->tc;
     const int rc = launch_gemm(GEMM_FWD_KN, t, st);
     if (rc) return rc;
     src = h->H[l]; prev = w;
@@ -451,7 +460,10 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
       IQLB_CUDA(cudaEventRecord(h->ev_fork, st));
       IQLB_CUDA(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
     }
-    rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, w <= 32, ws);
+    if (h->tc && w >= 64)
+      rc = launch_grouped_gemm_tc_bwd_weight(h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, ws);
+    else
+      rc = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)l * h->max_chunks, n_chunks, prev, w, w <= 32, ws);
     if (rc) return rc;
     mr_colsum_kernel<<<n_chunks, 128, 0, ws>>>(dz, w, w, nullptr, 0, M, chunk_rows, h->partial + (int64_t)prev * w,
                                                plen);
@@ -466,6 +478,7 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
       t.pre = h->Z[l - 1];                    // epilogue: dZ of the layer below = scale * dH * act'(Z)
       t.scale = 1.0f / sqrtf((float)prev);
       t.act = h->act;
+      t.allow_tc = h->tc;
       rc = launch_gemm(GEMM_LINEAR, t, st);
       if (rc) return rc;
     }

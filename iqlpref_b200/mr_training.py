@@ -27,7 +27,12 @@ def _linears(net) -> List[nn.Module]:
 
 class MRTrainer:
     def __init__(self, net: nn.Module, opt: torch.optim.Optimizer, num_datapoints: int, device: str = "cuda",
-                 bt_pool: str = "mean", max_rows: int = 0):
+                 bt_pool: str = "mean", max_rows: int = 0, precision: str = "fp32"):
+        """`precision`: "fp32" (FFMA GEMMs, the parity mode) or "split_bf16" (the step's GEMMs on the tensor cores,
+        every product as x_hi*w_hi + x_lo*w_hi + x_hi*w_lo with fp32 accumulation, ~1e-5 relative)."""
+        if precision not in ("fp32", "split_bf16"):
+            raise ValueError(f"precision must be 'fp32' or 'split_bf16', got {precision!r}")
+        self.precision = precision
         dev = torch.device(device)
         if dev.type != "cuda":
             raise RuntimeError("iqlpref_b200 has no CPU path: MRTrainer runs on a CUDA device")
@@ -82,6 +87,7 @@ class MRTrainer:
             _lib.check(lib.iqlb_mr_create(self.d_in, widths, len(self.widths), _lib.ACTIVATIONS[self.activation],
                                           1 if self.bt_pool == "mean" else 0, self._max_rows, C.byref(h)),
                        "iqlb_mr_create")
+        _lib.check(lib.iqlb_mr_set_precision(h, 1 if self.precision == "split_bf16" else 0), "iqlb_mr_set_precision")
         n = C.c_int64()
         _lib.check(lib.iqlb_mr_param_count(h, C.byref(n)), "iqlb_mr_param_count")
         assert n.value == self.flat.numel()

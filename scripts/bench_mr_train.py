@@ -33,7 +33,7 @@ def main():
         net = MLP(S + A, 1, widths, "relu")
         w0 = [p.detach().numpy().copy() for p in net.parameters()]
         opt = torch.optim.Adam(net.parameters(), lr=3e-4)
-        tr = MRTrainer(net, opt, 1, device=dev)
+        tr = MRTrainer(net, opt, 1, device=dev, precision=os.environ.get("MR_PRECISION", "fp32"))
         batch = synth_batch(rng, B, T, S, A)
         tb = [torch.from_numpy(x) for x in batch]
         for _ in range(3):
@@ -76,7 +76,7 @@ def main():
         t0 = time.perf_counter()
         orc.train(batch)
         cpu_ms = (time.perf_counter() - t0) * 1e3
-        print(json.dumps({"case": name, "rows": rows, "d_in": S + A, "widths": widths, "device_ms_per_step": round(dev_ms, 4),
+        print(json.dumps({"case": name, "precision": tr.precision, "rows": rows, "d_in": S + A, "widths": widths, "device_ms_per_step": round(dev_ms, 4),
                           "device_steps_per_s": round(1e3 / dev_ms, 1), "fp32_tflops": round(flop / dev_ms / 1e9, 2),
                           "api_ms_per_step": round(api_ms, 4), "api_steps_per_s": round(1e3 / api_ms, 1),
                           "h2d_bytes_per_step": int(sum(t.numel() * 4 for t in ts)),

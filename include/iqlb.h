@@ -264,7 +264,7 @@ int iqlb_relabel_debug_timeline(unsigned long long* buf);
  *   out[n] */
 typedef struct {
   int32_t state_dim, action_dim, embd_dim, num_heads, intermediate_dim, num_layers;
-  int32_t pref_dim;        /* pref_attn_embd_dim (only the value column of pref_linear is used) */
+  int32_t pref_dim;        /* pref_attn_embd_dim P: pref_linear is E -> 2P+1 = [query | key | value] */
   int32_t n_timesteps;     /* rows of timestep_embed = max_episode_steps + 1 */
   int32_t query_len;
   float eps;               /* LayerNorm eps (model_eps) */
@@ -277,9 +277,12 @@ int iqlb_relabel_pt(const iqlb_pt_desc* d, const float* weights, const float* ob
 
 /* RewardPT.forward on explicit windows (pref_trans.py:269-325; what the relabel loop calls at
  * iql.py:1294-1299): states[n][T][S], actions[n][T][A], timesteps int32[n][T], attn_mask[n][T]
- * -> value_out[n][T] (= result["value"][:, 0, :, 0]); T = d->query_len. */
+ * -> value_out[n][T] (= result["value"][:, 0, :, 0]) and, when weighted_sum_out is not NULL, weighted_sum_out[n][T]
+ * (= result["weighted_sum"][:, :, 0]: the preference-attention head, pref_trans.py:303-325 - what PTTrainer's
+ * Bradley-Terry loss pools, training.py:348); T = d->query_len. */
 int iqlb_pt_forward(const iqlb_pt_desc* d, const float* weights, const float* states, const float* actions,
-                    const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out, void* stream);
+                    const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out,
+                    float* weighted_sum_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * MR preference-model training step: replaces MRTrainer.train / .evaluation

@@ -63,7 +63,7 @@ _SIGNATURES = {
     "iqlb_relabel_debug_timeline": ([_P], C.c_int),
     "iqlb_pt_param_count": ([C.POINTER(PTDesc), C.POINTER(C.c_int64)], C.c_int),
     "iqlb_relabel_pt": ([C.POINTER(PTDesc), _P, _P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P], C.c_int),
-    "iqlb_pt_forward": ([C.POINTER(PTDesc), _P, _P, _P, _P, _P, C.c_int64, _P, _P], C.c_int),
+    "iqlb_pt_forward": ([C.POINTER(PTDesc), _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P], C.c_int),
     "iqlb_selftest_umma": ([_P, C.c_int64, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_int32, C.c_int32, _P, _P], C.c_int),
     "iqlb_selftest_gemm": ([C.c_int32, _P, C.c_int32, _P, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,

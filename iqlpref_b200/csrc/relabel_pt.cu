@@ -11,20 +11,21 @@
 // Packed weights (fp32), in the order reward_models/pref_transformer.py:pack_pt_weights emits them:
 //   state_linear W[E,S] b[E] | action_linear W[E,A] b[E] | timestep_embed [n_ts,E] | stacked LN g,b
 //   per layer: LN0 g,b | attn in W[3E,E] b[3E] | attn out W[E,E] b[E] | LN1 g,b | mlp in W[I,E] b[I] | mlp out W[E,I] b[E]
-//   final LN g,b | pref_linear.weight[2P] (value row) [E] | its bias [1]
+//   final LN g,b | pref_linear.weight[2P] (value row) [E] | its bias [1] | pref_linear W[2P+1,E] b[2P+1] (the whole head:
+//   query / key / value of the preference attention, pref_trans.py:303-320, needed for `weighted_sum` only)
 #include "iql_step.cuh"
 
 namespace iqlb {
 
 struct PtOff {
-  int S, A, E, H, I, L, T, n_ts;
+  int S, A, E, H, I, L, T, n_ts, Pd;
   float eps;
-  int64_t sw, sb, aw, ab, temb, slg, slb, layer0, layer_stride, fg, fb, vw, vb, total;
+  int64_t sw, sb, aw, ab, temb, slg, slb, layer0, layer_stride, fg, fb, vw, vb, pw, pb, total;
   // inside a layer
   int64_t ln0g, ln0b, inw, inb, outw, outb, ln1g, ln1b, m1w, m1b, m2w, m2b;
   __host__ void init(const iqlb_pt_desc& d) {
     S = d.state_dim; A = d.action_dim; E = d.embd_dim; H = d.num_heads; I = d.intermediate_dim; L = d.num_layers;
-    T = d.query_len; n_ts = d.n_timesteps; eps = d.eps;
+    T = d.query_len; n_ts = d.n_timesteps; eps = d.eps; Pd = d.pref_dim;
     int64_t o = 0;
     sw = o; o += (int64_t)E * S; sb = o; o += E;
     aw = o; o += (int64_t)E * A; ab = o; o += E;
@@ -42,6 +43,7 @@ struct PtOff {
     o += (int64_t)L * layer_stride;
     fg = o; o += E; fb = o; o += E;
     vw = o; o += E; vb = o; o += 1;
+    pw = o; o += (int64_t)(2 * Pd + 1) * E; pb = o; o += 2 * Pd + 1;
     total = o;
   }
 };
@@ -325,6 +327,44 @@ __global__ void __launch_bounds__(256) pt_value_kernel(int E, float eps, const f
   if (lane == 0) out[r] = acc + __ldg(bv);
 }
 
+// Preference attention head (pref_trans.py:303-320): y[n][t] = pref_linear(hidden action token t) = [q(P) | k(P) | v(1)];
+// weighted_sum[n][t] = sum_j softmax_j(q_t . k_j / sqrt(P) + (1 - m_j) * -10000) v_j - full (non-causal) attention, one
+// head, only the key-padding mask.  grid (sequences), one warp per query.
+__global__ void __launch_bounds__(256) pt_pref_attn_kernel(int T, int Pd, const float* __restrict__ y,
+                                                           const float* __restrict__ maskbuf, float* __restrict__ out) {
+  extern __shared__ float sh[];  // per warp: scores [T]
+  const int n = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ld = 2 * Pd + 1;
+  const float* yb = y + (int64_t)n * T * ld;
+  const float* mk = maskbuf + (int64_t)n * T;
+  float* sc = sh + warp * T;
+  const float scale = rsqrtf((float)Pd);
+  for (int t = warp; t < T; t += 8) {
+    const float* q = yb + (int64_t)t * ld;
+    float mx = -INFINITY;
+    for (int j = 0; j < T; ++j) {
+      const float* k = yb + (int64_t)j * ld + Pd;
+      float acc = 0.f;
+      for (int d = lane; d < Pd; d += 32) acc = fmaf(q[d], k[d], acc);
+      acc = warp_sum(acc);
+      const float v = acc * scale + (1.0f - mk[j]) * -10000.0f;
+      if (lane == 0) sc[j] = v;
+      mx = fmaxf(mx, v);
+    }
+    __syncwarp();
+    float sum = 0.f, ws = 0.f;
+    for (int j = lane; j < T; j += 32) {
+      const float e = expf(sc[j] - mx);
+      sum += e;
+      ws = fmaf(e, yb[(int64_t)j * ld + 2 * Pd], ws);
+    }
+    sum = warp_sum(sum);
+    ws = warp_sum(ws);
+    if (lane == 0) out[(int64_t)n * T + t] = ws / sum;
+    __syncwarp();
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host orchestration
 // ------------------------------------------------------------------------------------------------
@@ -350,7 +390,7 @@ static int pt_check(const iqlb_pt_desc* d) {
 // all_tokens: value for every position (RewardPT.forward); else only the last token (relabel)
 static int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float* obs, const float* act,
                   const int32_t* win_start, const int32_t* seq_len, const int32_t* timesteps, const float* attn_mask,
-                  int64_t n, bool all_tokens, float* out, cudaStream_t st) {
+                  int64_t n, bool all_tokens, float* out, float* wsum_out, cudaStream_t st) {
   int rc = pt_check(d);
   if (rc) return rc;
   if (n == 0) return IQLB_OK;
@@ -358,7 +398,8 @@ static int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float
   P.init(*d);
   const int E = P.E, T2 = 2 * P.T, I = P.I, dh = E / P.H;
   const int full_layers = all_tokens ? P.L : P.L - 1;
-  const int64_t big_cols = full_layers > 0 ? (3 * E > I ? 3 * E : I) : 2 * E;
+  int64_t big_cols = full_layers > 0 ? (3 * E > I ? 3 * E : I) : 2 * E;
+  if (wsum_out != nullptr && big_cols * 2 < 2 * P.Pd + 1) big_cols = (2 * P.Pd + 2) / 2;  // [n T, 2P+1] lives in `big` ([n 2T, big_cols])
   const int64_t per_tok = (int64_t)(2 * E + big_cols) * sizeof(float);
   int64_t chunk = (int64_t)(768ll << 20) / (per_tok * T2);
   if (chunk < 1) chunk = 1;
@@ -446,6 +487,16 @@ static int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float
     if (all_tokens) {
       pt_value_kernel<<<(unsigned)(((int64_t)nw * P.T + 7) / 8), 256, 0, st>>>(E, P.eps, w + P.fg, w + P.fb, w + P.vw, w + P.vb,
                                                                            x + E, 2 * E, (int64_t)nw * P.T, out + w0 * P.T);
+      if (wsum_out != nullptr) {
+        // final LayerNorm of the action tokens -> pref_linear (q | k | v) -> preference attention
+        const int64_t nt = (int64_t)nw * P.T;
+        const int ldy = 2 * P.Pd + 1;
+        pt_ln_kernel<<<(unsigned)((nt + 7) / 8), 256, 0, st>>>(E, P.eps, w + P.fg, w + P.fb, x + E, 2 * E, nt, hbuf);
+        PT_CUDA(cudaGetLastError());
+        PT_RC(pt_linear(hbuf, E, w + P.pw, w + P.pb, big, nullptr, (int)nt, ldy, E, false, st));
+        pt_pref_attn_kernel<<<nw, 256, (size_t)8 * P.T * sizeof(float), st>>>(P.T, P.Pd, big, maskbuf, wsum_out + w0 * P.T);
+        PT_CUDA(cudaGetLastError());
+      }
     } else {
       pt_value_kernel<<<(unsigned)((nw + 7) / 8), 256, 0, st>>>(E, P.eps, w + P.fg, w + P.fb, w + P.vw, w + P.vb, xl, E, nw,
                                                             out + w0);
@@ -477,12 +528,15 @@ extern "C" int iqlb_relabel_pt(const iqlb_pt_desc* d, const float* weights, cons
                                void* stream) {
   IQLB_REQUIRE(weights && obs && act && (n == 0 || (win_start && seq_len && out)), "null pointer");
   IQLB_REQUIRE(n >= 0 && n_data > 0, "sizes");
-  return pt_run(d, weights, 1, obs, act, win_start, seq_len, nullptr, nullptr, n, false, out, (cudaStream_t)stream);
+  return pt_run(d, weights, 1, obs, act, win_start, seq_len, nullptr, nullptr, n, false, out, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int iqlb_pt_forward(const iqlb_pt_desc* d, const float* weights, const float* states, const float* actions,
-                               const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out, void* stream) {
+                               const int32_t* timesteps, const float* attn_mask, int64_t n, float* value_out,
+                               float* weighted_sum_out, void* stream) {
   IQLB_REQUIRE(weights && (n == 0 || (states && actions && timesteps && attn_mask && value_out)), "null pointer");
   IQLB_REQUIRE(n >= 0, "sizes");
-  return pt_run(d, weights, 0, states, actions, nullptr, nullptr, timesteps, attn_mask, n, true, value_out, (cudaStream_t)stream);
+  IQLB_REQUIRE(d != nullptr && d->pref_dim >= 1, "pref_dim");
+  return pt_run(d, weights, 0, states, actions, nullptr, nullptr, timesteps, attn_mask, n, true, value_out, weighted_sum_out,
+                (cudaStream_t)stream);
 }

@@ -3,9 +3,10 @@
 (`reward_models/pref_transformer.py:210-277`: `(states, actions, timesteps, attn_mask)`).
 
 Parameter container with the reference's state_dict keys; `forward` runs the CUDA forward and
-returns `({"value": [B,1,T,1], "weighted_sum": None}, [None]*(L+1))` - the relabel pass reads only
-`value[:, 0, -1, 0]` (iql.py:1301); `weighted_sum` feeds the Bradley-Terry training loss
-(optbnn/training/training.py:348), which is outside the hot path.
+returns `({"weighted_sum": [B,T,1], "value": [B,1,T,1]}, [None]*(L+1))` exactly like the reference (whose SDPA
+returns no attention weights, pref_trans.py:321).  The relabel pass reads only `value[:, 0, -1, 0]` (iql.py:1301);
+`weighted_sum` (the preference-attention head, :303-325) is what the Bradley-Terry loss of `PTTrainer` pools
+(optbnn/training/training.py:348).
 """
 import ctypes as C
 from typing import Dict
@@ -81,10 +82,13 @@ class PT(nn.Module):
         ts = timesteps.to(torch.int32).contiguous()
         am = attn_mask.to(torch.float32).contiguous()
         out = torch.empty((b, t), dtype=torch.float32, device=dev)
+        wsum = torch.empty((b, t), dtype=torch.float32, device=dev)
         lib = _lib.load()
-        _lib.check(lib.iqlb_pt_forward(C.byref(desc), _lib.ptr(weights), _lib.ptr(st), _lib.ptr(ac), _lib.ptr(ts),
-                                       _lib.ptr(am), b, _lib.ptr(out), _lib.stream_ptr(dev)), "iqlb_pt_forward")
-        return {"weighted_sum": None, "value": out.view(b, 1, t, 1)}, [None] * (self.num_layers + 1)
+        with _lib.device_ctx(dev):
+            _lib.check(lib.iqlb_pt_forward(C.byref(desc), _lib.ptr(weights), _lib.ptr(st), _lib.ptr(ac), _lib.ptr(ts),
+                                           _lib.ptr(am), b, _lib.ptr(out), _lib.ptr(wsum), _lib.stream_ptr(dev)),
+                       "iqlb_pt_forward")
+        return {"weighted_sum": wsum.view(b, t, 1), "value": out.view(b, 1, t, 1)}, [None] * (self.num_layers + 1)
 
 
 def pt_desc_from_model(model, query_len: int) -> "_lib.PTDesc":
@@ -129,7 +133,7 @@ def pack_pt_weights(model, desc) -> torch.Tensor:
                   sd[p + "mlp.in_linear.weight"], sd[p + "mlp.in_linear.bias"], sd[p + "mlp.out_linear.weight"],
                   sd[p + "mlp.out_linear.bias"]]
     parts += [sd["gpt.layer_norm.weight"], sd["gpt.layer_norm.bias"], sd["pref_linear.weight"][-1],
-              sd["pref_linear.bias"][-1:].clone()]
+              sd["pref_linear.bias"][-1:].clone(), sd["pref_linear.weight"], sd["pref_linear.bias"]]
     flat = torch.cat([p.reshape(-1) for p in parts])
     n = C.c_int64()
     _lib.check(_lib.load().iqlb_pt_param_count(C.byref(desc), C.byref(n)), "iqlb_pt_param_count")

@@ -224,6 +224,7 @@ def gen_relabel(ref):
             res, _ = pt(torch.from_numpy(sts), torch.from_numpy(acts), torch.from_numpy(ts), torch.from_numpy(am))
         out[f"pt{L}.fw.sts"], out[f"pt{L}.fw.acts"], out[f"pt{L}.fw.ts"], out[f"pt{L}.fw.am"] = sts, acts, ts, am
         out[f"pt{L}.fw.value"] = res["value"][:, 0, :, 0].numpy().copy()
+        out[f"pt{L}.fw.weighted_sum"] = res["weighted_sum"][:, :, 0].numpy().copy()
         for tag, ds in (("ds_t", ds_t), ("ds_n", ds_n)):
             r = ref.qlearning_dataset_pt(env, pt, query_length=10, dataset=dict(ds))
             out[f"pt{L}.{tag}.rewards"] = r["rewards"]

@@ -122,8 +122,9 @@ def _layer_norm(x, g, b, eps):
 
 
 def pt_forward_value(p: Dict[str, np.ndarray], states, actions, timesteps, attn_mask,
-                     num_heads: int, eps: float) -> np.ndarray:
-    """pref_trans.py:269-312, eval mode.  p = state_dict as numpy.  Returns value [B, T]."""
+                     num_heads: int, eps: float, with_weighted_sum: bool = False):
+    """pref_trans.py:269-325, eval mode.  p = state_dict as numpy.  Returns value [B, T]
+    (and, with_weighted_sum, weighted_sum [B, T]: the preference-attention head :303-320)."""
     states = np.asarray(states, f32)
     actions = np.asarray(actions, f32)
     bsz, t, _ = states.shape
@@ -162,7 +163,18 @@ def pt_forward_value(p: Dict[str, np.ndarray], states, actions, timesteps, attn_
     hid = x.reshape(bsz, t, 2, e)[:, :, 1]  # action tokens
     wv = p["pref_linear.weight"][-1]
     bv = p["pref_linear.bias"][-1]
-    return (hid @ wv + bv).astype(f32)  # value [B, T]
+    value = (hid @ wv + bv).astype(f32)  # value [B, T]
+    if not with_weighted_sum:
+        return value
+    # preference attention (pref_trans.py:303-320): one head, not causal, additive key-padding mask, scale 1/sqrt(P)
+    y = (hid @ p["pref_linear.weight"].T + p["pref_linear.bias"]).astype(f32)  # [B, T, 2P+1]
+    pd = (y.shape[-1] - 1) // 2
+    q, k, v = y[..., :pd], y[..., pd:2 * pd], y[..., 2 * pd]
+    s = (q @ k.transpose(0, 2, 1)) * f32(1.0 / math.sqrt(pd)) + ((f32(1) - np.asarray(attn_mask, f32)) * f32(-10000.0))[:, None, :]
+    s = s - s.max(-1, keepdims=True)
+    w = np.exp(s)
+    w = w / w.sum(-1, keepdims=True)
+    return value, np.einsum("btj,bj->bt", w, v).astype(f32)
 
 
 def pt_windows(obs_all: np.ndarray, act_all: np.ndarray, ep_steps: np.ndarray, query_length: int):

@@ -45,8 +45,38 @@ def test_pt_forward_matches_reference(rel, L):
     res, attn = m(torch.from_numpy(rel[f"pt{L}.fw.sts"]).cuda(), torch.from_numpy(rel[f"pt{L}.fw.acts"]).cuda(),
                   torch.from_numpy(rel[f"pt{L}.fw.ts"]).cuda(), torch.from_numpy(rel[f"pt{L}.fw.am"]).cuda())
     got = res["value"][:, 0, :, 0].cpu().numpy()
-    assert res["value"].shape == (6, 1, 10, 1) and len(attn) == L + 1
+    assert res["value"].shape == (6, 1, 10, 1) and len(attn) == L + 1 and all(a is None for a in attn)
     np.testing.assert_allclose(got, rel[f"pt{L}.fw.value"], rtol=1e-3, atol=1e-5)
+    # the preference-attention head (pref_trans.py:303-325): what PTTrainer's loss pools (training.py:348)
+    assert res["weighted_sum"].shape == (6, 10, 1)
+    np.testing.assert_allclose(res["weighted_sum"][:, :, 0].cpu().numpy(), rel[f"pt{L}.fw.weighted_sum"], rtol=1e-3, atol=1e-5)
+
+
+def test_pt_weighted_sum_larger_shape_vs_oracle():
+    """E = P = 256, T = 100 (the antmaze PT config), ragged left padding: value and weighted_sum of every position."""
+    from iqlpref_b200.iql import RewardPT
+    S, A, T, n = 29, 8, 100, 9
+    torch.manual_seed(4)
+    m = RewardPT(state_dim=S, action_dim=A, max_episode_steps=150, embd_dim=256, pref_attn_embd_dim=256, num_heads=4,
+                 intermediate_dim=1024, num_layers=1, max_pos=256, eps=0.1)
+    with torch.no_grad():
+        for n_, p_ in m.named_parameters():
+            if "layer_norm" in n_ or n_.endswith("bias"):
+                p_.add_(torch.randn_like(p_) * 0.2)
+    rng = np.random.default_rng(9)
+    sts = rng.standard_normal((n, T, S)).astype(np.float32)
+    acts = rng.uniform(-1, 1, (n, T, A)).astype(np.float32)
+    ts = np.tile(np.arange(T), (n, 1)).astype(np.int64)
+    am = np.ones((n, T), np.float32)
+    for j, padn in enumerate((0, 3, 99, 50, 0, 7, 1, 64, 20)):
+        sts[j, :padn] = 0; acts[j, :padn] = 0; am[j, :padn] = 0
+        ts[j, :padn] = 0; ts[j, padn:] = np.arange(T - padn)
+    res, _ = m.cuda().eval()(torch.from_numpy(sts).cuda(), torch.from_numpy(acts).cuda(), torch.from_numpy(ts).cuda(),
+                             torch.from_numpy(am).cuda())
+    p = {k: v.detach().cpu().numpy() for k, v in m.state_dict().items()}
+    want_v, want_w = ro.pt_forward_value(p, sts, acts, ts, am, 4, 0.1, with_weighted_sum=True)
+    np.testing.assert_allclose(res["value"][:, 0, :, 0].cpu().numpy(), want_v, rtol=1e-3, atol=2e-5)
+    np.testing.assert_allclose(res["weighted_sum"][:, :, 0].cpu().numpy(), want_w, rtol=1e-3, atol=2e-5)
 
 
 @pytest.mark.parametrize("L", [1, 2])

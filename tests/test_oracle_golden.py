@@ -132,6 +132,10 @@ def test_pt_forward_value(rel, L):
     p = _pt_params(rel, L)
     v = ro.pt_forward_value(p, rel[f"pt{L}.fw.sts"], rel[f"pt{L}.fw.acts"], rel[f"pt{L}.fw.ts"], rel[f"pt{L}.fw.am"], 4, 0.1)
     np.testing.assert_allclose(v, rel[f"pt{L}.fw.value"], rtol=1e-4, atol=1e-5)
+    v2, w = ro.pt_forward_value(p, rel[f"pt{L}.fw.sts"], rel[f"pt{L}.fw.acts"], rel[f"pt{L}.fw.ts"], rel[f"pt{L}.fw.am"], 4,
+                                0.1, with_weighted_sum=True)
+    np.testing.assert_array_equal(v2, v)
+    np.testing.assert_allclose(w, rel[f"pt{L}.fw.weighted_sum"], rtol=1e-4, atol=1e-5)  # RewardPT's preference attention
 
 
 @pytest.mark.parametrize("L", [1, 2])

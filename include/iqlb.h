@@ -220,12 +220,15 @@ int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in,
  *                           accumulation (~1e-5 relative per layer); d_in <= 128, equal hidden widths of 64 or
  *                           128, depth <= 3 - IQLB_ERR_UNSUPPORTED otherwise
  *   IQLB_RELABEL_AUTO       split-bf16 where it applies, fp32 elsewhere (what iqlb_relabel_mlp does)
- * The member selection (CVaR tail) is exact given the predictions in every mode. */
+ * The member selection (CVaR tail) is exact given the predictions in every mode.
+ * mean_out (nullable): float[n_rows], the plain mean over all S members of every row, from the same pass (the
+ * "ensemble mean" diagnostic the reference prints next to the CVaR reward, iql.py:1013-1021, 1196-1204).  With
+ * preds_out == NULL the member predictions only ever exist as a row-chunked scratch of at most 512 MB. */
 enum { IQLB_RELABEL_AUTO = -1, IQLB_RELABEL_FP32 = 0, IQLB_RELABEL_SPLIT_BF16 = 1 };
 int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in,
                        const float* weights, int32_t n_members, const int32_t* host_widths, int32_t depth,
                        int32_t activation, int32_t n_tail, int32_t precision, float* out, float* preds_out,
-                       uint8_t* sel_out, void* stream);
+                       uint8_t* sel_out, float* mean_out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * (6) Dataset preparation on the device (between the relabel and the replay buffer).

@@ -59,7 +59,7 @@ _SIGNATURES = {
     "iqlb_relabel_mlp": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.c_int32,
                           C.c_int32, C.c_int32, _P, _P, _P, _P], C.c_int),
     "iqlb_relabel_mlp_p": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.c_int32,
-                            C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P], C.c_int),
+                            C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P, _P], C.c_int),
     "iqlb_relabel_debug_timeline": ([_P], C.c_int),
     "iqlb_pt_param_count": ([C.POINTER(PTDesc), C.POINTER(C.c_int64)], C.c_int),
     "iqlb_relabel_pt": ([C.POINTER(PTDesc), _P, _P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P], C.c_int),

@@ -730,7 +730,7 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
   }
   __syncwarp();
   const int trow = quarter * 32 + lane;  // tile row drained by this thread (two threads per row)
-  const int f = ot * 128 + trow;
+  // (tile row trow of output-feature tile ot = feature ot * 128 + trow)
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   const int64_t noff = L.net_off(s);
   float* gnet = grads + (int64_t)agent * L.Pstride + noff;

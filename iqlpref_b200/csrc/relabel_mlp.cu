@@ -42,9 +42,12 @@ __device__ __forceinline__ uint32_t float_key(float f) {
 // One thread per row: mean of the n_tail smallest of preds[0..S-1, i] (iql.py:1009-1011).
 // Radix select on order-preserving keys: 32 counting passes over the column (coalesced across
 // the rows of a warp, L2-resident), then one pass that sums everything below the threshold.
+// mean_out (nullable): the plain mean over ALL members of the same row, from the same pass (the reference prints
+// "ensemble mean +- std" next to the CVaR reward, iql.py:1013-1021, 1196-1204: no second ensemble pass, no [S, N] matrix).
 __global__ void __launch_bounds__(256) cvar_select_kernel(const float* __restrict__ preds, int64_t pred_stride, int S,
                                                           int n_tail, int rows, float* __restrict__ out,
-                                                          uint8_t* __restrict__ sel, int64_t sel_stride) {
+                                                          uint8_t* __restrict__ sel, int64_t sel_stride,
+                                                          float* __restrict__ mean_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= rows) return;
   const float* col = preds + i;
@@ -52,6 +55,7 @@ __global__ void __launch_bounds__(256) cvar_select_kernel(const float* __restric
     double acc = 0.0;
     for (int s = 0; s < S; ++s) acc += (double)col[(int64_t)s * pred_stride];
     out[i] = (float)(acc / (double)S);
+    if (mean_out) mean_out[i] = (float)(acc / (double)S);
     if (sel) for (int s = 0; s < S; ++s) sel[(int64_t)s * sel_stride + i] = 1;
     return;
   }
@@ -68,7 +72,7 @@ __global__ void __launch_bounds__(256) cvar_select_kernel(const float* __restric
     mask |= bm;
   }
   // prefix == key of the n_tail-th smallest; k == how many ties at the threshold are inside the tail
-  double acc = 0.0;
+  double acc = 0.0, tot = 0.0;
   int ties_left = k;
   for (int s = 0; s < S; ++s) {
     const float v = col[(int64_t)s * pred_stride];
@@ -76,9 +80,11 @@ __global__ void __launch_bounds__(256) cvar_select_kernel(const float* __restric
     bool in = key < prefix;
     if (key == prefix && ties_left > 0) { in = true; --ties_left; }
     if (in) acc += (double)v;
+    tot += (double)v;
     if (sel) sel[(int64_t)s * sel_stride + i] = in ? 1 : 0;
   }
   out[i] = (float)(acc / (double)n_tail);
+  if (mean_out) mean_out[i] = (float)(tot / (double)S);
 }
 
 }  // namespace iqlb
@@ -88,11 +94,11 @@ using namespace iqlb;
 // Tensor-core path (relabel_mlp_tc.cu): member predictions by split-bf16 tcgen05 MMAs, then the same selection.
 static int relabel_mlp_tensor(const float* x, int64_t n_rows, int ldx, int d_in, const float* weights, int S,
                               const int32_t* widths, int depth, int activation, int n_tail, float* out,
-                              float* preds_out, uint8_t* sel_out, cudaStream_t st) {
+                              float* preds_out, uint8_t* sel_out, float* mean_out, cudaStream_t st) {
   RelabelTc* ctx = nullptr;
   int rc = relabel_tc_begin(&ctx, ldx, d_in, weights, S, widths, depth, activation, st);
   if (rc) return rc;
-  const bool direct = S == 1 && !sel_out && !preds_out;  // a single model: its prediction is the result
+  const bool direct = S == 1 && !sel_out && !preds_out && !mean_out;  // a single model: its prediction is the result
   int64_t chunk = n_rows < (1ll << 30) ? n_rows : (1ll << 30);
   float* scratch = nullptr;
   if (!direct && !preds_out) {
@@ -113,7 +119,8 @@ static int relabel_mlp_tensor(const float* x, int64_t n_rows, int ldx, int d_in,
     rc = relabel_tc_forward(ctx, x + r0 * ldx, rows, preds, pstride, st);
     if (rc == IQLB_OK && !direct) {
       cvar_select_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(preds, pstride, S, n_tail, (int)rows, out + r0,
-                                                                        sel_out ? sel_out + r0 : nullptr, n_rows);
+                                                                        sel_out ? sel_out + r0 : nullptr, n_rows,
+                                                                        mean_out ? mean_out + r0 : nullptr);
       if (cudaGetLastError() != cudaSuccess) rc = fail(IQLB_ERR_CUDA, "cvar_select_kernel launch failed%s", "");
     }
   }
@@ -125,7 +132,7 @@ static int relabel_mlp_tensor(const float* x, int64_t n_rows, int ldx, int d_in,
 extern "C" int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in, const float* weights,
                                   int32_t n_members, const int32_t* host_widths, int32_t depth, int32_t activation,
                                   int32_t n_tail, int32_t precision, float* out, float* preds_out, uint8_t* sel_out,
-                                  void* stream) {
+                                  float* mean_out, void* stream) {
   IQLB_REQUIRE(x && weights && host_widths && out, "null pointer");
   IQLB_REQUIRE(n_rows >= 0 && d_in > 0 && ldx >= d_in, "row shape");
   IQLB_REQUIRE(n_members > 0 && depth > 0 && depth <= 16, "ensemble shape");
@@ -142,7 +149,7 @@ extern "C" int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, i
   }
   if (precision != IQLB_RELABEL_FP32 && tc_ok)
     return relabel_mlp_tensor(x, n_rows, ldx, d_in, weights, S, host_widths, depth, activation, n_tail, out, preds_out,
-                              sel_out, st);
+                              sel_out, mean_out, st);
   // member parameter offsets
   std::vector<int64_t> offW(depth + 1), offB(depth + 1);
   int64_t pm = 0;
@@ -210,7 +217,8 @@ extern "C" int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, i
                                                            1.0f / sqrtf((float)prev), rows, preds, pstride);
     RL_CUDA(cudaGetLastError());
     cvar_select_kernel<<<(rows + 255) / 256, 256, 0, st>>>(preds, pstride, S, n_tail, rows, out + r0,
-                                                           sel_out ? sel_out + r0 : nullptr, n_rows);
+                                                           sel_out ? sel_out + r0 : nullptr, n_rows,
+                                                           mean_out ? mean_out + r0 : nullptr);
     RL_CUDA(cudaGetLastError());
     // the task array is re-written next chunk: wait for this chunk's launches to consume it
     if (r0 + chunk < n_rows) RL_CUDA(cudaStreamSynchronize(st));
@@ -224,7 +232,7 @@ extern "C" int iqlb_relabel_mlp(const float* x, int64_t n_rows, int32_t ldx, int
                                 int32_t n_members, const int32_t* host_widths, int32_t depth, int32_t activation,
                                 int32_t n_tail, float* out, float* preds_out, uint8_t* sel_out, void* stream) {
   return iqlb_relabel_mlp_p(x, n_rows, ldx, d_in, weights, n_members, host_widths, depth, activation, n_tail,
-                            IQLB_RELABEL_AUTO, out, preds_out, sel_out, stream);
+                            IQLB_RELABEL_AUTO, out, preds_out, sel_out, nullptr, stream);
 }
 
 extern "C" int iqlb_keep_mask_scan(const uint8_t* terminals, const uint8_t* timeouts, int64_t n,

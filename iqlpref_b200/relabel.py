@@ -88,7 +88,8 @@ def pack_members(members: Sequence[Sequence[Any]], device="cuda") -> PackedMembe
 
 def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
                      activation: str = "relu", device="cuda", return_preds: bool = False,
-                     return_selection: bool = False, precision: str = "auto", out: Optional[torch.Tensor] = None):
+                     return_selection: bool = False, precision: str = "auto", out: Optional[torch.Tensor] = None,
+                     return_mean: bool = False):
     """Evaluate S reward MLPs on X [n, d_in] and reduce over members.
 
     members: S parameter lists [W0, b0, ..., Wout, bout] (numpy or torch; W stored (n_in, n_out) as
@@ -97,7 +98,9 @@ def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
     "split_bf16" (tcgen05, x_hi*W_hi + x_lo*W_hi + x_hi*W_lo; d_in <= 128, hidden [64|128] x <= 3) or "auto"
     (tensor cores where the shape allows).  X may be a row-strided view (stride(1) == 1) of a wider table.
     `out`: optional preallocated float32 CUDA tensor [n] to write into (repeated relabels without allocation).
-    Returns a float32 CUDA tensor [n] (plus `preds` [S, n] and/or the uint8 tail-membership mask [S, n])."""
+    `return_mean`: also return the plain per-row mean over all members (same pass; no [S, n] matrix is materialised).
+    Returns a float32 CUDA tensor [n] (plus, in this order, `preds` [S, n], the uint8 tail-membership mask [S, n] and
+    the member mean [n] when asked for)."""
     dev = _cuda_device(device)
     if precision not in RELABEL_PRECISIONS:
         raise ValueError(f"precision must be one of {sorted(RELABEL_PRECISIONS)}, got {precision!r}")
@@ -123,23 +126,28 @@ def ensemble_predict(members, X, reduce: str = "mean", alpha: float = 0.0,
         raise ValueError(f"out must be a contiguous float32 tensor [{n}] on {X.device}")
     if n == 0:  # nothing to launch (an empty tensor has no device pointer)
         res = [out] + ([torch.empty((S, 0), dtype=torch.float32, device=dev)] if return_preds else []) + \
-              ([torch.empty((S, 0), dtype=torch.uint8, device=dev)] if return_selection else [])
+              ([torch.empty((S, 0), dtype=torch.uint8, device=dev)] if return_selection else []) + \
+              ([torch.empty(0, dtype=torch.float32, device=dev)] if return_mean else [])
         return res[0] if len(res) == 1 else tuple(res)
     preds = torch.empty((S, n), dtype=torch.float32, device=dev) if return_preds else None
     sel = torch.empty((S, n), dtype=torch.uint8, device=dev) if return_selection else None
+    mean = torch.empty(n, dtype=torch.float32, device=dev) if return_mean else None
     w_arr = (C.c_int32 * len(widths))(*widths)
     lib = _lib.load()
     ldx = X.stride(0) if n > 1 else d_in
     with _lib.device_ctx(dev):
         _lib.check(lib.iqlb_relabel_mlp_p(_lib.ptr(X), n, ldx, d_in, _lib.ptr(weights), S, w_arr, len(widths),
                                           _lib.ACTIVATIONS[activation], n_tail, RELABEL_PRECISIONS[precision],
-                                          _lib.ptr(out), _lib.ptr(preds), _lib.ptr(sel), _lib.stream_ptr(dev)),
+                                          _lib.ptr(out), _lib.ptr(preds), _lib.ptr(sel), _lib.ptr(mean),
+                                          _lib.stream_ptr(dev)),
                    "iqlb_relabel_mlp_p")
     res = [out]
     if return_preds:
         res.append(preds)
     if return_selection:
         res.append(sel)
+    if return_mean:
+        res.append(mean)
     return res[0] if len(res) == 1 else tuple(res)
 
 
@@ -197,18 +205,29 @@ def empirical_cvar(samples: np.ndarray, alpha: float) -> float:
     return float(sorted_samples[:n_tail].mean())
 
 
-def cvar_stability_check(all_preds, alpha: float, n_checks: int = 50, remedy: str = "Increase bnn_n_samples") -> float:
-    """iql.py:766-827.  `all_preds` may be a CUDA tensor [S, N]; only the checked columns are copied."""
+def cvar_check_indices(n_rows: int, n_checks: int = 50) -> np.ndarray:
+    """The transitions `cvar_stability_check` looks at (iql.py:799-801: `default_rng(42).choice(N, min(n_checks, N))`)."""
+    return np.random.default_rng(seed=42).choice(n_rows, size=min(n_checks, n_rows), replace=False)
+
+
+def cvar_stability_check(all_preds, alpha: float, n_checks: int = 50, remedy: str = "Increase bnn_n_samples",
+                         cols: Optional[np.ndarray] = None) -> float:
+    """iql.py:766-827.  `all_preds` may be a CUDA tensor [S, N]; only the checked columns are copied.  `cols` [S, k]:
+    the member predictions of the transitions `cvar_check_indices(N)` names, evaluated on their own (the relabel pass
+    then never holds the [S, N] matrix the reference builds)."""
     if alpha == 0.0:
         print("[CVaR stability] alpha=0 (posterior mean); stability check skipped")
         return 0.0
-    S, N = all_preds.shape
-    rng = np.random.default_rng(seed=42)
-    indices = rng.choice(N, size=min(n_checks, N), replace=False)
-    if torch.is_tensor(all_preds):
-        cols = all_preds[:, torch.as_tensor(indices, device=all_preds.device)].cpu().numpy()
+    if cols is not None:
+        cols = np.asarray(cols)
+        S = cols.shape[0]
     else:
-        cols = all_preds[:, indices]
+        S, N = all_preds.shape
+        indices = cvar_check_indices(N, n_checks)
+        if torch.is_tensor(all_preds):
+            cols = all_preds[:, torch.as_tensor(indices, device=all_preds.device)].cpu().numpy()
+        else:
+            cols = all_preds[:, indices]
     ratios = []
     for j in range(cols.shape[1]):
         cvar_full = empirical_cvar(cols[:, j], alpha)
@@ -228,9 +247,18 @@ def cvar_stability_check(all_preds, alpha: float, n_checks: int = 50, remedy: st
 
 
 def _ensemble_rewards(members, obs_act, alpha, activation, device, tag, remedy, mean_label):
-    out, preds = ensemble_predict(members, obs_act, "cvar", alpha, activation, device, return_preds=True)
-    cvar_stability_check(preds, alpha, remedy=remedy)
-    pm = preds.mean(dim=0)
+    """CVaR reward of every transition + the reference's two diagnostics, without the [S, N] prediction matrix of
+    iql.py:982-1004 / 1162-1178 (3.9 GB at S = 981, N = 1M): the tail mean and the member mean come out of one pass over
+    row chunks, and the stability check evaluates the ensemble once more on its <= 50 transitions only."""
+    packed = members if isinstance(members, PackedMembers) else pack_members(members, _cuda_device(device))
+    out, pm = ensemble_predict(packed, obs_act, "cvar", alpha, activation, device, return_mean=True)
+    if alpha != 0.0:
+        idx = cvar_check_indices(int(np.asarray(obs_act).shape[0]) if not torch.is_tensor(obs_act) else int(obs_act.shape[0]))
+        x_chk = obs_act[torch.as_tensor(idx, device=obs_act.device)] if torch.is_tensor(obs_act) else np.asarray(obs_act)[idx]
+        _, cols = ensemble_predict(packed, x_chk, "cvar", alpha, activation, device, return_preds=True)
+        cvar_stability_check(None, alpha, remedy=remedy, cols=cols.cpu().numpy())
+    else:
+        cvar_stability_check(None, alpha, remedy=remedy, cols=np.zeros((len(packed), 0), np.float32))
     print(f"[{tag}] {mean_label}: {pm.mean().item():.4f} ± {pm.std(unbiased=False).item():.4f}")
     penalized = out.cpu().numpy()
     return penalized

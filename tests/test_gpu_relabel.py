@@ -328,3 +328,48 @@ def test_load_pt_reward_model(rel, tmp_path, L):
     assert model.timestep_embed.weight.shape[0] == 61 and abs(model.stacked_layer_norm.eps - 0.1) < 1e-12
     out = qlearning_dataset_pt(FakeEnv(), model, query_length=10, dataset=_ds(rel, "ds_t"))
     np.testing.assert_allclose(out["rewards"], rel[f"pt{L}.ds_t.rewards"], rtol=1e-3, atol=1e-5)
+
+
+def test_ensemble_diagnostics_without_the_prediction_matrix(capsys):
+    """`_ensemble_rewards` (the CVaR reward + the reference's "[CVaR stability]" and "ensemble mean +- std" prints,
+    iql.py:1013-1021, 1188-1204) evaluates the stability check on its <= 50 transitions only and takes the member mean
+    out of the reduction pass: the numbers must be the ones the full [S, N] matrix gives."""
+    from iqlpref_b200 import relabel
+    rng = np.random.default_rng(17)
+    S, n, d_in = 40, 5000, 37
+    members = _members(rng, d_in, 64, 3, S)
+    x = rng.standard_normal((n, d_in)).astype(np.float32)
+    out_full, preds = relabel.ensemble_predict(members, x, "cvar", 0.9, "relu", return_preds=True)
+    out_lean, mean = relabel.ensemble_predict(members, x, "cvar", 0.9, "relu", return_mean=True)
+    assert torch.equal(out_full, out_lean)
+    np.testing.assert_allclose(mean.cpu().numpy(), preds.double().mean(0).cpu().numpy(), rtol=1e-6, atol=1e-7)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        capsys.readouterr()
+        want_ratio = relabel.cvar_stability_check(preds, 0.9)
+        capsys.readouterr()
+        got = relabel._ensemble_rewards(members, x, 0.9, "relu", "cuda", "MR/CVaR", "remedy", "Ensemble mean reward")
+        printed = capsys.readouterr().out
+    np.testing.assert_array_equal(got, out_full.cpu().numpy())
+    pm = preds.mean(0)
+    assert f"mean relative diff = {want_ratio:.3f}" in printed
+    assert f"Ensemble mean reward: {pm.mean().item():.4f} ± {pm.std(unbiased=False).item():.4f}" in printed
+    # alpha = 0: the check is skipped like the reference's, the reward is the plain mean
+    got0 = relabel._ensemble_rewards(members, x, 0.0, "relu", "cuda", "MR/CVaR", "remedy", "Ensemble mean reward")
+    assert "stability check skipped" in capsys.readouterr().out
+    np.testing.assert_allclose(got0, pm.cpu().numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_large_ensemble_streams_in_row_chunks():
+    """S = 981 members x 400 000 rows: the [S, N] matrix would be 1.6 GB; the library walks row chunks of a <= 512 MB
+    scratch and the result equals a call that covers a slice of the rows on its own."""
+    from iqlpref_b200.relabel import ensemble_predict, pack_members
+    rng = np.random.default_rng(23)
+    packed = pack_members(_members(rng, 69, 64, 3, 981))
+    x = torch.randn((400_000, 69), device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
+    free0, _ = torch.cuda.mem_get_info()
+    out, mean = ensemble_predict(packed, x, "cvar", 0.95, "relu", return_mean=True)
+    torch.cuda.synchronize()
+    part = ensemble_predict(packed, x[250_000:251_000], "cvar", 0.95, "relu")
+    assert torch.equal(out[250_000:251_000], part)
+    assert torch.isfinite(out).all() and torch.isfinite(mean).all() and (out <= mean + 1e-6).all()

@@ -5,8 +5,10 @@
 //   warp 0  producer : bulk copies (X tile, b0 | W0 and the four W1 K-blocks through a 4-slot ring); b1, W2 by the epilogue
 //   warp 1  MMA      : tcgen05.mma issue; layer 1 starts on K-block kb as soon as the epilogue has
 //                      written H1 block kb, so the tensor core trails the epilogue by one block
-//   warps 2-9        : epilogue (2 warps per TMEM lane quarter, 32 of every 64 columns each)
-//   warp 10          : stores: H1 / H2 tiles staged in shared memory leave as bulk stores (one commit group per
+//   warps 2-17       : epilogue (4 warps per TMEM lane quarter: 32 of every 64 columns of the even or the odd blocks each;
+//                      16 warps = 4 per scheduler: with 8 the TMEM-load / convert / store chain of a block ran at 36 % issue
+//                      utilisation; epilogue 0 3.5 k -> 2.3 k clocks, forward 52.4 -> 50.0 us at 64 agents)
+//   warp 18          : stores: H1 / H2 tiles staged in shared memory leave as bulk stores (one commit group per
 //                      64-column block, so H2 block b moves in as soon as H1 block b has left), b1 | W2 | b2 loads
 //
 // While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
@@ -24,10 +26,13 @@ namespace fwdp {
 //                | X tile | b0 (x2) | b1 + W2 + b2 | head partial sums ((groups-1) x [8][128]) | barriers
 constexpr uint32_t oH = 0, oRing = 65536, kSlotBytes = 32768;
 constexpr int kSlots = 4, kPerTile = 5;
-constexpr int kEpiWarps = 8, kEpiThreads = kEpiWarps * 32, kAuxWarp = 2 + kEpiWarps, kThreads = 64 + kEpiThreads + 32;
+#ifndef IQLB_FWD_EPI_WARPS
+#define IQLB_FWD_EPI_WARPS 16
+#endif
+constexpr int kEpiWarps = IQLB_FWD_EPI_WARPS, kEpiThreads = kEpiWarps * 32, kAuxWarp = 2 + kEpiWarps, kThreads = 64 + kEpiThreads + 32;
 constexpr int kGroups = kEpiWarps / 4, kPar = kGroups / 2;  // column-half x block-parity groups of epilogue warps
 constexpr uint32_t oX = oRing + kSlots * kSlotBytes, oB0 = oX + 16384, oBW = oB0 + 2048, kBWBytes = 9216 + 32,
-                   oPart = oBW + kBWBytes, kPartBytes = (kGroups - 1) * 8 * 128 * 4, oCtrl = oPart + kPartBytes,
+                   oPart = oBW + kBWBytes, kPartBytes = 0, oCtrl = oPart + kPartBytes,
                    kSmem = oCtrl + 256;
 static_assert(kSmem <= 232448, "shared memory budget of one CTA (227 KB)");
 // barrier indices (8 bytes each) inside the control block
@@ -215,7 +220,6 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const uint32_t ph = (uint32_t)(it & 1);
-      float* part = reinterpret_cast<float*>(smem + oPart);
       const float* sb1 = reinterpret_cast<const float*>(smem + oBW);
       const float* sw2 = sb1 + 256;
       int agent, s, half;
@@ -306,37 +310,52 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         }
       }
       if (t >= 0) fence_async_smem();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(ACC1_FREE));
       if (et == 0) IQLB_TS(it * 8 + 5);
+      // The partial head sums of the column groups meet in TENSOR MEMORY: the warps that share a lane quarter own the
+      // same 32 rows, so group g parks its eight sums in the first columns of the accumulator block it drained last and
+      // group 0 reads them back after the barrier (no shared-memory staging: with 16 epilogue warps it did not fit).
+      constexpr int kLastBlk = (4 / kPar - 1) * kPar;
       if (grp > 0) {
+        uint32_t pr[16];
 #pragma unroll
-        for (int o = 0; o < 8; ++o)
-          if (o < nout) part[((grp - 1) * 8 + o) * 128 + row] = acc[o];
+        for (int o = 0; o < 16; ++o) pr[o] = o < 8 ? __float_as_uint(acc[o]) : 0u;
+        tmem_st16(lane_base + 256u + (uint32_t)((par + kLastBlk) * 64 + chalf * 32), pr);
+        tmem_st_wait();
       }
       const float b2v = lane < 8 ? sw2[nout * 256 + (lane < nout ? lane : 0)] : 0.f;  // before the bundle is reloaded
+      tc_fence_before();
       named_bar_sync(1, kEpiThreads);
       if (et == 0) IQLB_TS(it * 8 + 6);
       if (et == 0) mbar_arrive(bar(EPI1_DONE));  // H2 staged, b1 / W2 / b2 consumed: the store warp stores and reloads
       h1_store_pending = t >= 0;
       if (t >= 0) ++ntrain;
-      if (grp == 0) {
+      if (grp > 0) {
+        if (lane == 0) mbar_arrive(bar(ACC1_FREE));  // (layer 1 of the next tile still waits for group 0's arrival)
+      } else {
+        tc_fence_after();
+        float ps[kGroups > 1 ? kGroups - 1 : 1][16];
+#pragma unroll
+        for (int g = 1; g < kGroups; ++g)
+          tmem_ld16(lane_base + 256u + (uint32_t)(((g >> 1) + kLastBlk) * 64 + (g & 1) * 32), ps[g - 1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(ACC1_FREE));
         float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
 #pragma unroll
         for (int o = 0; o < 8; ++o) {
           if (o < nout) {
             float z = acc[o];
 #pragma unroll
-            for (int g = 0; g < kGroups - 1; ++g) z += part[(g * 8 + o) * 128 + row];
+            for (int g = 0; g < kGroups - 1; ++g) z += ps[g][o];
             z += __shfl_sync(0xffffffffu, b2v, o);
             if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
             else ho[(int64_t)s * L.B + brow] = z;
           }
         }
         if (et == 0) IQLB_TS(1536 + it * 8 + 2);
-        // the partial sums are read before any warp can overwrite them: the next write to `part` follows the
-        // next tile's layer-1 GEMM, which needs the H1 blocks that this warp writes only after these loads
+        // (the parked partial sums were read before this warp's ACC1_FREE arrival: layer 1 of the next tile cannot
+        //  overwrite them earlier)
       }
     }
   } else {

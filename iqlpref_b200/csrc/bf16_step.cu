@@ -366,18 +366,19 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
 // dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
 // each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
 // ------------------------------------------------------------------------------------------------
-// `flags` != nullptr: merged launch (bf16_bwd_merged_kernel) - the CTA publishes its (agent, net) tiles to the
-// weight-gradient CTAs of the same grid through flags[agent * 4 + net] instead of a kernel boundary.
+// 16 worker warps (four per TMEM lane quarter, 64 of the 256 columns each) + two MMA-issuing warps.  With eight workers
+// the CUDA-core dH2 = (dz W2) * relu' tile took 4.3 k of a CTA's 12 k clocks at two warps per scheduler.
+constexpr int kBdWorkerWarps = 16, kBdWorkerThreads = kBdWorkerWarps * 32, kBdThreads = kBdWorkerThreads + 64;
 __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __restrict__ params,
                                               const float* __restrict__ d_out, const int cta_lin, const int n_ag,
-                                              const int bx, const int by, const int bz, uint32_t* flags) {
+                                              const int bx, const int by, const int bz) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   // Longest tiles first: the actor's dH2 = dz W2 has out_dim columns of dz per row (8-24) against one for V / Q, and
   // its CTAs run ~14.5 us against ~8 us - launched in (agent, net) order they end up as the kernel's tail
   // (per-SM CTA timeline, scripts/timeline.py).  CTAs are scheduled in linear block order: actor tiles take the front.
   int half, t, aidx;
-  if (P.opt_lpt || flags != nullptr) {
+  if (P.opt_lpt) {
     if (cta_lin < 2 * n_ag) { half = cta_lin & 1; t = 3; aidx = cta_lin >> 1; }
     else { const int r = cta_lin - 2 * n_ag; half = r & 1; t = (r >> 1) % 3; aidx = (r >> 1) / 3; }
   } else {
@@ -386,7 +387,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
   const int s = train_stream(t), net = net_of_stream(s);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int quarter = warp & 3, chalf = warp >> 2;
+  const int quarter = warp & 3, cgrp = (warp >> 2) & 3;  // column group: 64 columns of the dH2 tile, 16 of every dH1 block
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
   const uint32_t bar_w = sbase + oCtrl, bar_mma = bar_w + 32;
@@ -426,20 +427,20 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
       asm volatile("prefetch.global.L2 [%0];" ::"l"(w1img + ((int64_t)(k * 256 + tid) << 7)));
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 64, 256);
-  // warps 0-7 compute and drain; warp 8 (one lane) issues the dH2 store and the MMAs, so the drain of block ib
-  // overlaps the issue of block ib+1 instead of waiting for the issuing thread's warp
-  const bool worker = warp < 8;
+  // the worker warps compute and drain; the first lanes of the two extra warps issue the dH2 store and the MMAs, so the
+  // drain of block ib overlaps the issue of block ib+1 instead of waiting for the issuing thread's warp
+  const bool worker = warp < kBdWorkerWarps;
   float* sw2 = reinterpret_cast<float*>(smem + oStage);
   if (worker)
-    for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
+    for (int i = tid; i < nout * 256; i += kBdWorkerThreads) sw2[i] = __ldg(fnet + L.w2(in) + i);
   const int row = quarter * 32 + lane, brow = half * 128 + row;
-  const int cbeg = chalf * 128;
-  const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32) + chalf * 4;
-  const uint4 m2w = worker ? *reinterpret_cast<const uint4*>(m2p) : make_uint4(0, 0, 0, 0);
+  const int cbeg = cgrp * 64;
+  const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32) + cgrp * 2;
+  const uint2 m2w = worker ? *reinterpret_cast<const uint2*>(m2p) : make_uint2(0, 0);
   const uint32_t* m1p = P.mask1 + (at * L.B + brow) * (L.H / 32);
-  uint32_t m1w[4];
+  uint32_t m1w[4];  // this thread's 16 columns of block ib: bits (cgrp & 1) * 16 .. + 15 of word 2 ib + cgrp / 2
 #pragma unroll
-  for (int ib = 0; ib < 4; ++ib) m1w[ib] = worker ? m1p[ib * 2 + chalf] : 0u;
+  for (int ib = 0; ib < 4; ++ib) m1w[ib] = worker ? (m1p[ib * 2 + (cgrp >> 1)] >> ((cgrp & 1) * 16)) & 0xffffu : 0u;
   // everything above reads the forward kernel's and Adam's outputs only; dz comes from the loss kernel
   pdl_wait();
   pdl_launch();
@@ -453,11 +454,11 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   IQLB_TSD(1);
   __syncthreads();
   IQLB_TSD(2);
-  if (worker) {  // dH2 tile: this thread's row, columns [cbeg, cbeg+128)
-    // (not unrolled: sixteen copies of the 24-output body would not fit the instruction cache)
+  if (worker) {  // dH2 tile: this thread's row, columns [cbeg, cbeg+64)
+    // (not unrolled: eight copies of the 24-output body would not fit the instruction cache)
 #pragma unroll 1
-    for (int wq = 0; wq < 4; ++wq) {
-      const uint32_t mword = wq == 0 ? m2w.x : (wq == 1 ? m2w.y : (wq == 2 ? m2w.z : m2w.w));
+    for (int wq = 0; wq < 2; ++wq) {
+      const uint32_t mword = wq == 0 ? m2w.x : m2w.y;
 #pragma unroll 1
       for (int cc = 0; cc < 32; cc += 8) {
         const int c0 = cbeg + wq * 32 + cc;
@@ -506,12 +507,13 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   tc_fence_after();
   IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
-  if (tid == 256 || tid == 288) {
+  constexpr int kIss0 = kBdWorkerThreads, kIss1 = kBdWorkerThreads + 32;
+  if (tid == kIss0 || tid == kIss1) {
     // two issuing threads (even / odd blocks): one thread gets an MMA out only every ~105-120 clocks whatever N is
     // (scripts/mma_rate.py), which at N = 64 is a quarter of the tensor pipe's rate
-    const int first = tid == 256 ? 0 : (P.opt_issuers == 2 ? 1 : 4);
+    const int first = tid == kIss0 ? 0 : (P.opt_issuers == 2 ? 1 : 4);
     const int step = P.opt_issuers == 2 ? 2 : 1;
-    if (tid == 256) {
+    if (tid == kIss0) {
       uint8_t* dh2 = P.dh2 + at * P.h_bytes;
       for (int cb = 0; cb < 4; ++cb)
         bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
@@ -524,7 +526,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
       gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
       mma_commit(bar_mma + 8 * ib);
     }
-    if (tid == 256) { if (flags) bulk_wait0(); else bulk_wait_read0(); }  // the dH2 tile has left shared memory (merged: reached global memory)
+    if (tid == kIss0) bulk_wait_read0();  // the dH2 tile has left shared memory
   }
   __syncwarp();
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -535,27 +537,27 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     tc_fence_after();
     IQLB_TSD(5 + ib);
     uint8_t* stage = smem + oW + ib * 32768;  // W1 block ib has been consumed by MMA ib: its space stages dH1 block ib
-    float v[32];
-    tmem_ld32(lane_base + 64u * ib + 32u * chalf, v);
+    float v[16];
+    tmem_ld16(lane_base + 64u * ib + 16u * cgrp, v);
     tmem_ld_wait();
     const uint32_t m = m1w[ib];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
+    for (int j = 0; j < 16; ++j) v[j] = ((m >> j) & 1u) ? v[j] : 0.f;
     if (gscale != 1.0f) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] *= gscale;
+      for (int j = 0; j < 16; ++j) v[j] *= gscale;
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) st_chunk(stage, row, 32 * chalf + 8 * q, v + 8 * q);
+    for (int q = 0; q < 2; ++q) st_chunk(stage, row, 16 * cgrp + 8 * q, v + 8 * q);
     fence_async_smem();
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(kBdWorkerThreads) : "memory");
     if (tid == 0) {
       bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oW + (uint32_t)ib * 32768u, 16384u);
       bulk_commit();
     }
   }
   IQLB_TSD(9);
-  if (tid == 0) { if (flags) bulk_wait0(); else bulk_wait_read0(); }
+  if (tid == 0) bulk_wait_read0();
   if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {
     unsigned long long gt;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
@@ -563,19 +565,13 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   }
   tc_fence_before();
   __syncthreads();
-  if (flags != nullptr && tid == 0) {
-    // both bulk-store groups (dH2 by thread 256, dH1 by this thread) have completed: publish the half tile
-    asm volatile("fence.proxy.async;" ::: "memory");
-    __threadfence();
-    atomicAdd(flags + at, 1u);
-  }
   if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
-__global__ void __launch_bounds__(320, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
+__global__ void __launch_bounds__(kBdThreads, 1) bf16_bwd_data_kernel(BfParams P, const float* __restrict__ params,
                                                                const float* __restrict__ d_out) {
   bwd_data_body(P, params, d_out, (int)blockIdx.x + 2 * ((int)blockIdx.y + kTrain * (int)blockIdx.z), (int)gridDim.z,
-                (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z, nullptr);
+                (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -625,8 +621,7 @@ template <bool kFused>
 __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __restrict__ grads, float* __restrict__ params,
                                                 float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                 float* __restrict__ target, const StepScalars* __restrict__ scal,
-                                                const int ot, const int t, const int aidx, const int n_ag,
-                                                uint32_t* flags) {
+                                                const int ot, const int t, const int aidx, const int n_ag) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
@@ -655,23 +650,8 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
     fence_barrier_init();
     mbar_expect_tx(bar_ld1, 7 * blk);
     bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward output: before the PDL wait
-    if (flags == nullptr) bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);  // loss output, two kernels back
-    pdl_wait();  // separate launch: dH2 / dH1 come from the data-gradient kernel; merged: dz from the loss kernel
-    if (flags != nullptr) {
-      bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);
-      // wait for both half-batch data-gradient CTAs of this (agent, net): they precede this CTA in block order, so
-      // they are running or done (no deadlock); bounded spin so that a scheduling surprise traps instead of hanging
-      uint32_t v = 0;
-      for (long long spin = 0;; ++spin) {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + at) : "memory");
-        if (v >= 2u) break;
-        __nanosleep(100);
-        if (spin > (1ll << 24)) __trap();
-      }
-      asm volatile("fence.proxy.async;" ::: "memory");
-      // self-cleaning: the second of the two consumers puts the flag back to zero for the next step
-      if (atomicAdd(flags + at, 1u) == 3u) atomicExch(flags + at, 0u);
-    }
+    bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);  // loss output, two kernels back
+    pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
     bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
     if (P.opt_pf2) {  // phase-2 operands: L2 prefetch behind the phase-1 copies (a whole phase of lead time)
       bulk_prefetch_l2(P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
@@ -998,29 +978,7 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
                                                                  float* __restrict__ exp_avg_sq, float* __restrict__ target,
                                                                  const StepScalars* __restrict__ scal) {
   bwd_weight_body<kFused>(P, grads, params, exp_avg, exp_avg_sq, target, scal, (int)blockIdx.x, (int)blockIdx.y,
-                          (int)blockIdx.z, (int)gridDim.z, nullptr);
-}
-
-// Both gradient kernels in ONE launch: blocks [0, 8N) are the data-gradient CTAs (longest first), blocks [8N, 16N) the
-// weight-gradient CTAs in the same (agent, net) order, each waiting on the flag its two producers raise.  1024 CTAs on
-// 148 SMs are 6.9 rounds instead of 3.46 + 3.46 rounded up to 4 + 4, a consumer starts while its operands are still
-// in L2, and one kernel boundary disappears.
-__global__ void __launch_bounds__(320, 1) bf16_bwd_merged_kernel(BfParams P, const float* __restrict__ params_c,
-                                                                 const float* __restrict__ d_out, float* __restrict__ grads,
-                                                                 float* __restrict__ params, float* __restrict__ exp_avg,
-                                                                 float* __restrict__ exp_avg_sq, float* __restrict__ target,
-                                                                 const StepScalars* __restrict__ scal, int n_ag,
-                                                                 uint32_t* __restrict__ flags) {
-  const int lin = (int)blockIdx.x;
-  if (lin < 8 * n_ag) {
-    bwd_data_body(P, params_c, d_out, lin, n_ag, 0, 0, 0, flags);
-  } else {
-    if (threadIdx.x >= 256) return;  // the weight-gradient tile is a 256-thread CTA
-    const int r = lin - 8 * n_ag, ot = r & 1, q = r >> 1;
-    int t, aidx;
-    if (q < n_ag) { t = 3; aidx = q; } else { t = (q - n_ag) % 3; aidx = (q - n_ag) / 3; }
-    bwd_weight_body<false>(P, grads, params, exp_avg, exp_avg_sq, target, scal, ot, t, aidx, n_ag, flags);
-  }
+                          (int)blockIdx.z, (int)gridDim.z);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1071,7 +1029,6 @@ int bf16_create(iqlb_agents* h) {
   if (!rc) rc = alloc((void**)&P.mask1, N * kTrain * L.B * (L.H / 32) * 4);
   if (!rc) rc = alloc((void**)&P.mask2, N * kTrain * L.B * (L.H / 32) * 4);
   if (!rc) rc = alloc((void**)&P.gradh, N * L.Pstride * 2);
-  if (!rc) rc = alloc((void**)&P.bwd_flags, N * kTrain * 4);  // zeroed; self-cleaning (merged gradient launch)
   P.dbg = nullptr;
   P.rev = 0;
   auto envi = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
@@ -1089,8 +1046,6 @@ int bf16_create(iqlb_agents* h) {
                                  (int)bwd_weight_smem(L.B)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)bwd_weight_smem(L.B)));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_merged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(bwd_data_smem() > bwd_weight_smem(L.B) ? bwd_data_smem() : bwd_weight_smem(L.B))));
   st->dirty = true;
   return IQLB_OK;
 }
@@ -1100,7 +1055,7 @@ void bf16_destroy(iqlb_agents* h) {
   if (!st) return;
   BfParams& P = st->P;
   cudaFree(P.wimg); cudaFree(P.xsa); cudaFree(P.xnext); cudaFree(P.h1); cudaFree(P.h2); cudaFree(P.dh2);
-  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2); cudaFree(P.gradh); cudaFree(P.bwd_flags); cudaFree(P.dbg);
+  cudaFree(P.dh1); cudaFree(P.dz); cudaFree(P.mask1); cudaFree(P.mask2); cudaFree(P.gradh); cudaFree(P.dbg);
   delete st;
   h->bf16_state = nullptr;
 }
@@ -1194,20 +1149,7 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   P.agent0 = a0;
   bf16_set_dropout(h, P);
   P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
-  // Measured on B200 (64 agents): 259.7 vs 259.0 us per step.  The round saved (6.9 instead of 4 + 4) is eaten by the
-  // hand-off: a producer must wait for its bulk stores to COMPLETE (not just to leave shared memory) before it raises
-  // the flag, and a consumer pays an acquire load + fence before its first operand copy - the gap between CTAs on an
-  // SM grows from 1.1 to 2-2.9 us (scripts/timeline.py).  Opt-in (IQLB_BWD_MERGED=1).
-  const bool merged_env = getenv("IQLB_BWD_MERGED") && atoi(getenv("IQLB_BWD_MERGED")) != 0;
-  if (merged_env && !h->prof && !h->fused_adam && P.bwd_flags != nullptr && a0 == 0 && N == h->desc.n_agents) {
-    const size_t smem = bwd_data_smem() > bwd_weight_smem(L.B) ? bwd_data_smem() : bwd_weight_smem(L.B);
-    IQLB_CUDA(launch_pdl(bf16_bwd_merged_kernel, dim3(16 * N), dim3(320), smem, stream, pdl_enabled(8), P,
-                         (const float*)h->params, (const float*)h->d_out, h->grads, h->params, h->exp_avg, h->exp_avg_sq,
-                         h->target, (const StepScalars*)h->scal, N, P.bwd_flags));
-    pf.mark("bf16_bwd_merged");
-    return IQLB_OK;
-  }
-  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(320), bwd_data_smem(), stream,
+  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(kBdThreads), bwd_data_smem(), stream,
                        pdl_enabled(8) && !h->prof, P,
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");

@@ -114,7 +114,6 @@ struct BfParams {
   int64_t z_bytes;        // one dz image [B x 64]
   uint8_t *wimg, *xsa, *xnext, *h1, *h2, *dh2, *dh1, *dz;
   uint32_t *mask1, *mask2;  // [agent][train net][B][H/32]
-  uint32_t* bwd_flags;      // [agent][4] data-gradient tiles published to the weight-gradient CTAs of a merged launch
   __nv_bfloat16* gradh;     // [agent][Pstride] gradients of the step in bf16 (what the reference's autocast GEMMs emit)
   // actor dropout (iql.py:436-437; include/iqlb.h iqlb_agents_set_actor_dropout): 0 = off
   uint32_t drop_thresh;   // keep an element when its Philox word >= drop_thresh (= p * 2^32)

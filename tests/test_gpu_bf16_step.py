@@ -181,30 +181,6 @@ def test_bf16_lookahead_sampling_changes_nothing(monkeypatch):
     assert out["1"][2][:, 1].tolist() == [32] * N  # eight sampled steps, four Philox draws each
 
 
-def test_bf16_merged_gradient_launch_is_bit_identical(monkeypatch):
-    """IQLB_BWD_MERGED=1: data- and weight-gradient CTAs in one grid with a flag hand-off - same arithmetic, so
-    losses and parameters must equal the two-kernel schedule bit for bit (a missed hand-off would show here)."""
-    from iqlpref_b200 import iql as biql
-    S, A, N = 29, 8, 5
-    rng = np.random.default_rng(4)
-    batches = [torch.stack([biql.pack_rows(*_batch(rng, 256, S, A), 68) for _ in range(N)]).cuda() for _ in range(6)]
-    out = {}
-    for mode in ("0", "1"):
-        monkeypatch.setenv("IQLB_BWD_MERGED", mode)
-        eng = biql.BatchedIQL(S, A, N, batch_size=256, hparams=[HP] * N, precision="bf16")
-        for a in range(N):
-            torch.manual_seed(30 + a)
-            eng.adopt(a, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0), bind=False)
-        trace = []
-        for rows in batches:
-            eng.train(rows)
-            trace.append(eng.losses.clone())
-        torch.cuda.synchronize()
-        out[mode] = (torch.stack(trace), eng.params.clone(), eng.target.clone())
-    for x, y in zip(out["0"], out["1"]):
-        assert torch.equal(x, y)
-
-
 # ------------------------------------------------------------------------------------------------
 # the benchmarked dtype against the reference's own CUDA-autocast output
 # ------------------------------------------------------------------------------------------------

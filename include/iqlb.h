@@ -323,6 +323,46 @@ int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float* states1, 
                  const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float* out2,
                  float* pred_out, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Preference-transformer training step (the PT half): replaces PTTrainer.train / .evaluation
+ * (gp_reward-priors/optbnn/training/training.py:308-416) with PT.forward in training mode
+ * (optbnn/bnn/nets/pref_trans.py:269-325 and the GPT2 blocks :69-227), bt_pool_logit on `weighted_sum`
+ * (optbnn/utils/util.py:356-364) and torch.optim.Adam(net.parameters(), lr) (scripts_pt/run_pt_training.py:137).
+ *   params / exp_avg / exp_avg_sq : device float[iqlb_pt_train_param_count], the parameters in net.parameters() order
+ *       (state_linear W b | action_linear W b | timestep_embed | stacked LN g b | per block: LN0 g b, attention in W b,
+ *       attention out W b, LN1 g b, mlp in W b, mlp out W b | final LN g b | pref_linear W b); caller-owned, updated in place
+ *   states{1,2} [B][T][S], actions{1,2} [B][T][A], timesteps{1,2} int32 [B][T] (< d->n_timesteps), mask{1,2} [B][T],
+ *   labels [B][2] : device; T = d->query_len
+ *   out2 (device float[2], nullable): mean soft-label cross entropy, accuracy;  grad_out (nullable): the gradient used
+ *   adam_step : 1 for the first step.  lr == 0 with exp_avg == NULL computes loss and gradients only.
+ *   training != 0 applies the dropouts set by iqlb_pt_trainer_set_dropout.  The reference draws its dropout masks from
+ *   torch's generator, which cannot be mirrored; here element e (row-major index in the tensor the mask multiplies:
+ *   [2B][2T][E] for the embedding / residual sites, [2B][H][2T][2T] for the attention probabilities) of site s
+ *   (0 = embd_dropout; for block l: 1 + 4l = attention probabilities, 2 + 4l = after attention.out_linear,
+ *   3 + 4l = after mlp.out_linear) at Adam step k is KEPT iff word (e & 3) of
+ *   Philox4x32-10(key = seed, counter = {lo32(k), hi32(k), lo32(e >> 2), (s << 8) | hi32(e >> 2)}) >= floor(p * 2^32),
+ *   kept values scaled by 1 / (1 - p).
+ * No host synchronisation, except on the first call for a new batch size (the weight-gradient task table is rebuilt).
+ * --------------------------------------------------------------------------------------------- */
+typedef struct iqlb_pt_trainer iqlb_pt_trainer;
+int iqlb_pt_train_param_count(const iqlb_pt_desc* d, int64_t* n_floats);
+int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, int32_t max_pairs, iqlb_pt_trainer** out);
+int iqlb_pt_trainer_destroy(iqlb_pt_trainer* h);
+/* 0 = fp32 FFMA GEMMs (default), 1 = every Linear (forward, data and weight gradients) on the tensor cores in split-bf16 */
+int iqlb_pt_trainer_set_precision(iqlb_pt_trainer* h, int32_t precision);
+int iqlb_pt_trainer_set_dropout(iqlb_pt_trainer* h, float p_embd, float p_attn, float p_resid_attn, float p_resid_mlp,
+                                uint64_t seed);
+int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_avg, float* exp_avg_sq, const float* states1,
+                       const float* actions1, const int32_t* timesteps1, const float* mask1, const float* states2,
+                       const float* actions2, const int32_t* timesteps2, const float* mask2, const float* labels,
+                       int32_t B, float lr, float beta1, float beta2, float eps, int64_t adam_step, int32_t training,
+                       float* out2, float* grad_out, void* stream);
+/* PTTrainer.evaluation: eval-mode forward + loss / accuracy; wsum_out (nullable) float[2B][T] = weighted_sum */
+int iqlb_pt_eval(iqlb_pt_trainer* h, const float* params, const float* states1, const float* actions1,
+                 const int32_t* timesteps1, const float* mask1, const float* states2, const float* actions2,
+                 const int32_t* timesteps2, const float* mask2, const float* labels, int32_t B, float* out2,
+                 float* wsum_out, void* stream);
+
 /* Diagnostic: one CTA computes D[128][n] (fp32, row-major) = A * B with tcgen05.mma from two bf16
  * operand images (128-byte-swizzled column blocks of 64, see csrc/umma.cuh).  a_mn / b_mn select
  * MN-major (1: image columns are the M/N index, starting at column a_off) or K-major (0: image rows

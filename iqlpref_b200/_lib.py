@@ -80,6 +80,14 @@ _SIGNATURES = {
     "iqlb_mr_train_step": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64, _P, _P, _P], C.c_int),
     "iqlb_mr_eval": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
+    "iqlb_pt_train_param_count": ([C.POINTER(PTDesc), C.POINTER(C.c_int64)], C.c_int),
+    "iqlb_pt_trainer_create": ([C.POINTER(PTDesc), C.c_int32, C.c_int32, C.POINTER(_P)], C.c_int),
+    "iqlb_pt_trainer_destroy": ([_P], C.c_int),
+    "iqlb_pt_trainer_set_precision": ([_P, C.c_int32], C.c_int),
+    "iqlb_pt_trainer_set_dropout": ([_P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_uint64], C.c_int),
+    "iqlb_pt_train_step": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_float, C.c_float, C.c_float,
+                            C.c_float, C.c_int64, C.c_int32, _P, _P, _P], C.c_int),
+    "iqlb_pt_eval": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_keep_mask_scan": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P], C.c_int),
 }
 

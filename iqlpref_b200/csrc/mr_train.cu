@@ -11,7 +11,7 @@
 #include <cstdlib>
 #include <vector>
 
-#include "iql_step.cuh"
+#include "pt.cuh"
 
 namespace iqlb {
 
@@ -191,6 +191,30 @@ __global__ void __launch_bounds__(256) mr_reduce_adam_kernel(const float* __rest
   m[e] = mm; v[e] = vv;
   const float denom = sqrtf(vv) / bc2_sqrt + eps;
   p[e] = p[e] - step_size * (mm / denom);
+}
+
+// host launchers shared with the preference-transformer trainer (pt_train.cu; declared in pt.cuh)
+int launch_bt_loss(const float* pred, const float* m1, const float* m2, const float* labels, int B, int T, int pool_mean,
+                   float* rowgrad, float* pair_out, unsigned int* counter, float* out2, cudaStream_t st) {
+  mr_loss_kernel<<<B, 64, 0, st>>>(pred, m1, m2, labels, B, T, pool_mean, rowgrad, pair_out, counter, out2);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+int launch_colsum(const float* X, int ld, int ncols, const float* rs, int rs_sum, int64_t M, int chunk_rows, int n_chunks,
+                  float* dst, int64_t plen, cudaStream_t st) {
+  mr_colsum_kernel<<<n_chunks, 128, 0, st>>>(X, ld, ncols, rs, rs_sum, M, chunk_rows, dst, plen);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
+int launch_reduce_adam(const float* partial, int n_chunks, int64_t plen, int64_t n_w, float wscale, float* p, float* m,
+                       float* v, float* grad_out, float beta1, float beta2, float eps, float step_size, float bc2_sqrt,
+                       cudaStream_t st) {
+  mr_reduce_adam_kernel<<<(unsigned)((plen + 63) / 64), 256, 0, st>>>(partial, n_chunks, plen, n_w, wscale, p, m, v, grad_out,
+                                                                   beta1, beta2, eps, step_size, bc2_sqrt);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
 }
 
 }  // namespace iqlb

@@ -1,0 +1,889 @@
+// Preference-transformer training step (the PT half):
+//   PTTrainer.train / .evaluation   gp_reward-priors/optbnn/training/training.py:308-416
+//   PT.forward in training mode     gp_reward-priors/optbnn/bnn/nets/pref_trans.py:269-325 (GPT2Model :186-227,
+//                                   GPT2Block :147-183, GPT2SelfAttention :91-144, GPT2MLP :69-88)
+//   bt_pool_logit                   gp_reward-priors/optbnn/utils/util.py:356-364
+//   optimizer                       torch.optim.Adam(net.parameters(), lr) (scripts_pt/run_pt_training.py:137)
+// One call = one forward over the 2B sequences of both segments (activations kept), Bradley-Terry pooling of
+// `weighted_sum`, soft-label cross entropy, the backward pass through the preference-attention head, the final
+// LayerNorm, every GPT2 block (MLP, causal attention, two LayerNorms, residual dropouts), the embedding LayerNorm and the
+// three embeddings, and Adam - ordered on the caller's stream, no host synchronisation, deterministic (every reduction
+// over rows is a fixed-order sum of per-chunk partials).
+//
+// fp32 throughout (the reference trains in fp32).  Every Linear - forward, data gradient, weight gradient - is a GEMM
+// through launch_gemm / the grouped weight-gradient launchers: fp32 FFMA, or with precision 1 split-bf16 on the tensor
+// cores (gemm_tc.cu).  LayerNorm / softmax / dropout are warp-per-row kernels.  The attention probabilities of the forward
+// pass are kept ([n, H, 2T, 2T]) and the backward pass is two kernels per layer: one walks the queries (dS, dQ; dS and the
+// dropped-out probabilities leave transposed), one walks the keys (dK, dV).
+//
+// Dropout (embd / attention / the two residual sites of a block): the reference draws its masks from torch's CUDA generator,
+// which cannot be mirrored; element e (row-major index in the tensor the mask multiplies) of site s at Adam step k is KEPT iff
+//   word (e & 3) of Philox4x32-10(key = seed, counter = {k, 0, lo32(e >> 2), (s << 8) | hi(e >> 2)}) >= p * 2^32
+// and kept values are scaled by 1 / (1 - p)   (include/iqlb.h; parity by injecting these masks into the oracle).
+#include <vector>
+
+#include "pt.cuh"
+
+namespace iqlb {
+
+struct PtDrop {
+  uint64_t seed, ctr;  // ctr = 4 * adam_step (philox4's offset argument)
+  uint32_t thresh;     // 0: no dropout at this site
+  float scale;
+  int site;
+};
+
+__device__ __forceinline__ float drop_factor(const PtDrop& d, int64_t e) {
+  if (d.thresh == 0) return 1.f;
+  uint32_t r[4];
+  philox4(d.seed, ((uint64_t)d.site << 40) | (uint64_t)(e >> 2), d.ctr, r);
+  return r[e & 3] >= d.thresh ? d.scale : 0.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm forward, one warp per row: y = LN(x (+ temb[ts])) * g + b (* dropout); keeps xhat and 1/std for the backward pass
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ptt_ln_fwd_kernel(int E, float eps, const float* __restrict__ g,
+                                                         const float* __restrict__ b, const float* x, int64_t in_stride,
+                                                         int64_t n_rows, const int32_t* __restrict__ ts_idx,
+                                                         const float* __restrict__ temb, float* y, float* __restrict__ xhat,
+                                                         float* __restrict__ rstd_out, PtDrop drop) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+  if (r >= n_rows) return;
+  const int per = E / 32;
+  float v[kPtMaxPerLane];
+  const float* xr = x + r * in_stride;
+  const float* te = temb ? temb + (int64_t)ts_idx[r >> 1] * E : nullptr;
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c)
+    if (c < per) v[c] = xr[lane + 32 * c] + (te ? __ldg(te + lane + 32 * c) : 0.f);
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) s += v[c];
+  const float mean = warp_sum(s) / (float)E;
+  float q = 0.f;
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) { const float d = v[c] - mean; q += d * d; }
+  const float rstd = rsqrtf(warp_sum(q) / (float)E + eps);
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c) {
+    if (c < per) {
+      const int col = lane + 32 * c;
+      const float xh = (v[c] - mean) * rstd;
+      float yv = xh * __ldg(g + col) + __ldg(b + col);
+      yv *= drop_factor(drop, r * E + col);
+      y[r * E + col] = yv;
+      if (xhat) xhat[r * E + col] = xh;
+    }
+  }
+  if (rstd_out && lane == 0) rstd_out[r] = rstd;
+}
+
+// LayerNorm backward over a block of rows.  dy (optionally through a dropout mask) -> dx (written or accumulated);
+// partial[block][0:E] = sum_rows dy * xhat (d gain), partial[block][E:2E] = sum_rows dy (d bias).
+__global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __restrict__ g, const float* dy,
+                                                         int64_t dy_stride, PtDrop drop, const float* __restrict__ xhat,
+                                                         const float* __restrict__ rstd, int64_t n_rows, int rows_per_block,
+                                                         float* dx, int64_t dx_stride, int accumulate,
+                                                         float* __restrict__ partial) {
+  extern __shared__ float red[];  // [8][2E]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per = E / 32;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < n_rows ? r0 + rows_per_block : n_rows;
+  float ag[kPtMaxPerLane], ab[kPtMaxPerLane], gv[kPtMaxPerLane];
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c) { ag[c] = 0.f; ab[c] = 0.f; gv[c] = c < per ? __ldg(g + lane + 32 * c) : 0.f; }
+  const float invE = 1.0f / (float)E;
+  for (int64_t r = r0 + warp; r < r1; r += 8) {
+    float d[kPtMaxPerLane], xh[kPtMaxPerLane];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < kPtMaxPerLane; ++c) {
+      if (c < per) {
+        const int col = lane + 32 * c;
+        d[c] = dy[r * dy_stride + col] * drop_factor(drop, r * E + col);
+        xh[c] = xhat[r * E + col];
+        ag[c] = fmaf(d[c], xh[c], ag[c]);
+        ab[c] += d[c];
+        d[c] *= gv[c];
+        s1 += d[c];
+        s2 = fmaf(d[c], xh[c], s2);
+      }
+    }
+    s1 = warp_sum(s1) * invE;
+    s2 = warp_sum(s2) * invE;
+    const float rs = rstd[r];
+#pragma unroll
+    for (int c = 0; c < kPtMaxPerLane; ++c) {
+      if (c < per) {
+        const int col = lane + 32 * c;
+        const float o = rs * (d[c] - s1 - xh[c] * s2);
+        float* dst = dx + r * dx_stride + col;
+        *dst = accumulate ? *dst + o : o;
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < kPtMaxPerLane; ++c) {
+    if (c < per) {
+      red[warp * 2 * E + lane + 32 * c] = ag[c];
+      red[warp * 2 * E + E + lane + 32 * c] = ab[c];
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * E; j += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[w * 2 * E + j];
+    partial[(int64_t)blockIdx.x * 2 * E + j] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Causal self-attention, training mode (pref_trans.py:118-140): like pt_attn_full_kernel (relabel_pt.cu), and the softmax
+// probabilities P[i][j] (j <= i) are kept; the output uses P * dropout mask.  grid (sequences, heads), a warp owns a query.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ptt_attn_fwd_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
+                                                           const float* __restrict__ maskbuf, float* __restrict__ out,
+                                                           float* __restrict__ Pbuf, PtDrop drop) {
+  extern __shared__ float sh[];
+  const int w = blockIdx.x, h = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ldk = dh + 1;
+  float* Ks = sh;
+  float* Vs = Ks + (size_t)T2 * ldk;
+  float* qs = Vs + (size_t)T2 * ldk;  // [8][dh]
+  float* ps = qs + 8 * dh;            // [8][T2]
+  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
+  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
+    const int j = i / dh, d = i % dh;
+    Ks[j * ldk + d] = base[(int64_t)j * 3 * E + E + d];
+    Vs[j * ldk + d] = base[(int64_t)j * 3 * E + 2 * E + d];
+  }
+  __syncthreads();
+  const float scale = rsqrtf((float)dh);
+  const float* mk = maskbuf + (int64_t)w * (T2 / 2);
+  const int nchunk = (T2 + 31) / 32;
+  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
+  float* q = qs + warp * dh;
+  float* p = ps + warp * T2;
+  for (int i = warp; i < T2; i += 8) {
+    for (int d = lane; d < dh; d += 32) q[d] = base[(int64_t)i * 3 * E + d];
+    __syncwarp();
+    float s[kPtMaxKeyChunks];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+      if (c < nchunk) {
+        const int j = lane + 32 * c;
+        float v = -INFINITY;
+        if (j < T2 && j <= i) {
+          float acc = 0.f;
+          for (int d = 0; d < dh; ++d) acc = fmaf(q[d], Ks[j * ldk + d], acc);
+          v = acc * scale + (1.0f - mk[j >> 1]) * -10000.0f;
+        }
+        s[c] = v;
+        mx = fmaxf(mx, v);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+      if (c < nchunk) {
+        const float e = (s[c] == -INFINITY) ? 0.f : expf(s[c] - mx);
+        s[c] = e;
+        sum += e;
+      }
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+      const int j = lane + 32 * c;
+      if (c < nchunk && j < T2) {
+        const float pv = s[c] * inv;
+        const int64_t e = pbase + (int64_t)i * T2 + j;
+        if (j <= i) {
+          Pbuf[e] = pv;
+          p[j] = pv * drop_factor(drop, e);
+        } else {
+          p[j] = 0.f;
+        }
+      }
+    }
+    __syncwarp();
+    for (int d = lane; d < dh; d += 32) {
+      float acc = 0.f;
+      for (int j = 0; j <= i; ++j) acc = fmaf(p[j], Vs[j * ldk + d], acc);
+      out[((int64_t)w * T2 + i) * E + h * dh + d] = acc;
+    }
+    __syncwarp();
+  }
+}
+
+// Backward of the attention, query walk.  dO[i] -> dPd[j] = dO[i].V[j]; dP = dPd * mask; dS = P (dP - sum_j P dP);
+// dQ[i] = scale sum_j dS[j] K[j].  dS and Pd = P * mask leave TRANSPOSED ([j][i]) for the key walk.
+__global__ void __launch_bounds__(256) ptt_attn_bwd_q_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
+                                                             const float* __restrict__ Pbuf, const float* __restrict__ dO,
+                                                             float* __restrict__ dST, float* __restrict__ PdT,
+                                                             float* __restrict__ dqkv, PtDrop drop) {
+  extern __shared__ float sh[];
+  const int w = blockIdx.x, h = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ldk = dh + 1;
+  float* Ks = sh;
+  float* Vs = Ks + (size_t)T2 * ldk;
+  float* dos = Vs + (size_t)T2 * ldk;  // [8][dh]
+  float* dss = dos + 8 * dh;           // [8][T2]
+  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
+  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
+    const int j = i / dh, d = i % dh;
+    Ks[j * ldk + d] = base[(int64_t)j * 3 * E + E + d];
+    Vs[j * ldk + d] = base[(int64_t)j * 3 * E + 2 * E + d];
+  }
+  __syncthreads();
+  const float scale = rsqrtf((float)dh);
+  const int nchunk = (T2 + 31) / 32;
+  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
+  float* dor = dos + warp * dh;
+  float* ds = dss + warp * T2;
+  for (int i = warp; i < T2; i += 8) {
+    for (int d = lane; d < dh; d += 32) dor[d] = dO[((int64_t)w * T2 + i) * E + h * dh + d];
+    __syncwarp();
+    float dp[kPtMaxKeyChunks], pv[kPtMaxKeyChunks];
+    float rowsum = 0.f;
+#pragma unroll
+    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+      dp[c] = 0.f; pv[c] = 0.f;
+      const int j = lane + 32 * c;
+      if (c < nchunk && j <= i) {
+        float acc = 0.f;
+        for (int d = 0; d < dh; ++d) acc = fmaf(dor[d], Vs[j * ldk + d], acc);
+        const int64_t e = pbase + (int64_t)i * T2 + j;
+        const float f = drop_factor(drop, e);
+        pv[c] = Pbuf[e];
+        dp[c] = acc * f;
+        rowsum = fmaf(pv[c], dp[c], rowsum);
+        PdT[pbase + (int64_t)j * T2 + i] = pv[c] * f;
+      }
+    }
+    rowsum = warp_sum(rowsum);
+#pragma unroll
+    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+      const int j = lane + 32 * c;
+      if (c < nchunk && j <= i) {
+        const float v = pv[c] * (dp[c] - rowsum);
+        ds[j] = v;
+        dST[pbase + (int64_t)j * T2 + i] = v;
+      }
+    }
+    __syncwarp();
+    for (int d = lane; d < dh; d += 32) {
+      float acc = 0.f;
+      for (int j = 0; j <= i; ++j) acc = fmaf(ds[j], Ks[j * ldk + d], acc);
+      dqkv[((int64_t)w * T2 + i) * 3 * E + h * dh + d] = acc * scale;
+    }
+    __syncwarp();
+  }
+}
+
+// Backward of the attention, key walk: dK[j] = scale sum_{i >= j} dS[i][j] Q[i], dV[j] = sum_{i >= j} Pd[i][j] dO[i]
+__global__ void __launch_bounds__(256) ptt_attn_bwd_kv_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
+                                                              const float* __restrict__ dO, const float* __restrict__ dST,
+                                                              const float* __restrict__ PdT, float* __restrict__ dqkv) {
+  extern __shared__ float sh[];
+  const int w = blockIdx.x, h = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ldk = dh + 1;
+  float* Qs = sh;
+  float* Os = Qs + (size_t)T2 * ldk;
+  float* rows = Os + (size_t)T2 * ldk;  // [8][2][T2]
+  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
+  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
+    const int j = i / dh, d = i % dh;
+    Qs[j * ldk + d] = base[(int64_t)j * 3 * E + d];
+    Os[j * ldk + d] = dO[((int64_t)w * T2 + j) * E + h * dh + d];
+  }
+  __syncthreads();
+  const float scale = rsqrtf((float)dh);
+  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
+  float* a = rows + warp * 2 * T2;
+  float* b = a + T2;
+  for (int j = warp; j < T2; j += 8) {
+    for (int i = j + lane; i < T2; i += 32) {
+      a[i] = dST[pbase + (int64_t)j * T2 + i];
+      b[i] = PdT[pbase + (int64_t)j * T2 + i];
+    }
+    __syncwarp();
+    for (int d = lane; d < dh; d += 32) {
+      float dk = 0.f, dv = 0.f;
+      for (int i = j; i < T2; ++i) {
+        dk = fmaf(a[i], Qs[i * ldk + d], dk);
+        dv = fmaf(b[i], Os[i * ldk + d], dv);
+      }
+      float* o = dqkv + ((int64_t)w * T2 + j) * 3 * E + h * dh + d;
+      o[E] = dk * scale;
+      o[2 * E] = dv;
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Preference-attention head, backward (pref_trans.py:303-320): y rows [q(P) | k(P) | v], full attention with the key-padding
+// bias only.  With w = softmax(s), ws[t] = sum_j w[t][j] v[j] and g[t] = dL/dws[t]:
+//   c[t][j] = w[t][j] g[t];  dv[j] = sum_t c[t][j];  ds[t][j] = c[t][j] (v[j] - ws[t]);
+//   dq[t] = scale sum_j ds[t][j] k[j];  dk[j] = scale sum_t ds[t][j] q[t].
+// grid (sequences); phase 1 a warp per query, phase 2 a warp per key; c goes through a global scratch [n][T][T].
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ptt_pref_attn_bwd_kernel(int T, int Pd, const float* __restrict__ y,
+                                                                const float* __restrict__ maskbuf,
+                                                                const float* __restrict__ gws, float* __restrict__ Cs,
+                                                                float* __restrict__ dy) {
+  extern __shared__ float sh[];  // ws [T] | per warp: sc [T]
+  const int n = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ld = 2 * Pd + 1;
+  const float* yb = y + (int64_t)n * T * ld;
+  float* dyb = dy + (int64_t)n * T * ld;
+  const float* mk = maskbuf + (int64_t)n * T;
+  float* cb = Cs + (int64_t)n * T * T;
+  float* wss = sh;
+  float* sc = sh + T + warp * T;
+  const float scale = rsqrtf((float)Pd);
+  for (int t = warp; t < T; t += 8) {
+    const float* q = yb + (int64_t)t * ld;
+    float mx = -INFINITY;
+    for (int j = 0; j < T; ++j) {
+      const float* k = yb + (int64_t)j * ld + Pd;
+      float acc = 0.f;
+      for (int d = lane; d < Pd; d += 32) acc = fmaf(q[d], k[d], acc);
+      acc = warp_sum(acc);
+      const float v = acc * scale + (1.0f - mk[j]) * -10000.0f;
+      if (lane == 0) sc[j] = v;
+      mx = fmaxf(mx, v);
+    }
+    __syncwarp();
+    float sum = 0.f, wsv = 0.f;
+    for (int j = lane; j < T; j += 32) {
+      const float e = expf(sc[j] - mx);
+      sum += e;
+      wsv = fmaf(e, yb[(int64_t)j * ld + 2 * Pd], wsv);
+    }
+    sum = warp_sum(sum);
+    wsv = warp_sum(wsv) / sum;
+    const float g = gws[(int64_t)n * T + t];
+    const float ginv = g / sum;
+    for (int j = lane; j < T; j += 32) {
+      const float c = expf(sc[j] - mx) * ginv;
+      cb[(int64_t)t * T + j] = c;
+      sc[j] = c * (yb[(int64_t)j * ld + 2 * Pd] - wsv);
+    }
+    if (lane == 0) wss[t] = wsv;
+    __syncwarp();
+    for (int d = lane; d < Pd; d += 32) {
+      float acc = 0.f;
+      for (int j = 0; j < T; ++j) acc = fmaf(sc[j], yb[(int64_t)j * ld + Pd + d], acc);
+      dyb[(int64_t)t * ld + d] = acc * scale;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  for (int j = warp; j < T; j += 8) {
+    const float vj = yb[(int64_t)j * ld + 2 * Pd];
+    float dv = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float c = cb[(int64_t)t * T + j];
+      sc[t] = c * (vj - wss[t]);
+      dv += c;
+    }
+    dv = warp_sum(dv);
+    if (lane == 0) dyb[(int64_t)j * ld + 2 * Pd] = dv;
+    __syncwarp();
+    for (int d = lane; d < Pd; d += 32) {
+      float acc = 0.f;
+      for (int t = 0; t < T; ++t) acc = fmaf(sc[t], yb[(int64_t)t * ld + d], acc);
+      dyb[(int64_t)j * ld + Pd + d] = acc * scale;
+    }
+    __syncwarp();
+  }
+}
+
+// x[e] += a[e] * dropout factor (the residual connections of a block, pref_trans.py:86, 142, 176-182)
+__global__ void ptt_resid_kernel(float* __restrict__ x, const float* __restrict__ a, int64_t total, PtDrop drop) {
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
+    x[e] = fmaf(a[e], drop_factor(drop, e), x[e]);
+}
+
+__global__ void ptt_mask_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t total, PtDrop drop) {
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
+    dst[e] = src[e] * drop_factor(drop, e);
+}
+
+__global__ void ptt_relu_mask_kernel(float* __restrict__ d, const float* __restrict__ z, int64_t total) {
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
+    if (!(z[e] > 0.f)) d[e] = 0.f;
+}
+
+// Gradient of timestep_embed (pref_trans.py:275-278: both tokens of a step add row ts of the table): one block per table
+// row v sums du[2 i] + du[2 i + 1] over the positions i with ts[i] == v, in index order (deterministic scatter-add).
+__global__ void __launch_bounds__(256) ptt_temb_grad_kernel(int E, const int32_t* __restrict__ ts, int64_t n_pos,
+                                                            const float* __restrict__ du, float* __restrict__ gtemb) {
+  __shared__ int flag[256];
+  const int v = blockIdx.x;
+  float acc[2] = {0.f, 0.f};  // E <= 512: columns threadIdx.x, threadIdx.x + 256
+  for (int64_t base = 0; base < n_pos; base += 256) {
+    const int64_t idx = base + threadIdx.x;
+    const int match = idx < n_pos && ts[idx] == v;
+    flag[threadIdx.x] = match;
+    if (__syncthreads_or(match)) {
+      const int lim = (int)(n_pos - base < 256 ? n_pos - base : 256);
+      for (int k = 0; k < lim; ++k) {
+        if (flag[k]) {
+          const float* r = du + (base + k) * 2 * E;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const int col = threadIdx.x + 256 * c;
+            if (col < E) acc[c] += r[col] + r[E + col];
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const int col = threadIdx.x + 256 * c;
+    if (col < E) gtemb[(int64_t)v * E + col] = acc[c];
+  }
+}
+
+}  // namespace iqlb
+
+using namespace iqlb;
+
+struct iqlb_pt_trainer {
+  iqlb_pt_desc d{};
+  PtOff P{};
+  int pool_mean = 1, tc = 0;
+  int n_max = 0;  // sequences (2 * pairs) the buffers hold
+  float p_embd = 0.f, p_attn = 0.f, p_ra = 0.f, p_rm = 0.f;
+  uint64_t seed = 0;
+  // inputs of both segments, concatenated
+  float *St = nullptr, *Ac = nullptr, *Mk = nullptr;
+  int32_t* Ts = nullptr;
+  // forward state
+  float *x = nullptr, *xhat_s = nullptr, *rstd_s = nullptr;
+  struct Layer { float *h0, *xhat0, *rstd0, *qkv, *Pb, *o, *h1, *xhat1, *rstd1, *z; };
+  std::vector<Layer> layers;
+  float *hid = nullptr, *xhat_f = nullptr, *rstd_f = nullptr, *y = nullptr, *ws = nullptr, *val = nullptr;
+  // backward scratch
+  float *rowgrad = nullptr, *Cs = nullptr, *dy = nullptr, *dx = nullptr, *tmpA = nullptr, *tmpB = nullptr, *dbig = nullptr;
+  float *dST = nullptr, *PdT = nullptr, *gtemb = nullptr, *partial = nullptr, *zero_bias = nullptr;
+  float *out2 = nullptr, *pair_out = nullptr;
+  unsigned int* counter = nullptr;
+  GemmTask* d_tasks = nullptr;  // [n_groups][max_chunks] weight-gradient tasks
+  int n_groups = 0, max_chunks = 0;
+  int64_t max_plen = 0;
+  int tasks_n = -1;  // sequence count the task table was built for
+  std::vector<void*> allocs;
+};
+
+static void ptt_free(iqlb_pt_trainer* h) {
+  if (!h) return;
+  for (void* p : h->allocs) cudaFree(p);
+  delete h;
+}
+
+static constexpr int kPttMaxChunks = 296;
+static constexpr int kPttChunkRows = 512;
+static constexpr int kLnRowsPerBlock = 64;
+
+static inline int ptt_chunks(int64_t rows, int& chunk_rows) {
+  int n_chunks = (int)((rows + kPttChunkRows - 1) / kPttChunkRows);
+  if (n_chunks > kPttMaxChunks) n_chunks = kPttMaxChunks;
+  if (n_chunks < 1) n_chunks = 1;
+  chunk_rows = (int)((rows + n_chunks - 1) / n_chunks);
+  chunk_rows = (chunk_rows + 7) / 8 * 8;
+  return (int)((rows + chunk_rows - 1) / chunk_rows);
+}
+
+extern "C" int iqlb_pt_train_param_count(const iqlb_pt_desc* d, int64_t* n_floats) {
+  int rc = pt_check(d);
+  if (rc) return rc;
+  IQLB_REQUIRE(n_floats != nullptr, "null output");
+  IQLB_REQUIRE(d->pref_dim >= 1, "pref_dim");
+  PtOff P;
+  P.init(*d, true);
+  *n_floats = P.total;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, int32_t max_pairs, iqlb_pt_trainer** out) {
+  IQLB_REQUIRE(out != nullptr, "null out");
+  int rc = pt_check(d);
+  if (rc) return rc;
+  IQLB_REQUIRE(d->pref_dim >= 1, "pref_dim");
+  IQLB_REQUIRE(max_pairs >= 1, "max_pairs");
+  auto* h = new iqlb_pt_trainer();
+  h->d = *d;
+  h->P.init(*d, true);
+  h->pool_mean = pool_mean ? 1 : 0;
+  h->n_max = 2 * max_pairs;
+  const PtOff& P = h->P;
+  const int E = P.E, T = P.T, T2 = 2 * T, I = P.I, H = P.H, L = P.L, ldy = 2 * P.Pd + 1;
+  const int64_t n = h->n_max, M = n * T2, nT = n * T;
+  const int64_t bigc = 3 * E > I ? 3 * E : I;
+  bool ok = true;
+  auto alloc = [&](int64_t floats) -> float* {
+    void* p = nullptr;
+    if (!ok) return nullptr;
+    if (cudaMalloc(&p, (size_t)(floats > 0 ? floats : 1) * sizeof(float)) != cudaSuccess) { cudaGetLastError(); ok = false; return nullptr; }
+    h->allocs.push_back(p);
+    return (float*)p;
+  };
+  h->St = alloc(nT * P.S); h->Ac = alloc(nT * P.A); h->Mk = alloc(nT); h->Ts = (int32_t*)alloc(nT);
+  h->x = alloc(M * E); h->xhat_s = alloc(M * E); h->rstd_s = alloc(M);
+  h->layers.resize(L);
+  for (int l = 0; l < L; ++l) {
+    auto& y = h->layers[l];
+    y.h0 = alloc(M * E); y.xhat0 = alloc(M * E); y.rstd0 = alloc(M); y.qkv = alloc(M * 3 * E);
+    y.Pb = alloc(n * H * T2 * T2); y.o = alloc(M * E); y.h1 = alloc(M * E); y.xhat1 = alloc(M * E); y.rstd1 = alloc(M);
+    y.z = alloc(M * I);
+  }
+  h->hid = alloc(nT * E); h->xhat_f = alloc(nT * E); h->rstd_f = alloc(nT); h->y = alloc(nT * ldy); h->ws = alloc(nT);
+  h->val = alloc(nT);
+  h->rowgrad = alloc(nT); h->Cs = alloc(nT * T); h->dy = alloc(nT * ldy); h->dx = alloc(M * E); h->tmpA = alloc(M * E);
+  h->tmpB = alloc(M * E); h->dbig = alloc(M * bigc); h->dST = alloc(n * H * T2 * T2); h->PdT = alloc(n * H * T2 * T2);
+  h->gtemb = alloc((int64_t)P.n_ts * E);
+  h->zero_bias = alloc(bigc > ldy ? bigc : ldy);
+  h->out2 = alloc(2); h->pair_out = alloc(2 * n); h->counter = (unsigned int*)alloc(1);
+  // weight-gradient partials: the largest Linear (+ bias), or the LayerNorm partials [M / 64][2E]
+  int64_t plen = (int64_t)I * E + I;
+  const int64_t p_in = (int64_t)3 * E * E + 3 * E, p_pref = (int64_t)ldy * E + ldy;
+  if (p_in > plen) plen = p_in;
+  if (p_pref > plen) plen = p_pref;
+  h->max_plen = plen;
+  h->max_chunks = kPttMaxChunks;
+  int cr = 0;
+  const int64_t need_w = (int64_t)ptt_chunks(M, cr) * plen;
+  const int64_t need_ln = ((M + kLnRowsPerBlock - 1) / kLnRowsPerBlock) * 2 * E;
+  h->partial = alloc(need_w > need_ln ? need_w : need_ln);
+  h->n_groups = 3 + 4 * L;
+  if (ok) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, (size_t)h->n_groups * h->max_chunks * sizeof(GemmTask)) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    else { h->allocs.push_back(p); h->d_tasks = (GemmTask*)p; }
+  }
+  if (!ok) {
+    ptt_free(h);
+    return fail(IQLB_ERR_NOMEM, "iqlb_pt_trainer_create: device allocation failed%s", "");
+  }
+  cudaMemset(h->counter, 0, sizeof(unsigned int));
+  cudaMemset(h->zero_bias, 0, (size_t)(bigc > ldy ? bigc : ldy) * sizeof(float));
+  *out = h;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_pt_trainer_destroy(iqlb_pt_trainer* h) {
+  if (h) cudaDeviceSynchronize();
+  ptt_free(h);
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_pt_trainer_set_precision(iqlb_pt_trainer* h, int32_t precision) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  IQLB_REQUIRE(precision == 0 || precision == 1, "precision must be 0 (fp32 FFMA) or 1 (split-bf16 tcgen05)");
+  h->tc = precision;
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_pt_trainer_set_dropout(iqlb_pt_trainer* h, float p_embd, float p_attn, float p_resid_attn,
+                                           float p_resid_mlp, uint64_t seed) {
+  IQLB_REQUIRE(h != nullptr, "null handle");
+  auto okp = [](float p) { return p >= 0.f && p < 1.f; };
+  IQLB_REQUIRE(okp(p_embd) && okp(p_attn) && okp(p_resid_attn) && okp(p_resid_mlp), "dropout probabilities in [0, 1)");
+  h->p_embd = p_embd; h->p_attn = p_attn; h->p_ra = p_resid_attn; h->p_rm = p_resid_mlp; h->seed = seed;
+  return IQLB_OK;
+}
+
+static PtDrop make_drop(const iqlb_pt_trainer* h, float p, int site, int64_t adam_step, bool training) {
+  PtDrop d{};
+  d.seed = h->seed; d.ctr = (uint64_t)adam_step * 4ull; d.site = site; d.thresh = 0; d.scale = 1.f;
+  if (training && p > 0.f) {
+    const double t = (double)p * 4294967296.0;
+    d.thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+    if (d.thresh == 0) d.thresh = 1;
+    d.scale = 1.0f / (1.0f - p);
+  }
+  return d;
+}
+
+static int ptt_check_batch(const iqlb_pt_trainer* h, const void* params, const void* s1, const void* a1, const void* t1,
+                           const void* m1, const void* s2, const void* a2, const void* t2, const void* m2,
+                           const void* labels, int B) {
+  IQLB_REQUIRE(h != nullptr, "null trainer");
+  IQLB_REQUIRE(params && s1 && a1 && t1 && m1 && s2 && a2 && t2 && m2 && labels, "null pointer");
+  IQLB_REQUIRE(B > 0 && 2 * B <= h->n_max, "pairs per batch must be in [1, max_pairs]");
+  return IQLB_OK;
+}
+
+static int ptt_pack(iqlb_pt_trainer* h, const float* s1, const float* a1, const int32_t* t1, const float* m1, const float* s2,
+                    const float* a2, const int32_t* t2, const float* m2, int B, cudaStream_t st) {
+  const PtOff& P = h->P;
+  const int64_t BT = (int64_t)B * P.T;
+  const auto D = cudaMemcpyDeviceToDevice;
+  IQLB_CUDA(cudaMemcpyAsync(h->St, s1, (size_t)BT * P.S * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->St + BT * P.S, s2, (size_t)BT * P.S * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Ac, a1, (size_t)BT * P.A * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Ac + BT * P.A, a2, (size_t)BT * P.A * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Ts, t1, (size_t)BT * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Ts + BT, t2, (size_t)BT * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Mk, m1, (size_t)BT * 4, D, st));
+  IQLB_CUDA(cudaMemcpyAsync(h->Mk + BT, m2, (size_t)BT * 4, D, st));
+  return IQLB_OK;
+}
+
+// nn.Linear forward: C = act(A W^T + b)
+static int ptt_linear(const iqlb_pt_trainer* h, const float* A, int lda, const float* W, const float* bias, float* C, int ldc,
+                      int64_t M, int N, int K, bool relu, cudaStream_t st) {
+  GemmTask t{};
+  t.A = A; t.lda = lda; t.Bm = W; t.ldb = K; t.bias = bias; t.C = C; t.ldc = ldc;
+  t.M = (int)M; t.N = N; t.K = K; t.act = relu ? IQLB_ACT_RELU : IQLB_ACT_LINEAR; t.scale = 1.f; t.allow_tc = h->tc;
+  return launch_gemm(GEMM_LINEAR, t, st);
+}
+
+// data gradient of nn.Linear: dX[M, in] = dY[M, out] W[out][in]
+static int ptt_linear_bwd_data(const iqlb_pt_trainer* h, const float* dY, int ldy, const float* W, float* dX, int64_t M,
+                               int n_in, int n_out, cudaStream_t st) {
+  GemmTask t{};
+  t.A = dY; t.lda = ldy; t.Bm = W; t.ldb = n_in; t.bias = h->zero_bias; t.C = dX; t.ldc = n_in;
+  t.M = (int)M; t.N = n_in; t.K = n_out; t.act = IQLB_ACT_LINEAR; t.scale = 1.f; t.allow_tc = h->tc;
+  return launch_gemm(GEMM_FWD_KN, t, st);
+}
+
+static inline unsigned ew_grid(int64_t total) {
+  const int64_t b = (total + 255) / 256;
+  return (unsigned)(b < 148 * 16 ? (b > 0 ? b : 1) : 148 * 16);
+}
+
+static int ptt_forward_train(iqlb_pt_trainer* h, const float* w, int n, int64_t adam_step, bool training, cudaStream_t st) {
+  const PtOff& P = h->P;
+  const int E = P.E, T = P.T, T2 = 2 * T, I = P.I, H = P.H, dh = E / H, ldy = 2 * P.Pd + 1;
+  const int64_t M = (int64_t)n * T2, nT = (int64_t)n * T;
+  int rc;
+  // embeddings: x[2t] = state_linear(s), x[2t+1] = action_linear(a); the LayerNorm kernel adds the timestep rows
+  if ((rc = ptt_linear(h, h->St, P.S, w + P.sw, w + P.sb, h->x, 2 * E, nT, E, P.S, false, st))) return rc;
+  if ((rc = ptt_linear(h, h->Ac, P.A, w + P.aw, w + P.ab, h->x + E, 2 * E, nT, E, P.A, false, st))) return rc;
+  const unsigned ln_grid = (unsigned)((M + 7) / 8);
+  ptt_ln_fwd_kernel<<<ln_grid, 256, 0, st>>>(E, P.eps, w + P.slg, w + P.slb, h->x, E, M, h->Ts, w + P.temb, h->x, h->xhat_s,
+                                             h->rstd_s, make_drop(h, h->p_embd, 0, adam_step, training));
+  IQLB_LAUNCH_CHECK();
+  const PtDrop none = make_drop(h, 0.f, 0, adam_step, false);
+  const size_t attn_smem = ((size_t)2 * T2 * (dh + 1) + 8 * dh + 8 * T2) * sizeof(float);
+  IQLB_REQUIRE(attn_smem <= 227 * 1024, "2T x head_dim too large for the shared-memory attention kernels");
+  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem));
+  for (int l = 0; l < P.L; ++l) {
+    const float* lw = w + P.layer0 + (int64_t)l * P.layer_stride;
+    auto& y = h->layers[l];
+    ptt_ln_fwd_kernel<<<ln_grid, 256, 0, st>>>(E, P.eps, lw + P.ln0g, lw + P.ln0b, h->x, E, M, nullptr, nullptr, y.h0, y.xhat0,
+                                               y.rstd0, none);
+    IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_linear(h, y.h0, E, lw + P.inw, lw + P.inb, y.qkv, 3 * E, M, 3 * E, E, false, st))) return rc;
+    ptt_attn_fwd_kernel<<<dim3(n, H), 256, attn_smem, st>>>(T2, E, H, dh, y.qkv, h->Mk, y.o, y.Pb,
+                                                           make_drop(h, h->p_attn, 1 + 4 * l, adam_step, training));
+    IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_linear(h, y.o, E, lw + P.outw, lw + P.outb, h->tmpA, E, M, E, E, false, st))) return rc;
+    ptt_resid_kernel<<<ew_grid(M * E), 256, 0, st>>>(h->x, h->tmpA, M * E, make_drop(h, h->p_ra, 2 + 4 * l, adam_step, training));
+    IQLB_LAUNCH_CHECK();
+    ptt_ln_fwd_kernel<<<ln_grid, 256, 0, st>>>(E, P.eps, lw + P.ln1g, lw + P.ln1b, h->x, E, M, nullptr, nullptr, y.h1, y.xhat1,
+                                               y.rstd1, none);
+    IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_linear(h, y.h1, E, lw + P.m1w, lw + P.m1b, y.z, I, M, I, E, true, st))) return rc;
+    if ((rc = ptt_linear(h, y.z, I, lw + P.m2w, lw + P.m2b, h->tmpA, E, M, E, I, false, st))) return rc;
+    ptt_resid_kernel<<<ew_grid(M * E), 256, 0, st>>>(h->x, h->tmpA, M * E, make_drop(h, h->p_rm, 3 + 4 * l, adam_step, training));
+    IQLB_LAUNCH_CHECK();
+  }
+  // final LayerNorm of the action tokens (pref_trans.py:298-301) -> pref_linear -> preference attention
+  ptt_ln_fwd_kernel<<<(unsigned)((nT + 7) / 8), 256, 0, st>>>(E, P.eps, w + P.fg, w + P.fb, h->x + E, 2 * E, nT, nullptr, nullptr,
+                                                              h->hid, h->xhat_f, h->rstd_f, none);
+  IQLB_LAUNCH_CHECK();
+  if ((rc = ptt_linear(h, h->hid, E, w + P.pw, w + P.pb, h->y, ldy, nT, ldy, E, false, st))) return rc;
+  return launch_pt_pref_attn(T, P.Pd, h->y, h->Mk, h->ws, n, st);
+}
+
+extern "C" int iqlb_pt_eval(iqlb_pt_trainer* h, const float* params, const float* states1, const float* actions1,
+                            const int32_t* timesteps1, const float* mask1, const float* states2, const float* actions2,
+                            const int32_t* timesteps2, const float* mask2, const float* labels, int32_t B, float* out2,
+                            float* wsum_out, void* stream) {
+  int rc = ptt_check_batch(h, params, states1, actions1, timesteps1, mask1, states2, actions2, timesteps2, mask2, labels, B);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if ((rc = ptt_pack(h, states1, actions1, timesteps1, mask1, states2, actions2, timesteps2, mask2, B, st))) return rc;
+  const int n = 2 * B;
+  if ((rc = ptt_forward_train(h, params, n, 1, false, st))) return rc;
+  if ((rc = launch_bt_loss(h->ws, h->Mk, h->Mk + (int64_t)B * h->P.T, labels, B, h->P.T, h->pool_mean, nullptr, h->pair_out,
+                           h->counter, out2 ? out2 : h->out2, st)))
+    return rc;
+  if (wsum_out) IQLB_CUDA(cudaMemcpyAsync(wsum_out, h->ws, (size_t)n * h->P.T * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return IQLB_OK;
+}
+
+extern "C" int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_avg, float* exp_avg_sq, const float* states1,
+                                  const float* actions1, const int32_t* timesteps1, const float* mask1, const float* states2,
+                                  const float* actions2, const int32_t* timesteps2, const float* mask2, const float* labels,
+                                  int32_t B, float lr, float beta1, float beta2, float eps, int64_t adam_step,
+                                  int32_t training, float* out2, float* grad_out, void* stream) {
+  int rc = ptt_check_batch(h, params, states1, actions1, timesteps1, mask1, states2, actions2, timesteps2, mask2, labels, B);
+  if (rc) return rc;
+  IQLB_REQUIRE((exp_avg != nullptr && exp_avg_sq != nullptr) || lr == 0.f, "null optimizer state");
+  IQLB_REQUIRE(adam_step >= 1, "adam_step counts from 1 (the step being taken)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const PtOff& P = h->P;
+  const int E = P.E, T = P.T, T2 = 2 * T, I = P.I, H = P.H, dh = E / H, L = P.L, ldy = 2 * P.Pd + 1;
+  const int n = 2 * B;
+  const int64_t M = (int64_t)n * T2, nT = (int64_t)n * T;
+  const bool tr = training != 0;
+  float* w = params;
+
+  if ((rc = ptt_pack(h, states1, actions1, timesteps1, mask1, states2, actions2, timesteps2, mask2, B, st))) return rc;
+  if ((rc = ptt_forward_train(h, w, n, adam_step, tr, st))) return rc;
+  if ((rc = launch_bt_loss(h->ws, h->Mk, h->Mk + (int64_t)B * T, labels, B, T, h->pool_mean, h->rowgrad, h->pair_out, h->counter,
+                           out2 ? out2 : h->out2, st)))
+    return rc;
+
+  // ---- weight-gradient task table: group g = one Linear, its tasks = row chunks ---------------------------------------
+  int cr_tok = 0, cr_pos = 0;
+  const int nc_tok = ptt_chunks(M, cr_tok), nc_pos = ptt_chunks(nT, cr_pos);
+  struct Group { const float* A; int lda; const float* X; int ldx; int n_out, n_in; int64_t rows; int chunk_rows, n_chunks; int64_t off; };
+  std::vector<Group> groups;
+  groups.push_back({h->dx, 2 * E, h->St, P.S, E, P.S, nT, cr_pos, nc_pos, P.sw});       // 0 state_linear
+  groups.push_back({h->dx + E, 2 * E, h->Ac, P.A, E, P.A, nT, cr_pos, nc_pos, P.aw});   // 1 action_linear
+  for (int l = 0; l < L; ++l) {
+    auto& y = h->layers[l];
+    const int64_t lo = P.layer0 + (int64_t)l * P.layer_stride;
+    groups.push_back({h->dbig, 3 * E, y.h0, E, 3 * E, E, M, cr_tok, nc_tok, lo + P.inw});                        // 2+4l attention in
+    groups.push_back({h->p_ra > 0.f && tr ? h->tmpA : h->dx, E, y.o, E, E, E, M, cr_tok, nc_tok, lo + P.outw});  // 3+4l attention out
+    groups.push_back({h->dbig, I, y.h1, E, I, E, M, cr_tok, nc_tok, lo + P.m1w});                                // 4+4l mlp in
+    groups.push_back({h->p_rm > 0.f && tr ? h->tmpA : h->dx, E, y.z, I, E, I, M, cr_tok, nc_tok, lo + P.m2w});   // 5+4l mlp out
+  }
+  groups.push_back({h->dy, ldy, h->hid, E, ldy, E, nT, cr_pos, nc_pos, P.pw});          // last: pref_linear
+  const int task_key = n * 2 + (tr ? 1 : 0);
+  if (h->tasks_n != task_key) {
+    std::vector<GemmTask> tasks((size_t)h->n_groups * h->max_chunks);
+    for (size_t g = 0; g < groups.size(); ++g) {
+      const Group& G = groups[g];
+      const int64_t plen = (int64_t)G.n_out * G.n_in + G.n_out;
+      for (int c = 0; c < G.n_chunks; ++c) {
+        const int64_t r0 = (int64_t)c * G.chunk_rows;
+        GemmTask t{};
+        t.A = G.A + r0 * G.lda; t.lda = G.lda;  // A[k, m] : rows of dY
+        t.Bm = G.X + r0 * G.ldx; t.ldb = G.ldx; // X[k, n] : rows of the layer input
+        t.C = h->partial + (int64_t)c * plen; t.ldc = G.n_in;
+        t.M = G.n_out; t.N = G.n_in; t.K = (int)((G.rows - r0 < G.chunk_rows) ? (G.rows - r0) : G.chunk_rows);
+        tasks[g * h->max_chunks + c] = t;
+      }
+    }
+    IQLB_CUDA(cudaStreamSynchronize(st));  // an earlier step on this stream may still read the old table
+    IQLB_CUDA(cudaMemcpy(h->d_tasks, tasks.data(), tasks.size() * sizeof(GemmTask), cudaMemcpyHostToDevice));
+    h->tasks_n = task_key;
+  }
+
+  const double bc1 = 1.0 - pow((double)beta1, (double)adam_step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)adam_step);
+  const float step_size = (float)((double)lr / bc1), bc2_sqrt = (float)sqrt(bc2);
+  const bool apply = exp_avg != nullptr;
+  auto reduce_adam = [&](int64_t off, int64_t plen, int n_chunks, const float* partial) -> int {
+    return launch_reduce_adam(partial, n_chunks, plen, 0, 1.f, apply ? params + off : nullptr, apply ? exp_avg + off : nullptr,
+                              apply ? exp_avg_sq + off : nullptr, grad_out ? grad_out + off : nullptr, beta1, beta2, eps,
+                              step_size, bc2_sqrt, st);
+  };
+  // dW = dY^T X (+ db = column sums of dY) of group g, then Adam on [W | b]
+  auto weight_grad = [&](int g) -> int {
+    const Group& G = groups[g];
+    const int64_t plen = (int64_t)G.n_out * G.n_in + G.n_out;
+    int r;
+    if (h->tc && G.n_in >= 64 && G.n_out >= 64)
+      r = launch_grouped_gemm_tc_bwd_weight(h->d_tasks + (size_t)g * h->max_chunks, G.n_chunks, G.n_out, G.n_in, st);
+    else
+      r = launch_grouped_gemm(GEMM_BWD_WEIGHT, h->d_tasks + (size_t)g * h->max_chunks, G.n_chunks, G.n_out, G.n_in, G.n_in <= 32, st);
+    if (r) return r;
+    if ((r = launch_colsum(G.A, G.lda, G.n_out, nullptr, 0, G.rows, G.chunk_rows, G.n_chunks, h->partial + (int64_t)G.n_out * G.n_in,
+                           plen, st)))
+      return r;
+    return reduce_adam(G.off, plen, G.n_chunks, h->partial);
+  };
+  auto ln_bwd = [&](const float* g_ptr, int64_t g_off, const float* dyp, int64_t dy_stride, const PtDrop& drop, const float* xhat,
+                    const float* rstd, int64_t rows, float* dxp, int64_t dx_stride, int accumulate) -> int {
+    const int blocks = (int)((rows + kLnRowsPerBlock - 1) / kLnRowsPerBlock);
+    ptt_ln_bwd_kernel<<<blocks, 256, (size_t)16 * E * sizeof(float), st>>>(E, g_ptr, dyp, dy_stride, drop, xhat, rstd, rows,
+                                                                          kLnRowsPerBlock, dxp, dx_stride, accumulate, h->partial);
+    IQLB_LAUNCH_CHECK();
+    return reduce_adam(g_off, 2 * E, blocks, h->partial);
+  };
+  const PtDrop none = make_drop(h, 0.f, 0, adam_step, false);
+
+  // ---- head: preference attention -> pref_linear -> final LayerNorm ----------------------------------------------------
+  ptt_pref_attn_bwd_kernel<<<n, 256, (size_t)9 * T * sizeof(float), st>>>(T, P.Pd, h->y, h->Mk, h->rowgrad, h->Cs, h->dy);
+  IQLB_LAUNCH_CHECK();
+  if ((rc = ptt_linear_bwd_data(h, h->dy, ldy, w + P.pw, h->tmpB, nT, E, ldy, st))) return rc;
+  if ((rc = weight_grad((int)groups.size() - 1))) return rc;
+  IQLB_CUDA(cudaMemsetAsync(h->dx, 0, (size_t)M * E * sizeof(float), st));  // state tokens of the last layer feed nothing
+  if ((rc = ln_bwd(w + P.fg, P.fg, h->tmpB, E, none, h->xhat_f, h->rstd_f, nT, h->dx + E, 2 * E, 0))) return rc;
+
+  const size_t q_smem = ((size_t)2 * T2 * (dh + 1) + 8 * dh + 8 * T2) * sizeof(float);
+  const size_t kv_smem = ((size_t)2 * T2 * (dh + 1) + 16 * T2) * sizeof(float);
+  IQLB_REQUIRE(kv_smem <= 227 * 1024 && q_smem <= 227 * 1024, "2T x head_dim too large for the shared-memory attention kernels");
+  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_bwd_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q_smem));
+  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kv_smem));
+
+  for (int l = L - 1; l >= 0; --l) {
+    const int64_t lo = P.layer0 + (int64_t)l * P.layer_stride;
+    const float* lw = w + lo;
+    auto& y = h->layers[l];
+    // MLP: x2 = x1 + drop(out_linear(relu(in_linear(LN1(x1)))))
+    const float* dm = h->dx;
+    if (h->p_rm > 0.f && tr) {
+      ptt_mask_kernel<<<ew_grid(M * E), 256, 0, st>>>(h->dx, h->tmpA, M * E, make_drop(h, h->p_rm, 3 + 4 * l, adam_step, tr));
+      IQLB_LAUNCH_CHECK();
+      dm = h->tmpA;
+    }
+    if ((rc = ptt_linear_bwd_data(h, dm, E, lw + P.m2w, h->dbig, M, I, E, st))) return rc;
+    ptt_relu_mask_kernel<<<ew_grid(M * I), 256, 0, st>>>(h->dbig, y.z, M * I);
+    IQLB_LAUNCH_CHECK();
+    if ((rc = weight_grad(5 + 4 * l))) return rc;
+    if ((rc = ptt_linear_bwd_data(h, h->dbig, I, lw + P.m1w, h->tmpB, M, E, I, st))) return rc;
+    if ((rc = weight_grad(4 + 4 * l))) return rc;
+    if ((rc = ln_bwd(lw + P.ln1g, lo + P.ln1g, h->tmpB, E, none, y.xhat1, y.rstd1, M, h->dx, E, 1))) return rc;
+    // attention: x1 = x0 + drop(out_linear(attn(in_linear(LN0(x0)))))
+    const float* da = h->dx;
+    if (h->p_ra > 0.f && tr) {
+      ptt_mask_kernel<<<ew_grid(M * E), 256, 0, st>>>(h->dx, h->tmpA, M * E, make_drop(h, h->p_ra, 2 + 4 * l, adam_step, tr));
+      IQLB_LAUNCH_CHECK();
+      da = h->tmpA;
+    }
+    if ((rc = ptt_linear_bwd_data(h, da, E, lw + P.outw, h->tmpB, M, E, E, st))) return rc;
+    if ((rc = weight_grad(3 + 4 * l))) return rc;
+    const PtDrop ad = make_drop(h, h->p_attn, 1 + 4 * l, adam_step, tr);
+    ptt_attn_bwd_q_kernel<<<dim3(n, H), 256, q_smem, st>>>(T2, E, H, dh, y.qkv, y.Pb, h->tmpB, h->dST, h->PdT, h->dbig, ad);
+    IQLB_LAUNCH_CHECK();
+    ptt_attn_bwd_kv_kernel<<<dim3(n, H), 256, kv_smem, st>>>(T2, E, H, dh, y.qkv, h->tmpB, h->dST, h->PdT, h->dbig);
+    IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_linear_bwd_data(h, h->dbig, 3 * E, lw + P.inw, h->tmpB, M, E, 3 * E, st))) return rc;
+    if ((rc = weight_grad(2 + 4 * l))) return rc;
+    if ((rc = ln_bwd(lw + P.ln0g, lo + P.ln0g, h->tmpB, E, none, y.xhat0, y.rstd0, M, h->dx, E, 1))) return rc;
+  }
+
+  // ---- embeddings: dropout -> stacked LayerNorm -> state / action Linear + timestep table -------------------------------
+  if ((rc = ln_bwd(w + P.slg, P.slg, h->dx, E, make_drop(h, h->p_embd, 0, adam_step, tr), h->xhat_s, h->rstd_s, M, h->dx, E, 0)))
+    return rc;
+  ptt_temb_grad_kernel<<<P.n_ts, 256, 0, st>>>(E, h->Ts, nT, h->dx, h->gtemb);
+  IQLB_LAUNCH_CHECK();
+  if ((rc = reduce_adam(P.temb, (int64_t)P.n_ts * E, 1, h->gtemb))) return rc;
+  if ((rc = weight_grad(0))) return rc;
+  if ((rc = weight_grad(1))) return rc;
+  return IQLB_OK;
+}

@@ -13,58 +13,9 @@
 //   per layer: LN0 g,b | attn in W[3E,E] b[3E] | attn out W[E,E] b[E] | LN1 g,b | mlp in W[I,E] b[I] | mlp out W[E,I] b[E]
 //   final LN g,b | pref_linear.weight[2P] (value row) [E] | its bias [1] | pref_linear W[2P+1,E] b[2P+1] (the whole head:
 //   query / key / value of the preference attention, pref_trans.py:303-320, needed for `weighted_sum` only)
-#include "iql_step.cuh"
+#include "pt.cuh"
 
 namespace iqlb {
-
-struct PtOff {
-  int S, A, E, H, I, L, T, n_ts, Pd;
-  float eps;
-  int64_t sw, sb, aw, ab, temb, slg, slb, layer0, layer_stride, fg, fb, vw, vb, pw, pb, total;
-  // inside a layer
-  int64_t ln0g, ln0b, inw, inb, outw, outb, ln1g, ln1b, m1w, m1b, m2w, m2b;
-  __host__ void init(const iqlb_pt_desc& d) {
-    S = d.state_dim; A = d.action_dim; E = d.embd_dim; H = d.num_heads; I = d.intermediate_dim; L = d.num_layers;
-    T = d.query_len; n_ts = d.n_timesteps; eps = d.eps; Pd = d.pref_dim;
-    int64_t o = 0;
-    sw = o; o += (int64_t)E * S; sb = o; o += E;
-    aw = o; o += (int64_t)E * A; ab = o; o += E;
-    temb = o; o += (int64_t)n_ts * E;
-    slg = o; o += E; slb = o; o += E;
-    layer0 = o;
-    int64_t q = 0;
-    ln0g = q; q += E; ln0b = q; q += E;
-    inw = q; q += (int64_t)3 * E * E; inb = q; q += 3 * E;
-    outw = q; q += (int64_t)E * E; outb = q; q += E;
-    ln1g = q; q += E; ln1b = q; q += E;
-    m1w = q; q += (int64_t)I * E; m1b = q; q += I;
-    m2w = q; q += (int64_t)E * I; m2b = q; q += E;
-    layer_stride = q;
-    o += (int64_t)L * layer_stride;
-    fg = o; o += E; fb = o; o += E;
-    vw = o; o += E; vb = o; o += 1;
-    pw = o; o += (int64_t)(2 * Pd + 1) * E; pb = o; o += 2 * Pd + 1;
-    total = o;
-  }
-};
-
-constexpr int kPtMaxPerLane = 16;  // E <= 512
-
-// LayerNorm of a row held as vals[c] = row[lane + 32 c]; two-pass (mean, then centred variance)
-__device__ __forceinline__ void warp_layer_norm(float (&vals)[kPtMaxPerLane], int per, int E, float eps,
-                                                const float* __restrict__ g, const float* __restrict__ b, int lane) {
-  float s = 0.f;
-#pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) s += vals[c];
-  const float mean = warp_sum(s) / (float)E;
-  float q = 0.f;
-#pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c) if (c < per) { const float d = vals[c] - mean; q += d * d; }
-  const float rstd = rsqrtf(warp_sum(q) / (float)E + eps);
-#pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c)
-    if (c < per) vals[c] = (vals[c] - mean) * rstd * __ldg(g + lane + 32 * c) + __ldg(b + lane + 32 * c);
-}
 
 // ------------------------------------------------------------------------------------------------
 // Embedding: one warp per (window, position).  x[2t] = LN(state_linear(s) + temb[ts]),
@@ -183,8 +134,6 @@ __global__ void __launch_bounds__(256) pt_copy_rows_kernel(int E, const float* _
 // grid (windows, heads), 8 warps; K and V of the head live in shared memory; a warp owns a query.
 // qkv rows are [q(E) | k(E) | v(E)]; head h is the slice [h*dh, (h+1)*dh) of each.
 // ------------------------------------------------------------------------------------------------
-constexpr int kPtMaxKeyChunks = 16;  // 2T <= 512
-
 __global__ void __launch_bounds__(256) pt_attn_full_kernel(int T2, int E, int dh, const float* __restrict__ qkv,
                                                            const float* __restrict__ maskbuf, float* __restrict__ out) {
   extern __shared__ float sh[];
@@ -365,6 +314,12 @@ __global__ void __launch_bounds__(256) pt_pref_attn_kernel(int T, int Pd, const 
   }
 }
 
+int launch_pt_pref_attn(int T, int Pd, const float* y, const float* maskbuf, float* out, int n, cudaStream_t st) {
+  pt_pref_attn_kernel<<<n, 256, (size_t)8 * T * sizeof(float), st>>>(T, Pd, y, maskbuf, out);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // host orchestration
 // ------------------------------------------------------------------------------------------------
@@ -377,7 +332,7 @@ static int pt_linear(const float* A, int64_t lda, const float* W, const float* b
   return launch_gemm(GEMM_LINEAR, t, st);
 }
 
-static int pt_check(const iqlb_pt_desc* d) {
+int pt_check(const iqlb_pt_desc* d) {
   IQLB_REQUIRE(d != nullptr, "null descriptor");
   IQLB_REQUIRE(d->state_dim > 0 && d->action_dim > 0 && d->num_layers >= 1 && d->intermediate_dim > 0, "dims");
   IQLB_REQUIRE(d->embd_dim >= 32 && d->embd_dim % 32 == 0 && d->embd_dim <= 32 * kPtMaxPerLane, "embd_dim multiple of 32, <= 512");
@@ -388,14 +343,14 @@ static int pt_check(const iqlb_pt_desc* d) {
 }
 
 // all_tokens: value for every position (RewardPT.forward); else only the last token (relabel)
-static int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float* obs, const float* act,
-                  const int32_t* win_start, const int32_t* seq_len, const int32_t* timesteps, const float* attn_mask,
-                  int64_t n, bool all_tokens, float* out, float* wsum_out, cudaStream_t st) {
+int pt_run(const iqlb_pt_desc* d, const float* w, int gather, const float* obs, const float* act,
+           const int32_t* win_start, const int32_t* seq_len, const int32_t* timesteps, const float* attn_mask,
+           int64_t n, bool all_tokens, float* out, float* wsum_out, cudaStream_t st, bool train_layout) {
   int rc = pt_check(d);
   if (rc) return rc;
   if (n == 0) return IQLB_OK;
   PtOff P;
-  P.init(*d);
+  P.init(*d, train_layout);
   const int E = P.E, T2 = 2 * P.T, I = P.I, dh = E / P.H;
   const int full_layers = all_tokens ? P.L : P.L - 1;
   int64_t big_cols = full_layers > 0 ? (3 * E > I ? 3 * E : I) : 2 * E;

@@ -192,7 +192,8 @@ class MRTrainer:
 
 
 def fit_mr(model: MRTrainer, training_batches, val_batches, epochs: int, eval_every: int = 5,
-           checkpoints_path: str = None, criteria_key: str = "acc", activations: str = None, log=None):
+           checkpoints_path: str = None, criteria_key: str = "acc", activations: str = None, log=None,
+           snapshots: bool = True):
     """The epoch loop of `scripts_mr/run_mr_training.py:117-215` around `MRTrainer`: epoch 0 evaluates only, every
     `eval_every` epochs the validation pass runs and `checkpoint_{epoch}.pt` is written (the snapshot ensemble that
     `qlearning_dataset_mr_ensemble` reads), `best_model.pt` follows the reference's criteria ("acc": higher accuracy,
@@ -232,7 +233,8 @@ def fit_mr(model: MRTrainer, training_batches, val_batches, epochs: int, eval_ev
                 for key, val in model.evaluation(batch).items():
                     metrics[key].append(val)
             loss, acc = np.mean(metrics["eval_loss"]), np.mean(metrics["eval_acc"])
-            save(f"checkpoint_{epoch}.pt")
+            if snapshots:
+                save(f"checkpoint_{epoch}.pt")
             first, second = (acc, -loss) if criteria_key == "acc" else (-loss, acc)
             best_first, best_second = (best_acc, -best_loss) if criteria_key == "acc" else (-best_loss, best_acc)
             if first > best_first or (first == best_first and second > best_second):

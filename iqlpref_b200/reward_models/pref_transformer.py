@@ -62,6 +62,10 @@ class PT(nn.Module):
             raise ValueError("embd_dim must be divisible by num_heads")
         self.embd_dim, self.pref_attn_embd_dim, self.num_heads = embd_dim, pref_attn_embd_dim, num_heads
         self.intermediate_dim, self.num_layers, self.eps = intermediate_dim, num_layers, eps
+        # dropout probabilities of training mode (iqlpref_b200.pt_training.PTTrainer; forward() here is eval mode).  The
+        # reference's GPT2Model does not hand `resid_dropout` to its blocks (pref_trans.py:203-213), so both residual sites
+        # of every block run at GPT2Block's default 0.1 whatever the argument says; mirrored.
+        self.embd_dropout_p, self.attn_dropout_p, self.resid_dropout_p = float(embd_dropout), float(attn_dropout), 0.1
         self.state_linear = nn.Linear(state_dim, embd_dim)
         self.action_linear = nn.Linear(action_dim, embd_dim)
         self.timestep_embed = nn.Embedding(max_episode_steps + 1, embd_dim)

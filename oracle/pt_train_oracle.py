@@ -175,3 +175,39 @@ def synth_pt_batch(rng, B, T, S, A, ragged=True):
     labels[0] = [0.5, 0.5]
     out.append(labels.astype(np.float32))
     return out
+
+
+def philox_dropout_mask(seed: int, adam_step: int, site: int, shape, p: float) -> np.ndarray:
+    """The keep mask the CUDA step applies (include/iqlb.h, csrc/pt_train.cu): element e (row-major) of `site` at Adam
+    step k is kept iff word (e & 3) of Philox4x32-10(key = seed, counter = {lo32(k), hi32(k), lo32(e >> 2),
+    (site << 8) | hi32(e >> 2)}) >= floor(p * 2^32); kept elements carry 1 / (1 - p) (float32 arithmetic)."""
+    from oracle.philox_oracle import philox4x32_10
+    numel = int(np.prod(shape))
+    if p <= 0:
+        return np.ones(shape, np.float32)
+    q = np.arange((numel + 3) // 4, dtype=np.uint64)
+    ctr = np.stack([np.full_like(q, adam_step & 0xFFFFFFFF), np.full_like(q, adam_step >> 32), q & np.uint64(0xFFFFFFFF),
+                    (np.uint64(site) << np.uint64(8)) | (q >> np.uint64(32))], axis=-1)
+    key = np.stack([np.full_like(q, seed & 0xFFFFFFFF), np.full_like(q, (seed >> 32) & 0xFFFFFFFF)], axis=-1)
+    words = philox4x32_10(ctr, key).reshape(-1)[:numel]
+    thresh = min(int(np.float64(np.float32(p)) * 4294967296.0), 0xFFFFFFFF)
+    scale = np.float32(1.0) / (np.float32(1.0) - np.float32(p))
+    return np.where(words >= max(thresh, 1), scale, np.float32(0)).astype(np.float32).reshape(shape)
+
+
+def dropout_masks(seed: int, adam_step: int, n: int, T: int, E: int, H: int, L: int, p_embd: float, p_attn: float,
+                  p_resid_attn: float, p_resid_mlp: float) -> Dict[int, torch.Tensor]:
+    """All sites of one training step, keyed like `pt_forward`'s `masks`."""
+    m = {}
+    if p_embd > 0:
+        m[SITE_EMBD] = torch.from_numpy(philox_dropout_mask(seed, adam_step, SITE_EMBD, (n, 2 * T, E), p_embd))
+    for l in range(L):
+        if p_attn > 0:
+            m[site_attn(l)] = torch.from_numpy(philox_dropout_mask(seed, adam_step, site_attn(l), (n, H, 2 * T, 2 * T), p_attn))
+        if p_resid_attn > 0:
+            m[site_resid_attn(l)] = torch.from_numpy(
+                philox_dropout_mask(seed, adam_step, site_resid_attn(l), (n, 2 * T, E), p_resid_attn))
+        if p_resid_mlp > 0:
+            m[site_resid_mlp(l)] = torch.from_numpy(
+                philox_dropout_mask(seed, adam_step, site_resid_mlp(l), (n, 2 * T, E), p_resid_mlp))
+    return m

@@ -77,7 +77,9 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   using namespace fwdp;
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // single-thread roles (producer, MMA issuer, store thread) are chosen by elect.sync inside warp-uniform branches, so the
+  // operands of their bulk copies / MMAs / commits stay in uniform registers (umma.cuh: elect_one)
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bars = sbase + oCtrl;
   auto bar = [&](int i) -> uint32_t { return bars + 8u * (uint32_t)i; };
@@ -130,7 +132,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   };
   // PDL: the weight images (Adam of the previous step) are older than the immediate predecessor (the gather):
   // the first tile's weights start towards L2 before this grid waits for the gather's input images
-  if (tid == 0 && (int)blockIdx.x < n_tiles) {
+  if (warp == 0 && (int)blockIdx.x < n_tiles && elect_one()) {
     int a0, s0, h0;
     const uint8_t *w0p, *x0p;
     const float* f0p;
@@ -141,7 +143,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   pdl_launch();
   if (warp == 0) {
     // ------------------------------------------------------------------ producer
-    if (lane == 0) {
+    if (elect_one()) {
       int c = 0;  // ring entries issued so far (5 per tile: W0, W1 block 0..3)
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         int agent, s, half;
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    if (elect_one()) {
       int c = 0;
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
@@ -360,7 +362,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     }
   } else {
     // ------------------------------------------------------------------ store warp
-    if (lane == 0) {
+    if (elect_one()) {
       if ((int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
       int ntr = 0;
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {

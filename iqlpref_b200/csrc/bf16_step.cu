@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int half = blockIdx.x, s = blockIdx.y, agent = P.agent0 + blockIdx.z;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
   const int quarter = warp & 3, chalf = warp >> 2;
   const int KXB = P.KXB, nring = 4 - KXB;
   const uint32_t sbase = smem_u32(smem);
@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   float* sb1 = reinterpret_cast<float*>(smem + oX);   // valid after layer 0 has consumed X
   float* sw2 = sb1 + 256;
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
     mbar_init(bar_l0, 1);
     for (int c = 0; c < 4; ++c) mbar_init(bar_w1 + 8 * c, 1);
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     mbar_wait(bar_l0, 0);
     tc_fence_after();
     gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oW0, L.H, 0), 256, (in + 15) / 16, false);
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   __syncwarp();
   mbar_wait(bar_mma0, 0);
   tc_fence_after();
-  if (tid == 0) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
+  if (warp == 0 && elect_one()) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
     for (int c = nring; c < 4; ++c) {
       mbar_expect_tx(bar_w1 + 8 * c, 32768u);
       bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   fence_async_smem();
   tc_fence_before();
   __syncthreads();
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     tc_fence_after();
     if (t >= 0) {
       uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
       }
     }
   }
-  if (t >= 0 && tid == 0) {
+  if (t >= 0 && warp == 0 && elect_one()) {
     uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
     for (int cb = 0; cb < 4; ++cb)
       bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
@@ -386,7 +386,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   }
   const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
   const int s = train_stream(t), net = net_of_stream(s);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
   const int quarter = warp & 3, cgrp = (warp >> 2) & 3;  // column group: 64 columns of the dH2 tile, 16 of every dH1 block
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
@@ -409,7 +409,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
     P.dbg[4096 + cta_lin * 3] = smid; P.dbg[4096 + cta_lin * 3 + 1] = gt;
   }
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
     fence_barrier_init();
@@ -507,13 +507,12 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   tc_fence_after();
   IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
-  constexpr int kIss0 = kBdWorkerThreads, kIss1 = kBdWorkerThreads + 32;
-  if (tid == kIss0 || tid == kIss1) {
+  if ((warp == kBdWorkerWarps || warp == kBdWorkerWarps + 1) && elect_one()) {
     // two issuing threads (even / odd blocks): one thread gets an MMA out only every ~105-120 clocks whatever N is
     // (scripts/mma_rate.py), which at N = 64 is a quarter of the tensor pipe's rate
-    const int first = tid == kIss0 ? 0 : (P.opt_issuers == 2 ? 1 : 4);
+    const int first = warp == kBdWorkerWarps ? 0 : (P.opt_issuers == 2 ? 1 : 4);
     const int step = P.opt_issuers == 2 ? 2 : 1;
-    if (tid == kIss0) {
+    if (warp == kBdWorkerWarps) {
       uint8_t* dh2 = P.dh2 + at * P.h_bytes;
       for (int cb = 0; cb < 4; ++cb)
         bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
@@ -526,7 +525,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
       gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
       mma_commit(bar_mma + 8 * ib);
     }
-    if (tid == kIss0) bulk_wait_read0();  // the dH2 tile has left shared memory
+    if (warp == kBdWorkerWarps) bulk_wait_read0();  // the dH2 tile has left shared memory
   }
   __syncwarp();
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -551,13 +550,13 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     for (int q = 0; q < 2; ++q) st_chunk(stage, row, 16 * cgrp + 8 * q, v + 8 * q);
     fence_async_smem();
     asm volatile("bar.sync 1, %0;" ::"n"(kBdWorkerThreads) : "memory");
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
       bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oW + (uint32_t)ib * 32768u, 16384u);
       bulk_commit();
     }
   }
   IQLB_TSD(9);
-  if (tid == 0) bulk_wait_read0();
+  if (warp == 0 && elect_one()) bulk_wait_read0();
   if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {
     unsigned long long gt;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
@@ -626,7 +625,7 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
   const Layout& L = P.L;
   const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
   const int s = train_stream(t);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
   const int quarter = warp & 3, chalf = warp >> 2;
   const uint32_t blk = (uint32_t)L.B * 128u;
   const uint32_t sbase = smem_u32(smem);
@@ -642,7 +641,7 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
   // (bias columns, dW2, dW0) cost as much issue time as the 256-wide one: lane 0 of warps 0-2 issue them side by side.
   const bool multi = P.opt_issuers == 2;
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 3; ++i) mbar_init(bar_ld1 + 8 * i, 1);
     mbar_init(bar_p1, multi ? 2 : 1);  // one arrival per issuing thread
@@ -658,7 +657,7 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
       bulk_prefetch_l2(P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
     }
   }
-  if (kFused && tid == 32) {
+  if (kFused && warp == 1 && elect_one()) {
     // the optimizer state of this tile starts its trip from HBM to L2 now, under the operand loads and the
     // MMAs: p, m, v (and the Polyak target) rows of W1 and W0 that the Adam epilogue below streams
     const int64_t noff_ = L.net_off(s);
@@ -691,19 +690,19 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
     P.dbg[4096 + 1536 + wlin * 4] = smid; P.dbg[4096 + 1536 + wlin * 4 + 1] = gt; P.dbg[4096 + 1536 + wlin * 4 + 3] = (unsigned)t;
   }
   const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
-  if (tid == 0 || (multi && tid == 32)) {
+  if ((warp == 0 || (multi && warp == 1)) && elect_one()) {
     mbar_wait(bar_ld1, 0);
     tc_fence_after();
     const Operand a1 = operand_mn_major(sbase + oA, L.B, 0, 0);
-    if (tid == 0) gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
-    if (tid == 32 || !multi) gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
+    if (warp == 0) gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
+    if (warp == 1 || !multi) gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
     mma_commit(bar_p1);
   }
   __syncwarp();
   mbar_wait(bar_p1, 0);
   tc_fence_after();
   IQLB_TSW(1);
-  if (tid == 0) {  // phase-1 operands consumed: refill (H2 follows once the staging area is free again)
+  if (warp == 0 && elect_one()) {  // phase-1 operands consumed: refill (H2 follows once the staging area is free again)
     mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
     bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
     bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
@@ -823,20 +822,20 @@ __device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __rest
     }
     fence_async_smem();
     __syncthreads();  // staging area free: H2 may move in
-    if (tid == 0) {
+    if (warp == 0 && elect_one()) {
       mbar_expect_tx(bar_ld3, 2 * blk);
       bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
     }
   }
-  if (tid == 0 || (multi && (tid == 32 || tid == 64))) {
-    if (tid != 64) {
+  if ((warp == 0 || (multi && (warp == 1 || warp == 2))) && elect_one()) {
+    if (warp != 2) {
       mbar_wait(bar_ld2, 0);
       tc_fence_after();
       const Operand a0 = operand_mn_major(sbase + oA, L.B, 0, 0);
-      if (tid == 0) gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
-      if (tid == 32 || !multi) gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
+      if (warp == 0) gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
+      if (warp == 1 || !multi) gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
     }
-    if (tid == 64 || !multi) {
+    if (warp == 2 || !multi) {
       mbar_wait(bar_ld3, 0);
       tc_fence_after();
       gemm_issue(tmem + 416, operand_mn_major(sbase + oB + 2 * blk, L.B, 0, 0), z, 32, ksteps, false);

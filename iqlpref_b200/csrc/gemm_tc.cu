@@ -62,6 +62,7 @@ __device__ __forceinline__ void gemm_tc_body(const GemmTask& t, const int tile) 
   constexpr bool A_MN = (MODE == GEMM_BWD_WEIGHT);
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int warp_u = warp_uniform();
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bar_empty = sbase + oCtrl, bar_done = bar_empty + 8 * kStages;
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 8 * kStages + 8);
@@ -164,7 +165,7 @@ __device__ __forceinline__ void gemm_tc_body(const GemmTask& t, const int tile) 
     fence_async_smem();
     __syncthreads();
     if (kb < 4) GTC_TS(4 + 3 * kb);
-    if (tid == 0) {
+    if (warp_u == 0 && elect_one()) {  // one issuing thread, chosen so that the operands stay in uniform registers (umma.cuh)
       tc_fence_after();
       const uint32_t st = sbase + (uint32_t)slot * kStageBytes;
       const Operand a_hi = A_MN ? operand_mn_major(st, 64, 0, 0) : operand_k_major(st, 128, 0);

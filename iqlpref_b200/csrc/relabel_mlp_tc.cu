@@ -130,7 +130,7 @@ __global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
   const uint32_t oTmem = oBar + N_BARS * 8;
   const uint32_t oRed = oTmem + 16;  // 256 partial dot products
   auto bar = [&](int i) { return base + oBar + 8u * (uint32_t)i; };
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_uniform(), lane = threadIdx.x & 31;
   constexpr int w = kW;
   const int depth = P.depth;
 
@@ -159,7 +159,7 @@ __global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
   const bool reload = nm > 1;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {  // single-thread roles are chosen by elect.sync: the operands of the bulk copies / MMAs stay uniform (umma.cuh)
       const bool x_aligned = (P.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.x) & 15) == 0);
       for (int i = 0; i < n_it; ++i) {
         const uint8_t* mb = P.wimg + (int64_t)(s0 + i % nm) * P.member_bytes;
@@ -189,9 +189,9 @@ __global__ void __maxnreg__(96) relabel_mlp_tc_kernel(const RtcParams P) {
       }
     }
   } else if (warp == 1 || warp == 2) {
-    // One MMA issuer per subtile.  A single thread issues a 128 x N x 16 MMA only every ~105-120 clocks whatever N
-    // is (scripts/mma_rate.py): at N = 128 one issuer reaches 55 % of the tensor pipe, two reach 92 %.
-    if (lane == 0) {
+    // One MMA issuer per subtile (scripts/mma_rate.py: with A in tensor memory one elected thread issues a 128 x 128 x 16
+    // MMA every 72 clocks = 88 % of the tensor pipe; chosen by `lane == 0` it was 122 clocks, see umma.cuh).
+    if (elect_one()) {
       const int p = warp - 1;
       const uint32_t idesc = instr_desc_bf16(w, 0, 0);
       const uint32_t acc = tmem + p * PC, ah = acc + w, al = ah + P.aw;

@@ -32,6 +32,20 @@ __host__ __device__ __forceinline__ int64_t image_off(int rows, int r, int c) {
 #ifdef __CUDACC__
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// ---- single-thread issue --------------------------------------------------------------------------
+// tcgen05.mma / tcgen05.commit / cp.async.bulk take their operands from UNIFORM registers.  Guarded by a per-thread
+// condition (`threadIdx.x == 0`, `lane == 0`) the compiler cannot prove the operands warp-uniform and wraps EVERY such
+// instruction in a loop over the active threads (SASS: VOTEU / ELECT / R2UR.BROADCAST / UTCHMMA / BRA.U.ANY), ~120 clocks
+// per MMA whatever its shape (profiles/r01_mma_issue_rate.md).  Guarded by `elect.sync` inside a warp-uniform branch the
+// operands stay in uniform registers and consecutive MMAs issue back to back (profiles/r02_mma_issue_rate.md).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.b32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// warp index as a value the compiler knows to be the same in every lane
+__device__ __forceinline__ int warp_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 // ---- mbarrier -----------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");

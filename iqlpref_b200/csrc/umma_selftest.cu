@@ -78,7 +78,29 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int mode, int n, int 
   const uint32_t tmem = tmem_slot;
   // mode bit 0: A from tensor memory; bit 1: two issuing warps (accumulators 128 columns apart, n <= 128)
   const int issuers = (mode & 2) ? 2 : 1;
-  if ((threadIdx.x & 31) == 0 && warp < issuers) {
+  if (mode & 4) {  // issue guarded by elect.sync inside a warp-uniform branch (umma.cuh: elect_one)
+    if (warp_uniform() < issuers) {
+      if (elect_one()) {
+        const int wu = (int)(threadIdx.x >> 5);
+        const uint32_t idesc = instr_desc_bf16(n, 0, 0);
+        const Operand a = operand_k_major(a_s, 128, 0), b = operand_k_major(b_s, n, 0);
+        const uint32_t acc = tmem + 128u * (uint32_t)wu, at = tmem + 256u + 64u * (uint32_t)wu;
+        const long long t0 = clock64();
+        for (int i = 0; i < count; ++i) {
+          if ((mode & 1) == 0) mma_bf16(acc, a.desc(i & 3), b.desc(i & 3), idesc, i > 0);
+          else mma_bf16_ts(acc, at + 8u * (uint32_t)(i & 7), b.desc(i & 3), idesc, i > 0);
+        }
+        const long long t1 = clock64();
+        mma_commit(bar);
+        mbar_wait(bar, 0);
+        const long long t2 = clock64();
+        if (wu == 0) {
+          out[0] = (unsigned long long)(t1 - t0);
+          out[1] = (unsigned long long)(t2 - t0);
+        }
+      }
+    }
+  } else if ((threadIdx.x & 31) == 0 && warp < issuers) {
     const uint32_t idesc = instr_desc_bf16(n, 0, 0);
     const Operand a = operand_k_major(a_s, 128, 0), b = operand_k_major(b_s, n, 0);
     const uint32_t acc = tmem + 128u * (uint32_t)warp, at = tmem + 256u + 64u * (uint32_t)warp;
@@ -109,7 +131,7 @@ extern "C" int iqlb_selftest_mma_rate(int32_t a_from_tmem, int32_t n, int32_t co
                                       void* stream) {
   IQLB_REQUIRE(clocks_out != nullptr, "null pointer");
   IQLB_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0 && count >= 1, "n multiple of 16 in [16,256]");
-  IQLB_REQUIRE(a_from_tmem >= 0 && a_from_tmem <= 3 && (!(a_from_tmem & 2) || n <= 128), "mode");
+  IQLB_REQUIRE(a_from_tmem >= 0 && a_from_tmem <= 7 && (!(a_from_tmem & 2) || n <= 128), "mode");
   const size_t smem = 16384 + 32768 + 1024;
   IQLB_CUDA(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   umma_rate_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(a_from_tmem, n, count, clocks_out);

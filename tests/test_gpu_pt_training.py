@@ -50,13 +50,18 @@ def tb(batch):
     return [torch.from_numpy(np.asarray(x)) for x in batch]
 
 
-def assert_grads_close(got, want, rel=1e-3):
+def assert_grads_close(got, want, rel=1e-3, outliers=0.0):
+    """`outliers`: fraction of a tensor's elements that may miss the bar by up to 3x (split-bf16 with dropout: a hidden unit
+    whose pre-activation is within rounding of 0 switches its ReLU between the two arithmetics)."""
     floor = max(float(np.abs(np.asarray(g)).max()) for g in want.values())
     assert set(got) == set(want)
     for k, w in want.items():
         w = np.asarray(w)
         g = got[k].detach().cpu().numpy()
-        np.testing.assert_allclose(g, w, rtol=0, atol=rel * max(float(np.abs(w).max()), 1e-3 * floor) + 1e-9, err_msg=k)
+        atol = rel * max(float(np.abs(w).max()), 1e-3 * floor) + 1e-9
+        d = np.abs(g - w)
+        assert d.max() <= (3 * atol if outliers else atol), (k, float(d.max()), atol)
+        assert np.sum(d > atol) <= outliers * d.size, (k, int(np.sum(d > atol)))
 
 
 def assert_weights_close(got, want, g0, K, lr=3e-4):
@@ -144,7 +149,8 @@ def test_pt_step_matches_oracle_with_injected_masks(shape, drops, precision, rel
             loss, acc, grad = tr.loss_and_grad(tb(batch), training=True)
             assert loss == pytest.approx(want_loss, rel=rel_l)
             assert acc == pytest.approx(want_acc, abs=1e-7)
-            assert_grads_close(tr.grad_dict(grad), {k_: v.numpy() for k_, v in want_g.items()}, rel=rel_g)
+            assert_grads_close(tr.grad_dict(grad), {k_: v.numpy() for k_, v in want_g.items()}, rel=rel_g,
+                               outliers=0.0 if precision == "fp32" else 1e-3)
             g_first = want_g
         want = orc.train(batch, masks)
         got = tr.train(tb(batch))

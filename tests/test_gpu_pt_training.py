@@ -51,7 +51,7 @@ def tb(batch):
 
 
 def assert_grads_close(got, want, rel=1e-3, outliers=0.0):
-    """`outliers`: fraction of a tensor's elements that may miss the bar by up to 3x (split-bf16 with dropout: a hidden unit
+    """`outliers`: fraction of a tensor's elements (at least one) that may miss the bar by up to 3x (split-bf16: a hidden unit
     whose pre-activation is within rounding of 0 switches its ReLU between the two arithmetics)."""
     floor = max(float(np.abs(np.asarray(g)).max()) for g in want.values())
     assert set(got) == set(want)
@@ -61,7 +61,7 @@ def assert_grads_close(got, want, rel=1e-3, outliers=0.0):
         atol = rel * max(float(np.abs(w).max()), 1e-3 * floor) + 1e-9
         d = np.abs(g - w)
         assert d.max() <= (3 * atol if outliers else atol), (k, float(d.max()), atol)
-        assert np.sum(d > atol) <= outliers * d.size, (k, int(np.sum(d > atol)))
+        assert np.sum(d > atol) <= (max(1, outliers * d.size) if outliers else 0), (k, int(np.sum(d > atol)))
 
 
 def assert_weights_close(got, want, g0, K, lr=3e-4):

@@ -241,6 +241,16 @@ int iqlb_relabel_mlp_p(const float* x, int64_t n_rows, int32_t ldx, int32_t d_in
 int iqlb_reward_range(const float* rewards, const uint8_t* terminals, int64_t n, int32_t max_episode_steps,
                       double* min_max, float* trj_lens, void* stream);
 
+/* Allocation-free variant of iqlb_reward_range.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same result bit for bit; the scan scratch lives in a static device array of the library
+ * (256 KB on every GPU that loads it, held until exit) instead of the stream-ordered pool, so the call makes no
+ * cudaMalloc / cudaFree of any kind.  n > IQLB_REWARD_RANGE_STATIC_MAX_ROWS is rejected with IQLB_ERR_INVALID.  All calls on a
+ * device share the array: calls that overlap on the GPU (different streams) race - serialise them. */
+#define IQLB_REWARD_RANGE_STATIC_MAX_ROWS 16777216
+int iqlb_reward_range_static(const float* rewards, const uint8_t* terminals, int64_t n, int32_t max_episode_steps,
+                             double* min_max, float* trj_lens, void* stream);
+
 /* modify_reward (iql.py:363-401), in place on rewards[n] with numpy's op sequence and dtypes.
  * env_kind 0: halfcheetah / hopper / walker2d; 1: antmaze with normalize_reward 0..7 (other environments are not
  * touched by the reference: do not call). */

@@ -70,6 +70,7 @@ _SIGNATURES = {
                             C.c_int32, C.c_float, C.c_int32, _P], C.c_int),
     "iqlb_selftest_mma_rate": ([C.c_int32, C.c_int32, C.c_int32, _P, _P], C.c_int),
     "iqlb_reward_range": ([_P, _P, C.c_int64, C.c_int32, _P, _P, _P], C.c_int),
+    "iqlb_reward_range_static": ([_P, _P, C.c_int64, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_modify_reward": ([_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P], C.c_int),
     "iqlb_state_mean_std": ([_P, C.c_int64, C.c_int32, C.c_int32, C.c_float, _P, _P, _P], C.c_int),
     "iqlb_normalize_states": ([_P, C.c_int64, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),

@@ -212,6 +212,48 @@ extern "C" int iqlb_reward_range(const float* rewards, const uint8_t* terminals,
   return IQLB_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) --------------
+// Same launches as iqlb_reward_range, with the scratch (blk_last[nb] | carry[nb] | range[3]) in a file-scope device array
+// instead of cudaMallocAsync: for callers that may not allocate (CUDA graph capture, tight serving loops).  256 KB per GPU
+// that loads the library, held until exit.  Every call on a device shares it: calls that overlap on the GPU race.
+static constexpr int64_t kStaticMaxRows = IQLB_REWARD_RANGE_STATIC_MAX_ROWS;
+static constexpr int kStaticMaxBlocks = (int)((kStaticMaxRows + kScanBlock - 1) / kScanBlock);
+static __device__ __align__(256) long long g_range_scratch[2 * kStaticMaxBlocks + 3];
+
+extern "C" int iqlb_reward_range_static(const float* rewards, const uint8_t* terminals, int64_t n, int32_t max_episode_steps,
+                                        double* min_max, float* trj_lens, void* stream) {
+  IQLB_REQUIRE(rewards && terminals && min_max, "null pointer");
+  IQLB_REQUIRE(n >= 1 && max_episode_steps >= 1, "empty dataset / episode cap");
+  if (n > kStaticMaxRows)
+    return fail(IQLB_ERR_INVALID, "invalid argument: iqlb_reward_range_static handles at most %s%lld rows (use iqlb_reward_range)",
+                "", (long long)kStaticMaxRows);
+  // The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that
+  // device current (the caller's), and cached.
+  constexpr int kMaxDev = 64;
+  static long long* dev_ptr[kMaxDev] = {};
+  int dev = 0;
+  IQLB_CUDA(cudaGetDevice(&dev));
+  IQLB_REQUIRE(dev >= 0 && dev < kMaxDev, "device ordinal");
+  if (dev_ptr[dev] == nullptr) {
+    long long* p = nullptr;
+    IQLB_CUDA(cudaGetSymbolAddress((void**)&p, g_range_scratch));
+    dev_ptr[dev] = p;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = (int)((n + kScanBlock - 1) / kScanBlock);
+  long long *blk_last = dev_ptr[dev], *carry = blk_last + nb;
+  unsigned long long* range = reinterpret_cast<unsigned long long*>(blk_last + 2 * nb);
+  // nothing of the previous call survives: range_init rewrites range[3], the two scans write all nb entries they read
+  range_init_kernel<<<1, 1, 0, st>>>(range);
+  last_terminal_kernel<<<nb, kScanBlock, 0, st>>>(terminals, n, blk_last);
+  carry_scan_kernel<<<1, 1024, 0, st>>>(blk_last, nb, carry);
+  episode_walk_kernel<<<nb, kScanBlock, 0, st>>>(rewards, terminals, n, max_episode_steps, carry, range, trj_lens);
+  range_finish_kernel<<<1, 1, 0, st>>>(range, min_max);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(IQLB_ERR_CUDA, "iqlb_reward_range_static: %s", cudaGetErrorString(e));
+  return IQLB_OK;
+}
+
 extern "C" int iqlb_modify_reward(float* rewards, const uint8_t* terminals, int64_t n, int32_t env_kind,
                                   int32_t normalize_reward, int32_t max_episode_steps, void* stream) {
   IQLB_REQUIRE(rewards && terminals, "null pointer");

@@ -134,7 +134,8 @@ __global__ void __launch_bounds__(128) mr_colsum_kernel(const float* __restrict_
   const int64_t r0 = (int64_t)blockIdx.x * chunk_rows;
   const int64_t r1 = r0 + chunk_rows < M ? r0 + chunk_rows : M;
   float* d = dst + (int64_t)blockIdx.x * plen;
-  for (int j = threadIdx.x; j < ncols + (rs_sum ? 1 : 0); j += blockDim.x) {
+  // (gridDim.y column tiles: the preference transformer's 768 / 1024-wide layers would leave 25-50 blocks on 148 SMs)
+  for (int j = blockIdx.y * blockDim.x + threadIdx.x; j < ncols + (rs_sum ? 1 : 0); j += blockDim.x * gridDim.y) {
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     if (j < ncols) {
       int64_t m = r0;
@@ -203,7 +204,8 @@ int launch_bt_loss(const float* pred, const float* m1, const float* m2, const fl
 
 int launch_colsum(const float* X, int ld, int ncols, const float* rs, int rs_sum, int64_t M, int chunk_rows, int n_chunks,
                   float* dst, int64_t plen, cudaStream_t st) {
-  mr_colsum_kernel<<<n_chunks, 128, 0, st>>>(X, ld, ncols, rs, rs_sum, M, chunk_rows, dst, plen);
+  const int col_tiles = (ncols + (rs_sum ? 1 : 0) + 127) / 128;
+  mr_colsum_kernel<<<dim3(n_chunks, col_tiles), 128, 0, st>>>(X, ld, ncols, rs, rs_sum, M, chunk_rows, dst, plen);
   IQLB_LAUNCH_CHECK();
   return IQLB_OK;
 }

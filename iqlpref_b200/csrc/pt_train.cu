@@ -82,6 +82,8 @@ __global__ void __launch_bounds__(256) ptt_ln_fwd_kernel(int E, float eps, const
 
 // LayerNorm backward over a block of rows.  dy (optionally through a dropout mask) -> dx (written or accumulated);
 // partial[block][0:E] = sum_rows dy * xhat (d gain), partial[block][E:2E] = sum_rows dy (d bias).
+// (PM = upper bound of E / 32 the register arrays are sized for: at PM = 16 the kernel needs 162 registers)
+template <int PM>
 __global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __restrict__ g, const float* dy,
                                                          int64_t dy_stride, PtDrop drop, const float* __restrict__ xhat,
                                                          const float* __restrict__ rstd, int64_t n_rows, int rows_per_block,
@@ -92,15 +94,15 @@ __global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __r
   const int per = E / 32;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
   const int64_t r1 = r0 + rows_per_block < n_rows ? r0 + rows_per_block : n_rows;
-  float ag[kPtMaxPerLane], ab[kPtMaxPerLane], gv[kPtMaxPerLane];
+  float ag[PM], ab[PM], gv[PM];
 #pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c) { ag[c] = 0.f; ab[c] = 0.f; gv[c] = c < per ? __ldg(g + lane + 32 * c) : 0.f; }
+  for (int c = 0; c < PM; ++c) { ag[c] = 0.f; ab[c] = 0.f; gv[c] = c < per ? __ldg(g + lane + 32 * c) : 0.f; }
   const float invE = 1.0f / (float)E;
   for (int64_t r = r0 + warp; r < r1; r += 8) {
-    float d[kPtMaxPerLane], xh[kPtMaxPerLane];
+    float d[PM], xh[PM];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int c = 0; c < kPtMaxPerLane; ++c) {
+    for (int c = 0; c < PM; ++c) {
       if (c < per) {
         const int col = lane + 32 * c;
         d[c] = dy[r * dy_stride + col] * drop_factor(drop, r * E + col);
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __r
     s2 = warp_sum(s2) * invE;
     const float rs = rstd[r];
 #pragma unroll
-    for (int c = 0; c < kPtMaxPerLane; ++c) {
+    for (int c = 0; c < PM; ++c) {
       if (c < per) {
         const int col = lane + 32 * c;
         const float o = rs * (d[c] - s1 - xh[c] * s2);
@@ -126,7 +128,7 @@ __global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __r
     }
   }
 #pragma unroll
-  for (int c = 0; c < kPtMaxPerLane; ++c) {
+  for (int c = 0; c < PM; ++c) {
     if (c < per) {
       red[warp * 2 * E + lane + 32 * c] = ag[c];
       red[warp * 2 * E + E + lane + 32 * c] = ab[c];
@@ -428,36 +430,49 @@ __global__ void ptt_relu_mask_kernel(float* __restrict__ d, const float* __restr
     if (!(z[e] > 0.f)) d[e] = 0.f;
 }
 
-// Gradient of timestep_embed (pref_trans.py:275-278: both tokens of a step add row ts of the table): one block per table
-// row v sums du[2 i] + du[2 i + 1] over the positions i with ts[i] == v, in index order (deterministic scatter-add).
+// Gradient of timestep_embed (pref_trans.py:275-278: both tokens of a step add row ts of the table).  Deterministic
+// scatter-add in two levels: block (v, c) sums du[2 i] + du[2 i + 1] over the positions i of chunk c with ts[i] == v, in index
+// order, into partial[c][v]; the Adam kernel adds the chunks in a fixed order.  (One block per table row walking all
+// positions took 1.2 ms: the padded positions all carry ts = 0, thousands of dependent row loads in one block.)
+constexpr int kTembChunk = 1024;
 __global__ void __launch_bounds__(256) ptt_temb_grad_kernel(int E, const int32_t* __restrict__ ts, int64_t n_pos,
-                                                            const float* __restrict__ du, float* __restrict__ gtemb) {
-  __shared__ int flag[256];
-  const int v = blockIdx.x;
-  float acc[2] = {0.f, 0.f};  // E <= 512: columns threadIdx.x, threadIdx.x + 256
-  for (int64_t base = 0; base < n_pos; base += 256) {
+                                                            const float* __restrict__ du, float* __restrict__ partial,
+                                                            int64_t plen) {
+  __shared__ int list[kTembChunk];
+  __shared__ int wcount[8];
+  __shared__ int n_list;
+  const int v = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t p0 = (int64_t)blockIdx.y * kTembChunk;
+  const int64_t p1 = p0 + kTembChunk < n_pos ? p0 + kTembChunk : n_pos;
+  if (threadIdx.x == 0) n_list = 0;
+  __syncthreads();
+  for (int64_t base = p0; base < p1; base += 256) {  // ordered compaction of the matching positions
     const int64_t idx = base + threadIdx.x;
-    const int match = idx < n_pos && ts[idx] == v;
-    flag[threadIdx.x] = match;
-    if (__syncthreads_or(match)) {
-      const int lim = (int)(n_pos - base < 256 ? n_pos - base : 256);
-      for (int k = 0; k < lim; ++k) {
-        if (flag[k]) {
-          const float* r = du + (base + k) * 2 * E;
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            const int col = threadIdx.x + 256 * c;
-            if (col < E) acc[c] += r[col] + r[E + col];
-          }
-        }
-      }
-    }
+    const bool match = idx < p1 && ts[idx] == v;
+    const unsigned bal = __ballot_sync(0xffffffffu, match);
+    if (lane == 0) wcount[warp] = __popc(bal);
     __syncthreads();
+    int off = n_list;
+    for (int w = 0; w < warp; ++w) off += wcount[w];
+    if (match) list[off + __popc(bal & ((1u << lane) - 1u))] = (int)(idx - p0);
+    __syncthreads();
+    if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < 8; ++w) t += wcount[w]; n_list += t; }
+    __syncthreads();
+  }
+  const int nl = n_list;
+  float acc[2] = {0.f, 0.f};  // E <= 512: columns threadIdx.x, threadIdx.x + 256
+  for (int k = 0; k < nl; ++k) {
+    const float* r = du + (p0 + list[k]) * 2 * E;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int col = threadIdx.x + 256 * c;
+      if (col < E) acc[c] += r[col] + r[E + col];
+    }
   }
 #pragma unroll
   for (int c = 0; c < 2; ++c) {
     const int col = threadIdx.x + 256 * c;
-    if (col < E) gtemb[(int64_t)v * E + col] = acc[c];
+    if (col < E) partial[(int64_t)blockIdx.y * plen + (int64_t)v * E + col] = acc[c];
   }
 }
 
@@ -482,7 +497,7 @@ struct iqlb_pt_trainer {
   float *hid = nullptr, *xhat_f = nullptr, *rstd_f = nullptr, *y = nullptr, *ws = nullptr, *val = nullptr;
   // backward scratch
   float *rowgrad = nullptr, *Cs = nullptr, *dy = nullptr, *dx = nullptr, *tmpA = nullptr, *tmpB = nullptr, *dbig = nullptr;
-  float *dST = nullptr, *PdT = nullptr, *gtemb = nullptr, *partial = nullptr, *zero_bias = nullptr;
+  float *dST = nullptr, *PdT = nullptr, *partial = nullptr, *zero_bias = nullptr;
   float *out2 = nullptr, *pair_out = nullptr;
   unsigned int* counter = nullptr;
   GemmTask* d_tasks = nullptr;  // [n_groups][max_chunks] weight-gradient tasks
@@ -500,7 +515,7 @@ static void ptt_free(iqlb_pt_trainer* h) {
 
 static constexpr int kPttMaxChunks = 296;
 static constexpr int kPttChunkRows = 512;
-static constexpr int kLnRowsPerBlock = 64;
+static constexpr int kLnRowsPerBlock = 32;
 
 static inline int ptt_chunks(int64_t rows, int& chunk_rows) {
   int n_chunks = (int)((rows + kPttChunkRows - 1) / kPttChunkRows);
@@ -558,7 +573,6 @@ extern "C" int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, 
   h->val = alloc(nT);
   h->rowgrad = alloc(nT); h->Cs = alloc(nT * T); h->dy = alloc(nT * ldy); h->dx = alloc(M * E); h->tmpA = alloc(M * E);
   h->tmpB = alloc(M * E); h->dbig = alloc(M * bigc); h->dST = alloc(n * H * T2 * T2); h->PdT = alloc(n * H * T2 * T2);
-  h->gtemb = alloc((int64_t)P.n_ts * E);
   h->zero_bias = alloc(bigc > ldy ? bigc : ldy);
   h->out2 = alloc(2); h->pair_out = alloc(2 * n); h->counter = (unsigned int*)alloc(1);
   // weight-gradient partials: the largest Linear (+ bias), or the LayerNorm partials [M / 64][2E]
@@ -571,7 +585,10 @@ extern "C" int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, 
   int cr = 0;
   const int64_t need_w = (int64_t)ptt_chunks(M, cr) * plen;
   const int64_t need_ln = ((M + kLnRowsPerBlock - 1) / kLnRowsPerBlock) * 2 * E;
-  h->partial = alloc(need_w > need_ln ? need_w : need_ln);
+  const int64_t need_te = ((nT + kTembChunk - 1) / kTembChunk) * P.n_ts * E;
+  int64_t need = need_w > need_ln ? need_w : need_ln;
+  if (need_te > need) need = need_te;
+  h->partial = alloc(need);
   h->n_groups = 3 + 4 * L;
   if (ok) {
     void* p = nullptr;
@@ -819,8 +836,12 @@ extern "C" int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_
   auto ln_bwd = [&](const float* g_ptr, int64_t g_off, const float* dyp, int64_t dy_stride, const PtDrop& drop, const float* xhat,
                     const float* rstd, int64_t rows, float* dxp, int64_t dx_stride, int accumulate) -> int {
     const int blocks = (int)((rows + kLnRowsPerBlock - 1) / kLnRowsPerBlock);
-    ptt_ln_bwd_kernel<<<blocks, 256, (size_t)16 * E * sizeof(float), st>>>(E, g_ptr, dyp, dy_stride, drop, xhat, rstd, rows,
-                                                                          kLnRowsPerBlock, dxp, dx_stride, accumulate, h->partial);
+    if (E <= 256)
+      ptt_ln_bwd_kernel<8><<<blocks, 256, (size_t)16 * E * sizeof(float), st>>>(E, g_ptr, dyp, dy_stride, drop, xhat, rstd, rows,
+                                                                               kLnRowsPerBlock, dxp, dx_stride, accumulate, h->partial);
+    else
+      ptt_ln_bwd_kernel<kPtMaxPerLane><<<blocks, 256, (size_t)16 * E * sizeof(float), st>>>(
+          E, g_ptr, dyp, dy_stride, drop, xhat, rstd, rows, kLnRowsPerBlock, dxp, dx_stride, accumulate, h->partial);
     IQLB_LAUNCH_CHECK();
     return reduce_adam(g_off, 2 * E, blocks, h->partial);
   };
@@ -880,9 +901,10 @@ extern "C" int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_
   // ---- embeddings: dropout -> stacked LayerNorm -> state / action Linear + timestep table -------------------------------
   if ((rc = ln_bwd(w + P.slg, P.slg, h->dx, E, make_drop(h, h->p_embd, 0, adam_step, tr), h->xhat_s, h->rstd_s, M, h->dx, E, 0)))
     return rc;
-  ptt_temb_grad_kernel<<<P.n_ts, 256, 0, st>>>(E, h->Ts, nT, h->dx, h->gtemb);
+  const int te_chunks = (int)((nT + kTembChunk - 1) / kTembChunk);
+  ptt_temb_grad_kernel<<<dim3(P.n_ts, te_chunks), 256, 0, st>>>(E, h->Ts, nT, h->dx, h->partial, (int64_t)P.n_ts * E);
   IQLB_LAUNCH_CHECK();
-  if ((rc = reduce_adam(P.temb, (int64_t)P.n_ts * E, 1, h->gtemb))) return rc;
+  if ((rc = reduce_adam(P.temb, (int64_t)P.n_ts * E, te_chunks, h->partial))) return rc;
   if ((rc = weight_grad(0))) return rc;
   if ((rc = weight_grad(1))) return rc;
   return IQLB_OK;

@@ -321,6 +321,24 @@ int launch_grouped_gemm_tc_bwd_weight(const GemmTask* d_tasks, int n_tasks, int 
   return IQLB_OK;
 }
 
+// Grouped launch of any arrangement over a device-resident task array (every task at most maxM x maxN): the batched small
+// GEMMs of the preference transformer's attention (Q K^T, P V and their gradients per (sequence, head), pt_train.cu).
+int launch_grouped_gemm_tc(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, cudaStream_t stream) {
+  if (mode == GEMM_BWD_WEIGHT) return launch_grouped_gemm_tc_bwd_weight(d_tasks, n_tasks, maxM, maxN, stream);
+  static bool attr = false;
+  if (!attr) {
+    IQLB_CUDA(cudaFuncSetAttribute(gemm_tc_grouped_kernel<GEMM_LINEAR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gtc::kSmem));
+    IQLB_CUDA(cudaFuncSetAttribute(gemm_tc_grouped_kernel<GEMM_FWD_KN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gtc::kSmem));
+    attr = true;
+  }
+  const dim3 grid((unsigned)(((maxM + gtc::BM - 1) / gtc::BM) * ((maxN + gtc::BN - 1) / gtc::BN)), (unsigned)n_tasks);
+  if (mode == GEMM_LINEAR) gemm_tc_grouped_kernel<GEMM_LINEAR><<<grid, 256, gtc::kSmem, stream>>>(d_tasks);
+  else if (mode == GEMM_FWD_KN) gemm_tc_grouped_kernel<GEMM_FWD_KN><<<grid, 256, gtc::kSmem, stream>>>(d_tasks);
+  else return fail(IQLB_ERR_UNSUPPORTED, "launch_grouped_gemm_tc: unsupported mode%s", "");
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
+}
+
 }  // namespace iqlb
 
 using namespace iqlb;

@@ -96,6 +96,7 @@ int launch_gemm(GemmMode mode, const GemmTask& t, cudaStream_t stream);
 bool gemm_tc_eligible(GemmMode mode, const GemmTask& t);
 int launch_gemm_tc(GemmMode mode, const GemmTask& t, cudaStream_t stream);
 int launch_grouped_gemm_tc_bwd_weight(const GemmTask* d_tasks, int n_tasks, int M, int N, cudaStream_t stream);
+int launch_grouped_gemm_tc(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, cudaStream_t stream);
 int launch_grouped_gemm(GemmMode mode, const GemmTask* d_tasks, int n_tasks, int maxM, int maxN, bool narrow_n,
                         cudaStream_t stream);
 

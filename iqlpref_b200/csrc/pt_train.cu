@@ -12,9 +12,9 @@
 //
 // fp32 throughout (the reference trains in fp32).  Every Linear - forward, data gradient, weight gradient - is a GEMM
 // through launch_gemm / the grouped weight-gradient launchers: fp32 FFMA, or with precision 1 split-bf16 on the tensor
-// cores (gemm_tc.cu).  LayerNorm / softmax / dropout are warp-per-row kernels.  The attention probabilities of the forward
-// pass are kept ([n, H, 2T, 2T]) and the backward pass is two kernels per layer: one walks the queries (dS, dQ; dS and the
-// dropped-out probabilities leave transposed), one walks the keys (dK, dV).
+// cores (gemm_tc.cu).  So are the attention products (Q K^T, P V and their four gradients per (sequence, head), the preference
+// head's per sequence): grouped launches over task tables built once per handle.  LayerNorm / softmax / dropout are
+// warp-per-row kernels.  The attention probabilities of the forward pass are kept ([n, H, 2T, 2T]).
 //
 // Dropout (embd / attention / the two residual sites of a block): the reference draws its masks from torch's CUDA generator,
 // which cannot be mirrored; element e (row-major index in the tensor the mask multiplies) of site s at Adam step k is KEPT iff
@@ -144,273 +144,158 @@ __global__ void __launch_bounds__(256) ptt_ln_bwd_kernel(int E, const float* __r
 }
 
 // ------------------------------------------------------------------------------------------------
-// Causal self-attention, training mode (pref_trans.py:118-140): like pt_attn_full_kernel (relabel_pt.cu), and the softmax
-// probabilities P[i][j] (j <= i) are kept; the output uses P * dropout mask.  grid (sequences, heads), a warp owns a query.
+// Causal self-attention (pref_trans.py:118-140).  The products are batched GEMMs over the (sequence, head) pairs
+// (S = Q K^T, O = Pd V; backward dPd = dO V^T, dQ = dS K, dK = dS^T Q, dV = Pd^T dO - grouped launches, on the tensor cores
+// in split-bf16 mode); the kernels below are the row-wise softmax between them.  Score buffers are [n][H][2T][2T].
+// Forward: P[i][j] = softmax_{j <= i}(S[i][j] / sqrt(dh) + (1 - m[j]) * -10000), 0 above the diagonal (kept for the
+// backward pass); Pd = P * dropout mask (a second buffer when dropout is on, else Pd aliases P).  One warp per row.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ptt_attn_fwd_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
-                                                           const float* __restrict__ maskbuf, float* __restrict__ out,
-                                                           float* __restrict__ Pbuf, PtDrop drop) {
-  extern __shared__ float sh[];
-  const int w = blockIdx.x, h = blockIdx.y;
+__global__ void __launch_bounds__(256) ptt_softmax_fwd_kernel(int T2, int H, float scale, float* S, float* Pd,
+                                                              const float* __restrict__ maskbuf, int64_t n_rows, PtDrop drop) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ldk = dh + 1;
-  float* Ks = sh;
-  float* Vs = Ks + (size_t)T2 * ldk;
-  float* qs = Vs + (size_t)T2 * ldk;  // [8][dh]
-  float* ps = qs + 8 * dh;            // [8][T2]
-  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
-  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
-    const int j = i / dh, d = i % dh;
-    Ks[j * ldk + d] = base[(int64_t)j * 3 * E + E + d];
-    Vs[j * ldk + d] = base[(int64_t)j * 3 * E + 2 * E + d];
-  }
-  __syncthreads();
-  const float scale = rsqrtf((float)dh);
-  const float* mk = maskbuf + (int64_t)w * (T2 / 2);
+  const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+  if (r >= n_rows) return;
+  const int i = (int)(r % T2);
+  const int64_t w = r / T2 / H;
+  const float* mk = maskbuf + w * (T2 / 2);
+  float* srow = S + r * T2;
   const int nchunk = (T2 + 31) / 32;
-  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
-  float* q = qs + warp * dh;
-  float* p = ps + warp * T2;
-  for (int i = warp; i < T2; i += 8) {
-    for (int d = lane; d < dh; d += 32) q[d] = base[(int64_t)i * 3 * E + d];
-    __syncwarp();
-    float s[kPtMaxKeyChunks];
-    float mx = -INFINITY;
+  float s[kPtMaxKeyChunks];
+  float mx = -INFINITY;
 #pragma unroll
-    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
-      if (c < nchunk) {
-        const int j = lane + 32 * c;
-        float v = -INFINITY;
-        if (j < T2 && j <= i) {
-          float acc = 0.f;
-          for (int d = 0; d < dh; ++d) acc = fmaf(q[d], Ks[j * ldk + d], acc);
-          v = acc * scale + (1.0f - mk[j >> 1]) * -10000.0f;
-        }
-        s[c] = v;
-        mx = fmaxf(mx, v);
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    float sum = 0.f;
-#pragma unroll
-    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
-      if (c < nchunk) {
-        const float e = (s[c] == -INFINITY) ? 0.f : expf(s[c] - mx);
-        s[c] = e;
-        sum += e;
-      }
-    }
-    sum = warp_sum(sum);
-    const float inv = 1.0f / sum;
-#pragma unroll
-    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    if (c < nchunk) {
       const int j = lane + 32 * c;
-      if (c < nchunk && j < T2) {
-        const float pv = s[c] * inv;
-        const int64_t e = pbase + (int64_t)i * T2 + j;
-        if (j <= i) {
-          Pbuf[e] = pv;
-          p[j] = pv * drop_factor(drop, e);
-        } else {
-          p[j] = 0.f;
-        }
-      }
-    }
-    __syncwarp();
-    for (int d = lane; d < dh; d += 32) {
-      float acc = 0.f;
-      for (int j = 0; j <= i; ++j) acc = fmaf(p[j], Vs[j * ldk + d], acc);
-      out[((int64_t)w * T2 + i) * E + h * dh + d] = acc;
-    }
-    __syncwarp();
-  }
-}
-
-// Backward of the attention, query walk.  dO[i] -> dPd[j] = dO[i].V[j]; dP = dPd * mask; dS = P (dP - sum_j P dP);
-// dQ[i] = scale sum_j dS[j] K[j].  dS and Pd = P * mask leave TRANSPOSED ([j][i]) for the key walk.
-__global__ void __launch_bounds__(256) ptt_attn_bwd_q_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
-                                                             const float* __restrict__ Pbuf, const float* __restrict__ dO,
-                                                             float* __restrict__ dST, float* __restrict__ PdT,
-                                                             float* __restrict__ dqkv, PtDrop drop) {
-  extern __shared__ float sh[];
-  const int w = blockIdx.x, h = blockIdx.y;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ldk = dh + 1;
-  float* Ks = sh;
-  float* Vs = Ks + (size_t)T2 * ldk;
-  float* dos = Vs + (size_t)T2 * ldk;  // [8][dh]
-  float* dss = dos + 8 * dh;           // [8][T2]
-  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
-  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
-    const int j = i / dh, d = i % dh;
-    Ks[j * ldk + d] = base[(int64_t)j * 3 * E + E + d];
-    Vs[j * ldk + d] = base[(int64_t)j * 3 * E + 2 * E + d];
-  }
-  __syncthreads();
-  const float scale = rsqrtf((float)dh);
-  const int nchunk = (T2 + 31) / 32;
-  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
-  float* dor = dos + warp * dh;
-  float* ds = dss + warp * T2;
-  for (int i = warp; i < T2; i += 8) {
-    for (int d = lane; d < dh; d += 32) dor[d] = dO[((int64_t)w * T2 + i) * E + h * dh + d];
-    __syncwarp();
-    float dp[kPtMaxKeyChunks], pv[kPtMaxKeyChunks];
-    float rowsum = 0.f;
-#pragma unroll
-    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
-      dp[c] = 0.f; pv[c] = 0.f;
-      const int j = lane + 32 * c;
-      if (c < nchunk && j <= i) {
-        float acc = 0.f;
-        for (int d = 0; d < dh; ++d) acc = fmaf(dor[d], Vs[j * ldk + d], acc);
-        const int64_t e = pbase + (int64_t)i * T2 + j;
-        const float f = drop_factor(drop, e);
-        pv[c] = Pbuf[e];
-        dp[c] = acc * f;
-        rowsum = fmaf(pv[c], dp[c], rowsum);
-        PdT[pbase + (int64_t)j * T2 + i] = pv[c] * f;
-      }
-    }
-    rowsum = warp_sum(rowsum);
-#pragma unroll
-    for (int c = 0; c < kPtMaxKeyChunks; ++c) {
-      const int j = lane + 32 * c;
-      if (c < nchunk && j <= i) {
-        const float v = pv[c] * (dp[c] - rowsum);
-        ds[j] = v;
-        dST[pbase + (int64_t)j * T2 + i] = v;
-      }
-    }
-    __syncwarp();
-    for (int d = lane; d < dh; d += 32) {
-      float acc = 0.f;
-      for (int j = 0; j <= i; ++j) acc = fmaf(ds[j], Ks[j * ldk + d], acc);
-      dqkv[((int64_t)w * T2 + i) * 3 * E + h * dh + d] = acc * scale;
-    }
-    __syncwarp();
-  }
-}
-
-// Backward of the attention, key walk: dK[j] = scale sum_{i >= j} dS[i][j] Q[i], dV[j] = sum_{i >= j} Pd[i][j] dO[i]
-__global__ void __launch_bounds__(256) ptt_attn_bwd_kv_kernel(int T2, int E, int H, int dh, const float* __restrict__ qkv,
-                                                              const float* __restrict__ dO, const float* __restrict__ dST,
-                                                              const float* __restrict__ PdT, float* __restrict__ dqkv) {
-  extern __shared__ float sh[];
-  const int w = blockIdx.x, h = blockIdx.y;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ldk = dh + 1;
-  float* Qs = sh;
-  float* Os = Qs + (size_t)T2 * ldk;
-  float* rows = Os + (size_t)T2 * ldk;  // [8][2][T2]
-  const float* base = qkv + (int64_t)w * T2 * 3 * E + h * dh;
-  for (int i = threadIdx.x; i < T2 * dh; i += blockDim.x) {
-    const int j = i / dh, d = i % dh;
-    Qs[j * ldk + d] = base[(int64_t)j * 3 * E + d];
-    Os[j * ldk + d] = dO[((int64_t)w * T2 + j) * E + h * dh + d];
-  }
-  __syncthreads();
-  const float scale = rsqrtf((float)dh);
-  const int64_t pbase = ((int64_t)w * H + h) * T2 * T2;
-  float* a = rows + warp * 2 * T2;
-  float* b = a + T2;
-  for (int j = warp; j < T2; j += 8) {
-    for (int i = j + lane; i < T2; i += 32) {
-      a[i] = dST[pbase + (int64_t)j * T2 + i];
-      b[i] = PdT[pbase + (int64_t)j * T2 + i];
-    }
-    __syncwarp();
-    for (int d = lane; d < dh; d += 32) {
-      float dk = 0.f, dv = 0.f;
-      for (int i = j; i < T2; ++i) {
-        dk = fmaf(a[i], Qs[i * ldk + d], dk);
-        dv = fmaf(b[i], Os[i * ldk + d], dv);
-      }
-      float* o = dqkv + ((int64_t)w * T2 + j) * 3 * E + h * dh + d;
-      o[E] = dk * scale;
-      o[2 * E] = dv;
-    }
-    __syncwarp();
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// Preference-attention head, backward (pref_trans.py:303-320): y rows [q(P) | k(P) | v], full attention with the key-padding
-// bias only.  With w = softmax(s), ws[t] = sum_j w[t][j] v[j] and g[t] = dL/dws[t]:
-//   c[t][j] = w[t][j] g[t];  dv[j] = sum_t c[t][j];  ds[t][j] = c[t][j] (v[j] - ws[t]);
-//   dq[t] = scale sum_j ds[t][j] k[j];  dk[j] = scale sum_t ds[t][j] q[t].
-// grid (sequences); phase 1 a warp per query, phase 2 a warp per key; c goes through a global scratch [n][T][T].
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ptt_pref_attn_bwd_kernel(int T, int Pd, const float* __restrict__ y,
-                                                                const float* __restrict__ maskbuf,
-                                                                const float* __restrict__ gws, float* __restrict__ Cs,
-                                                                float* __restrict__ dy) {
-  extern __shared__ float sh[];  // ws [T] | per warp: sc [T]
-  const int n = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ld = 2 * Pd + 1;
-  const float* yb = y + (int64_t)n * T * ld;
-  float* dyb = dy + (int64_t)n * T * ld;
-  const float* mk = maskbuf + (int64_t)n * T;
-  float* cb = Cs + (int64_t)n * T * T;
-  float* wss = sh;
-  float* sc = sh + T + warp * T;
-  const float scale = rsqrtf((float)Pd);
-  for (int t = warp; t < T; t += 8) {
-    const float* q = yb + (int64_t)t * ld;
-    float mx = -INFINITY;
-    for (int j = 0; j < T; ++j) {
-      const float* k = yb + (int64_t)j * ld + Pd;
-      float acc = 0.f;
-      for (int d = lane; d < Pd; d += 32) acc = fmaf(q[d], k[d], acc);
-      acc = warp_sum(acc);
-      const float v = acc * scale + (1.0f - mk[j]) * -10000.0f;
-      if (lane == 0) sc[j] = v;
+      float v = -INFINITY;
+      if (j <= i) v = srow[j] * scale + (1.0f - mk[j >> 1]) * -10000.0f;
+      s[c] = v;
       mx = fmaxf(mx, v);
     }
-    __syncwarp();
-    float sum = 0.f, wsv = 0.f;
-    for (int j = lane; j < T; j += 32) {
-      const float e = expf(sc[j] - mx);
-      sum += e;
-      wsv = fmaf(e, yb[(int64_t)j * ld + 2 * Pd], wsv);
-    }
-    sum = warp_sum(sum);
-    wsv = warp_sum(wsv) / sum;
-    const float g = gws[(int64_t)n * T + t];
-    const float ginv = g / sum;
-    for (int j = lane; j < T; j += 32) {
-      const float c = expf(sc[j] - mx) * ginv;
-      cb[(int64_t)t * T + j] = c;
-      sc[j] = c * (yb[(int64_t)j * ld + 2 * Pd] - wsv);
-    }
-    if (lane == 0) wss[t] = wsv;
-    __syncwarp();
-    for (int d = lane; d < Pd; d += 32) {
-      float acc = 0.f;
-      for (int j = 0; j < T; ++j) acc = fmaf(sc[j], yb[(int64_t)j * ld + Pd + d], acc);
-      dyb[(int64_t)t * ld + d] = acc * scale;
-    }
-    __syncwarp();
   }
-  __syncthreads();
-  for (int j = warp; j < T; j += 8) {
-    const float vj = yb[(int64_t)j * ld + 2 * Pd];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    if (c < nchunk) {
+      const float e = (s[c] == -INFINITY) ? 0.f : expf(s[c] - mx);
+      s[c] = e;
+      sum += e;
+    }
+  }
+  const float inv = 1.0f / warp_sum(sum);
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    const int j = lane + 32 * c;
+    if (c < nchunk && j < T2) {
+      const float pv = s[c] * inv;  // 0 above the diagonal
+      srow[j] = pv;
+      if (Pd != S) Pd[r * T2 + j] = pv * drop_factor(drop, r * T2 + j);
+    }
+  }
+}
+
+// Backward: dS (in: dPd = dO V^T) <- scale * P * (dP - sum_j P dP) with dP = dPd * dropout mask; 0 above the diagonal.
+__global__ void __launch_bounds__(256) ptt_softmax_bwd_kernel(int T2, float scale, const float* __restrict__ P, float* dS,
+                                                              int64_t n_rows, PtDrop drop) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+  if (r >= n_rows) return;
+  const int i = (int)(r % T2);
+  const int nchunk = (T2 + 31) / 32;
+  float dp[kPtMaxKeyChunks], pv[kPtMaxKeyChunks];
+  float rowsum = 0.f;
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    dp[c] = 0.f; pv[c] = 0.f;
+    const int j = lane + 32 * c;
+    if (c < nchunk && j <= i) {
+      const int64_t e = r * T2 + j;
+      pv[c] = P[e];
+      dp[c] = dS[e] * drop_factor(drop, e);
+      rowsum = fmaf(pv[c], dp[c], rowsum);
+    }
+  }
+  rowsum = warp_sum(rowsum);
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    const int j = lane + 32 * c;
+    if (c < nchunk && j < T2) dS[r * T2 + j] = j <= i ? scale * pv[c] * (dp[c] - rowsum) : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Preference-attention head (pref_trans.py:303-320): y rows [q(P) | k(P) | v], full attention, key-padding bias only; the
+// products Q K^T, dS K and dS^T Q are grouped GEMMs per sequence.  Forward (one warp per query): W[t][j] = softmax_j(S / sqrt(P)
+// + (1 - m[j]) * -10000) (in place, kept), ws[t] = sum_j W[t][j] v[j].  Backward (one block per sequence), with g = dL/dws:
+// dS[t][j] = scale * W[t][j] g[t] (v[j] - ws[t]);  dv[j] = sum_t W[t][j] g[t] (written into dy).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ptt_pref_softmax_fwd_kernel(int T, int Pd, float scale, float* S,
+                                                                   const float* __restrict__ y,
+                                                                   const float* __restrict__ maskbuf, int64_t n_rows,
+                                                                   float* __restrict__ ws) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + warp;
+  if (r >= n_rows) return;
+  const int64_t n = r / T;
+  const int ld = 2 * Pd + 1;
+  const float* mk = maskbuf + n * T;
+  const float* vb = y + n * T * ld + 2 * Pd;
+  float* srow = S + r * T;
+  const int nchunk = (T + 31) / 32;
+  float s[kPtMaxKeyChunks];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    const int j = lane + 32 * c;
+    if (c < nchunk) {
+      s[c] = j < T ? srow[j] * scale + (1.0f - mk[j]) * -10000.0f : -INFINITY;
+      mx = fmaxf(mx, s[c]);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f, wsv = 0.f;
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    const int j = lane + 32 * c;
+    if (c < nchunk && j < T) {
+      const float e = expf(s[c] - mx);
+      s[c] = e;
+      sum += e;
+      wsv = fmaf(e, vb[(int64_t)j * ld], wsv);
+    }
+  }
+  sum = warp_sum(sum);
+  wsv = warp_sum(wsv);
+  const float inv = 1.0f / sum;
+#pragma unroll
+  for (int c = 0; c < kPtMaxKeyChunks; ++c) {
+    const int j = lane + 32 * c;
+    if (c < nchunk && j < T) srow[j] = s[c] * inv;
+  }
+  if (lane == 0) ws[r] = wsv * inv;
+}
+
+__global__ void __launch_bounds__(256) ptt_pref_softmax_bwd_kernel(int T, int Pd, float scale, const float* __restrict__ W,
+                                                                   const float* __restrict__ y, const float* __restrict__ ws,
+                                                                   const float* __restrict__ g, float* __restrict__ dS,
+                                                                   float* __restrict__ dy) {
+  const int n = blockIdx.x;
+  const int ld = 2 * Pd + 1;
+  const float* wb = W + (int64_t)n * T * T;
+  float* db = dS + (int64_t)n * T * T;
+  const float* vb = y + (int64_t)n * T * ld + 2 * Pd;
+  const float* gn = g + (int64_t)n * T;
+  const float* wsn = ws + (int64_t)n * T;
+  for (int e = threadIdx.x; e < T * T; e += blockDim.x) {
+    const int t = e / T, j = e - t * T;
+    db[e] = scale * wb[e] * gn[t] * (vb[(int64_t)j * ld] - wsn[t]);
+  }
+  for (int j = threadIdx.x; j < T; j += blockDim.x) {  // column sums, coalesced over j
     float dv = 0.f;
-    for (int t = lane; t < T; t += 32) {
-      const float c = cb[(int64_t)t * T + j];
-      sc[t] = c * (vj - wss[t]);
-      dv += c;
-    }
-    dv = warp_sum(dv);
-    if (lane == 0) dyb[(int64_t)j * ld + 2 * Pd] = dv;
-    __syncwarp();
-    for (int d = lane; d < Pd; d += 32) {
-      float acc = 0.f;
-      for (int t = 0; t < T; ++t) acc = fmaf(sc[t], yb[(int64_t)t * ld + d], acc);
-      dyb[(int64_t)j * ld + Pd + d] = acc * scale;
-    }
-    __syncwarp();
+    for (int t = 0; t < T; ++t) dv = fmaf(wb[(int64_t)t * T + j], gn[t], dv);
+    dy[((int64_t)n * T + j) * ld + 2 * Pd] = dv;
   }
 }
 
@@ -492,15 +377,23 @@ struct iqlb_pt_trainer {
   int32_t* Ts = nullptr;
   // forward state
   float *x = nullptr, *xhat_s = nullptr, *rstd_s = nullptr;
-  struct Layer { float *h0, *xhat0, *rstd0, *qkv, *Pb, *o, *h1, *xhat1, *rstd1, *z; };
+  struct Layer { float *h0, *xhat0, *rstd0, *qkv, *Pb, *Pd, *o, *h1, *xhat1, *rstd1, *z; };  // Pb: softmax, Pd: after dropout
   std::vector<Layer> layers;
   float *hid = nullptr, *xhat_f = nullptr, *rstd_f = nullptr, *y = nullptr, *ws = nullptr, *val = nullptr;
   // backward scratch
-  float *rowgrad = nullptr, *Cs = nullptr, *dy = nullptr, *dx = nullptr, *tmpA = nullptr, *tmpB = nullptr, *dbig = nullptr;
-  float *dST = nullptr, *PdT = nullptr, *partial = nullptr, *zero_bias = nullptr;
+  float *rowgrad = nullptr, *Sp = nullptr, *dy = nullptr, *dx = nullptr, *tmpA = nullptr, *tmpB = nullptr, *dbig = nullptr;
+  float *dS = nullptr, *dSp = nullptr, *partial = nullptr, *zero_bias = nullptr;
   float *out2 = nullptr, *pair_out = nullptr;
   unsigned int* counter = nullptr;
   GemmTask* d_tasks = nullptr;  // [n_groups][max_chunks] weight-gradient tasks
+  // Batched attention GEMMs, built once for n_max sequences (a launch over the first n * H tasks serves any batch size).
+  // Per layer kAttnArrays arrays of n_max * H tasks: 0 S = Q K^T | 1 O = Pd V | 2 O = P V (no attention dropout) |
+  // 3 dPd = dO V^T | 4 dQ = dS K | 5 dK = dS^T Q | 6 dV = Pd^T dO | 7 dV = P^T dO; then three arrays of n_max tasks for the
+  // preference head: S = Q K^T | dQ = dS K | dK = dS^T Q.
+  GemmTask* d_attn = nullptr;
+  static constexpr int kAttnArrays = 8;
+  GemmTask* attn_tasks(int layer, int which) const { return d_attn + ((size_t)layer * kAttnArrays + which) * n_max * P.H; }
+  GemmTask* pref_tasks(int which) const { return d_attn + (size_t)P.L * kAttnArrays * n_max * P.H + (size_t)which * n_max; }
   int n_groups = 0, max_chunks = 0;
   int64_t max_plen = 0;
   int tasks_n = -1;  // sequence count the task table was built for
@@ -566,13 +459,13 @@ extern "C" int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, 
   for (int l = 0; l < L; ++l) {
     auto& y = h->layers[l];
     y.h0 = alloc(M * E); y.xhat0 = alloc(M * E); y.rstd0 = alloc(M); y.qkv = alloc(M * 3 * E);
-    y.Pb = alloc(n * H * T2 * T2); y.o = alloc(M * E); y.h1 = alloc(M * E); y.xhat1 = alloc(M * E); y.rstd1 = alloc(M);
+    y.Pb = alloc(n * H * T2 * T2); y.Pd = alloc(n * H * T2 * T2); y.o = alloc(M * E); y.h1 = alloc(M * E); y.xhat1 = alloc(M * E); y.rstd1 = alloc(M);
     y.z = alloc(M * I);
   }
   h->hid = alloc(nT * E); h->xhat_f = alloc(nT * E); h->rstd_f = alloc(nT); h->y = alloc(nT * ldy); h->ws = alloc(nT);
   h->val = alloc(nT);
-  h->rowgrad = alloc(nT); h->Cs = alloc(nT * T); h->dy = alloc(nT * ldy); h->dx = alloc(M * E); h->tmpA = alloc(M * E);
-  h->tmpB = alloc(M * E); h->dbig = alloc(M * bigc); h->dST = alloc(n * H * T2 * T2); h->PdT = alloc(n * H * T2 * T2);
+  h->rowgrad = alloc(nT); h->Sp = alloc(nT * T); h->dy = alloc(nT * ldy); h->dx = alloc(M * E); h->tmpA = alloc(M * E);
+  h->tmpB = alloc(M * E); h->dbig = alloc(M * bigc); h->dS = alloc(n * H * T2 * T2); h->dSp = alloc(nT * T);
   h->zero_bias = alloc(bigc > ldy ? bigc : ldy);
   h->out2 = alloc(2); h->pair_out = alloc(2 * n); h->counter = (unsigned int*)alloc(1);
   // weight-gradient partials: the largest Linear (+ bias), or the LayerNorm partials [M / 64][2E]
@@ -595,9 +488,63 @@ extern "C" int iqlb_pt_trainer_create(const iqlb_pt_desc* d, int32_t pool_mean, 
     if (cudaMalloc(&p, (size_t)h->n_groups * h->max_chunks * sizeof(GemmTask)) != cudaSuccess) { cudaGetLastError(); ok = false; }
     else { h->allocs.push_back(p); h->d_tasks = (GemmTask*)p; }
   }
+  const size_t n_attn = (size_t)L * iqlb_pt_trainer::kAttnArrays * n * H + 3 * (size_t)n;
+  if (ok) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, n_attn * sizeof(GemmTask)) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    else { h->allocs.push_back(p); h->d_attn = (GemmTask*)p; }
+  }
   if (!ok) {
     ptt_free(h);
     return fail(IQLB_ERR_NOMEM, "iqlb_pt_trainer_create: device allocation failed%s", "");
+  }
+  {
+    std::vector<GemmTask> tk(n_attn);
+    const int dh = E / H;
+    auto task = [](const float* A, int lda, const float* B, int ldb, float* C, int ldc, int Mm, int Nn, int Kk, const float* bias) {
+      GemmTask t{};
+      t.A = A; t.lda = lda; t.Bm = B; t.ldb = ldb; t.C = C; t.ldc = ldc; t.M = Mm; t.N = Nn; t.K = Kk; t.bias = bias;
+      t.scale = 1.f; t.act = IQLB_ACT_LINEAR; t.allow_tc = 1;
+      return t;
+    };
+    for (int l = 0; l < L; ++l) {
+      auto& y = h->layers[l];
+      for (int64_t w = 0; w < n; ++w) {
+        for (int hh = 0; hh < H; ++hh) {
+          const size_t i = (size_t)w * H + hh;
+          const float* q = y.qkv + w * T2 * 3 * E + hh * dh;
+          const float *k = q + E, *v = q + 2 * E;
+          float* Pb = y.Pb + (int64_t)i * T2 * T2;
+          float* Pdr = y.Pd + (int64_t)i * T2 * T2;
+          float* dS = h->dS + (int64_t)i * T2 * T2;
+          float* o = y.o + w * T2 * E + hh * dh;
+          const float* dO = h->tmpB + w * T2 * E + hh * dh;
+          float* dq = h->dbig + w * T2 * 3 * E + hh * dh;
+          const size_t base = (size_t)l * iqlb_pt_trainer::kAttnArrays * n * H;
+          auto at = [&](int which) -> GemmTask& { return tk[base + (size_t)which * n * H + i]; };
+          at(0) = task(q, 3 * E, k, 3 * E, Pb, T2, T2, T2, dh, nullptr);             // LINEAR: S = Q K^T
+          at(1) = task(Pdr, T2, v, 3 * E, o, E, T2, dh, T2, h->zero_bias);           // FWD_KN: O = Pd V
+          at(2) = task(Pb, T2, v, 3 * E, o, E, T2, dh, T2, h->zero_bias);            //         O = P V
+          at(3) = task(dO, E, v, 3 * E, dS, T2, T2, T2, dh, nullptr);                // LINEAR: dPd = dO V^T
+          at(4) = task(dS, T2, k, 3 * E, dq, 3 * E, T2, dh, T2, h->zero_bias);       // FWD_KN: dQ = dS K
+          at(5) = task(dS, T2, q, 3 * E, dq + E, 3 * E, T2, dh, T2, nullptr);        // BWD_WEIGHT: dK = dS^T Q
+          at(6) = task(Pdr, T2, dO, E, dq + 2 * E, 3 * E, T2, dh, T2, nullptr);      //             dV = Pd^T dO
+          at(7) = task(Pb, T2, dO, E, dq + 2 * E, 3 * E, T2, dh, T2, nullptr);       //             dV = P^T dO
+        }
+      }
+    }
+    const size_t pbase = (size_t)L * iqlb_pt_trainer::kAttnArrays * n * H;
+    for (int64_t w = 0; w < n; ++w) {
+      const float* yq = h->y + w * T * ldy;
+      float* dyq = h->dy + w * T * ldy;
+      tk[pbase + w] = task(yq, ldy, yq + P.Pd, ldy, h->Sp + w * T * T, T, T, T, P.Pd, nullptr);                    // S = Q K^T
+      tk[pbase + n + w] = task(h->dSp + w * T * T, T, yq + P.Pd, ldy, dyq, ldy, T, P.Pd, T, h->zero_bias);        // dQ = dS K
+      tk[pbase + 2 * n + w] = task(h->dSp + w * T * T, T, yq, ldy, dyq + P.Pd, ldy, T, P.Pd, T, nullptr);         // dK = dS^T Q
+    }
+    if (cudaMemcpy(h->d_attn, tk.data(), n_attn * sizeof(GemmTask), cudaMemcpyHostToDevice) != cudaSuccess) {
+      cudaGetLastError(); ptt_free(h);
+      return fail(IQLB_ERR_CUDA, "iqlb_pt_trainer_create: task table upload failed%s", "");
+    }
   }
   cudaMemset(h->counter, 0, sizeof(unsigned int));
   cudaMemset(h->zero_bias, 0, (size_t)(bigc > ldy ? bigc : ldy) * sizeof(float));
@@ -682,6 +629,14 @@ static int ptt_linear_bwd_data(const iqlb_pt_trainer* h, const float* dY, int ld
   return launch_gemm(GEMM_FWD_KN, t, st);
 }
 
+// one grouped launch of an attention product (tasks built at create): tensor cores in split-bf16 mode when a 128 x 128 tile
+// is worth it, else the grouped FFMA kernel
+static int ptt_batched(const iqlb_pt_trainer* h, GemmMode mode, const GemmTask* tasks, int n_tasks, int M, int N, int K,
+                       cudaStream_t st) {
+  if (h->tc && M >= 64 && N >= 64 && K >= 16) return launch_grouped_gemm_tc(mode, tasks, n_tasks, M, N, st);
+  return launch_grouped_gemm(mode, tasks, n_tasks, M, N, N <= 32, st);
+}
+
 static inline unsigned ew_grid(int64_t total) {
   const int64_t b = (total + 255) / 256;
   return (unsigned)(b < 148 * 16 ? (b > 0 ? b : 1) : 148 * 16);
@@ -700,9 +655,9 @@ static int ptt_forward_train(iqlb_pt_trainer* h, const float* w, int n, int64_t 
                                              h->rstd_s, make_drop(h, h->p_embd, 0, adam_step, training));
   IQLB_LAUNCH_CHECK();
   const PtDrop none = make_drop(h, 0.f, 0, adam_step, false);
-  const size_t attn_smem = ((size_t)2 * T2 * (dh + 1) + 8 * dh + 8 * T2) * sizeof(float);
-  IQLB_REQUIRE(attn_smem <= 227 * 1024, "2T x head_dim too large for the shared-memory attention kernels");
-  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem));
+  const int nh = n * H;
+  const int64_t srows = (int64_t)nh * T2;
+  const bool adrop = training && h->p_attn > 0.f;
   for (int l = 0; l < P.L; ++l) {
     const float* lw = w + P.layer0 + (int64_t)l * P.layer_stride;
     auto& y = h->layers[l];
@@ -710,9 +665,11 @@ static int ptt_forward_train(iqlb_pt_trainer* h, const float* w, int n, int64_t 
                                                y.rstd0, none);
     IQLB_LAUNCH_CHECK();
     if ((rc = ptt_linear(h, y.h0, E, lw + P.inw, lw + P.inb, y.qkv, 3 * E, M, 3 * E, E, false, st))) return rc;
-    ptt_attn_fwd_kernel<<<dim3(n, H), 256, attn_smem, st>>>(T2, E, H, dh, y.qkv, h->Mk, y.o, y.Pb,
-                                                           make_drop(h, h->p_attn, 1 + 4 * l, adam_step, training));
+    if ((rc = ptt_batched(h, GEMM_LINEAR, h->attn_tasks(l, 0), nh, T2, T2, dh, st))) return rc;
+    ptt_softmax_fwd_kernel<<<(unsigned)((srows + 7) / 8), 256, 0, st>>>(T2, H, rsqrtf((float)dh), y.Pb, adrop ? y.Pd : y.Pb, h->Mk,
+                                                                       srows, make_drop(h, h->p_attn, 1 + 4 * l, adam_step, training));
     IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_batched(h, GEMM_FWD_KN, h->attn_tasks(l, adrop ? 1 : 2), nh, T2, dh, T2, st))) return rc;
     if ((rc = ptt_linear(h, y.o, E, lw + P.outw, lw + P.outb, h->tmpA, E, M, E, E, false, st))) return rc;
     ptt_resid_kernel<<<ew_grid(M * E), 256, 0, st>>>(h->x, h->tmpA, M * E, make_drop(h, h->p_ra, 2 + 4 * l, adam_step, training));
     IQLB_LAUNCH_CHECK();
@@ -729,7 +686,10 @@ static int ptt_forward_train(iqlb_pt_trainer* h, const float* w, int n, int64_t 
                                                               h->hid, h->xhat_f, h->rstd_f, none);
   IQLB_LAUNCH_CHECK();
   if ((rc = ptt_linear(h, h->hid, E, w + P.pw, w + P.pb, h->y, ldy, nT, ldy, E, false, st))) return rc;
-  return launch_pt_pref_attn(T, P.Pd, h->y, h->Mk, h->ws, n, st);
+  if ((rc = ptt_batched(h, GEMM_LINEAR, h->pref_tasks(0), n, T, T, P.Pd, st))) return rc;
+  ptt_pref_softmax_fwd_kernel<<<(unsigned)((nT + 7) / 8), 256, 0, st>>>(T, P.Pd, rsqrtf((float)P.Pd), h->Sp, h->y, h->Mk, nT, h->ws);
+  IQLB_LAUNCH_CHECK();
+  return IQLB_OK;
 }
 
 extern "C" int iqlb_pt_eval(iqlb_pt_trainer* h, const float* params, const float* states1, const float* actions1,
@@ -848,18 +808,18 @@ extern "C" int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_
   const PtDrop none = make_drop(h, 0.f, 0, adam_step, false);
 
   // ---- head: preference attention -> pref_linear -> final LayerNorm ----------------------------------------------------
-  ptt_pref_attn_bwd_kernel<<<n, 256, (size_t)9 * T * sizeof(float), st>>>(T, P.Pd, h->y, h->Mk, h->rowgrad, h->Cs, h->dy);
+  ptt_pref_softmax_bwd_kernel<<<n, 256, 0, st>>>(T, P.Pd, rsqrtf((float)P.Pd), h->Sp, h->y, h->ws, h->rowgrad, h->dSp, h->dy);
   IQLB_LAUNCH_CHECK();
+  if ((rc = ptt_batched(h, GEMM_FWD_KN, h->pref_tasks(1), n, T, P.Pd, T, st))) return rc;      // dq = dS k
+  if ((rc = ptt_batched(h, GEMM_BWD_WEIGHT, h->pref_tasks(2), n, T, P.Pd, T, st))) return rc;  // dk = dS^T q
   if ((rc = ptt_linear_bwd_data(h, h->dy, ldy, w + P.pw, h->tmpB, nT, E, ldy, st))) return rc;
   if ((rc = weight_grad((int)groups.size() - 1))) return rc;
   IQLB_CUDA(cudaMemsetAsync(h->dx, 0, (size_t)M * E * sizeof(float), st));  // state tokens of the last layer feed nothing
   if ((rc = ln_bwd(w + P.fg, P.fg, h->tmpB, E, none, h->xhat_f, h->rstd_f, nT, h->dx + E, 2 * E, 0))) return rc;
 
-  const size_t q_smem = ((size_t)2 * T2 * (dh + 1) + 8 * dh + 8 * T2) * sizeof(float);
-  const size_t kv_smem = ((size_t)2 * T2 * (dh + 1) + 16 * T2) * sizeof(float);
-  IQLB_REQUIRE(kv_smem <= 227 * 1024 && q_smem <= 227 * 1024, "2T x head_dim too large for the shared-memory attention kernels");
-  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_bwd_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q_smem));
-  IQLB_CUDA(cudaFuncSetAttribute(ptt_attn_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kv_smem));
+  const int nh = n * H;
+  const int64_t srows = (int64_t)nh * T2;
+  const bool adrop = tr && h->p_attn > 0.f;
 
   for (int l = L - 1; l >= 0; --l) {
     const int64_t lo = P.layer0 + (int64_t)l * P.layer_stride;
@@ -889,10 +849,12 @@ extern "C" int iqlb_pt_train_step(iqlb_pt_trainer* h, float* params, float* exp_
     if ((rc = ptt_linear_bwd_data(h, da, E, lw + P.outw, h->tmpB, M, E, E, st))) return rc;
     if ((rc = weight_grad(3 + 4 * l))) return rc;
     const PtDrop ad = make_drop(h, h->p_attn, 1 + 4 * l, adam_step, tr);
-    ptt_attn_bwd_q_kernel<<<dim3(n, H), 256, q_smem, st>>>(T2, E, H, dh, y.qkv, y.Pb, h->tmpB, h->dST, h->PdT, h->dbig, ad);
+    if ((rc = ptt_batched(h, GEMM_LINEAR, h->attn_tasks(l, 3), nh, T2, T2, dh, st))) return rc;                      // dPd = dO V^T
+    if ((rc = ptt_batched(h, GEMM_BWD_WEIGHT, h->attn_tasks(l, adrop ? 6 : 7), nh, T2, dh, T2, st))) return rc;      // dV = Pd^T dO
+    ptt_softmax_bwd_kernel<<<(unsigned)((srows + 7) / 8), 256, 0, st>>>(T2, rsqrtf((float)dh), y.Pb, h->dS, srows, ad);
     IQLB_LAUNCH_CHECK();
-    ptt_attn_bwd_kv_kernel<<<dim3(n, H), 256, kv_smem, st>>>(T2, E, H, dh, y.qkv, h->tmpB, h->dST, h->PdT, h->dbig);
-    IQLB_LAUNCH_CHECK();
+    if ((rc = ptt_batched(h, GEMM_FWD_KN, h->attn_tasks(l, 4), nh, T2, dh, T2, st))) return rc;                      // dQ = dS K
+    if ((rc = ptt_batched(h, GEMM_BWD_WEIGHT, h->attn_tasks(l, 5), nh, T2, dh, T2, st))) return rc;                  // dK = dS^T Q
     if ((rc = ptt_linear_bwd_data(h, h->dbig, 3 * E, lw + P.inw, h->tmpB, M, E, 3 * E, st))) return rc;
     if ((rc = weight_grad(2 + 4 * l))) return rc;
     if ((rc = ln_bwd(lw + P.ln0g, lo + P.ln0g, h->tmpB, E, none, y.xhat0, y.rstd0, M, h->dx, E, 1))) return rc;

@@ -18,6 +18,7 @@
 #include <stdlib.h>
 
 #include "umma.cuh"
+#include "gather_pack.cuh"
 
 namespace iqlb {
 using namespace umma;
@@ -77,57 +78,11 @@ __global__ void __launch_bounds__(256) pack_x_kernel(BfParams P, const float* __
 // fp32 batch rows (the loss kernel reads reward / done / action from them) and both bf16 input images
 // in one pass.  A CTA stages 256 / vec_per_row rows in shared memory.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) replay_gather_pack_kernel(
-    BfParams P, const float4* __restrict__ table, uint64_t n_rows, int vec_per_row, int rows_per_cta, int reward_col,
-    const float* __restrict__ reward_cols, const int32_t* __restrict__ reward_variant, const uint64_t* __restrict__ rng,
-    int64_t* __restrict__ idx_out, float4* __restrict__ batch_out) {
+__global__ void __launch_bounds__(256) replay_gather_pack_kernel(BfParams P, GatherArgs G) {
   extern __shared__ __align__(16) float srow[];  // [rows_per_cta][R]
   pdl_wait();  // first kernel of a step: the previous step's Adam (launched before it) must be complete
   pdl_launch();
-  const Layout& L = P.L;
-  const int agent = P.agent0 + blockIdx.y;
-  const int t = threadIdx.x;
-  const int lb = t / vec_per_row, v = t - lb * vec_per_row;
-  const int b = blockIdx.x * rows_per_cta + lb;
-  if (lb < rows_per_cta && b < L.B) {
-    uint32_t r[4];
-    philox4(rng[2 * agent], (uint64_t)b, rng[2 * agent + 1], r);
-    const int64_t row = randint_from_philox(r, n_rows);
-    if (idx_out != nullptr && v == 0) idx_out[(int64_t)agent * L.B + b] = row;
-    float4 val = __ldg(table + row * vec_per_row + v);
-    if (reward_cols != nullptr && (reward_col >> 2) == v) {
-      const int variant = reward_variant ? reward_variant[agent] : 0;
-      const float rw = __ldg(reward_cols + (int64_t)variant * (int64_t)n_rows + row);
-      switch (reward_col & 3) {
-        case 0: val.x = rw; break;
-        case 1: val.y = rw; break;
-        case 2: val.z = rw; break;
-        default: val.w = rw; break;
-      }
-    }
-    batch_out[((int64_t)agent * L.B + b) * vec_per_row + v] = val;
-    *reinterpret_cast<float4*>(srow + lb * L.R + 4 * v) = val;
-  }
-  __syncthreads();
-  const int cpr = P.KXB * 8;
-  for (int i = t; i < rows_per_cta * cpr; i += 256) {
-    const int rb = i / cpr, ch = i - rb * cpr;
-    const int bb = blockIdx.x * rows_per_cta + rb;
-    if (bb >= L.B) break;
-    const float* row = srow + rb * L.R;
-    uint32_t sa[4], nx[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int c = ch * 8 + 2 * q;
-      const float a0 = c < L.Dq ? row[c] : 0.f, a1 = c + 1 < L.Dq ? row[c + 1] : 0.f;
-      const float n0 = c < L.S ? row[L.Dq + c] : 0.f, n1 = c + 1 < L.S ? row[L.Dq + c + 1] : 0.f;
-      sa[q] = pack_bf16(a0, a1);
-      nx[q] = pack_bf16(n0, n1);
-    }
-    const int64_t off = image_off(L.B, bb, ch * 8);
-    *reinterpret_cast<uint4*>(P.xsa + (int64_t)agent * P.x_bytes + off) = make_uint4(sa[0], sa[1], sa[2], sa[3]);
-    *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
-  }
+  gather_pack_body(P, G, (int)blockIdx.x, (int)blockIdx.y, srow);
 }
 
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
@@ -1079,6 +1034,16 @@ int bf16_refresh(iqlb_agents* h, cudaStream_t stream) {
   return IQLB_OK;
 }
 
+GatherArgs bf16_gather_args(const iqlb_agents* h) {
+  const Layout& L = h->L;
+  GatherArgs G{};
+  G.table = (const float4*)h->table; G.n_rows = (uint64_t)h->n_rows; G.vec_per_row = L.R / 4;
+  G.rows_per_cta = 256 / G.vec_per_row; G.reward_col = 2 * L.S + L.A; G.reward_cols = h->reward_cols;
+  G.reward_variant = h->reward_variant; G.rng = (const uint64_t*)h->rng; G.idx_out = h->idx_out; G.batch_out = (float4*)h->batch;
+  G.blocks_x = (L.B + G.rows_per_cta - 1) / G.rows_per_cta;
+  return G;
+}
+
 // sampled steps: Philox gather + image packing in one launch (replaces replay_gather + pack_x)
 int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream) {
   Bf16State* st = (Bf16State*)h->bf16_state;
@@ -1090,9 +1055,9 @@ int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t strea
   const int vpr = L.R / 4;
   IQLB_REQUIRE(vpr <= 256, "row_stride too wide");
   const int rpc = 256 / vpr;
-  IQLB_CUDA(launch_pdl(replay_gather_pack_kernel, dim3((unsigned)((L.B + rpc - 1) / rpc), n), dim3(256), (size_t)rpc * L.R * 4,
-                       stream, pdl_enabled(1) && !h->prof, P, (const float4*)h->table, (uint64_t)h->n_rows, vpr, rpc,
-                       2 * L.S + L.A, h->reward_cols, h->reward_variant, (const uint64_t*)h->rng, h->idx_out, (float4*)h->batch));
+  const GatherArgs G = bf16_gather_args(h);
+  IQLB_CUDA(launch_pdl(replay_gather_pack_kernel, dim3((unsigned)G.blocks_x, n), dim3(256), (size_t)rpc * L.R * 4, stream,
+                       pdl_enabled(1) && !h->prof, P, G));
   pf.mark("replay_gather_pack");
   return IQLB_OK;
 }

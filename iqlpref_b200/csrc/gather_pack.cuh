@@ -1,0 +1,72 @@
+// ReplayBuffer.sample (iql.py:211-221) fused with the packing of the tensor-core input images: the body shared by the stand-alone
+// kernel (bf16_step.cu: replay_gather_pack_kernel) and by the gather CTAs that ride in the optimizer launch (iql_step.cu:
+// adam_polyak_kernel, look-ahead sampling of the next step's batch).
+#pragma once
+#include "iql_step.cuh"
+#include "umma.cuh"
+
+namespace iqlb {
+
+struct GatherArgs {
+  const float4* table;
+  uint64_t n_rows;
+  int vec_per_row, rows_per_cta, reward_col;
+  const float* reward_cols;
+  const int32_t* reward_variant;
+  const uint64_t* rng;
+  int64_t* idx_out;
+  float4* batch_out;
+  int blocks_x;  // gather CTAs per agent
+};
+
+// Block (bx, agent index by) of 256 threads: Philox index, 128-bit row gather, fp32 batch rows (the loss kernel reads reward /
+// done / action from them) and both bf16 input images in one pass.  srow: rows_per_cta * R floats of shared memory.
+__device__ __forceinline__ void gather_pack_body(const BfParams& P, const GatherArgs& G, int bx, int by, float* srow) {
+  const Layout& L = P.L;
+  const int agent = P.agent0 + by;
+  const int t = threadIdx.x;
+  const int vec_per_row = G.vec_per_row, rows_per_cta = G.rows_per_cta;
+  const int lb = t / vec_per_row, v = t - lb * vec_per_row;
+  const int b = bx * rows_per_cta + lb;
+  if (lb < rows_per_cta && b < L.B) {
+    uint32_t r[4];
+    philox4(G.rng[2 * agent], (uint64_t)b, G.rng[2 * agent + 1], r);
+    const int64_t row = randint_from_philox(r, G.n_rows);
+    if (G.idx_out != nullptr && v == 0) G.idx_out[(int64_t)agent * L.B + b] = row;
+    float4 val = __ldg(G.table + row * vec_per_row + v);
+    if (G.reward_cols != nullptr && (G.reward_col >> 2) == v) {
+      const int variant = G.reward_variant ? G.reward_variant[agent] : 0;
+      const float rw = __ldg(G.reward_cols + (int64_t)variant * (int64_t)G.n_rows + row);
+      switch (G.reward_col & 3) {
+        case 0: val.x = rw; break;
+        case 1: val.y = rw; break;
+        case 2: val.z = rw; break;
+        default: val.w = rw; break;
+      }
+    }
+    G.batch_out[((int64_t)agent * L.B + b) * vec_per_row + v] = val;
+    *reinterpret_cast<float4*>(srow + lb * L.R + 4 * v) = val;
+  }
+  __syncthreads();
+  const int cpr = P.KXB * 8;
+  for (int i = t; i < rows_per_cta * cpr; i += 256) {
+    const int rb = i / cpr, ch = i - rb * cpr;
+    const int bb = bx * rows_per_cta + rb;
+    if (bb >= L.B) break;
+    const float* row = srow + rb * L.R;
+    uint32_t sa[4], nx[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int c = ch * 8 + 2 * q;
+      const float a0 = c < L.Dq ? row[c] : 0.f, a1 = c + 1 < L.Dq ? row[c + 1] : 0.f;
+      const float n0 = c < L.S ? row[L.Dq + c] : 0.f, n1 = c + 1 < L.S ? row[L.Dq + c + 1] : 0.f;
+      sa[q] = umma::pack_bf16(a0, a1);
+      nx[q] = umma::pack_bf16(n0, n1);
+    }
+    const int64_t off = umma::image_off(L.B, bb, ch * 8);
+    *reinterpret_cast<uint4*>(P.xsa + (int64_t)agent * P.x_bytes + off) = make_uint4(sa[0], sa[1], sa[2], sa[3]);
+    *reinterpret_cast<uint4*>(P.xnext + (int64_t)agent * P.x_bytes + off) = make_uint4(nx[0], nx[1], nx[2], nx[3]);
+  }
+}
+
+}  // namespace iqlb

@@ -10,6 +10,7 @@
 #include <stdlib.h>
 
 #include "iql_step.cuh"
+#include "gather_pack.cuh"
 
 namespace iqlb {
 
@@ -20,6 +21,7 @@ int bf16_create(iqlb_agents* h);
 void bf16_destroy(iqlb_agents* h);
 int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream, bool packed);
 int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
+GatherArgs bf16_gather_args(const iqlb_agents* h);
 int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
 const BfParams* bf16_params(const iqlb_agents* h);
 void bf16_mark_dirty(iqlb_agents* h);
@@ -346,7 +348,20 @@ __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layo
                                                           float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                           float* __restrict__ target, const float* __restrict__ grads,
                                                           const StepScalars* __restrict__ scal, BfParams BP, int shadow,
-                                                          int agent0, int n_agents_launch, int chunks_per_agent) {
+                                                          int agent0, int n_agents_launch, int chunks_per_agent,
+                                                          GatherArgs GA, int n_gather) {
+  // Look-ahead sampling: the first n_gather CTAs of the one-shot launch gather and pack the NEXT step's batch (the loss
+  // kernel has already advanced the RNG offsets, and every consumer of this step's batch rows / input images - forward,
+  // loss, weight gradients - completed before this launch).  The random row reads hide under the optimizer's HBM stream
+  // and the next step starts with its forward kernel.
+  if (!kPersist && n_gather > 0) {
+    if ((int)blockIdx.x < n_gather) {
+      extern __shared__ __align__(16) float gather_srow[];
+      BP.agent0 = agent0;
+      gather_pack_body(BP, GA, (int)blockIdx.x % GA.blocks_x, (int)blockIdx.x / GA.blocks_x, gather_srow);
+      return;
+    }
+  }
   // Thread t handles the 16-byte words t (and t + 256, ...) of the chunk, so every warp access is 512 contiguous bytes per
   // array.  Network segments start on multiples of 8 floats: a word never straddles two optimizers, and inside W1 it
   // is half of a 16-byte chunk of the image.
@@ -462,7 +477,7 @@ __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layo
       first = false;
     }
   } else {
-    body((int)blockIdx.x, true);
+    body((int)blockIdx.x - n_gather, true);
   }
 }
 
@@ -548,7 +563,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   int rc;
   if (sampled && bf && h->pre_valid) {
     // gathered and packed during the previous step's optimizer kernel (look-ahead sampling)
-    IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
+    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
     h->pre_valid = false;
   } else if (sampled && bf) {
     if ((rc = bf16_gather_pack(h, a0, n, pf, st))) return rc;
@@ -600,7 +615,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   return IQLB_OK;
 }
 
-static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded) {
+static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded, bool ride_gather = false) {
   const Layout& L = h->L;
   const bool bf = h->desc.precision == 1;
   if (bf && h->fused_adam) return IQLB_OK;
@@ -613,10 +628,19 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, b
   const int n_chunks = cpa * n;
   int grid = n_chunks;
   if (bounded && h->n_sm > 0 && h->adam_ctas_per_sm > 0 && grid > h->n_sm * h->adam_ctas_per_sm) grid = h->n_sm * h->adam_ctas_per_sm;
-  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)grid), dim3(256), 0, st,
+  GatherArgs GA{};
+  int n_gather = 0;
+  size_t smem = 0;
+  if (ride_gather && bf && grid == n_chunks) {
+    GA = bf16_gather_args(h);
+    n_gather = GA.blocks_x * n;
+    smem = (size_t)GA.rows_per_cta * L.R * 4;
+  }
+  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)(grid + n_gather)), dim3(256), smem, st,
                        bf && !bounded && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
-                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa));
+                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa, GA, n_gather));
+  if (n_gather > 0) { h->pre_valid = true; h->pre_inline = true; }
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
 }
@@ -647,13 +671,21 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   Prof pf(h, st);
   int G = (h->desc.precision == 1 && !h->prof && !h->fused_adam) ? h->n_groups : 1;
   if (h->pre_valid && !sampled) {  // an explicit batch follows a look-ahead gather: let it finish, then overwrite it
-    IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
+    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
     h->pre_valid = false;
   }
   if (G <= 1) {
     if ((rc = join_groups(h, st))) return rc;  // (a profiled or fused-Adam step after overlapped ones)
     if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
-    if (sampled && h->desc.precision == 1 && h->presample && !h->prof && h->idx_out == nullptr) {
+    const bool lookahead = sampled && h->desc.precision == 1 && !h->prof && h->idx_out == nullptr && !h->fused_adam;
+    if (lookahead && h->presample == 2) {  // the next step's gather rides in the optimizer launch
+      if ((rc = step_adam(h, 0, N, pf, st, false, true))) return rc;
+      pf.done();
+      if (h->zig >= 0) h->zig ^= 1;
+      return IQLB_OK;
+    }
+    if (lookahead && h->presample == 1) {
+      h->pre_inline = false;
       if (!h->pre_stream) {
         int prio_lo = 0, prio_hi = 0;  // highest priority: the small gather must not queue behind the optimizer's CTAs
         IQLB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
@@ -770,7 +802,8 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   h->zig = (getenv("IQLB_ZIGZAG") && atoi(getenv("IQLB_ZIGZAG")) == 0) ? -1 : 0;
   // measured on B200 (64 agents): 268.7 vs 269.1 us per step - the forward kernel loses its programmatic overlap
   // with the optimizer's tail to the cross-stream join, which eats what the hidden gather saves.  Off by default.
-  h->presample = (getenv("IQLB_PRESAMPLE") && atoi(getenv("IQLB_PRESAMPLE")) != 0) ? 1 : 0;
+  // look-ahead sampling: 0 off, 1 the next step's gather on a side stream (measured neutral), 2 (default) in the optimizer launch
+  h->presample = getenv("IQLB_PRESAMPLE") ? atoi(getenv("IQLB_PRESAMPLE")) : 2;
   if (!rc && d->precision == 1) {
     const char* env = getenv("IQLB_GROUPS");
     // Opt-in (IQLB_GROUPS=2): measured on B200 with 64 agents, two groups are SLOWER than one (313-370 vs 260 us per
@@ -845,8 +878,8 @@ extern "C" int iqlb_agents_set_replay(iqlb_agents* h, const float* table, int64_
   IQLB_REQUIRE(h && table, "null handle/table");
   IQLB_REQUIRE(n_rows > 0, "empty table");
   IQLB_REQUIRE(((uintptr_t)table & 15) == 0, "table must be 16-byte aligned");
-  if (h->pre_valid) {  // a look-ahead gather of the old table is in flight: drop it
-    IQLB_CUDA(cudaStreamSynchronize(h->pre_stream));
+  if (h->pre_valid) {  // a look-ahead gather of the old table is in flight (or done): drop it
+    if (!h->pre_inline) IQLB_CUDA(cudaStreamSynchronize(h->pre_stream));
     h->pre_valid = false;
   }
   h->table = table; h->n_rows = n_rows; h->reward_cols = reward_cols; h->reward_variant = reward_variant;
@@ -956,7 +989,7 @@ extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   { int rcj = join_groups(h, (cudaStream_t)stream); if (rcj) return rcj; }
   if (h->pre_valid) {  // caller-owned state (parameters, RNG offsets) changed: the look-ahead batch is stale
-    IQLB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_pre_join, 0));
+    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_pre_join, 0));
     h->pre_valid = false;
   }
   if (h->desc.precision == 1) return bf16_refresh(h, (cudaStream_t)stream);

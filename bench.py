@@ -420,6 +420,50 @@ def bench_relabel(args, dev, table, R, peaks):
     return out, r_hat
 
 
+def bench_trainers(dev):
+    """Reward-model training steps of BASELINE configs[2] / [1] on synthetic preference pairs, device-resident
+    batches, no per-step host sync: the preference transformer at the reference's shape (scripts_pt/*.yaml: E = 2^8, 4 heads,
+    I = 4E, 1 layer, dropouts 0.1, batch 64 pairs x 100 steps) and the MR reward MLP (37 -> 128 x 3 -> 1, 256 pairs x 100)."""
+    import numpy as np
+    import torch
+    from iqlpref_b200.mr_training import MRTrainer
+    from iqlpref_b200.pt_training import PTTrainer
+    from iqlpref_b200.reward_models.pref_transformer import PT
+    from iqlpref_b200.reward_models.q_mlp import MLP as RewardMLP
+    out = {}
+    rng = np.random.default_rng(0)
+
+    def pairs(B, T, with_ts):
+        b = []
+        for _ in range(2):
+            b += [torch.randn((B, T, S_DIM), device=dev), torch.rand((B, T, A_DIM), device=dev) * 2 - 1,
+                  torch.arange(T, device=dev).repeat(B, 1), torch.ones((B, T), device=dev)]
+        y = torch.from_numpy((rng.uniform(size=B) < 0.5).astype(np.float32)).to(dev)
+        return b + [torch.stack([y, 1 - y], dim=1)]
+    torch.manual_seed(0)
+    net = PT(S_DIM, A_DIM, 1000, 256, 256, 4, 0.1, 0.1, 1024, 1, 0.1, 2048, 0.1)
+    tr = PTTrainer(net, torch.optim.Adam(net.parameters(), lr=3e-4), device=dev, precision="split_bf16", seed=1)
+    batch = pairs(64, 100, True)
+    fn = lambda: tr.train(batch, sync=False)
+    for _ in range(3):
+        fn()
+    ms = min(time_gpu(fn, 10, dev) for _ in range(2))
+    out["pt_train"] = {"ms_per_step": ms, "steps_per_s": 1e3 / ms, "pairs": 64, "segment_len": 100, "precision": "split_bf16",
+                       "note": "PTTrainer.train(sync=False): forward + backward + Adam of RewardPT(29, 8, E=256, heads 4, I=1024, "
+                               "L=1) with the reference's dropouts, through the Python mirror (input checks included)"}
+    torch.manual_seed(0)
+    mlp = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
+    mr = MRTrainer(mlp, torch.optim.Adam(mlp.parameters(), lr=3e-4), 1, device=dev, precision="split_bf16")
+    mb = pairs(256, 100, False)
+    fm = lambda: mr.train(mb, sync=False)
+    for _ in range(3):
+        fm()
+    ms = min(time_gpu(fm, 20, dev) for _ in range(2))
+    out["mr_train"] = {"ms_per_step": ms, "steps_per_s": 1e3 / ms, "pairs": 256, "segment_len": 100, "precision": "split_bf16",
+                       "note": "MRTrainer.train(sync=False), RewardMLP(37, 1, [128]*3, relu)"}
+    return out
+
+
 def build_workload(args, dev, rank, world):
     import torch
     from iqlpref_b200 import iql as biql
@@ -649,6 +693,10 @@ def run_cuda(args):
         ref_cuda = reference_cuda(args, dev)
         log(f"reference_cuda: {ref_cuda['value']:.1f} updates/s (stock PyTorch eager, 1 agent)")
 
+    trainers = None
+    if rank == 0 and world == 1 and not getattr(args, "skip_relabel", False):
+        trainers = bench_trainers(dev)
+        log(f"reward-model training: PT {trainers['pt_train']['steps_per_s']:.0f} steps/s, MR {trainers['mr_train']['steps_per_s']:.0f} steps/s")
     eng, buf, cols, variant, relabel = build_workload(args, dev, rank, world)
     N, K, W = agents_per_gpu(args, world), args.steps, args.warmup
     stream = torch.cuda.current_stream(dev)
@@ -765,6 +813,8 @@ def run_cuda(args):
                                   "hbm_frac": bytes_per_update() * per_gpu / 1e9 / peaks["hbm"],
                                   "flops_per_update": flops_per_update(), "bytes_per_update": bytes_per_update()},
                 "relabel": relabel}
+        if trainers is not None:
+            line["reward_model_training"] = trainers
         if "mlp" in relabel:
             relabel["roofline"] = {"bound": "tensor", "achieved": 3.0 * relabel["mlp"]["tflops_fp32_equiv"],
                                    "peak": peaks["tensor_burst"], "unit": "TFLOP/s",

@@ -19,21 +19,56 @@ struct GatherArgs {
   int blocks_x;  // gather CTAs per agent
 };
 
-// Block (bx, agent index by) of 256 threads: Philox index, 128-bit row gather, fp32 batch rows (the loss kernel reads reward /
-// done / action from them) and both bf16 input images in one pass.  srow: rows_per_cta * R floats of shared memory.
-__device__ __forceinline__ void gather_pack_body(const BfParams& P, const GatherArgs& G, int bx, int by, float* srow) {
+// Block (bx, agent index by) of 256 threads: Philox indices, TMA staging of the rows (one cp.async.bulk per 16-byte aligned
+// row of obs | action | next_obs | reward | done into shared memory, completion on an mbarrier), fp32 batch rows (the loss kernel
+// reads reward / done / action from them) and both bf16 input images in one pass.  srow: rows_per_cta * R floats.
+// call: number of earlier calls by this CTA (persistent callers loop over blocks; the mbarrier is initialised by call 0 and
+// waited on with the call's phase parity; the caller separates calls with __syncthreads()).
+__device__ __forceinline__ void gather_pack_body(const BfParams& P, const GatherArgs& G, int bx, int by, float* srow, int call = 0) {
+  __shared__ __align__(8) uint64_t gather_bar;
+  __shared__ int64_t gather_row[32];
   const Layout& L = P.L;
   const int agent = P.agent0 + by;
   const int t = threadIdx.x;
   const int vec_per_row = G.vec_per_row, rows_per_cta = G.rows_per_cta;
+  const int b0 = bx * rows_per_cta;
+  const int n_here = L.B - b0 < rows_per_cta ? L.B - b0 : rows_per_cta;
+  const uint32_t bar = umma::smem_u32(&gather_bar);
+  const bool tma = rows_per_cta <= 32;  // one issuing lane per row (rows of >= 32 floats: every reference shape)
+  if (tma) {
+    if (call == 0) {
+      if (t == 0) { umma::mbar_init(bar, 1); umma::fence_barrier_init(); }
+      __syncthreads();
+    }
+    if (t < 32) {
+      if (t < n_here) {
+        uint32_t r[4];
+        philox4(G.rng[2 * agent], (uint64_t)(b0 + t), G.rng[2 * agent + 1], r);
+        const int64_t row = randint_from_philox(r, G.n_rows);
+        gather_row[t] = row;
+        if (G.idx_out != nullptr) G.idx_out[(int64_t)agent * L.B + b0 + t] = row;
+        umma::bulk_g2s(umma::smem_u32(srow + t * L.R), G.table + row * vec_per_row, (uint32_t)L.R * 4u, bar);
+      }
+      if (t == 0) umma::mbar_expect_tx(bar, (uint32_t)n_here * (uint32_t)L.R * 4u);
+    }
+    __syncthreads();  // gather_row visible
+    umma::mbar_wait(bar, (uint32_t)(call & 1));
+  }
   const int lb = t / vec_per_row, v = t - lb * vec_per_row;
-  const int b = bx * rows_per_cta + lb;
+  const int b = b0 + lb;
   if (lb < rows_per_cta && b < L.B) {
-    uint32_t r[4];
-    philox4(G.rng[2 * agent], (uint64_t)b, G.rng[2 * agent + 1], r);
-    const int64_t row = randint_from_philox(r, G.n_rows);
-    if (G.idx_out != nullptr && v == 0) G.idx_out[(int64_t)agent * L.B + b] = row;
-    float4 val = __ldg(G.table + row * vec_per_row + v);
+    int64_t row;
+    float4 val;
+    if (tma) {
+      row = gather_row[lb];
+      val = *reinterpret_cast<const float4*>(srow + lb * L.R + 4 * v);
+    } else {
+      uint32_t r[4];
+      philox4(G.rng[2 * agent], (uint64_t)b, G.rng[2 * agent + 1], r);
+      row = randint_from_philox(r, G.n_rows);
+      if (G.idx_out != nullptr && v == 0) G.idx_out[(int64_t)agent * L.B + b] = row;
+      val = __ldg(G.table + row * vec_per_row + v);
+    }
     if (G.reward_cols != nullptr && (G.reward_col >> 2) == v) {
       const int variant = G.reward_variant ? G.reward_variant[agent] : 0;
       const float rw = __ldg(G.reward_cols + (int64_t)variant * (int64_t)G.n_rows + row);

@@ -354,12 +354,20 @@ __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layo
   // kernel has already advanced the RNG offsets, and every consumer of this step's batch rows / input images - forward,
   // loss, weight gradients - completed before this launch).  The random row reads hide under the optimizer's HBM stream
   // and the next step starts with its forward kernel.
-  if (!kPersist && n_gather > 0) {
-    if ((int)blockIdx.x < n_gather) {
-      extern __shared__ __align__(16) float gather_srow[];
-      BP.agent0 = agent0;
-      gather_pack_body(BP, GA, (int)blockIdx.x % GA.blocks_x, (int)blockIdx.x / GA.blocks_x, gather_srow);
-      return;
+  if (n_gather > 0) {
+    extern __shared__ __align__(16) float gather_srow[];
+    BP.agent0 = agent0;
+    if (!kPersist) {
+      if ((int)blockIdx.x < n_gather) {
+        gather_pack_body(BP, GA, (int)blockIdx.x % GA.blocks_x, (int)blockIdx.x / GA.blocks_x, gather_srow);
+        return;
+      }
+    } else {  // persistent grid: every CTA takes its share of the gather blocks first, then walks its optimizer chunks
+      int call = 0;
+      for (int gb = blockIdx.x; gb < n_gather; gb += gridDim.x, ++call) {
+        gather_pack_body(BP, GA, gb % GA.blocks_x, gb / GA.blocks_x, gather_srow, call);
+        __syncthreads();
+      }
     }
   }
   // Thread t handles the 16-byte words t (and t + 256, ...) of the chunk, so every warp access is 512 contiguous bytes per
@@ -477,7 +485,7 @@ __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layo
       first = false;
     }
   } else {
-    body((int)blockIdx.x - n_gather, true);
+    body((int)blockIdx.x - (kPersist ? 0 : n_gather), true);
   }
 }
 
@@ -628,15 +636,20 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, b
   const int n_chunks = cpa * n;
   int grid = n_chunks;
   if (bounded && h->n_sm > 0 && h->adam_ctas_per_sm > 0 && grid > h->n_sm * h->adam_ctas_per_sm) grid = h->n_sm * h->adam_ctas_per_sm;
+  // One-shot launch of the whole sweep: with many more chunks than resident CTAs a persistent grid of 5 CTAs per SM (full
+  // residency at <= 48 registers) streams HBM a few percent faster than one short-lived CTA per 4 KB chunk (measured on
+  // B200, scripts/gpu_adam_ab.sh: 265.4 -> 260.9 us per step; 4 or 8 CTAs per SM are slower).  IQLB_ADAM_PERSIST=0: off.
+  static const int persist_env = getenv("IQLB_ADAM_PERSIST") ? atoi(getenv("IQLB_ADAM_PERSIST")) : 5;
+  if (!bounded && persist_env > 0 && h->n_sm > 0 && grid >= 8 * h->n_sm * persist_env) grid = h->n_sm * persist_env;
   GatherArgs GA{};
   int n_gather = 0;
   size_t smem = 0;
-  if (ride_gather && bf && grid == n_chunks) {
+  if (ride_gather && bf && !bounded) {
     GA = bf16_gather_args(h);
     n_gather = GA.blocks_x * n;
     smem = (size_t)GA.rows_per_cta * L.R * 4;
   }
-  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)(grid + n_gather)), dim3(256), smem, st,
+  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)(grid < n_chunks ? grid : grid + n_gather)), dim3(256), smem, st,
                        bf && !bounded && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
                        (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa, GA, n_gather));

@@ -936,6 +936,215 @@ __global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, flo
 }
 
 // ------------------------------------------------------------------------------------------------
+// Weight gradients, second schedule (round 2).  Same arithmetic, operands, TMEM columns and outputs as bwd_weight_body<false>;
+// what changes is who does what:
+//   warps 0-15  drain: 4 warps per TMEM lane quarter (16 of every 64 columns each) - the 8-warp version spent 5 of its 10 us
+//               per CTA moving the 128 x 256 dW1 tile TMEM -> shared memory -> global at 12 % warp occupancy;
+//   warp 16     one elected thread does every bulk copy and every MMA issue, so the phase-2 products (dW0, db0, and with
+//               one input block also dW2) are loaded and ISSUED under the dW1 drain instead of after it.
+// Shared memory as before ([dH2|dH1 2 blk][H1 4 blk -> X, H2, staging][dz 1 blk]); with one input block (state_dim + action_dim
+// <= 64) the H2 tile is requested right after phase 1 into the two H1 blocks behind X and the dW1 drain stages through one
+// 32 KB buffer; with two input blocks H2 still follows the drain.
+// ------------------------------------------------------------------------------------------------
+constexpr int kBwDrainThreads = 512, kBwThreads = kBwDrainThreads + 32;
+
+__device__ __forceinline__ void bw_bar(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kBwDrainThreads) : "memory"); }
+
+// the 16 drain warps of bf16_bwd_weight2_kernel
+__device__ __forceinline__ void bwd_weight2_drain(const BfParams& P, uint8_t* smem, const uint32_t tmem, const uint32_t bar_p1,
+                                                  const uint32_t bar_p2, const uint32_t bar_d1, const int ot, const int t,
+                                                  const int agent, const int in, const int nout, const int n0, const int warp,
+                                                  const int lane, const int quarter, const int cgrp, const int tid) {
+  const Layout& L = P.L;
+  const int s = train_stream(t);
+  const uint32_t blk = (uint32_t)L.B * 128u;
+  const uint32_t oB = 2 * blk;
+  const int trow = quarter * 32 + lane;  // tile row (= output feature ot * 128 + trow) this thread drains
+  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+  const int64_t noff = L.net_off(s);
+  __nv_bfloat16* gagent = P.gradh + (int64_t)agent * L.Pstride;
+  mbar_wait(bar_p1, 0);
+  tc_fence_after();
+  {
+    // ---- dW1: four 64-column chunks through one [128 rows][64] fp32 buffer (float4 index ^ (row & 15)); bf16 rows leave
+    //      as 128-bit stores, 8 lanes per 128-byte row segment
+    float* sb = reinterpret_cast<float*>(smem + oB + 3 * blk);
+    const int rr = lane >> 3, l8 = lane & 7;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      float v[16];
+      tmem_ld16(lane_base + (uint32_t)(cc * 64 + cgrp * 16), v);
+      tmem_ld_wait();
+      if (cc > 0) bw_bar(2);  // every warp has read chunk cc - 1 out of the buffer
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<float4*>(sb + trow * 64 + (((cgrp * 4 + q) ^ (trow & 15)) << 2)) =
+            make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      bw_bar(1);  // chunk cc staged
+      __nv_bfloat16* gw1 = gagent + noff + L.w1(in) + (int64_t)(ot * 128) * L.H + cc * 64 + 8 * l8;
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {  // bf16, as the reference's autocast weight-gradient GEMM emits them
+        const int r = warp * 8 + it * 4 + rr;
+        const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
+        const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
+        *reinterpret_cast<uint4*>(gw1 + (int64_t)r * L.H) =
+            make_uint4(pack_bf16(g0.x, g0.y), pack_bf16(g0.z, g0.w), pack_bf16(g1.x, g1.y), pack_bf16(g1.z, g1.w));
+      }
+    }
+  }
+  if (P.KXB != 1) {  // the H2 tile moves into the staging buffer's neighbourhood: tell the issuing thread the drain is over
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_d1);
+  }
+  mbar_wait(bar_p2, 0);
+  tc_fence_after();
+  // ---- everything else through shared memory in packed-parameter order (the operands of phase 2 are dead):
+  //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
+  // each a contiguous, 16-byte aligned span of the parameter vector -> one flat 128-bit pass
+  float* stg = reinterpret_cast<float*>(smem + oB + 2 * blk);
+  const int g1 = 128 * in, g2 = g1 + 128, g3 = g2 + 128, gtot = g3 + 128 * nout;
+  const int64_t e_w0 = noff + L.w0() + (int64_t)ot * 128 * in, e_b1 = noff + L.b1(in) + ot * 128,
+                e_b0 = noff + L.b0(in) + ot * 128, e_w2 = noff + L.w2(in) + ot * 128;
+  auto flat_elem = [&](int i) -> int64_t {
+    if (i < g1) return e_w0 + i;
+    if (i < g2) return e_b1 + (i - g1);
+    if (i < g3) return e_b0 + (i - g2);
+    return e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
+  };
+  if (cgrp < 2) {
+    for (int c0 = cgrp * 16; c0 < n0; c0 += 32) {
+      float v[16];
+      tmem_ld16(lane_base + 256u + (uint32_t)c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (c0 + j < in) stg[trow * in + c0 + j] = v[j];
+    }
+  } else if (cgrp == 2) {  // the bias gradients ride on the ones column (index nout) of the dz image
+    float v[32];
+    tmem_ld32(lane_base + 384u, v);
+    tmem_ld_wait();
+    float db = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+    stg[g2 + trow] = db;
+    tmem_ld32(lane_base + 352u, v);
+    tmem_ld_wait();
+    db = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
+    stg[g1 + trow] = db;
+  } else {
+    float v[32];
+    tmem_ld32(lane_base + 416u, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int o = 0; o < kOutMax; ++o)
+      if (o < nout) stg[g3 + o * 128 + trow] = v[o];
+  }
+  bw_bar(1);
+  for (int i = tid * 4; i < gtot; i += 4 * kBwDrainThreads) {
+    const float4 g = *reinterpret_cast<const float4*>(stg + i);
+    *reinterpret_cast<uint2*>(gagent + flat_elem(i)) = make_uint2(pack_bf16(g.x, g.y), pack_bf16(g.z, g.w));
+  }
+}
+
+__global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight2_kernel(BfParams P) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const Layout& L = P.L;
+  const int ot = (int)blockIdx.x, t = (int)blockIdx.y, aidx = (int)blockIdx.z, n_ag = (int)gridDim.z;
+  const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
+  const int s = train_stream(t);
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;
+  const int quarter = warp & 3, cgrp = (warp >> 2) & 3;
+  const uint32_t blk = (uint32_t)L.B * 128u;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t oA = 0, oB = 2 * blk, oZ = 6 * blk, oCtrl = 7 * blk;
+  const uint32_t bar_ld1 = sbase + oCtrl, bar_ld2 = bar_ld1 + 8, bar_ld3 = bar_ld1 + 16, bar_p1 = bar_ld1 + 24,
+                 bar_p2 = bar_ld1 + 32, bar_d1 = bar_ld1 + 40;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 48);
+  const int in = L.in_dim(s), nout = L.out_dim(s);
+  const int64_t at = (int64_t)agent * kTrain + t;
+  const int ksteps = L.B / 16;
+  const int n0 = (in + 15) / 16 * 16;
+  const bool preload_h2 = P.KXB == 1;
+  const uint32_t oH2 = preload_h2 ? oB + blk : oB + 2 * blk;
+  const bool issuer_warp = warp == kBwDrainThreads / 32;
+
+  if (issuer_warp && elect_one()) {
+    if (sbase & 1023u) __trap();
+    for (int i = 0; i < 5; ++i) mbar_init(bar_ld1 + 8 * i, 1);
+    mbar_init(bar_d1, kBwDrainThreads / 32);
+    fence_barrier_init();
+    mbar_expect_tx(bar_ld1, 7 * blk);
+    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward output: before the PDL wait
+    bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);      // loss output, two kernels back
+    pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
+    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
+  }
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 48, 512);
+  pdl_wait();
+  pdl_launch();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int wlin = ot + 2 * (t + kTrain * aidx);
+  if (P.dbg != nullptr && tid == 0 && wlin < 512) {  // (SM, start) of every CTA: scripts/timeline.py
+    unsigned smid; unsigned long long gt;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + 1536 + wlin * 4] = smid; P.dbg[4096 + 1536 + wlin * 4 + 1] = gt; P.dbg[4096 + 1536 + wlin * 4 + 3] = (unsigned)t;
+  }
+
+  if (issuer_warp) {
+    if (elect_one()) {
+      const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
+      const Operand a = operand_mn_major(sbase + oA, L.B, 0, 0);
+      // phase 1: dW1 tile = dH2[:, ot]^T H1 (128 x 256), db1 = dH2[:, ot]^T [dz | 1]
+      mbar_wait(bar_ld1, 0);
+      tc_fence_after();
+      gemm_issue(tmem, a, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
+      gemm_issue(tmem + 352, a, z, 32, ksteps, false);
+      mma_commit(bar_p1);
+      mbar_wait(bar_p1, 0);  // dH2 and H1 consumed: their space takes the phase-2 operands
+      mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
+      bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
+      bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
+      if (preload_h2) {
+        mbar_expect_tx(bar_ld3, 2 * blk);
+        bulk_g2s(sbase + oH2, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
+      }
+      // phase 2 (under the dW1 drain): dW0 tile = dH1[:, ot]^T X, db0 = dH1[:, ot]^T [dz | 1], dW2 = H2[:, ot]^T [dz | 1]
+      mbar_wait(bar_ld2, 0);
+      tc_fence_after();
+      gemm_issue(tmem + 256, a, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
+      gemm_issue(tmem + 384, a, z, 32, ksteps, false);
+      if (!preload_h2) {  // the H2 tile overlaps the drain's staging buffer: wait for the drain
+        mbar_wait(bar_d1, 0);
+        mbar_expect_tx(bar_ld3, 2 * blk);
+        bulk_g2s(sbase + oH2, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
+      }
+      mbar_wait(bar_ld3, 0);
+      tc_fence_after();
+      gemm_issue(tmem + 416, operand_mn_major(sbase + oH2, L.B, 0, 0), z, 32, ksteps, false);
+      mma_commit(bar_p2);
+    }
+  } else {
+    bwd_weight2_drain(P, smem, tmem, bar_p1, bar_p2, bar_d1, ot, t, agent, in, nout, n0, warp, lane, quarter, cgrp, tid);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (P.dbg != nullptr && tid == 0 && wlin < 512) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + 1536 + wlin * 4 + 2] = gt;
+  }
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u + 1024u; }
@@ -996,6 +1205,8 @@ int bf16_create(iqlb_agents* h) {
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   P.drop_thresh = 0; P.drop_scale = 1.0f; P.drop_rng = h->rng; P.drop_it = h->it;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bwd_weight_smem(L.B)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)bwd_weight_smem(L.B)));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1118,6 +1329,11 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");
   if (h->zig >= 0) P.rev ^= 1;
+  static const bool bw_v1 = getenv("IQLB_BWDW_V1") && atoi(getenv("IQLB_BWDW_V1")) != 0;
+  if (!h->fused_adam && !bw_v1)
+    IQLB_CUDA(launch_pdl(bf16_bwd_weight2_kernel, dim3(L.H / 128, kTrain, N), dim3(kBwThreads), bwd_weight_smem(L.B), stream,
+                         pdl_enabled(16) && !h->prof, P));
+  else
   IQLB_CUDA(launch_pdl(h->fused_adam ? bf16_bwd_weight_kernel<true> : bf16_bwd_weight_kernel<false>, dim3(L.H / 128, kTrain, N),
                        dim3(256), bwd_weight_smem(L.B), stream, pdl_enabled(16) && !h->prof, P, h->grads, h->params, h->exp_avg, h->exp_avg_sq,
                        h->target, (const StepScalars*)h->scal));

@@ -505,8 +505,6 @@ def build_workload(args, dev, rank, world):
         ac = biql.GaussianPolicy(S_DIM, A_DIM, 1.0, dropout=ACTOR_DROPOUT)
         eng.adopt(a, qf, vf, ac, bind=False)
     eng.attach_replay(buf, reward_cols=cols, reward_variant=variant)
-    if args.precision == "bf16":
-        eng.debug_option(0, int(args.fused_adam))
     eng.set_overlap(bool(args.overlap))  # training-loop mode: the last group's optimizer runs under the next update
     return eng, buf, cols, variant, relabel
 
@@ -852,8 +850,6 @@ def main():
     ap.add_argument("--skip-relabel", action="store_true", help="skip the relabel benchmarks (kernel experiments)")
     ap.add_argument("--overlap", type=int, default=int(os.environ.get("IQLB_OVERLAP_ARG", "1")),
                     help="1: iqlb_agents_set_overlap (deferred join of the optimizer stream, synced before the clock stops)")
-    ap.add_argument("--fused-adam", type=int, default=int(os.environ.get("IQLB_FUSED_ADAM", "0")),
-                    help="1: Adam/Polyak inside the weight-gradient kernel (gradients never reach HBM)")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
                     help="cfg2: antmaze-shaped headline (configs[1]); cfg4: pen-human-shaped IQL leg of configs[3] "
                          "(45 obs / 24 act, actor_dropout 0.1) - relabel benchmarks and the CPU legs are skipped")

@@ -529,429 +529,33 @@ __global__ void __launch_bounds__(kBdThreads, 1) bf16_bwd_data_kernel(BfParams P
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward, weight gradients + optimizer.  grid (H/128 output-feature tiles, 4 nets, agents), 256 threads.
+// Backward, weight gradients.  grid (H/128 output-feature tiles, 4 nets, agents), 544 threads.
 // Every product reduces over the batch (K = B), with both operands read MN-major from images whose
 // rows are batch rows.  blk = B*128 bytes = one 64-column block of a batch-row image.
 // Shared memory: [bufA 2 blk | bufB 4 blk | dz image 1 blk | ctrl]
 //   phase 1: bufA = dH2[:, tile], bufB = H1          -> dW1 tile (TMEM 0..255), db1 (col 352+out)
 //   phase 2: bufA = dH1[:, tile], bufB[0..] = X_sa   -> dW0 tile (TMEM 256..), db0 (col 384+out)
-//            bufB[2 blk..] = H2[:, tile]             -> dW2^T tile (TMEM 416 + o)
+//            H2[:, tile] (2 blk of bufB)             -> dW2^T tile (TMEM 416 + o)
 // The dz image holds dz[b, 0..out) and a column of ones at `out`, so bias gradients are MMA columns.
-//
-// kFused: the gradient tile never leaves the SM.  It is transposed through shared memory (the upper
-// half of bufB, before H2 moves in) and consumed by Adam (torch _fused_adam math), the Polyak target
-// update (iql.py:127-129, Q nets) and the refresh of the bf16 weight images, all with 128-bit
-// row-contiguous accesses: HBM sees p, m, v (and target) exactly once per step and no gradient.
-// !kFused (debug/parity): gradients are written to `grads` for the stand-alone Adam kernel.
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void adam_update(float& p, float& m, float& v, float g, float ss, float bc2_sqrt) {
-  m = m + (1.0f - 0.9f) * (g - m);
-  v = 0.999f * v + (1.0f - 0.999f) * g * g;
-  const float denom = sqrtf(v) / bc2_sqrt + 1e-8f;
-  p = p - ss * (m / denom);
-}
-
-struct AdamPtrs {
-  float *p, *m, *v, *tgt;  // agent base pointers (tgt = nullptr for V / actor)
-  uint8_t *img, *timg;     // weight-image base of this network / of its target twin
-  float ss, bc2_sqrt, tau;
-};
-
-// one scalar parameter at packed offset e; img_off < 0: no bf16 image for this element
-__device__ __forceinline__ void adam_scalar(const AdamPtrs& A, int64_t e, float g, int64_t img_off) {
-  float p = A.p[e], m = A.m[e], v = A.v[e];
-  adam_update(p, m, v, g, A.ss, A.bc2_sqrt);
-  A.p[e] = p; A.m[e] = m; A.v[e] = v;
-  if (img_off >= 0) *reinterpret_cast<__nv_bfloat16*>(A.img + img_off) = __float2bfloat16_rn(p);
-  if (A.tgt) {
-    float tg = A.tgt[e];
-    tg = tg + A.tau * (p - tg);
-    A.tgt[e] = tg;
-    if (img_off >= 0) *reinterpret_cast<__nv_bfloat16*>(A.timg + img_off) = __float2bfloat16_rn(tg);
-  }
-}
-
-template <bool kFused>
-__device__ __forceinline__ void bwd_weight_body(const BfParams& P, float* __restrict__ grads, float* __restrict__ params,
-                                                float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
-                                                float* __restrict__ target, const StepScalars* __restrict__ scal,
-                                                const int ot, const int t, const int aidx, const int n_ag) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const Layout& L = P.L;
-  const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
-  const int s = train_stream(t);
-  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
-  const int quarter = warp & 3, chalf = warp >> 2;
-  const uint32_t blk = (uint32_t)L.B * 128u;
-  const uint32_t sbase = smem_u32(smem);
-  const uint32_t oA = 0, oB = 2 * blk, oZ = 6 * blk, oCtrl = 7 * blk;
-  const uint32_t bar_ld1 = sbase + oCtrl, bar_ld2 = bar_ld1 + 8, bar_ld3 = bar_ld1 + 16, bar_p1 = bar_ld1 + 24,
-                 bar_p2 = bar_ld1 + 32;
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 40);
-  const int in = L.in_dim(s), nout = L.out_dim(s);
-  const int64_t at = (int64_t)agent * kTrain + t;
-  const int ksteps = L.B / 16;
-  const int n0 = (in + 15) / 16 * 16;
-  // One thread issues an MMA only every ~105-120 clocks whatever N is (scripts/mma_rate.py), so the narrow products
-  // (bias columns, dW2, dW0) cost as much issue time as the 256-wide one: lane 0 of warps 0-2 issue them side by side.
-  const bool multi = P.opt_issuers == 2;
-
-  if (warp == 0 && elect_one()) {
-    if (sbase & 1023u) __trap();
-    for (int i = 0; i < 3; ++i) mbar_init(bar_ld1 + 8 * i, 1);
-    mbar_init(bar_p1, multi ? 2 : 1);  // one arrival per issuing thread
-    mbar_init(bar_p2, multi ? 3 : 1);
-    fence_barrier_init();
-    mbar_expect_tx(bar_ld1, 7 * blk);
-    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward output: before the PDL wait
-    bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);  // loss output, two kernels back
-    pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
-    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
-    if (P.opt_pf2) {  // phase-2 operands: L2 prefetch behind the phase-1 copies (a whole phase of lead time)
-      bulk_prefetch_l2(P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
-      bulk_prefetch_l2(P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk);
-    }
-  }
-  if (kFused && warp == 1 && elect_one()) {
-    // the optimizer state of this tile starts its trip from HBM to L2 now, under the operand loads and the
-    // MMAs: p, m, v (and the Polyak target) rows of W1 and W0 that the Adam epilogue below streams
-    const int64_t noff_ = L.net_off(s);
-    const int64_t e1 = (int64_t)agent * L.Pstride + noff_ + L.w1(in) + (int64_t)ot * 128 * L.H;
-    const int64_t e0 = (int64_t)agent * L.Pstride + noff_ + (int64_t)ot * 128 * in;
-    const uint32_t b1 = 128u * (uint32_t)L.H * 4u, b0 = 128u * (uint32_t)in * 4u;
-    bulk_prefetch_l2(params + e1, b1); bulk_prefetch_l2(exp_avg + e1, b1); bulk_prefetch_l2(exp_avg_sq + e1, b1);
-    bulk_prefetch_l2(params + e0, b0); bulk_prefetch_l2(exp_avg + e0, b0); bulk_prefetch_l2(exp_avg_sq + e0, b0);
-    if (t == 1 || t == 2) {
-      const int64_t q1 = (int64_t)agent * L.PQstride + noff_ + L.w1(in) + (int64_t)ot * 128 * L.H;
-      const int64_t q0 = (int64_t)agent * L.PQstride + noff_ + (int64_t)ot * 128 * in;
-      bulk_prefetch_l2(target + q1, b1); bulk_prefetch_l2(target + q0, b0);
-    }
-  }
-  if (warp == 1) tmem_alloc(sbase + oCtrl + 40, 512);
-  pdl_wait();
-  pdl_launch();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const bool dbgw = P.dbg != nullptr && ot == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
-#define IQLB_TSW(slot) do { if (dbgw) P.dbg[2048 + (slot)] = (unsigned long long)clock64(); } while (0)
-  IQLB_TSW(0);
-  const int wlin = ot + 2 * (t + kTrain * aidx);
-  if (P.dbg != nullptr && tid == 0 && wlin < 512) {  // (SM, start) of every CTA: scripts/timeline.py
-    unsigned smid; unsigned long long gt;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-    P.dbg[4096 + 1536 + wlin * 4] = smid; P.dbg[4096 + 1536 + wlin * 4 + 1] = gt; P.dbg[4096 + 1536 + wlin * 4 + 3] = (unsigned)t;
-  }
-  const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
-  if ((warp == 0 || (multi && warp == 1)) && elect_one()) {
-    mbar_wait(bar_ld1, 0);
-    tc_fence_after();
-    const Operand a1 = operand_mn_major(sbase + oA, L.B, 0, 0);
-    if (warp == 0) gemm_issue(tmem, a1, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
-    if (warp == 1 || !multi) gemm_issue(tmem + 352, a1, z, 32, ksteps, false);
-    mma_commit(bar_p1);
-  }
-  __syncwarp();
-  mbar_wait(bar_p1, 0);
-  tc_fence_after();
-  IQLB_TSW(1);
-  if (warp == 0 && elect_one()) {  // phase-1 operands consumed: refill (H2 follows once the staging area is free again)
-    mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
-    bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
-    bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
-  }
-  __syncwarp();
-  const int trow = quarter * 32 + lane;  // tile row drained by this thread (two threads per row)
-  // (tile row trow of output-feature tile ot = feature ot * 128 + trow)
-  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-  const int64_t noff = L.net_off(s);
-  float* gnet = grads + (int64_t)agent * L.Pstride + noff;
-  AdamPtrs A;
-  {
-    const StepScalars sc = scal[agent];
-    A.p = params + (int64_t)agent * L.Pstride;
-    A.m = exp_avg + (int64_t)agent * L.Pstride;
-    A.v = exp_avg_sq + (int64_t)agent * L.Pstride;
-    const bool is_q = (t == 1 || t == 2);
-    A.tgt = is_q ? target + (int64_t)agent * L.PQstride : nullptr;
-    A.img = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net_of_stream(s) * P.net_bytes;
-    A.timg = A.img + 4 * P.net_bytes;
-    A.ss = t == 0 ? sc.ss_v : (is_q ? sc.ss_q : sc.ss_a);
-    A.bc2_sqrt = sc.bc2_sqrt;
-    A.tau = sc.tau;
-  }
-  float* stg = reinterpret_cast<float*>(smem + oB + 2 * blk);  // 2 x [128 rows][64] fp32, float4 index ^ (row & 15)
-
-  {
-    if (!kFused) {
-    // ---- dW1: four 64-column chunks, double-buffered through shared memory ----
-#pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      float* sb = stg + (cc & 1) * (128 * 64);
-      float v[32];
-      tmem_ld32(lane_base + (uint32_t)(cc * 64 + chalf * 32), v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int q = 0; q < 8; ++q)
-        *reinterpret_cast<float4*>(sb + trow * 64 + (((chalf * 8 + q) ^ (trow & 15)) << 2)) =
-            make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-      __syncthreads();  // chunk cc staged (and every warp is done reading buffer cc&1 from chunk cc-2)
-      const int rr = lane >> 3, l8 = lane & 7;
-      if (!kFused) {  // row-contiguous 128-bit stores of the gradient tile (8 lanes cover 256 B of a row)
-        __nv_bfloat16* gw1 = P.gradh + (int64_t)agent * L.Pstride + noff + L.w1(in) + (int64_t)(ot * 128) * L.H + cc * 64 + 8 * l8;
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {  // bf16, as the reference's autocast weight-gradient GEMM emits them
-          const int r = warp * 16 + it * 4 + rr;
-          const float4 g0 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8) ^ (r & 15)) << 2));
-          const float4 g1 = *reinterpret_cast<const float4*>(sb + r * 64 + (((2 * l8 + 1) ^ (r & 15)) << 2));
-          *reinterpret_cast<uint4*>(gw1 + (int64_t)r * L.H) =
-              make_uint4(pack_bf16(g0.x, g0.y), pack_bf16(g0.z, g0.w), pack_bf16(g1.x, g1.y), pack_bf16(g1.z, g1.w));
-        }
-        continue;
-      }
-    }
-    }
-    if (kFused) {
-      // ---- dW1 with Adam: four chunks of 32 rows x 256 columns.  The two warps that own TMEM lane quarter
-      // qq stage chunk qq (fp32, 16-byte words XOR-swizzled by row) while all eight warps stream the previous
-      // chunk: every row is 1 KB of contiguous p / m / v / target, a chunk 32 KB, so HBM sees the same linear
-      // streams as the stand-alone Adam kernel (the L2 prefetch at the top of the kernel covers the latency).
-      auto write_chunk = [&](int qq) {
-        float* sb = stg + (qq & 1) * (32 * 256);
-#pragma unroll 1
-        for (int c4 = 0; c4 < 4; ++c4) {
-          const int c0 = chalf * 128 + c4 * 32;
-          float v[32];
-          tmem_ld32(lane_base + (uint32_t)c0, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int q = 0; q < 8; ++q)
-            *reinterpret_cast<float4*>(sb + lane * 256 + ((((c0 >> 2) + q) ^ (lane & 7)) << 2)) =
-                make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-        }
-      };
-      if (quarter == 0) write_chunk(0);
-      __syncthreads();
-      IQLB_TSW(2);
-#pragma unroll 1
-      for (int qq = 0; qq < 4; ++qq) {
-        if (qq < 3 && quarter == qq + 1) write_chunk(qq + 1);
-        const float* sb = stg + (qq & 1) * (32 * 256);
-        float4 pq[8], mq[8], vq[8], tq[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {  // row warp*4 + u/2 of the chunk, 16-byte word lane + 32*(u%2): 512 B per warp access
-          const int r = warp * 4 + (u >> 1), j = lane + 32 * (u & 1);
-          const int64_t e = noff + L.w1(in) + (int64_t)(ot * 128 + qq * 32 + r) * L.H + 4 * j;
-          pq[u] = *reinterpret_cast<const float4*>(A.p + e);
-          mq[u] = *reinterpret_cast<const float4*>(A.m + e);
-          vq[u] = *reinterpret_cast<const float4*>(A.v + e);
-          tq[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
-        }
-        IQLB_TSW(13 + qq);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int r = warp * 4 + (u >> 1), j = lane + 32 * (u & 1);
-          const int fr = ot * 128 + qq * 32 + r;
-          const int64_t e = noff + L.w1(in) + (int64_t)fr * L.H + 4 * j;
-          const float4 g = *reinterpret_cast<const float4*>(sb + r * 256 + ((j ^ (r & 7)) << 2));
-          float4 &p = pq[u], &m = mq[u], &v = vq[u], &tg = tq[u];
-          adam_update(p.x, m.x, v.x, g.x, A.ss, A.bc2_sqrt); adam_update(p.y, m.y, v.y, g.y, A.ss, A.bc2_sqrt);
-          adam_update(p.z, m.z, v.z, g.z, A.ss, A.bc2_sqrt); adam_update(p.w, m.w, v.w, g.w, A.ss, A.bc2_sqrt);
-          *reinterpret_cast<float4*>(A.p + e) = p;
-          *reinterpret_cast<float4*>(A.m + e) = m;
-          *reinterpret_cast<float4*>(A.v + e) = v;
-          const int64_t ioff = P.w0_bytes + image_off(L.H, fr, 4 * j);  // 4 bf16 = half a 16-byte image chunk
-          *reinterpret_cast<uint2*>(A.img + ioff) = make_uint2(pack_bf16(p.x, p.y), pack_bf16(p.z, p.w));
-          if (A.tgt) {
-            tg.x += A.tau * (p.x - tg.x); tg.y += A.tau * (p.y - tg.y); tg.z += A.tau * (p.z - tg.z); tg.w += A.tau * (p.w - tg.w);
-            *reinterpret_cast<float4*>(A.tgt + e) = tg;
-            *reinterpret_cast<uint2*>(A.timg + ioff) = make_uint2(pack_bf16(tg.x, tg.y), pack_bf16(tg.z, tg.w));
-          }
-        }
-        IQLB_TSW(8 + qq);
-        __syncthreads();  // chunk qq consumed, chunk qq+1 staged
-        IQLB_TSW(3 + qq);
-      }
-    }
-    fence_async_smem();
-    __syncthreads();  // staging area free: H2 may move in
-    if (warp == 0 && elect_one()) {
-      mbar_expect_tx(bar_ld3, 2 * blk);
-      bulk_g2s(sbase + oB + 2 * blk, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
-    }
-  }
-  if ((warp == 0 || (multi && (warp == 1 || warp == 2))) && elect_one()) {
-    if (warp != 2) {
-      mbar_wait(bar_ld2, 0);
-      tc_fence_after();
-      const Operand a0 = operand_mn_major(sbase + oA, L.B, 0, 0);
-      if (warp == 0) gemm_issue(tmem + 256, a0, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
-      if (warp == 1 || !multi) gemm_issue(tmem + 384, a0, z, 32, ksteps, false);
-    }
-    if (warp == 2 || !multi) {
-      mbar_wait(bar_ld3, 0);
-      tc_fence_after();
-      gemm_issue(tmem + 416, operand_mn_major(sbase + oB + 2 * blk, L.B, 0, 0), z, 32, ksteps, false);
-    }
-    mma_commit(bar_p2);
-  }
-  __syncwarp();
-  // Everything of the second drain that does not depend on the MMAs is done while they run: the head-bias /
-  // log_std update (gradients come from the loss kernel) and the optimizer-state loads of the flat pass.
-  const int g1 = 128 * in, g2 = g1 + 128, g3 = g2 + 128, gtot = g3 + 128 * nout;
-  const int64_t e_w0 = noff + L.w0() + (int64_t)ot * 128 * in, e_b1 = noff + L.b1(in) + ot * 128,
-                e_b0 = noff + L.b0(in) + ot * 128, e_w2 = noff + L.w2(in) + ot * 128;
-  auto flat_elem = [&](int i) -> int64_t {  // packed-parameter offset of staged gradient word i (see G0..G3 below)
-    if (i < g1) return e_w0 + i;
-    if (i < g2) return e_b1 + (i - g1);
-    if (i < g3) return e_b0 + (i - g2);
-    return e_w2 + (int64_t)((i - g3) >> 7) * L.H + ((i - g3) & 127);
-  };
-  constexpr int kU = 6;  // 16-byte words per thread and array in flight (covers in <= 40 in one pass)
-  float4 pq2[kU], mq2[kU], vq2[kU], tq2[kU];
-  if (kFused) {
-    if (ot == 0) {  // head bias (and log_std)
-      if (tid < nout) adam_scalar(A, noff + L.b2(in, nout) + tid, gnet[L.b2(in, nout) + tid], -1);
-      if (t == 3 && !L.deterministic && tid >= 32 && tid < 32 + L.A)
-        adam_scalar(A, L.off_logstd + (tid - 32), grads[(int64_t)agent * L.Pstride + L.off_logstd + (tid - 32)], -1);
-    }
-#pragma unroll
-    for (int u = 0; u < kU; ++u) {
-      const int i = tid * 4 + u * 1024;
-      if (i < gtot) {
-        const int64_t e = flat_elem(i);
-        pq2[u] = *reinterpret_cast<const float4*>(A.p + e); mq2[u] = *reinterpret_cast<const float4*>(A.m + e);
-        vq2[u] = *reinterpret_cast<const float4*>(A.v + e);
-        tq2[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
-      }
-    }
-  }
-  mbar_wait(bar_p2, 0);
-  tc_fence_after();
-  IQLB_TSW(7);
-  {
-    // ---- everything else through shared memory in packed-parameter order:
-    //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
-    // each a contiguous, 16-byte aligned span of the parameter vector -> one flat float4 Adam pass
-    if (chalf == 0) {
-      for (int c0 = 0; c0 < n0; c0 += 16) {
-        float v[16];
-        tmem_ld16(lane_base + 256u + (uint32_t)c0, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (c0 + j < in) stg[trow * in + c0 + j] = v[j];
-      }
-      float v[32];
-      tmem_ld32(lane_base + 384u, v);
-      tmem_ld_wait();
-      float db = 0.f;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
-      stg[g2 + trow] = db;
-    } else {
-      float v[32];
-      tmem_ld32(lane_base + 352u, v);
-      tmem_ld_wait();
-      float db = 0.f;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
-      stg[g1 + trow] = db;
-      tmem_ld32(lane_base + 416u, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int o = 0; o < kOutMax; ++o)
-        if (o < nout) stg[g3 + o * 128 + trow] = v[o];
-    }
-    __syncthreads();
-    if (!kFused) {  // flat, 128-bit copy of the staged gradients into the gradient buffer
-      __nv_bfloat16* gagent = P.gradh + (int64_t)agent * L.Pstride;
-      for (int i = tid * 4; i < gtot; i += 1024) {
-        const float4 g = *reinterpret_cast<const float4*>(stg + i);
-        *reinterpret_cast<uint2*>(gagent + flat_elem(i)) = make_uint2(pack_bf16(g.x, g.y), pack_bf16(g.z, g.w));
-      }
-    }
-    for (int i0 = tid * 4; kFused && i0 < gtot; i0 += 1024 * kU) {
-      if (i0 != tid * 4) {  // wider first layers: later passes load here
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-          const int i = i0 + u * 1024;
-          if (i < gtot) {
-            const int64_t e = flat_elem(i);
-            pq2[u] = *reinterpret_cast<const float4*>(A.p + e); mq2[u] = *reinterpret_cast<const float4*>(A.m + e);
-            vq2[u] = *reinterpret_cast<const float4*>(A.v + e);
-            tq2[u] = A.tgt ? *reinterpret_cast<const float4*>(A.tgt + e) : make_float4(0, 0, 0, 0);
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const int i = i0 + u * 1024;
-        if (i >= gtot) continue;
-        const int64_t e = flat_elem(i);
-        const float4 g = *reinterpret_cast<const float4*>(stg + i);
-        float4 &p = pq2[u], &m = mq2[u], &v = vq2[u], &tg = tq2[u];
-        adam_update(p.x, m.x, v.x, g.x, A.ss, A.bc2_sqrt); adam_update(p.y, m.y, v.y, g.y, A.ss, A.bc2_sqrt);
-        adam_update(p.z, m.z, v.z, g.z, A.ss, A.bc2_sqrt); adam_update(p.w, m.w, v.w, g.w, A.ss, A.bc2_sqrt);
-        *reinterpret_cast<float4*>(A.p + e) = p;
-        *reinterpret_cast<float4*>(A.m + e) = m;
-        *reinterpret_cast<float4*>(A.v + e) = v;
-        if (A.tgt) {
-          tg.x += A.tau * (p.x - tg.x); tg.y += A.tau * (p.y - tg.y); tg.z += A.tau * (p.z - tg.z); tg.w += A.tau * (p.w - tg.w);
-          *reinterpret_cast<float4*>(A.tgt + e) = tg;
-        }
-        if (i < g1) {  // W0 elements also live in the bf16 weight image
-          const float pv[4] = {p.x, p.y, p.z, p.w}, tv[4] = {tg.x, tg.y, tg.z, tg.w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int r = (i + j) / in, c = (i + j) - r * in;
-            const int64_t ioff = image_off(L.H, ot * 128 + r, c);
-            *reinterpret_cast<__nv_bfloat16*>(A.img + ioff) = __float2bfloat16_rn(pv[j]);
-            if (A.tgt) *reinterpret_cast<__nv_bfloat16*>(A.timg + ioff) = __float2bfloat16_rn(tv[j]);
-          }
-        }
-      }
-    }
-  }
-  IQLB_TSW(12);
-  tc_fence_before();
-  __syncthreads();
-  if (P.dbg != nullptr && tid == 0 && wlin < 512) {
-    unsigned long long gt;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-    P.dbg[4096 + 1536 + wlin * 4 + 2] = gt;
-  }
-  if (warp == 1) tmem_dealloc(tmem, 512);
-}
-
-template <bool kFused>
-__global__ void __launch_bounds__(256, 1) bf16_bwd_weight_kernel(BfParams P, float* __restrict__ grads,
-                                                                 float* __restrict__ params, float* __restrict__ exp_avg,
-                                                                 float* __restrict__ exp_avg_sq, float* __restrict__ target,
-                                                                 const StepScalars* __restrict__ scal) {
-  bwd_weight_body<kFused>(P, grads, params, exp_avg, exp_avg_sq, target, scal, (int)blockIdx.x, (int)blockIdx.y,
-                          (int)blockIdx.z, (int)gridDim.z);
-}
-
-// ------------------------------------------------------------------------------------------------
-// Weight gradients, second schedule (round 2).  Same arithmetic, operands, TMEM columns and outputs as bwd_weight_body<false>;
-// what changes is who does what:
-//   warps 0-15  drain: 4 warps per TMEM lane quarter (16 of every 64 columns each) - the 8-warp version spent 5 of its 10 us
-//               per CTA moving the 128 x 256 dW1 tile TMEM -> shared memory -> global at 12 % warp occupancy;
+// Gradients leave as bf16 (what the reference's autocast weight-gradient GEMMs emit) for the stand-alone optimizer kernel.
+//   warps 0-15  drain: 4 warps per TMEM lane quarter (16 of every 64 columns each) - the round-1 kernel (8 warps that also
+//               issued the MMAs) spent 5 of its 10 us per CTA moving the 128 x 256 dW1 tile TMEM -> shared memory -> global
+//               at 12 % warp occupancy;
 //   warp 16     one elected thread does every bulk copy and every MMA issue, so the phase-2 products (dW0, db0, and with
 //               one input block also dW2) are loaded and ISSUED under the dW1 drain instead of after it.
-// Shared memory as before ([dH2|dH1 2 blk][H1 4 blk -> X, H2, staging][dz 1 blk]); with one input block (state_dim + action_dim
-// <= 64) the H2 tile is requested right after phase 1 into the two H1 blocks behind X and the dW1 drain stages through one
-// 32 KB buffer; with two input blocks H2 still follows the drain.
+// With one input block (state_dim + action_dim <= 64) the H2 tile is requested right after phase 1 into the two H1 blocks
+// behind X and the dW1 drain stages through one 32 KB buffer (H1 block 3); with two input blocks H2 follows the drain.
+// Measured (scripts/gpu_bw_ab.sh, same box): CTA 9.9 -> 8.0 us, kernel 53.7 -> 45.9 us.  Not kept: the dW1 product as four
+// 64-column MMAs with a barrier each, so that the drain starts after the first (the products are shared-memory bound, the
+// A tile is re-read per block and the phase-2 operands arrive later: CTA 8.4 us); Adam / Polyak fused into this kernel's
+// epilogue (round 1: with one CTA per SM its HBM streaming is serialised behind operand loads and MMAs, 276 vs 55 + 119 us).
 // ------------------------------------------------------------------------------------------------
 constexpr int kBwDrainThreads = 512, kBwThreads = kBwDrainThreads + 32;
 
 __device__ __forceinline__ void bw_bar(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kBwDrainThreads) : "memory"); }
 
-// the 16 drain warps of bf16_bwd_weight2_kernel
-__device__ __forceinline__ void bwd_weight2_drain(const BfParams& P, uint8_t* smem, const uint32_t tmem, const uint32_t bar_p1,
+// the 16 drain warps of bf16_bwd_weight_kernel
+__device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* smem, const uint32_t tmem, const uint32_t bar_p1,
                                                   const uint32_t bar_p2, const uint32_t bar_d1, const int ot, const int t,
                                                   const int agent, const int in, const int nout, const int n0, const int warp,
                                                   const int lane, const int quarter, const int cgrp, const int tid) {
@@ -1050,7 +654,7 @@ __device__ __forceinline__ void bwd_weight2_drain(const BfParams& P, uint8_t* sm
   }
 }
 
-__global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight2_kernel(BfParams P) {
+__global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int ot = (int)blockIdx.x, t = (int)blockIdx.y, aidx = (int)blockIdx.z, n_ag = (int)gridDim.z;
@@ -1132,7 +736,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight2_kernel(BfParam
       mma_commit(bar_p2);
     }
   } else {
-    bwd_weight2_drain(P, smem, tmem, bar_p1, bar_p2, bar_d1, ot, t, agent, in, nout, n0, warp, lane, quarter, cgrp, tid);
+    bwd_weight_drain(P, smem, tmem, bar_p1, bar_p2, bar_d1, ot, t, agent, in, nout, n0, warp, lane, quarter, cgrp, tid);
   }
   tc_fence_before();
   __syncthreads();
@@ -1205,11 +809,7 @@ int bf16_create(iqlb_agents* h) {
   IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   P.drop_thresh = 0; P.drop_scale = 1.0f; P.drop_rng = h->rng; P.drop_it = h->it;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)bwd_weight_smem(L.B)));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)bwd_weight_smem(L.B)));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)bwd_weight_smem(L.B)));
   st->dirty = true;
   return IQLB_OK;
@@ -1329,15 +929,9 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");
   if (h->zig >= 0) P.rev ^= 1;
-  static const bool bw_v1 = getenv("IQLB_BWDW_V1") && atoi(getenv("IQLB_BWDW_V1")) != 0;
-  if (!h->fused_adam && !bw_v1)
-    IQLB_CUDA(launch_pdl(bf16_bwd_weight2_kernel, dim3(L.H / 128, kTrain, N), dim3(kBwThreads), bwd_weight_smem(L.B), stream,
-                         pdl_enabled(16) && !h->prof, P));
-  else
-  IQLB_CUDA(launch_pdl(h->fused_adam ? bf16_bwd_weight_kernel<true> : bf16_bwd_weight_kernel<false>, dim3(L.H / 128, kTrain, N),
-                       dim3(256), bwd_weight_smem(L.B), stream, pdl_enabled(16) && !h->prof, P, h->grads, h->params, h->exp_avg, h->exp_avg_sq,
-                       h->target, (const StepScalars*)h->scal));
-  pf.mark(h->fused_adam ? "bf16_bwd_weight_adam" : "bf16_bwd_weight");
+  IQLB_CUDA(launch_pdl(bf16_bwd_weight_kernel, dim3(L.H / 128, kTrain, N), dim3(kBwThreads), bwd_weight_smem(L.B), stream,
+                       pdl_enabled(16) && !h->prof, P));
+  pf.mark("bf16_bwd_weight");
   return IQLB_OK;
 }
 

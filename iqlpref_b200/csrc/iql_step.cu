@@ -626,7 +626,6 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
 static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded, bool ride_gather = false) {
   const Layout& L = h->L;
   const bool bf = h->desc.precision == 1;
-  if (bf && h->fused_adam) return IQLB_OK;
   const BfParams* bp = bf16_params(h);
   static const int l2hint_env = getenv("IQLB_L2HINT") ? atoi(getenv("IQLB_L2HINT")) : -1;
   // bounded (under the next group's tensor-core kernels): the optimizer state streams through L2 with evict_first so that
@@ -682,7 +681,7 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   const int N = h->desc.n_agents;
   int rc;
   Prof pf(h, st);
-  int G = (h->desc.precision == 1 && !h->prof && !h->fused_adam) ? h->n_groups : 1;
+  int G = (h->desc.precision == 1 && !h->prof) ? h->n_groups : 1;
   if (h->pre_valid && !sampled) {  // an explicit batch follows a look-ahead gather: let it finish, then overwrite it
     if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
     h->pre_valid = false;
@@ -690,7 +689,7 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   if (G <= 1) {
     if ((rc = join_groups(h, st))) return rc;  // (a profiled or fused-Adam step after overlapped ones)
     if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
-    const bool lookahead = sampled && h->desc.precision == 1 && !h->prof && h->idx_out == nullptr && !h->fused_adam;
+    const bool lookahead = sampled && h->desc.precision == 1 && !h->prof && h->idx_out == nullptr;
     if (lookahead && h->presample == 2) {  // the next step's gather rides in the optimizer launch
       if ((rc = step_adam(h, 0, N, pf, st, false, true))) return rc;
       pf.done();
@@ -1074,7 +1073,9 @@ extern "C" int iqlb_agents_set_actor_dropout(iqlb_agents* h, float p) {
 extern "C" int iqlb_agents_debug_option(iqlb_agents* h, int32_t option, int32_t value) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   IQLB_REQUIRE(option == 0, "unknown option");
-  h->fused_adam = value != 0;
+  // option 0 selected the optimizer fused into the weight-gradient kernel (round 1; measured slower, removed in round 2):
+  // only 0 - gradients materialised for the stand-alone optimizer kernel, the one schedule left - is accepted
+  IQLB_REQUIRE(value == 0, "option 0 (fused optimizer) has been removed: value must be 0");
   return IQLB_OK;
 }
 
@@ -1131,7 +1132,7 @@ extern "C" int iqlb_agents_debug_copy(iqlb_agents* h, int32_t which, void* dst, 
     case 5: src = h->dH1; n = N * kTrain * BH; break;
     case 6:
       n = N * L.Pstride;
-      if (h->desc.precision == 1 && !h->fused_adam && bf16_params(h)) {
+      if (h->desc.precision == 1 && bf16_params(h)) {
         if (nbytes) *nbytes = n * (int64_t)sizeof(float);
         if (dst) {
           bf16_to_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(bf16_params(h)->gradh, (float*)dst, n);

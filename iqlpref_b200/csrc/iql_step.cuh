@@ -209,7 +209,6 @@ struct iqlb_agents {
   iqlb::GemmTask *t_fwd0 = nullptr, *t_fwd1 = nullptr, *t_bw1 = nullptr, *t_bd1 = nullptr, *t_bw0 = nullptr;
   void* bf16_state = nullptr;  // precision==1 extension (tcgen05 path)
   float drop_p = 0.f;          // actor dropout probability (precision 0 only)
-  bool fused_adam = false;     // precision==1: Adam/Polyak inside the weight-gradient kernel (debug option 0)
   // per-kernel CUDA-event timing (iqlb_agents_profile): ev[i], ev[i+1] bracket launch i of a step
   static constexpr int kMaxProf = 24;
   bool prof = false;

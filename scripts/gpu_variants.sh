@@ -16,7 +16,6 @@ try:
 except Exception as e: print(sys.argv[1], "FAILED", e)
 PY
 }
-run base IQLB_FUSED_ADAM=0
-run fused IQLB_FUSED_ADAM=1
+run base IQLB_X=0
 run groups2 IQLB_GROUPS=2
 run oldfwd IQLB_FWD_PERSIST=0

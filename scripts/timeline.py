@@ -11,14 +11,11 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--agents-per-gpu", type=int, default=64)
 ap.add_argument("--rows", type=int, default=1_000_000)
 ap.add_argument("--precision", default="bf16")
-ap.add_argument("--fused-adam", type=int, default=0)
 args = ap.parse_args()
 args.scaling, args.agents_total, args.pt_windows, args.overlap, args.skip_relabel = "weak", 64, 0, 0, True
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
 eng, buf, cols, variant, _ = bench.build_workload(args, dev, 0, 1)
-if args.fused_adam:
-    eng.debug_option(0, 1)
 for _ in range(5):
     eng.train(None)
 torch.cuda.synchronize()
@@ -35,12 +32,6 @@ show("epilogue: start, MMA0 ok, epi0 end, BW ok, MMA1 ok, epi1 end, barrier, pre
 show("tile end: load_bw issued, stores issued, heads written", 1536, 3)
 show("mma: L0 issue, kb0..kb3 issue", 512, 5)
 show("producer: X issue, ring e0..e4 issue", 1024, 6)
-
-w = ts[2048:2048 + 24]
-if w[0]:
-    names = ["start", "p1 done", "chunk0 staged", "c0 sync", "c1 sync", "c2 sync", "c3 sync", "p2 done", "c0 adam", "c1 adam", "c2 adam",
-             "c3 adam", "end", "c0 loads issued", "c1 loads", "c2 loads", "c3 loads"]
-    print("bwd_weight (fused) CTA (0,1,0): " + ", ".join(f"{n}={int(x - w[0])}" for n, x in zip(names, w) if x))
 
 l = ts[3072:3072 + 8]
 if l[0]:

@@ -529,7 +529,7 @@ __global__ void __launch_bounds__(kBdThreads, 1) bf16_bwd_data_kernel(BfParams P
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward, weight gradients.  grid (H/128 output-feature tiles, 4 nets, agents), 544 threads.
+// Backward, weight gradients.  Tiles = (H/128 output-feature tiles, 4 nets, agents), one persistent CTA of 544 threads per SM.
 // Every product reduces over the batch (K = B), with both operands read MN-major from images whose
 // rows are batch rows.  blk = B*128 bytes = one 64-column block of a batch-row image.
 // Shared memory: [bufA 2 blk | bufB 4 blk | dz image 1 blk | ctrl]
@@ -554,11 +554,14 @@ constexpr int kBwDrainThreads = 512, kBwThreads = kBwDrainThreads + 32;
 
 __device__ __forceinline__ void bw_bar(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(kBwDrainThreads) : "memory"); }
 
-// the 16 drain warps of bf16_bwd_weight_kernel
-__device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* smem, const uint32_t tmem, const uint32_t bar_p1,
-                                                  const uint32_t bar_p2, const uint32_t bar_d1, const int ot, const int t,
-                                                  const int agent, const int in, const int nout, const int n0, const int warp,
-                                                  const int lane, const int quarter, const int cgrp, const int tid) {
+// the 16 drain warps of bf16_bwd_weight_kernel (ph = parity of the tile count, d1col = TMEM column of this tile's db1,
+// bar_d2 = "final drain done")
+__device__ __forceinline__ void bwd_weight_drain_p(const BfParams& P, uint8_t* smem, const uint32_t tmem, const uint32_t bar_p1,
+                                                   const uint32_t bar_p2, const uint32_t bar_d1, const uint32_t bar_d2,
+                                                   const uint32_t ph, const uint32_t d1col, const int ot, const int t,
+                                                   const int agent, const int in, const int nout, const int n0, const int warp,
+                                                   const int lane, const int quarter, const int cgrp, const int tid,
+                                                   const int tile) {
   const Layout& L = P.L;
   const int s = train_stream(t);
   const uint32_t blk = (uint32_t)L.B * 128u;
@@ -567,7 +570,14 @@ __device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* sme
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   const int64_t noff = L.net_off(s);
   __nv_bfloat16* gagent = P.gradh + (int64_t)agent * L.Pstride;
-  mbar_wait(bar_p1, 0);
+  const bool persist = bar_d2 != 0;
+  if (P.dbg != nullptr && tid == 0 && tile < 512) {  // (SM, start) of every tile: scripts/timeline.py
+    unsigned smid; unsigned long long gt;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[4096 + 1536 + tile * 4] = smid; P.dbg[4096 + 1536 + tile * 4 + 1] = gt; P.dbg[4096 + 1536 + tile * 4 + 3] = (unsigned)t;
+  }
+  mbar_wait(bar_p1, ph);
   tc_fence_after();
   {
     // ---- dW1: four 64-column chunks through one [128 rows][64] fp32 buffer (float4 index ^ (row & 15)); bf16 rows leave
@@ -579,7 +589,7 @@ __device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* sme
       float v[16];
       tmem_ld16(lane_base + (uint32_t)(cc * 64 + cgrp * 16), v);
       tmem_ld_wait();
-      if (cc > 0) bw_bar(2);  // every warp has read chunk cc - 1 out of the buffer
+      if (cc > 0 || persist) bw_bar(2);  // every warp has read chunk cc - 1 (persistent: the previous tile's staged gradients) out of the buffer
 #pragma unroll
       for (int q = 0; q < 4; ++q)
         *reinterpret_cast<float4*>(sb + trow * 64 + (((cgrp * 4 + q) ^ (trow & 15)) << 2)) =
@@ -596,12 +606,13 @@ __device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* sme
       }
     }
   }
-  if (P.KXB != 1) {  // the H2 tile moves into the staging buffer's neighbourhood: tell the issuing thread the drain is over
+  if (P.KXB != 1 || persist) {  // the staging buffer (and, for the next tile, TMEM columns 0..255) may be reused
     fence_async_smem();
+    tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_d1);
   }
-  mbar_wait(bar_p2, 0);
+  mbar_wait(bar_p2, ph);
   tc_fence_after();
   // ---- everything else through shared memory in packed-parameter order (the operands of phase 2 are dead):
   //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
@@ -633,7 +644,7 @@ __device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* sme
 #pragma unroll
     for (int j = 0; j < 32; ++j) db = (j == nout) ? v[j] : db;
     stg[g2 + trow] = db;
-    tmem_ld32(lane_base + 352u, v);
+    tmem_ld32(lane_base + d1col, v);
     tmem_ld_wait();
     db = 0.f;
 #pragma unroll
@@ -652,26 +663,59 @@ __device__ __forceinline__ void bwd_weight_drain(const BfParams& P, uint8_t* sme
     const float4 g = *reinterpret_cast<const float4*>(stg + i);
     *reinterpret_cast<uint2*>(gagent + flat_elem(i)) = make_uint2(pack_bf16(g.x, g.y), pack_bf16(g.z, g.w));
   }
+  if (persist) {  // staging area and TMEM columns 256.. are free for the next tile
+    fence_async_smem();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_d2);
+    if (P.dbg != nullptr && tid == 0 && tile < 512) {
+      unsigned long long gt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+      P.dbg[4096 + 1536 + tile * 4 + 2] = gt;
+    }
+  }
 }
 
-__global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams P) {
+// ------------------------------------------------------------------------------------------------
+// The kernel is persistent: one CTA per SM walks the tiles (ot, net, agent) round-robin (253.2 -> 251.4 us per step against
+// one CTA per tile).  What the loop adds:
+//   * the next tile's phase-1 operands are requested as soon as the current tile's last product has completed (dH2, dz and
+//     the first two H1 blocks at once, H1 blocks 2-3 when the final drain has left the staging area), i.e. under the final
+//     drain instead of behind a CTA exit / launch (1.2 us) + barrier / TMEM set-up;
+//   * db1 alternates between TMEM columns 352 and 448, so phase 1 of tile i+1 never waits for the final drain of tile i.
+// Every barrier completes once per tile: parity = tile count & 1.
+// ------------------------------------------------------------------------------------------------
+struct BwTile {
+  int ot, t, agent, s, in, nout, n0;
+  int64_t at;
+};
+__device__ __forceinline__ BwTile bw_tile(const BfParams& P, int tile, int n_ag) {
+  BwTile T;
+  T.ot = tile & 1;
+  T.t = (tile >> 1) & 3;
+  const int aidx = tile >> 3;
+  T.agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
+  T.s = train_stream(T.t);
+  T.in = P.L.in_dim(T.s);
+  T.nout = P.L.out_dim(T.s);
+  T.n0 = (T.in + 15) / 16 * 16;
+  T.at = (int64_t)T.agent * kTrain + T.t;
+  return T;
+}
+
+__global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams P, int n_tiles) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
-  const int ot = (int)blockIdx.x, t = (int)blockIdx.y, aidx = (int)blockIdx.z, n_ag = (int)gridDim.z;
-  const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
-  const int s = train_stream(t);
+  const int n_ag = n_tiles >> 3;
   const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;
   const int quarter = warp & 3, cgrp = (warp >> 2) & 3;
   const uint32_t blk = (uint32_t)L.B * 128u;
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oB = 2 * blk, oZ = 6 * blk, oCtrl = 7 * blk;
   const uint32_t bar_ld1 = sbase + oCtrl, bar_ld2 = bar_ld1 + 8, bar_ld3 = bar_ld1 + 16, bar_p1 = bar_ld1 + 24,
-                 bar_p2 = bar_ld1 + 32, bar_d1 = bar_ld1 + 40;
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 48);
-  const int in = L.in_dim(s), nout = L.out_dim(s);
-  const int64_t at = (int64_t)agent * kTrain + t;
+                 bar_p2 = bar_ld1 + 32, bar_d1 = bar_ld1 + 40, bar_d2 = bar_ld1 + 48;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 56);
   const int ksteps = L.B / 16;
-  const int n0 = (in + 15) / 16 * 16;
   const bool preload_h2 = P.KXB == 1;
   const uint32_t oH2 = preload_h2 ? oB + blk : oB + 2 * blk;
   const bool issuer_warp = warp == kBwDrainThreads / 32;
@@ -680,71 +724,88 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 5; ++i) mbar_init(bar_ld1 + 8 * i, 1);
     mbar_init(bar_d1, kBwDrainThreads / 32);
+    mbar_init(bar_d2, kBwDrainThreads / 32);
     fence_barrier_init();
-    mbar_expect_tx(bar_ld1, 7 * blk);
-    bulk_g2s(sbase + oB, P.h1 + at * P.h_bytes, 4 * blk, bar_ld1);  // forward output: before the PDL wait
-    bulk_g2s(sbase + oZ, P.dz + at * P.z_bytes, blk, bar_ld1);      // loss output, two kernels back
-    pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
-    bulk_g2s(sbase + oA, P.dh2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld1);
+    if ((int)blockIdx.x < n_tiles) {
+      const BwTile T = bw_tile(P, blockIdx.x, n_ag);
+      mbar_expect_tx(bar_ld1, 7 * blk);
+      bulk_g2s(sbase + oB, P.h1 + T.at * P.h_bytes, 4 * blk, bar_ld1);  // forward output: before the PDL wait
+      bulk_g2s(sbase + oZ, P.dz + T.at * P.z_bytes, blk, bar_ld1);      // loss output, two kernels back
+      pdl_wait();  // dH2 / dH1 come from the data-gradient kernel
+      bulk_g2s(sbase + oA, P.dh2 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld1);
+    }
   }
-  if (warp == 1) tmem_alloc(sbase + oCtrl + 48, 512);
+  if (warp == 1) tmem_alloc(sbase + oCtrl + 56, 512);
   pdl_wait();
   pdl_launch();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const int wlin = ot + 2 * (t + kTrain * aidx);
-  if (P.dbg != nullptr && tid == 0 && wlin < 512) {  // (SM, start) of every CTA: scripts/timeline.py
-    unsigned smid; unsigned long long gt;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-    P.dbg[4096 + 1536 + wlin * 4] = smid; P.dbg[4096 + 1536 + wlin * 4 + 1] = gt; P.dbg[4096 + 1536 + wlin * 4 + 3] = (unsigned)t;
-  }
 
   if (issuer_warp) {
     if (elect_one()) {
       const Operand z = operand_mn_major(sbase + oZ, L.B, 0, 0);
       const Operand a = operand_mn_major(sbase + oA, L.B, 0, 0);
-      // phase 1: dW1 tile = dH2[:, ot]^T H1 (128 x 256), db1 = dH2[:, ot]^T [dz | 1]
-      mbar_wait(bar_ld1, 0);
-      tc_fence_after();
-      gemm_issue(tmem, a, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
-      gemm_issue(tmem + 352, a, z, 32, ksteps, false);
-      mma_commit(bar_p1);
-      mbar_wait(bar_p1, 0);  // dH2 and H1 consumed: their space takes the phase-2 operands
-      mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
-      bulk_g2s(sbase + oA, P.dh1 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld2);
-      bulk_g2s(sbase + oB, P.xsa + (int64_t)agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
-      if (preload_h2) {
-        mbar_expect_tx(bar_ld3, 2 * blk);
-        bulk_g2s(sbase + oH2, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t ph = (uint32_t)(it & 1);
+        const BwTile T = bw_tile(P, tile, n_ag);
+        const uint32_t d1col = (it & 1) ? 448u : 352u;
+        // phase 1: dW1 tile = dH2[:, ot]^T H1 (128 x 256), db1 = dH2[:, ot]^T [dz | 1]
+        mbar_wait(bar_ld1, ph);
+        if (it > 0) mbar_wait(bar_d1, ph ^ 1u);  // the previous tile's dW1 has left TMEM columns 0..255
+        tc_fence_after();
+        gemm_issue(tmem, a, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
+        gemm_issue(tmem + d1col, a, z, 32, ksteps, false);
+        mma_commit(bar_p1);
+        mbar_wait(bar_p1, ph);  // dH2 and H1 consumed: their space takes the phase-2 operands
+        mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
+        bulk_g2s(sbase + oA, P.dh1 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld2);
+        bulk_g2s(sbase + oB, P.xsa + (int64_t)T.agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
+        if (preload_h2) {
+          mbar_expect_tx(bar_ld3, 2 * blk);
+          bulk_g2s(sbase + oH2, P.h2 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld3);
+        }
+        // phase 2 (under the dW1 drain): dW0 tile = dH1[:, ot]^T X, db0 = dH1[:, ot]^T [dz | 1], dW2 = H2[:, ot]^T [dz | 1]
+        mbar_wait(bar_ld2, ph);
+        if (it > 0) mbar_wait(bar_d2, ph ^ 1u);  // the previous tile's final drain has read TMEM columns 256..447
+        tc_fence_after();
+        gemm_issue(tmem + 256, a, operand_mn_major(sbase + oB, L.B, 0, 0), T.n0, ksteps, false);
+        gemm_issue(tmem + 384, a, z, 32, ksteps, false);
+        if (!preload_h2) {  // the H2 tile overlaps the drain's staging buffer: wait for the drain
+          mbar_wait(bar_d1, ph);
+          mbar_expect_tx(bar_ld3, 2 * blk);
+          bulk_g2s(sbase + oH2, P.h2 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld3);
+        }
+        mbar_wait(bar_ld3, ph);
+        tc_fence_after();
+        gemm_issue(tmem + 416, operand_mn_major(sbase + oH2, L.B, 0, 0), z, 32, ksteps, false);
+        mma_commit(bar_p2);
+        // the next tile's phase-1 operands, under this tile's final drain
+        const int next = tile + (int)gridDim.x;
+        if (next < n_tiles) {
+          const BwTile Nx = bw_tile(P, next, n_ag);
+          mbar_wait(bar_p2, ph);  // every operand of this tile is dead
+          mbar_expect_tx(bar_ld1, 7 * blk);
+          bulk_g2s(sbase + oA, P.dh2 + Nx.at * P.h_bytes + (int64_t)(2 * Nx.ot) * blk, 2 * blk, bar_ld1);
+          bulk_g2s(sbase + oZ, P.dz + Nx.at * P.z_bytes, blk, bar_ld1);
+          bulk_g2s(sbase + oB, P.h1 + Nx.at * P.h_bytes, 2 * blk, bar_ld1);
+          mbar_wait(bar_d2, ph);  // the final drain has read its staging area (H1 blocks 2-3)
+          bulk_g2s(sbase + oB + 2 * blk, P.h1 + Nx.at * P.h_bytes + 2 * (int64_t)blk, 2 * blk, bar_ld1);
+        }
       }
-      // phase 2 (under the dW1 drain): dW0 tile = dH1[:, ot]^T X, db0 = dH1[:, ot]^T [dz | 1], dW2 = H2[:, ot]^T [dz | 1]
-      mbar_wait(bar_ld2, 0);
-      tc_fence_after();
-      gemm_issue(tmem + 256, a, operand_mn_major(sbase + oB, L.B, 0, 0), n0, ksteps, false);
-      gemm_issue(tmem + 384, a, z, 32, ksteps, false);
-      if (!preload_h2) {  // the H2 tile overlaps the drain's staging buffer: wait for the drain
-        mbar_wait(bar_d1, 0);
-        mbar_expect_tx(bar_ld3, 2 * blk);
-        bulk_g2s(sbase + oH2, P.h2 + at * P.h_bytes + (int64_t)(2 * ot) * blk, 2 * blk, bar_ld3);
-      }
-      mbar_wait(bar_ld3, 0);
-      tc_fence_after();
-      gemm_issue(tmem + 416, operand_mn_major(sbase + oH2, L.B, 0, 0), z, 32, ksteps, false);
-      mma_commit(bar_p2);
     }
   } else {
-    bwd_weight_drain(P, smem, tmem, bar_p1, bar_p2, bar_d1, ot, t, agent, in, nout, n0, warp, lane, quarter, cgrp, tid);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const BwTile T = bw_tile(P, tile, n_ag);
+      bwd_weight_drain_p(P, smem, tmem, bar_p1, bar_p2, bar_d1, bar_d2, (uint32_t)(it & 1), (it & 1) ? 448u : 352u, T.ot, T.t,
+                         T.agent, T.in, T.nout, T.n0, warp, lane, quarter, cgrp, tid, tile);
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (P.dbg != nullptr && tid == 0 && wlin < 512) {
-    unsigned long long gt;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-    P.dbg[4096 + 1536 + wlin * 4 + 2] = gt;
-  }
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
@@ -929,8 +990,10 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
                        (const float*)h->params, (const float*)h->d_out));
   pf.mark("bf16_bwd_data");
   if (h->zig >= 0) P.rev ^= 1;
-  IQLB_CUDA(launch_pdl(bf16_bwd_weight_kernel, dim3(L.H / 128, kTrain, N), dim3(kBwThreads), bwd_weight_smem(L.B), stream,
-                       pdl_enabled(16) && !h->prof, P));
+  const int n_tiles = (L.H / 128) * kTrain * N;
+  const int n_sm = h->n_sm > 0 ? h->n_sm : 148;
+  IQLB_CUDA(launch_pdl(bf16_bwd_weight_kernel, dim3((unsigned)(n_tiles < n_sm ? n_tiles : n_sm)), dim3(kBwThreads),
+                       bwd_weight_smem(L.B), stream, pdl_enabled(16) && !h->prof, P, n_tiles));
   pf.mark("bf16_bwd_weight");
   return IQLB_OK;
 }

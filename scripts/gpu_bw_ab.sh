@@ -13,6 +13,5 @@ except Exception as e: print(sys.argv[2], "FAILED", e)
 PY
 }
 run new IQLB_X=0
-run old IQLB_BWDW_V1=1
 run new2 IQLB_X=0
 timeout 200 python scripts/timeline.py > $OUT/timeline.txt 2>&1; grep -A12 "bwd_weight CTAs" $OUT/timeline.txt | tail -8

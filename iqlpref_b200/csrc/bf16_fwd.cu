@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   const Layout& L = P.L;
   // single-thread roles (producer, MMA issuer, store thread) are chosen by elect.sync inside warp-uniform branches, so the
   // operands of their bulk copies / MMAs / commits stay in uniform registers (umma.cuh: elect_one)
-  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31, wu = warp;  // (measured: with warp = tid >> 5 for the
+  // epilogue arithmetic this kernel is 3 us slower, while the non-persistent bf16_fwd_kernel is 30 % FASTER that way)
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bars = sbase + oCtrl;
   auto bar = [&](int i) -> uint32_t { return bars + 8u * (uint32_t)i; };
@@ -132,7 +133,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   };
   // PDL: the weight images (Adam of the previous step) are older than the immediate predecessor (the gather):
   // the first tile's weights start towards L2 before this grid waits for the gather's input images
-  if (warp == 0 && (int)blockIdx.x < n_tiles && elect_one()) {
+  if (wu == 0 && (int)blockIdx.x < n_tiles && elect_one()) {
     int a0, s0, h0;
     const uint8_t *w0p, *x0p;
     const float* f0p;
@@ -141,7 +142,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   }
   pdl_wait();
   pdl_launch();
-  if (warp == 0) {
+  if (wu == 0) {
     // ------------------------------------------------------------------ producer
     if (elect_one()) {
       int c = 0;  // ring entries issued so far (5 per tile: W0, W1 block 0..3)
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (wu == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (elect_one()) {
       int c = 0;
@@ -209,7 +210,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         mma_commit(bar(MMA1));
       }
     }
-  } else if (warp < kAuxWarp) {
+  } else if (wu < kAuxWarp) {
     // ------------------------------------------------------------------ epilogue
     // warp -> TMEM lane quarter (warp % 4, the hardware rule), column half of a 64-column block, and
     // block parity: warps of parity p drain blocks p and p + 2, so blocks 0 and 1 finish together and

@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(256) replay_gather_pack_kernel(BfParams P, Gat
   extern __shared__ __align__(16) float srow[];  // [rows_per_cta][R]
   pdl_wait();  // first kernel of a step: the previous step's Adam (launched before it) must be complete
   pdl_launch();
-  gather_pack_body(P, G, (int)blockIdx.x, (int)blockIdx.y, srow);
+  gather_pack_body(P, G, (int)blockIdx.x, P.agent0 + (int)blockIdx.y, srow);
 }
 
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
@@ -111,7 +111,8 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int half = blockIdx.x, s = blockIdx.y, agent = P.agent0 + blockIdx.z;
-  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int wu = warp_uniform();  // for the single-thread roles only (elect_one(), umma.cuh): as the source of quarter / chalf it cost 30 %
   const int quarter = warp & 3, chalf = warp >> 2;
   const int KXB = P.KXB, nring = 4 - KXB;
   const uint32_t sbase = smem_u32(smem);
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   float* sb1 = reinterpret_cast<float*>(smem + oX);   // valid after layer 0 has consumed X
   float* sw2 = sb1 + 256;
 
-  if (warp == 0 && elect_one()) {
+  if (wu == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
     mbar_init(bar_l0, 1);
     for (int c = 0; c < 4; ++c) mbar_init(bar_w1 + 8 * c, 1);
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 0 && elect_one()) {
+  if (wu == 0 && elect_one()) {
     mbar_wait(bar_l0, 0);
     tc_fence_after();
     gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oW0, L.H, 0), 256, (in + 15) / 16, false);
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   __syncwarp();
   mbar_wait(bar_mma0, 0);
   tc_fence_after();
-  if (warp == 0 && elect_one()) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
+  if (wu == 0 && elect_one()) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
     for (int c = nring; c < 4; ++c) {
       mbar_expect_tx(bar_w1 + 8 * c, 32768u);
       bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
   fence_async_smem();
   tc_fence_before();
   __syncthreads();
-  if (warp == 0 && elect_one()) {
+  if (wu == 0 && elect_one()) {
     tc_fence_after();
     if (t >= 0) {
       uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
@@ -302,7 +303,7 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
       }
     }
   }
-  if (t >= 0 && warp == 0 && elect_one()) {
+  if (t >= 0 && wu == 0 && elect_one()) {
     uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
     for (int cb = 0; cb < 4; ++cb)
       bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
@@ -341,7 +342,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   }
   const int agent = P.agent0 + (P.rev ? n_ag - 1 - aidx : aidx);
   const int s = train_stream(t), net = net_of_stream(s);
-  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;  // single-thread roles: elect_one() (umma.cuh)
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wu = warp_uniform();  // wu: single-thread roles only (elect_one(), umma.cuh)
   const int quarter = warp & 3, cgrp = (warp >> 2) & 3;  // column group: 64 columns of the dH2 tile, 16 of every dH1 block
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
@@ -364,7 +365,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
     P.dbg[4096 + cta_lin * 3] = smid; P.dbg[4096 + cta_lin * 3 + 1] = gt;
   }
-  if (warp == 0 && elect_one()) {
+  if (wu == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
     fence_barrier_init();
@@ -462,12 +463,12 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   tc_fence_after();
   IQLB_TSD(4);
   const uint32_t tmem = *tmem_slot;
-  if ((warp == kBdWorkerWarps || warp == kBdWorkerWarps + 1) && elect_one()) {
+  if ((wu == kBdWorkerWarps || wu == kBdWorkerWarps + 1) && elect_one()) {
     // two issuing threads (even / odd blocks): one thread gets an MMA out only every ~105-120 clocks whatever N is
     // (scripts/mma_rate.py), which at N = 64 is a quarter of the tensor pipe's rate
-    const int first = warp == kBdWorkerWarps ? 0 : (P.opt_issuers == 2 ? 1 : 4);
+    const int first = wu == kBdWorkerWarps ? 0 : (P.opt_issuers == 2 ? 1 : 4);
     const int step = P.opt_issuers == 2 ? 2 : 1;
-    if (warp == kBdWorkerWarps) {
+    if (wu == kBdWorkerWarps) {
       uint8_t* dh2 = P.dh2 + at * P.h_bytes;
       for (int cb = 0; cb < 4; ++cb)
         bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
@@ -480,7 +481,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
       gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
       mma_commit(bar_mma + 8 * ib);
     }
-    if (warp == kBdWorkerWarps) bulk_wait_read0();  // the dH2 tile has left shared memory
+    if (wu == kBdWorkerWarps) bulk_wait_read0();  // the dH2 tile has left shared memory
   }
   __syncwarp();
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -505,13 +506,13 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     for (int q = 0; q < 2; ++q) st_chunk(stage, row, 16 * cgrp + 8 * q, v + 8 * q);
     fence_async_smem();
     asm volatile("bar.sync 1, %0;" ::"n"(kBdWorkerThreads) : "memory");
-    if (warp == 0 && elect_one()) {
+    if (wu == 0 && elect_one()) {
       bulk_s2g(dh1 + (int64_t)ib * L.B * 128 + (int64_t)half * 16384, sbase + oW + (uint32_t)ib * 32768u, 16384u);
       bulk_commit();
     }
   }
   IQLB_TSD(9);
-  if (warp == 0 && elect_one()) bulk_wait_read0();
+  if (wu == 0 && elect_one()) bulk_wait_read0();
   if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {
     unsigned long long gt;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
@@ -707,7 +708,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   const int n_ag = n_tiles >> 3;
-  const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wu = warp_uniform();
   const int quarter = warp & 3, cgrp = (warp >> 2) & 3;
   const uint32_t blk = (uint32_t)L.B * 128u;
   const uint32_t sbase = smem_u32(smem);
@@ -718,7 +719,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
   const int ksteps = L.B / 16;
   const bool preload_h2 = P.KXB == 1;
   const uint32_t oH2 = preload_h2 ? oB + blk : oB + 2 * blk;
-  const bool issuer_warp = warp == kBwDrainThreads / 32;
+  const bool issuer_warp = wu == kBwDrainThreads / 32;
 
   if (issuer_warp && elect_one()) {
     if (sbase & 1023u) __trap();

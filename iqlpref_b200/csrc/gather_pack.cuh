@@ -1,6 +1,5 @@
-// ReplayBuffer.sample (iql.py:211-221) fused with the packing of the tensor-core input images: the body shared by the stand-alone
-// kernel (bf16_step.cu: replay_gather_pack_kernel) and by the gather CTAs that ride in the optimizer launch (iql_step.cu:
-// adam_polyak_kernel, look-ahead sampling of the next step's batch).
+// ReplayBuffer.sample (iql.py:211-221) fused with the packing of the tensor-core input images: the body of
+// replay_gather_pack_kernel (bf16_step.cu).
 #pragma once
 #include "iql_step.cuh"
 #include "umma.cuh"
@@ -24,11 +23,12 @@ struct GatherArgs {
 // reads reward / done / action from them) and both bf16 input images in one pass.  srow: rows_per_cta * R floats.
 // call: number of earlier calls by this CTA (persistent callers loop over blocks; the mbarrier is initialised by call 0 and
 // waited on with the call's phase parity; the caller separates calls with __syncthreads()).
-__device__ __forceinline__ void gather_pack_body(const BfParams& P, const GatherArgs& G, int bx, int by, float* srow, int call = 0) {
+// agent = first agent of the launch + by (the caller passes it: writing P.agent0 in a kernel would copy the whole parameter
+// struct to local memory).
+__device__ __forceinline__ void gather_pack_body(const BfParams& P, const GatherArgs& G, int bx, int agent, float* srow, int call = 0) {
   __shared__ __align__(8) uint64_t gather_bar;
   __shared__ int64_t gather_row[32];
   const Layout& L = P.L;
-  const int agent = P.agent0 + by;
   const int t = threadIdx.x;
   const int vec_per_row = G.vec_per_row, rows_per_cta = G.rows_per_cta;
   const int b0 = bx * rows_per_cta;

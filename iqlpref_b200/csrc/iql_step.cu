@@ -10,7 +10,6 @@
 #include <stdlib.h>
 
 #include "iql_step.cuh"
-#include "gather_pack.cuh"
 
 namespace iqlb {
 
@@ -21,7 +20,6 @@ int bf16_create(iqlb_agents* h);
 void bf16_destroy(iqlb_agents* h);
 int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream, bool packed);
 int bf16_gather_pack(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
-GatherArgs bf16_gather_args(const iqlb_agents* h);
 int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t stream);
 const BfParams* bf16_params(const iqlb_agents* h);
 void bf16_mark_dirty(iqlb_agents* h);
@@ -343,33 +341,16 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(Layout L, const float* __
 //     with ~39 K registers and all of shared memory; a 256-thread CTA of this kernel needs no shared memory and
 //     <= 48 registers per thread (launch bound: 5 CTAs per SM), so two of them fit beside it on every SM and stream HBM while the GEMM CTA waits on
 //     its own latencies.  An unbounded grid would instead fill every SM's thread slots and lock the GEMM kernels out.
+// (Round 2, measured and removed: the next step's gather as extra CTAs of this launch, and a one-shot persistent grid of 5
+//  CTAs per SM.  With the gather code merely COMPILED INTO this kernel - shared memory, an mbarrier, one __syncthreads, none
+//  of it executed by the optimizer CTAs - the optimizer pass went from 121 to 133 us; same box, same step otherwise:
+//  241.6 us with this plain kernel and a separate gather launch, 257.3 with the gather CTAs riding along, 252.6 persistent.)
 template <bool kPersist>
 __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layout L, float* __restrict__ params,
                                                           float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
                                                           float* __restrict__ target, const float* __restrict__ grads,
                                                           const StepScalars* __restrict__ scal, BfParams BP, int shadow,
-                                                          int agent0, int n_agents_launch, int chunks_per_agent,
-                                                          GatherArgs GA, int n_gather) {
-  // Look-ahead sampling: the first n_gather CTAs of the one-shot launch gather and pack the NEXT step's batch (the loss
-  // kernel has already advanced the RNG offsets, and every consumer of this step's batch rows / input images - forward,
-  // loss, weight gradients - completed before this launch).  The random row reads hide under the optimizer's HBM stream
-  // and the next step starts with its forward kernel.
-  if (n_gather > 0) {
-    extern __shared__ __align__(16) float gather_srow[];
-    BP.agent0 = agent0;
-    if (!kPersist) {
-      if ((int)blockIdx.x < n_gather) {
-        gather_pack_body(BP, GA, (int)blockIdx.x % GA.blocks_x, (int)blockIdx.x / GA.blocks_x, gather_srow);
-        return;
-      }
-    } else {  // persistent grid: every CTA takes its share of the gather blocks first, then walks its optimizer chunks
-      int call = 0;
-      for (int gb = blockIdx.x; gb < n_gather; gb += gridDim.x, ++call) {
-        gather_pack_body(BP, GA, gb % GA.blocks_x, gb / GA.blocks_x, gather_srow, call);
-        __syncthreads();
-      }
-    }
-  }
+                                                          int agent0, int n_agents_launch, int chunks_per_agent) {
   // Thread t handles the 16-byte words t (and t + 256, ...) of the chunk, so every warp access is 512 contiguous bytes per
   // array.  Network segments start on multiples of 8 floats: a word never straddles two optimizers, and inside W1 it
   // is half of a 16-byte chunk of the image.
@@ -485,7 +466,7 @@ __global__ void __launch_bounds__(256, kPersist ? 5 : 1) adam_polyak_kernel(Layo
       first = false;
     }
   } else {
-    body((int)blockIdx.x - (kPersist ? 0 : n_gather), true);
+    body((int)blockIdx.x, true);
   }
 }
 
@@ -571,7 +552,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   int rc;
   if (sampled && bf && h->pre_valid) {
     // gathered and packed during the previous step's optimizer kernel (look-ahead sampling)
-    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
+    IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
     h->pre_valid = false;
   } else if (sampled && bf) {
     if ((rc = bf16_gather_pack(h, a0, n, pf, st))) return rc;
@@ -623,7 +604,7 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
   return IQLB_OK;
 }
 
-static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded, bool ride_gather = false) {
+static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, bool bounded) {
   const Layout& L = h->L;
   const bool bf = h->desc.precision == 1;
   const BfParams* bp = bf16_params(h);
@@ -635,24 +616,10 @@ static int step_adam(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st, b
   const int n_chunks = cpa * n;
   int grid = n_chunks;
   if (bounded && h->n_sm > 0 && h->adam_ctas_per_sm > 0 && grid > h->n_sm * h->adam_ctas_per_sm) grid = h->n_sm * h->adam_ctas_per_sm;
-  // One-shot launch of the whole sweep: with many more chunks than resident CTAs a persistent grid of 5 CTAs per SM (full
-  // residency at <= 48 registers) streams HBM a few percent faster than one short-lived CTA per 4 KB chunk (measured on
-  // B200, scripts/gpu_adam_ab.sh: 265.4 -> 260.9 us per step; 4 or 8 CTAs per SM are slower).  IQLB_ADAM_PERSIST=0: off.
-  static const int persist_env = getenv("IQLB_ADAM_PERSIST") ? atoi(getenv("IQLB_ADAM_PERSIST")) : 5;
-  if (!bounded && persist_env > 0 && h->n_sm > 0 && grid >= 8 * h->n_sm * persist_env) grid = h->n_sm * persist_env;
-  GatherArgs GA{};
-  int n_gather = 0;
-  size_t smem = 0;
-  if (ride_gather && bf && !bounded) {
-    GA = bf16_gather_args(h);
-    n_gather = GA.blocks_x * n;
-    smem = (size_t)GA.rows_per_cta * L.R * 4;
-  }
-  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)(grid < n_chunks ? grid : grid + n_gather)), dim3(256), smem, st,
+  IQLB_CUDA(launch_pdl(grid < n_chunks ? adam_polyak_kernel<true> : adam_polyak_kernel<false>, dim3((unsigned)grid), dim3(256), 0, st,
                        bf && !bounded && pdl_enabled(32) && !h->prof, L, h->params, h->exp_avg, h->exp_avg_sq, h->target,
                        (const float*)h->grads, (const StepScalars*)h->scal, bf ? *bp : BfParams{},
-                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa, GA, n_gather));
-  if (n_gather > 0) { h->pre_valid = true; h->pre_inline = true; }
+                       (bf ? 1 : 0) | (l2hint ? 2 : 0) | ((bf && h->zig == 1) ? 4 : 0), a0, n, cpa));
   pf.mark(bf ? "adam_polyak_shadow" : "adam_polyak");
   return IQLB_OK;
 }
@@ -683,21 +650,14 @@ static int step_device(iqlb_agents* h, bool sampled, cudaStream_t st) {
   Prof pf(h, st);
   int G = (h->desc.precision == 1 && !h->prof) ? h->n_groups : 1;
   if (h->pre_valid && !sampled) {  // an explicit batch follows a look-ahead gather: let it finish, then overwrite it
-    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
+    IQLB_CUDA(cudaStreamWaitEvent(st, h->ev_pre_join, 0));
     h->pre_valid = false;
   }
   if (G <= 1) {
     if ((rc = join_groups(h, st))) return rc;  // (a profiled or fused-Adam step after overlapped ones)
     if ((rc = step_chain(h, 0, N, sampled, pf, st))) return rc;
     const bool lookahead = sampled && h->desc.precision == 1 && !h->prof && h->idx_out == nullptr;
-    if (lookahead && h->presample == 2) {  // the next step's gather rides in the optimizer launch
-      if ((rc = step_adam(h, 0, N, pf, st, false, true))) return rc;
-      pf.done();
-      if (h->zig >= 0) h->zig ^= 1;
-      return IQLB_OK;
-    }
     if (lookahead && h->presample == 1) {
-      h->pre_inline = false;
       if (!h->pre_stream) {
         int prio_lo = 0, prio_hi = 0;  // highest priority: the small gather must not queue behind the optimizer's CTAs
         IQLB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
@@ -814,8 +774,8 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   h->zig = (getenv("IQLB_ZIGZAG") && atoi(getenv("IQLB_ZIGZAG")) == 0) ? -1 : 0;
   // measured on B200 (64 agents): 268.7 vs 269.1 us per step - the forward kernel loses its programmatic overlap
   // with the optimizer's tail to the cross-stream join, which eats what the hidden gather saves.  Off by default.
-  // look-ahead sampling: 0 off, 1 the next step's gather on a side stream (measured neutral), 2 (default) in the optimizer launch
-  h->presample = getenv("IQLB_PRESAMPLE") ? atoi(getenv("IQLB_PRESAMPLE")) : 2;
+  // look-ahead sampling: the next step's gather on a side stream under the optimizer kernel (measured neutral, off)
+  h->presample = (getenv("IQLB_PRESAMPLE") && atoi(getenv("IQLB_PRESAMPLE")) != 0) ? 1 : 0;
   if (!rc && d->precision == 1) {
     const char* env = getenv("IQLB_GROUPS");
     // Opt-in (IQLB_GROUPS=2): measured on B200 with 64 agents, two groups are SLOWER than one (313-370 vs 260 us per
@@ -891,7 +851,7 @@ extern "C" int iqlb_agents_set_replay(iqlb_agents* h, const float* table, int64_
   IQLB_REQUIRE(n_rows > 0, "empty table");
   IQLB_REQUIRE(((uintptr_t)table & 15) == 0, "table must be 16-byte aligned");
   if (h->pre_valid) {  // a look-ahead gather of the old table is in flight (or done): drop it
-    if (!h->pre_inline) IQLB_CUDA(cudaStreamSynchronize(h->pre_stream));
+    IQLB_CUDA(cudaStreamSynchronize(h->pre_stream));
     h->pre_valid = false;
   }
   h->table = table; h->n_rows = n_rows; h->reward_cols = reward_cols; h->reward_variant = reward_variant;
@@ -1001,7 +961,7 @@ extern "C" int iqlb_agents_refresh(iqlb_agents* h, void* stream) {
   IQLB_REQUIRE(h != nullptr, "null handle");
   { int rcj = join_groups(h, (cudaStream_t)stream); if (rcj) return rcj; }
   if (h->pre_valid) {  // caller-owned state (parameters, RNG offsets) changed: the look-ahead batch is stale
-    if (!h->pre_inline) IQLB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_pre_join, 0));
+    IQLB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_pre_join, 0));
     h->pre_valid = false;
   }
   if (h->desc.precision == 1) return bf16_refresh(h, (cudaStream_t)stream);

@@ -248,7 +248,6 @@ struct iqlb_agents {
   cudaStream_t pre_stream = nullptr;
   cudaEvent_t ev_pre_fork = nullptr, ev_pre_join = nullptr;
   bool pre_valid = false;
-  bool pre_inline = false;  // the look-ahead batch was gathered by CTAs of the optimizer launch (same stream: no event to wait on)
   int presample = 0;
 };
 

@@ -102,7 +102,11 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const bool dbg = P.dbg != nullptr && blockIdx.x == 0;
+#ifdef IQLB_NO_TIMELINE
+#define IQLB_TS(slot) do { } while (0)
+#else
 #define IQLB_TS(slot) do { if (dbg) P.dbg[(slot)] = (unsigned long long)clock64(); } while (0)
+#endif
 
   auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
                        const float*& fnet) {

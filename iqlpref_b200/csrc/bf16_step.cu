@@ -357,7 +357,11 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   // relu' AND keep); exactly 1 when dropout is off
   const float gscale = (t == 3 && P.drop_thresh != 0) ? P.drop_scale : 1.0f;
   const bool dbgd = P.dbg != nullptr && half == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
+#ifdef IQLB_NO_TIMELINE
+#define IQLB_TSD(slot) do { } while (0)
+#else
 #define IQLB_TSD(slot) do { if (dbgd) P.dbg[2560 + (slot)] = (unsigned long long)clock64(); } while (0)
+#endif
   IQLB_TSD(0);
   if (P.dbg != nullptr && tid == 0 && cta_lin < 1024) {  // (SM, start) of every CTA: scripts/timeline.py --waves
     unsigned smid; unsigned long long gt;

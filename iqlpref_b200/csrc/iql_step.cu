@@ -81,7 +81,11 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
                             uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0, unsigned long long* dbg,
                             const uint8_t* __restrict__ wimg, int64_t agent_w_bytes, int64_t net_bytes,
                             __nv_bfloat16* __restrict__ gradh, float* __restrict__ losses_snap) {
+#ifdef IQLB_NO_TIMELINE
+#define IQLB_TSL(slot) do { } while (0)
+#else
 #define IQLB_TSL(slot) do { if (dbg && blockIdx.x == 0) dbg[3072 + (slot)] = (unsigned long long)clock64(); } while (0)
+#endif
   if (threadIdx.x == 0) IQLB_TSL(0);
   // per-warp partial sums of every reduced quantity: 0 vl | 1 ql | 2 al | 3..5 head bias grads (V, Q1, Q2)
   // | 6.. actor head bias grads [A] | 6+A.. log_std grads [A]; one block-wide pass at the end

@@ -1,5 +1,7 @@
 #!/usr/bin/env python
-"""Per-tile clock64 timeline of CTA 0 of the persistent forward kernel (IQLB_TIMELINE=1)."""
+"""Per-tile clock64 timeline of CTA 0 of the persistent forward kernel (IQLB_TIMELINE=1).
+Needs a library built with the stamps: `make -C iqlpref_b200/csrc clean && make -C iqlpref_b200/csrc TIMELINE=1` (the default
+build leaves them out; the per-SM wave tables of the gradient kernels work with either build)."""
 import os, sys, argparse
 os.environ["IQLB_TIMELINE"] = "1"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

@@ -322,9 +322,11 @@ __global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const floa
 // dH1[:, 64*ib..] = dH2 * W1[:, 64*ib..] as four N=64 MMAs (W1 image read MN-major: N = in, K = out),
 // each drained (mask, bf16) while the next one runs.  Both tiles go to HBM as images for the weight kernel.
 // ------------------------------------------------------------------------------------------------
-// 16 worker warps (four per TMEM lane quarter, 64 of the 256 columns each) + two MMA-issuing warps.  With eight workers
-// the CUDA-core dH2 = (dz W2) * relu' tile took 4.3 k of a CTA's 12 k clocks at two warps per scheduler.
-constexpr int kBdWorkerWarps = 16, kBdWorkerThreads = kBdWorkerWarps * 32, kBdThreads = kBdWorkerThreads + 64;
+// 16 worker warps (four per TMEM lane quarter) + one issuing warp.  With eight workers the CUDA-core dH2 = (dz W2) * relu'
+// tile took 4.3 k of a CTA's 12 k clocks at two warps per scheduler.  Round 2: the tile is produced K-block by K-block (64 of
+// its 256 columns at a time, every worker 16 of them) and the issuing thread multiplies block kb by W1 (N = 256, 4 k-steps)
+// while the workers compute block kb + 1, so the tensor-core product hides under the CUDA-core one instead of following it.
+constexpr int kBdWorkerWarps = 16, kBdWorkerThreads = kBdWorkerWarps * 32, kBdThreads = kBdWorkerThreads + 32;
 __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __restrict__ params,
                                               const float* __restrict__ d_out, const int cta_lin, const int n_ag,
                                               const int bx, const int by, const int bz) {
@@ -346,7 +348,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   const int quarter = warp & 3, cgrp = (warp >> 2) & 3;  // column group: 64 columns of the dH2 tile, 16 of every dH1 block
   const uint32_t sbase = smem_u32(smem);
   const uint32_t oA = 0, oW = 65536u, oStage = oW + 131072u, oCtrl = oStage + 32768u;
-  const uint32_t bar_w = sbase + oCtrl, bar_mma = bar_w + 32;
+  const uint32_t bar_w = sbase + oCtrl, bar_mma = bar_w + 32, bar_k = bar_w + 72;  // (tmem slot at + 64)
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 64);
   const int in = L.in_dim(s), nout = L.out_dim(s);
   const uint8_t* w1img = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net * P.net_bytes + P.w0_bytes;
@@ -371,7 +373,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   }
   if (wu == 0 && elect_one()) {
     if (sbase & 1023u) __trap();
-    for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); }
+    for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); mbar_init(bar_k + 8 * i, kBdWorkerWarps); }
     fence_barrier_init();
     // the TMA engine keeps only a few tens of KB in flight per SM: ask L2 for the whole image first, so the
     // copies below trail a DRAM fetch that runs at full rate instead of paying one DRAM latency per piece
@@ -395,8 +397,12 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     for (int i = tid; i < nout * 256; i += kBdWorkerThreads) sw2[i] = __ldg(fnet + L.w2(in) + i);
   const int row = quarter * 32 + lane, brow = half * 128 + row;
   const int cbeg = cgrp * 64;
-  const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32) + cgrp * 2;
-  const uint2 m2w = worker ? *reinterpret_cast<const uint2*>(m2p) : make_uint2(0, 0);
+  // this thread's 16 columns of K-block kb of the dH2 tile: bits (cgrp & 1) * 16 .. + 15 of mask word 2 kb + cgrp / 2
+  const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32);
+  uint64_t m2h = 0;
+#pragma unroll
+  for (int kb = 0; kb < 4; ++kb)
+    m2h |= (uint64_t)(worker ? (m2p[kb * 2 + (cgrp >> 1)] >> ((cgrp & 1) * 16)) & 0xffffu : 0u) << (16 * kb);
   const uint32_t* m1p = P.mask1 + (at * L.B + brow) * (L.H / 32);
   uint32_t m1w[4];  // this thread's 16 columns of block ib: bits (cgrp & 1) * 16 .. + 15 of word 2 ib + cgrp / 2
 #pragma unroll
@@ -412,16 +418,19 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     for (int o = 0; o < kOutMax; ++o) dz[o] = (worker && o < nout) ? dout[(int64_t)(drow0 + o) * L.B + brow] : 0.f;
   }
   IQLB_TSD(1);
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
   IQLB_TSD(2);
-  if (worker) {  // dH2 tile: this thread's row, columns [cbeg, cbeg+64)
-    // (not unrolled: eight copies of the 24-output body would not fit the instruction cache)
+  const uint32_t tmem = *tmem_slot;
+  if (wu < kBdWorkerWarps) {  // dH2 tile, one 64-column K-block at a time: this thread's row, columns [kb * 64 + cgrp * 16, + 16)
+    // (not unrolled: copies of the 24-output body would not fit the instruction cache)
 #pragma unroll 1
-    for (int wq = 0; wq < 2; ++wq) {
-      const uint32_t mword = wq == 0 ? m2w.x : m2w.y;
+    for (int kb = 0; kb < 4; ++kb) {
+      const uint32_t mh = (uint32_t)(m2h >> (16 * kb)) & 0xffffu;
 #pragma unroll 1
-      for (int cc = 0; cc < 32; cc += 8) {
-        const int c0 = cbeg + wq * 32 + cc;
+      for (int hh = 0; hh < 2; ++hh) {
+        const int c0 = kb * 64 + cgrp * 16 + hh * 8;
         float g[8];
         if (nout == 1) {
           const float4 w0 = *reinterpret_cast<const float4*>(sw2 + c0), w1 = *reinterpret_cast<const float4*>(sw2 + c0 + 4);
@@ -449,7 +458,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
             }
           }
         }
-        const uint32_t m = mword >> cc;
+        const uint32_t m = mh >> (8 * hh);
 #pragma unroll
         for (int j = 0; j < 8; ++j) g[j] = ((m >> j) & 1u) ? g[j] : 0.f;
         if (gscale != 1.0f) {
@@ -458,42 +467,36 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
         }
         st_chunk(smem + oA, row, c0, g);
       }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_k + 8 * kb);  // K-block kb of this warp's rows is in shared memory
     }
-  }
-  IQLB_TSD(3);
-  fence_async_smem();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  IQLB_TSD(4);
-  const uint32_t tmem = *tmem_slot;
-  if ((wu == kBdWorkerWarps || wu == kBdWorkerWarps + 1) && elect_one()) {
-    // two issuing threads (even / odd blocks): one thread gets an MMA out only every ~105-120 clocks whatever N is
-    // (scripts/mma_rate.py), which at N = 64 is a quarter of the tensor pipe's rate
-    const int first = wu == kBdWorkerWarps ? 0 : (P.opt_issuers == 2 ? 1 : 4);
-    const int step = P.opt_issuers == 2 ? 2 : 1;
-    if (wu == kBdWorkerWarps) {
-      uint8_t* dh2 = P.dh2 + at * P.h_bytes;
-      for (int cb = 0; cb < 4; ++cb)
-        bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
-      bulk_commit();
-    }
-    const Operand a = operand_k_major(sbase + oA, 128, 0);
-    for (int ib = first; ib < 4; ib += step) {
-      mbar_wait(bar_w + 8 * ib, 0);
+    IQLB_TSD(3);
+  } else if (elect_one()) {  // the issuing thread
+    for (int ib = 0; ib < 4; ++ib) mbar_wait(bar_w + 8 * ib, 0);
+    for (int kb = 0; kb < 4; ++kb) {
+      mbar_wait(bar_k + 8 * kb, 0);
       tc_fence_after();
-      gemm_issue(tmem + 64u * ib, a, operand_mn_major(sbase + oW + (uint32_t)ib * 32768u, L.H, 0, 0), 64, 16, false);
-      mma_commit(bar_mma + 8 * ib);
+      gemm_issue(tmem, operand_k_major(sbase + oA + (uint32_t)kb * 16384u, 128, 0), operand_mn_major(sbase + oW, L.H, 0, 64 * kb), 256, 4,
+                 kb > 0);
     }
-    if (wu == kBdWorkerWarps) bulk_wait_read0();  // the dH2 tile has left shared memory
+    mma_commit(bar_mma);
+    uint8_t* dh2 = P.dh2 + at * P.h_bytes;  // the finished dH2 tile also goes to HBM for the weight-gradient kernel
+    for (int cb = 0; cb < 4; ++cb)
+      bulk_s2g(dh2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oA + (uint32_t)cb * 16384u, 16384u);
+    bulk_commit();
+    bulk_wait_read0();
   }
   __syncwarp();
+  if (worker) {
+    mbar_wait(bar_mma, 0);
+    tc_fence_after();
+    IQLB_TSD(4);
+  }
   const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
   uint8_t* dh1 = P.dh1 + at * P.h_bytes;
 #pragma unroll
   for (int ib = 0; worker && ib < 4; ++ib) {
-    mbar_wait(bar_mma + 8 * ib, 0);
-    tc_fence_after();
     IQLB_TSD(5 + ib);
     uint8_t* stage = smem + oW + ib * 32768;  // W1 block ib has been consumed by MMA ib: its space stages dH1 block ib
     float v[16];

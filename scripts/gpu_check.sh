@@ -16,7 +16,7 @@ timeout 300 $CMD > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv $CMD > $OUT/ncu_launch.log 2>&1
 echo "ncu launches rc=$?" | tee -a $OUT/rc.txt
 timeout 300 $CMD > $OUT/plain2.log 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'bf16_|adam_polyak|loss_kernel|replay_gather|pack_x' -s 16 -c 5 -f -o $OUT/prof_step $CMD > $OUT/ncu_full.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'bf16_|adam_polyak|loss_kernel|replay_gather|pack_x' -s 18 -c 6 -f -o $OUT/prof_step $CMD > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?" | tee -a $OUT/rc.txt
 fi
 tail -3 $OUT/pytest_gpu.log; tail -2 $OUT/smoke.log; cat $OUT/bench_n1.json | cut -c1-600

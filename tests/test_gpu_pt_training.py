@@ -103,6 +103,9 @@ SHAPES = {
     # name: (S, A, T, B, E, P, heads, I, L, pool)
     "l2_ragged": (11, 4, 25, 6, 64, 32, 2, 128, 2, "mean"),
     "l1_wide": (29, 8, 20, 8, 128, 128, 2, 256, 1, "sum"),
+    # 2T = 128 tokens, head_dim 64, T = 64 >= the tensor-core threshold of the grouped attention GEMMs (pt_train.cu ptt_batched):
+    # with precision="split_bf16" S = Q K^T, O = P V and their four gradients run on tcgen05, per (sequence, head)
+    "l1_tc_attn": (11, 4, 64, 4, 128, 64, 2, 256, 1, "mean"),
 }
 
 

@@ -14,7 +14,9 @@
 // While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
 // MMA warp has issued its layer 0, so loads, both GEMMs, TMEM allocation and barrier set-up disappear
 // from the critical path: a tile costs roughly its two epilogues.
-// Used when the input image is one 64-column block (state_dim + action_dim <= 64) and action_dim <= 8.
+// Two instantiations: narrow (the input image is one 64-column block: state_dim + action_dim <= 64, action_dim <= 8, no actor
+// dropout - the D4RL locomotion / antmaze shapes) and wide (two input blocks, action_dim <= 24, actor dropout: pen / adroit).
+// The wide one trades a ring slot for the second X block and the 24-row W2; W0 takes one ring entry per input block.
 #include "iql_step.cuh"
 #include "umma.cuh"
 
@@ -22,23 +24,27 @@ namespace iqlb {
 using namespace umma;
 
 namespace fwdp {
-// shared memory: H tile | 4-slot ring of 32 KB operand blocks (W0, then the four W1 K-blocks of a tile)
-//                | X tile | b0 (x2) | b1 + W2 + b2 | head partial sums ((groups-1) x [8][128]) | barriers
+// shared memory: H tile | ring of 32 KB operand blocks (the W0 K-blocks, then the four W1 K-blocks of a tile)
+//                | X tile | b0 (x2) | b1 + W2 + b2 | barriers
 constexpr uint32_t oH = 0, oRing = 65536, kSlotBytes = 32768;
-constexpr int kSlots = 4, kPerTile = 5;
 #ifndef IQLB_FWD_EPI_WARPS
 #define IQLB_FWD_EPI_WARPS 16
 #endif
 constexpr int kEpiWarps = IQLB_FWD_EPI_WARPS, kEpiThreads = kEpiWarps * 32, kAuxWarp = 2 + kEpiWarps, kThreads = 64 + kEpiThreads + 32;
 constexpr int kGroups = kEpiWarps / 4, kPar = kGroups / 2;  // column-half x block-parity groups of epilogue warps
-constexpr uint32_t oX = oRing + kSlots * kSlotBytes, oB0 = oX + 16384, oBW = oB0 + 2048, kBWBytes = 9216 + 32,
-                   oPart = oBW + kBWBytes, kPartBytes = 0, oCtrl = oPart + kPartBytes,
-                   kSmem = oCtrl + 256;
-static_assert(kSmem <= 232448, "shared memory budget of one CTA (227 KB)");
+template <bool kWide>
+struct Lay {
+  static constexpr int kSlots = kWide ? 3 : 4, kXB = kWide ? 2 : 1, kOut = kWide ? kOutMax : 8;
+  static constexpr uint32_t oX = oRing + kSlots * kSlotBytes, oB0 = oX + kXB * 16384, oBW = oB0 + 2048,
+                            kBWBytes = kWide ? 1024 + kOutMax * 1024 + 128 : 9216 + 32, oCtrl = oBW + kBWBytes,
+                            kSmem = oCtrl + 256;
+  static_assert(kSmem <= 232448, "shared memory budget of one CTA (227 KB)");
+  static_assert(kSlots <= 4, "barrier indices reserve four ring slots");
+  static_assert(kOut <= 32, "partial head sums are parked in 32 accumulator columns");
+};
 // barrier indices (8 bytes each) inside the control block
 enum { FULL_L0 = 0, MMA0 = 1, MMA1 = 2, FULL_R = 3, EMPTY_R = 7, HBLK = 11, ACC0_FREE = 15, ACC1_FREE = 16, FULL_BW = 17,
        EPI0_DONE = 18, EPI1_DONE = 19, H1_OUT = 20 /* ..23: H1 block b has left the H tile */, H2_OUT = 24 /* ..27 */, N_BARS = 28 };
-static_assert(kSlots <= 4, "barrier indices reserve four ring slots");
 }  // namespace fwdp
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -71,10 +77,14 @@ __device__ __forceinline__ uint32_t bias_relu32(float (&v)[32], const float* __r
   return m;
 }
 
+template <bool kWide>
 __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfParams P, const float* __restrict__ params,
                                                                              const float* __restrict__ target,
                                                                              float* __restrict__ head_out, int n_tiles) {
   using namespace fwdp;
+  using Ly = Lay<kWide>;
+  constexpr int kSlots = Ly::kSlots, kOut = Ly::kOut;
+  constexpr uint32_t oX = Ly::oX, oB0 = Ly::oB0, oBW = Ly::oBW, oCtrl = Ly::oCtrl;
   extern __shared__ __align__(1024) uint8_t smem[];
   const Layout& L = P.L;
   // single-thread roles (producer, MMA issuer, store thread) are chosen by elect.sync inside warp-uniform branches, so the
@@ -102,6 +112,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const bool dbg = P.dbg != nullptr && blockIdx.x == 0;
+  // 64-column blocks of a stream's input image (wide: the Q streams read state | action, the others the state alone)
+  auto x_blocks = [&](int in) -> int { return kWide ? (in + 63) >> 6 : 1; };
 #ifdef IQLB_NO_TIMELINE
 #define IQLB_TS(slot) do { } while (0)
 #else
@@ -110,12 +122,22 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
 
   auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
                        const float*& fnet) {
-    if (P.rev) tile = n_tiles - 1 - tile;
     const int nh = L.B / 128;
-    half = tile % nh;
-    const int r = tile / nh;
-    s = r % kStreams;
-    agent = P.agent0 + r / kStreams;
+    if (kWide) {
+      // Actor tiles cost about twice the others here (dropout masks, 24-row head), so they go first (longest processing time
+      // first) and to the CTAs that do not take part in the last, partial round: round 0 is dealt from the last CTA down.
+      const int G = gridDim.x, n_agents = n_tiles / (kStreams * nh), n_heavy = n_agents * nh;
+      int j = tile < G ? G - 1 - tile : tile, r;
+      if (j < n_heavy) { half = j % nh; r = j / nh; s = 6; }
+      else { j -= n_heavy; half = j % nh; r = j / nh; s = r % 6; r /= 6; }
+      agent = P.agent0 + (P.rev ? n_agents - 1 - r : r);
+    } else {
+      if (P.rev) tile = n_tiles - 1 - tile;
+      half = tile % nh;
+      const int r = tile / nh;
+      s = r % kStreams;
+      agent = P.agent0 + r / kStreams;
+    }
     wnet = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net_of_stream(s) * P.net_bytes;
     ximg = (s == 0 ? P.xnext : P.xsa) + (int64_t)agent * P.x_bytes;
     fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
@@ -149,7 +171,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   if (wu == 0) {
     // ------------------------------------------------------------------ producer
     if (elect_one()) {
-      int c = 0;  // ring entries issued so far (5 per tile: W0, W1 block 0..3)
+      int c = 0;  // ring entries issued so far (per tile: the W0 K-blocks, then W1 block 0..3)
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         int agent, s, half;
         const uint8_t *wnet, *ximg;
@@ -163,19 +185,23 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
           tile_ptrs(tile + gridDim.x, a2, s2, h2, w2, x2, f2);
           bulk_prefetch_l2(w2, (uint32_t)P.net_bytes);
           bulk_prefetch_l2(x2 + (int64_t)h2 * 16384, 16384u);
+          if (kWide && L.in_dim(s2) > 64) bulk_prefetch_l2(x2 + (int64_t)L.B * 128 + (int64_t)h2 * 16384, 16384u);
         }
         if (it > 0) mbar_wait(bar(MMA0), (uint32_t)((it - 1) & 1));  // layer 0 of the previous tile has consumed X
         IQLB_TS(1024 + it * 8);
-        mbar_expect_tx(bar(FULL_L0), 16384u + 1024u);
-        bulk_g2s(sbase + oX, ximg + (int64_t)half * 16384, 16384u, bar(FULL_L0));
+        const int nxb = x_blocks(in);
+        mbar_expect_tx(bar(FULL_L0), (uint32_t)nxb * 16384u + 1024u);
+        for (int kx = 0; kx < nxb; ++kx)
+          bulk_g2s(sbase + oX + (uint32_t)kx * 16384u, ximg + (int64_t)kx * L.B * 128 + (int64_t)half * 16384, 16384u, bar(FULL_L0));
         bulk_g2s(sbase + oB0 + (uint32_t)(it & 1) * 1024u, fnet + L.b0(in), 1024u, bar(FULL_L0));
-        for (int e = 0; e < kPerTile; ++e, ++c) {
+        for (int e = 0; e < nxb + 4; ++e, ++c) {
           const int slot = c % kSlots, use = c / kSlots;
           if (use > 0) mbar_wait(bar(EMPTY_R + slot), (uint32_t)((use - 1) & 1));
-          IQLB_TS(1024 + it * 8 + 1 + e);
+          if (!kWide) IQLB_TS(1024 + it * 8 + 1 + e);
           mbar_expect_tx(bar(FULL_R + slot), kSlotBytes);
-          bulk_g2s(sbase + oRing + (uint32_t)slot * kSlotBytes, e == 0 ? wnet : wnet + P.w0_bytes + (int64_t)(e - 1) * 32768,
-                   kSlotBytes, bar(FULL_R + slot));
+          bulk_g2s(sbase + oRing + (uint32_t)slot * kSlotBytes,
+                   e < nxb ? wnet + (int64_t)e * 32768 : wnet + P.w0_bytes + (int64_t)(e - nxb) * 32768, kSlotBytes,
+                   bar(FULL_R + slot));
         }
       }
     }
@@ -185,21 +211,25 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       int c = 0;
       for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
-        const int s = ((P.rev ? n_tiles - 1 - tile : tile) / (L.B / 128)) % kStreams;
+        int agent, s, half;
+        const uint8_t *wnet, *ximg;
+        const float* fnet;
+        tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
         const int in = L.in_dim(s);
-        {
+        const int nxb = x_blocks(in);
+        for (int kx = 0; kx < nxb; ++kx, ++c) {
           const int slot = c % kSlots, use = c / kSlots;
-          mbar_wait(bar(FULL_L0), ph);
+          if (kx == 0) mbar_wait(bar(FULL_L0), ph);
           mbar_wait(bar(FULL_R + slot), (uint32_t)(use & 1));
-          if (it > 0) mbar_wait(bar(ACC0_FREE), (uint32_t)((it - 1) & 1));
+          if (kx == 0 && it > 0) mbar_wait(bar(ACC0_FREE), (uint32_t)((it - 1) & 1));
           tc_fence_after();
-          IQLB_TS(512 + it * 8);
-          gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oRing + (uint32_t)slot * kSlotBytes, L.H, 0),
-                     256, (in + 15) / 16, false);
+          if (kx == 0) IQLB_TS(512 + it * 8);
+          const int kin = in - 64 * kx;  // input columns left from this block on
+          gemm_issue(tmem, operand_k_major(sbase + oX + (uint32_t)kx * 16384u, 128, 0),
+                     operand_k_major(sbase + oRing + (uint32_t)slot * kSlotBytes, L.H, 0), 256, kin >= 64 ? 4 : (kin + 15) / 16, kx > 0);
           mma_commit(bar(EMPTY_R + slot));
-          mma_commit(bar(MMA0));
-          ++c;
         }
+        mma_commit(bar(MMA0));
         for (int kb = 0; kb < 4; ++kb, ++c) {
           const int slot = c % kSlots, use = c / kSlots;
           mbar_wait(bar(HBLK + kb), ph);
@@ -238,6 +268,9 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       const float* sb0 = reinterpret_cast<const float*>(smem + oB0 + (it & 1) * 1024);
       uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
       uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
+      // actor dropout (wide instantiation only): keep mask applied after the ReLU, stored masks = relu' AND keep (bf16_fwd_kernel)
+      const bool drop = kWide && s == 6 && P.drop_thresh != 0;
+      const uint64_t drop_seed = drop ? P.drop_rng[2 * agent] : 0ull, drop_step = drop ? (uint64_t)P.drop_it[agent] : 0ull;
       // (b0 landed before layer 0 was issued; FULL_L0 itself may already be a phase ahead, so it is
       //  not waited on here - MMA0 cannot run ahead of this warp because layer 0 waits for ACC0_FREE)
       if (et == 0) IQLB_TS(it * 8);
@@ -252,7 +285,14 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         tmem_ld32(lane_base + (uint32_t)c0, v);
         if (h1_store_pending) mbar_wait(bar(H2_OUT + blk), (uint32_t)((ntrain - 1) & 1));  // previous tile's H2 block has left
         tmem_ld_wait();
-        if (t >= 0) m1[c0 >> 5] = bias_relu32<true>(v, sb0 + c0);
+        if (kWide && drop) {
+          bias_relu32<false>(v, sb0 + c0);
+          dropout32(v, drop_seed, drop_step, 0, brow, L.H, c0, P.drop_thresh, P.drop_scale);
+          uint32_t m = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
+          m1[c0 >> 5] = m;  // (the actor stream is trainable: m1 is not null)
+        } else if (t >= 0) m1[c0 >> 5] = bias_relu32<true>(v, sb0 + c0);
         else bias_relu32<false>(v, sb0 + c0);
 #pragma unroll
         for (int q = 0; q < 4; ++q) st_chunk128(smem + oH, row, c0 + 8 * q, v + 8 * q);
@@ -272,9 +312,9 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       if (et == 0) IQLB_TS(it * 8 + 4);
       if (et == 0) IQLB_TS(it * 8 + 7);
       // ---- epilogue 1: H2 = relu(acc1 + b1); head = H2 . W2 + b2
-      float acc[8];
+      float acc[kOut];
 #pragma unroll
-      for (int o = 0; o < 8; ++o) acc[o] = 0.f;
+      for (int o = 0; o < kOut; ++o) acc[o] = 0.f;
 #pragma unroll 1
       for (int blk = par; blk < 4; blk += kPar) {
         const int c0 = blk * 64 + chalf * 32;
@@ -283,7 +323,12 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         if (t >= 0) mbar_wait(bar(H1_OUT + blk), (uint32_t)(ntrain & 1));  // H1 block blk has left: H2 block blk may move in
         tmem_ld_wait();
         uint32_t m = 0;
-        if (t >= 0) m = bias_relu32<true>(v, sb1 + c0);
+        if (kWide && drop) {
+          bias_relu32<false>(v, sb1 + c0);
+          dropout32(v, drop_seed, drop_step, 1, brow, L.H, c0, P.drop_thresh, P.drop_scale);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
+        } else if (t >= 0) m = bias_relu32<true>(v, sb1 + c0);
         else bias_relu32<false>(v, sb1 + c0);
         if (nout == 1) {
           float a = acc[0];
@@ -296,7 +341,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
           acc[0] = a;
         } else {
 #pragma unroll
-          for (int o = 0; o < 8; ++o) {
+          for (int o = 0; o < kOut; ++o) {
             if (o < nout) {
               const float* wr = sw2 + o * 256 + c0;
               float a = acc[o];
@@ -323,13 +368,16 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       // group 0 reads them back after the barrier (no shared-memory staging: with 16 epilogue warps it did not fit).
       constexpr int kLastBlk = (4 / kPar - 1) * kPar;
       if (grp > 0) {
-        uint32_t pr[16];
 #pragma unroll
-        for (int o = 0; o < 16; ++o) pr[o] = o < 8 ? __float_as_uint(acc[o]) : 0u;
-        tmem_st16(lane_base + 256u + (uint32_t)((par + kLastBlk) * 64 + chalf * 32), pr);
+        for (int o0 = 0; o0 < kOut; o0 += 16) {
+          uint32_t pr[16];
+#pragma unroll
+          for (int o = 0; o < 16; ++o) pr[o] = o0 + o < kOut ? __float_as_uint(acc[o0 + o]) : 0u;
+          tmem_st16(lane_base + 256u + (uint32_t)((par + kLastBlk) * 64 + chalf * 32 + o0), pr);
+        }
         tmem_st_wait();
       }
-      const float b2v = lane < 8 ? sw2[nout * 256 + (lane < nout ? lane : 0)] : 0.f;  // before the bundle is reloaded
+      const float b2v = lane < kOut ? sw2[nout * 256 + (lane < nout ? lane : 0)] : 0.f;  // before the bundle is reloaded
       tc_fence_before();
       named_bar_sync(1, kEpiThreads);
       if (et == 0) IQLB_TS(it * 8 + 6);
@@ -340,21 +388,37 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
         if (lane == 0) mbar_arrive(bar(ACC1_FREE));  // (layer 1 of the next tile still waits for group 0's arrival)
       } else {
         tc_fence_after();
-        float ps[kGroups > 1 ? kGroups - 1 : 1][16];
+        float ps[kWide ? 1 : (kGroups > 1 ? kGroups - 1 : 1)][16];
+        if (kWide) {  // 24 sums per group: one group and 16 sums at a time, added in the same (group) order as below
 #pragma unroll
-        for (int g = 1; g < kGroups; ++g)
-          tmem_ld16(lane_base + 256u + (uint32_t)(((g >> 1) + kLastBlk) * 64 + (g & 1) * 32), ps[g - 1]);
-        tmem_ld_wait();
+          for (int g = 1; g < kGroups; ++g) {
+#pragma unroll
+            for (int o0 = 0; o0 < kOut; o0 += 16) {
+              tmem_ld16(lane_base + 256u + (uint32_t)(((g >> 1) + kLastBlk) * 64 + (g & 1) * 32 + o0), ps[0]);
+              tmem_ld_wait();
+#pragma unroll
+              for (int o = 0; o < 16; ++o)
+                if (o0 + o < kOut) acc[o0 + o] += ps[0][o];
+            }
+          }
+        } else {
+#pragma unroll
+          for (int g = 1; g < kGroups; ++g)
+            tmem_ld16(lane_base + 256u + (uint32_t)(((g >> 1) + kLastBlk) * 64 + (g & 1) * 32), ps[kWide ? 0 : g - 1]);
+          tmem_ld_wait();
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(ACC1_FREE));
         float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
 #pragma unroll
-        for (int o = 0; o < 8; ++o) {
+        for (int o = 0; o < kOut; ++o) {
           if (o < nout) {
             float z = acc[o];
+            if (!kWide) {
 #pragma unroll
-            for (int g = 0; g < kGroups - 1; ++g) z += ps[g][o];
+              for (int g = 0; g < kGroups - 1; ++g) z += ps[g][o];
+            }
             z += __shfl_sync(0xffffffffu, b2v, o);
             if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
             else ho[(int64_t)s * L.B + brow] = z;
@@ -412,24 +476,35 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
-                            cudaStream_t stream, bool pdl) {
+template <bool kWide>
+static int persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
+                          cudaStream_t stream, bool pdl) {
   static int n_sm = 0;
   static bool attr_set = false;
+  constexpr uint32_t smem = fwdp::Lay<kWide>::kSmem;
   if (!attr_set) {
     int dev = 0;
     IQLB_CUDA(cudaGetDevice(&dev));
     IQLB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwdp::kSmem));
+    IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_persist_kernel<kWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int n_tiles = n_agents * kStreams * (P.L.B / 128);
   const int grid = n_tiles < n_sm ? n_tiles : n_sm;
-  IQLB_CUDA(launch_pdl(bf16_fwd_persist_kernel, dim3(grid), dim3(fwdp::kThreads), fwdp::kSmem, stream, pdl, P, params, target,
+  IQLB_CUDA(launch_pdl(bf16_fwd_persist_kernel<kWide>, dim3(grid), dim3(fwdp::kThreads), smem, stream, pdl, P, params, target,
                        head_out, n_tiles));
   return IQLB_OK;
 }
 
-bool bf16_fwd_persist_ok(const BfParams& P) { return P.KXB == 1 && P.L.A <= 8 && P.L.H == 256; }
+static bool persist_narrow(const BfParams& P) { return P.KXB == 1 && P.L.A <= 8 && P.drop_thresh == 0; }
+
+int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
+                            cudaStream_t stream, bool pdl) {
+  return persist_narrow(P) ? persist_launch<false>(P, params, target, head_out, n_agents, stream, pdl)
+                           : persist_launch<true>(P, params, target, head_out, n_agents, stream, pdl);
+}
+
+// every shape bf16_create accepts: hidden 256, batch 256, state_dim + action_dim <= 128, action_dim <= 24
+bool bf16_fwd_persist_ok(const BfParams& P) { return P.KXB <= 2 && P.L.A <= kOutMax && P.L.H == 256; }
 
 }  // namespace iqlb

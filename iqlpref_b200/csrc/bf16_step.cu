@@ -971,7 +971,7 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   }
   static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
   bf16_set_dropout(h, P);
-  if (persist_env && bf16_fwd_persist_ok(P) && P.drop_thresh == 0) {
+  if (persist_env && bf16_fwd_persist_ok(P)) {
     if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream, pdl_enabled(2) && !h->prof))) return rc;
   } else if (P.drop_thresh != 0) {
     bf16_fwd_kernel<true><<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);

@@ -426,3 +426,43 @@ def test_agents_are_bit_identical_however_they_are_sharded(precision):
             assert torch.equal(part, whole[ids]), (precision, ids)
             for name in ("params", "exp_avg", "exp_avg_sq", "target", "it", "actor_lr", "rng"):
                 assert torch.equal(getattr(e, name), getattr(e_all, name)[ids]), (precision, ids, name)
+
+
+def test_wide_shape_agents_are_bit_identical_across_tile_schedules():
+    """The pen / adroit shape (two input blocks, 24 actions, actor dropout) on the persistent forward kernel: 24 agents are
+    336 forward tiles, more than one round over the SMs, with the actor tiles dealt first; 8-agent engines and a 5 + 19
+    split schedule the same tiles on other CTAs in other rounds.  Every agent must come out bit for bit the same."""
+    from iqlpref_b200 import iql as biql
+    S, A, N, K = 45, 24, 24, 3
+    buf = biql.ReplayBuffer(S, A, 5000)
+    g = torch.Generator(device="cuda").manual_seed(9)
+    buf._table[:, :2 * S + A + 2] = torch.randn((5000, 2 * S + A + 2), generator=g, device="cuda")
+    buf._table[:, S:S + A].clamp_(-1, 1)
+    buf._table[:, 2 * S + A + 1] = (buf._table[:, 2 * S + A + 1] > 1.3).float()
+    buf._size = buf._pointer = 5000
+
+    def run(agent_ids):
+        n = len(agent_ids)
+        eng = biql.BatchedIQL(S, A, n, batch_size=256, precision="bf16", actor_dropout=0.1,
+                              hparams=[dict(max_steps=100, beta=3.0 + 0.1 * a) for a in agent_ids],
+                              seeds=[21 + a for a in agent_ids])
+        for j, a in enumerate(agent_ids):
+            torch.manual_seed(70 + a)
+            eng.adopt(j, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0, dropout=0.1), bind=False)
+        eng.attach_replay(buf)
+        trace = []
+        for _ in range(K):
+            eng.train(None)
+            trace.append(eng.losses.clone())
+        eng.sync()
+        torch.cuda.synchronize()
+        return torch.stack(trace, 1), eng
+
+    whole, e_all = run(list(range(N)))
+    assert torch.isfinite(whole).all()
+    for ids in (range(0, 8), range(8, 16), range(16, 24), range(0, 5), range(5, 24)):
+        ids = list(ids)
+        part, e = run(ids)
+        assert torch.equal(part, whole[ids]), ids
+        for name in ("params", "exp_avg", "exp_avg_sq", "target"):
+            assert torch.equal(getattr(e, name), getattr(e_all, name)[ids]), (ids, name)

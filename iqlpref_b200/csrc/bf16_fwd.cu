@@ -1,6 +1,6 @@
 // Persistent, warp-specialised forward kernel of the bf16 IQL step (one CTA per SM, tiles =
-// (agent, stream, half batch) taken round-robin).  Same arithmetic and outputs as bf16_fwd_kernel
-// (bf16_step.cu); what changes is the schedule:
+// (agent, stream, half batch) taken round-robin): X -> relu(X W0^T + b0) -> relu(H1 W1^T + b1) -> head (W2, b2 in fp32,
+// tanh for the actor); keeps H1, H2 (bf16 images) and the ReLU masks of the four trainable streams for the backward pass.
 //
 //   warp 0  producer : bulk copies (X tile, b0 | W0 and the four W1 K-blocks through a 4-slot ring); b1, W2 by the epilogue
 //   warp 1  MMA      : tcgen05.mma issue; layer 1 starts on K-block kb as soon as the epilogue has
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   // single-thread roles (producer, MMA issuer, store thread) are chosen by elect.sync inside warp-uniform branches, so the
   // operands of their bulk copies / MMAs / commits stay in uniform registers (umma.cuh: elect_one)
   const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31, wu = warp;  // (measured: with warp = tid >> 5 for the
-  // epilogue arithmetic this kernel is 3 us slower, while the non-persistent bf16_fwd_kernel is 30 % FASTER that way)
+  // epilogue arithmetic this kernel is 3 us slower, while round 1's one-tile-per-CTA kernel was 30 % FASTER that way)
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bars = sbase + oCtrl;
   auto bar = [&](int i) -> uint32_t { return bars + 8u * (uint32_t)i; };
@@ -268,7 +268,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
       const float* sb0 = reinterpret_cast<const float*>(smem + oB0 + (it & 1) * 1024);
       uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
       uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
-      // actor dropout (wide instantiation only): keep mask applied after the ReLU, stored masks = relu' AND keep (bf16_fwd_kernel)
+      // actor dropout (wide instantiation only): keep mask applied after the ReLU, stored masks = relu' AND keep, so the
+      // backward pass needs only the 1 / (1 - p) factor
       const bool drop = kWide && s == 6 && P.drop_thresh != 0;
       const uint64_t drop_seed = drop ? P.drop_rng[2 * agent] : 0ull, drop_step = drop ? (uint64_t)P.drop_it[agent] : 0ull;
       // (b0 landed before layer 0 was issued; FULL_L0 itself may already be a phase ahead, so it is
@@ -500,11 +501,10 @@ static bool persist_narrow(const BfParams& P) { return P.KXB == 1 && P.L.A <= 8 
 
 int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
                             cudaStream_t stream, bool pdl) {
+  // every shape bf16_create accepts (hidden 256, batch 256, state_dim + action_dim <= 125, action_dim <= 24) fits the wide one
+  IQLB_REQUIRE(P.KXB <= 2 && P.L.A <= kOutMax && P.L.H == 256, "forward kernel: shape outside what bf16_create accepts");
   return persist_narrow(P) ? persist_launch<false>(P, params, target, head_out, n_agents, stream, pdl)
                            : persist_launch<true>(P, params, target, head_out, n_agents, stream, pdl);
 }
-
-// every shape bf16_create accepts: hidden 256, batch 256, state_dim + action_dim <= 128, action_dim <= 24
-bool bf16_fwd_persist_ok(const BfParams& P) { return P.KXB <= 2 && P.L.A <= kOutMax && P.L.H == 256; }
 
 }  // namespace iqlb

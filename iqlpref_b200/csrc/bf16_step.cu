@@ -2,7 +2,7 @@
 // Replaces the 7 MLP forwards and 4 MLP backwards of ImplicitQLearning.train
 // (/root/reference/algorithms/offline/iql.py:581-637) with three tensor-core kernels:
 //
-//   bf16_fwd_kernel         (half-batch, stream, agent): X -> relu(X W0^T + b0) -> relu(H1 W1^T + b1)
+//   bf16_fwd_persist_kernel (bf16_fwd.cu; tile = half-batch, stream, agent): X -> relu(X W0^T + b0) -> relu(H1 W1^T + b1)
 //                           -> head (W2, b2, tanh for the actor); keeps H1, H2 (bf16 images) and the
 //                           ReLU masks of the four trainable streams for the backward pass.
 //   bf16_bwd_data_kernel    (half-batch, net, agent): dH2 = (dz W2) * relu'(H2) on CUDA cores,
@@ -95,226 +95,10 @@ __device__ __forceinline__ void st_chunk(uint8_t* tile, int row, int col0, const
 }
 
 // ------------------------------------------------------------------------------------------------
-// Forward.  grid (B/128, 7 streams, agents), 256 threads (warp w drains TMEM lane quarter w%4,
-// column half w/4), 1 CTA per SM.
-// Shared memory (H = 256): [W0 image KXB*32K | X tile KXB*16K | W1 ring (4-KXB)*32K | H tile 64K | ctrl | b0]
-// W1 streams in as four 32 KB K-blocks; the last KXB of them land in the W0 region once layer 0
-// has been consumed, and b1 / W2 (fp32) take over the X region.  TMEM: layer-0 accumulator in
-// columns [0,256), layer-1 in [256,512).
+// Forward: bf16_fwd_persist_kernel (bf16_fwd.cu) - persistent, warp-specialised, one CTA per SM.  (Round 1's one-tile-per-CTA
+// kernel lived here; the persistent kernel now covers every shape bf16_create accepts - pen-human forward 118 -> 75 us,
+// profiles/r02f_fwd_wide_ab.jsonl - so it was removed.)
 // ------------------------------------------------------------------------------------------------
-// kDrop: actor dropout (pen / adroit configs): the keep mask is applied to the actor stream's hidden activations
-// after the ReLU, and the stored bit masks become relu' AND keep, so the backward pass needs only the 1/(1-p) factor.
-template <bool kDrop>
-__global__ void __launch_bounds__(256, 1) bf16_fwd_kernel(BfParams P, const float* __restrict__ params,
-                                                          const float* __restrict__ target,
-                                                          float* __restrict__ head_out) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const Layout& L = P.L;
-  const int half = blockIdx.x, s = blockIdx.y, agent = P.agent0 + blockIdx.z;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int wu = warp_uniform();  // for the single-thread roles only (elect_one(), umma.cuh): as the source of quarter / chalf it cost 30 %
-  const int quarter = warp & 3, chalf = warp >> 2;
-  const int KXB = P.KXB, nring = 4 - KXB;
-  const uint32_t sbase = smem_u32(smem);
-  const uint32_t oW0 = 0, oX = (uint32_t)KXB * 32768u, oRing = oX + (uint32_t)KXB * 16384u,
-                 oH = oRing + (uint32_t)nring * 32768u, oCtrl = oH + 65536u, oB0 = oCtrl + 128u;
-  const uint32_t bar_l0 = sbase + oCtrl, bar_w1 = bar_l0 + 8, bar_mma0 = bar_l0 + 40, bar_mma1 = bar_l0 + 48;
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 56);
-  const int net = net_of_stream(s), t = train_index(s);
-  const int in = L.in_dim(s), nout = L.out_dim(s);
-  const uint8_t* wnet = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net * P.net_bytes;
-  const uint8_t* ximg = (s == 0 ? P.xnext : P.xsa) + (int64_t)agent * P.x_bytes;
-  const float* fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
-                                       : params + (int64_t)agent * L.Pstride + L.net_off(s);
-  auto chunk_off = [&](int c) -> uint32_t { return c < nring ? oRing + (uint32_t)c * 32768u : oW0 + (uint32_t)(c - nring) * 32768u; };
-  float* sb0 = reinterpret_cast<float*>(smem + oB0);
-  float* sb1 = reinterpret_cast<float*>(smem + oX);   // valid after layer 0 has consumed X
-  float* sw2 = sb1 + 256;
-
-  if (wu == 0 && elect_one()) {
-    if (sbase & 1023u) __trap();
-    mbar_init(bar_l0, 1);
-    for (int c = 0; c < 4; ++c) mbar_init(bar_w1 + 8 * c, 1);
-    mbar_init(bar_mma0, 1);
-    mbar_init(bar_mma1, 1);
-    fence_barrier_init();
-    mbar_expect_tx(bar_l0, (uint32_t)KXB * (32768u + 16384u));
-    bulk_g2s(sbase + oW0, wnet, (uint32_t)KXB * 32768u, bar_l0);
-    for (int cb = 0; cb < KXB; ++cb)
-      bulk_g2s(sbase + oX + (uint32_t)cb * 16384u, ximg + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, 16384u, bar_l0);
-    for (int c = 0; c < nring; ++c) {
-      mbar_expect_tx(bar_w1 + 8 * c, 32768u);
-      bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
-    }
-  }
-  if (warp == 1) tmem_alloc(sbase + oCtrl + 56, 512);
-  sb0[tid] = __ldg(fnet + L.b0(in) + tid);
-  const float b1_pref = __ldg(fnet + L.b1(in) + tid);  // parked in a register until the X region is free
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-
-  if (wu == 0 && elect_one()) {
-    mbar_wait(bar_l0, 0);
-    tc_fence_after();
-    gemm_issue(tmem, operand_k_major(sbase + oX, 128, 0), operand_k_major(sbase + oW0, L.H, 0), 256, (in + 15) / 16, false);
-    mma_commit(bar_mma0);
-  }
-  __syncwarp();
-  mbar_wait(bar_mma0, 0);
-  tc_fence_after();
-  if (wu == 0 && elect_one()) {  // layer 0 consumed: the W0 region takes the remaining W1 blocks
-    for (int c = nring; c < 4; ++c) {
-      mbar_expect_tx(bar_w1 + 8 * c, 32768u);
-      bulk_g2s(sbase + chunk_off(c), wnet + P.w0_bytes + (int64_t)c * 32768, 32768u, bar_w1 + 8 * c);
-    }
-  }
-  __syncwarp();
-  sb1[tid] = b1_pref;
-  for (int i = tid; i < nout * 256; i += 256) sw2[i] = __ldg(fnet + L.w2(in) + i);
-  const int row = quarter * 32 + lane, brow = half * 128 + row;
-  const int cbeg = chalf * 128;
-  const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-  uint32_t* m1 = t >= 0 ? P.mask1 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
-  uint32_t* m2 = t >= 0 ? P.mask2 + (((int64_t)agent * kTrain + t) * L.B + brow) * (L.H / 32) : nullptr;
-  const bool drop = kDrop && s == 6 && P.drop_thresh != 0;
-  const uint64_t drop_seed = drop ? P.drop_rng[2 * agent] : 0ull, drop_step = drop ? (uint64_t)P.drop_it[agent] : 0ull;
-  // epilogue 0: H1 = relu(acc + b0) -> bf16 tile (A operand of layer 1)
-  for (int c0 = cbeg; c0 < cbeg + 128; c0 += 32) {
-    float v[32];
-    tmem_ld32(lane_base + (uint32_t)c0, v);
-    tmem_ld_wait();
-    uint32_t m = 0;
-#pragma unroll
-    for (int j4 = 0; j4 < 8; ++j4) {
-      const float4 bb = *reinterpret_cast<const float4*>(sb0 + c0 + 4 * j4);
-      const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
-      const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
-      v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
-      m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
-    }
-    if (kDrop && drop) {
-      dropout32(v, drop_seed, drop_step, 0, brow, L.H, c0, P.drop_thresh, P.drop_scale);
-      m = 0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
-    }
-    if (m1) m1[c0 >> 5] = m;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
-  }
-  fence_async_smem();
-  tc_fence_before();
-  __syncthreads();
-  if (wu == 0 && elect_one()) {
-    tc_fence_after();
-    if (t >= 0) {
-      uint8_t* h1 = P.h1 + ((int64_t)agent * kTrain + t) * P.h_bytes;
-      for (int cb = 0; cb < 4; ++cb)
-        bulk_s2g(h1 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
-      bulk_commit();
-    }
-    for (int kb = 0; kb < 4; ++kb) {
-      mbar_wait(bar_w1 + 8 * kb, 0);
-      tc_fence_after();
-      gemm_issue(tmem + 256, operand_k_major(sbase + oH + (uint32_t)kb * 16384u, 128, 0),
-                 operand_k_major(sbase + chunk_off(kb), L.H, 0), 256, 4, kb > 0);
-    }
-    mma_commit(bar_mma1);
-    if (t >= 0) bulk_wait_read0();  // the H1 tile must be out before epilogue 1 overwrites it with H2
-  }
-  __syncwarp();
-  mbar_wait(bar_mma1, 0);
-  tc_fence_after();
-  __syncthreads();
-  // epilogue 1: H2 = relu(acc + b1); head = H2 . W2 + b2 (two column halves per row, combined below)
-  float acc[kOutMax];
-#pragma unroll
-  for (int o = 0; o < kOutMax; ++o) acc[o] = 0.f;
-  for (int c0 = cbeg; c0 < cbeg + 128; c0 += 32) {
-    float v[32];
-    tmem_ld32(lane_base + 256u + (uint32_t)c0, v);
-    tmem_ld_wait();
-    uint32_t m = 0;
-#pragma unroll
-    for (int j4 = 0; j4 < 8; ++j4) {
-      const float4 bb = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * j4);
-      const float x0 = fmaxf(v[4 * j4] + bb.x, 0.f), x1 = fmaxf(v[4 * j4 + 1] + bb.y, 0.f);
-      const float x2 = fmaxf(v[4 * j4 + 2] + bb.z, 0.f), x3 = fmaxf(v[4 * j4 + 3] + bb.w, 0.f);
-      v[4 * j4] = x0; v[4 * j4 + 1] = x1; v[4 * j4 + 2] = x2; v[4 * j4 + 3] = x3;
-      m |= ((x0 > 0.f ? 1u : 0u) | (x1 > 0.f ? 2u : 0u) | (x2 > 0.f ? 4u : 0u) | (x3 > 0.f ? 8u : 0u)) << (4 * j4);
-    }
-    if (kDrop && drop) {
-      dropout32(v, drop_seed, drop_step, 1, brow, L.H, c0, P.drop_thresh, P.drop_scale);
-      m = 0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) m |= (v[j] > 0.f ? 1u : 0u) << j;
-    }
-    if (nout == 1) {
-      float a = acc[0];
-#pragma unroll
-      for (int j4 = 0; j4 < 8; ++j4) {
-        const float4 w = *reinterpret_cast<const float4*>(sw2 + c0 + 4 * j4);
-        a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
-        a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
-      }
-      acc[0] = a;
-    } else {
-#pragma unroll
-      for (int o = 0; o < kOutMax; ++o) {
-        if (o < nout) {
-          const float* wr = sw2 + o * 256 + c0;
-          float a = acc[o];
-#pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
-            a = fmaf(v[4 * j4], w.x, a); a = fmaf(v[4 * j4 + 1], w.y, a);
-            a = fmaf(v[4 * j4 + 2], w.z, a); a = fmaf(v[4 * j4 + 3], w.w, a);
-          }
-          acc[o] = a;
-        }
-      }
-    }
-    if (t >= 0) {
-      m2[c0 >> 5] = m;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) st_chunk(smem + oH, row, c0 + 8 * q, v + 8 * q);
-    }
-  }
-  // combine the two column halves through the (now idle) W1 ring
-  float* part = reinterpret_cast<float*>(smem + oRing);
-  if (chalf == 1) {
-#pragma unroll
-    for (int o = 0; o < kOutMax; ++o)
-      if (o < nout) part[o * 128 + row] = acc[o];
-  }
-  if (t >= 0) fence_async_smem();
-  __syncthreads();
-  if (chalf == 0) {
-    const float* b2 = fnet + L.b2(in, nout);
-    float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
-#pragma unroll
-    for (int o = 0; o < kOutMax; ++o) {
-      if (o < nout) {
-        const float z = acc[o] + part[o * 128 + row] + __ldg(b2 + o);
-        if (s == 6) ho[(int64_t)(6 + o) * L.B + brow] = tanhf(z);
-        else ho[(int64_t)s * L.B + brow] = z;
-      }
-    }
-  }
-  if (t >= 0 && wu == 0 && elect_one()) {
-    uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
-    for (int cb = 0; cb < 4; ++cb)
-      bulk_s2g(h2 + (int64_t)cb * L.B * 128 + (int64_t)half * 16384, sbase + oH + (uint32_t)cb * 16384u, 16384u);
-    bulk_commit();
-    bulk_wait_read0();
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
-}
-
 // ------------------------------------------------------------------------------------------------
 // Backward, data gradients.  grid (B/128, 4 trainable nets, agents), 256 threads.
 // Shared memory: [dH2 tile 64K | W1 image 128K | 2 x 16K output staging (first: W2 fp32) | ctrl].
@@ -541,7 +325,7 @@ __global__ void __launch_bounds__(kBdThreads, 1) bf16_bwd_data_kernel(BfParams P
 // Every product reduces over the batch (K = B), with both operands read MN-major from images whose
 // rows are batch rows.  blk = B*128 bytes = one 64-column block of a batch-row image.
 // Shared memory: [bufA 2 blk | bufB 4 blk | dz image 1 blk | ctrl]
-//   phase 1: bufA = dH2[:, tile], bufB = H1          -> dW1 tile (TMEM 0..255), db1 (col 352+out)
+//   phase 1: bufA = dH2[:, tile], bufB = H1          -> dW1 tile (TMEM 0..255), db1 (col 448 or 480 + out: clear of a 128-column dW0 tile)
 //   phase 2: bufA = dH1[:, tile], bufB[0..] = X_sa   -> dW0 tile (TMEM 256..), db0 (col 384+out)
 //            H2[:, tile] (2 blk of bufB)             -> dW2^T tile (TMEM 416 + o)
 // The dz image holds dz[b, 0..out) and a column of ones at `out`, so bias gradients are MMA columns.
@@ -690,7 +474,7 @@ __device__ __forceinline__ void bwd_weight_drain_p(const BfParams& P, uint8_t* s
 //   * the next tile's phase-1 operands are requested as soon as the current tile's last product has completed (dH2, dz and
 //     the first two H1 blocks at once, H1 blocks 2-3 when the final drain has left the staging area), i.e. under the final
 //     drain instead of behind a CTA exit / launch (1.2 us) + barrier / TMEM set-up;
-//   * db1 alternates between TMEM columns 352 and 448, so phase 1 of tile i+1 never waits for the final drain of tile i.
+//   * db1 alternates between TMEM columns 480 and 448, so phase 1 of tile i+1 never waits for the final drain of tile i.
 // Every barrier completes once per tile: parity = tile count & 1.
 // ------------------------------------------------------------------------------------------------
 struct BwTile {
@@ -759,7 +543,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t ph = (uint32_t)(it & 1);
         const BwTile T = bw_tile(P, tile, n_ag);
-        const uint32_t d1col = (it & 1) ? 448u : 352u;
+        const uint32_t d1col = (it & 1) ? 448u : 480u;
         // phase 1: dW1 tile = dH2[:, ot]^T H1 (128 x 256), db1 = dH2[:, ot]^T [dz | 1]
         mbar_wait(bar_ld1, ph);
         if (it > 0) mbar_wait(bar_d1, ph ^ 1u);  // the previous tile's dW1 has left TMEM columns 0..255
@@ -808,7 +592,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const BwTile T = bw_tile(P, tile, n_ag);
-      bwd_weight_drain_p(P, smem, tmem, bar_p1, bar_p2, bar_d1, bar_d2, (uint32_t)(it & 1), (it & 1) ? 448u : 352u, T.ot, T.t,
+      bwd_weight_drain_p(P, smem, tmem, bar_p1, bar_p2, bar_d1, bar_d2, (uint32_t)(it & 1), (it & 1) ? 448u : 480u, T.ot, T.t,
                          T.agent, T.in, T.nout, T.n0, warp, lane, quarter, cgrp, tid, tile);
     }
   }
@@ -820,19 +604,19 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-static size_t fwd_smem(int KXB) { return 196608u + 16384u * (size_t)KXB + 128u + 1024u; }
 static size_t bwd_data_smem() { return 65536u + 131072u + 32768u + 128u; }
 static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
 
 int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
                             cudaStream_t stream, bool pdl);
-bool bf16_fwd_persist_ok(const BfParams& P);
 
 int bf16_create(iqlb_agents* h) {
   const Layout& L = h->L;
   IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
   IQLB_REQUIRE(L.B == 256, "the tcgen05 path is built for batch_size 256 (every reference config); use precision fp32 otherwise");
-  IQLB_REQUIRE(L.A <= kOutMax && L.Dq <= 128, "action_dim <= 24 and state_dim + action_dim <= 128");
+  // (125, not 128: the weight-gradient kernel stages dW0 | db1 | db0 | dW2 of a 128-row tile, (128 in + 256 + 128 out) floats,
+  //  in the 64 KB behind the X image; Ant-v2, 111 + 8, is the widest D4RL shape this covers)
+  IQLB_REQUIRE(L.A <= kOutMax && L.Dq <= 125, "action_dim <= 24 and state_dim + action_dim <= 125");
   IQLB_REQUIRE(1 + L.A <= 16 * ((L.Dq + 63) / 64), "action_dim too wide for the head staging area");
   Bf16State* st = new (std::nothrow) Bf16State();
   if (!st) return fail(IQLB_ERR_NOMEM, "out of host memory%s", "");
@@ -874,8 +658,6 @@ int bf16_create(iqlb_agents* h) {
   P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 8192 * 8);
   if (rc) return rc;
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
-  IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(P.KXB)));
   P.drop_thresh = 0; P.drop_scale = 1.0f; P.drop_rng = h->rng; P.drop_it = h->it;
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_data_smem()));
   IQLB_CUDA(cudaFuncSetAttribute(bf16_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -969,17 +751,8 @@ int bf16_step_gemms_fwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
                          pdl_enabled(1) && !h->prof, P, h->batch_src ? h->batch_src : (const float*)h->batch));
     pf.mark("pack_x");
   }
-  static const bool persist_env = !(getenv("IQLB_FWD_PERSIST") && atoi(getenv("IQLB_FWD_PERSIST")) == 0);
   bf16_set_dropout(h, P);
-  if (persist_env && bf16_fwd_persist_ok(P)) {
-    if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream, pdl_enabled(2) && !h->prof))) return rc;
-  } else if (P.drop_thresh != 0) {
-    bf16_fwd_kernel<true><<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
-    IQLB_LAUNCH_CHECK();
-  } else {
-    bf16_fwd_kernel<false><<<dim3(L.B / 128, kStreams, N), 256, fwd_smem(P.KXB), stream>>>(P, h->params, h->target, h->head_out);
-    IQLB_LAUNCH_CHECK();
-  }
+  if ((rc = bf16_fwd_persist_launch(P, h->params, h->target, h->head_out, N, stream, pdl_enabled(2) && !h->prof))) return rc;
   pf.mark("bf16_fwd");
   return IQLB_OK;
 }

@@ -55,7 +55,8 @@ def _engines(biql, S, A, det, n_agents, B=256):
     return engs, mods
 
 
-@pytest.mark.parametrize("S,A,det", [(17, 6, False), (29, 8, False), (45, 24, True)])
+# (111, 8): the Ant shape - every stream reads two input blocks (45, 24: only the Q streams do)
+@pytest.mark.parametrize("S,A,det", [(17, 6, False), (29, 8, False), (45, 24, True), (111, 8, False)])
 def test_bf16_forward_and_gradients_match_fp32_path(S, A, det):
     from iqlpref_b200 import iql as biql
     N = 2

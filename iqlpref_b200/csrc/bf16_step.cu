@@ -159,18 +159,10 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
     if (sbase & 1023u) __trap();
     for (int i = 0; i < 4; ++i) { mbar_init(bar_w + 8 * i, 1); mbar_init(bar_mma + 8 * i, 1); mbar_init(bar_k + 8 * i, kBdWorkerWarps); }
     fence_barrier_init();
-    // the TMA engine keeps only a few tens of KB in flight per SM: ask L2 for the whole image first, so the
-    // copies below trail a DRAM fetch that runs at full rate instead of paying one DRAM latency per piece
-    if (P.opt_pf1 == 1) bulk_prefetch_l2(w1img, 131072u);
     for (int ib = 0; ib < 4; ++ib) {
       mbar_expect_tx(bar_w + 8 * ib, 32768u);
       bulk_g2s(sbase + oW + (uint32_t)ib * 32768u, w1img + (int64_t)ib * 32768, 32768u, bar_w + 8 * ib);
     }
-  }
-  if (P.opt_pf1 == 2) {  // every thread asks L2 for four 128-byte lines of the W1 image (LSU path, full memory parallelism)
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(w1img + ((int64_t)(k * 256 + tid) << 7)));
   }
   if (warp == 1) tmem_alloc(sbase + oCtrl + 64, 256);
   // the worker warps compute and drain; the first lanes of the two extra warps issue the dH2 store and the MMAs, so the
@@ -655,7 +647,6 @@ int bf16_create(iqlb_agents* h) {
   P.opt_issuers = envi("IQLB_ISSUERS", 2);
   P.opt_lpt = envi("IQLB_LPT", 1);
   P.dbg_z = envi("IQLB_DBG_Z", 0);  // which agent's CTA records the clock64 timeline
-  P.opt_pf1 = envi("IQLB_PF1", 0); P.opt_pf2 = envi("IQLB_PF2", 0); P.opt_pf3 = envi("IQLB_PF3", 0);  // measured: no gain, off
   if (!rc && getenv("IQLB_TIMELINE") && atoi(getenv("IQLB_TIMELINE"))) rc = alloc((void**)&P.dbg, 8192 * 8);
   if (rc) return rc;
   P.drop_thresh = 0; P.drop_scale = 1.0f; P.drop_rng = h->rng; P.drop_it = h->it;

@@ -79,7 +79,6 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
                             float* __restrict__ loss_sum, int64_t* __restrict__ it, double* __restrict__ actor_lr,
                             uint64_t* __restrict__ rng, StepScalars* __restrict__ scal, int advance_rng,
                             uint8_t* __restrict__ dzimg, int64_t z_bytes, int agent0, unsigned long long* dbg,
-                            const uint8_t* __restrict__ wimg, int64_t agent_w_bytes, int64_t net_bytes,
                             __nv_bfloat16* __restrict__ gradh, float* __restrict__ losses_snap) {
 #ifdef IQLB_NO_TIMELINE
 #define IQLB_TSL(slot) do { } while (0)
@@ -121,11 +120,6 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
     if (advance_rng & 1) rng[2 * agent + 1] += 4;  // one torch.randint of <= 256*grid draws (ATen :50-63)
     IQLB_TSL(6);
   };
-  if (wimg != nullptr && b < 4) {
-    // the data-gradient kernel that follows reads W1 of the four trainable networks (images 0..3 of the agent):
-    // start their trip HBM -> L2 now, while this latency-bound kernel runs
-    umma::bulk_prefetch_l2(wimg + (int64_t)agent * agent_w_bytes + (int64_t)b * net_bytes, (uint32_t)net_bytes);
-  }
   if (extra_warp && b == (int)blockDim.x - 32) bookkeeping();
   const float* ho = head_out + (int64_t)agent * L.head_rows() * L.B;
   float* dout = d_out + (int64_t)agent * L.dout_rows() * L.B;
@@ -586,8 +580,6 @@ static int step_chain(iqlb_agents* h, int a0, int n, bool sampled, Prof& pf, cud
                        h->hparams, (const float*)((bf && h->batch_src) ? h->batch_src : h->batch), (const float*)h->head_out, h->d_out, h->grads, h->losses,
                        h->loss_sum, h->it, h->actor_lr, h->rng, h->scal, sampled ? 1 : 0, bf ? bp->dz : (uint8_t*)nullptr,
                        bf ? bp->z_bytes : (int64_t)0, a0, bf ? bp->dbg : (unsigned long long*)nullptr,
-                       (bf && bp->opt_pf3) ? (const uint8_t*)bp->wimg : (const uint8_t*)nullptr,
-                       bf ? bp->agent_w_bytes : (int64_t)0, bf ? bp->net_bytes : (int64_t)0,
                        bf ? bp->gradh : (__nv_bfloat16*)nullptr, h->loss_snap_cur));
   pf.mark("loss");
   if (bf) {

@@ -124,7 +124,6 @@ struct BfParams {
   int opt_lpt;            // data-gradient kernel: actor tiles (the longest) first (IQLB_LPT)
   int dbg_z;              // timeline: blockIdx.z of the recording CTA
   int opt_issuers;        // MMA-issuing threads of the gradient kernels (IQLB_ISSUERS, 1 or 2)
-  int opt_pf1, opt_pf2, opt_pf3;  // L2-prefetch experiments (IQLB_PF1 bwd_data W1, IQLB_PF2 bwd_weight phase 2, IQLB_PF3 loss -> W1)
   unsigned long long* dbg;  // IQLB_TIMELINE=1: clock64 stamps of CTA 0 (kernel timelines, debug tensor 8)
 };
 

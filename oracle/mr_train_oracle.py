@@ -152,3 +152,101 @@ def synth_batch(rng: np.random.Generator, B: int, T: int, S: int, A: int, ragged
     s2, a2, t2, m2 = seg()
     lab = rng.choice(np.array([[1, 0], [0, 1], [0.5, 0.5]], dtype=f32), B)
     return (s1, a1, t1, m1, s2, a2, t2, m2, lab.astype(f32))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# MRTrainerF: the MR step plus the functional GP prior of an LCF model (training.py:132-305, gp/models/model.py:202-513)
+# Pinned to the unmodified reference by `tests/golden/mrf_train.npz` (`oracle/gen_golden_mrf.py`).
+# ------------------------------------------------------------------------------------------------------------------
+f64 = np.float64
+
+
+def synth_features(X: np.ndarray, n_concepts: int = 6) -> np.ndarray:
+    """The feature map Phi: X -> R^d the MRTrainerF fixtures use as `function_vect` (an LCF prior takes any callable,
+    model.py:213-217): an intercept, the first inputs, and two bounded non-linear columns.  float64 [n, d]."""
+    X = np.asarray(X, dtype=f64)
+    cols = [np.ones(X.shape[0]), X[:, 0], X[:, 1], np.tanh(X[:, 2]), np.sin(X[:, 0] * X[:, 1]), X[:, -1] ** 2]
+    return np.stack(cols[:n_concepts], axis=1)
+
+
+def woodbury_solve(phi: np.ndarray, residual: np.ndarray, sigma: np.ndarray, jitter: float = 1e-6):
+    """alpha = (eps I + Phi Sigma Phi^T)^-1 residual and log|eps I + Phi Sigma Phi^T| through the d x d system
+    (model.py:262-325): eps = jitter * max(trace(Sigma Phi^T Phi) / n, 1), A = Sigma^-1 + Phi^T Phi / eps."""
+    phi, residual, sigma = np.asarray(phi, f64), np.asarray(residual, f64).reshape(-1), np.asarray(sigma, f64)
+    n = phi.shape[0]
+    if n == 0:
+        return np.zeros(0, f64), 0.0
+    ptp = phi.T @ phi
+    eps = jitter * max(float(np.einsum("ij,ij->", sigma, ptp)) / n, 1.0)
+    A = np.linalg.inv(sigma) + ptp / eps
+    LA = np.linalg.cholesky(A)
+    b = phi.T @ residual
+    z = np.linalg.solve(LA.T, np.linalg.solve(LA, b))
+    alpha = (residual - (phi @ z) / eps) / eps
+    logdet = 2.0 * np.log(np.diag(LA)).sum() + np.linalg.slogdet(sigma)[1] + n * math.log(eps)
+    return alpha, float(logdet)
+
+
+def lcf_log_prior(phi, f, p_mean, sigma, jitter: float = 1e-6) -> float:
+    """log p_GP(f(X_M)) (model.py:422-449)."""
+    phi = np.asarray(phi, f64)
+    residual = np.asarray(f, f64).reshape(-1) - phi @ np.asarray(p_mean, f64)
+    alpha, logdet = woodbury_solve(phi, residual, sigma, jitter)
+    n = residual.shape[0]
+    return float(-0.5 * (residual @ alpha) - 0.5 * logdet - 0.5 * n * math.log(2.0 * math.pi))
+
+
+def mlp_rows(weights, X: np.ndarray, activation: str):
+    """RewardMLP forward over plain rows -> (f [n], cache) (mlp.py:73-111)."""
+    n_layers = len(weights) // 2
+    h = np.asarray(X, f32)
+    hs, zs = [h], []
+    for l in range(n_layers):
+        w, b = weights[2 * l].astype(f32), weights[2 * l + 1].astype(f32)
+        z = (h @ w) / f32(math.sqrt(w.shape[0])) + b
+        if l < n_layers - 1:
+            zs.append(z)
+            h = _act(activation, z).astype(f32)
+            hs.append(h)
+    return z.reshape(-1), dict(hs=hs, zs=zs)
+
+
+def mlp_rows_vjp(weights, cache, cot: np.ndarray, activation: str) -> List[np.ndarray]:
+    """J_w^T cot for the rows of `cache` (what torch.autograd.grad(f, params, cot) returns, model.py:496-503)."""
+    n_layers = len(weights) // 2
+    grads: List[np.ndarray] = [None] * len(weights)
+    dz = np.asarray(cot, f32).reshape(-1, 1)
+    for l in range(n_layers - 1, -1, -1):
+        w = weights[2 * l].astype(f32)
+        sc = f32(1.0 / math.sqrt(w.shape[0]))
+        grads[2 * l] = (cache["hs"][l].T @ dz) * sc
+        grads[2 * l + 1] = dz.sum(0)
+        if l > 0:
+            dz = (((dz @ w.T) * sc) * _act_grad(activation, cache["zs"][l - 1])).astype(f32)
+    return grads
+
+
+class MRTrainerFOracle(MRTrainerOracle):
+    """MRTrainerF.train (training.py:166-262): likelihood gradient, plus J^T alpha / N from the functional prior, Adam, and
+    the logged energy U / N = CE - log p_GP(f_new(X_M)) / N evaluated with the updated weights."""
+
+    def __init__(self, weights, activation, num_datapoints, p_mean, sigma, lr=3e-4, bt_pool="mean"):
+        super().__init__(weights, activation, lr=lr, bt_pool=bt_pool)
+        self.N, self.p_mean, self.sigma = float(num_datapoints), np.asarray(p_mean, f64), np.asarray(sigma, f64)
+
+    def grads(self, batch, x_meas, phi, jitter=1e-6):
+        loss, acc, g = mr_loss_and_grads(self.weights, batch, self.activation, self.bt_pool)
+        f, cache = mlp_rows(self.weights, x_meas, self.activation)
+        alpha, _ = woodbury_solve(phi, f.astype(f64) - np.asarray(phi, f64) @ self.p_mean, self.sigma, jitter)
+        vjp = mlp_rows_vjp(self.weights, cache, alpha.astype(f32), self.activation)  # grad_out = alpha.to(f32), :484
+        # functional_prior_grad returns -J^T alpha; param.grad.add_(-fg / N) (training.py:236-238)
+        g = [(gi.reshape(vi.shape) + vi / f32(self.N)).astype(f32) for gi, vi in zip(g, vjp)]
+        return loss, acc, g
+
+    def train(self, batch, x_meas, phi, jitter=1e-6) -> Dict[str, float]:
+        loss, acc, g = self.grads(batch, x_meas, phi, jitter)
+        self.step += 1
+        adam_update(self.weights, g, self.m, self.v, self.step, lr=self.lr)
+        f_new, _ = mlp_rows(self.weights, x_meas, self.activation)
+        prior = lcf_log_prior(phi, f_new, self.p_mean, self.sigma, jitter)
+        return {"training_loss": loss - prior / self.N, "training_acc": acc, "ce_loss": loss, "log_prior": prior}

@@ -327,6 +327,26 @@ int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float*
                        const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
                        float beta1, float beta2, float eps, int64_t adam_step, float* out2,
                        float* grad_out, void* stream);
+/* MRTrainerF.train (training.py:166-262): the step above with the functional GP prior of an LCF model
+ * (optbnn/gp/models/model.py:202-513: f = Phi(x)^T w, w ~ N(p_mean, Sigma)) in place of a weight prior.  The gradient the
+ * step descends is dCE/dw + J_w(X_M)^T alpha / N with alpha = (Phi Sigma Phi^T + eps I)^-1 (f(X_M) - Phi p_mean), solved
+ * through the d x d Woodbury system in fp64 (model.py:262-325: eps = jitter * max(trace(Sigma Phi^T Phi) / n_meas, 1)).
+ *   x_meas [n_meas][d_in] device fp32 : the measurement points; they go through the step's GEMMs as extra rows, so
+ *       iqlb_mr_create's max_rows must cover 2*B*T + n_meas
+ *   phi [n_meas][n_concepts] device fp64 : Phi(X_M), evaluated by the caller (the reference's `function_vect` is user code)
+ *   p_mean [d], sigma [d][d], sigma_inv [d][d] device fp64, logdet_sigma = log|Sigma| : the prior's constants; d <= 64
+ *   num_datapoints : N of training.py:238;  jitter : relative nugget (1e-6 in the reference)
+ *   prior_out (nullable) device double[2] : log p_GP(f(X_M)) evaluated with the UPDATED weights (training.py:242-250; the
+ *       reference logs training_loss = out2[0] - prior_out[0] / N) and eps
+ * A covariance that is not positive definite gives NaN where the reference's torch.linalg.cholesky raises. */
+int iqlb_mr_train_step_f(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
+                         const float* states1, const float* actions1, const float* mask1,
+                         const float* states2, const float* actions2, const float* mask2,
+                         const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                         float beta1, float beta2, float eps, int64_t adam_step, const float* x_meas,
+                         const double* phi, int32_t n_meas, int32_t n_concepts, const double* p_mean,
+                         const double* sigma, const double* sigma_inv, double logdet_sigma, double jitter,
+                         double num_datapoints, float* out2, double* prior_out, float* grad_out, void* stream);
 /* MRTrainer.evaluation: forward + loss/accuracy only; pred_out (nullable) float[2*B*T] per-row rewards */
 int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float* states1, const float* actions1,
                  const float* mask1, const float* states2, const float* actions2, const float* mask2,

@@ -80,6 +80,9 @@ _SIGNATURES = {
     "iqlb_mr_param_count": ([_P, C.POINTER(C.c_int64)], C.c_int),
     "iqlb_mr_train_step": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                             C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64, _P, _P, _P], C.c_int),
+    "iqlb_mr_train_step_f": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                              C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64, _P, _P, C.c_int32, C.c_int32, _P, _P, _P,
+                              C.c_double, C.c_double, C.c_double, _P, _P, _P, _P], C.c_int),
     "iqlb_mr_eval": ([_P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P], C.c_int),
     "iqlb_pt_train_param_count": ([C.POINTER(PTDesc), C.POINTER(C.c_int64)], C.c_int),
     "iqlb_pt_trainer_create": ([C.POINTER(PTDesc), C.c_int32, C.c_int32, C.POINTER(_P)], C.c_int),

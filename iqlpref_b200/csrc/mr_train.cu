@@ -195,6 +195,106 @@ __global__ void __launch_bounds__(256) mr_reduce_adam_kernel(const float* __rest
 }
 
 // host launchers shared with the preference-transformer trainer (pt_train.cu; declared in pt.cuh)
+// ------------------------------------------------------------------------------------------------
+// Functional GP prior of an LCF model at the measurement points (MRTrainerF; gp/models/model.py:262-325, 422-449,
+// 451-513): K = Phi Sigma Phi^T has rank <= d, so alpha = (K + eps I)^-1 (f - Phi p_mean) comes from the d x d system
+//   eps = jitter * max(trace(Sigma Phi^T Phi) / n, 1),  A = Sigma^-1 + Phi^T Phi / eps = L L^T,
+//   alpha = (r - Phi A^-1 Phi^T r / eps) / eps,  log|K + eps I| = log|A| + log|Sigma| + n log eps,
+// all in fp64 as the reference does.  One CTA (d <= 64, a few hundred points: the algebra is ~1 MFLOP).
+//   rowgrad != null : rowgrad[i] = float(alpha_i) * cot_scale   (the cotangent of f(X_M) in the backward pass: the step
+//                     adds J^T alpha / N to the likelihood gradient, training.py:233-238)
+//   prior_out != null : prior_out[0] = log p_GP(f) = -r.alpha / 2 - log|K + eps I| / 2 - n log(2 pi) / 2, prior_out[1] = eps
+// ------------------------------------------------------------------------------------------------
+constexpr int kFpMaxD = 64;
+__global__ void __launch_bounds__(256) mr_fprior_kernel(const float* __restrict__ f, const double* __restrict__ phi, int n,
+                                                        int d, const double* __restrict__ p_mean,
+                                                        const double* __restrict__ sigma,
+                                                        const double* __restrict__ sigma_inv, double logdet_sigma,
+                                                        double jitter, float cot_scale, double* __restrict__ r_scratch,
+                                                        float* __restrict__ rowgrad, double* __restrict__ prior_out) {
+  __shared__ double A[kFpMaxD * kFpMaxD];
+  __shared__ double bvec[kFpMaxD], red[256];
+  __shared__ double s_eps, s_logdet;
+  const int tid = threadIdx.x;
+  auto block_sum = [&](double v) -> double {  // fixed-order tree: the result does not depend on scheduling
+    red[tid] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (tid < o) red[tid] += red[tid + o];
+      __syncthreads();
+    }
+    const double t = red[0];
+    __syncthreads();
+    return t;
+  };
+  for (int i = tid; i < n; i += 256) {  // r = f - Phi p_mean
+    double m = 0.0;
+    for (int j = 0; j < d; ++j) m += phi[(int64_t)i * d + j] * p_mean[j];
+    r_scratch[i] = (double)f[i] - m;
+  }
+  for (int idx = tid; idx < d * d; idx += 256) {  // Phi^T Phi
+    const int j = idx / d, k = idx % d;
+    double acc = 0.0;
+    for (int i = 0; i < n; ++i) acc += phi[(int64_t)i * d + j] * phi[(int64_t)i * d + k];
+    A[idx] = acc;
+  }
+  __syncthreads();
+  double part = 0.0;
+  for (int idx = tid; idx < d * d; idx += 256) part += sigma[idx] * A[idx];
+  const double kdm = block_sum(part) / (double)n;
+  const double eps = jitter * (kdm > 1.0 ? kdm : 1.0);
+  for (int idx = tid; idx < d * d; idx += 256) A[idx] = sigma_inv[idx] + A[idx] / eps;
+  if (tid < d) {  // b = Phi^T r
+    double acc = 0.0;
+    for (int i = 0; i < n; ++i) acc += phi[(int64_t)i * d + tid] * r_scratch[i];
+    bvec[tid] = acc;
+  }
+  __syncthreads();
+  for (int k = 0; k < d; ++k) {  // Cholesky, lower triangle in place (a non-positive pivot gives NaN, where torch raises)
+    if (tid == 0) A[k * d + k] = sqrt(A[k * d + k]);
+    __syncthreads();
+    for (int i = k + 1 + tid; i < d; i += 256) A[i * d + k] /= A[k * d + k];
+    __syncthreads();
+    const int rem = d - k - 1;
+    for (int idx = tid; idx < rem * rem; idx += 256) {
+      const int i = k + 1 + idx / rem, j = k + 1 + idx % rem;
+      if (j <= i) A[i * d + j] -= A[i * d + k] * A[j * d + k];
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {  // z = A^-1 b (two triangular solves), log|A|
+    double ld = 0.0;
+    for (int i = 0; i < d; ++i) {
+      double v = bvec[i];
+      for (int j = 0; j < i; ++j) v -= A[i * d + j] * bvec[j];
+      bvec[i] = v / A[i * d + i];
+      ld += log(A[i * d + i]);
+    }
+    for (int i = d - 1; i >= 0; --i) {
+      double v = bvec[i];
+      for (int j = i + 1; j < d; ++j) v -= A[j * d + i] * bvec[j];
+      bvec[i] = v / A[i * d + i];
+    }
+    s_logdet = 2.0 * ld;
+    s_eps = eps;
+  }
+  __syncthreads();
+  double quad = 0.0;
+  for (int i = tid; i < n; i += 256) {
+    double pz = 0.0;
+    for (int j = 0; j < d; ++j) pz += phi[(int64_t)i * d + j] * bvec[j];
+    const double r = r_scratch[i], alpha = (r - pz / eps) / eps;
+    if (rowgrad) rowgrad[i] = (float)alpha * cot_scale;
+    quad += r * alpha;
+  }
+  quad = block_sum(quad);
+  if (tid == 0 && prior_out) {
+    const double logdet = s_logdet + logdet_sigma + (double)n * log(s_eps);
+    prior_out[0] = -0.5 * quad - 0.5 * logdet - 0.5 * (double)n * 1.8378770664093453;  // log(2 pi)
+    prior_out[1] = s_eps;
+  }
+}
+
 int launch_bt_loss(const float* pred, const float* m1, const float* m2, const float* labels, int B, int T, int pool_mean,
                    float* rowgrad, float* pair_out, unsigned int* counter, float* out2, cudaStream_t st) {
   mr_loss_kernel<<<B, 64, 0, st>>>(pred, m1, m2, labels, B, T, pool_mean, rowgrad, pair_out, counter, out2);
@@ -242,12 +342,20 @@ struct iqlb_mr_trainer {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;  // IQLB_MR_OVERLAP=0: everything on the caller's stream
   int tc = 0;           // iqlb_mr_set_precision: 1 = the seven GEMMs of a step run on the tensor cores in split-bf16
+  double* fp_r = nullptr;  // [max_rows] residual f - Phi p_mean of the functional-prior kernel (first iqlb_mr_train_step_f)
+};
+
+struct MrFPrior {  // arguments of iqlb_mr_train_step_f beyond those of iqlb_mr_train_step
+  const float* x_meas; const double* phi; int n_meas, d;
+  const double *p_mean, *sigma, *sigma_inv;
+  double logdet_sigma, jitter, num_datapoints;
+  double* prior_out;
 };
 
 static void mr_free(iqlb_mr_trainer* h) {
   if (!h) return;
   cudaFree(h->X); cudaFree(h->pred); cudaFree(h->rowgrad); cudaFree(h->partial); cudaFree(h->G0); cudaFree(h->G1);
-  cudaFree(h->out2); cudaFree(h->d_tasks); cudaFree(h->pair_out); cudaFree(h->counter);
+  cudaFree(h->out2); cudaFree(h->d_tasks); cudaFree(h->pair_out); cudaFree(h->counter); cudaFree(h->fp_r);
   for (float* p : h->Z) cudaFree(p);
   for (float* p : h->H) cudaFree(p);
   if (h->side) cudaStreamDestroy(h->side);
@@ -335,15 +443,21 @@ extern "C" int iqlb_mr_param_count(const iqlb_mr_trainer* h, int64_t* n_params) 
   return IQLB_OK;
 }
 
+// Forward over the 2*B*T rows of both segments (B == 0: none) followed by n_extra plain rows x_extra [n_extra][d_in]
+// (the measurement points of MRTrainerF): pred[0 .. 2BT + n_extra).
 static int mr_forward(iqlb_mr_trainer* h, const float* params, const float* s1, const float* a1, const float* s2,
-                      const float* a2, int B, int T, int S, int A, bool keep_pre, cudaStream_t st) {
-  const int64_t BT = (int64_t)B * T, M = 2 * BT;
-  {
-    const int64_t total = M * h->d_in;
+                      const float* a2, int B, int T, int S, int A, bool keep_pre, cudaStream_t st,
+                      const float* x_extra = nullptr, int n_extra = 0) {
+  const int64_t BT = (int64_t)B * T, M = 2 * BT + n_extra;
+  if (BT > 0) {
+    const int64_t total = 2 * BT * h->d_in;
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
     mr_pack_kernel<<<blocks, 256, 0, st>>>(s1, a1, s2, a2, BT, S, A, h->X);
     IQLB_LAUNCH_CHECK();
   }
+  if (n_extra > 0)
+    IQLB_CUDA(cudaMemcpyAsync(h->X + 2 * BT * h->d_in, x_extra, (size_t)n_extra * h->d_in * sizeof(float),
+                              cudaMemcpyDeviceToDevice, st));
   int prev = h->d_in;
   const float* src = h->X;
   for (int l = 0; l < h->depth; ++l) {
@@ -397,24 +511,37 @@ extern "C" int iqlb_mr_eval(iqlb_mr_trainer* h, const float* params, const float
   return IQLB_OK;
 }
 
-extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
-                                  const float* states1, const float* actions1, const float* mask1,
-                                  const float* states2, const float* actions2, const float* mask2,
-                                  const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
-                                  float beta1, float beta2, float eps, int64_t adam_step, float* out2,
-                                  float* grad_out, void* stream) {
+static int mr_train_impl(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq, const float* states1,
+                         const float* actions1, const float* mask1, const float* states2, const float* actions2,
+                         const float* mask2, const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                         float beta1, float beta2, float eps, int64_t adam_step, float* out2, float* grad_out,
+                         const MrFPrior* fp, void* stream) {
   int rc = mr_check_batch(h, params, states1, actions1, mask1, states2, actions2, mask2, labels, B, T, S, A);
   if (rc) return rc;
   IQLB_REQUIRE((exp_avg != nullptr && exp_avg_sq != nullptr) || lr == 0.f, "null optimizer state");
   IQLB_REQUIRE(adam_step >= 1, "adam_step counts from 1 (the step being taken)");
   cudaStream_t st = (cudaStream_t)stream;
-  const int64_t M = 2ll * B * T;
+  const int n_meas = fp ? fp->n_meas : 0;
+  if (fp) {
+    IQLB_REQUIRE(fp->x_meas && fp->phi && fp->p_mean && fp->sigma && fp->sigma_inv, "null prior pointer");
+    IQLB_REQUIRE(n_meas > 0 && fp->d > 0 && fp->d <= kFpMaxD, "1 <= n_concepts <= 64 and at least one measurement point");
+    IQLB_REQUIRE(2ll * B * T + n_meas <= h->max_rows, "2*B*T + n_meas larger than max_rows given to iqlb_mr_create");
+    IQLB_REQUIRE(fp->num_datapoints > 0 && fp->jitter > 0, "num_datapoints and jitter must be positive");
+    if (!h->fp_r) IQLB_CUDA(cudaMalloc((void**)&h->fp_r, (size_t)h->max_rows * sizeof(double)));
+  }
+  const int64_t M = 2ll * B * T + n_meas;  // the measurement points ride through the same GEMMs as extra rows
   const int L = h->depth;
-  rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, true, st);
+  rc = mr_forward(h, params, states1, actions1, states2, actions2, B, T, S, A, true, st, fp ? fp->x_meas : nullptr, n_meas);
   if (rc) return rc;
   mr_loss_kernel<<<B, 64, 0, st>>>(h->pred, mask1, mask2, labels, B, T, h->pool_mean, h->rowgrad, h->pair_out,
                                    h->counter, out2 ? out2 : h->out2);
   IQLB_LAUNCH_CHECK();
+  if (fp) {  // dU/df(X_M) = alpha / N (training.py:233-238: param.grad += J^T alpha / N)
+    mr_fprior_kernel<<<1, 256, 0, st>>>(h->pred + 2ll * B * T, fp->phi, n_meas, fp->d, fp->p_mean, fp->sigma, fp->sigma_inv,
+                                        fp->logdet_sigma, fp->jitter, (float)(1.0 / fp->num_datapoints), h->fp_r,
+                                        h->rowgrad + 2ll * B * T, nullptr);
+    IQLB_LAUNCH_CHECK();
+  }
 
   // row chunks of the split weight-gradient reductions
   int n_chunks = (int)((M + 127) / 128);
@@ -512,5 +639,36 @@ extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_
     rc = reduce_adam(h->offW[l], plen, (int64_t)prev * w, 1.0f / sqrtf((float)prev));
     if (rc) return rc;
   }
+  if (fp && fp->prior_out) {  // log p_GP(f(X_M)) with the updated weights (training.py:242-250)
+    rc = mr_forward(h, params, nullptr, nullptr, nullptr, nullptr, 0, 0, S, A, false, st, fp->x_meas, n_meas);
+    if (rc) return rc;
+    mr_fprior_kernel<<<1, 256, 0, st>>>(h->pred, fp->phi, n_meas, fp->d, fp->p_mean, fp->sigma, fp->sigma_inv,
+                                        fp->logdet_sigma, fp->jitter, 0.f, h->fp_r, nullptr, fp->prior_out);
+    IQLB_LAUNCH_CHECK();
+  }
   return IQLB_OK;
+}
+
+extern "C" int iqlb_mr_train_step(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
+                                  const float* states1, const float* actions1, const float* mask1,
+                                  const float* states2, const float* actions2, const float* mask2,
+                                  const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                                  float beta1, float beta2, float eps, int64_t adam_step, float* out2,
+                                  float* grad_out, void* stream) {
+  return mr_train_impl(h, params, exp_avg, exp_avg_sq, states1, actions1, mask1, states2, actions2, mask2, labels, B, T, S,
+                       A, lr, beta1, beta2, eps, adam_step, out2, grad_out, nullptr, stream);
+}
+
+extern "C" int iqlb_mr_train_step_f(iqlb_mr_trainer* h, float* params, float* exp_avg, float* exp_avg_sq,
+                                    const float* states1, const float* actions1, const float* mask1,
+                                    const float* states2, const float* actions2, const float* mask2,
+                                    const float* labels, int32_t B, int32_t T, int32_t S, int32_t A, float lr,
+                                    float beta1, float beta2, float eps, int64_t adam_step, const float* x_meas,
+                                    const double* phi, int32_t n_meas, int32_t n_concepts, const double* p_mean,
+                                    const double* sigma, const double* sigma_inv, double logdet_sigma, double jitter,
+                                    double num_datapoints, float* out2, double* prior_out, float* grad_out,
+                                    void* stream) {
+  MrFPrior fp{x_meas, phi, n_meas, n_concepts, p_mean, sigma, sigma_inv, logdet_sigma, jitter, num_datapoints, prior_out};
+  return mr_train_impl(h, params, exp_avg, exp_avg_sq, states1, actions1, mask1, states2, actions2, mask2, labels, B, T, S,
+                       A, lr, beta1, beta2, eps, adam_step, out2, grad_out, &fp, stream);
 }

@@ -1,4 +1,4 @@
-"""`MRTrainer` of /root/reference/gp_reward-priors/optbnn/training/training.py:11-129 behind the same surface
+"""`MRTrainer` (and `MRTrainerF`, :132-305, below) of /root/reference/gp_reward-priors/optbnn/training/training.py:11-129 behind the same surface
 (`MRTrainer(net, opt, num_datapoints, device, bt_pool)`, `.train(batch) -> {"training_loss", "training_acc"}`,
 `.evaluation(batch) -> {"eval_loss", "eval_acc"}`, `.state_dict()`, `.load_state_dict()`), SURVEY.md §8f-1.
 
@@ -189,6 +189,71 @@ class MRTrainer:
         self.net.load_state_dict(state_dict["net"])  # copies into the views of the flat buffer
         self.opt.load_state_dict(state_dict["optimizer"])
         self._adopt_optimizer_state()
+
+
+class MRTrainerF(MRTrainer):
+    """`MRTrainerF` of training.py:132-305: the MR step with the functional GP prior of an `LCFModel` in place of a
+    weight-space prior.  `train(batch, x_meas, aux_meas=None, jitter=1e-6)` descends U(f) / N = CE + I_0(f) / N: the
+    measurement points ride through the step's GEMMs as extra rows, their cotangent alpha / N =
+    (K + eps I)^-1 (f(X_M) - m(X_M)) / N comes from the d x d Woodbury system in fp64 (`mr_fprior_kernel`), and the logged
+    `training_loss` is CE - log p_GP(f_new(X_M)) / N with the updated weights (training.py:242-250) -
+    `iqlb_mr_train_step_f` (`csrc/mr_train.cu`).  `prior` is this package's `gp_prior.LCFModel`, or any object with the
+    reference LCFModel's `p_mean`, `p_covariance` and `function_vect` (it is re-wrapped).  `evaluation`, `state_dict`,
+    `load_state_dict` are MRTrainer's (the reference's bodies are identical, training.py:264-305)."""
+
+    def __init__(self, net, opt, num_datapoints: int, prior, device: str = "cuda", bt_pool: str = "mean",
+                 max_rows: int = 0, precision: str = "fp32"):
+        super().__init__(net, opt, num_datapoints, device=device, bt_pool=bt_pool, max_rows=max_rows, precision=precision)
+        from .gp_prior import LCFModel
+        if prior is None:
+            raise ValueError("MRTrainerF: the functional prior is required (training.py:141)")
+        if not isinstance(prior, LCFModel):
+            prior = LCFModel(prior.p_covariance.detach().cpu(), prior.function_vect, self.device,
+                             p_mean=prior.p_mean.detach().cpu(), name=getattr(prior, "name", None))
+        self.prior = prior
+        self._prior_out = torch.zeros(2, dtype=torch.float64, device=self.device)
+
+    def train(self, batch: TensorBatch, x_meas, aux_meas=None, jitter: float = 1e-6, return_grad: bool = False,
+              sync: bool = True) -> Dict[str, float]:
+        ts, B, T, S, A = self._unpack(batch)
+        if not self.net.training:
+            self.net.train()
+        x_meas_t = torch.as_tensor(x_meas, dtype=torch.float32, device=self.device).contiguous()  # training.py:219
+        aux_t = torch.as_tensor(aux_meas, dtype=torch.float32, device=self.device) if aux_meas is not None else None
+        if x_meas_t.ndim != 2 or x_meas_t.shape[1] != self.d_in:
+            raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({tuple(x_meas_t.shape)} and {self.d_in}x{self.widths[0]})")
+        n_meas = int(x_meas_t.shape[0])
+        if n_meas == 0:
+            raise ValueError("MRTrainerF: empty measurement set")
+        phi = self.prior.features64(x_meas_t, aux_t)
+        if phi.shape[0] != n_meas:
+            raise ValueError("function_vect must return one row per measurement point")
+        rows = 2 * B * T + n_meas
+        lib = self._ensure(rows + (rows & 1))
+        g = self.opt.param_groups[0]
+        grad = torch.empty_like(self.flat) if return_grad else None
+        self.step_count += 1
+        pr = self.prior
+        with torch.cuda.device(self.device):
+            _lib.check(lib.iqlb_mr_train_step_f(
+                self._handle, _lib.ptr(self.flat), _lib.ptr(self.exp_avg), _lib.ptr(self.exp_avg_sq),
+                *[_lib.ptr(t) for t in ts], B, T, S, A, float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]),
+                float(g["eps"]), self.step_count, _lib.ptr(x_meas_t), _lib.ptr(phi), n_meas, pr.n_concepts,
+                _lib.ptr(pr._p_mean64), _lib.ptr(pr._sigma64), _lib.ptr(pr._sigma_inv64), pr._logdet_sigma, float(jitter),
+                float(self.num_datapoints), _lib.ptr(self._out2), _lib.ptr(self._prior_out), _lib.ptr(grad),
+                _lib.stream_ptr(self.device)), "iqlb_mr_train_step_f")
+        if sync:
+            loss, acc = self._out2.tolist()
+            prior_val = float(self._prior_out[0])
+            log = {"training_loss": loss - prior_val / self.num_datapoints, "training_acc": acc}
+        else:
+            snap, psnap = self._out2.clone(), self._prior_out.clone()
+            log = {"training_loss": snap[0].double() - psnap[0] / self.num_datapoints, "training_acc": snap[1]}
+        if return_grad:
+            log["grad"] = grad
+            log["ce_loss"] = float(self._out2[0])
+            log["log_prior"] = float(self._prior_out[0])
+        return log
 
 
 def fit_mr(model: MRTrainer, training_batches, val_batches, epochs: int, eval_every: int = 5,

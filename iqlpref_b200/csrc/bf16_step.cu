@@ -602,6 +602,9 @@ static size_t bwd_weight_smem(int B) { return 7u * (size_t)B * 128u + 64u; }
 int bf16_fwd_persist_launch(const BfParams& P, const float* params, const float* target, float* head_out, int n_agents,
                             cudaStream_t stream, bool pdl);
 
+int bf16_bwd_data_persist_launch(const BfParams& P, const float* params, const float* d_out, int n_agents, int n_sm,
+                                 cudaStream_t stream, bool pdl);
+
 int bf16_create(iqlb_agents* h) {
   const Layout& L = h->L;
   IQLB_REQUIRE(L.H == 256, "the tcgen05 path is built for hidden_dim == 256");
@@ -757,9 +760,16 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   P.agent0 = a0;
   bf16_set_dropout(h, P);
   P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
-  IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(kBdThreads), bwd_data_smem(), stream,
-                       pdl_enabled(8) && !h->prof, P,
-                       (const float*)h->params, (const float*)h->d_out));
+  static const bool bd_persist = !(getenv("IQLB_BD_PERSIST") && atoi(getenv("IQLB_BD_PERSIST")) == 0);
+  if (bd_persist) {
+    int rc = bf16_bwd_data_persist_launch(P, h->params, h->d_out, N, h->n_sm > 0 ? h->n_sm : 148, stream,
+                                          pdl_enabled(8) && !h->prof);
+    if (rc) return rc;
+  } else {
+    IQLB_CUDA(launch_pdl(bf16_bwd_data_kernel, dim3(L.B / 128, kTrain, N), dim3(kBdThreads), bwd_data_smem(), stream,
+                         pdl_enabled(8) && !h->prof, P,
+                         (const float*)h->params, (const float*)h->d_out));
+  }
   pf.mark("bf16_bwd_data");
   if (h->zig >= 0) P.rev ^= 1;
   const int n_tiles = (L.H / 128) * kTrain * N;

@@ -40,7 +40,17 @@ if l[0]:
     print("loss CTA 0: " + ", ".join(f"{n}={int(x - l[0])}" for n, x in zip(["start", "loads done", "loop done", "sync", "sums written", "scalars start", "scalars end"], l) if x))
 
 d = ts[2560:2560 + 12]
-if d[0]:
+if os.environ.get("IQLB_BD_PERSIST", "1") != "0":
+    print("bwd_data (persistent) CTA 0, clocks from the first stamp; per half-tile n: worker [unit start, half start, loads issued, "
+          "A free, produced, drained prev] | issuer [W1+TMEM ready, MMAs issued, MMAs done, dH2 store read]")
+    t0 = min(int(x) for x in ts[2560:2560 + 128] if x)
+    for n in range(8):
+        r = ts[2560 + n * 16: 2560 + n * 16 + 12]
+        if not r.any():
+            break
+        f = lambda x: f"{int(x) - t0:7d}" if x else "      -"
+        print(f"  n={n}: w " + " ".join(f(x) for x in r[0:6]) + "  | i " + " ".join(f(x) for x in r[8:12]))
+elif d[0]:
     print("bwd_data CTA (0,1,0): " + ", ".join(f"{n}={int(x - d[0])}" for n, x in zip(["start", "loads in regs", "sync", "dH2 tile done", "sync2", "mma0", "mma1", "mma2", "mma3", "drained"], d) if x))
 
 import collections

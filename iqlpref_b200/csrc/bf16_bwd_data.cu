@@ -171,7 +171,8 @@ __global__ void __launch_bounds__(bdp::kThreads, 1) bf16_bwd_data_persist_kernel
         }
       }
       if (cnt > 0) store_dh1(prev_dh1, (uint32_t)((cnt - 1) & 1));
-      bulk_wait0();
+      // (every store has been READ out of shared memory: the CTA may exit, the writes complete with the grid - waiting for
+      //  them here, cp.async.bulk.wait_group 0, kept every CTA ~1 us longer and cost 1.2 us per step at 8 agents)
     }
   } else {
     // ------------------------------------------------------------------ workers

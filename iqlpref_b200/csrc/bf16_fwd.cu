@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
           ++ntr;
         }
       }
-      bulk_wait0();
+      bulk_wait_read0();  // (read out of shared memory; the global writes complete with the grid)
     }
   }
   tc_fence_before();

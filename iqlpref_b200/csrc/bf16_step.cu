@@ -760,9 +760,15 @@ int bf16_step_gemms_bwd(iqlb_agents* h, int a0, int n, Prof& pf, cudaStream_t st
   P.agent0 = a0;
   bf16_set_dropout(h, P);
   P.rev = h->zig == 1;  // data gradients in the forward's direction, weight gradients against it
-  static const bool bd_persist = !(getenv("IQLB_BD_PERSIST") && atoi(getenv("IQLB_BD_PERSIST")) == 0);
+  // More half-tiles than SMs: the persistent kernel (bf16_bwd_data.cu; shared W1 loads, loads a tile ahead, packed schedule:
+  // 40.0 -> 31.7 us at 64 agents).  Otherwise every half-tile gets its own SM either way and the one-tile-per-CTA kernel
+  // below is the one that measured faster inside the PDL chain (8 agents: 59.7 vs 61.0 us per step, 16: 81.1 vs 83.2,
+  // although the persistent kernel alone is 1.5 us shorter; profiles/r02f_bwd_data_persist_ab.jsonl).
+  static const int bd_env = getenv("IQLB_BD_PERSIST") ? atoi(getenv("IQLB_BD_PERSIST")) : -1;
+  const int n_sm_bd = h->n_sm > 0 ? h->n_sm : 148;
+  const bool bd_persist = bd_env >= 0 ? bd_env != 0 : N * kTrain * (L.B / 128) > n_sm_bd;
   if (bd_persist) {
-    int rc = bf16_bwd_data_persist_launch(P, h->params, h->d_out, N, h->n_sm > 0 ? h->n_sm : 148, stream,
+    int rc = bf16_bwd_data_persist_launch(P, h->params, h->d_out, N, n_sm_bd, stream,
                                           pdl_enabled(8) && !h->prof);
     if (rc) return rc;
   } else {

@@ -361,7 +361,13 @@ __device__ __forceinline__ void bwd_weight_drain_p(const BfParams& P, uint8_t* s
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
     P.dbg[4096 + 1536 + tile * 4] = smid; P.dbg[4096 + 1536 + tile * 4 + 1] = gt; P.dbg[4096 + 1536 + tile * 4 + 3] = (unsigned)t;
   }
+#ifdef IQLB_NO_TIMELINE
+#define IQLB_TSWD(k) do { } while (0)
+#else
+#define IQLB_TSWD(k) do { if (P.dbg != nullptr && blockIdx.x == 0 && tid == 0 && tile / (int)gridDim.x < 8) P.dbg[3200 + (tile / (int)gridDim.x) * 16 + (k)] = (unsigned long long)clock64(); } while (0)
+#endif
   mbar_wait(bar_p1, ph);
+  IQLB_TSWD(9);
   tc_fence_after();
   {
     // ---- dW1: four 64-column chunks through one [128 rows][64] fp32 buffer (float4 index ^ (row & 15)); bf16 rows leave
@@ -396,7 +402,9 @@ __device__ __forceinline__ void bwd_weight_drain_p(const BfParams& P, uint8_t* s
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_d1);
   }
+  IQLB_TSWD(10);
   mbar_wait(bar_p2, ph);
+  IQLB_TSWD(12);
   tc_fence_after();
   // ---- everything else through shared memory in packed-parameter order (the operands of phase 2 are dead):
   //      G0 = dW0 tile [128][in] | G1 = db1[128] | G2 = db0[128] | G3 = dW2[nout][128]
@@ -526,6 +534,11 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+#ifdef IQLB_NO_TIMELINE
+#define IQLB_TSW(slot) do { } while (0)
+#else  // clock64 stamps of CTA 0, 16 slots per tile (issuing thread 0..7, drain thread 0 8..11): scripts/timeline.py
+#define IQLB_TSW(slot) do { if (P.dbg != nullptr && blockIdx.x == 0 && (slot) < 128) P.dbg[3200 + (slot)] = (unsigned long long)clock64(); } while (0)
+#endif
 
   if (issuer_warp) {
     if (elect_one()) {
@@ -537,13 +550,17 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
         const BwTile T = bw_tile(P, tile, n_ag);
         const uint32_t d1col = (it & 1) ? 448u : 480u;
         // phase 1: dW1 tile = dH2[:, ot]^T H1 (128 x 256), db1 = dH2[:, ot]^T [dz | 1]
+        IQLB_TSW(it * 16 + 0);
         mbar_wait(bar_ld1, ph);
+        IQLB_TSW(it * 16 + 1);
         if (it > 0) mbar_wait(bar_d1, ph ^ 1u);  // the previous tile's dW1 has left TMEM columns 0..255
+        IQLB_TSW(it * 16 + 2);
         tc_fence_after();
         gemm_issue(tmem, a, operand_mn_major(sbase + oB, L.B, 0, 0), 256, ksteps, false);
         gemm_issue(tmem + d1col, a, z, 32, ksteps, false);
         mma_commit(bar_p1);
         mbar_wait(bar_p1, ph);  // dH2 and H1 consumed: their space takes the phase-2 operands
+        IQLB_TSW(it * 16 + 3);
         mbar_expect_tx(bar_ld2, 2 * blk + (uint32_t)P.KXB * blk);
         bulk_g2s(sbase + oA, P.dh1 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld2);
         bulk_g2s(sbase + oB, P.xsa + (int64_t)T.agent * P.x_bytes, (uint32_t)P.KXB * blk, bar_ld2);
@@ -553,6 +570,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
         }
         // phase 2 (under the dW1 drain): dW0 tile = dH1[:, ot]^T X, db0 = dH1[:, ot]^T [dz | 1], dW2 = H2[:, ot]^T [dz | 1]
         mbar_wait(bar_ld2, ph);
+        IQLB_TSW(it * 16 + 4);
         if (it > 0) mbar_wait(bar_d2, ph ^ 1u);  // the previous tile's final drain has read TMEM columns 256..447
         tc_fence_after();
         gemm_issue(tmem + 256, a, operand_mn_major(sbase + oB, L.B, 0, 0), T.n0, ksteps, false);
@@ -563,6 +581,7 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
           bulk_g2s(sbase + oH2, P.h2 + T.at * P.h_bytes + (int64_t)(2 * T.ot) * blk, 2 * blk, bar_ld3);
         }
         mbar_wait(bar_ld3, ph);
+        IQLB_TSW(it * 16 + 5);
         tc_fence_after();
         gemm_issue(tmem + 416, operand_mn_major(sbase + oH2, L.B, 0, 0), z, 32, ksteps, false);
         mma_commit(bar_p2);
@@ -571,11 +590,13 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
         if (next < n_tiles) {
           const BwTile Nx = bw_tile(P, next, n_ag);
           mbar_wait(bar_p2, ph);  // every operand of this tile is dead
+          IQLB_TSW(it * 16 + 6);
           mbar_expect_tx(bar_ld1, 7 * blk);
           bulk_g2s(sbase + oA, P.dh2 + Nx.at * P.h_bytes + (int64_t)(2 * Nx.ot) * blk, 2 * blk, bar_ld1);
           bulk_g2s(sbase + oZ, P.dz + Nx.at * P.z_bytes, blk, bar_ld1);
           bulk_g2s(sbase + oB, P.h1 + Nx.at * P.h_bytes, 2 * blk, bar_ld1);
           mbar_wait(bar_d2, ph);  // the final drain has read its staging area (H1 blocks 2-3)
+          IQLB_TSW(it * 16 + 7);
           bulk_g2s(sbase + oB + 2 * blk, P.h1 + Nx.at * P.h_bytes + 2 * (int64_t)blk, 2 * blk, bar_ld1);
         }
       }
@@ -584,8 +605,10 @@ __global__ void __launch_bounds__(kBwThreads, 1) bf16_bwd_weight_kernel(BfParams
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const BwTile T = bw_tile(P, tile, n_ag);
+      if (tid == 0) IQLB_TSW(it * 16 + 8);
       bwd_weight_drain_p(P, smem, tmem, bar_p1, bar_p2, bar_d1, bar_d2, (uint32_t)(it & 1), (it & 1) ? 448u : 480u, T.ot, T.t,
                          T.agent, T.in, T.nout, T.n0, warp, lane, quarter, cgrp, tid, tile);
+      if (tid == 0) IQLB_TSW(it * 16 + 11);
     }
   }
   tc_fence_before();

@@ -39,6 +39,17 @@ l = ts[3072:3072 + 8]
 if l[0]:
     print("loss CTA 0: " + ", ".join(f"{n}={int(x - l[0])}" for n, x in zip(["start", "loads done", "loop done", "sync", "sums written", "scalars start", "scalars end"], l) if x))
 
+w = ts[3200:3200 + 128]
+if w.any():
+    print("bwd_weight CTA 0, clocks from the first stamp; per tile: issuer [tile start, P1 operands in, prev dW1 drained, P1 MMAs done, "
+          "P2 operands in, H2 in, P2 MMAs done, prev final drain read] | drain [start, dW1 ready, dW1 drained, (end), P2 ready]")
+    t0 = min(int(x) for x in w if x)
+    for it in range(8):
+        r = w[it * 16: it * 16 + 13]
+        if not r.any():
+            break
+        f = lambda x: f"{int(x) - t0:7d}" if x else "      -"
+        print(f"  it={it}: i " + " ".join(f(x) for x in r[0:8]) + "  | d " + " ".join(f(x) for x in (r[8], r[9], r[10], r[11], r[12])))
 d = ts[2560:2560 + 12]
 if os.environ.get("IQLB_BD_PERSIST", "1") != "0":
     print("bwd_data (persistent) CTA 0, clocks from the first stamp; per half-tile n: worker [unit start, half start, loads issued, "

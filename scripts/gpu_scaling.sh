@@ -1,8 +1,8 @@
 #!/bin/bash
 # strong (64 agents total, BASELINE configs[4]) and weak (64 agents per GPU) scaling on one 8-GPU box
-OUT=gpurun_out/scaling_r02; mkdir -p $OUT
+OUT=gpurun_out/${TAG:-scaling_r02}; mkdir -p $OUT
 for mode in strong weak; do
-  for n in 1 2 4 8; do
+  for n in ${NS:-1 2 4 8}; do
     timeout 600 python bench.py --gpus $n --steps 200 --warmup 10 --scaling $mode --agents-total 64 --skip-cpu-baseline --skip-reference-cuda --skip-relabel \
       > $OUT/bench_${mode}_n$n.json 2> $OUT/bench_${mode}_n$n.err
     echo "$mode n=$n rc=$?"

@@ -40,6 +40,7 @@ def main():
     out = {}
 
     def timed(name, fn, flush=None):
+        nonlocal K
         for i in range(20):
             fn(i)
         if flush:
@@ -57,6 +58,13 @@ def main():
         out[name] = {"us_per_step_events": round(e0.elapsed_time(e1) * 1e3 / K, 2),
                      "us_per_step_wall": round((time.perf_counter() - t0) * 1e6 / K, 2)}
 
+    for K in (20, 100, 300):  # fixed cost vs per-step cost of the host-fed path
+        timed(f"host_pipelined_K{K}", lambda i: eng.train_host_pipelined(host_rows[i % ring], host_losses),
+              flush=lambda: eng.train_host_pipelined(None, host_losses))
+        out[f"host_pipelined_K{K}"]["total_ms"] = round(out[f"host_pipelined_K{K}"]["us_per_step_wall"] * K / 1e3, 3)
+        timed(f"sampled_K{K}", lambda i: eng.train(None))
+        out[f"sampled_K{K}"]["total_ms"] = round(out[f"sampled_K{K}"]["us_per_step_wall"] * K / 1e3, 3)
+    K = a.steps
     timed("sampled", lambda i: eng.train(None))
     timed("device_rows", lambda i: eng.train(dev_rows[i % ring]))
     timed("host_pipelined", lambda i: eng.train_host_pipelined(host_rows[i % ring], host_losses),

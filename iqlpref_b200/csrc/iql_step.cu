@@ -174,15 +174,10 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
   }
   // bf16 path: the dz image (dz columns + a column of ones) feeds the weight-gradient MMAs, and the
   // head bias gradients are reduced here (the fp32 path does both in head_bwd_kernel)
-  auto put_dz = [&](int t, int col, float val) {
-    *reinterpret_cast<__nv_bfloat16*>(dzimg + ((int64_t)agent * kTrain + t) * z_bytes + umma::image_off(L.B, b, col)) =
-        __float2bfloat16_rn(val);
-  };
   if (bf && live) {
     for (int t = 0; t < 3; ++t)  // columns 0 (dz) and 1 (ones) share one 32-bit word of the image
       *reinterpret_cast<uint32_t*>(dzimg + ((int64_t)agent * kTrain + t) * z_bytes + umma::image_off(L.B, b, 0)) =
           umma::pack_bf16(t == 0 ? d0 : (t == 1 ? d1 : d2), 1.0f);
-    put_dz(3, L.A, 1.0f);
   }
   float bc = 0.f;
   // phase A: per-action terms in registers (no cross-lane traffic); phase B: warp sums of eight actions at a
@@ -207,9 +202,23 @@ __global__ void __launch_bounds__(kMaxThreads) loss_kernel(Layout L, const float
       }
       dza = dmu * (1.0f - mu[a] * mu[a]);
       dout[(int64_t)(3 + a) * L.B + b] = dza;
-      if (bf) put_dz(3, a, dza);
     }
     dzs[a] = dza; gss[a] = gls;
+  }
+  if (bf && live) {
+    // the actor's dz row (columns 0..A-1) and its column of ones (A): eight bf16 = one 16-byte chunk of the image per store
+    // (one 2-byte store per action cost a 32-line LSU pass each)
+    uint8_t* zrow = dzimg + ((int64_t)agent * kTrain + 3) * z_bytes;
+#pragma unroll
+    for (int a0 = 0; a0 <= kOutMax; a0 += 8) {
+      if (a0 <= L.A) {  // uniform
+        float c[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) c[k] = (a0 + k < kOutMax && a0 + k < L.A) ? dzs[a0 + k < kOutMax ? a0 + k : 0] : (a0 + k == L.A ? 1.0f : 0.f);
+        *reinterpret_cast<uint4*>(zrow + umma::image_off(L.B, b, a0)) =
+            make_uint4(umma::pack_bf16(c[0], c[1]), umma::pack_bf16(c[2], c[3]), umma::pack_bf16(c[4], c[5]), umma::pack_bf16(c[6], c[7]));
+      }
+    }
   }
 #pragma unroll
   for (int a0 = 0; a0 < kOutMax; a0 += 8) {

@@ -14,9 +14,11 @@
 // While the epilogue of tile i drains layer 1, the producer already holds tile i+1's operands and the
 // MMA warp has issued its layer 0, so loads, both GEMMs, TMEM allocation and barrier set-up disappear
 // from the critical path: a tile costs roughly its two epilogues.
-// Two instantiations: narrow (the input image is one 64-column block: state_dim + action_dim <= 64, action_dim <= 8, no actor
+// Tiles come from a host-built work list (fwd_schedule below).  Two instantiations: narrow (the input image is one 64-column block: state_dim + action_dim <= 64, action_dim <= 8, no actor
 // dropout - the D4RL locomotion / antmaze shapes) and wide (two input blocks, action_dim <= 24, actor dropout: pen / adroit).
 // The wide one trades a ring slot for the second X block and the 24-row W2; W0 takes one ring entry per input block.
+#include <vector>
+
 #include "iql_step.cuh"
 #include "umma.cuh"
 
@@ -80,7 +82,9 @@ __device__ __forceinline__ uint32_t bias_relu32(float (&v)[32], const float* __r
 template <bool kWide>
 __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfParams P, const float* __restrict__ params,
                                                                              const float* __restrict__ target,
-                                                                             float* __restrict__ head_out, int n_tiles) {
+                                                                             float* __restrict__ head_out, int n_agents,
+                                                                             const int32_t* __restrict__ wl_off,
+                                                                             const int32_t* __restrict__ wl) {
   using namespace fwdp;
   using Ly = Lay<kWide>;
   constexpr int kSlots = Ly::kSlots, kOut = Ly::kOut;
@@ -92,6 +96,9 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   const int tid = threadIdx.x, warp = warp_uniform(), lane = tid & 31, wu = warp;  // (measured: with warp = tid >> 5 for the
   // epilogue arithmetic this kernel is 3 us slower, while round 1's one-tile-per-CTA kernel was 30 % FASTER that way)
   const uint32_t sbase = smem_u32(smem);
+  // this CTA's tiles, in the order it runs them: a host-built schedule (persist_launch), entry = agent index << 4 | stream << 1 | half
+  const int wl_beg = __ldg(wl_off + blockIdx.x), cnt = __ldg(wl_off + blockIdx.x + 1) - wl_beg;
+  auto entry = [&](int it) -> int { return __ldg(wl + wl_beg + it); };
   const uint32_t bars = sbase + oCtrl;
   auto bar = [&](int i) -> uint32_t { return bars + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + oCtrl + 8 * N_BARS);
@@ -122,22 +129,10 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
 
   auto tile_ptrs = [&](int tile, int& agent, int& s, int& half, const uint8_t*& wnet, const uint8_t*& ximg,
                        const float*& fnet) {
-    const int nh = L.B / 128;
-    if (kWide) {
-      // Actor tiles cost about twice the others here (dropout masks, 24-row head), so they go first (longest processing time
-      // first) and to the CTAs that do not take part in the last, partial round: round 0 is dealt from the last CTA down.
-      const int G = gridDim.x, n_agents = n_tiles / (kStreams * nh), n_heavy = n_agents * nh;
-      int j = tile < G ? G - 1 - tile : tile, r;
-      if (j < n_heavy) { half = j % nh; r = j / nh; s = 6; }
-      else { j -= n_heavy; half = j % nh; r = j / nh; s = r % 6; r /= 6; }
-      agent = P.agent0 + (P.rev ? n_agents - 1 - r : r);
-    } else {
-      if (P.rev) tile = n_tiles - 1 - tile;
-      half = tile % nh;
-      const int r = tile / nh;
-      s = r % kStreams;
-      agent = P.agent0 + r / kStreams;
-    }
+    half = tile & 1;
+    s = (tile >> 1) & 7;
+    const int r = tile >> 4;
+    agent = P.agent0 + (P.rev ? n_agents - 1 - r : r);
     wnet = P.wimg + (int64_t)agent * P.agent_w_bytes + (int64_t)net_of_stream(s) * P.net_bytes;
     ximg = (s == 0 ? P.xnext : P.xsa) + (int64_t)agent * P.x_bytes;
     fnet = L.uses_target(s) ? target + (int64_t)agent * L.PQstride + L.net_off(s)
@@ -159,30 +154,38 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   };
   // PDL: the weight images (Adam of the previous step) are older than the immediate predecessor (the gather):
   // the first tile's weights start towards L2 before this grid waits for the gather's input images
-  if (wu == 0 && (int)blockIdx.x < n_tiles && elect_one()) {
+  if (wu == 0 && cnt > 0 && elect_one()) {
     int a0, s0, h0;
     const uint8_t *w0p, *x0p;
     const float* f0p;
-    tile_ptrs(blockIdx.x, a0, s0, h0, w0p, x0p, f0p);
+    tile_ptrs(entry(0), a0, s0, h0, w0p, x0p, f0p);
     bulk_prefetch_l2(w0p, (uint32_t)P.net_bytes);
   }
   pdl_wait();
   pdl_launch();
+#ifndef IQLB_NO_TIMELINE
+  if (P.dbg != nullptr && tid == 0 && blockIdx.x < 148) {  // (start, end) of every CTA on the global timer: scripts/timeline.py
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[7700 + blockIdx.x * 2] = gt;
+  }
+#endif
   if (wu == 0) {
     // ------------------------------------------------------------------ producer
     if (elect_one()) {
       int c = 0;  // ring entries issued so far (per tile: the W0 K-blocks, then W1 block 0..3)
-      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int it = 0; it < cnt; ++it) {
+        const int tile = entry(it);
         int agent, s, half;
         const uint8_t *wnet, *ximg;
         const float* fnet;
         tile_ptrs(tile, agent, s, half, wnet, ximg, fnet);
         const int in = L.in_dim(s);
-        if (tile + (int)gridDim.x < n_tiles) {  // next tile's operands start their trip HBM -> L2 one tile ahead
+        if (it + 1 < cnt) {  // next tile's operands start their trip HBM -> L2 one tile ahead
           int a2, s2, h2;
           const uint8_t *w2, *x2;
           const float* f2;
-          tile_ptrs(tile + gridDim.x, a2, s2, h2, w2, x2, f2);
+          tile_ptrs(entry(it + 1), a2, s2, h2, w2, x2, f2);
           bulk_prefetch_l2(w2, (uint32_t)P.net_bytes);
           bulk_prefetch_l2(x2 + (int64_t)h2 * 16384, 16384u);
           if (kWide && L.in_dim(s2) > 64) bulk_prefetch_l2(x2 + (int64_t)L.B * 128 + (int64_t)h2 * 16384, 16384u);
@@ -209,7 +212,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     // ------------------------------------------------------------------ MMA issuer
     if (elect_one()) {
       int c = 0;
-      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int it = 0; it < cnt; ++it) {
+        const int tile = entry(it);
         const uint32_t ph = (uint32_t)(it & 1);
         int agent, s, half;
         const uint8_t *wnet, *ximg;
@@ -255,7 +259,8 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
     const int quarter = warp & 3, grp = (warp - 2) >> 2, chalf = grp & 1, par = grp >> 1;  // par < kPar
     const int row = quarter * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-    for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (int it = 0; it < cnt; ++it) {
+      const int tile = entry(it);
       const uint32_t ph = (uint32_t)(it & 1);
       const float* sb1 = reinterpret_cast<const float*>(smem + oBW);
       const float* sw2 = sb1 + 256;
@@ -433,9 +438,10 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   } else {
     // ------------------------------------------------------------------ store warp
     if (elect_one()) {
-      if ((int)blockIdx.x < n_tiles) load_bw(blockIdx.x);
+      if (cnt > 0) load_bw(entry(0));
       int ntr = 0;
-      for (int it = 0, tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      for (int it = 0; it < cnt; ++it) {
+        const int tile = entry(it);
         const uint32_t ph = (uint32_t)(it & 1);
         int agent, s, half;
         const uint8_t *wnet, *ximg;
@@ -455,7 +461,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
           asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); mbar_arrive(bar(H1_OUT + 3));
         }
         mbar_wait(bar(EPI1_DONE), ph);
-        if (tile + (int)gridDim.x < n_tiles) load_bw(tile + gridDim.x);
+        if (it + 1 < cnt) load_bw(entry(it + 1));
         if (t >= 0) {
           uint8_t* h2 = P.h2 + ((int64_t)agent * kTrain + t) * P.h_bytes;
           for (int cb = 0; cb < 4; ++cb) {
@@ -474,7 +480,68 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   }
   tc_fence_before();
   __syncthreads();
+#ifndef IQLB_NO_TIMELINE
+  if (P.dbg != nullptr && tid == 0 && blockIdx.x < 148) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    P.dbg[7700 + blockIdx.x * 2 + 1] = gt;
+  }
+#endif
   if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host-built schedule.  Tiles are not equal: per-tile clock64 stamps (scripts/timeline.py) give ~6 k clocks for the three
+// streams that keep nothing (next-state V, the two target Qs), ~9.5 k for V / Q1 / Q2 (H1 / H2 tiles and masks leave for the
+// backward pass) and ~11.6 k for the actor (8 heads; more with 24 heads and dropout masks).  896 tiles dealt round-robin give
+// every CTA six or seven of mixed cost (CTA ends 25-35 us); here they are sorted by cost and each goes to the least-loaded CTA.
+// ------------------------------------------------------------------------------------------------
+struct FwdSchedule {
+  int dev = -1, n_agents = 0, n_sm = 0, A = 0, drop = 0, grid = 0;
+  int32_t *d_off = nullptr, *d_list = nullptr;
+};
+
+static int fwd_schedule(int n_agents, int n_sm, int A, bool wide, bool drop, const FwdSchedule** out) {
+  static std::vector<FwdSchedule> cache;  // (a handful of shapes per process; entries live until exit)
+  int dev = 0;
+  IQLB_CUDA(cudaGetDevice(&dev));
+  for (const FwdSchedule& c : cache)
+    if (c.dev == dev && c.n_agents == n_agents && c.n_sm == n_sm && c.A == A && c.drop == (int)drop) { *out = &c; return IQLB_OK; }
+  const int n_tiles = n_agents * kStreams * 2;
+  const int G = n_tiles < n_sm ? n_tiles : n_sm;
+  const double c_keep = 9.5, c_none = 6.0;
+  const double c_actor = wide ? 9.5 + 2.0 * ((A + 7) / 8) + (drop ? 10.0 : 0.0) : 11.6;
+  auto cost = [&](int s) { return s == 6 ? c_actor : (train_index(s) >= 0 ? c_keep : c_none); };
+  std::vector<int32_t> order;
+  for (int cls = 0; cls < 3; ++cls)  // actor, then the streams that keep activations, then the rest; natural order inside a class
+    for (int r = 0; r < n_agents; ++r)
+      for (int s = 0; s < kStreams; ++s) {
+        const int c = s == 6 ? 0 : (train_index(s) >= 0 ? 1 : 2);
+        if (c != cls) continue;
+        for (int h = 0; h < 2; ++h) order.push_back((int32_t)(r << 4 | s << 1 | h));
+      }
+  std::vector<double> load(G, 0.0);
+  std::vector<std::vector<int32_t>> lists(G);
+  for (int32_t e : order) {
+    int b = 0;
+    for (int i = 1; i < G; ++i) if (load[i] < load[b]) b = i;
+    lists[b].push_back(e);
+    load[b] += cost((e >> 1) & 7);
+  }
+  std::vector<int32_t> off(G + 1, 0), flat;
+  for (int i = 0; i < G; ++i) {
+    off[i + 1] = off[i] + (int32_t)lists[i].size();
+    flat.insert(flat.end(), lists[i].begin(), lists[i].end());
+  }
+  FwdSchedule sc;
+  sc.dev = dev; sc.n_agents = n_agents; sc.n_sm = n_sm; sc.A = A; sc.drop = (int)drop; sc.grid = G;
+  IQLB_CUDA(cudaMalloc((void**)&sc.d_off, off.size() * sizeof(int32_t)));
+  IQLB_CUDA(cudaMalloc((void**)&sc.d_list, flat.size() * sizeof(int32_t)));
+  IQLB_CUDA(cudaMemcpy(sc.d_off, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  IQLB_CUDA(cudaMemcpy(sc.d_list, flat.data(), flat.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  cache.push_back(sc);
+  *out = &cache.back();
+  return IQLB_OK;
 }
 
 template <bool kWide>
@@ -490,10 +557,12 @@ static int persist_launch(const BfParams& P, const float* params, const float* t
     IQLB_CUDA(cudaFuncSetAttribute(bf16_fwd_persist_kernel<kWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  const int n_tiles = n_agents * kStreams * (P.L.B / 128);
-  const int grid = n_tiles < n_sm ? n_tiles : n_sm;
-  IQLB_CUDA(launch_pdl(bf16_fwd_persist_kernel<kWide>, dim3(grid), dim3(fwdp::kThreads), smem, stream, pdl, P, params, target,
-                       head_out, n_tiles));
+  IQLB_REQUIRE(P.L.B == 256, "forward kernel: batch 256 (two 128-row tiles per stream)");
+  const FwdSchedule* sc = nullptr;
+  const int rc = fwd_schedule(n_agents, n_sm, P.L.A, kWide, P.drop_thresh != 0, &sc);
+  if (rc) return rc;
+  IQLB_CUDA(launch_pdl(bf16_fwd_persist_kernel<kWide>, dim3(sc->grid), dim3(fwdp::kThreads), smem, stream, pdl, P, params, target,
+                       head_out, n_agents, (const int32_t*)sc->d_off, (const int32_t*)sc->d_list));
   return IQLB_OK;
 }
 

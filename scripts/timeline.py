@@ -39,6 +39,14 @@ l = ts[3072:3072 + 8]
 if l[0]:
     print("loss CTA 0: " + ", ".join(f"{n}={int(x - l[0])}" for n, x in zip(["start", "loads done", "loop done", "sync", "sums written", "scalars start", "scalars end"], l) if x))
 
+fw = ts[7700:7700 + 296].reshape(148, 2)
+if fw[:, 1].any():
+    t0 = int(fw[:, 0][fw[:, 0] > 0].min())
+    dur = [(int(b_) - t0) for a_, b_ in fw if b_]
+    st = [(int(a_) - t0) for a_, b_ in fw if a_]
+    import numpy as _np
+    print(f"forward CTAs (global timer, ns from the first start): starts {min(st)}..{max(st)}, ends min {min(dur)} median "
+          f"{int(_np.median(dur))} max {max(dur)}; ends by CTA index (every 8th): " + " ".join(str(int(fw[i, 1]) - t0) for i in range(0, 148, 8)))
 w = ts[3200:3200 + 128]
 if w.any():
     print("bwd_weight CTA 0, clocks from the first stamp; per tile: issuer [tile start, P1 operands in, prev dW1 drained, P1 MMAs done, "

@@ -461,6 +461,28 @@ def bench_trainers(dev):
     ms = min(time_gpu(fm, 20, dev) for _ in range(2))
     out["mr_train"] = {"ms_per_step": ms, "steps_per_s": 1e3 / ms, "pairs": 256, "segment_len": 100, "precision": "split_bf16",
                        "note": "MRTrainer.train(sync=False), RewardMLP(37, 1, [128]*3, relu)"}
+    # MRTrainerF: the same step + the functional GP prior of an LCF model at 256 measurement points (d = 6 concepts)
+    from iqlpref_b200.gp_prior import LCFModel
+    from iqlpref_b200.mr_training import MRTrainerF
+    torch.manual_seed(0)
+    mlp_f = RewardMLP(S_DIM + A_DIM, 1, [128, 128, 128], "relu")
+
+    def feats(X, device):  # the caller's feature map (function_vect): intercept, two inputs and three bounded non-linear columns
+        X = X.double()
+        return torch.stack([torch.ones_like(X[:, 0]), X[:, 0], X[:, 1], torch.tanh(X[:, 2]), torch.sin(X[:, 0] * X[:, 1]),
+                            X[:, -1] ** 2], dim=1)
+    prior = LCFModel(np.ones(6, np.float32), feats, dev)
+    mrf = MRTrainerF(mlp_f, torch.optim.Adam(mlp_f.parameters(), lr=3e-4), 25600, prior, device=dev, precision="split_bf16")
+    xm = torch.randn((256, S_DIM + A_DIM), device=dev)
+    ff = lambda: mrf.train(mb, xm, sync=False)
+    for _ in range(3):
+        ff()
+    ms = min(time_gpu(ff, 20, dev) for _ in range(2))
+    out["mrf_train"] = {"ms_per_step": ms, "steps_per_s": 1e3 / ms, "pairs": 256, "segment_len": 100, "n_meas": 256, "n_concepts": 6,
+                        "precision": "split_bf16",
+                        "note": "MRTrainerF.train(sync=False): the MR step with 256 measurement points as extra rows, the d x d "
+                                "Woodbury system in fp64 on the device, log p_GP at the updated weights; Phi(X_M) by a torch "
+                                "callable on the device (the reference's function_vect is user code)"}
     return out
 
 

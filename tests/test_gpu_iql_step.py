@@ -428,12 +428,15 @@ def test_agents_are_bit_identical_however_they_are_sharded(precision):
                 assert torch.equal(getattr(e, name), getattr(e_all, name)[ids]), (precision, ids, name)
 
 
-def test_wide_shape_agents_are_bit_identical_across_tile_schedules():
-    """The pen / adroit shape (two input blocks, 24 actions, actor dropout) on the persistent forward kernel: 24 agents are
-    336 forward tiles, more than one round over the SMs, with the actor tiles dealt first; 8-agent engines and a 5 + 19
-    split schedule the same tiles on other CTAs in other rounds.  Every agent must come out bit for bit the same."""
+@pytest.mark.parametrize("S,A,drop", [(45, 24, 0.1), (29, 8, None)])
+def test_agents_are_bit_identical_across_tile_schedules_and_kernels(S, A, drop):
+    """24 agents are 336 forward tiles and 192 data-gradient half-tiles, more than one round over the SMs: the host-built
+    schedules deal them by cost, and the data gradients run on the persistent kernel (more half-tiles than SMs).  8-agent
+    engines and a 5 + 19 split schedule the same tiles on other CTAs in other rounds, the small ones on the one-tile-per-CTA
+    data-gradient kernel.  Every agent must come out bit for bit the same - for the pen / adroit shape (two input blocks,
+    24 actions, actor dropout: the wide forward instantiation) and for the antmaze shape (narrow)."""
     from iqlpref_b200 import iql as biql
-    S, A, N, K = 45, 24, 24, 3
+    N, K = 24, 3
     buf = biql.ReplayBuffer(S, A, 5000)
     g = torch.Generator(device="cuda").manual_seed(9)
     buf._table[:, :2 * S + A + 2] = torch.randn((5000, 2 * S + A + 2), generator=g, device="cuda")
@@ -443,12 +446,12 @@ def test_wide_shape_agents_are_bit_identical_across_tile_schedules():
 
     def run(agent_ids):
         n = len(agent_ids)
-        eng = biql.BatchedIQL(S, A, n, batch_size=256, precision="bf16", actor_dropout=0.1,
+        eng = biql.BatchedIQL(S, A, n, batch_size=256, precision="bf16", actor_dropout=drop,
                               hparams=[dict(max_steps=100, beta=3.0 + 0.1 * a) for a in agent_ids],
                               seeds=[21 + a for a in agent_ids])
         for j, a in enumerate(agent_ids):
             torch.manual_seed(70 + a)
-            eng.adopt(j, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0, dropout=0.1), bind=False)
+            eng.adopt(j, biql.TwinQ(S, A), biql.ValueFunction(S), biql.GaussianPolicy(S, A, 1.0, dropout=drop), bind=False)
         eng.attach_replay(buf)
         trace = []
         for _ in range(K):

@@ -1,5 +1,6 @@
 #!/bin/bash
 # wide persistent forward kernel (KXB = 2, action_dim <= 24, actor dropout): parity, then A/B against the non-persistent kernel
+# (historical: IQLB_FWD_PERSIST=0 selected the one-tile-per-CTA forward kernel, removed after this A/B - profiles/r02f_fwd_wide_ab.jsonl)
 mkdir -p gpurun_out; cd /root/repo
 timeout 900 python -m pytest tests/test_gpu_bf16_step.py tests/test_gpu_iql_step.py -x -q -m gpu 2>&1 | tail -5
 for i in 1 2; do

@@ -18,4 +18,3 @@ PY
 }
 run base IQLB_X=0
 run groups2 IQLB_GROUPS=2
-run oldfwd IQLB_FWD_PERSIST=0

@@ -779,7 +779,12 @@ extern "C" int iqlb_agents_create(const iqlb_agents_desc* d, float* params, floa
   h->zig = (getenv("IQLB_ZIGZAG") && atoi(getenv("IQLB_ZIGZAG")) == 0) ? -1 : 0;
   // measured on B200 (64 agents): 268.7 vs 269.1 us per step - the forward kernel loses its programmatic overlap
   // with the optimizer's tail to the cross-stream join, which eats what the hidden gather saves.  Off by default.
-  // look-ahead sampling: the next step's gather on a side stream under the optimizer kernel (measured neutral, off)
+  // look-ahead sampling: the next step's gather on a side stream under the optimizer kernel.  Measured at the end of round 2:
+  // slower with 64 agents (228.3 vs 225.2 us per step: the optimizer is HBM-bound and the forward kernel loses its programmatic
+  // overlap with the optimizer's tail to the cross-stream join), faster with 8 (58.1 vs 59.6 us: the optimizer's 34 MB sit in
+  // L2 and every kernel is a partial wave).  Opt-in (IQLB_PRESAMPLE=1) at any size: the look-ahead batch is gathered one
+  // call early, so a caller that rewrites rows of the attached table in place between two steps would train on the old
+  // rows - iqlb_agents_set_replay and every state-changing entry point drop it, an in-place write cannot be seen.
   h->presample = (getenv("IQLB_PRESAMPLE") && atoi(getenv("IQLB_PRESAMPLE")) != 0) ? 1 : 0;
   if (!rc && d->precision == 1) {
     const char* env = getenv("IQLB_GROUPS");

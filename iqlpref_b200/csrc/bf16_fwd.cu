@@ -522,11 +522,22 @@ static int fwd_schedule(int n_agents, int n_sm, int A, bool wide, bool drop, con
       }
   std::vector<double> load(G, 0.0);
   std::vector<std::vector<int32_t>> lists(G);
-  for (int32_t e : order) {
-    int b = 0;
-    for (int i = 1; i < G; ++i) if (load[i] < load[b]) b = i;
-    lists[b].push_back(e);
-    load[b] += cost((e >> 1) & 7);
+  if (wide) {
+    for (int32_t e : order) {
+      int b = 0;
+      for (int i = 1; i < G; ++i) if (load[i] < load[b]) b = i;
+      lists[b].push_back(e);
+      load[b] += cost((e >> 1) & 7);
+    }
+  } else {
+    // Narrow shapes: natural (agent, stream, half) order dealt round-robin.  The cost-sorted deal evens the CTA end times
+    // (25-35 us -> 29-35 us) without shortening the kernel - it is bound by L2 <-> SM traffic, DESIGN.md section 4 - and reads
+    // 110 MB instead of 91 MB from DRAM per launch (profiles/r02j vs r02g): tiles of one agent no longer run together, so
+    // fewer of its weight images are found in L2 by the second half batch.
+    int i = 0;
+    for (int r = 0; r < n_agents; ++r)
+      for (int s = 0; s < kStreams; ++s)
+        for (int h = 0; h < 2; ++h, ++i) lists[i % G].push_back((int32_t)(r << 4 | s << 1 | h));
   }
   std::vector<int32_t> off(G + 1, 0), flat;
   for (int i = 0; i < G; ++i) {

@@ -613,7 +613,7 @@ def kernel_roofline(prof, n_agents, peaks):
             top = e
     roof = {"bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"],
             "frac": top["frac"], "traffic": ncu_traffic(top["kernel"]), "kernel": top["kernel"], "peak_source": peaks["source"],
-            "traffic_source": "profiles/r02j_bf16_ncu_full.json (dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+            "traffic_source": "profiles/r02k_bf16_ncu_full.json (dram__bytes_read.sum + dram__bytes_write.sum per launch, "
                               "64 agents)",
             "algorithmic_per_launch": work.get(top["kernel"], ("", 0))[1] * n_agents,
             "algorithmic_definition": "SURVEY 8(d): 24 B/param (p, m, v read + write) + 8 B/target param (Polyak read + "
@@ -631,7 +631,7 @@ NCU_NAMES = {"adam_polyak_shadow": "adam_polyak_kernel", "adam_polyak": "adam_po
 def ncu_traffic(kernel):
     """DRAM bytes per launch (read + write) of `kernel` from the committed `ncu --set full` capture, or None."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r02j_bf16_ncu_full.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02k_bf16_ncu_full.json")) as f:
             prof = json.load(f)
         want = NCU_NAMES.get(kernel, kernel)
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}

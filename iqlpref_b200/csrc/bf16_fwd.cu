@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(fwdp::kThreads, 1) bf16_fwd_persist_kernel(BfP
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const bool dbg = P.dbg != nullptr && blockIdx.x == 0;
+  [[maybe_unused]] const bool dbg = P.dbg != nullptr && blockIdx.x == 0;
   // 64-column blocks of a stream's input image (wide: the Q streams read state | action, the others the state alone)
   auto x_blocks = [&](int in) -> int { return kWide ? (in + 63) >> 6 : 1; };
 #ifdef IQLB_NO_TIMELINE

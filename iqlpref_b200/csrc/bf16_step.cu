@@ -142,7 +142,7 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   // actor dropout: both hidden layers' gradients pass through a kept-and-scaled mask (the stored bit masks already are
   // relu' AND keep); exactly 1 when dropout is off
   const float gscale = (t == 3 && P.drop_thresh != 0) ? P.drop_scale : 1.0f;
-  const bool dbgd = P.dbg != nullptr && half == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
+  [[maybe_unused]] const bool dbgd = P.dbg != nullptr && half == 0 && t == 1 && aidx == P.dbg_z && tid == 64;
 #ifdef IQLB_NO_TIMELINE
 #define IQLB_TSD(slot) do { } while (0)
 #else
@@ -172,7 +172,6 @@ __device__ __forceinline__ void bwd_data_body(const BfParams& P, const float* __
   if (worker)
     for (int i = tid; i < nout * 256; i += kBdWorkerThreads) sw2[i] = __ldg(fnet + L.w2(in) + i);
   const int row = quarter * 32 + lane, brow = half * 128 + row;
-  const int cbeg = cgrp * 64;
   // this thread's 16 columns of K-block kb of the dH2 tile: bits (cgrp & 1) * 16 .. + 15 of mask word 2 kb + cgrp / 2
   const uint32_t* m2p = P.mask2 + (at * L.B + brow) * (L.H / 32);
   uint64_t m2h = 0;

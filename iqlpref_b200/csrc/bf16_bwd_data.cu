@@ -4,7 +4,8 @@
 // Both tiles go to HBM as bf16 images for the weight-gradient kernel (ImplicitQLearning.train's loss.backward(),
 // /root/reference/algorithms/offline/iql.py:581-637).
 //
-// One CTA per SM walks UNITS = (agent, trainable net); a unit is the two 128-row half batches that share one W1 image:
+// One CTA per SM walks a host-built list of half-tiles (bd_schedule below); the two 128-row half batches of a UNIT =
+// (agent, trainable net) share one W1 image and are adjacent in a CTA's list whenever the schedule can keep them together:
 //   * W1 (128 KB) is loaded once per unit instead of once per half batch, and the next unit's W1 is requested as soon as
 //     the last MMA of the current one has completed - under the drain and the next unit's dH2 production - instead of at
 //     the head of a new CTA (where it cost ~3 us of a ~9 us CTA, plus the 1.2 us exit / launch gap);
@@ -14,8 +15,8 @@
 //   * the dH1 tile is staged in the A-tile region (free once the MMAs and the dH2 store have read it) and leaves as bulk
 //     stores; the next dH2 K-block is written as soon as the store of the dH1 block in its place has been read.  (Stores
 //     straight from registers - 32 lanes x 16 bytes to 32 different lines per instruction - cost 5.6 k clocks per half-tile.)
-//   * actor units (out_dim 8-24 columns of dz per row against one for V / Q) are dealt first and to the CTAs that take
-//     part in fewer rounds.
+//   * half-tiles are dealt by cost (the actor's dH2 has out_dim = 8-24 columns of dz per row against one for V / Q),
+//     heaviest first, each to the least-loaded CTA.
 //   warps 0-15  workers: 4 per TMEM lane quarter; drain of the previous half, then dH2 K-block by K-block
 //   warp 16     one elected thread: W1 loads, dH2 / dH1 bulk stores and every MMA issue
 #include <vector>
